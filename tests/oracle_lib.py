@@ -1,0 +1,226 @@
+"""ctypes bindings to the CPU checkers under oracle/ (test infrastructure only).
+
+OraclePort  -> oracle/_build/liborbport.so  (our restatement, always buildable)
+OracleRef   -> oracle/_ref/liborbref.so     (the unmodified reference extractor; built in the dev
+                                             container where /root/reference exists, travels prebuilt)
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE = os.path.join(ROOT, "oracle")
+PORT_SO = os.path.join(ORACLE, "_build", "liborbport.so")
+REF_SO = os.path.join(ORACLE, "_ref", "liborbref.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-f", os.path.join(ORACLE, "Makefile"), "all"], check=True)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _i32(n):
+    return np.zeros(max(n, 1), np.int32)
+
+
+class OraclePort:
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        if not os.path.exists(PORT_SO):
+            build_oracle()
+        L = self.L = C.CDLL(PORT_SO)
+        L.orbport_create.restype = C.c_void_p
+        L.orbport_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orbport_destroy.argtypes = [C.c_void_p]
+        L.orbport_tables.argtypes = [C.c_void_p] * 4
+        L.orbport_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
+                                      C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.orbport_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.orbport_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orbport_level_pixels.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        L.orbport_level_blurred.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        for f in (L.orbport_level_candidates, L.orbport_level_selected):
+            f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbport_octree.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_void_p, C.c_int]
+        L.orbport_hamming256.argtypes = [C.c_void_p, C.c_void_p]
+        L.orbport_match_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                               C.c_void_p, C.c_void_p]
+        L.orbport_match_count.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float]
+        self.nlevels = nlevels
+        self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orbport_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        s4 = np.zeros(4 * self.nlevels, np.float32)
+        feats = _i32(self.nlevels)
+        umax = _i32(16)
+        self.L.orbport_tables(self.h, _ptr(s4), _ptr(feats), _ptr(umax))
+        return s4.reshape(4, self.nlevels), feats, umax
+
+    def extract(self, img, cap=None):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        cap = cap or 65536
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        rc = self.L.orbport_extract(self.h, _ptr(img), w, h, img.strides[0], _ptr(kps), _ptr(desc), cap, C.byref(n))
+        if rc != 0:
+            raise RuntimeError("orbport_extract rc=%d n=%d" % (rc, n.value))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def pyramid(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        self.L.orbport_pyramid(self.h, _ptr(img), img.shape[1], img.shape[0], img.strides[0])
+        return [self.level_pixels(l) for l in range(self.nlevels)]
+
+    def level_size(self, l):
+        w, h = C.c_int(), C.c_int()
+        self.L.orbport_level_size(self.h, l, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level_pixels(self, l, blurred=False):
+        w, h = self.level_size(l)
+        out = np.zeros((h, w), np.uint8)
+        f = self.L.orbport_level_blurred if blurred else self.L.orbport_level_pixels
+        rc = f(self.h, l, _ptr(out), w)
+        return out if rc == 0 else None
+
+    def _cands(self, f, l):
+        cap = 1 << 20
+        x, y, s = _i32(cap), _i32(cap), _i32(cap)
+        n = f(self.h, l, _ptr(x), _ptr(y), _ptr(s), cap)
+        return np.stack([x[:n], y[:n], s[:n]], 1)
+
+    def level_candidates(self, l):
+        return self._cands(self.L.orbport_level_candidates, l)
+
+    def level_selected(self, l):
+        return self._cands(self.L.orbport_level_selected, l)
+
+    def octree(self, xs, ys, resp, W, H, N):
+        xs = np.ascontiguousarray(xs, np.int32); ys = np.ascontiguousarray(ys, np.int32)
+        resp = np.ascontiguousarray(resp, np.int32)
+        out = _i32(len(xs) + 8)
+        n = self.L.orbport_octree(_ptr(xs), _ptr(ys), _ptr(resp), len(xs), W, H, N, _ptr(out), len(out))
+        if n < 0:
+            raise RuntimeError("orbport_octree rc=%d" % n)
+        return out[:n].copy()
+
+    def hamming(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return self.L.orbport_hamming256(_ptr(a), _ptr(b))
+
+    def match_bruteforce(self, A, B):
+        A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)
+        bi = np.zeros(len(A), np.int32); b1 = np.zeros(len(A), np.uint16); b2 = np.zeros(len(A), np.uint16)
+        self.L.orbport_match_bruteforce(_ptr(A), len(A), _ptr(B), len(B), _ptr(bi), _ptr(b1), _ptr(b2))
+        return bi, b1, b2
+
+    def match_count(self, A, B, th_low=50, ratio=0.6):
+        A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)
+        return self.L.orbport_match_count(_ptr(A), len(A), _ptr(B), len(B), th_low, ratio)
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+class OracleRef:
+    """The unmodified reference ORBextractor (src/ORBextractor.cc) behind a C wrapper."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        L = self.L = C.CDLL(REF_SO)
+        L.orbref_create.restype = C.c_void_p
+        L.orbref_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orbref_destroy.argtypes = [C.c_void_p]
+        L.orbref_tables.argtypes = [C.c_void_p] * 4
+        L.orbref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p,
+                                     C.c_int, C.POINTER(C.c_int), C.c_int]
+        L.orbref_compute_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.orbref_pyramid_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_int),
+                                           C.POINTER(C.c_int)]
+        L.orbref_pyramid_level_bordered.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        L.orbref_octree.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.orbref_bench.restype = C.c_double
+        L.orbref_bench.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_float, C.c_int,
+                                   C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_long)]
+        self.params = (nfeatures, scale, nlevels, ini_th, min_th)
+        self.nlevels = nlevels
+        self.h = L.orbref_create(nfeatures, scale, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orbref_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        s4 = np.zeros(4 * self.nlevels, np.float32)
+        feats = _i32(self.nlevels)
+        umax = _i32(16)
+        self.L.orbref_tables(self.h, _ptr(s4), _ptr(feats), _ptr(umax))
+        return s4.reshape(4, self.nlevels), feats, umax
+
+    def extract(self, img, arena_mode=1, cap=65536):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        rc = self.L.orbref_extract(self.h, _ptr(img), w, h, img.strides[0], _ptr(kps), _ptr(desc), cap,
+                                   C.byref(n), arena_mode)
+        if rc != 0:
+            raise RuntimeError("orbref_extract rc=%d" % rc)
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def pyramid(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        self.L.orbref_compute_pyramid(self.h, _ptr(img), img.shape[1], img.shape[0], img.strides[0])
+        out = []
+        for l in range(self.nlevels):
+            w, h = C.c_int(), C.c_int()
+            self.L.orbref_pyramid_level(self.h, l, None, 0, C.byref(w), C.byref(h))
+            a = np.zeros((h.value, w.value), np.uint8)
+            self.L.orbref_pyramid_level(self.h, l, _ptr(a), w.value, C.byref(w), C.byref(h))
+            out.append(a)
+        return out
+
+    def pyramid_level_bordered(self, l, w, h):
+        a = np.zeros((h + 38, w + 38), np.uint8)
+        self.L.orbref_pyramid_level_bordered(self.h, l, _ptr(a), w + 38)
+        return a
+
+    def octree(self, xs, ys, resp, W, H, N, arena_mode=1):
+        """Returns (x, y, response) rows of the selected keys, in result order."""
+        xs = np.ascontiguousarray(xs, np.float32); ys = np.ascontiguousarray(ys, np.float32)
+        resp = np.ascontiguousarray(resp, np.float32)
+        cap = len(xs) + 8
+        ox, oy, orr = np.zeros(cap, np.float32), np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+        n = self.L.orbref_octree(self.h, _ptr(xs), _ptr(ys), _ptr(resp), len(xs), 0, W, 0, H, N,
+                                 _ptr(ox), _ptr(oy), _ptr(orr), cap, arena_mode)
+        if n < 0:
+            raise RuntimeError("orbref_octree rc=%d" % n)
+        return np.stack([ox[:n], oy[:n], orr[:n]], 1)
+
+    def bench(self, frames, threads, reps=1):
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape
+        tot = C.c_long(0)
+        nf, sc, nl, ini, mn = self.params
+        sec = self.L.orbref_bench(_ptr(frames), n, w, h, frames.strides[0], nf, sc, nl, ini, mn, threads, reps,
+                                  C.byref(tot))
+        return sec, tot.value
