@@ -1,0 +1,165 @@
+/* orbgpu.h -- C ABI of the B200-native ORB front end (drop-in boundary).
+ *
+ * The reference has no FFI layer on this path: the boundary is the C++ surface of two classes.
+ * Each entry point below names the reference interface it stands behind (paths relative to the
+ * reference tree).  The C++ drop-in classes in my-slam_b200/host/ (ORB_SLAM2::ORBextractor,
+ * ORB_SLAM2::ORBmatcher, same signatures as include/ORBextractor.h:45-111 and
+ * include/ORBmatcher.h:37-102) are thin wrappers over these calls; INTEGRATION.md shows the binding.
+ *
+ * Conventions: plain C types only; the caller owns every host buffer passed in or out; the library
+ * owns device and pinned memory; every call returns 0 (ORBGPU_OK) or a negative error code, never
+ * throws and never exits; one call in flight per extractor handle (the reference extractor is not
+ * re-entrant either: it mutates mvImagePyramid, src/ORBextractor.cc:1117), distinct handles may be
+ * used concurrently from different threads (src/Frame.cc:78-81).  There is no CPU fallback: without a
+ * CUDA device every compute call fails with ORBGPU_ERR_CUDA.
+ */
+#ifndef ORBGPU_H
+#define ORBGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBGPU_OK                0
+#define ORBGPU_ERR_ARG          -1   /* null pointer, bad size, bad level ...                       */
+#define ORBGPU_ERR_CAPACITY     -2   /* caller's output capacity < orbgpu_max_keypoints()           */
+#define ORBGPU_ERR_CUDA         -3   /* CUDA runtime/driver error (orbgpu_last_cuda_error())        */
+#define ORBGPU_ERR_NOMEM        -4
+#define ORBGPU_ERR_UNSUPPORTED  -5   /* image shape / parameters outside the supported envelope     */
+#define ORBGPU_ERR_STATE        -6   /* ticket unknown, queue full, nothing extracted yet ...       */
+
+#define ORBGPU_MAX_LEVELS 16
+
+typedef struct orbgpu_extractor orbgpu_extractor;   /* opaque: streams, device + pinned buffers     */
+typedef struct orbgpu_matcher orbgpu_matcher;       /* opaque: resident descriptor sets            */
+
+/* == cv::KeyPoint (28-byte POD) as filled by the reference: include/ORBextractor.h:39,60;
+ * field values per src/ORBextractor.cc:842-849 (octave, size), :479 (angle), :1097-1103 (pt*=scale) */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbgpu_keypoint;
+
+/* ---- extractor ----------------------------------------------------------------------------- */
+
+/* ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * include/ORBextractor.h:51-52, src/ORBextractor.cc:412-472.  Builds the scale / features-per-level /
+ * umax / pattern tables on the host with the reference's float-double mix and uploads them. */
+int orbgpu_create(orbgpu_extractor** out, int device, int nfeatures, float scale_factor, int nlevels,
+                  int ini_th_fast, int min_th_fast);
+void orbgpu_destroy(orbgpu_extractor* e);
+
+/* Getters GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares / GetInverseScaleSigmaSquares
+ * (include/ORBextractor.h:63-83): scale4 = [scale | 1/scale | sigma^2 | 1/sigma^2], nlevels floats each;
+ * features_per_level[nlevels]; umax[16].  Any pointer may be NULL.  Returns nlevels. */
+int orbgpu_get_tables(orbgpu_extractor* e, float* scale4, int* features_per_level, int* umax);
+
+/* Upper bound of keypoints per frame for this shape (sum over levels of max(N_l, 4*nIni_l) + 3;
+ * the reference can return N_l + 2 per level, src/ORBextractor.cc:730-733).  Negative = error code. */
+int orbgpu_max_keypoints(orbgpu_extractor* e, int w, int h);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors), include/ORBextractor.h:59-61,
+ * src/ORBextractor.cc:1045-1107.  Synchronous, one frame: img is CV_8UC1 with row stride `stride`
+ * bytes (host memory); kps[capacity], desc[capacity*32].  The mask of the reference is ignored there
+ * and absent here.  w==0 || h==0 || img==NULL -> returns ORBGPU_OK with *n_out = -1 and outputs
+ * untouched (the reference's silent return on an empty image, :1048-1049). */
+int orbgpu_extract(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride,
+                   orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
+
+/* Same operator over n same-shape frames (frame i at frames + i*frame_stride, rows row_stride apart),
+ * host buffers; H2D copy, kernels and D2H copy of successive chunks overlap on internal streams.
+ * Output for frame i: kps + i*capacity, desc + i*capacity*32, n_out[i].  Pinned (cudaHostAlloc /
+ * cudaHostRegister) caller buffers are used in place; pageable ones are staged through the
+ * library's pinned ring. */
+int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h,
+                         size_t row_stride, size_t frame_stride,
+                         orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
+
+/* Same, with every buffer already resident in device memory (frames, kps, desc, n_out are device
+ * pointers of this extractor's device).  Returns after the work has completed. */
+int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, int n, int w, int h,
+                                size_t row_stride, size_t frame_stride,
+                                orbgpu_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out);
+
+/* The pinned-memory frame queue for Frame construction (north_star): submit copies the image into
+ * a pinned ring slot and enqueues upload + kernels + download without blocking; collect blocks on
+ * that frame only.  Frame::Frame (src/Frame.cc:174-228) or Tracking::GrabImage* one frame ahead
+ * submits; Frame::ExtractORB (src/Frame.cc:247-253) collects.  Tickets are collected in any order;
+ * at most orbgpu_queue_depth() tickets may be outstanding (else ORBGPU_ERR_STATE). */
+int orbgpu_submit(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride, uint64_t* ticket);
+int orbgpu_collect(orbgpu_extractor* e, uint64_t ticket, orbgpu_keypoint* kps, uint8_t* desc,
+                   int capacity, int* n_out);
+int orbgpu_queue_depth(orbgpu_extractor* e);
+
+/* std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:85; read by src/Frame.cc:473,563,575,580
+ * in stereo mode): level pixels of the most recent orbgpu_extract / orbgpu_collect'ed frame, copied to
+ * dst (dst may be NULL to query the size).  The 19-px REFLECT_101 frame of the reference's buffers is
+ * rebuilt on the host by the C++ wrapper. */
+int orbgpu_pyramid_level(orbgpu_extractor* e, int level, uint8_t* dst, size_t dst_stride, int* w, int* h);
+
+/* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
+ * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),
+ * FAST candidates in list order (:791-831) and octree survivors in list order (:541-765); x, y are
+ * relative to the (16,16) cell-grid origin as at :824-825.  Return the count or a negative code. */
+int orbgpu_debug_level_blurred(orbgpu_extractor* e, int level, uint8_t* dst, size_t dst_stride);
+int orbgpu_debug_level_candidates(orbgpu_extractor* e, int level, int* x, int* y, int* score, int cap);
+int orbgpu_debug_level_selected(orbgpu_extractor* e, int level, int* x, int* y, int* score, int cap);
+
+/* ORBextractor::DistributeOctTree (src/ORBextractor.cc:541-765) run by the octree kernel on an
+ * arbitrary candidate list (coordinates relative to the cell-grid origin, 0 <= x < W <= 4095,
+ * 0 <= y < H <= 4095, 0 <= resp <= 255); out_idx receives indices into the input list in result
+ * order.  Returns the count or a negative code. */
+int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* resp, int n,
+                  int W, int H, int N, int* out_idx, int cap);
+
+/* Profiling: with profiling on, CUDA events bracket every stage of each chunk on its stream.
+ * orbgpu_get_stage_ms returns accumulated milliseconds per stage since the last reset:
+ * [0] upload, [1] pyramid, [2] FAST cells, [3] octree, [4] blur, [5] orientation+descriptors,
+ * [6] download; launches = kernels launched by this handle since creation. */
+#define ORBGPU_NUM_STAGES 7
+int orbgpu_set_profiling(orbgpu_extractor* e, int on);
+int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset);
+uint64_t orbgpu_launch_count(orbgpu_extractor* e);
+
+/* ---- matcher ------------------------------------------------------------------------------- */
+
+/* ORBmatcher::DescriptorDistance(a, b), include/ORBmatcher.h:44, src/ORBmatcher.cc:1647-1663:
+ * Hamming distance of two 256-bit descriptors (host, hardware popcount). */
+int orbgpu_hamming256(const void* a, const void* b);
+
+/* The best / second-best scan shared by the Search* routines (canonical form
+ * src/ORBmatcher.cc:201-226): every row of A (nA x 32 B) against every row of B in index order,
+ * strict '<' updates, so ties keep the lowest index; best/second start at 256, best_idx at -1.
+ * Host buffers; device = CUDA ordinal. */
+int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t* B, int nB,
+                            int32_t* best_idx, uint16_t* best, uint16_t* second);
+
+/* All-pairs keyframe matching (BASELINE config 5).  A matcher holds K keyframes x n descriptors
+ * resident in HBM; pair p = (a[p], b[p]) yields counts[p] = number of rows of keyframe a whose best
+ * match in keyframe b passes best <= th_low && float(best) < ratio*float(second)
+ * (accept rule of src/ORBmatcher.cc:228-232 with TH_LOW, mfNNratio). */
+int orbgpu_matcher_create(orbgpu_matcher** out, int device);
+void orbgpu_matcher_destroy(orbgpu_matcher* m);
+int orbgpu_matcher_set_keyframes(orbgpu_matcher* m, const uint8_t* desc, int num_keyframes, int n_per_keyframe);
+int orbgpu_matcher_set_keyframes_device(orbgpu_matcher* m, const uint8_t* d_desc, int num_keyframes, int n_per_keyframe);
+int orbgpu_matcher_count_pairs(orbgpu_matcher* m, const int32_t* kf_a, const int32_t* kf_b, int num_pairs,
+                               int th_low, float ratio, int32_t* counts);
+/* device-resident variant: d_pairs = num_pairs x (a, b) int32 pairs, d_counts int32[num_pairs] */
+int orbgpu_matcher_count_pairs_device(orbgpu_matcher* m, const int32_t* d_pairs, int num_pairs,
+                                      int th_low, float ratio, int32_t* d_counts);
+/* milliseconds of the most recent count_pairs kernel (CUDA events on its stream) */
+double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m);
+
+/* ---- misc ---------------------------------------------------------------------------------- */
+const char* orbgpu_strerror(int code);
+const char* orbgpu_last_cuda_error(void);   /* thread-local text of the last CUDA failure */
+int orbgpu_device_count(void);              /* 0 when no CUDA device / driver */
+const char* orbgpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBGPU_H */

@@ -1,0 +1,9 @@
+"""orbgpu: B200-native ORB front end (pyramid, FAST + octree, IC_Angle, rBRIEF, Hamming matching).
+
+The product is the CUDA library liborbgpu.so (csrc/, C ABI in include/orbgpu.h) and the C++ drop-in
+classes in host/.  This package is the thin ctypes binding used by the tests and bench.py; the
+directory name has a hyphen, so import it through __graft_entry__.load_package() (module name
+`my_slam_b200`).
+"""
+from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path)  # noqa: F401
+from . import synth  # noqa: F401

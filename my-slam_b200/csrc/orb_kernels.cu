@@ -1,0 +1,751 @@
+// orb_kernels.cu -- hand-written CUDA kernels (sm_100a) of the ORB front end.
+//
+// Stage -> reference function it reproduces bit-for-bit (paths relative to the reference tree):
+//   k_resize_level   ORBextractor::ComputePyramid      src/ORBextractor.cc:1109-1137 (cv::resize INTER_LINEAR 8U)
+//   k_fast_cells     ComputeKeyPointsOctTree cell loop src/ORBextractor.cc:767-831   (cv::FAST 9/16 + NMS + fallback)
+//   k_octree         DistributeOctTree / DivideNode    src/ORBextractor.cc:483-765
+//   k_blur           GaussianBlur 7x7 sigma 2          src/ORBextractor.cc:1083-1088
+//   k_describe       IC_Angle + computeOrbDescriptor   src/ORBextractor.cc:79-149, 474-481, 1036-1043, 1097-1103
+// All of it is byte / integer work bound by on-chip bandwidth and issue rate, not a dense float
+// contraction: no tensor cores.  Float arithmetic that feeds rounding decisions uses explicit
+// __fmul_rn/__fadd_rn (no FMA contraction) and __float2int_rn (round-half-even == cvRound).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "orb_common.cuh"
+#include "orb_pattern.h"
+
+__constant__ int8_t c_pattern[1024];     // 512 (x,y) rBRIEF sample offsets
+__constant__ int c_umax[16];             // half-widths of the circular patch rows, src/ORBextractor.cc:456-471
+
+int orb_upload_constants(const int* umax16)
+{
+    if (cudaMemcpyToSymbol(c_pattern, ORB_PATTERN_XY, 1024) != cudaSuccess) return -1;
+    if (cudaMemcpyToSymbol(c_umax, umax16, 16 * sizeof(int)) != cudaSuccess) return -1;
+    return 0;
+}
+
+// =================================================================================================
+// Pyramid: level l from level l-1, OpenCV's fixed-point bilinear (11-bit weights; horizontal pass in
+// int32, vertical pass ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.  The per-axis tables
+// (source index, weights) are built on the host in double/float exactly as OpenCV does.
+// One thread = 4 horizontally adjacent output pixels = one aligned 32-bit store.
+// =================================================================================================
+__global__ void __launch_bounds__(256) k_resize_level(OrbPlanDev P, int l)
+{
+    const OrbLevel& D = P.lv[l];
+    const int frame = blockIdx.z;
+    const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int dy = blockIdx.y * 8 + threadIdx.y;
+    if (dx0 >= D.w || dy >= D.h) return;
+    const int sw = P.lv[l - 1].w, sh = P.lv[l - 1].h;
+    const uint8_t* __restrict__ src = orb_level_ptr(P, l - 1, frame);
+    const int sp = orb_level_pitch(P, l - 1);
+    uint8_t* __restrict__ dst = P.pyr + (long long)frame * P.pyr_frame_bytes + D.pyr_off;
+
+    const int sy = P.rs_ofs[D.yofs_off + dy];
+    const int b0 = P.rs_a[2 * (D.yofs_off + dy)], b1 = P.rs_a[2 * (D.yofs_off + dy) + 1];
+    const int y0 = min(max(sy, 0), sh - 1), y1 = min(max(sy + 1, 0), sh - 1);
+    const uint8_t* __restrict__ S0 = src + (long long)y0 * sp;
+    const uint8_t* __restrict__ S1 = src + (long long)y1 * sp;
+    uint32_t packed = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int dx = min(dx0 + i, D.w - 1);          // tail lanes recompute the last pixel (pitch is padded)
+        const int s = P.rs_ofs[D.xofs_off + dx];
+        const int a0 = P.rs_a[2 * (D.xofs_off + dx)], a1 = P.rs_a[2 * (D.xofs_off + dx) + 1];
+        const int s1 = min(s + 1, sw - 1);
+        const int h0 = S0[s] * a0 + S0[s1] * a1;
+        const int h1 = S1[s] * a0 + S1[s1] * a1;
+        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+        packed |= (uint32_t)(v & 0xFF) << (8 * i);
+    }
+    *reinterpret_cast<uint32_t*>(dst + (long long)dy * D.pitch + dx0) = packed;
+}
+
+int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
+{
+    int launches = 0;
+    for (int l = 1; l < P.nlevels; ++l) {
+        dim3 block(32, 8);
+        dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + 7) / 8, nframes);
+        k_resize_level<<<grid, block, 0, st>>>(P, l);
+        ++launches;
+    }
+    return launches;
+}
+
+// =================================================================================================
+// FAST-9/16 per 30-px cell with per-cell non-max suppression and the iniTh -> minTh fallback.
+// One warp owns one cell: the cell image (<= 59 x 59 bytes) is staged in shared memory, the arc
+// value V = max over the 16 arcs of 9 contiguous circle pixels of min(+-(v - p)) is evaluated for
+// every interior pixel with packed 16x2 three-input min/max (VIMNMX3, both polarities at once),
+// score = V-1 where V > min(iniTh, minTh).  NMS uses the cell-local score map (neighbours outside
+// the cell interior count as 0, as in cv::FAST on the cell sub-image).  Survivors are the strict
+// local maxima with score >= iniTh, or, if the cell has none, those with score >= minTh.  They
+// are written in row-major order (warp ballot + popc prefix) to the cell's slot area.
+// =================================================================================================
+#define FAST_TP 64            // shared-memory row pitch of the cell tile (max cell image width is 59)
+#define FAST_WARPS 8
+
+__device__ __forceinline__ int fast_arc_value(const uint8_t* c)
+{
+    // e_k = (v - p_k + 256) | (p_k - v + 256) << 16, built with one IMAD per circle pixel
+    const unsigned v = c[0];
+    const unsigned kv = v * (1u - 65536u) + 256u * 65537u;
+#define E(dx, dy) ((unsigned)c[(dy) * FAST_TP + (dx)] * 65535u + kv)
+    const unsigned e0 = E(0, 3), e1 = E(1, 3), e2 = E(2, 2), e3 = E(3, 1), e4 = E(3, 0), e5 = E(3, -1),
+                   e6 = E(2, -2), e7 = E(1, -3), e8 = E(0, -3), e9 = E(-1, -3), e10 = E(-2, -2),
+                   e11 = E(-3, -1), e12 = E(-3, 0), e13 = E(-3, 1), e14 = E(-2, 2), e15 = E(-1, 3);
+#undef E
+#define MN3(a, b, c) __vimin3_s16x2(a, b, c)
+#define MX3(a, b, c) __vimax3_s16x2(a, b, c)
+    // minima of 3 consecutive, then of 9 consecutive (3 + 3 + 3)
+    const unsigned t0 = MN3(e0, e1, e2), t1 = MN3(e1, e2, e3), t2 = MN3(e2, e3, e4), t3 = MN3(e3, e4, e5),
+                   t4 = MN3(e4, e5, e6), t5 = MN3(e5, e6, e7), t6 = MN3(e6, e7, e8), t7 = MN3(e7, e8, e9),
+                   t8 = MN3(e8, e9, e10), t9 = MN3(e9, e10, e11), t10 = MN3(e10, e11, e12),
+                   t11 = MN3(e11, e12, e13), t12 = MN3(e12, e13, e14), t13 = MN3(e13, e14, e15),
+                   t14 = MN3(e14, e15, e0), t15 = MN3(e15, e0, e1);
+    const unsigned n0 = MN3(t0, t3, t6), n1 = MN3(t1, t4, t7), n2 = MN3(t2, t5, t8), n3 = MN3(t3, t6, t9),
+                   n4 = MN3(t4, t7, t10), n5 = MN3(t5, t8, t11), n6 = MN3(t6, t9, t12), n7 = MN3(t7, t10, t13),
+                   n8 = MN3(t8, t11, t14), n9 = MN3(t9, t12, t15), n10 = MN3(t10, t13, t0),
+                   n11 = MN3(t11, t14, t1), n12 = MN3(t12, t15, t2), n13 = MN3(t13, t0, t3),
+                   n14 = MN3(t14, t1, t4), n15 = MN3(t15, t2, t5);
+    const unsigned a = MX3(n0, n1, n2), b = MX3(n3, n4, n5), d = MX3(n6, n7, n8), f = MX3(n9, n10, n11),
+                   g = MX3(n12, n13, n14);
+    const unsigned r = MX3(MX3(a, b, d), MX3(f, g, n15), n15);
+#undef MN3
+#undef MX3
+    const int lo = (int)(r & 0xFFFFu), hi = (int)(r >> 16);
+    return max(lo, hi) - 256;
+}
+
+__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, int tile_rows)
+{
+    extern __shared__ __align__(16) uint8_t fast_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cell_id = blockIdx.x * FAST_WARPS + warp;
+    const int frame = blockIdx.y;
+    if (cell_id >= P.ncells) return;
+    const OrbCell cell = P.cells[cell_id];
+    const int l = cell.level;
+    uint8_t* tile = fast_smem + (size_t)warp * 2 * FAST_TP * tile_rows;
+    uint8_t* smap = tile + FAST_TP * tile_rows;
+    const int cw = cell.cw, ch = cell.ch, iw = cw - 6, ih = ch - 6;
+    uint32_t* cnt_out = P.cellcnt + (long long)frame * P.ncells + cell_id;
+    if (iw <= 0 || ih <= 0) { if (lane == 0) *cnt_out = 0; return; }
+
+    // stage the cell image; zero the score map
+    const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame) + (long long)cell.ini_y * orb_level_pitch(P, l) + cell.ini_x;
+    const int pitch = orb_level_pitch(P, l);
+    for (int r = 0; r < ch; ++r) {
+        for (int c = lane; c < cw; c += 32) tile[r * FAST_TP + c] = __ldg(img + (long long)r * pitch + c);
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(smap);
+        const int n16 = FAST_TP * ch / 16;
+        for (int i = lane; i < n16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
+
+    const int tot = iw * ih;
+    const float inv_iw = 1.0f / (float)iw;
+    const int base_th = min(P.ini_th, P.min_th);
+    for (int idx = lane; idx < tot; idx += 32) {
+        const int y = __float2int_rd(((float)idx + 0.5f) * inv_iw), x = idx - y * iw;
+        const int V = fast_arc_value(tile + (y + 3) * FAST_TP + (x + 3));
+        if (V > base_th) smap[(y + 3) * FAST_TP + (x + 3)] = (uint8_t)(V - 1);
+    }
+    __syncwarp();
+
+    // strict 8-neighbour maxima -> F (flat, reusing the tile memory), and "any survivor at iniTh"
+    uint8_t* F = tile;
+    bool any_ini = false;
+    for (int idx = lane; idx < tot; idx += 32) {
+        const int y = __float2int_rd(((float)idx + 0.5f) * inv_iw), x = idx - y * iw;
+        const uint8_t* s = smap + (y + 3) * FAST_TP + (x + 3);
+        const int v = s[0];
+        int keep = 0;
+        if (v > 0) {
+            const int m = max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
+                              max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
+            keep = v > m ? v : 0;
+        }
+        F[idx] = (uint8_t)keep;
+        any_ini |= (keep > 0 && keep >= P.ini_th);
+    }
+    const int thr = __any_sync(0xffffffffu, any_ini) ? P.ini_th : P.min_th;
+    __syncwarp();
+
+    uint32_t* slot = P.slots + (long long)frame * P.slot_frame_words + P.lv[l].slot_off + cell.slot_off;
+    int cnt = 0;
+    for (int base = 0; base < tot; base += 32) {
+        const int idx = base + lane;
+        int f = 0, x = 0, y = 0;
+        if (idx < tot) {
+            f = F[idx];
+            y = __float2int_rd(((float)idx + 0.5f) * inv_iw); x = idx - y * iw;
+        }
+        const bool flag = f > 0 && f >= thr;
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
+        if (flag) {
+            const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+            if (pos < cell.cap) slot[pos] = ORB_PACK(x + cell.off_x, y + cell.off_y, f);
+        }
+        cnt += __popc(bal);
+    }
+    if (lane == 0) *cnt_out = (uint32_t)min(cnt, cell.cap);
+}
+
+int orb_fast_smem_bytes(int max_cw, int max_ch)
+{
+    if (max_cw > FAST_TP - 4) return -1;
+    return FAST_WARPS * 2 * FAST_TP * max_ch;
+}
+
+int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream_t st)
+{
+    static int configured = 0;
+    if (smem_bytes > configured) {
+        if (cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) return -1;
+        configured = smem_bytes;
+    }
+    dim3 grid((P.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes);
+    k_fast_cells<<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P, smem_bytes / (FAST_WARPS * 2 * FAST_TP));
+    return 1;
+}
+
+// =================================================================================================
+// DistributeOctTree as array passes; one CTA per (level, frame).
+//
+// The reference keeps a std::list of nodes and splits them with push_front (src/ORBextractor.cc:
+// 596-739).  Here a node IS its list position: every pass computes, for all nodes at once, the new
+// list  reverse(children in creation order) ++ (unsplit nodes in old order)  with prefix scans, and
+// remaps each key's node index.  Only nodes created by the previous pass can hold more than one key,
+// so the expandable set is {i < M : cnt[i] > 1} (M = number of nodes the last pass created).
+//   full sweep   (:596-667)  split every expandable node, in list order
+//   budgeted pass(:675-739)  order expandable nodes by (key count desc, newest first) -- the
+//                            reference's sort by (size, node address) read from the back, with the
+//                            address tie pinned to creation order -- and split the prefix that
+//                            keeps list size < N before each split (the `break` at :732-733)
+// Selection (:743-762): per node the key with the highest response, first in input order on ties.
+// Keys and node tables live in shared memory when they fit, else in a global scratch area.
+// =================================================================================================
+#define OCT_THREADS 256
+#define OCT_NODE_BYTES 64     // per-node bytes in the node pool (see carve below)
+
+struct OctPools {
+    uint32_t* kxy; uint16_t* knode; uint8_t* kq;                 // per key
+    short4* bnd[2]; int* cnt[2]; int* cc; int* A; int* B; int* ord; int* X; int* np;   // per node
+};
+
+__device__ __forceinline__ void oct_carve(OctPools& o, uint8_t* keypool, int kcap, uint8_t* nodepool, int ncap)
+{
+    o.kxy = reinterpret_cast<uint32_t*>(keypool);
+    o.knode = reinterpret_cast<uint16_t*>(keypool + 4 * (size_t)kcap);
+    o.kq = keypool + 6 * (size_t)kcap;
+    uint8_t* p = nodepool;
+    o.bnd[0] = reinterpret_cast<short4*>(p); p += 8 * (size_t)ncap;
+    o.bnd[1] = reinterpret_cast<short4*>(p); p += 8 * (size_t)ncap;
+    o.cnt[0] = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap;
+    o.cnt[1] = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap;
+    o.cc = reinterpret_cast<int*>(p); p += 16 * (size_t)ncap;
+    o.A = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap;
+    o.B = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap;
+    o.ord = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap;
+    o.X = reinterpret_cast<int*>(p); p += 4 * (size_t)ncap + 16;
+    o.np = reinterpret_cast<int*>(p);
+}
+
+// in-place exclusive prefix sum of a[0..n) by the whole CTA; returns the total to every thread.
+__device__ int block_excl_scan(int* a, int n, int* s_part /* 33 ints of shared memory */)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ipt = (n + OCT_THREADS - 1) / OCT_THREADS;
+    const int lo = min(tid * ipt, n), hi = min(lo + ipt, n);
+    __syncthreads();
+    int sum = 0;
+    for (int i = lo; i < hi; ++i) sum += a[i];
+    int inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < OCT_THREADS / 32 ? s_part[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += t;
+        }
+        if (lane < OCT_THREADS / 32) s_part[lane] = winc - w;
+        if (lane == OCT_THREADS / 32 - 1) s_part[32] = winc;
+    }
+    __syncthreads();
+    int run = s_part[warp] + inc - sum;
+    for (int i = lo; i < hi; ++i) { const int v = a[i]; a[i] = run; run += v; }
+    const int total = s_part[32];
+    __syncthreads();
+    return total;
+}
+
+// Runs the octree on keys o.kxy[0..nK); writes the survivors (packed) to out[0..count) in list order.
+__device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N, int n_ini, float hx,
+                          uint32_t* out, int out_cap, int* s_part, int* s_misc)
+{
+    const int tid = threadIdx.x;
+    (void)W;
+    // ---- roots (:548-587)
+    for (int i = tid; i < n_ini; i += OCT_THREADS) {
+        o.bnd[0][i] = make_short4((short)(int)__fmul_rn(hx, (float)i), (short)(int)__fmul_rn(hx, (float)(i + 1)), 0, (short)H);
+        o.cnt[0][i] = 0;
+    }
+    __syncthreads();
+    for (int k = tid; k < nK; k += OCT_THREADS) {
+        int r = (int)__fdiv_rn((float)ORB_PX(o.kxy[k]), hx);
+        r = min(r, n_ini - 1);
+        o.knode[k] = (uint16_t)r;
+        atomicAdd(&o.cnt[0][r], 1);
+    }
+    __syncthreads();
+    for (int i = tid; i < n_ini; i += OCT_THREADS) o.A[i] = o.cnt[0][i] > 0;
+    int n = block_excl_scan(o.A, n_ini, s_part);
+    for (int i = tid; i < n_ini; i += OCT_THREADS)
+        if (o.cnt[0][i] > 0) { o.bnd[1][o.A[i]] = o.bnd[0][i]; o.cnt[1][o.A[i]] = o.cnt[0][i]; }
+    for (int k = tid; k < nK; k += OCT_THREADS) o.knode[k] = (uint16_t)o.A[o.knode[k]];
+    __syncthreads();
+
+    int cur = 1, M = n;
+    bool phaseB = false;
+    while (true) {
+        short4* bnd = o.bnd[cur]; int* cnt = o.cnt[cur];
+        short4* bnd2 = o.bnd[cur ^ 1]; int* cnt2 = o.cnt[cur ^ 1];
+        // ---- child key counts of every expandable node (DivideNode, :483-539)
+        for (int i = tid; i < 4 * M; i += OCT_THREADS) o.cc[i] = 0;
+        if (tid == 0) { s_misc[0] = 0; s_misc[1] = 0; }
+        __syncthreads();
+        for (int k = tid; k < nK; k += OCT_THREADS) {
+            const int nd = o.knode[k];
+            if (nd < M && cnt[nd] > 1) {
+                const short4 b = bnd[nd];
+                const int mx = b.x + ((b.y - b.x + 1) >> 1), my = b.z + ((b.w - b.z + 1) >> 1);
+                const uint32_t p = o.kxy[k];
+                const int q = (ORB_PX(p) < mx ? 0 : 1) + (ORB_PY(p) < my ? 0 : 2);
+                o.kq[k] = (uint8_t)q;
+                atomicAdd(&o.cc[4 * nd + q], 1);
+            }
+        }
+        __syncthreads();
+        // ---- processing order of the expandable nodes
+        int nE;
+        if (!phaseB) {
+            for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (i < M && cnt[i] > 1);
+            nE = block_excl_scan(o.A, n, s_part);
+            for (int i = tid; i < n; i += OCT_THREADS) {
+                const bool e = (i < M && cnt[i] > 1);
+                o.B[i] = e ? o.A[i] : -1;
+                if (e) o.ord[o.A[i]] = i;
+            }
+        } else {
+            int local = 0;
+            for (int i = tid; i < n; i += OCT_THREADS) {
+                int rank = -1;
+                if (i < M && cnt[i] > 1) {
+                    const int ci = cnt[i];
+                    rank = 0;
+                    for (int j = 0; j < M; ++j) {
+                        const int cj = cnt[j];
+                        rank += (cj > 1) && (cj > ci || (cj == ci && j < i));
+                    }
+                    o.ord[rank] = i;
+                    ++local;
+                }
+                o.B[i] = rank;
+            }
+            if (local) atomicAdd(&s_misc[0], local);
+            __syncthreads();
+            nE = s_misc[0];
+        }
+        __syncthreads();
+        // ---- X[r] = list growth caused by the parents processed before r (nonempty children - 1)
+        for (int r = tid; r < nE; r += OCT_THREADS) {
+            const int p = o.ord[r];
+            o.X[r] = (o.cc[4 * p] > 0) + (o.cc[4 * p + 1] > 0) + (o.cc[4 * p + 2] > 0) + (o.cc[4 * p + 3] > 0) - 1;
+        }
+        const int growth_all = block_excl_scan(o.X, nE, s_part);
+        if (tid == 0) o.X[nE] = growth_all;
+        __syncthreads();
+        // committed prefix: everything in a full sweep; in a budgeted pass, parents reached while size < N
+        int nCommit = nE;
+        if (phaseB) {
+            int local = 0;
+            for (int r = tid; r < nE; r += OCT_THREADS) local += (n + o.X[r] < N);
+            if (local) atomicAdd(&s_misc[1], local);
+            __syncthreads();
+            nCommit = s_misc[1];
+        }
+        const int Mnew = o.X[nCommit] + nCommit;
+        const int newSize = n - nCommit + Mnew;
+        if (newSize > node_cap || newSize > out_cap) return -1;      // cannot happen (see node_cap derivation)
+        // ---- unsplit nodes keep their order behind the new ones
+        for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (o.B[i] >= 0 && o.B[i] < nCommit);
+        block_excl_scan(o.A, n, s_part);
+        if (tid == 0) s_misc[2] = 0;
+        __syncthreads();
+        int to_expand = 0;
+        for (int i = tid; i < n; i += OCT_THREADS) {
+            const int r = o.B[i];
+            if (r >= 0 && r < nCommit) {
+                int c = o.X[r] + r;                       // creation index of this parent's first child
+                const short4 b = bnd[i];
+                const int mx = b.x + ((b.y - b.x + 1) >> 1), my = b.z + ((b.w - b.z + 1) >> 1);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int kc = o.cc[4 * i + q];
+                    if (kc > 0) {
+                        const int pos = Mnew - 1 - c; ++c;
+                        bnd2[pos] = make_short4((q & 1) ? (short)mx : b.x, (q & 1) ? b.y : (short)mx,
+                                                (q & 2) ? (short)my : b.z, (q & 2) ? b.w : (short)my);
+                        cnt2[pos] = kc;
+                        o.cc[4 * i + q] = pos;
+                        to_expand += (kc > 1);
+                    }
+                }
+            } else {
+                const int pos = Mnew + i - o.A[i];
+                o.np[i] = pos;
+                bnd2[pos] = bnd[i];
+                cnt2[pos] = cnt[i];
+            }
+        }
+        if (to_expand) atomicAdd(&s_misc[2], to_expand);
+        __syncthreads();
+        for (int k = tid; k < nK; k += OCT_THREADS) {
+            const int nd = o.knode[k];
+            const int r = o.B[nd];
+            o.knode[k] = (uint16_t)((r >= 0 && r < nCommit) ? o.cc[4 * nd + o.kq[k]] : o.np[nd]);
+        }
+        const int nToExpand = s_misc[2];
+        __syncthreads();
+        const int prev = n;
+        n = newSize; M = Mnew; cur ^= 1;
+        if (n >= N || n == prev) break;                   // :671-674, :736-737
+        if (!phaseB && n + 3 * nToExpand > N) phaseB = true;   // :675
+    }
+    // ---- best key per node (:743-762)
+    unsigned* best = reinterpret_cast<unsigned*>(o.A);
+    for (int i = tid; i < n; i += OCT_THREADS) best[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < nK; k += OCT_THREADS)
+        atomicMax(&best[o.knode[k]], ((unsigned)ORB_PS(o.kxy[k]) << 24) | (0xFFFFFFu - (unsigned)k));
+    __syncthreads();
+    for (int i = tid; i < n; i += OCT_THREADS) out[i] = o.kxy[0xFFFFFFu - (best[i] & 0xFFFFFFu)];
+    return n;
+}
+
+__device__ __forceinline__ size_t oct_key_pool_bytes(int kcap) { return ((size_t)7 * kcap + 15) & ~(size_t)15; }
+
+__global__ void __launch_bounds__(OCT_THREADS) k_octree(OrbPlanDev P, int key_smem_cap, int node_smem_cap)
+{
+    extern __shared__ __align__(16) uint8_t oct_smem[];
+    __shared__ int s_part[33];
+    __shared__ int s_misc[4];
+    const int l = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+    const OrbLevel& L = P.lv[l];
+    int* selcnt = P.selcnt + (long long)frame * ORB_MAX_LEVELS + l;
+    int* candcnt = P.candcnt + (long long)frame * ORB_MAX_LEVELS + l;
+    if (L.ncells == 0 || L.n_ini < 1) { if (tid == 0) { *selcnt = 0; *candcnt = 0; } return; }
+
+    // candidate list order = cell row-major, then in-cell row-major (:791-828): exclusive scan of the
+    // per-cell survivor counts gives every cell's offset (kept in place for the debug accessors)
+    int* cbase = reinterpret_cast<int*>(P.cellcnt + (long long)frame * P.ncells + L.cell0);
+    const int nK = block_excl_scan(cbase, L.ncells, s_part);
+    if (tid == 0) *candcnt = nK;
+
+    const bool keys_in_smem = nK <= key_smem_cap, nodes_in_smem = L.node_cap <= node_smem_cap;
+    uint8_t* scratch = P.scratch + (long long)frame * P.scratch_frame_bytes;
+    OctPools o;
+    oct_carve(o, keys_in_smem ? oct_smem : scratch + L.key_scratch_off, keys_in_smem ? key_smem_cap : L.slot_total,
+              nodes_in_smem ? oct_smem + oct_key_pool_bytes(key_smem_cap) : scratch + L.node_scratch_off, L.node_cap);
+
+    const uint32_t* slots = P.slots + (long long)frame * P.slot_frame_words + L.slot_off;
+    const OrbCell* cells = P.cells + L.cell0;
+    for (int c = tid >> 5; c < L.ncells; c += OCT_THREADS / 32) {
+        const int base = cbase[c], cnt = (c + 1 < L.ncells ? cbase[c + 1] : nK) - base;
+        const uint32_t* s = slots + cells[c].slot_off;
+        for (int i = tid & 31; i < cnt; i += 32) o.kxy[base + i] = s[i];
+    }
+    __syncthreads();
+
+    uint32_t* out = P.sel + (long long)frame * P.sel_total + L.sel_off;
+    const int n = octree_run(o, nK, L.node_cap, L.W, L.H, L.nfeat, L.n_ini, L.hx, out, L.sel_cap, s_part, s_misc);
+    if (tid == 0) *selcnt = n;
+}
+
+int orb_launch_octree(const OrbPlanDev& P, int nframes, int key_smem_cap, int node_smem_cap, cudaStream_t st)
+{
+    const int smem = (int)((((size_t)7 * key_smem_cap + 15) & ~(size_t)15) + (size_t)OCT_NODE_BYTES * node_smem_cap + 64);
+    static int configured = 0;
+    if (smem > configured) {
+        if (cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+        configured = smem;
+    }
+    k_octree<<<dim3(P.nlevels, nframes), OCT_THREADS, smem, st>>>(P, key_smem_cap, node_smem_cap);
+    return 1;
+}
+
+__global__ void __launch_bounds__(OCT_THREADS) k_octree_single(const uint32_t* keys, int nK, int W, int H, int N, int n_ini,
+                                                               float hx, int node_cap, uint8_t* scratch, uint32_t* out,
+                                                               int* count, int key_smem_cap, int node_smem_cap)
+{
+    extern __shared__ __align__(16) uint8_t oct_smem[];
+    __shared__ int s_part[33];
+    __shared__ int s_misc[4];
+    const bool keys_in_smem = nK <= key_smem_cap, nodes_in_smem = node_cap <= node_smem_cap;
+    OctPools o;
+    const size_t key_bytes = ((size_t)7 * nK + 15) & ~(size_t)15;
+    oct_carve(o, keys_in_smem ? oct_smem : scratch, keys_in_smem ? key_smem_cap : nK,
+              nodes_in_smem ? oct_smem + oct_key_pool_bytes(key_smem_cap) : scratch + key_bytes, node_cap);
+    for (int k = threadIdx.x; k < nK; k += OCT_THREADS) o.kxy[k] = keys[k];
+    __syncthreads();
+    const int n = octree_run(o, nK, node_cap, W, H, N, n_ini, hx, out, node_cap, s_part, s_misc);
+    if (threadIdx.x == 0) *count = n;
+}
+
+int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N, int n_ini, float hx, int node_cap,
+                             uint8_t* d_scratch, uint32_t* d_out, int* d_count, int key_smem_cap, int node_smem_cap,
+                             cudaStream_t st)
+{
+    const int smem = (int)((((size_t)7 * key_smem_cap + 15) & ~(size_t)15) + (size_t)OCT_NODE_BYTES * node_smem_cap + 64);
+    static int configured = 0;
+    if (smem > configured) {
+        if (cudaFuncSetAttribute(k_octree_single, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+        configured = smem;
+    }
+    k_octree_single<<<1, OCT_THREADS, smem, st>>>(d_keys, n, W, H, N, n_ini, hx, node_cap, d_scratch, d_out, d_count,
+                                                  key_smem_cap, node_smem_cap);
+    return 1;
+}
+
+// =================================================================================================
+// GaussianBlur 7x7, sigma 2, REFLECT_101, in OpenCV's unsigned fixed point: 8.8 taps
+// [18,34,48,56,48,34,18], horizontal sums in 16 bits, vertical sums in 32 bits, (v + 2^15) >> 16.
+// One CTA = one 128 x 32 output tile of one level of one frame; the (128+6) x (32+6) input window
+// is staged in shared memory with the border reflection applied at load time.
+// =================================================================================================
+#define BLUR_TW 128
+#define BLUR_TH 32
+#define BLUR_IP 144           // input tile pitch (>= 128 + 6, multiple of 16)
+
+__device__ __forceinline__ int reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = i < 0 ? -i : 2 * (n - 1) - i;
+    return i;
+}
+
+__global__ void __launch_bounds__(256) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
+{
+    __shared__ __align__(16) uint8_t s_in[(BLUR_TH + 6) * BLUR_IP];
+    __shared__ __align__(16) uint16_t s_h[(BLUR_TH + 6) * BLUR_TW];
+    const int4 t = tiles[blockIdx.x];
+    const int l = t.x, x0 = t.y, y0 = t.z, frame = blockIdx.y, tid = threadIdx.x;
+    const OrbLevel& L = P.lv[l];
+    const uint8_t* __restrict__ src = orb_level_ptr(P, l, frame);
+    const int sp = orb_level_pitch(P, l);
+    uint8_t* __restrict__ dst = P.blur + (long long)frame * P.blur_frame_bytes + L.blur_off;
+
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
+        const int r = i / (BLUR_TW + 6), c = i - r * (BLUR_TW + 6);
+        const int sy = reflect101(y0 + r - 3, L.h), sx = reflect101(x0 + c - 3, L.w);
+        s_in[r * BLUR_IP + c] = __ldg(src + (long long)sy * sp + sx);
+    }
+    __syncthreads();
+    // horizontal: each task = 4 adjacent outputs of one row (10 input bytes)
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW / 4); i += 256) {
+        const int r = i / (BLUR_TW / 4), q = i - r * (BLUR_TW / 4);
+        const uint8_t* p = s_in + r * BLUR_IP + 4 * q;
+        unsigned v[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) v[k] = p[k];
+        unsigned o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            o[k] = 18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3];
+        uint2 w2 = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
+        *reinterpret_cast<uint2*>(s_h + r * BLUR_TW + 4 * q) = w2;
+    }
+    __syncthreads();
+    // vertical: each task = 4 adjacent outputs of one row, one aligned 32-bit store
+    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
+        const int r = i / (BLUR_TW / 4), q = i - r * (BLUR_TW / 4);
+        const int x = x0 + 4 * q, y = y0 + r;
+        if (y >= L.h || x >= L.pitch) continue;
+        unsigned acc[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const unsigned kk = (k == 0 || k == 6) ? 18u : (k == 1 || k == 5) ? 34u : (k == 2 || k == 4) ? 48u : 56u;
+            const uint2 h = *reinterpret_cast<const uint2*>(s_h + (r + k) * BLUR_TW + 4 * q);
+            acc[0] += kk * (h.x & 0xFFFFu); acc[1] += kk * (h.x >> 16);
+            acc[2] += kk * (h.y & 0xFFFFu); acc[3] += kk * (h.y >> 16);
+        }
+        const uint32_t out = ((acc[0] + 32768u) >> 16) | (((acc[1] + 32768u) >> 16) << 8) |
+                             (((acc[2] + 32768u) >> 16) << 16) | (((acc[3] + 32768u) >> 16) << 24);
+        *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x) = out;
+    }
+}
+
+int orb_launch_blur(const OrbPlanDev& P, int nframes, const int4* tiles, int ntiles, cudaStream_t st)
+{
+    k_blur<<<dim3(ntiles, nframes), 256, 0, st>>>(P, tiles);
+    return 1;
+}
+
+// =================================================================================================
+// Orientation + descriptor + output record; one warp per octree survivor.
+//   IC_Angle (:79-106): integer moments over the 749-pixel disc of the UNBLURRED level, lane = column;
+//   cv::fastAtan2: degree-7 polynomial in plain float mul/add (no FMA), pinned to OpenCV 4.13;
+//   steered BRIEF (:110-149) on the BLURRED level: lane i produces descriptor byte i;
+//   cos/sin follow glibc 2.39's sincosf (x86-64 FMA variant) operation by operation in double,
+//   so the rounded sample offsets agree with the host for every float angle.
+// =================================================================================================
+__device__ __forceinline__ float orb_fast_atan2(float y, float x)
+{
+    const float P1 = 57.283626556396484f, P3 = -18.66744613647461f, P5 = 8.914000511169434f, P7 = -2.539724588394165f;
+    const float eps = 2.2204460492503131e-16f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, eps)), c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(P7, c2), P5), c2), P3), c2), P1), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, eps)), c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(P7, c2), P5), c2), P3), c2), P1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__device__ __forceinline__ void orb_sincosf(float y, float* sinp, float* cosp)
+{
+    const double HPI_INV = 0x1.45f306dc9c883p+23, HPI = 0x1.921fb54442d18p+0;
+    const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+                 C4 = 0x1.99343027bf8c3p-16;
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    const unsigned top12 = (__float_as_uint(y) >> 20) & 0x7ffu;
+    double x = (double)y, xs, flip = 1.0;
+    int n = 0;
+    if (top12 < 0x3f4u) {
+        if (top12 < 0x398u) { *sinp = y; *cosp = 1.0f; return; }
+        xs = x;
+    } else {
+        const double r = __dmul_rn(x, HPI_INV);
+        n = (__double2int_rz(r) + 0x800000) >> 24;
+        x = __fma_rn(-(double)n, HPI, x);
+        xs = ((n & 3) == 1 || (n & 3) == 2) ? -x : x;
+        if (n & 2) flip = -1.0;
+    }
+    const double x2 = __dmul_rn(x, x);
+    const double sp = __fma_rn(x2, S3, S2);
+    const double cp = __fma_rn(x2, flip * C4, flip * C3);
+    const double x3 = __dmul_rn(x2, xs), x4 = __dmul_rn(x2, x2);
+    const double x5 = __dmul_rn(x2, x3), x6 = __dmul_rn(x2, x4);
+    const double c1 = __fma_rn(x2, flip * C1, flip * C0);
+    const double s = __fma_rn(x3, S1, xs);
+    const double c = __fma_rn(x4, flip * C2, c1);
+    const float fs = __double2float_rn(__fma_rn(sp, x5, s));
+    const float fc = __double2float_rn(__fma_rn(cp, x6, c));
+    if (n & 1) { *sinp = fc; *cosp = fs; } else { *sinp = fs; *cosp = fc; }
+}
+
+struct OrbKeypointRec { float x, y, size, angle, response; int octave, class_id; };
+
+__global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
+{
+    __shared__ uint32_t s_pat[256];       // [pair k][lane]: (x0, y0, x1, y1) of points 16*lane+2k, +1
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, frame = blockIdx.y;
+    {
+        const int k = tid >> 5, ln = tid & 31, p = 16 * ln + 2 * k;
+        s_pat[tid] = (uint32_t)(uint8_t)c_pattern[2 * p] | ((uint32_t)(uint8_t)c_pattern[2 * p + 1] << 8) |
+                     ((uint32_t)(uint8_t)c_pattern[2 * p + 2] << 16) | ((uint32_t)(uint8_t)c_pattern[2 * p + 3] << 24);
+    }
+    __syncthreads();
+    const int g = blockIdx.x * 8 + warp;
+    const int* selcnt = P.selcnt + (long long)frame * ORB_MAX_LEVELS;
+    if (g == 0 && lane == 0) {
+        int tot = 0; bool bad = false;
+        for (int l = 0; l < P.nlevels; ++l) { const int c = selcnt[l]; bad |= c < 0; tot += max(c, 0); }
+        P.nout[frame] = (bad || tot > P.kp_capacity) ? -1 : tot;
+    }
+    if (g >= P.sel_total) return;
+    int l = 0, before = 0;
+    while (l + 1 < P.nlevels && g >= P.lv[l].sel_off + P.lv[l].sel_cap) { before += max(selcnt[l], 0); ++l; }
+    const OrbLevel& L = P.lv[l];
+    const int idx = g - L.sel_off;
+    if (idx >= selcnt[l]) return;
+    const int o = before + idx;
+    if (o >= P.kp_capacity) return;
+    const uint32_t key = P.sel[(long long)frame * P.sel_total + g];
+    const int cx = ORB_PX(key) + ORB_BORDER, cy = ORB_PY(key) + ORB_BORDER;
+
+    // ---- IC_Angle on the unblurred level
+    const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame);
+    const int pitch = orb_level_pitch(P, l);
+    const int u = lane - ORB_HALF_PATCH;
+    int m10 = 0, m01 = 0;
+    if (lane < ORB_PATCH) {
+        const uint8_t* c = img + (long long)cy * pitch + cx + u;
+        const int au = abs(u);
+#pragma unroll 4
+        for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
+            if (au <= c_umax[abs(v)]) {
+                const int val = __ldg(c + (long long)v * pitch);
+                m10 += u * val; m01 += v * val;
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, d);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, d);
+    }
+    const float angle = orb_fast_atan2((float)m01, (float)m10);
+
+    // ---- steered BRIEF on the blurred level
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);
+    float a, b;
+    orb_sincosf(__fmul_rn(angle, factorPI), &b, &a);
+    const uint8_t* __restrict__ bc = P.blur + (long long)frame * P.blur_frame_bytes + L.blur_off + (long long)cy * L.pitch + cx;
+    unsigned byte = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t w = s_pat[k * 32 + lane];
+        const float x0 = (float)(int8_t)(w & 0xFF), y0 = (float)(int8_t)((w >> 8) & 0xFF);
+        const float x1 = (float)(int8_t)((w >> 16) & 0xFF), y1 = (float)(int8_t)(w >> 24);
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = __ldg(bc + r0 * L.pitch + c0), t1 = __ldg(bc + r1 * L.pitch + c1);
+        byte |= (unsigned)(t0 < t1) << k;
+    }
+    P.desc[((long long)frame * P.kp_capacity + o) * 32 + lane] = (uint8_t)byte;
+
+    if (lane == 0) {
+        OrbKeypointRec kp;
+        kp.x = l ? __fmul_rn((float)cx, L.scale) : (float)cx;
+        kp.y = l ? __fmul_rn((float)cy, L.scale) : (float)cy;
+        kp.size = L.kp_size; kp.angle = angle; kp.response = (float)ORB_PS(key); kp.octave = l; kp.class_id = -1;
+        reinterpret_cast<OrbKeypointRec*>(P.kps)[(long long)frame * P.kp_capacity + o] = kp;
+    }
+}
+
+int orb_launch_describe(const OrbPlanDev& P, int nframes, cudaStream_t st)
+{
+    k_describe<<<dim3((P.sel_total + 7) / 8, nframes), 256, 0, st>>>(P);
+    return 1;
+}

@@ -1,0 +1,236 @@
+// orb_match.cu -- Hamming matching (ORBmatcher::DescriptorDistance + the best / second-best scan).
+//
+// Reference: src/ORBmatcher.cc:1647-1663 (256-bit XOR + popcount) and the scan body shared by all
+// Search* routines (canonical form :201-226): candidates are visited in index order with strict
+// '<' updates, so ties keep the lowest index.  The kernels are integer-ALU (popc) bound, not a
+// float contraction: one thread owns one query descriptor in 8 registers, candidate descriptors are
+// staged in shared memory as uint4 pairs and broadcast to the warp.  No tensor cores.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+
+#include "../../include/orbgpu.h"
+
+#define MATCH_THREADS 128
+#define MATCH_TILE 128        // candidates staged per shared-memory tile (4 KB)
+
+void orbgpu_internal_set_error(const char* s);   // orbgpu_extractor.cu (thread-local text behind orbgpu_last_cuda_error)
+#define CUM(call)                                                                                     \
+    do {                                                                                              \
+        cudaError_t _e = (call);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            char _b[256];                                                                             \
+            snprintf(_b, sizeof(_b), "%s: %s", #call, cudaGetErrorString(_e));                        \
+            orbgpu_internal_set_error(_b);                                                            \
+            return ORBGPU_ERR_CUDA;                                                                   \
+        }                                                                                             \
+    } while (0)
+
+__device__ __forceinline__ int hamming256(const uint4& q0, const uint4& q1, const uint4& c0, const uint4& c1)
+{
+    return __popc(q0.x ^ c0.x) + __popc(q0.y ^ c0.y) + __popc(q0.z ^ c0.z) + __popc(q0.w ^ c0.w) +
+           __popc(q1.x ^ c1.x) + __popc(q1.y ^ c1.y) + __popc(q1.z ^ c1.z) + __popc(q1.w ^ c1.w);
+}
+
+// scan all nB candidates (index order) for this thread's query; the CTA cooperates on staging
+__device__ __forceinline__ void scan_candidates(const uint4* __restrict__ B, int nB, bool active, const uint4& q0,
+                                                const uint4& q1, uint4* s_tile, int& best, int& second, int& best_idx)
+{
+    for (int t0 = 0; t0 < nB; t0 += MATCH_TILE) {
+        const int tn = min(MATCH_TILE, nB - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < 2 * tn; i += MATCH_THREADS) s_tile[i] = __ldg(B + 2 * (size_t)t0 + i);
+        __syncthreads();
+        if (active) {
+#pragma unroll 4
+            for (int j = 0; j < tn; ++j) {
+                const int d = hamming256(q0, q1, s_tile[2 * j], s_tile[2 * j + 1]);
+                if (d < best) { second = best; best = d; best_idx = t0 + j; }
+                else if (d < second) second = d;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(MATCH_THREADS) k_match_bruteforce(const uint4* __restrict__ A, int nA,
+                                                                    const uint4* __restrict__ B, int nB,
+                                                                    int32_t* best_idx, uint16_t* best, uint16_t* second)
+{
+    __shared__ uint4 s_tile[2 * MATCH_TILE];
+    const int q = blockIdx.x * MATCH_THREADS + threadIdx.x;
+    const bool active = q < nA;
+    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+    if (active) { q0 = __ldg(A + 2 * (size_t)q); q1 = __ldg(A + 2 * (size_t)q + 1); }
+    int b1 = 256, b2 = 256, bi = -1;
+    scan_candidates(B, nB, active, q0, q1, s_tile, b1, b2, bi);
+    if (active) { best_idx[q] = bi; best[q] = (uint16_t)b1; second[q] = (uint16_t)b2; }
+}
+
+// one CTA = MATCH_THREADS queries of keyframe a against all descriptors of keyframe b
+__global__ void __launch_bounds__(MATCH_THREADS) k_match_count_pairs(const uint4* __restrict__ desc, int n_per_kf,
+                                                                     const int2* __restrict__ pairs, int th_low, float ratio,
+                                                                     int32_t* counts)
+{
+    __shared__ uint4 s_tile[2 * MATCH_TILE];
+    const int2 pr = pairs[blockIdx.y];
+    const uint4* A = desc + 2 * (size_t)pr.x * n_per_kf;
+    const uint4* B = desc + 2 * (size_t)pr.y * n_per_kf;
+    const int q = blockIdx.x * MATCH_THREADS + threadIdx.x;
+    const bool active = q < n_per_kf;
+    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+    if (active) { q0 = __ldg(A + 2 * (size_t)q); q1 = __ldg(A + 2 * (size_t)q + 1); }
+    int b1 = 256, b2 = 256, bi = -1;
+    scan_candidates(B, n_per_kf, active, q0, q1, s_tile, b1, b2, bi);
+    const bool ok = active && b1 <= th_low && (float)b1 < __fmul_rn(ratio, (float)b2);
+    const int c = __syncthreads_count(ok);
+    if (threadIdx.x == 0 && c) atomicAdd(&counts[blockIdx.y], c);
+}
+
+struct orbgpu_matcher {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    uint4* d_desc = nullptr; bool own_desc = false;
+    int num_kf = 0, n_per_kf = 0;
+    int2* d_pairs = nullptr; int32_t* d_counts = nullptr; int pair_cap = 0;
+    double last_ms = 0;
+};
+
+extern "C" {
+
+int orbgpu_hamming256(const void* a, const void* b)
+{
+    uint64_t x[4], y[4];
+    memcpy(x, a, 32); memcpy(y, b, 32);
+    return __builtin_popcountll(x[0] ^ y[0]) + __builtin_popcountll(x[1] ^ y[1]) +
+           __builtin_popcountll(x[2] ^ y[2]) + __builtin_popcountll(x[3] ^ y[3]);
+}
+
+int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t* B, int nB,
+                            int32_t* best_idx, uint16_t* best, uint16_t* second)
+{
+    if (!A || !B || !best_idx || !best || !second || nA < 1 || nB < 0) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(device));
+    uint4 *dA = nullptr, *dB = nullptr; int32_t* di = nullptr; uint16_t *d1 = nullptr, *d2 = nullptr;
+    CUM(cudaMalloc(&dA, 32 * (size_t)nA));
+    CUM(cudaMalloc(&dB, 32 * (size_t)(nB > 0 ? nB : 1)));
+    CUM(cudaMalloc(&di, 4 * (size_t)nA)); CUM(cudaMalloc(&d1, 2 * (size_t)nA)); CUM(cudaMalloc(&d2, 2 * (size_t)nA));
+    CUM(cudaMemcpy(dA, A, 32 * (size_t)nA, cudaMemcpyHostToDevice));
+    if (nB > 0) CUM(cudaMemcpy(dB, B, 32 * (size_t)nB, cudaMemcpyHostToDevice));
+    k_match_bruteforce<<<(nA + MATCH_THREADS - 1) / MATCH_THREADS, MATCH_THREADS>>>(dA, nA, dB, nB, di, d1, d2);
+    CUM(cudaGetLastError());
+    CUM(cudaMemcpy(best_idx, di, 4 * (size_t)nA, cudaMemcpyDeviceToHost));
+    CUM(cudaMemcpy(best, d1, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
+    CUM(cudaMemcpy(second, d2, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
+    cudaFree(dA); cudaFree(dB); cudaFree(di); cudaFree(d1); cudaFree(d2);
+    return ORBGPU_OK;
+}
+
+int orbgpu_matcher_create(orbgpu_matcher** out, int device)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    CUM(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(device));
+    orbgpu_matcher* m = new (std::nothrow) orbgpu_matcher();
+    if (!m) return ORBGPU_ERR_NOMEM;
+    m->device = device;
+    CUM(cudaStreamCreateWithFlags(&m->st, cudaStreamNonBlocking));
+    CUM(cudaEventCreate(&m->e0)); CUM(cudaEventCreate(&m->e1));
+    *out = m;
+    return ORBGPU_OK;
+}
+
+void orbgpu_matcher_destroy(orbgpu_matcher* m)
+{
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->st) cudaStreamSynchronize(m->st);
+    if (m->own_desc) cudaFree(m->d_desc);
+    cudaFree(m->d_pairs); cudaFree(m->d_counts);
+    if (m->e0) cudaEventDestroy(m->e0);
+    if (m->e1) cudaEventDestroy(m->e1);
+    if (m->st) cudaStreamDestroy(m->st);
+    delete m;
+}
+
+int orbgpu_matcher_set_keyframes(orbgpu_matcher* m, const uint8_t* desc, int num_keyframes, int n_per_keyframe)
+{
+    if (!m || !desc || num_keyframes < 1 || n_per_keyframe < 1) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(m->device));
+    if (m->own_desc) cudaFree(m->d_desc);
+    m->d_desc = nullptr; m->own_desc = false;
+    const size_t bytes = 32 * (size_t)num_keyframes * n_per_keyframe;
+    CUM(cudaMalloc(&m->d_desc, bytes));
+    m->own_desc = true;
+    CUM(cudaMemcpy(m->d_desc, desc, bytes, cudaMemcpyHostToDevice));
+    m->num_kf = num_keyframes; m->n_per_kf = n_per_keyframe;
+    return ORBGPU_OK;
+}
+
+int orbgpu_matcher_set_keyframes_device(orbgpu_matcher* m, const uint8_t* d_desc, int num_keyframes, int n_per_keyframe)
+{
+    if (!m || !d_desc || num_keyframes < 1 || n_per_keyframe < 1 || ((uintptr_t)d_desc & 15)) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(m->device));
+    if (m->own_desc) cudaFree(m->d_desc);
+    m->d_desc = reinterpret_cast<uint4*>(const_cast<uint8_t*>(d_desc));
+    m->own_desc = false;
+    m->num_kf = num_keyframes; m->n_per_kf = n_per_keyframe;
+    return ORBGPU_OK;
+}
+
+int orbgpu_matcher_count_pairs_device(orbgpu_matcher* m, const int32_t* d_pairs, int num_pairs, int th_low, float ratio,
+                                      int32_t* d_counts)
+{
+    if (!m || !m->d_desc || !d_pairs || !d_counts || num_pairs < 1) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(m->device));
+    CUM(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)num_pairs, m->st));
+    CUM(cudaEventRecord(m->e0, m->st));
+    const int qblocks = (m->n_per_kf + MATCH_THREADS - 1) / MATCH_THREADS;
+    for (int p0 = 0; p0 < num_pairs; p0 += 65535) {          // gridDim.y limit
+        const int np = num_pairs - p0 < 65535 ? num_pairs - p0 : 65535;
+        k_match_count_pairs<<<dim3(qblocks, np), MATCH_THREADS, 0, m->st>>>(m->d_desc, m->n_per_kf,
+                                                                           reinterpret_cast<const int2*>(d_pairs) + p0,
+                                                                           th_low, ratio, d_counts + p0);
+    }
+    CUM(cudaGetLastError());
+    CUM(cudaEventRecord(m->e1, m->st));
+    CUM(cudaStreamSynchronize(m->st));
+    float ms = 0.f;
+    CUM(cudaEventElapsedTime(&ms, m->e0, m->e1));
+    m->last_ms = ms;
+    return ORBGPU_OK;
+}
+
+int orbgpu_matcher_count_pairs(orbgpu_matcher* m, const int32_t* kf_a, const int32_t* kf_b, int num_pairs, int th_low,
+                               float ratio, int32_t* counts)
+{
+    if (!m || !m->d_desc || !kf_a || !kf_b || !counts || num_pairs < 1) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(m->device));
+    for (int p = 0; p < num_pairs; ++p)
+        if (kf_a[p] < 0 || kf_a[p] >= m->num_kf || kf_b[p] < 0 || kf_b[p] >= m->num_kf) return ORBGPU_ERR_ARG;
+    if (num_pairs > m->pair_cap) {
+        cudaFree(m->d_pairs); cudaFree(m->d_counts); m->d_pairs = nullptr; m->d_counts = nullptr; m->pair_cap = 0;
+        CUM(cudaMalloc(&m->d_pairs, sizeof(int2) * (size_t)num_pairs));
+        CUM(cudaMalloc(&m->d_counts, sizeof(int32_t) * (size_t)num_pairs));
+        m->pair_cap = num_pairs;
+    }
+    int2* h = new (std::nothrow) int2[num_pairs];
+    if (!h) return ORBGPU_ERR_NOMEM;
+    for (int p = 0; p < num_pairs; ++p) h[p] = make_int2(kf_a[p], kf_b[p]);
+    cudaError_t ce = cudaMemcpy(m->d_pairs, h, sizeof(int2) * (size_t)num_pairs, cudaMemcpyHostToDevice);
+    delete[] h;
+    CUM(ce);
+    int rc = orbgpu_matcher_count_pairs_device(m, reinterpret_cast<const int32_t*>(m->d_pairs), num_pairs, th_low, ratio, m->d_counts);
+    if (rc != ORBGPU_OK) return rc;
+    CUM(cudaMemcpy(counts, m->d_counts, sizeof(int32_t) * (size_t)num_pairs, cudaMemcpyDeviceToHost));
+    return ORBGPU_OK;
+}
+
+double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m) { return m ? m->last_ms : 0.0; }
+
+}  // extern "C"

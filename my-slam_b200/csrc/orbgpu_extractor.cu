@@ -1,0 +1,827 @@
+// orbgpu_extractor.cu -- host engine behind the orbgpu_* extractor entry points (include/orbgpu.h).
+//
+// One extractor handle = the reference's ORBextractor instance (include/ORBextractor.h:45-111):
+// constructor tables, a per-shape plan (level sizes, FAST cell table, octree budgets, resize
+// tables), and NSTREAM stream contexts that each own the device + pinned buffers of one chunk of
+// frames, so upload, kernels and download of successive chunks overlap.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "../../include/orbgpu.h"
+#include "orb_common.cuh"
+
+static thread_local char g_cuda_err[256] = "";
+extern "C" const char* orbgpu_last_cuda_error(void) { return g_cuda_err; }
+void orbgpu_internal_set_error(const char* s) { snprintf(g_cuda_err, sizeof(g_cuda_err), "%s", s); }
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            snprintf(g_cuda_err, sizeof(g_cuda_err), "%s at %s:%d: %s", #call, __FILE__, __LINE__, \
+                     cudaGetErrorString(_e));                                                      \
+            return ORBGPU_ERR_CUDA;                                                                \
+        }                                                                                          \
+    } while (0)
+
+namespace {
+
+const int NSTREAM = 3;
+enum { EV_BEGIN = 0, EV_UP, EV_PYR, EV_FAST, EV_OCT, EV_BLUR, EV_DESC, EV_DOWN, EV_COUNT };
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Plan {
+    int w = 0, h = 0;
+    OrbPlanDev dev;                    // offsets + device table pointers; per-chunk pointers filled per launch
+    std::vector<OrbCell> cells;
+    OrbCell* d_cells = nullptr;
+    short* d_rs_ofs = nullptr;
+    short* d_rs_a = nullptr;
+    int4* d_tiles = nullptr;
+    int ntiles = 0;
+    int fast_smem = 0, key_smem_cap = 0, node_smem_cap = 0;
+    int kmax = 0;                      // max keypoints per frame
+    size_t in_frame_bytes = 0;         // dense upload buffer, pitch = w
+    size_t bytes_per_frame = 0;
+    int chunk_cap = 1;
+    void free_dev()
+    {
+        cudaFree(d_cells); cudaFree(d_rs_ofs); cudaFree(d_rs_a); cudaFree(d_tiles);
+        d_cells = nullptr; d_rs_ofs = nullptr; d_rs_a = nullptr; d_tiles = nullptr;
+    }
+};
+
+struct StreamCtx {
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev[EV_COUNT] = {};
+    cudaEvent_t done = nullptr;
+    int cap = 0;                       // frames the buffers below can hold
+    uint8_t *d_in = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_scratch = nullptr, *d_desc = nullptr;
+    uint32_t *d_cellcnt = nullptr, *d_slots = nullptr, *d_sel = nullptr;
+    int *d_selcnt = nullptr, *d_candcnt = nullptr, *d_nout = nullptr;
+    orbgpu_keypoint* d_kps = nullptr;
+    uint8_t *h_in = nullptr, *h_desc = nullptr;     // pinned staging
+    orbgpu_keypoint* h_kps = nullptr;
+    int* h_nout = nullptr;
+    // pending job
+    bool busy = false, profiled = false;
+    int job_frames = 0;
+    bool staged_out = false;
+    orbgpu_keypoint* user_kps = nullptr; uint8_t* user_desc = nullptr; int* user_nout = nullptr;
+    int user_capacity = 0;
+    uint64_t ticket = 0; bool ticket_live = false;
+    int job_w = 0, job_h = 0;
+};
+
+}  // namespace
+
+struct orbgpu_extractor {
+    int device = 0;
+    int nfeatures = 0, nlevels = 0, ini_th = 0, min_th = 0;
+    double scale_factor = 0;           // the reference keeps the ctor's float in a double member
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> feats;
+    int umax[16];
+    Plan plan;
+    StreamCtx ctx[NSTREAM];
+    bool profiling = false;
+    double stage_ms[ORBGPU_NUM_STAGES] = {};
+    uint64_t launches = 0;
+    uint64_t next_ticket = 1;
+    int last_ctx = -1;                 // context holding the most recent single frame (pyramid / debug views)
+    // scratch for orbgpu_octree
+    uint8_t* d_oct_scratch = nullptr; size_t oct_scratch_bytes = 0;
+};
+
+// -------------------------------------------------------------------------------------------------
+// Constructor tables: same float/double mix as src/ORBextractor.cc:412-472.
+// -------------------------------------------------------------------------------------------------
+static void build_tables(orbgpu_extractor* e, float scale_factor)
+{
+    const int nl = e->nlevels;
+    e->scale_factor = scale_factor;
+    e->scale.assign(nl, 1.0f); e->sigma2.assign(nl, 1.0f);
+    for (int i = 1; i < nl; ++i) {
+        e->scale[i] = (float)(e->scale[i - 1] * e->scale_factor);
+        e->sigma2[i] = e->scale[i] * e->scale[i];
+    }
+    e->inv_scale.resize(nl); e->inv_sigma2.resize(nl);
+    for (int i = 0; i < nl; ++i) { e->inv_scale[i] = 1.0f / e->scale[i]; e->inv_sigma2[i] = 1.0f / e->sigma2[i]; }
+
+    e->feats.assign(nl, 0);
+    const float factor = (float)(1.0f / e->scale_factor);
+    float per_scale = e->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        e->feats[l] = (int)lrintf(per_scale);
+        sum += e->feats[l];
+        per_scale *= factor;
+    }
+    e->feats[nl - 1] = std::max(e->nfeatures - sum, 0);
+
+    // row half-widths of the 31-px circular patch
+    const int hp = ORB_HALF_PATCH;
+    int* umax = e->umax;
+    memset(umax, 0, sizeof(e->umax));
+    const int vmax = (int)floor(hp * sqrtf(2.f) / 2 + 1), vmin = (int)ceil(hp * sqrtf(2.f) / 2);
+    for (int v = 0; v <= vmax; ++v) umax[v] = (int)lrint(sqrt((double)hp * hp - v * v));
+    for (int v = hp, v0 = 0; v >= vmin; --v) {
+        while (umax[v0] == umax[v0 + 1]) ++v0;
+        umax[v] = v0;
+        ++v0;
+    }
+}
+
+// per-axis tables of cv::resize INTER_LINEAR 8U (see k_resize_level)
+static void resize_axis(int ssize, int dsize, bool clamp_fraction, short* ofs, short* a)
+{
+    const double scale = 1.0 / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= (float)s;
+        if (clamp_fraction) {            // x axis: out-of-range taps collapse onto the edge pixel
+            if (s < 0) { s = 0; f = 0.f; }
+            if (s >= ssize - 1) { s = ssize - 1; f = 0.f; }
+        }                                // y axis: both row indices are clipped in the kernel instead
+        ofs[d] = (short)s;
+        a[2 * d] = (short)lrintf((1.f - f) * 2048);
+        a[2 * d + 1] = (short)lrintf(f * 2048);
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// Per-shape plan: pyramid level sizes (src/ORBextractor.cc:1113-1114), FAST cell grid (:771-810),
+// octree roots and budgets (:544-546), buffer offsets.
+// -------------------------------------------------------------------------------------------------
+static int build_plan(orbgpu_extractor* e, int w, int h)
+{
+    Plan& pl = e->plan;
+    if (pl.w == w && pl.h == h) return ORBGPU_OK;
+    for (int s = 0; s < NSTREAM; ++s)
+        if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;   // shape change with work in flight
+    if (w < 1 || h < 1 || w > 32767 || h > 32767) return ORBGPU_ERR_UNSUPPORTED;
+
+    Plan np;
+    np.w = w; np.h = h;
+    OrbPlanDev& D = np.dev;
+    memset(&D, 0, sizeof(D));
+    D.nlevels = e->nlevels; D.ini_th = e->ini_th; D.min_th = e->min_th;
+
+    std::vector<short> rs_ofs, rs_a;
+    std::vector<int4> tiles;
+    size_t pyr = 0, blur = 0, scratch = 0;
+    long long slot_words = 0;
+    int sel_total = 0, max_cw = 7, max_ch = 7, max_node_cap = 0;
+
+    for (int l = 0; l < e->nlevels; ++l) {
+        OrbLevel& L = D.lv[l];
+        const float s = e->inv_scale[l];
+        L.w = (int)lrintf((float)w * s);
+        L.h = (int)lrintf((float)h * s);
+        if (L.w < 1 || L.h < 1) return ORBGPU_ERR_UNSUPPORTED;
+        L.pitch = (int)align_up((size_t)L.w, 16);
+        if (l > 0) { L.pyr_off = (long long)pyr; pyr += (size_t)L.pitch * L.h; }
+        L.blur_off = (long long)blur; blur += (size_t)L.pitch * L.h;
+        L.nfeat = e->feats[l];
+        L.scale = e->scale[l];
+        L.kp_size = (float)(int)(ORB_PATCH * e->scale[l]);
+        if (l > 0) {
+            const OrbLevel& S = D.lv[l - 1];
+            if (S.w == 2 * L.w && S.h == 2 * L.h) return ORBGPU_ERR_UNSUPPORTED;   // cv::resize would switch to INTER_AREA
+            L.xofs_off = (int)rs_ofs.size();
+            rs_ofs.resize(rs_ofs.size() + L.w); rs_a.resize(rs_a.size() + 2 * (size_t)L.w);
+            resize_axis(S.w, L.w, true, &rs_ofs[L.xofs_off], &rs_a[2 * (size_t)L.xofs_off]);
+            L.yofs_off = (int)rs_ofs.size();
+            rs_ofs.resize(rs_ofs.size() + L.h); rs_a.resize(rs_a.size() + 2 * (size_t)L.h);
+            resize_axis(S.h, L.h, false, &rs_ofs[L.yofs_off], &rs_a[2 * (size_t)L.yofs_off]);
+        }
+        for (int y0 = 0; y0 < L.h; y0 += 32)
+            for (int x0 = 0; x0 < L.w; x0 += 128) tiles.push_back(make_int4(l, x0, y0, 0));
+
+        // FAST cell grid
+        const int minB = ORB_BORDER, maxBX = L.w - ORB_BORDER, maxBY = L.h - ORB_BORDER;
+        L.W = maxBX - minB; L.H = maxBY - minB;
+        const float width = (float)L.W, height = (float)L.H;
+        const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f);
+        L.cell0 = (int)np.cells.size();
+        L.slot_off = slot_words;
+        int slot_total = 0;
+        if (nCols >= 1 && nRows >= 1 && L.W > 0 && L.H > 0) {
+            if (L.W > 4096 || L.H > 4096) return ORBGPU_ERR_UNSUPPORTED;     // 12-bit packed coordinates
+            const int wCell = (int)ceilf(width / nCols), hCell = (int)ceilf(height / nRows);
+            for (int i = 0; i < nRows; ++i) {
+                const int iniY = minB + i * hCell;
+                if (iniY >= maxBY - 3) continue;
+                const int maxY = std::min(iniY + hCell + 6, maxBY);
+                for (int j = 0; j < nCols; ++j) {
+                    const int iniX = minB + j * wCell;
+                    if (iniX >= maxBX - 6) continue;
+                    const int maxX = std::min(iniX + wCell + 6, maxBX);
+                    OrbCell c;
+                    memset(&c, 0, sizeof(c));
+                    c.level = (short)l;
+                    c.cw = (short)(maxX - iniX); c.ch = (short)(maxY - iniY);
+                    c.ini_x = (short)iniX; c.ini_y = (short)iniY;
+                    c.off_x = (short)(j * wCell + 3); c.off_y = (short)(i * hCell + 3);
+                    const int iw = std::max(c.cw - 6, 0), ih = std::max(c.ch - 6, 0);
+                    c.cap = ((iw + 1) / 2) * ((ih + 1) / 2);
+                    c.slot_off = slot_total;
+                    slot_total += c.cap;
+                    max_cw = std::max(max_cw, (int)c.cw); max_ch = std::max(max_ch, (int)c.ch);
+                    np.cells.push_back(c);
+                }
+            }
+            L.n_ini = (int)roundf((float)L.W / (float)L.H);
+            if (L.n_ini < 1) return ORBGPU_ERR_UNSUPPORTED;   // the reference indexes an empty vector here (:571)
+            L.hx = (float)L.W / L.n_ini;
+        } else {
+            L.n_ini = 0; L.hx = 1.f;                          // level too small for one 30-px cell: no keypoints
+        }
+        L.ncells = (int)np.cells.size() - L.cell0;
+        L.slot_total = slot_total;
+        if (slot_total >= (1 << 24)) return ORBGPU_ERR_UNSUPPORTED;
+        slot_words += slot_total;
+        L.node_cap = L.ncells ? std::max(L.nfeat, 4 * L.n_ini) + 4 : 0;
+        if (L.node_cap > 65535) return ORBGPU_ERR_UNSUPPORTED;
+        L.sel_cap = L.node_cap; L.sel_off = sel_total; sel_total += L.sel_cap;
+        max_node_cap = std::max(max_node_cap, L.node_cap);
+        L.key_scratch_off = (long long)scratch; scratch += align_up((size_t)7 * std::max(slot_total, 1), 16);
+        L.node_scratch_off = (long long)scratch; scratch += align_up((size_t)64 * L.node_cap + 64, 16);
+    }
+    D.ncells = (int)np.cells.size();
+    D.sel_total = sel_total;
+    D.pyr_frame_bytes = (long long)align_up(pyr, 256);
+    D.blur_frame_bytes = (long long)align_up(blur, 256);
+    D.slot_frame_words = (long long)align_up((size_t)slot_words, 64);
+    D.scratch_frame_bytes = (long long)align_up(scratch, 256);
+    np.kmax = sel_total;
+    np.ntiles = (int)tiles.size();
+    np.fast_smem = orb_fast_smem_bytes(max_cw, max_ch);
+    if (np.fast_smem < 0 || np.fast_smem > 200 * 1024) return ORBGPU_ERR_UNSUPPORTED;
+    np.key_smem_cap = std::min(std::max(8 * D.lv[0].nfeat, 1024), 6144);
+    np.node_smem_cap = std::min(max_node_cap, 1024);
+    np.in_frame_bytes = (size_t)w * h;
+    np.bytes_per_frame = np.in_frame_bytes + (size_t)D.pyr_frame_bytes + (size_t)D.blur_frame_bytes +
+                         (size_t)D.slot_frame_words * 4 + (size_t)D.scratch_frame_bytes + (size_t)D.ncells * 4 +
+                         (size_t)sel_total * 4 + (size_t)np.kmax * 60 + 256;
+    np.chunk_cap = (int)std::min<size_t>(64, std::max<size_t>(1, ((size_t)1536 << 20) / np.bytes_per_frame));
+
+    CU(cudaMalloc(&np.d_cells, sizeof(OrbCell) * std::max<size_t>(np.cells.size(), 1)));
+    CU(cudaMalloc(&np.d_rs_ofs, sizeof(short) * std::max<size_t>(rs_ofs.size(), 1)));
+    CU(cudaMalloc(&np.d_rs_a, sizeof(short) * std::max<size_t>(rs_a.size(), 1)));
+    CU(cudaMalloc(&np.d_tiles, sizeof(int4) * std::max<size_t>(tiles.size(), 1)));
+    if (!np.cells.empty()) CU(cudaMemcpy(np.d_cells, np.cells.data(), sizeof(OrbCell) * np.cells.size(), cudaMemcpyHostToDevice));
+    if (!rs_ofs.empty()) CU(cudaMemcpy(np.d_rs_ofs, rs_ofs.data(), sizeof(short) * rs_ofs.size(), cudaMemcpyHostToDevice));
+    if (!rs_a.empty()) CU(cudaMemcpy(np.d_rs_a, rs_a.data(), sizeof(short) * rs_a.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(np.d_tiles, tiles.data(), sizeof(int4) * tiles.size(), cudaMemcpyHostToDevice));
+    D.cells = np.d_cells; D.rs_ofs = np.d_rs_ofs; D.rs_a = np.d_rs_a;
+
+    pl.free_dev();
+    pl = np;
+    e->last_ctx = -1;
+    return ORBGPU_OK;
+}
+
+static void ctx_free_buffers(StreamCtx& c)
+{
+    cudaFree(c.d_in); cudaFree(c.d_pyr); cudaFree(c.d_blur); cudaFree(c.d_scratch); cudaFree(c.d_desc);
+    cudaFree(c.d_cellcnt); cudaFree(c.d_slots); cudaFree(c.d_sel); cudaFree(c.d_selcnt); cudaFree(c.d_candcnt);
+    cudaFree(c.d_nout); cudaFree(c.d_kps);
+    cudaFreeHost(c.h_in); cudaFreeHost(c.h_desc); cudaFreeHost(c.h_kps); cudaFreeHost(c.h_nout);
+    c.d_in = c.d_pyr = c.d_blur = c.d_scratch = c.d_desc = nullptr;
+    c.d_cellcnt = c.d_slots = c.d_sel = nullptr;
+    c.d_selcnt = c.d_candcnt = c.d_nout = nullptr; c.d_kps = nullptr;
+    c.h_in = c.h_desc = nullptr; c.h_kps = nullptr; c.h_nout = nullptr;
+    c.cap = 0;
+}
+
+// (re)allocate one context's buffers for `frames` frames of the current plan
+static int ctx_reserve(orbgpu_extractor* e, StreamCtx& c, int frames, int plan_w, int plan_h)
+{
+    const Plan& pl = e->plan;
+    if (c.cap >= frames && c.job_w == plan_w && c.job_h == plan_h) return ORBGPU_OK;
+    ctx_free_buffers(c);
+    const OrbPlanDev& D = pl.dev;
+    const size_t n = (size_t)frames;
+    CU(cudaMalloc(&c.d_in, n * pl.in_frame_bytes + 64));
+    CU(cudaMalloc(&c.d_pyr, n * (size_t)D.pyr_frame_bytes + 64));
+    CU(cudaMalloc(&c.d_blur, n * (size_t)D.blur_frame_bytes + 64));
+    CU(cudaMalloc(&c.d_scratch, n * (size_t)D.scratch_frame_bytes + 64));
+    CU(cudaMalloc(&c.d_cellcnt, n * (size_t)std::max(D.ncells, 1) * 4));
+    CU(cudaMalloc(&c.d_slots, n * (size_t)std::max<long long>(D.slot_frame_words, 1) * 4));
+    CU(cudaMalloc(&c.d_sel, n * (size_t)std::max(D.sel_total, 1) * 4));
+    CU(cudaMalloc(&c.d_selcnt, n * ORB_MAX_LEVELS * 4));
+    CU(cudaMalloc(&c.d_candcnt, n * ORB_MAX_LEVELS * 4));
+    CU(cudaMalloc(&c.d_nout, n * 4));
+    CU(cudaMalloc(&c.d_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint)));
+    CU(cudaMalloc(&c.d_desc, n * (size_t)std::max(pl.kmax, 1) * 32));
+    CU(cudaHostAlloc(&c.h_in, n * pl.in_frame_bytes + 64, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&c.h_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint), cudaHostAllocDefault));
+    CU(cudaHostAlloc(&c.h_desc, n * (size_t)std::max(pl.kmax, 1) * 32, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&c.h_nout, n * 4, cudaHostAllocDefault));
+    c.cap = frames; c.job_w = plan_w; c.job_h = plan_h;
+    return ORBGPU_OK;
+}
+
+// -------------------------------------------------------------------------------------------------
+// One chunk of frames through the kernels, on the context's stream.
+// -------------------------------------------------------------------------------------------------
+static int enqueue_kernels(orbgpu_extractor* e, StreamCtx& c, const uint8_t* d_src, long long src_frame_stride,
+                           int src_pitch, int nframes, orbgpu_keypoint* d_kps, uint8_t* d_desc, int* d_nout,
+                           int kp_capacity)
+{
+    const Plan& pl = e->plan;
+    OrbPlanDev P = pl.dev;
+    P.src = d_src; P.src_frame_stride = src_frame_stride; P.src_pitch = src_pitch;
+    P.pyr = c.d_pyr; P.blur = c.d_blur; P.cellcnt = c.d_cellcnt; P.slots = c.d_slots; P.sel = c.d_sel;
+    P.selcnt = c.d_selcnt; P.candcnt = c.d_candcnt; P.scratch = c.d_scratch;
+    P.kps = d_kps; P.desc = d_desc; P.nout = d_nout; P.kp_capacity = kp_capacity;
+    const bool prof = e->profiling;
+    int n, total = 0;
+    if ((n = orb_launch_pyramid(P, nframes, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
+    if (prof) CU(cudaEventRecord(c.ev[EV_PYR], c.st));
+    if (P.ncells > 0) { if ((n = orb_launch_fast(P, nframes, pl.fast_smem, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n; }
+    if (prof) CU(cudaEventRecord(c.ev[EV_FAST], c.st));
+    if ((n = orb_launch_octree(P, nframes, pl.key_smem_cap, pl.node_smem_cap, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
+    if (prof) CU(cudaEventRecord(c.ev[EV_OCT], c.st));
+    if ((n = orb_launch_blur(P, nframes, pl.d_tiles, pl.ntiles, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
+    if (prof) CU(cudaEventRecord(c.ev[EV_BLUR], c.st));
+    if ((n = orb_launch_describe(P, nframes, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
+    if (prof) CU(cudaEventRecord(c.ev[EV_DESC], c.st));
+    CU(cudaGetLastError());
+    e->launches += (uint64_t)total;
+    return ORBGPU_OK;
+}
+
+static bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// wait for the context's pending job and hand its results to the caller
+static int ctx_finish(orbgpu_extractor* e, StreamCtx& c)
+{
+    if (!c.busy) return ORBGPU_OK;
+    CU(cudaEventSynchronize(c.done));
+    c.busy = false;
+    int rc = ORBGPU_OK;
+    const int kmax = e->plan.kmax;
+    const int* nout = c.staged_out ? c.h_nout : c.user_nout;
+    if (c.staged_out && c.user_nout) {
+        for (int i = 0; i < c.job_frames; ++i) {
+            const int n = c.h_nout[i];
+            c.user_nout[i] = n;
+            if (n > 0) {
+                memcpy(c.user_kps + (size_t)i * c.user_capacity, c.h_kps + (size_t)i * kmax, sizeof(orbgpu_keypoint) * (size_t)n);
+                memcpy(c.user_desc + (size_t)i * c.user_capacity * 32, c.h_desc + (size_t)i * kmax * 32, 32 * (size_t)n);
+            }
+        }
+    }
+    if (nout)
+        for (int i = 0; i < c.job_frames; ++i) if (nout[i] < 0) rc = ORBGPU_ERR_CAPACITY;
+    if (c.profiled) {
+        for (int s = 0; s < ORBGPU_NUM_STAGES; ++s) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, c.ev[s], c.ev[s + 1]) == cudaSuccess) e->stage_ms[s] += ms;
+            else cudaGetLastError();
+        }
+        c.profiled = false;
+    }
+    return rc;
+}
+
+static int use_device(orbgpu_extractor* e)
+{
+    CU(cudaSetDevice(e->device));
+    return ORBGPU_OK;
+}
+
+// upload `m` frames starting at host pointer `src` into c.d_in (dense, pitch = w)
+static int upload_frames(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, int m, int w, int h,
+                         size_t row_stride, size_t frame_stride, bool pinned)
+{
+    const size_t fb = (size_t)w * h;
+    if (pinned && row_stride == (size_t)w && frame_stride == fb) {
+        CU(cudaMemcpyAsync(c.d_in, src, fb * m, cudaMemcpyHostToDevice, c.st));
+    } else if (pinned && frame_stride == row_stride * h) {
+        CU(cudaMemcpy2DAsync(c.d_in, (size_t)w, src, row_stride, (size_t)w, (size_t)h * m, cudaMemcpyHostToDevice, c.st));
+    } else {
+        for (int i = 0; i < m; ++i) {
+            const uint8_t* f = src + (size_t)i * frame_stride;
+            uint8_t* d = c.h_in + (size_t)i * fb;
+            if (row_stride == (size_t)w) memcpy(d, f, fb);
+            else for (int y = 0; y < h; ++y) memcpy(d + (size_t)y * w, f + (size_t)y * row_stride, (size_t)w);
+        }
+        CU(cudaMemcpyAsync(c.d_in, c.h_in, fb * m, cudaMemcpyHostToDevice, c.st));
+    }
+    (void)e;
+    return ORBGPU_OK;
+}
+
+static int download_results(orbgpu_extractor* e, StreamCtx& c, int m, orbgpu_keypoint* kps, uint8_t* desc, int* n_out,
+                            int capacity, bool pinned_out)
+{
+    const size_t kmax = (size_t)e->plan.kmax;
+    c.staged_out = !pinned_out;
+    c.user_kps = kps; c.user_desc = desc; c.user_nout = n_out; c.user_capacity = capacity;
+    if (pinned_out) {
+        CU(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(orbgpu_keypoint), c.d_kps, kmax * sizeof(orbgpu_keypoint),
+                             kmax * sizeof(orbgpu_keypoint), (size_t)m, cudaMemcpyDeviceToHost, c.st));
+        CU(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, c.d_desc, kmax * 32, kmax * 32, (size_t)m, cudaMemcpyDeviceToHost, c.st));
+        CU(cudaMemcpyAsync(n_out, c.d_nout, sizeof(int) * (size_t)m, cudaMemcpyDeviceToHost, c.st));
+    } else {
+        CU(cudaMemcpyAsync(c.h_kps, c.d_kps, kmax * sizeof(orbgpu_keypoint) * m, cudaMemcpyDeviceToHost, c.st));
+        CU(cudaMemcpyAsync(c.h_desc, c.d_desc, kmax * 32 * m, cudaMemcpyDeviceToHost, c.st));
+        CU(cudaMemcpyAsync(c.h_nout, c.d_nout, sizeof(int) * (size_t)m, cudaMemcpyDeviceToHost, c.st));
+    }
+    return ORBGPU_OK;
+}
+
+// one chunk, host buffers: upload -> kernels -> download, all asynchronous on the context's stream
+static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, int m, int w, int h, size_t row_stride,
+                        size_t frame_stride, bool pinned_in, orbgpu_keypoint* kps, uint8_t* desc, int* n_out,
+                        int capacity, bool pinned_out)
+{
+    int rc;
+    if ((rc = ctx_finish(e, c)) != ORBGPU_OK) return rc;
+    if ((rc = ctx_reserve(e, c, m, w, h)) != ORBGPU_OK) return rc;
+    const bool prof = e->profiling;
+    if (prof) CU(cudaEventRecord(c.ev[EV_BEGIN], c.st));
+    if ((rc = upload_frames(e, c, src, m, w, h, row_stride, frame_stride, pinned_in)) != ORBGPU_OK) return rc;
+    if (prof) CU(cudaEventRecord(c.ev[EV_UP], c.st));
+    if ((rc = enqueue_kernels(e, c, c.d_in, (long long)w * h, w, m, c.d_kps, c.d_desc, c.d_nout, e->plan.kmax)) != ORBGPU_OK) return rc;
+    if ((rc = download_results(e, c, m, kps, desc, n_out, capacity, pinned_out)) != ORBGPU_OK) return rc;
+    if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
+    CU(cudaEventRecord(c.done, c.st));
+    c.busy = true; c.profiled = prof; c.job_frames = m;
+    return ORBGPU_OK;
+}
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+int orbgpu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* orbgpu_version(void) { return "orbgpu 0.1 (sm_100a)"; }
+
+const char* orbgpu_strerror(int code)
+{
+    switch (code) {
+        case ORBGPU_OK: return "ok";
+        case ORBGPU_ERR_ARG: return "invalid argument";
+        case ORBGPU_ERR_CAPACITY: return "output capacity too small";
+        case ORBGPU_ERR_CUDA: return "CUDA error (see orbgpu_last_cuda_error)";
+        case ORBGPU_ERR_NOMEM: return "out of memory";
+        case ORBGPU_ERR_UNSUPPORTED: return "unsupported image shape or parameters";
+        case ORBGPU_ERR_STATE: return "invalid state (ticket, queue or no frame extracted yet)";
+        default: return "unknown error";
+    }
+}
+
+int orbgpu_create(orbgpu_extractor** out, int device, int nfeatures, float scale_factor, int nlevels,
+                  int ini_th_fast, int min_th_fast)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    if (nfeatures < 1 || nlevels < 1 || nlevels > ORB_MAX_LEVELS || !(scale_factor > 1.0f)) return ORBGPU_ERR_ARG;
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return ORBGPU_ERR_ARG;
+    CU(cudaSetDevice(device));
+    orbgpu_extractor* e = new (std::nothrow) orbgpu_extractor();
+    if (!e) return ORBGPU_ERR_NOMEM;
+    e->device = device; e->nfeatures = nfeatures; e->nlevels = nlevels;
+    e->ini_th = std::min(std::max(ini_th_fast, 0), 255);     // cv::FAST clamps its threshold
+    e->min_th = std::min(std::max(min_th_fast, 0), 255);
+    build_tables(e, scale_factor);
+    if (orb_upload_constants(e->umax) != 0) { delete e; return ORBGPU_ERR_CUDA; }
+    for (int s = 0; s < NSTREAM; ++s) {
+        StreamCtx& c = e->ctx[s];
+        if (cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking) != cudaSuccess) { delete e; return ORBGPU_ERR_CUDA; }
+        for (int k = 0; k < EV_COUNT; ++k) cudaEventCreate(&c.ev[k]);
+        cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming);
+    }
+    *out = e;
+    return ORBGPU_OK;
+}
+
+void orbgpu_destroy(orbgpu_extractor* e)
+{
+    if (!e) return;
+    cudaSetDevice(e->device);
+    for (int s = 0; s < NSTREAM; ++s) {
+        StreamCtx& c = e->ctx[s];
+        if (c.st) cudaStreamSynchronize(c.st);
+        ctx_free_buffers(c);
+        for (int k = 0; k < EV_COUNT; ++k) if (c.ev[k]) cudaEventDestroy(c.ev[k]);
+        if (c.done) cudaEventDestroy(c.done);
+        if (c.st) cudaStreamDestroy(c.st);
+    }
+    e->plan.free_dev();
+    cudaFree(e->d_oct_scratch);
+    delete e;
+}
+
+int orbgpu_get_tables(orbgpu_extractor* e, float* scale4, int* feats, int* umax)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    const int nl = e->nlevels;
+    if (scale4)
+        for (int i = 0; i < nl; ++i) {
+            scale4[i] = e->scale[i]; scale4[nl + i] = e->inv_scale[i];
+            scale4[2 * nl + i] = e->sigma2[i]; scale4[3 * nl + i] = e->inv_sigma2[i];
+        }
+    if (feats) for (int i = 0; i < nl; ++i) feats[i] = e->feats[i];
+    if (umax) for (int i = 0; i < 16; ++i) umax[i] = e->umax[i];
+    return nl;
+}
+
+int orbgpu_max_keypoints(orbgpu_extractor* e, int w, int h)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    return e->plan.kmax;
+}
+
+int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
+                         size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    const bool pin_in = is_pinned(frames);
+    const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
+    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
+    int result = ORBGPU_OK, k = 0;
+    for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
+        StreamCtx& c = e->ctx[k % NSTREAM];
+        const int m = std::min(chunk, n - i0);
+        if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
+        if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
+        rc = submit_chunk(e, c, frames + (size_t)i0 * frame_stride, m, w, h, row_stride, frame_stride, pin_in,
+                          kps + (size_t)i0 * capacity, desc + (size_t)i0 * capacity * 32, n_out + i0, capacity, pin_out);
+        if (rc != ORBGPU_OK) { result = rc; break; }
+    }
+    for (int s = 0; s < NSTREAM; ++s)
+        if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) result = rc;
+    e->last_ctx = (n == 1 && result == ORBGPU_OK) ? 0 : -1;
+    return result;
+}
+
+int orbgpu_extract(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride,
+                   orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !n_out) return ORBGPU_ERR_ARG;
+    if (!img || w == 0 || h == 0) { *n_out = -1; return ORBGPU_OK; }   // empty image: outputs untouched
+    return orbgpu_extract_batch(e, img, 1, w, h, stride, stride * (size_t)h, kps, desc, capacity, n_out);
+}
+
+int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, int n, int w, int h, size_t row_stride,
+                                size_t frame_stride, orbgpu_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out)
+{
+    if (!e || !d_frames || !d_kps || !d_desc || !d_n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
+    int result = ORBGPU_OK, k = 0;
+    for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
+        StreamCtx& c = e->ctx[k % NSTREAM];
+        const int m = std::min(chunk, n - i0);
+        if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
+        if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
+        const bool prof = e->profiling;
+        if (prof) { CU(cudaEventRecord(c.ev[EV_BEGIN], c.st)); CU(cudaEventRecord(c.ev[EV_UP], c.st)); }
+        rc = enqueue_kernels(e, c, d_frames + (size_t)i0 * frame_stride, (long long)frame_stride, (int)row_stride, m,
+                             d_kps + (size_t)i0 * capacity, d_desc + (size_t)i0 * capacity * 32, d_n_out + i0, capacity);
+        if (rc != ORBGPU_OK) { result = rc; break; }
+        if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
+        CU(cudaEventRecord(c.done, c.st));
+        c.busy = true; c.profiled = prof; c.job_frames = m; c.staged_out = false; c.user_nout = nullptr;
+    }
+    for (int s = 0; s < NSTREAM; ++s)
+        if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) result = rc;
+    e->last_ctx = -1;
+    return result;
+}
+
+// ---- pinned frame queue ---------------------------------------------------------------------------
+int orbgpu_queue_depth(orbgpu_extractor* e) { return e ? NSTREAM : ORBGPU_ERR_ARG; }
+
+int orbgpu_submit(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride, uint64_t* ticket)
+{
+    if (!e || !img || !ticket || w < 1 || h < 1 || stride < (size_t)w) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    const uint64_t t = e->next_ticket;
+    StreamCtx& c = e->ctx[t % NSTREAM];
+    if (c.ticket_live) return ORBGPU_ERR_STATE;          // ring slot not collected yet
+    if ((rc = ctx_reserve(e, c, 1, w, h)) != ORBGPU_OK) return rc;
+    // always staged: the caller's image may be reused as soon as submit returns
+    rc = submit_chunk(e, c, img, 1, w, h, stride, stride * (size_t)h, false, nullptr, nullptr, nullptr, 0, false);
+    if (rc != ORBGPU_OK) return rc;
+    c.ticket = t; c.ticket_live = true;
+    e->next_ticket = t + 1;
+    *ticket = t;
+    return ORBGPU_OK;
+}
+
+int orbgpu_collect(orbgpu_extractor* e, uint64_t ticket, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !kps || !desc || !n_out) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    StreamCtx& c = e->ctx[ticket % NSTREAM];
+    if (!c.ticket_live || c.ticket != ticket) return ORBGPU_ERR_STATE;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    rc = ctx_finish(e, c);                                // staged, user pointers null: nothing copied yet
+    c.ticket_live = false;
+    if (rc != ORBGPU_OK) return rc;
+    const int n = c.h_nout[0];
+    if (n < 0) return ORBGPU_ERR_CAPACITY;
+    *n_out = n;
+    memcpy(kps, c.h_kps, sizeof(orbgpu_keypoint) * (size_t)n);
+    memcpy(desc, c.h_desc, 32 * (size_t)n);
+    e->last_ctx = (int)(ticket % NSTREAM);
+    return ORBGPU_OK;
+}
+
+// ---- views of the most recent single frame ------------------------------------------------------
+static StreamCtx* last_frame_ctx(orbgpu_extractor* e)
+{
+    if (!e || e->last_ctx < 0) return nullptr;
+    StreamCtx& c = e->ctx[e->last_ctx];
+    return c.busy ? nullptr : &c;
+}
+
+int orbgpu_pyramid_level(orbgpu_extractor* e, int level, uint8_t* dst, size_t dst_stride, int* w, int* h)
+{
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    if (level < 0 || level >= e->nlevels) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    const OrbLevel& L = e->plan.dev.lv[level];
+    if (w) *w = L.w;
+    if (h) *h = L.h;
+    if (!dst) return ORBGPU_OK;
+    if (dst_stride < (size_t)L.w) return ORBGPU_ERR_ARG;
+    if (level == 0) CU(cudaMemcpy2D(dst, dst_stride, c->d_in, (size_t)e->plan.w, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+    else CU(cudaMemcpy2D(dst, dst_stride, c->d_pyr + L.pyr_off, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+    return ORBGPU_OK;
+}
+
+int orbgpu_debug_level_blurred(orbgpu_extractor* e, int level, uint8_t* dst, size_t dst_stride)
+{
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    if (level < 0 || level >= e->nlevels || !dst) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    const OrbLevel& L = e->plan.dev.lv[level];
+    CU(cudaMemcpy2D(dst, dst_stride, c->d_blur + L.blur_off, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+    return ORBGPU_OK;
+}
+
+int orbgpu_debug_level_candidates(orbgpu_extractor* e, int level, int* x, int* y, int* score, int cap)
+{
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    if (level < 0 || level >= e->nlevels) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    const Plan& pl = e->plan;
+    const OrbLevel& L = pl.dev.lv[level];
+    if (L.ncells == 0) return 0;
+    int total = 0;
+    CU(cudaMemcpy(&total, c->d_candcnt + level, sizeof(int), cudaMemcpyDeviceToHost));
+    std::vector<int> base((size_t)L.ncells);          // exclusive scan left in place by the octree kernel
+    CU(cudaMemcpy(base.data(), c->d_cellcnt + L.cell0, sizeof(int) * (size_t)L.ncells, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> slots((size_t)L.slot_total);
+    CU(cudaMemcpy(slots.data(), c->d_slots + L.slot_off, sizeof(uint32_t) * (size_t)L.slot_total, cudaMemcpyDeviceToHost));
+    int o = 0;
+    for (int ci = 0; ci < L.ncells; ++ci) {
+        const int cnt = (ci + 1 < L.ncells ? base[ci + 1] : total) - base[ci];
+        const uint32_t* s = &slots[(size_t)pl.cells[L.cell0 + ci].slot_off];
+        for (int i = 0; i < cnt; ++i, ++o)
+            if (o < cap) { x[o] = ORB_PX(s[i]); y[o] = ORB_PY(s[i]); score[o] = ORB_PS(s[i]); }
+    }
+    return o;
+}
+
+int orbgpu_debug_level_selected(orbgpu_extractor* e, int level, int* x, int* y, int* score, int cap)
+{
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    if (level < 0 || level >= e->nlevels) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    const OrbLevel& L = e->plan.dev.lv[level];
+    int n = 0;
+    CU(cudaMemcpy(&n, c->d_selcnt + level, sizeof(int), cudaMemcpyDeviceToHost));
+    if (n <= 0) return n;
+    std::vector<uint32_t> sel((size_t)n);
+    CU(cudaMemcpy(sel.data(), c->d_sel + L.sel_off, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && i < cap; ++i) { x[i] = ORB_PX(sel[i]); y[i] = ORB_PY(sel[i]); score[i] = ORB_PS(sel[i]); }
+    return n;
+}
+
+int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* resp, int n, int W, int H, int N,
+                  int* out_idx, int cap)
+{
+    if (!e || n < 0 || (n && (!xs || !ys || !resp)) || !out_idx || W < 1 || H < 1 || W > 4096 || H > 4096 || N < 1) return ORBGPU_ERR_ARG;
+    if (n >= (1 << 24)) return ORBGPU_ERR_UNSUPPORTED;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    const int n_ini = (int)roundf((float)W / (float)H);
+    if (n_ini < 1) return ORBGPU_ERR_UNSUPPORTED;
+    const float hx = (float)W / n_ini;
+    const int node_cap = std::max(N, 4 * n_ini) + 4;
+    if (node_cap > 65535) return ORBGPU_ERR_UNSUPPORTED;
+    std::vector<uint32_t> keys((size_t)std::max(n, 1));
+    for (int i = 0; i < n; ++i) {
+        if (xs[i] < 0 || xs[i] >= W || ys[i] < 0 || ys[i] > 4095 || resp[i] < 0 || resp[i] > 255) return ORBGPU_ERR_ARG;
+        keys[i] = ORB_PACK(xs[i], ys[i], resp[i]);
+    }
+    const size_t key_bytes = align_up((size_t)7 * std::max(n, 1), 16), node_bytes = (size_t)64 * node_cap + 64;
+    const size_t need = key_bytes + node_bytes + 4 * (size_t)std::max(n, 1) + 4 * (size_t)node_cap + 64;
+    if (need > e->oct_scratch_bytes) {
+        cudaFree(e->d_oct_scratch); e->d_oct_scratch = nullptr; e->oct_scratch_bytes = 0;
+        CU(cudaMalloc(&e->d_oct_scratch, need));
+        e->oct_scratch_bytes = need;
+    }
+    uint8_t* base = e->d_oct_scratch;
+    uint32_t* d_keys = reinterpret_cast<uint32_t*>(base + key_bytes + node_bytes);
+    uint32_t* d_out = d_keys + std::max(n, 1);
+    int* d_count = reinterpret_cast<int*>(d_out + node_cap);
+    cudaStream_t st = e->ctx[0].st;
+    CU(cudaMemcpyAsync(d_keys, keys.data(), 4 * (size_t)std::max(n, 1), cudaMemcpyHostToDevice, st));
+    const int key_smem_cap = std::min(std::max(8 * N, 1024), 6144), node_smem_cap = std::min(node_cap, 1024);
+    if (orb_launch_octree_single(d_keys, n, W, H, N, n_ini, hx, node_cap, base, d_out, d_count, key_smem_cap,
+                                 node_smem_cap, st) < 0) return ORBGPU_ERR_CUDA;
+    e->launches += 1;
+    int count = 0;
+    CU(cudaMemcpyAsync(&count, d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (count < 0) return ORBGPU_ERR_CAPACITY;
+    std::vector<uint32_t> out((size_t)std::max(count, 1));
+    CU(cudaMemcpy(out.data(), d_out, 4 * (size_t)count, cudaMemcpyDeviceToHost));
+    // the kernel returns packed keys; map them back to input indices (first occurrence = the key
+    // that wins response ties, since equal packed values are the same candidate)
+    std::vector<int> first_index;
+    {
+        std::vector<std::pair<uint32_t, int>> order((size_t)n);
+        for (int i = 0; i < n; ++i) order[i] = std::make_pair(keys[i], i);
+        std::sort(order.begin(), order.end());
+        for (int i = 0; i < count; ++i) {
+            auto it = std::lower_bound(order.begin(), order.end(), std::make_pair(out[i], -1));
+            if (it == order.end() || it->first != out[i]) return ORBGPU_ERR_STATE;
+            if (i < cap) out_idx[i] = it->second;
+        }
+    }
+    return count;
+}
+
+int orbgpu_set_profiling(orbgpu_extractor* e, int on)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    e->profiling = on != 0;
+    return ORBGPU_OK;
+}
+
+int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset)
+{
+    if (!e || !ms) return ORBGPU_ERR_ARG;
+    for (int i = 0; i < n && i < ORBGPU_NUM_STAGES; ++i) ms[i] = e->stage_ms[i];
+    if (reset) memset(e->stage_ms, 0, sizeof(e->stage_ms));
+    return ORBGPU_OK;
+}
+
+uint64_t orbgpu_launch_count(orbgpu_extractor* e) { return e ? e->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,281 @@
+"""ctypes binding of include/orbgpu.h.  No CPU fallback: every compute call goes to liborbgpu.so and
+raises OrbGpuError when the library or a CUDA device is missing."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+NUM_STAGES = 7
+STAGE_NAMES = ("upload", "pyramid", "fast_cells", "octree", "blur", "describe", "download")
+
+
+class OrbGpuError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "liborbgpu.so")
+
+
+_lib = None
+
+
+def lib():
+    """Loads liborbgpu.so (built in-tree by csrc/Makefile); fails loudly when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise OrbGpuError("%s not built: run `python -c 'import __graft_entry__ as g; g.build()'`" % p)
+    L = C.CDLL(p)
+    vp, i32, sz, f32, u64 = C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_uint64
+    pi = C.POINTER(C.c_int)
+    sig = {
+        "orbgpu_create": (i32, [C.POINTER(vp), i32, i32, f32, i32, i32, i32]),
+        "orbgpu_destroy": (None, [vp]),
+        "orbgpu_get_tables": (i32, [vp, vp, vp, vp]),
+        "orbgpu_max_keypoints": (i32, [vp, i32, i32]),
+        "orbgpu_extract": (i32, [vp, vp, i32, i32, sz, vp, vp, i32, pi]),
+        "orbgpu_extract_batch": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
+        "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
+        "orbgpu_submit": (i32, [vp, vp, i32, i32, sz, C.POINTER(u64)]),
+        "orbgpu_collect": (i32, [vp, u64, vp, vp, i32, pi]),
+        "orbgpu_queue_depth": (i32, [vp]),
+        "orbgpu_pyramid_level": (i32, [vp, i32, vp, sz, pi, pi]),
+        "orbgpu_debug_level_blurred": (i32, [vp, i32, vp, sz]),
+        "orbgpu_debug_level_candidates": (i32, [vp, i32, vp, vp, vp, i32]),
+        "orbgpu_debug_level_selected": (i32, [vp, i32, vp, vp, vp, i32]),
+        "orbgpu_octree": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp, i32]),
+        "orbgpu_set_profiling": (i32, [vp, i32]),
+        "orbgpu_get_stage_ms": (i32, [vp, vp, i32, i32]),
+        "orbgpu_launch_count": (u64, [vp]),
+        "orbgpu_hamming256": (i32, [vp, vp]),
+        "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
+        "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
+        "orbgpu_matcher_destroy": (None, [vp]),
+        "orbgpu_matcher_set_keyframes": (i32, [vp, vp, i32, i32]),
+        "orbgpu_matcher_set_keyframes_device": (i32, [vp, vp, i32, i32]),
+        "orbgpu_matcher_count_pairs": (i32, [vp, vp, vp, i32, i32, f32, vp]),
+        "orbgpu_matcher_count_pairs_device": (i32, [vp, vp, i32, i32, f32, vp]),
+        "orbgpu_matcher_last_kernel_ms": (C.c_double, [vp]),
+        "orbgpu_strerror": (C.c_char_p, [i32]),
+        "orbgpu_last_cuda_error": (C.c_char_p, []),
+        "orbgpu_device_count": (i32, []),
+        "orbgpu_version": (C.c_char_p, []),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)           # AttributeError here = header/library mismatch
+        f.restype = res
+        f.argtypes = args
+    L._orbgpu_symbols = tuple(sig)
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc < 0:
+        L = lib()
+        msg = L.orbgpu_strerror(rc).decode()
+        if rc == -3:
+            msg += ": " + L.orbgpu_last_cuda_error().decode()
+        raise OrbGpuError("orbgpu error %d: %s" % (rc, msg))
+    return rc
+
+
+def device_count():
+    return lib().orbgpu_device_count()
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class ORBextractor:
+    """Mirror of ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:45-111): same constructor
+    arguments, __call__(image) == operator()(image, mask, keypoints, descriptors), same getters."""
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device=0):
+        self._L = lib()
+        self._h = C.c_void_p()
+        _check(self._L.orbgpu_create(C.byref(self._h), device, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST))
+        self.nlevels = nlevels
+        self.device = device
+        s4 = np.zeros(4 * nlevels, np.float32)
+        self._feats = np.zeros(nlevels, np.int32)
+        self._umax = np.zeros(16, np.int32)
+        _check(self._L.orbgpu_get_tables(self._h, _p(s4), _p(self._feats), _p(self._umax)))
+        self._s4 = s4.reshape(4, nlevels)
+        self._scale_arg = np.float32(scaleFactor)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbgpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    # getters, include/ORBextractor.h:63-83
+    def GetLevels(self): return self.nlevels
+    def GetScaleFactor(self): return float(self._scale_arg)
+    def GetScaleFactors(self): return self._s4[0].copy()
+    def GetInverseScaleFactors(self): return self._s4[1].copy()
+    def GetScaleSigmaSquares(self): return self._s4[2].copy()
+    def GetInverseScaleSigmaSquares(self): return self._s4[3].copy()
+    def features_per_level(self): return self._feats.copy()
+    def umax(self): return self._umax.copy()
+
+    def max_keypoints(self, w, h):
+        return _check(self._L.orbgpu_max_keypoints(self._h, w, h))
+
+    def __call__(self, image, mask=None):
+        """Returns (keypoints[KP_DTYPE], descriptors[N,32] uint8); (None, None) for an empty image
+        (the reference returns without touching its outputs, src/ORBextractor.cc:1048-1049)."""
+        if image is None or image.size == 0:
+            return None, None
+        if image.dtype != np.uint8 or image.ndim != 2:
+            raise ValueError("image must be CV_8UC1 (2-D uint8)")    # reference: assert, src/ORBextractor.cc:1052
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        cap = self.max_keypoints(w, h)
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        _check(self._L.orbgpu_extract(self._h, _p(image), w, h, image.strides[0], _p(kps), _p(desc), cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, frames, kps=None, desc=None, n_out=None):
+        """frames: [n,h,w] uint8 host array (pinned or pageable).  Returns (kps[n,cap], desc[n,cap,32], n_out[n])."""
+        n, h, w = frames.shape
+        cap = self.max_keypoints(w, h)
+        if kps is None:
+            kps = np.zeros((n, cap), KP_DTYPE); desc = np.zeros((n, cap, 32), np.uint8); n_out = np.zeros(n, np.int32)
+        _check(self._L.orbgpu_extract_batch(self._h, _p(frames), n, w, h, frames.strides[1], frames.strides[0],
+                                            _p(kps), _p(desc), kps.shape[1], _p(n_out)))
+        return kps, desc, n_out
+
+    def extract_batch_ptr(self, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr, device=False):
+        f = self._L.orbgpu_extract_batch_device if device else self._L.orbgpu_extract_batch
+        _check(f(self._h, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr))
+
+    def submit(self, image):
+        image = np.ascontiguousarray(image, np.uint8)
+        t = C.c_uint64(0)
+        _check(self._L.orbgpu_submit(self._h, _p(image), image.shape[1], image.shape[0], image.strides[0], C.byref(t)))
+        return t.value
+
+    def collect(self, ticket, w, h):
+        cap = self.max_keypoints(w, h)
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int(0)
+        _check(self._L.orbgpu_collect(self._h, ticket, _p(kps), _p(desc), cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def queue_depth(self):
+        return _check(self._L.orbgpu_queue_depth(self._h))
+
+    # mvImagePyramid, include/ORBextractor.h:85
+    def pyramid_level(self, level, bordered=False):
+        w, h = C.c_int(), C.c_int()
+        _check(self._L.orbgpu_pyramid_level(self._h, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        _check(self._L.orbgpu_pyramid_level(self._h, level, _p(out), w.value, C.byref(w), C.byref(h)))
+        return np.pad(out, 19, mode="reflect") if bordered else out
+
+    def debug_blurred(self, level):
+        w, h = C.c_int(), C.c_int()
+        _check(self._L.orbgpu_pyramid_level(self._h, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        _check(self._L.orbgpu_debug_level_blurred(self._h, level, _p(out), w.value))
+        return out
+
+    def _cands(self, fn, level):
+        cap = 1 << 16
+        while True:
+            x = np.zeros(cap, np.int32); y = np.zeros(cap, np.int32); s = np.zeros(cap, np.int32)
+            n = _check(fn(self._h, level, _p(x), _p(y), _p(s), cap))
+            if n <= cap:
+                return np.stack([x[:n], y[:n], s[:n]], 1)
+            cap = n
+
+    def debug_candidates(self, level): return self._cands(self._L.orbgpu_debug_level_candidates, level)
+    def debug_selected(self, level): return self._cands(self._L.orbgpu_debug_level_selected, level)
+
+    def octree(self, xs, ys, resp, W, H, N):
+        xs = np.ascontiguousarray(xs, np.int32); ys = np.ascontiguousarray(ys, np.int32); resp = np.ascontiguousarray(resp, np.int32)
+        out = np.zeros(len(xs) + 8, np.int32)
+        n = _check(self._L.orbgpu_octree(self._h, _p(xs), _p(ys), _p(resp), len(xs), W, H, N, _p(out), len(out)))
+        return out[:n].copy()
+
+    def set_profiling(self, on): _check(self._L.orbgpu_set_profiling(self._h, int(on)))
+
+    def stage_ms(self, reset=True):
+        ms = np.zeros(NUM_STAGES, np.float64)
+        _check(self._L.orbgpu_get_stage_ms(self._h, _p(ms), NUM_STAGES, int(reset)))
+        return dict(zip(STAGE_NAMES, ms.tolist()))
+
+    def launch_count(self): return int(self._L.orbgpu_launch_count(self._h))
+
+
+class ORBmatcher:
+    """The Hamming part of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-102): the static
+    DescriptorDistance, the constants, and the batched best/second-best scan + all-pairs counts."""
+    TH_LOW = 50        # src/ORBmatcher.cc:38
+    TH_HIGH = 100      # :37
+    HISTO_LENGTH = 30  # :39
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio = np.float32(nnratio)
+        self.mbCheckOrientation = checkOri
+        self.device = device
+        self._L = lib()
+        self._m = None
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return lib().orbgpu_hamming256(_p(a), _p(b))
+
+    def match_bruteforce(self, A, B):
+        A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)
+        bi = np.zeros(len(A), np.int32); b1 = np.zeros(len(A), np.uint16); b2 = np.zeros(len(A), np.uint16)
+        _check(self._L.orbgpu_match_bruteforce(self.device, _p(A), len(A), _p(B), len(B), _p(bi), _p(b1), _p(b2)))
+        return bi, b1, b2
+
+    def _matcher(self):
+        if self._m is None:
+            self._m = C.c_void_p()
+            _check(self._L.orbgpu_matcher_create(C.byref(self._m), self.device))
+        return self._m
+
+    def set_keyframes(self, desc):
+        """desc: [K, n, 32] uint8 host array."""
+        desc = np.ascontiguousarray(desc, np.uint8)
+        _check(self._L.orbgpu_matcher_set_keyframes(self._matcher(), _p(desc), desc.shape[0], desc.shape[1]))
+
+    def set_keyframes_device(self, ptr, K, n):
+        _check(self._L.orbgpu_matcher_set_keyframes_device(self._matcher(), ptr, K, n))
+
+    def count_pairs(self, kf_a, kf_b, th_low=None):
+        a = np.ascontiguousarray(kf_a, np.int32); b = np.ascontiguousarray(kf_b, np.int32)
+        out = np.zeros(len(a), np.int32)
+        _check(self._L.orbgpu_matcher_count_pairs(self._matcher(), _p(a), _p(b), len(a),
+                                                  self.TH_LOW if th_low is None else th_low, float(self.mfNNratio), _p(out)))
+        return out
+
+    def count_pairs_device(self, pairs_ptr, num_pairs, counts_ptr, th_low=None):
+        _check(self._L.orbgpu_matcher_count_pairs_device(self._matcher(), pairs_ptr, num_pairs,
+                                                         self.TH_LOW if th_low is None else th_low, float(self.mfNNratio), counts_ptr))
+
+    def last_kernel_ms(self):
+        return float(self._L.orbgpu_matcher_last_kernel_ms(self._matcher()))
+
+    def close(self):
+        if self._m is not None:
+            self._L.orbgpu_matcher_destroy(self._m)
+            self._m = None
+
+    __del__ = close
