@@ -115,6 +115,14 @@ int orbgpu_debug_level_selected(orbgpu_extractor* e, int level, int* x, int* y, 
 int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* resp, int n,
                   int W, int H, int N, int* out_idx, int cap);
 
+/* Test hooks for the float steps that decide descriptor bits: cv::fastAtan2 (src/ORBextractor.cc:105)
+ * and cos/sin of the keypoint angle (:115) exactly as the kernels evaluate them.  Host arrays.
+ * sincos_checksum folds (x, sin x, cos x) of the float bit patterns first_bits + i*step, i < count,
+ * into an order-independent 64-bit sum (oracle/orb_prims.c computes the same sum with glibc's sincosf). */
+int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg);
+int orbgpu_debug_sincosf(orbgpu_extractor* e, const float* rad, int n, float* out_sin, float* out_cos);
+int orbgpu_debug_sincos_checksum(orbgpu_extractor* e, uint32_t first_bits, uint32_t count, uint32_t step, uint64_t* checksum);
+
 /* Profiling: with profiling on, CUDA events bracket every stage of each chunk on its stream.
  * orbgpu_get_stage_ms returns accumulated milliseconds per stage since the last reset:
  * [0] upload, [1] pyramid, [2] FAST cells, [3] octree, [4] blur, [5] orientation+descriptors,

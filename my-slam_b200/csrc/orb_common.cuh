@@ -103,3 +103,6 @@ int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N,
                              int key_smem_cap, int node_smem_cap, cudaStream_t st);
 int orb_upload_constants(const int* umax16);
 int orb_fast_smem_bytes(int max_cw, int max_ch);
+int orb_debug_atan2(const float* d_y, const float* d_x, int n, float* d_out, cudaStream_t st);
+int orb_debug_sincosf(const float* d_rad, int n, float* d_s, float* d_c, cudaStream_t st);
+int orb_debug_sincos_checksum(unsigned first_bits, unsigned count, unsigned step, unsigned long long* d_sum, cudaStream_t st);

@@ -746,6 +746,59 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
 
 int orb_launch_describe(const OrbPlanDev& P, int nframes, cudaStream_t st)
 {
-    k_describe<<<dim3((P.sel_total + 7) / 8, nframes), 256, 0, st>>>(P);
+    k_describe<<<dim3(P.sel_total > 0 ? (P.sel_total + 7) / 8 : 1, nframes), 256, 0, st>>>(P);   // >= 1 block: block 0 writes nout
+    return 1;
+}
+
+// =================================================================================================
+// Test hooks for the float steps that decide descriptor bits (orbgpu_debug_* in include/orbgpu.h).
+// =================================================================================================
+__global__ void k_debug_atan2(const float* y, const float* x, int n, float* out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = orb_fast_atan2(y[i], x[i]);
+}
+
+__global__ void k_debug_sincosf(const float* rad, int n, float* s, float* c)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) orb_sincosf(rad[i], &s[i], &c[i]);
+}
+
+__device__ __host__ inline unsigned long long orb_mix64(unsigned bits, unsigned sbits, unsigned cbits)
+{
+    unsigned long long h = (unsigned long long)bits * 0x9E3779B97F4A7C15ull ^ (((unsigned long long)sbits << 32) | cbits);
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    return h;
+}
+
+__global__ void k_debug_sincos_checksum(unsigned first_bits, unsigned count, unsigned step, unsigned long long* sum)
+{
+    unsigned long long acc = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < count;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned bits = first_bits + (unsigned)i * step;
+        float s, c;
+        orb_sincosf(__uint_as_float(bits), &s, &c);
+        acc += orb_mix64(bits, __float_as_uint(s), __float_as_uint(c));
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0) atomicAdd(sum, acc);
+}
+
+int orb_debug_atan2(const float* d_y, const float* d_x, int n, float* d_out, cudaStream_t st)
+{
+    k_debug_atan2<<<(n + 255) / 256, 256, 0, st>>>(d_y, d_x, n, d_out);
+    return 1;
+}
+int orb_debug_sincosf(const float* d_rad, int n, float* d_s, float* d_c, cudaStream_t st)
+{
+    k_debug_sincosf<<<(n + 255) / 256, 256, 0, st>>>(d_rad, n, d_s, d_c);
+    return 1;
+}
+int orb_debug_sincos_checksum(unsigned first_bits, unsigned count, unsigned step, unsigned long long* d_sum, cudaStream_t st)
+{
+    k_debug_sincos_checksum<<<148 * 8, 256, 0, st>>>(first_bits, count, step, d_sum);
     return 1;
 }

@@ -807,6 +807,56 @@ int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* 
     return count;
 }
 
+// ---- float-step test hooks ------------------------------------------------------------------------
+int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg)
+{
+    if (!e || !y || !x || !out_deg || n < 1) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    float* d = nullptr;
+    CU(cudaMalloc(&d, 3 * sizeof(float) * (size_t)n));
+    CU(cudaMemcpy(d, y, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d + n, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
+    orb_debug_atan2(d, d + n, n, d + 2 * (size_t)n, 0);
+    e->launches += 1;
+    CU(cudaMemcpy(out_deg, d + 2 * (size_t)n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return ORBGPU_OK;
+}
+
+int orbgpu_debug_sincosf(orbgpu_extractor* e, const float* rad, int n, float* out_sin, float* out_cos)
+{
+    if (!e || !rad || !out_sin || !out_cos || n < 1) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    float* d = nullptr;
+    CU(cudaMalloc(&d, 3 * sizeof(float) * (size_t)n));
+    CU(cudaMemcpy(d, rad, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
+    orb_debug_sincosf(d, n, d + n, d + 2 * (size_t)n, 0);
+    e->launches += 1;
+    CU(cudaMemcpy(out_sin, d + n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out_cos, d + 2 * (size_t)n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return ORBGPU_OK;
+}
+
+int orbgpu_debug_sincos_checksum(orbgpu_extractor* e, uint32_t first_bits, uint32_t count, uint32_t step, uint64_t* checksum)
+{
+    if (!e || !checksum) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    unsigned long long* d = nullptr;
+    CU(cudaMalloc(&d, sizeof(unsigned long long)));
+    CU(cudaMemset(d, 0, sizeof(unsigned long long)));
+    orb_debug_sincos_checksum(first_bits, count, step, d, 0);
+    e->launches += 1;
+    unsigned long long h = 0;
+    CU(cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    *checksum = h;
+    return ORBGPU_OK;
+}
+
 int orbgpu_set_profiling(orbgpu_extractor* e, int on)
 {
     if (!e) return ORBGPU_ERR_ARG;

@@ -50,6 +50,9 @@ def lib():
         "orbgpu_debug_level_candidates": (i32, [vp, i32, vp, vp, vp, i32]),
         "orbgpu_debug_level_selected": (i32, [vp, i32, vp, vp, vp, i32]),
         "orbgpu_octree": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp, i32]),
+        "orbgpu_debug_atan2": (i32, [vp, vp, vp, i32, vp]),
+        "orbgpu_debug_sincosf": (i32, [vp, vp, i32, vp, vp]),
+        "orbgpu_debug_sincos_checksum": (i32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(u64)]),
         "orbgpu_set_profiling": (i32, [vp, i32]),
         "orbgpu_get_stage_ms": (i32, [vp, vp, i32, i32]),
         "orbgpu_launch_count": (u64, [vp]),
@@ -209,6 +212,23 @@ class ORBextractor:
         out = np.zeros(len(xs) + 8, np.int32)
         n = _check(self._L.orbgpu_octree(self._h, _p(xs), _p(ys), _p(resp), len(xs), W, H, N, _p(out), len(out)))
         return out[:n].copy()
+
+    def debug_atan2(self, y, x):
+        y = np.ascontiguousarray(y, np.float32); x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros(len(y), np.float32)
+        _check(self._L.orbgpu_debug_atan2(self._h, _p(y), _p(x), len(y), _p(out)))
+        return out
+
+    def debug_sincosf(self, rad):
+        rad = np.ascontiguousarray(rad, np.float32)
+        s = np.zeros(len(rad), np.float32); c = np.zeros(len(rad), np.float32)
+        _check(self._L.orbgpu_debug_sincosf(self._h, _p(rad), len(rad), _p(s), _p(c)))
+        return s, c
+
+    def debug_sincos_checksum(self, first_bits, count, step=1):
+        h = C.c_uint64(0)
+        _check(self._L.orbgpu_debug_sincos_checksum(self._h, first_bits, count, step, C.byref(h)))
+        return h.value
 
     def set_profiling(self, on): _check(self._L.orbgpu_set_profiling(self._h, int(on)))
 

@@ -281,3 +281,22 @@ void orbo_sincosf(float y, float* sinp, float* cosp)
     float fc = (float)fma(cp, x6, c);
     if (n & 1) { *sinp = fc; *cosp = fs; } else { *sinp = fs; *cosp = fc; }
 }
+
+/* Order-independent checksum of (x, sin x, cos x) over the float bit patterns first + i*step, i < count.
+ * which = 0: this file's restatement; 1: the host's glibc sincosf.  Same mixing as the CUDA test hook. */
+extern void sincosf(float, float*, float*);
+uint64_t orbo_sincos_checksum(uint32_t first, uint32_t count, uint32_t step, int which)
+{
+    uint64_t sum = 0;
+    for (uint32_t i = 0; i < count; ++i) {
+        uint32_t bits = first + i * step, sb, cb;
+        float x, s, c;
+        memcpy(&x, &bits, 4);
+        if (which) sincosf(x, &s, &c); else orbo_sincosf(x, &s, &c);
+        memcpy(&sb, &s, 4); memcpy(&cb, &c, 4);
+        uint64_t h = (uint64_t)bits * 0x9E3779B97F4A7C15ull ^ (((uint64_t)sb << 32) | cb);
+        h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+        sum += h;
+    }
+    return sum;
+}

@@ -61,6 +61,9 @@ float orbo_fast_atan2(float y, float x);
  * evaluation with fused multiply-adds).  Valid for |x| < 120. */
 void orbo_sincosf(float x, float* s, float* c);
 
+/* checksum of (x, sin x, cos x) over float bit patterns; which = 0 restatement, 1 host glibc */
+uint64_t orbo_sincos_checksum(uint32_t first, uint32_t count, uint32_t step, int which);
+
 #ifdef __cplusplus
 }
 #endif
