@@ -1,0 +1,433 @@
+#!/usr/bin/env python
+"""bench.py -- ORB extraction throughput (frames/s) of the orbgpu CUDA path on 1..8 B200s.
+
+Workload = BASELINE.json configs[0] (the shape the metric is quoted on): synthetic 640x480 grayscale
+frames, nFeatures=1000, 8 levels, scale 1.2, iniThFAST 20 / minThFAST 7.  A "step" is one pass of the
+whole hot path (pyramid -> FAST cells -> octree -> blur -> orientation + rBRIEF) over one batch of
+FRAMES_PER_STEP frames per GPU.  Frames shard across ranks with no data-path collective (weak scaling:
+every rank owns its own batch); torch.distributed is used only for the barrier and the max over ranks.
+
+  value          frames already resident in HBM, device buffers in and out (orbgpu_extract_batch_device)
+  e2e            the same batch from pinned HOST memory through orbgpu_extract_batch: H2D of the frames
+                 and D2H of keypoints + descriptors + counts inside the timed region
+  roofline       dominant kernel stage: algorithmic bytes per launch / CUDA-event duration of the launch
+                 on the library's own stream, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline   the UNMODIFIED reference ORBextractor (oracle/_ref, built against oracle/cvshim) timed
+                 on this box's host cores, bounded sample (rank 0, N=1 only)
+  --impl reference   the reference arm: that CPU extractor on all host threads, same metric and config
+
+torch is plumbing here (device buffers, pinned buffers, NCCL barrier); every kernel in the timed region
+is ours (liborbgpu.so).  There is no CPU fallback: without the library or a GPU this script fails.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOAD = "C1_tum_640x480_nf1000"
+PARAMS = dict(nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7)
+FRAMES_PER_STEP = 512            # per GPU: 512 x 307200 B = 157 MB of input per step > 126 MB L2
+METRIC = "orb_extract_frames_per_s_640x480_1000kp"
+UNIT = "frames/s"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def make_frames(pkg, count, start):
+    w, h, _, base, _ = pkg.synth.CONFIGS[WORKLOAD]
+    out = np.empty((count, h, w), np.uint8)
+    for i in range(count):
+        out[i] = pkg.synth.synth(w, h, base + start + i)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md "clocks line"), via NVML, nvidia-smi as fallback
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    BAD = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
+
+    def __init__(self, index):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nvml = None
+
+    def _poll_nvml(self):
+        n = self._nvml
+        names = {"hw_slowdown": getattr(n, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(n, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(n, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(n, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM))
+                mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def _poll_smi(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        keys = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.samples.append(int(float(f[0])))
+                self.max_mhz = int(float(f[1]))
+                for k, v in zip(keys, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._thr = threading.Thread(target=self._poll_nvml if self._nvml else self._poll_smi, daemon=True)
+        self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=10)
+        med = int(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# algorithmic bytes (DESIGN.md "Measurement")
+# ---------------------------------------------------------------------------------------------------
+def level_sizes(w, h, nlevels, scale):
+    sf = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        sf.append(np.float32(np.float64(sf[-1]) * np.float64(np.float32(scale))))
+    out = []
+    for s in sf:
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes(w, h, nfeatures, nlevels, scale):
+    """Per-frame algorithmic bytes of the whole path and of each kernel stage."""
+    lv = level_sizes(w, h, nlevels, scale)
+    px = [a * b for a, b in lv]
+    P0, P = px[0], sum(px)
+    path = P0 + (P - P0) + P + 60 * nfeatures          # read source, write levels 1.., read every level once, write records
+    stage = {
+        "pyramid": (P - px[-1]) + (P - P0),            # read levels 0..L-2, write levels 1..L-1
+        "fast_cells": P,                               # read every level once (candidates stay on chip / tiny)
+        "octree": 8 * nfeatures,                       # candidate words in, survivor words out: latency-bound, not HBM
+        "blur": 2 * P,                                 # read level, write blurred level
+        "describe": nfeatures * (749 + 512 + 60),      # disc pixels + sample pixels + 28 B keypoint + 32 B descriptor
+    }
+    return path, stage
+
+
+# ---------------------------------------------------------------------------------------------------
+# the reference's CPU extractor on this box's host cores (oracle/_ref = unmodified src/ORBextractor.cc)
+# ---------------------------------------------------------------------------------------------------
+def cpu_extractor_fps(frames, threads, target_s):
+    """Times the reference CPU extractor over `frames` (bounded sample), repeating the sample until about
+    target_s seconds of wall time have been spent.  Returns (frames/s, kind, seconds, frames processed)."""
+    import oracle_lib
+    p = PARAMS
+    if oracle_lib.have_ref():
+        ref = oracle_lib.OracleRef(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"])
+        ref.bench(frames[:max(threads, 1)], threads, 1)                       # warm the per-thread arenas
+        sec, _ = ref.bench(frames, threads, 1)
+        reps = int(max(1, min(100000, round(target_s / max(sec, 1e-3)))))
+        sec, _ = ref.bench(frames, threads, reps)
+        return len(frames) * reps / sec, "reference", sec, len(frames) * reps
+    port = oracle_lib.OraclePort(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"])
+    t0 = time.perf_counter()
+    done = 0
+    while True:
+        for f in frames:
+            port.extract(f)
+            done += 1
+        if time.perf_counter() - t0 >= target_s:
+            break
+    sec = time.perf_counter() - t0
+    return done / sec, "port", sec, done
+
+
+def run_reference(args, rank):
+    """Reference arm: the reference's own CPU implementation of the path, all host threads."""
+    if rank != 0:
+        return 0
+    import __graft_entry__ as g
+    pkg = g.load_package()
+    w, h, nf, _, _ = pkg.synth.CONFIGS[WORKLOAD]
+    import oracle_lib
+    threads = host_threads() if oracle_lib.have_ref() else 1
+    sample = max(32, 4 * threads)
+    frames = make_frames(pkg, sample, 0)
+    per_step_s = max(2.0, min(15.0, 150.0 / max(args.steps + args.warmup, 1)))
+    for _ in range(args.warmup):
+        cpu_extractor_fps(frames, threads, per_step_s * 0.25)
+    tot_frames, tot_s, kind = 0, 0.0, "reference"
+    for _ in range(args.steps):
+        fps, kind, sec, n = cpu_extractor_fps(frames, threads, per_step_s)
+        tot_frames += n
+        tot_s += sec
+    value = tot_frames / tot_s
+    sample_txt = "%d synthetic %dx%d frames (seeds 0x5EED0000+i), repeated ~%.0f s per step on %d threads; CPU %s" % (
+        sample, w, h, per_step_s, threads, cpu_model())
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "nfeatures": nf, "nlevels": PARAMS["nlevels"], "scale": PARAMS["scale"],
+                   "ini_th": PARAMS["ini_th"], "min_th": PARAMS["min_th"], "width": w, "height": h,
+                   "note": "host CPU only; does not scale with --gpus"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample_txt},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    pkg = g.load_package()
+    if not torch.cuda.is_available() or pkg.device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device visible; the orbgpu path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    p = PARAMS
+    w, h, nf, _, _ = pkg.synth.CONFIGS[WORKLOAD]
+    n = args.frames
+    ex = pkg.ORBextractor(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"], device=local_rank)
+    cap = ex.max_keypoints(w, h)
+
+    # synthetic frames: every rank owns its own batch (weak scaling)
+    h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
+    h_frames.numpy()[:] = make_frames(pkg, n, rank * n)
+    d_frames = h_frames.cuda()
+    d_kps = torch.empty((n, cap, 28), dtype=torch.uint8, device="cuda")
+    d_desc = torch.empty((n, cap, 32), dtype=torch.uint8, device="cuda")
+    d_nout = torch.empty((n,), dtype=torch.int32, device="cuda")
+    h_kps = torch.empty((n, cap, 28), dtype=torch.uint8, pin_memory=True)
+    h_desc = torch.empty((n, cap, 32), dtype=torch.uint8, pin_memory=True)
+    h_nout = torch.empty((n,), dtype=torch.int32, pin_memory=True)
+
+    def step_device():
+        ex.extract_batch_ptr(d_frames.data_ptr(), n, w, h, w, w * h, d_kps.data_ptr(), d_desc.data_ptr(), cap,
+                             d_nout.data_ptr(), device=True)
+        return ex.last_batch_ms()
+
+    def step_host():
+        ex.extract_batch_ptr(h_frames.data_ptr(), n, w, h, w, w * h, h_kps.data_ptr(), h_desc.data_ptr(), cap,
+                             h_nout.data_ptr(), device=False)
+        return ex.last_batch_ms()
+
+    sampler = ClockSampler(local_rank)
+
+    # ---- device-resident: `value`
+    for _ in range(args.warmup):
+        step_device()
+    ex.set_profiling(True)
+    ex.stage_ms(reset=True)
+    barrier()
+    sampler.start()
+    l0 = ex.launch_count()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        dev_ms += step_device()
+    barrier()
+    wall_dev_ms = (time.perf_counter() - t0) * 1e3
+    launches = ex.launch_count() - l0
+    stage = ex.stage_ms(reset=True)
+    ex.set_profiling(False)
+    dev_ms = max_over_ranks(dev_ms)
+    wall_dev_ms = max_over_ranks(wall_dev_ms)
+    nkp_dev = int(d_nout.sum().item())
+
+    # ---- end to end from pinned host memory: `e2e`
+    for _ in range(args.warmup):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_ms = 0.0
+    for _ in range(args.steps):
+        e2e_ms += step_host()
+    barrier()
+    wall_e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    e2e_ms = max_over_ranks(e2e_ms)
+    wall_e2e_ms = max_over_ranks(wall_e2e_ms)
+    nkp_host = int(h_nout.numpy().sum())
+    if nkp_host != nkp_dev or not np.array_equal(h_nout.numpy(), d_nout.cpu().numpy()):
+        raise RuntimeError("host-buffer and device-buffer paths disagree on keypoint counts")
+    total_launches = sum_over_ranks(float(launches))
+
+    total_frames = n * world * args.steps
+    value = total_frames / (dev_ms * 1e-3)
+    e2e_value = total_frames / (max(e2e_ms, wall_e2e_ms) * 1e-3)      # the slower of device events and host wall clock
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel stage (rank 0's own stream events)
+    peak, peak_src = load_peaks()
+    path_bytes, stage_bytes = algorithmic_bytes(w, h, p["nfeatures"], p["nlevels"], p["scale"])
+    kstages = {k: stage[k] for k in ("pyramid", "fast_cells", "octree", "blur", "describe")}
+    dom = max(kstages, key=kstages.get)
+    per_chunk_launches = (p["nlevels"] - 1) + 4
+    chunks = max(1, int(round(launches / per_chunk_launches)))
+    frames_per_launch = n * args.steps / chunks
+    launch_ms = kstages[dom] / chunks
+    achieved = stage_bytes[dom] * frames_per_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+    roofline = {
+        "bound": "hbm", "kernel": {"pyramid": "k_resize_level (x%d levels)" % (p["nlevels"] - 1), "fast_cells": "k_fast_cells",
+                                   "octree": "k_octree", "blur": "k_blur", "describe": "k_describe"}[dom],
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "peak_source": peak_src, "bytes_per_frame": stage_bytes[dom], "frames_per_launch": frames_per_launch,
+        "launch_ms": launch_ms,
+        "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
+        "path_bytes_per_frame": path_bytes,
+        "path_achieved": value / world * path_bytes / 1e9, "path_frac": value / world * path_bytes / 1e9 / peak,
+        "note": "stage times are CUDA events on the library's 3 chunk streams; chunks overlap, so each stage time "
+                "includes sharing the GPU with the other streams' kernels",
+    }
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "nfeatures": nf, "nlevels": p["nlevels"], "scale": p["scale"],
+                   "ini_th": p["ini_th"], "min_th": p["min_th"], "width": w, "height": h,
+                   "frames_per_step_per_gpu": n, "parallelism": "frames sharded %d-way, no data-path collective" % world,
+                   "l2": "inputs larger than L2: %.0f MB of frames per step vs %.0f MB L2" % (n * w * h / 1e6, L2_BYTES / 1e6),
+                   "keypoints_per_step_per_gpu": nkp_dev},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * w * h * world,
+                "d2h_bytes_per_step": (n * cap * 60 + 4 * n) * world,
+                "ms_per_step_events": e2e_ms / args.steps, "ms_per_step_wall": wall_e2e_ms / args.steps},
+        "gpu_launches": int(total_launches),
+        "wall_ms_per_step": wall_dev_ms / args.steps,
+        "roofline": roofline,
+    }
+    if world == 1 and not args.no_cpu:
+        threads = host_threads()
+        sample = max(32, 4 * threads)
+        fps, kind, sec, done = cpu_extractor_fps(make_frames(pkg, sample, 0), threads if True else 1, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads if kind == "reference" else 1, "kind": kind,
+                                "sample": "%d synthetic %dx%d frames x %d passes = %.1f s on %d threads (one extractor per thread); CPU %s"
+                                          % (sample, w, h, done // sample, sec, threads if kind == "reference" else 1, cpu_model())}
+        if kind == "reference":
+            fps1, _, sec1, done1 = cpu_extractor_fps(make_frames(pkg, 16, 0), 1, min(args.cpu_seconds, 5.0))
+            line["cpu_baseline"]["single_thread_value"] = fps1
+    if world > 1:
+        dist.destroy_process_group()
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=FRAMES_PER_STEP, help="frames per step per GPU")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="wall time budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank)
+    if world == 1 and args.gpus > 1:
+        # convenience: python bench.py --gpus N re-launches itself under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -131,6 +131,9 @@ int orbgpu_debug_sincos_checksum(orbgpu_extractor* e, uint32_t first_bits, uint3
 int orbgpu_set_profiling(orbgpu_extractor* e, int on);
 int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset);
 uint64_t orbgpu_launch_count(orbgpu_extractor* e);
+/* Device time (ms) of the most recent orbgpu_extract / _batch / _batch_device call: CUDA events on the
+ * library's own streams, from before the first upload/kernel to after the last kernel/download. */
+double orbgpu_last_batch_ms(orbgpu_extractor* e);
 
 /* ---- matcher ------------------------------------------------------------------------------- */
 

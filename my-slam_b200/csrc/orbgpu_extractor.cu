@@ -95,6 +95,8 @@ struct orbgpu_extractor {
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
+    cudaEvent_t ev_batch0 = nullptr, ev_batch1 = nullptr;   // bracket the most recent batch call on ctx[0].st
+    double last_batch_ms = 0;
     int last_ctx = -1;                 // context holding the most recent single frame (pyramid / debug views)
     // scratch for orbgpu_octree
     uint8_t* d_oct_scratch = nullptr; size_t oct_scratch_bytes = 0;
@@ -467,6 +469,29 @@ static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, i
     return ORBGPU_OK;
 }
 
+// Device-side bracket of one batch call: begin is recorded on ctx[0].st before any chunk is enqueued
+// (all streams are idle between calls); end is recorded on ctx[0].st after it has been made to wait
+// for the last chunk of every other stream.
+static int batch_begin(orbgpu_extractor* e)
+{
+    CU(cudaEventRecord(e->ev_batch0, e->ctx[0].st));
+    return ORBGPU_OK;
+}
+static int batch_end(orbgpu_extractor* e)
+{
+    for (int s = 1; s < NSTREAM; ++s)
+        if (e->ctx[s].busy) CU(cudaStreamWaitEvent(e->ctx[0].st, e->ctx[s].done, 0));
+    CU(cudaEventRecord(e->ev_batch1, e->ctx[0].st));
+    return ORBGPU_OK;
+}
+static void batch_collect_ms(orbgpu_extractor* e)
+{
+    float ms = 0.f;
+    if (cudaEventSynchronize(e->ev_batch1) == cudaSuccess && cudaEventElapsedTime(&ms, e->ev_batch0, e->ev_batch1) == cudaSuccess)
+        e->last_batch_ms = ms;
+    else { cudaGetLastError(); e->last_batch_ms = 0; }
+}
+
 // =================================================================================================
 // C ABI
 // =================================================================================================
@@ -518,6 +543,7 @@ int orbgpu_create(orbgpu_extractor** out, int device, int nfeatures, float scale
         for (int k = 0; k < EV_COUNT; ++k) cudaEventCreate(&c.ev[k]);
         cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming);
     }
+    cudaEventCreate(&e->ev_batch0); cudaEventCreate(&e->ev_batch1);
     *out = e;
     return ORBGPU_OK;
 }
@@ -534,6 +560,8 @@ void orbgpu_destroy(orbgpu_extractor* e)
         if (c.done) cudaEventDestroy(c.done);
         if (c.st) cudaStreamDestroy(c.st);
     }
+    if (e->ev_batch0) cudaEventDestroy(e->ev_batch0);
+    if (e->ev_batch1) cudaEventDestroy(e->ev_batch1);
     e->plan.free_dev();
     cudaFree(e->d_oct_scratch);
     delete e;
@@ -575,6 +603,7 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
     const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
     const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
     int result = ORBGPU_OK, k = 0;
+    if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
         StreamCtx& c = e->ctx[k % NSTREAM];
         const int m = std::min(chunk, n - i0);
@@ -584,8 +613,10 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
                           kps + (size_t)i0 * capacity, desc + (size_t)i0 * capacity * 32, n_out + i0, capacity, pin_out);
         if (rc != ORBGPU_OK) { result = rc; break; }
     }
+    if (result == ORBGPU_OK) result = batch_end(e);
     for (int s = 0; s < NSTREAM; ++s)
         if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) result = rc;
+    batch_collect_ms(e);
     e->last_ctx = (n == 1 && result == ORBGPU_OK) ? 0 : -1;
     return result;
 }
@@ -609,6 +640,7 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
     const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
     int result = ORBGPU_OK, k = 0;
+    if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
         StreamCtx& c = e->ctx[k % NSTREAM];
         const int m = std::min(chunk, n - i0);
@@ -623,8 +655,10 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
         CU(cudaEventRecord(c.done, c.st));
         c.busy = true; c.profiled = prof; c.job_frames = m; c.staged_out = false; c.user_nout = nullptr;
     }
+    if (result == ORBGPU_OK) result = batch_end(e);
     for (int s = 0; s < NSTREAM; ++s)
         if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) result = rc;
+    batch_collect_ms(e);
     e->last_ctx = -1;
     return result;
 }
@@ -873,5 +907,7 @@ int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset)
 }
 
 uint64_t orbgpu_launch_count(orbgpu_extractor* e) { return e ? e->launches : 0; }
+
+double orbgpu_last_batch_ms(orbgpu_extractor* e) { return e ? e->last_batch_ms : 0.0; }
 
 }  // extern "C"
