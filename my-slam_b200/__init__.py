@@ -6,4 +6,4 @@ directory name has a hyphen, so import it through __graft_entry__.load_package()
 `my_slam_b200`).
 """
 from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path)  # noqa: F401
-from . import synth  # noqa: F401
+from . import shard, synth  # noqa: F401
