@@ -18,6 +18,8 @@
 #define ORB_BORDER 16        // EDGE_THRESHOLD - 3: origin of the FAST cell grid, :773
 #define ORB_HALF_PATCH 15    // HALF_PATCH_SIZE, :75
 #define ORB_PATCH 31         // PATCH_SIZE, :74
+#define ORB_BLUR_ROWS 28     // output rows per k_blur thread
+#define ORB_BLUR_THREADS 128 // tasks per k_blur CTA
 
 struct OrbLevel {
     int w, h, pitch;             // level size; pitch of pyr/blur rows for this level

@@ -30,45 +30,113 @@ int orb_upload_constants(const int* umax16)
 // (source index, weights) are built on the host in double/float exactly as OpenCV does.
 // One thread = 4 horizontally adjacent output pixels = one aligned 32-bit store.
 // =================================================================================================
-__global__ void __launch_bounds__(256) k_resize_level(OrbPlanDev P, int l)
+#define RS_ROWS 8             // output rows per thread
+#define RS_THREADS 128
+
+// horizontal pass of one source row for this thread's 4 output pixels: H[j] = S[s_j]*a0_j + S[s_j + 1]*a1_j.
+// WORDS: the 4 pixel pairs lie inside three aligned words starting at word wb (byte offsets o_j = s_j - 4wb).
+template <bool WORDS>
+__device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int wb, int wlast, const int s[4], const int o[4],
+                                            const unsigned a01[4], int sw, int H[4])
+{
+    if (WORDS) {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(row);
+        const unsigned w0 = __ldg(p + wb), w1 = __ldg(p + min(wb + 1, wlast)), w2 = __ldg(p + min(wb + 2, wlast));
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const unsigned pair = o[j] < 4 ? __funnelshift_r(w0, w1, 8 * o[j])
+                                  : o[j] < 8 ? __funnelshift_r(w1, w2, 8 * (o[j] - 4)) : w2 >> (8 * (o[j] - 8));
+            H[j] = (int)__dp2a_lo(a01[j], pair, 0u);           // a0 * byte0 + a1 * byte1
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            H[j] = (int)(__ldg(row + s[j]) * (a01[j] & 0xFFFFu) + __ldg(row + min(s[j] + 1, sw - 1)) * (a01[j] >> 16));
+    }
+}
+
+template <bool WORDS>
+__device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel& D, const uint8_t* __restrict__ src, int sp,
+                                             int sw, int sh, uint8_t* __restrict__ dst, int wc, int y0, const int s[4],
+                                             const int o[4], const unsigned a01[4], int wb, int wlast)
+{
+    int Ha[4], Hb[4], ya = -1, yb = -1;                        // cached horizontal rows (source row indices ya, yb)
+    const int yend = min(y0 + RS_ROWS, D.h);
+    for (int dy = y0; dy < yend; ++dy) {
+        const int sy = P.rs_ofs[D.yofs_off + dy];
+        const unsigned b01 = *reinterpret_cast<const unsigned*>(P.rs_a + 2 * (D.yofs_off + dy));
+        const int b0 = (int)(b01 & 0xFFFFu), b1 = (int)(b01 >> 16);
+        const int r0 = min(max(sy, 0), sh - 1), r1 = min(max(sy + 1, 0), sh - 1);
+        if (r0 == yb) {                                        // the usual step: last row's lower line is this row's upper line
+#pragma unroll
+            for (int j = 0; j < 4; ++j) Ha[j] = Hb[j];
+            ya = yb;
+        } else if (r0 != ya) {
+            resize_hrow<WORDS>(src + (size_t)r0 * sp, wb, wlast, s, o, a01, sw, Ha);
+            ya = r0;
+        }
+        if (r1 == ya) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) Hb[j] = Ha[j];
+            yb = ya;
+        } else if (r1 != yb) {
+            resize_hrow<WORDS>(src + (size_t)r1 * sp, wb, wlast, s, o, a01, sw, Hb);
+            yb = r1;
+        }
+        uint32_t packed = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int v = (((b0 * (Ha[j] >> 4)) >> 16) + ((b1 * (Hb[j] >> 4)) >> 16) + 2) >> 2;
+            packed |= (uint32_t)(v & 0xFF) << (8 * j);
+        }
+        *reinterpret_cast<uint32_t*>(dst + (size_t)dy * D.pitch + 4 * wc) = packed;
+    }
+}
+
+// One thread = 4 horizontally adjacent output pixels (one aligned 32-bit store per row) x RS_ROWS rows.  The
+// x-axis table entries of the 4 pixels stay in registers; a source row costs three aligned word loads and
+// four IDP.2A dot products, and is reused when consecutive output rows share it.
+__global__ void __launch_bounds__(RS_THREADS) k_resize_level(OrbPlanDev P, int l)
 {
     const OrbLevel& D = P.lv[l];
-    const int frame = blockIdx.z;
-    const int dx0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int dy = blockIdx.y * 8 + threadIdx.y;
-    if (dx0 >= D.w || dy >= D.h) return;
+    const int frame = blockIdx.y;
+    const int nwc = (D.w + 3) >> 2;
+    const int task = blockIdx.x * RS_THREADS + threadIdx.x;
+    const int strip = task / nwc, wc = task - strip * nwc;
+    const int y0 = strip * RS_ROWS;
+    if (y0 >= D.h) return;
     const int sw = P.lv[l - 1].w, sh = P.lv[l - 1].h;
     const uint8_t* __restrict__ src = orb_level_ptr(P, l - 1, frame);
     const int sp = orb_level_pitch(P, l - 1);
     uint8_t* __restrict__ dst = P.pyr + (long long)frame * P.pyr_frame_bytes + D.pyr_off;
 
-    const int sy = P.rs_ofs[D.yofs_off + dy];
-    const int b0 = P.rs_a[2 * (D.yofs_off + dy)], b1 = P.rs_a[2 * (D.yofs_off + dy) + 1];
-    const int y0 = min(max(sy, 0), sh - 1), y1 = min(max(sy + 1, 0), sh - 1);
-    const uint8_t* __restrict__ S0 = src + (long long)y0 * sp;
-    const uint8_t* __restrict__ S1 = src + (long long)y1 * sp;
-    uint32_t packed = 0;
+    int s[4], o[4];
+    unsigned a01[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int dx = min(dx0 + i, D.w - 1);          // tail lanes recompute the last pixel (pitch is padded)
-        const int s = P.rs_ofs[D.xofs_off + dx];
-        const int a0 = P.rs_a[2 * (D.xofs_off + dx)], a1 = P.rs_a[2 * (D.xofs_off + dx) + 1];
-        const int s1 = min(s + 1, sw - 1);
-        const int h0 = S0[s] * a0 + S0[s1] * a1;
-        const int h1 = S1[s] * a0 + S1[s1] * a1;
-        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-        packed |= (uint32_t)(v & 0xFF) << (8 * i);
+    for (int j = 0; j < 4; ++j) {
+        const int dx = min(4 * wc + j, D.w - 1);               // tail lanes recompute the last pixel (pitch is padded)
+        s[j] = P.rs_ofs[D.xofs_off + dx];
+        a01[j] = *reinterpret_cast<const unsigned*>(P.rs_a + 2 * (D.xofs_off + dx));   // a0 | a1 << 16
     }
-    *reinterpret_cast<uint32_t*>(dst + (long long)dy * D.pitch + dx0) = packed;
+    const int smin = min(min(s[0], s[1]), min(s[2], s[3])), smax = max(max(s[0], s[1]), max(s[2], s[3]));
+    const int wb = smin >> 2;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = s[j] - 4 * wb;
+    // word path: rows 4-byte aligned and every (s_j, s_j + 1) pair inside words wb .. wb + 2 (clamped to the
+    // last word that lies inside the pitch; a pair byte beyond the row only ever meets weight a1 = 0)
+    const int wlast = (sp >> 2) - 1;
+    const bool words = ((sp & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 3) == 0) && (smax + 1 - 4 * wb <= 11) &&
+                       (wb + 2 <= wlast || 4 * wlast + 3 >= min(smax + 1, sw - 1));
+    if (words) resize_strip<true>(P, D, src, sp, sw, sh, dst, wc, y0, s, o, a01, wb, wlast);
+    else resize_strip<false>(P, D, src, sp, sw, sh, dst, wc, y0, s, o, a01, wb, wlast);
 }
 
 int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
 {
     int launches = 0;
     for (int l = 1; l < P.nlevels; ++l) {
-        dim3 block(32, 8);
-        dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + 7) / 8, nframes);
-        k_resize_level<<<grid, block, 0, st>>>(P, l);
+        const int ntask = ((P.lv[l].w + 3) / 4) * ((P.lv[l].h + RS_ROWS - 1) / RS_ROWS);
+        k_resize_level<<<dim3((ntask + RS_THREADS - 1) / RS_THREADS, nframes), RS_THREADS, 0, st>>>(P, l);
         ++launches;
     }
     return launches;
@@ -119,10 +187,22 @@ __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
     return max(lo, hi) - 256;
 }
 
+#define FAST_QCAP 256         // ring queue of quick-test survivors (per warp)
+#define FAST_CCAP 256         // corner list (per warp); denser cells take the dense NMS path
+
+// flags (bit 7 of each byte) of  max(a, b) > th  for 4 packed bytes, th <= 126; K = (127 - th) * 0x01010101
+__device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned b, unsigned K)
+{
+    return ((a & 0x7f7f7f7fu) + K) | a | ((b & 0x7f7f7f7fu) + K) | b;
+}
+
 __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, int tile_rows)
 {
     extern __shared__ __align__(16) uint8_t fast_smem[];
+    __shared__ uint16_t s_queue[FAST_WARPS][FAST_QCAP];
+    __shared__ uint16_t s_corner[FAST_WARPS][FAST_CCAP];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
     const int cell_id = blockIdx.x * FAST_WARPS + warp;
     const int frame = blockIdx.y;
     if (cell_id >= P.ncells) return;
@@ -134,71 +214,165 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
     uint32_t* cnt_out = P.cellcnt + (long long)frame * P.ncells + cell_id;
     if (iw <= 0 || ih <= 0) { if (lane == 0) *cnt_out = 0; return; }
 
-    // stage the cell image; zero the score map
-    const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame) + (long long)cell.ini_y * orb_level_pitch(P, l) + cell.ini_x;
+    // ---- stage the cell image (tile column = x - ini_x + sh); zero the score map
     const int pitch = orb_level_pitch(P, l);
-    for (int r = 0; r < ch; ++r) {
-        for (int c = lane; c < cw; c += 32) tile[r * FAST_TP + c] = __ldg(img + (long long)r * pitch + c);
+    const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame) + (long long)cell.ini_y * pitch + cell.ini_x;
+    int sh = 0;
+    if (((pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img - cell.ini_x) & 3) == 0)) {
+        sh = cell.ini_x & 3;                                   // aligned 32-bit loads, two rows per pass
+        const int nw = (cw + sh + 3) >> 2, c = lane & 15;
+        if (c < nw) {
+            const uint32_t* g = reinterpret_cast<const uint32_t*>(img - sh + (long long)(lane >> 4) * pitch) + c;
+            uint32_t* t = reinterpret_cast<uint32_t*>(tile + (lane >> 4) * FAST_TP) + c;
+            for (int r = lane >> 4; r < ch; r += 2, g += pitch >> 1, t += FAST_TP / 2) *t = __ldg(g);
+        }
+    } else {
+        for (int r = 0; r < ch; ++r)
+            for (int c = lane; c < cw; c += 32) tile[r * FAST_TP + c] = __ldg(img + (long long)r * pitch + c);
     }
     {
-        uint4* z = reinterpret_cast<uint4*>(smap);
-        const int n16 = FAST_TP * ch / 16;
-        for (int i = lane; i < n16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+        uint4* z = reinterpret_cast<uint4*>(smap + 2 * FAST_TP);            // rows 2 .. ih+3: interior + NMS rim
+        for (int i = lane; i < (ih + 2) * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncwarp();
 
-    const int tot = iw * ih;
-    const float inv_iw = 1.0f / (float)iw;
     const int base_th = min(P.ini_th, P.min_th);
-    for (int idx = lane; idx < tot; idx += 32) {
-        const int y = __float2int_rd(((float)idx + 0.5f) * inv_iw), x = idx - y * iw;
-        const int V = fast_arc_value(tile + (y + 3) * FAST_TP + (x + 3));
-        if (V > base_th) smap[(y + 3) * FAST_TP + (x + 3)] = (uint8_t)(V - 1);
+    const int cs = 3 + sh, ce = cs + iw;                       // interior tile columns [cs, ce), rows [3, 3 + ih)
+    const int w0 = cs >> 2, nwi = ((ce - 1) >> 2) - w0 + 1;    // words of a row that hold interior pixels
+    const int ntask = ih * nwi;
+    const float inv_nwi = 1.0f / (float)nwi;
+    uint16_t* q = s_queue[warp];
+    uint16_t* cl = s_corner[warp];
+    int head = 0, tail = 0, ncor = 0;
+
+    // scores 32 queued pixels with the arc network; corners go to the score map and the corner list
+#define FAST_DRAIN(active)                                                               \
+    {                                                                                    \
+        int o_ = 0, V_ = 0;                                                              \
+        if (active) { o_ = q[(head + lane) & (FAST_QCAP - 1)]; V_ = fast_arc_value(tile + o_); } \
+        const bool c_ = V_ > base_th;                                                    \
+        const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                             \
+        if (c_) {                                                                        \
+            smap[o_] = (uint8_t)(V_ - 1);                                                \
+            const int p_ = ncor + __popc(bc_ & lt);                                      \
+            if (p_ < FAST_CCAP) cl[p_] = (uint16_t)o_;                                   \
+        }                                                                                \
+        ncor += __popc(bc_);                                                             \
     }
+
+    // ---- pass 1: quick rejection, 4 pixels per lane.  A 9-arc always contains ring pixel 0 or 8 and pixel
+    //      4 or 12, so a corner needs max(|p0-v|,|p8-v|) > th and max(|p4-v|,|p12-v|) > th.
+    if (base_th <= 126) {
+        const unsigned K = (unsigned)(127 - base_th) * 0x01010101u;
+        for (int base = 0; base < ntask; base += 32) {
+            const int t = base + lane;
+            unsigned f = 0;
+            int off = 0;
+            if (t < ntask) {
+                const int yi = __float2int_rd(((float)t + 0.5f) * inv_nwi), wi = w0 + t - yi * nwi;
+                off = (yi + 3) * FAST_TP + 4 * wi;
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off);
+                const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
+                const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
+                f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & 0x80808080u;
+                if (4 * wi < cs) f &= 0xFFFFFFFFu << (8 * (cs - 4 * wi));
+                if (4 * wi + 4 > ce) f &= 0xFFFFFFFFu >> (8 * (4 * wi + 4 - ce));
+            }
+            if (__ballot_sync(0xffffffffu, f != 0) == 0) continue;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const bool on = (f >> (8 * b + 7)) & 1u;
+                const unsigned bal = __ballot_sync(0xffffffffu, on);
+                if (on) q[(tail + __popc(bal & lt)) & (FAST_QCAP - 1)] = (uint16_t)(off + b);
+                tail += __popc(bal);
+            }
+            __syncwarp();
+            while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
+            __syncwarp();
+        }
+    } else {                                                   // thresholds above 126: score every pixel
+        for (int i = 0; i < iw * ih; i += 32) {
+            const int idx = i + lane, y = idx / iw, x = idx - y * iw;
+            if (idx < iw * ih) q[lane] = (uint16_t)((y + 3) * FAST_TP + cs + x);
+            __syncwarp();
+            head = 0;
+            FAST_DRAIN(idx < iw * ih);
+            __syncwarp();
+        }
+        head = tail = 0;
+    }
+    FAST_DRAIN(lane < tail - head);
+#undef FAST_DRAIN
     __syncwarp();
 
-    // strict 8-neighbour maxima -> F (flat, reusing the tile memory), and "any survivor at iniTh"
-    uint8_t* F = tile;
+    // ---- pass 2: strict 8-neighbour maxima -> keep map (in the tile memory; the pixels are no longer needed)
+    uint8_t* keep = tile;
+    {
+        uint4* z = reinterpret_cast<uint4*>(keep + 3 * FAST_TP);
+        for (int i = lane; i < ih * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
     bool any_ini = false;
-    for (int idx = lane; idx < tot; idx += 32) {
-        const int y = __float2int_rd(((float)idx + 0.5f) * inv_iw), x = idx - y * iw;
-        const uint8_t* s = smap + (y + 3) * FAST_TP + (x + 3);
-        const int v = s[0];
-        int keep = 0;
-        if (v > 0) {
+    if (ncor <= FAST_CCAP) {
+        for (int i = lane; i < ncor; i += 32) {
+            const int o = cl[i];
+            const uint8_t* s = smap + o;
+            const int v = s[0];
             const int m = max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
                               max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
-            keep = v > m ? v : 0;
+            if (v > m) { keep[o] = (uint8_t)v; any_ini |= v >= P.ini_th; }
         }
-        F[idx] = (uint8_t)keep;
-        any_ini |= (keep > 0 && keep >= P.ini_th);
+    } else {
+        for (int idx = lane; idx < iw * ih; idx += 32) {
+            const int y = idx / iw, x = idx - y * iw, o = (y + 3) * FAST_TP + cs + x;
+            const uint8_t* s = smap + o;
+            const int v = s[0];
+            if (v) {
+                const int m = max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
+                                  max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
+                if (v > m) { keep[o] = (uint8_t)v; any_ini |= v >= P.ini_th; }
+            }
+        }
     }
     const int thr = __any_sync(0xffffffffu, any_ini) ? P.ini_th : P.min_th;
     __syncwarp();
 
+    // ---- pass 3: ordered compaction (row-major == word order, then byte order inside a word)
     uint32_t* slot = P.slots + (long long)frame * P.slot_frame_words + P.lv[l].slot_off + cell.slot_off;
     int cnt = 0;
-    for (int base = 0; base < tot; base += 32) {
-        const int idx = base + lane;
-        int f = 0, x = 0, y = 0;
-        if (idx < tot) {
-            f = F[idx];
-            y = __float2int_rd(((float)idx + 0.5f) * inv_iw); x = idx - y * iw;
+    for (int base = 0; base < ntask; base += 32) {
+        const int t = base + lane;
+        uint32_t wv = 0;
+        int yi = 0, c4 = 0;
+        if (t < ntask) {
+            yi = __float2int_rd(((float)t + 0.5f) * inv_nwi); c4 = 4 * (w0 + t - yi * nwi);
+            wv = *reinterpret_cast<const uint32_t*>(keep + (yi + 3) * FAST_TP + c4);
         }
-        const bool flag = f > 0 && f >= thr;
-        const unsigned bal = __ballot_sync(0xffffffffu, flag);
-        if (flag) {
-            const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
-            if (pos < cell.cap) slot[pos] = ORB_PACK(x + cell.off_x, y + cell.off_y, f);
+        if (__ballot_sync(0xffffffffu, wv != 0) == 0) continue;
+        unsigned f = 0;                                        // bit b: byte b survives at thr
+#pragma unroll
+        for (int b = 0; b < 4; ++b) { const int v = (wv >> (8 * b)) & 0xFF; f |= (unsigned)(v != 0 && v >= thr) << b; }
+        int mine = __popc(f), incl = mine;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
         }
-        cnt += __popc(bal);
+        int pos = cnt + incl - mine;
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+            if (f & (1u << b)) {
+                if (pos < cell.cap) slot[pos] = ORB_PACK(c4 + b - cs + cell.off_x, yi + cell.off_y, (wv >> (8 * b)) & 0xFF);
+                ++pos;
+            }
+        cnt += __shfl_sync(0xffffffffu, incl, 31);
     }
     if (lane == 0) *cnt_out = (uint32_t)min(cnt, cell.cap);
 }
 
 int orb_fast_smem_bytes(int max_cw, int max_ch)
 {
-    if (max_cw > FAST_TP - 4) return -1;
+    if (max_cw + 3 > FAST_TP) return -1;                  // + up to 3 bytes of alignment shift
     return FAST_WARPS * 2 * FAST_TP * max_ch;
 }
 
@@ -536,9 +710,8 @@ int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N,
 // One CTA = one 128 x 32 output tile of one level of one frame; the (128+6) x (32+6) input window
 // is staged in shared memory with the border reflection applied at load time.
 // =================================================================================================
-#define BLUR_TW 128
-#define BLUR_TH 32
-#define BLUR_IP 144           // input tile pitch (>= 128 + 6, multiple of 16)
+#define BLUR_R ORB_BLUR_ROWS   // output rows per thread (4 x the 7-row register ring)
+#define BLUR_THREADS ORB_BLUR_THREADS
 
 __device__ __forceinline__ int reflect101(int i, int n)
 {
@@ -547,60 +720,100 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-__global__ void __launch_bounds__(256) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
+// horizontal pass of one input row for the 4 pixels of word column wc: h[p] = sum_i k_i * I(4wc + p + i - 3).
+// WORDS: three aligned 32-bit loads (the whole 10-byte window lies inside the row); otherwise byte loads
+// with REFLECT_101 (row ends, or rows that are not 4-byte aligned).
+template <bool WORDS>
+__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ rowp, int wc, int w, unsigned h[4])
 {
-    __shared__ __align__(16) uint8_t s_in[(BLUR_TH + 6) * BLUR_IP];
-    __shared__ __align__(16) uint16_t s_h[(BLUR_TH + 6) * BLUR_TW];
+    unsigned wl, wm, wr;
+    if (WORDS) {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(rowp) + wc;
+        wm = __ldg(p);
+        wr = __ldg(p + 1);
+        wl = wc ? __ldg(p - 1) : __byte_perm(wm, 0, 0x1233);   // REFLECT_101: I(-1..-3) = I(1..3)
+    } else {
+        wl = wm = wr = 0;
+        const int x0 = 4 * wc - 4;
+#pragma unroll
+        for (int k = 1; k < 11; ++k) {
+            const unsigned v = __ldg(rowp + reflect101(x0 + k, w));
+            if (k < 4) wl |= v << (8 * k); else if (k < 8) wm |= v << (8 * (k - 4)); else wr |= v << (8 * (k - 8));
+        }
+    }
+    unsigned b[10];
+    b[0] = (wl >> 8) & 0xFF; b[1] = (wl >> 16) & 0xFF; b[2] = wl >> 24;
+    b[3] = wm & 0xFF; b[4] = (wm >> 8) & 0xFF; b[5] = (wm >> 16) & 0xFF; b[6] = wm >> 24;
+    b[7] = wr & 0xFF; b[8] = (wr >> 8) & 0xFF; b[9] = (wr >> 16) & 0xFF;
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+        h[p] = 18u * (b[p] + b[p + 6]) + 34u * (b[p + 1] + b[p + 5]) + 48u * (b[p + 2] + b[p + 4]) + 56u * b[p + 3];
+}
+
+// One thread = one 4-pixel word column x BLUR_R output rows.  The horizontal sums of the last 7 input rows
+// live in registers (28 values); every new input row costs three aligned 32-bit loads (L1 serves the
+// overlap with the neighbouring threads), every output row one aligned 32-bit store.  No shared memory.
+template <bool WORDS>
+__device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int sp, uint8_t* __restrict__ dst, int dp,
+                                           int w, int hgt, int wc, int y0)
+{
+    // input row y0 - 3 + k; rows are REFLECT_101-mapped only in the first / last strip
+    const bool inner = y0 >= 3 && y0 + BLUR_R + 3 <= hgt;
+    unsigned ring[7][4];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const int yy = inner ? y0 - 3 + k : reflect101(y0 - 3 + k, hgt);
+        blur_hrow<WORDS>(src + (size_t)yy * sp, wc, w, ring[k]);
+    }
+    for (int yb = 0; yb < BLUR_R; yb += 7) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            const int y = y0 + yb + j;
+            const int yy = inner ? y + 3 : reflect101(y + 3, hgt);
+            blur_hrow<WORDS>(src + (size_t)yy * sp, wc, w, ring[(j + 6) % 7]);
+            uint32_t out = 0;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const unsigned v = 18u * (ring[j % 7][p] + ring[(j + 6) % 7][p]) + 34u * (ring[(j + 1) % 7][p] + ring[(j + 5) % 7][p]) +
+                                   48u * (ring[(j + 2) % 7][p] + ring[(j + 4) % 7][p]) + 56u * ring[(j + 3) % 7][p] + 32768u;
+                out |= (v >> 16) << (8 * p);
+            }
+            if (y < hgt) *reinterpret_cast<uint32_t*>(dst + (size_t)y * dp + 4 * wc) = out;
+        }
+    }
+}
+
+// Work list entry: (level, first task, kind).  kind 0 = interior word columns [0, nfast) on the aligned
+// word path; kind 1 = the remaining columns (row ends; or every column when the level's rows are not
+// 4-byte aligned) on the byte path.  Splitting them keeps every warp on one path.
+__global__ void __launch_bounds__(BLUR_THREADS) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
+{
     const int4 t = tiles[blockIdx.x];
-    const int l = t.x, x0 = t.y, y0 = t.z, frame = blockIdx.y, tid = threadIdx.x;
+    const int l = t.x, frame = blockIdx.y;
     const OrbLevel& L = P.lv[l];
+    const int w = L.w, hgt = L.h, nwc = (w + 3) >> 2;
     const uint8_t* __restrict__ src = orb_level_ptr(P, l, frame);
     const int sp = orb_level_pitch(P, l);
     uint8_t* __restrict__ dst = P.blur + (long long)frame * P.blur_frame_bytes + L.blur_off;
-
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
-        const int r = i / (BLUR_TW + 6), c = i - r * (BLUR_TW + 6);
-        const int sy = reflect101(y0 + r - 3, L.h), sx = reflect101(x0 + c - 3, L.w);
-        s_in[r * BLUR_IP + c] = __ldg(src + (long long)sy * sp + sx);
-    }
-    __syncthreads();
-    // horizontal: each task = 4 adjacent outputs of one row (10 input bytes)
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW / 4); i += 256) {
-        const int r = i / (BLUR_TW / 4), q = i - r * (BLUR_TW / 4);
-        const uint8_t* p = s_in + r * BLUR_IP + 4 * q;
-        unsigned v[10];
-#pragma unroll
-        for (int k = 0; k < 10; ++k) v[k] = p[k];
-        unsigned o[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            o[k] = 18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3];
-        uint2 w2 = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
-        *reinterpret_cast<uint2*>(s_h + r * BLUR_TW + 4 * q) = w2;
-    }
-    __syncthreads();
-    // vertical: each task = 4 adjacent outputs of one row, one aligned 32-bit store
-    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
-        const int r = i / (BLUR_TW / 4), q = i - r * (BLUR_TW / 4);
-        const int x = x0 + 4 * q, y = y0 + r;
-        if (y >= L.h || x >= L.pitch) continue;
-        unsigned acc[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int k = 0; k < 7; ++k) {
-            const unsigned kk = (k == 0 || k == 6) ? 18u : (k == 1 || k == 5) ? 34u : (k == 2 || k == 4) ? 48u : 56u;
-            const uint2 h = *reinterpret_cast<const uint2*>(s_h + (r + k) * BLUR_TW + 4 * q);
-            acc[0] += kk * (h.x & 0xFFFFu); acc[1] += kk * (h.x >> 16);
-            acc[2] += kk * (h.y & 0xFFFFu); acc[3] += kk * (h.y >> 16);
-        }
-        const uint32_t out = ((acc[0] + 32768u) >> 16) | (((acc[1] + 32768u) >> 16) << 8) |
-                             (((acc[2] + 32768u) >> 16) << 16) | (((acc[3] + 32768u) >> 16) << 24);
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x) = out;
+    const bool aligned = ((sp & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 3) == 0);
+    const int nfast = (aligned && w >= 8) ? (w - 4) >> 2 : 0;  // word columns with 4wc + 8 <= w
+    const int task = t.y + threadIdx.x;
+    if (t.z == 0) {
+        if (nfast == 0) return;
+        const int strip = task / nfast, wc = task - strip * nfast;
+        if (strip * BLUR_R >= hgt) return;
+        blur_strip<true>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
+    } else {
+        const int nslow = nwc - nfast;
+        const int strip = task / nslow, wc = nfast + task - strip * nslow;
+        if (strip * BLUR_R >= hgt) return;
+        blur_strip<false>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
     }
 }
 
 int orb_launch_blur(const OrbPlanDev& P, int nframes, const int4* tiles, int ntiles, cudaStream_t st)
 {
-    k_blur<<<dim3(ntiles, nframes), 256, 0, st>>>(P, tiles);
+    k_blur<<<dim3(ntiles, nframes), BLUR_THREADS, 0, st>>>(P, tiles);
     return 1;
 }
 

@@ -92,6 +92,7 @@ struct orbgpu_extractor {
     Plan plan;
     StreamCtx ctx[NSTREAM];
     bool profiling = false;
+    int nstream = NSTREAM;              // chunk streams a batch call deals its chunks to (1..NSTREAM)
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
@@ -205,9 +206,16 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
             rs_ofs.resize(rs_ofs.size() + L.h); rs_a.resize(rs_a.size() + 2 * (size_t)L.h);
             resize_axis(S.h, L.h, false, &rs_ofs[L.yofs_off], &rs_a[2 * (size_t)L.yofs_off]);
         }
-        for (int y0 = 0; y0 < L.h; y0 += 32)
-            for (int x0 = 0; x0 < L.w; x0 += 128) tiles.push_back(make_int4(l, x0, y0, 0));
-
+        {   // blur work list: one entry per CTA of ORB_BLUR_THREADS tasks; task = (row strip, 4-pixel word column).
+            // kind 0: interior columns on the aligned word path; kind 1: row-end columns on the byte path.  Level 0
+            // is read from the caller's buffer, whose alignment is only known at launch: both kinds are listed for
+            // the worst case and the kernel drops the entries that do not apply.
+            const int nwc = (L.w + 3) / 4, nstrip = (L.h + ORB_BLUR_ROWS - 1) / ORB_BLUR_ROWS;
+            const int nfast = L.w >= 8 ? (L.w - 4) / 4 : 0;
+            for (int t0 = 0; t0 < nfast * nstrip; t0 += ORB_BLUR_THREADS) tiles.push_back(make_int4(l, t0, 0, 0));
+            const int nslow_max = (l == 0) ? nwc : nwc - nfast;     // level 0 may turn out unaligned: all columns slow
+            for (int t0 = 0; t0 < nslow_max * nstrip; t0 += ORB_BLUR_THREADS) tiles.push_back(make_int4(l, t0, 1, 0));
+        }
         // FAST cell grid
         const int minB = ORB_BORDER, maxBX = L.w - ORB_BORDER, maxBY = L.h - ORB_BORDER;
         L.W = maxBX - minB; L.H = maxBY - minB;
@@ -601,11 +609,11 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
     const bool pin_in = is_pinned(frames);
     const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
-    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
+    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + e->nstream - 1) / e->nstream));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
-        StreamCtx& c = e->ctx[k % NSTREAM];
+        StreamCtx& c = e->ctx[k % e->nstream];
         const int m = std::min(chunk, n - i0);
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
@@ -638,11 +646,11 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
     for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
     if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
-    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + NSTREAM - 1) / NSTREAM));
+    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + e->nstream - 1) / e->nstream));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
-        StreamCtx& c = e->ctx[k % NSTREAM];
+        StreamCtx& c = e->ctx[k % e->nstream];
         const int m = std::min(chunk, n - i0);
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
@@ -907,6 +915,13 @@ int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset)
 }
 
 uint64_t orbgpu_launch_count(orbgpu_extractor* e) { return e ? e->launches : 0; }
+
+int orbgpu_set_streams(orbgpu_extractor* e, int n)
+{
+    if (!e || n < 1 || n > NSTREAM) return ORBGPU_ERR_ARG;
+    e->nstream = n;
+    return ORBGPU_OK;
+}
 
 double orbgpu_last_batch_ms(orbgpu_extractor* e) { return e ? e->last_batch_ms : 0.0; }
 

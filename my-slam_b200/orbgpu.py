@@ -57,6 +57,7 @@ def lib():
         "orbgpu_get_stage_ms": (i32, [vp, vp, i32, i32]),
         "orbgpu_launch_count": (u64, [vp]),
         "orbgpu_last_batch_ms": (C.c_double, [vp]),
+        "orbgpu_set_streams": (i32, [vp, i32]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
@@ -239,6 +240,8 @@ class ORBextractor:
         return dict(zip(STAGE_NAMES, ms.tolist()))
 
     def launch_count(self): return int(self._L.orbgpu_launch_count(self._h))
+
+    def set_streams(self, n): _check(self._L.orbgpu_set_streams(self._h, int(n)))
 
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
 
