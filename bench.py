@@ -277,8 +277,8 @@ def run_ours(args, rank, world, local_rank):
     n = args.frames
     ex = pkg.ORBextractor(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"], device=local_rank)
     cap = ex.max_keypoints(w, h)
-    if args.streams:
-        ex.set_streams(args.streams)
+    if args.streams or args.chunk:
+        ex.set_batching(args.streams or 3, args.chunk or 64)
 
     # synthetic frames: every rank owns its own batch (weak scaling)
     h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
@@ -416,7 +416,8 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_STEP, help="frames per step per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="wall time budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--streams", type=int, default=0, help="internal chunk streams (1..3); 0 = library default")
+    ap.add_argument("--streams", type=int, default=0, help="internal chunk streams; 0 = library default")
+    ap.add_argument("--chunk", type=int, default=0, help="max frames per chunk; 0 = library default")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -134,9 +134,11 @@ uint64_t orbgpu_launch_count(orbgpu_extractor* e);
 /* Device time (ms) of the most recent orbgpu_extract / _batch / _batch_device call: CUDA events on the
  * library's own streams, from before the first upload/kernel to after the last kernel/download. */
 double orbgpu_last_batch_ms(orbgpu_extractor* e);
-/* Number of internal chunk streams a batch call spreads its chunks over (1..3, default 3).  1 serialises
- * the chunks, so per-stage event times are those of each kernel running alone. */
-int orbgpu_set_streams(orbgpu_extractor* e, int n);
+/* How a batch call is cut up: chunks of at most max_chunk_frames frames are dealt round-robin to
+ * `streams` internal CUDA streams (1..orbgpu_queue_depth()), so upload, kernels and download of
+ * successive chunks overlap.  streams = 1 serialises the chunks (per-stage event times are then those of
+ * each kernel running alone).  Small chunks keep a chunk's pyramid + blurred levels inside L2. */
+int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames);
 
 /* ---- matcher ------------------------------------------------------------------------------- */
 

@@ -10,6 +10,7 @@
 // contraction: no tensor cores.  Float arithmetic that feeds rounding decisions uses explicit
 // __fmul_rn/__fadd_rn (no FMA contraction) and __float2int_rn (round-half-even == cvRound).
 #include <cuda_runtime.h>
+#include <cuda_pipeline.h>
 #include <stdint.h>
 #include "orb_common.cuh"
 #include "orb_pattern.h"
@@ -188,7 +189,8 @@ __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
 }
 
 #define FAST_QCAP 256         // ring queue of quick-test survivors (per warp)
-#define FAST_CCAP 256         // corner list (per warp); denser cells take the dense NMS path
+#define FAST_CCAP 256         // corner list (per warp); denser cells take the dense path
+#define FAST_KCAP 96          // strict maxima ranked by pairwise comparison; more take the dense path
 
 // flags (bit 7 of each byte) of  max(a, b) > th  for 4 packed bytes, th <= 126; K = (127 - th) * 0x01010101
 __device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned b, unsigned K)
@@ -196,6 +198,20 @@ __device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned b, unsigned K)
     return ((a & 0x7f7f7f7fu) + K) | a | ((b & 0x7f7f7f7fu) + K) | b;
 }
 
+__device__ __forceinline__ int fast_max8(const uint8_t* s)
+{
+    return max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
+               max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
+}
+
+// One warp = one cell, exactly as the reference runs it: cv::FAST(cell, iniThFAST, nonmax) and, when that
+// returns nothing, cv::FAST(cell, minThFAST, nonmax) (src/ORBextractor.cc:811-818).  Per attempt:
+//   1. quick rejection on 4 packed pixels per lane: every 9-arc of the ring contains pixel 0 or 8 and pixel
+//      4 or 12, so a corner needs max(|p0-v|,|p8-v|) > th and max(|p4-v|,|p12-v|) > th (VABSDIFF4 + carry trick);
+//   2. survivors go through a ring queue and are scored 32 at a time by the 16x2 min/max arc network;
+//      score = V - 1 where V > th, into the cell-local score map; corners are also appended to a list;
+//   3. strict 8-neighbour maxima of the listed corners, ranked by position (row-major) by pairwise comparison
+//      and written in order.  Cells too dense for the lists fall back to an ordered scan of the score map.
 __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, int tile_rows)
 {
     extern __shared__ __align__(16) uint8_t fast_smem[];
@@ -214,158 +230,158 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
     uint32_t* cnt_out = P.cellcnt + (long long)frame * P.ncells + cell_id;
     if (iw <= 0 || ih <= 0) { if (lane == 0) *cnt_out = 0; return; }
 
-    // ---- stage the cell image (tile column = x - ini_x + sh); zero the score map
+    // ---- stage the cell image (tile column = x - ini_x + sh) with asynchronous 4-byte copies
     const int pitch = orb_level_pitch(P, l);
     const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame) + (long long)cell.ini_y * pitch + cell.ini_x;
     int sh = 0;
     if (((pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img - cell.ini_x) & 3) == 0)) {
-        sh = cell.ini_x & 3;                                   // aligned 32-bit loads, two rows per pass
+        sh = cell.ini_x & 3;
         const int nw = (cw + sh + 3) >> 2, c = lane & 15;
         if (c < nw) {
-            const uint32_t* g = reinterpret_cast<const uint32_t*>(img - sh + (long long)(lane >> 4) * pitch) + c;
-            uint32_t* t = reinterpret_cast<uint32_t*>(tile + (lane >> 4) * FAST_TP) + c;
-            for (int r = lane >> 4; r < ch; r += 2, g += pitch >> 1, t += FAST_TP / 2) *t = __ldg(g);
+            const uint8_t* g = img - sh + (size_t)(lane >> 4) * pitch + 4 * c;
+            uint8_t* t = tile + (lane >> 4) * FAST_TP + 4 * c;
+            for (int r = lane >> 4; r < ch; r += 2, g += 2 * (size_t)pitch, t += 2 * FAST_TP) __pipeline_memcpy_async(t, g, 4);
         }
+        __pipeline_commit();
+        __pipeline_wait_prior(0);
     } else {
         for (int r = 0; r < ch; ++r)
             for (int c = lane; c < cw; c += 32) tile[r * FAST_TP + c] = __ldg(img + (long long)r * pitch + c);
     }
-    {
-        uint4* z = reinterpret_cast<uint4*>(smap + 2 * FAST_TP);            // rows 2 .. ih+3: interior + NMS rim
-        for (int i = lane; i < (ih + 2) * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
-    }
     __syncwarp();
 
-    const int base_th = min(P.ini_th, P.min_th);
     const int cs = 3 + sh, ce = cs + iw;                       // interior tile columns [cs, ce), rows [3, 3 + ih)
     const int w0 = cs >> 2, nwi = ((ce - 1) >> 2) - w0 + 1;    // words of a row that hold interior pixels
     const int ntask = ih * nwi;
-    const float inv_nwi = 1.0f / (float)nwi;
+    const float inv_nwi = 1.0f / (float)nwi, inv_iw = 1.0f / (float)iw;
     uint16_t* q = s_queue[warp];
     uint16_t* cl = s_corner[warp];
-    int head = 0, tail = 0, ncor = 0;
-
-    // scores 32 queued pixels with the arc network; corners go to the score map and the corner list
-#define FAST_DRAIN(active)                                                               \
-    {                                                                                    \
-        int o_ = 0, V_ = 0;                                                              \
-        if (active) { o_ = q[(head + lane) & (FAST_QCAP - 1)]; V_ = fast_arc_value(tile + o_); } \
-        const bool c_ = V_ > base_th;                                                    \
-        const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                             \
-        if (c_) {                                                                        \
-            smap[o_] = (uint8_t)(V_ - 1);                                                \
-            const int p_ = ncor + __popc(bc_ & lt);                                      \
-            if (p_ < FAST_CCAP) cl[p_] = (uint16_t)o_;                                   \
-        }                                                                                \
-        ncor += __popc(bc_);                                                             \
-    }
-
-    // ---- pass 1: quick rejection, 4 pixels per lane.  A 9-arc always contains ring pixel 0 or 8 and pixel
-    //      4 or 12, so a corner needs max(|p0-v|,|p8-v|) > th and max(|p4-v|,|p12-v|) > th.
-    if (base_th <= 126) {
-        const unsigned K = (unsigned)(127 - base_th) * 0x01010101u;
-        for (int base = 0; base < ntask; base += 32) {
-            const int t = base + lane;
-            unsigned f = 0;
-            int off = 0;
-            if (t < ntask) {
-                const int yi = __float2int_rd(((float)t + 0.5f) * inv_nwi), wi = w0 + t - yi * nwi;
-                off = (yi + 3) * FAST_TP + 4 * wi;
-                const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off);
-                const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
-                const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
-                f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & 0x80808080u;
-                if (4 * wi < cs) f &= 0xFFFFFFFFu << (8 * (cs - 4 * wi));
-                if (4 * wi + 4 > ce) f &= 0xFFFFFFFFu >> (8 * (4 * wi + 4 - ce));
-            }
-            if (__ballot_sync(0xffffffffu, f != 0) == 0) continue;
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                const bool on = (f >> (8 * b + 7)) & 1u;
-                const unsigned bal = __ballot_sync(0xffffffffu, on);
-                if (on) q[(tail + __popc(bal & lt)) & (FAST_QCAP - 1)] = (uint16_t)(off + b);
-                tail += __popc(bal);
-            }
-            __syncwarp();
-            while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
-            __syncwarp();
-        }
-    } else {                                                   // thresholds above 126: score every pixel
-        for (int i = 0; i < iw * ih; i += 32) {
-            const int idx = i + lane, y = idx / iw, x = idx - y * iw;
-            if (idx < iw * ih) q[lane] = (uint16_t)((y + 3) * FAST_TP + cs + x);
-            __syncwarp();
-            head = 0;
-            FAST_DRAIN(idx < iw * ih);
-            __syncwarp();
-        }
-        head = tail = 0;
-    }
-    FAST_DRAIN(lane < tail - head);
-#undef FAST_DRAIN
-    __syncwarp();
-
-    // ---- pass 2: strict 8-neighbour maxima -> keep map (in the tile memory; the pixels are no longer needed)
-    uint8_t* keep = tile;
-    {
-        uint4* z = reinterpret_cast<uint4*>(keep + 3 * FAST_TP);
-        for (int i = lane; i < ih * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncwarp();
-    bool any_ini = false;
-    if (ncor <= FAST_CCAP) {
-        for (int i = lane; i < ncor; i += 32) {
-            const int o = cl[i];
-            const uint8_t* s = smap + o;
-            const int v = s[0];
-            const int m = max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
-                              max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
-            if (v > m) { keep[o] = (uint8_t)v; any_ini |= v >= P.ini_th; }
-        }
-    } else {
-        for (int idx = lane; idx < iw * ih; idx += 32) {
-            const int y = idx / iw, x = idx - y * iw, o = (y + 3) * FAST_TP + cs + x;
-            const uint8_t* s = smap + o;
-            const int v = s[0];
-            if (v) {
-                const int m = max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
-                                  max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
-                if (v > m) { keep[o] = (uint8_t)v; any_ini |= v >= P.ini_th; }
-            }
-        }
-    }
-    const int thr = __any_sync(0xffffffffu, any_ini) ? P.ini_th : P.min_th;
-    __syncwarp();
-
-    // ---- pass 3: ordered compaction (row-major == word order, then byte order inside a word)
     uint32_t* slot = P.slots + (long long)frame * P.slot_frame_words + P.lv[l].slot_off + cell.slot_off;
     int cnt = 0;
-    for (int base = 0; base < ntask; base += 32) {
-        const int t = base + lane;
-        uint32_t wv = 0;
-        int yi = 0, c4 = 0;
-        if (t < ntask) {
-            yi = __float2int_rd(((float)t + 0.5f) * inv_nwi); c4 = 4 * (w0 + t - yi * nwi);
-            wv = *reinterpret_cast<const uint32_t*>(keep + (yi + 3) * FAST_TP + c4);
+
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const int th = attempt ? P.min_th : P.ini_th;
+        {
+            uint4* z = reinterpret_cast<uint4*>(smap + 2 * FAST_TP);        // rows 2 .. ih+3: interior + NMS rim
+            for (int i = lane; i < (ih + 2) * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
         }
-        if (__ballot_sync(0xffffffffu, wv != 0) == 0) continue;
-        unsigned f = 0;                                        // bit b: byte b survives at thr
-#pragma unroll
-        for (int b = 0; b < 4; ++b) { const int v = (wv >> (8 * b)) & 0xFF; f |= (unsigned)(v != 0 && v >= thr) << b; }
-        int mine = __popc(f), incl = mine;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int u = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += u;
+        __syncwarp();
+        int head = 0, tail = 0, ncor = 0;
+
+        // scores 32 queued pixels with the arc network; corners go to the score map and the corner list
+#define FAST_DRAIN(active)                                                               \
+        {                                                                                \
+            int o_ = 0, V_ = 0;                                                          \
+            if (active) { o_ = q[(head + lane) & (FAST_QCAP - 1)]; V_ = fast_arc_value(tile + o_); } \
+            const bool c_ = V_ > th;                                                     \
+            const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                         \
+            if (c_) {                                                                    \
+                smap[o_] = (uint8_t)(V_ - 1);                                            \
+                const int p_ = ncor + __popc(bc_ & lt);                                  \
+                if (p_ < FAST_CCAP) cl[p_] = (uint16_t)o_;                               \
+            }                                                                            \
+            ncor += __popc(bc_);                                                         \
         }
-        int pos = cnt + incl - mine;
+
+        if (th <= 126) {
+            const unsigned K = (unsigned)(127 - th) * 0x01010101u;
+            for (int base = 0; base < ntask; base += 32) {
+                const int t = base + lane;
+                unsigned f = 0;
+                int off = 0;
+                if (t < ntask) {
+                    const int yi = __float2int_rd(((float)t + 0.5f) * inv_nwi), wi = w0 + t - yi * nwi;
+                    off = (yi + 3) * FAST_TP + 4 * wi;
+                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off);
+                    const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
+                    const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
+                    f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & 0x80808080u;
+                    if (4 * wi < cs) f &= 0xFFFFFFFFu << (8 * (cs - 4 * wi));
+                    if (4 * wi + 4 > ce) f &= 0xFFFFFFFFu >> (8 * (4 * wi + 4 - ce));
+                }
+                if (__ballot_sync(0xffffffffu, f != 0) == 0) continue;
+                // queue order is irrelevant (results are keyed by position): exclusive prefix of the per-lane counts
+                const int mine = __popc(f);
+                int incl = mine;
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
-            if (f & (1u << b)) {
-                if (pos < cell.cap) slot[pos] = ORB_PACK(c4 + b - cs + cell.off_x, yi + cell.off_y, (wv >> (8 * b)) & 0xFF);
-                ++pos;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int u = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += u;
+                }
+                int pos = tail + incl - mine;
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if (f & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(off + b); ++pos; }
+                tail += __shfl_sync(0xffffffffu, incl, 31);
+                __syncwarp();
+                while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
+                __syncwarp();
             }
-        cnt += __shfl_sync(0xffffffffu, incl, 31);
+        } else {                                               // thresholds above 126: score every pixel
+            for (int i = 0; i < iw * ih; i += 32) {
+                const int idx = i + lane, y = idx / iw, x = idx - y * iw;
+                if (idx < iw * ih) q[lane] = (uint16_t)((y + 3) * FAST_TP + cs + x);
+                __syncwarp();
+                head = 0;
+                FAST_DRAIN(idx < iw * ih);
+                __syncwarp();
+            }
+            head = tail = 0;
+        }
+        FAST_DRAIN(lane < tail - head);
+#undef FAST_DRAIN
+        __syncwarp();
+
+        // ---- strict 8-neighbour maxima, emitted in row-major order
+        cnt = 0;
+        bool dense = ncor > FAST_CCAP;
+        if (!dense) {
+            uint32_t* kl = reinterpret_cast<uint32_t*>(q);     // kept list (the queue is idle now): offset << 8 | score
+            int K2 = 0;
+            for (int i = 0; i < ncor; i += 32) {
+                bool kp = false;
+                unsigned key = 0;
+                if (i + lane < ncor) {
+                    const int o = cl[i + lane];
+                    const int v = smap[o];
+                    kp = v > fast_max8(smap + o);
+                    key = ((unsigned)o << 8) | (unsigned)v;
+                }
+                const unsigned bk = __ballot_sync(0xffffffffu, kp);
+                if (kp) { const int p = K2 + __popc(bk & lt); if (p < FAST_KCAP) kl[p] = key; }
+                K2 += __popc(bk);
+            }
+            __syncwarp();
+            if (K2 <= FAST_KCAP) {
+                for (int i = lane; i < K2; i += 32) {
+                    const unsigned key = kl[i];
+                    int rank = 0;
+                    for (int j = 0; j < K2; ++j) rank += kl[j] < key;
+                    const int o = (int)(key >> 8);
+                    if (rank < cell.cap) slot[rank] = ORB_PACK((o & (FAST_TP - 1)) - cs + cell.off_x, (o >> 6) - 3 + cell.off_y, key & 0xFF);
+                }
+                cnt = K2;
+            } else dense = true;
+            __syncwarp();
+        }
+        if (dense) {                                           // ordered scan of the whole score map
+            const int tot = iw * ih;
+            for (int base = 0; base < tot; base += 32) {
+                const int idx = base + lane;
+                int v = 0, x = 0, y = 0;
+                bool kp = false;
+                if (idx < tot) {
+                    y = __float2int_rd(((float)idx + 0.5f) * inv_iw); x = idx - y * iw;
+                    const uint8_t* sp = smap + (y + 3) * FAST_TP + cs + x;
+                    v = sp[0];
+                    kp = v > 0 && v > fast_max8(sp);
+                }
+                const unsigned bk = __ballot_sync(0xffffffffu, kp);
+                if (kp) { const int p = cnt + __popc(bk & lt); if (p < cell.cap) slot[p] = ORB_PACK(x + cell.off_x, y + cell.off_y, v); }
+                cnt += __popc(bk);
+            }
+        }
+        if (cnt > 0 || P.min_th == P.ini_th) break;
     }
     if (lane == 0) *cnt_out = (uint32_t)min(cnt, cell.cap);
 }

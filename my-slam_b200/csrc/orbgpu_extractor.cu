@@ -32,7 +32,7 @@ void orbgpu_internal_set_error(const char* s) { snprintf(g_cuda_err, sizeof(g_cu
 
 namespace {
 
-const int NSTREAM = 3;
+const int NSTREAM = 8;               // stream contexts per handle (queue depth); batch calls use `nstream` of them
 enum { EV_BEGIN = 0, EV_UP, EV_PYR, EV_FAST, EV_OCT, EV_BLUR, EV_DESC, EV_DOWN, EV_COUNT };
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -92,7 +92,8 @@ struct orbgpu_extractor {
     Plan plan;
     StreamCtx ctx[NSTREAM];
     bool profiling = false;
-    int nstream = NSTREAM;              // chunk streams a batch call deals its chunks to (1..NSTREAM)
+    int nstream = 4;                    // chunk streams a batch call deals its chunks to (1..NSTREAM)
+    int max_chunk = 32;                 // frames per chunk (upper bound; also capped by plan.chunk_cap)
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
@@ -609,7 +610,7 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
     const bool pin_in = is_pinned(frames);
     const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
-    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + e->nstream - 1) / e->nstream));
+    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk), (n + e->nstream - 1) / e->nstream));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
@@ -646,7 +647,7 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
     for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
     if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
-    const int chunk = std::max(1, std::min(e->plan.chunk_cap, (n + e->nstream - 1) / e->nstream));
+    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk), (n + e->nstream - 1) / e->nstream));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
@@ -916,10 +917,13 @@ int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset)
 
 uint64_t orbgpu_launch_count(orbgpu_extractor* e) { return e ? e->launches : 0; }
 
-int orbgpu_set_streams(orbgpu_extractor* e, int n)
+int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames)
 {
-    if (!e || n < 1 || n > NSTREAM) return ORBGPU_ERR_ARG;
-    e->nstream = n;
+    if (!e || streams < 1 || streams > NSTREAM || max_chunk_frames < 1) return ORBGPU_ERR_ARG;
+    for (int s = 0; s < NSTREAM; ++s)
+        if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    e->nstream = streams;
+    e->max_chunk = max_chunk_frames;
     return ORBGPU_OK;
 }
 

@@ -65,7 +65,7 @@ static int cmd_extract(int argc, char** argv)
     } else if (mode == "queue") {
         FrameQueue q(&ex);
         int pushed = 0;
-        while (!q.Full() && q.Push(image, 0.1 * pushed)) ++pushed;
+        while (pushed < 3 && !q.Full() && q.Push(image, 0.1 * pushed)) ++pushed;
         double ts;
         int popped = 0;
         while (q.Pop(ts, kps, desc)) { put(out, kps, desc); ++popped; }

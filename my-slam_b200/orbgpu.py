@@ -57,7 +57,7 @@ def lib():
         "orbgpu_get_stage_ms": (i32, [vp, vp, i32, i32]),
         "orbgpu_launch_count": (u64, [vp]),
         "orbgpu_last_batch_ms": (C.c_double, [vp]),
-        "orbgpu_set_streams": (i32, [vp, i32]),
+        "orbgpu_set_batching": (i32, [vp, i32, i32]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
@@ -241,7 +241,7 @@ class ORBextractor:
 
     def launch_count(self): return int(self._L.orbgpu_launch_count(self._h))
 
-    def set_streams(self, n): _check(self._L.orbgpu_set_streams(self._h, int(n)))
+    def set_batching(self, streams, max_chunk_frames): _check(self._L.orbgpu_set_batching(self._h, int(streams), int(max_chunk_frames)))
 
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
 

@@ -151,10 +151,10 @@ def test_device_resident_and_pinned_paths(pkg, ex1000):
 def test_frame_queue_submit_collect(pkg):
     synth = pkg.synth
     ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
-    frames = [synth.synth(640, 480, 500 + i) for i in range(7)]
-    expect = [ex(f) for f in frames]
     depth = ex.queue_depth()
     assert depth >= 2
+    frames = [synth.synth(640, 480, 500 + i) for i in range(depth + 4)]
+    expect = [ex(f) for f in frames]
     tickets = [ex.submit(frames[i]) for i in range(depth)]
     with pytest.raises(pkg.OrbGpuError):
         ex.submit(frames[0])                                     # ring full: error code, no blocking, no crash
