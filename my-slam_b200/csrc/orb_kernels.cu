@@ -15,13 +15,18 @@
 #include "orb_common.cuh"
 #include "orb_pattern.h"
 
-__constant__ int8_t c_pattern[1024];     // 512 (x,y) rBRIEF sample offsets
-__constant__ int c_umax[16];             // half-widths of the circular patch rows, src/ORBextractor.cc:456-471
+// rBRIEF pattern in global memory: lane i of a warp owns bytes [32i, 32i+32) = its 16 sample points
+__device__ __align__(16) int8_t g_pattern[1024];
+// umax[|v|] of the 31-px disc packed as nibbles (src/ORBextractor.cc:456-471 with HALF_PATCH_SIZE 15):
+// 15,15,15,15,14,14,14,13,13,12,11,10,9,8,6,3.  The disc is symmetric, so column u holds rows |v| <= umax[|u|].
+#define ORB_UMAX_NIBBLES 0x3689abcddeeeffffull
 
 int orb_upload_constants(const int* umax16)
 {
-    if (cudaMemcpyToSymbol(c_pattern, ORB_PATTERN_XY, 1024) != cudaSuccess) return -1;
-    if (cudaMemcpyToSymbol(c_umax, umax16, 16 * sizeof(int)) != cudaSuccess) return -1;
+    // the disc table is a constant of the algorithm (HALF_PATCH_SIZE 15); the kernels carry it packed
+    for (int i = 0; i < 16; ++i)
+        if (umax16[i] != (int)((ORB_UMAX_NIBBLES >> (4 * i)) & 15ull)) return -1;
+    if (cudaMemcpyToSymbol(g_pattern, ORB_PATTERN_XY, 1024) != cudaSuccess) return -1;
     return 0;
 }
 
@@ -895,47 +900,59 @@ struct OrbKeypointRec { float x, y, size, angle, response; int octave, class_id;
 
 __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
 {
-    __shared__ uint32_t s_pat[256];       // [pair k][lane]: (x0, y0, x1, y1) of points 16*lane+2k, +1
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, frame = blockIdx.y;
-    {
-        const int k = tid >> 5, ln = tid & 31, p = 16 * ln + 2 * k;
-        s_pat[tid] = (uint32_t)(uint8_t)c_pattern[2 * p] | ((uint32_t)(uint8_t)c_pattern[2 * p + 1] << 8) |
-                     ((uint32_t)(uint8_t)c_pattern[2 * p + 2] << 16) | ((uint32_t)(uint8_t)c_pattern[2 * p + 3] << 24);
-    }
-    __syncthreads();
     const int g = blockIdx.x * 8 + warp;
     const int* selcnt = P.selcnt + (long long)frame * ORB_MAX_LEVELS;
-    if (g == 0 && lane == 0) {
-        int tot = 0; bool bad = false;
-        for (int l = 0; l < P.nlevels; ++l) { const int c = selcnt[l]; bad |= c < 0; tot += max(c, 0); }
-        P.nout[frame] = (bad || tot > P.kp_capacity) ? -1 : tot;
+    // per-level survivor counts, one per lane; exclusive prefix = output offset of each level
+    const int cl = lane < P.nlevels ? selcnt[lane] : 0;
+    int incl = max(cl, 0);
+#pragma unroll
+    for (int d = 1; d < ORB_MAX_LEVELS; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (g == 0) {
+        const bool bad = __any_sync(0xffffffffu, cl < 0);
+        const int tot = __shfl_sync(0xffffffffu, incl, ORB_MAX_LEVELS - 1);
+        if (lane == 0) P.nout[frame] = (bad || tot > P.kp_capacity) ? -1 : tot;
     }
     if (g >= P.sel_total) return;
-    int l = 0, before = 0;
-    while (l + 1 < P.nlevels && g >= P.lv[l].sel_off + P.lv[l].sel_cap) { before += max(selcnt[l], 0); ++l; }
+    // level of slot g: the last level whose sel_off <= g
+    const unsigned lv_mask = __ballot_sync(0xffffffffu, lane < P.nlevels && P.lv[min(lane, ORB_MAX_LEVELS - 1)].sel_off <= g &&
+                                                        P.lv[min(lane, ORB_MAX_LEVELS - 1)].sel_cap > 0);
+    const int l = lv_mask ? 31 - __clz(lv_mask) : 0;
     const OrbLevel& L = P.lv[l];
     const int idx = g - L.sel_off;
-    if (idx >= selcnt[l]) return;
+    const int cnt_l = __shfl_sync(0xffffffffu, cl, l);
+    const int before = __shfl_sync(0xffffffffu, incl - max(cl, 0), l);
+    if (idx >= cnt_l) return;
     const int o = before + idx;
     if (o >= P.kp_capacity) return;
     const uint32_t key = P.sel[(long long)frame * P.sel_total + g];
     const int cx = ORB_PX(key) + ORB_BORDER, cy = ORB_PY(key) + ORB_BORDER;
 
-    // ---- IC_Angle on the unblurred level
+    // this lane's 16 pattern points (issued early; used after the angle is known)
+    const uint4 pat0 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + 2 * lane);
+    const uint4 pat1 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + 2 * lane + 1);
+
+    // ---- IC_Angle on the unblurred level: lane = column u of the disc, rows v = -vm .. vm
     const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame);
     const int pitch = orb_level_pitch(P, l);
     const int u = lane - ORB_HALF_PATCH;
     int m10 = 0, m01 = 0;
     if (lane < ORB_PATCH) {
-        const uint8_t* c = img + (long long)cy * pitch + cx + u;
-        const int au = abs(u);
-#pragma unroll 4
-        for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
-            if (au <= c_umax[abs(v)]) {
-                const int val = __ldg(c + (long long)v * pitch);
-                m10 += u * val; m01 += v * val;
+        const int vm = (int)((ORB_UMAX_NIBBLES >> (4 * abs(u))) & 15ull);
+        const uint8_t* c = img + (size_t)cy * pitch + cx + u;
+        int sum = __ldg(c);
+#pragma unroll
+        for (int v = 1; v <= ORB_HALF_PATCH; ++v) {
+            if (v <= vm) {
+                const int lo = __ldg(c + v * pitch), up = __ldg(c - v * pitch);
+                sum += lo + up;
+                m01 += v * (lo - up);
             }
         }
+        m10 = u * sum;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
@@ -950,18 +967,21 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
     orb_sincosf(__fmul_rn(angle, factorPI), &b, &a);
     const uint8_t* __restrict__ bc = P.blur + (long long)frame * P.blur_frame_bytes + L.blur_off + (long long)cy * L.pitch + cx;
     unsigned byte = 0;
+    const uint32_t pw[8] = {pat0.x, pat0.y, pat0.z, pat0.w, pat1.x, pat1.y, pat1.z, pat1.w};
+    int t0[8], t1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const uint32_t w = s_pat[k * 32 + lane];
+        const uint32_t w = pw[k];
         const float x0 = (float)(int8_t)(w & 0xFF), y0 = (float)(int8_t)((w >> 8) & 0xFF);
         const float x1 = (float)(int8_t)((w >> 16) & 0xFF), y1 = (float)(int8_t)(w >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
         const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = __ldg(bc + r0 * L.pitch + c0), t1 = __ldg(bc + r1 * L.pitch + c1);
-        byte |= (unsigned)(t0 < t1) << k;
+        t0[k] = __ldg(bc + r0 * L.pitch + c0); t1[k] = __ldg(bc + r1 * L.pitch + c1);
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) byte |= (unsigned)(t0[k] < t1[k]) << k;
     P.desc[((long long)frame * P.kp_capacity + o) * 32 + lane] = (uint8_t)byte;
 
     if (lane == 0) {
