@@ -278,7 +278,7 @@ def run_ours(args, rank, world, local_rank):
     ex = pkg.ORBextractor(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"], device=local_rank)
     cap = ex.max_keypoints(w, h)
     if args.streams or args.chunk:
-        ex.set_batching(args.streams or 3, args.chunk or 64)
+        ex.set_batching(args.streams or 4, args.chunk or 64)
 
     # synthetic frames: every rank owns its own batch (weak scaling)
     h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
@@ -342,6 +342,26 @@ def run_ours(args, rank, world, local_rank):
         raise RuntimeError("host-buffer and device-buffer paths disagree on keypoint counts")
     total_launches = sum_over_ranks(float(launches))
 
+    # ---- per-kernel durations with each kernel running alone: the same batch, chunks serialised on one stream
+    #      (in the timed region above the chunk streams overlap, which inflates every per-stream stage time)
+    ser_stage, ser_launches, ser_ms = None, 0, 0.0
+    if rank == 0:
+        ex.set_batching(1, args.chunk or 64)
+        step_device()
+        ex.set_profiling(True)
+        ex.stage_ms(reset=True)
+        l1 = ex.launch_count()
+        for _ in range(min(args.steps, 3)):
+            ser_ms += step_device()
+        ser_launches = ex.launch_count() - l1
+        ser_stage = ex.stage_ms(reset=True)
+        ex.set_profiling(False)
+        ex.set_batching(args.streams or 4, args.chunk or 64)
+    ser_steps = min(args.steps, 3)
+    hamming = None
+    if args.hamming_keyframes >= 2:
+        hamming = bench_hamming(pkg, torch, dist, rank, world, local_rank, args.hamming_keyframes, 1000)
+
     total_frames = n * world * args.steps
     value = total_frames / (dev_ms * 1e-3)
     e2e_value = total_frames / (max(e2e_ms, wall_e2e_ms) * 1e-3)      # the slower of device events and host wall clock
@@ -351,27 +371,36 @@ def run_ours(args, rank, world, local_rank):
             dist.destroy_process_group()
         return 0
 
-    # ---- roofline of the dominant kernel stage (rank 0's own stream events)
+    # ---- roofline of the dominant kernel (rank 0): CUDA events on the launching stream, serialised pass
     peak, peak_src = load_peaks()
     path_bytes, stage_bytes = algorithmic_bytes(w, h, p["nfeatures"], p["nlevels"], p["scale"])
-    kstages = {k: stage[k] for k in ("pyramid", "fast_cells", "octree", "blur", "describe")}
+    knames = ("pyramid", "fast_cells", "octree", "blur", "describe")
+    kstages = {k: ser_stage[k] for k in knames}
     dom = max(kstages, key=kstages.get)
     per_chunk_launches = (p["nlevels"] - 1) + 4
-    chunks = max(1, int(round(launches / per_chunk_launches)))
-    frames_per_launch = n * args.steps / chunks
+    chunks = max(1, int(round(ser_launches / per_chunk_launches)))
+    frames_per_launch = n * ser_steps / chunks
     launch_ms = kstages[dom] / chunks
     achieved = stage_bytes[dom] * frames_per_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+    ktot = sum(kstages.values())
     roofline = {
         "bound": "hbm", "kernel": {"pyramid": "k_resize_level (x%d levels)" % (p["nlevels"] - 1), "fast_cells": "k_fast_cells",
                                    "octree": "k_octree", "blur": "k_blur", "describe": "k_describe"}[dom],
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
         "peak_source": peak_src, "bytes_per_frame": stage_bytes[dom], "frames_per_launch": frames_per_launch,
         "launch_ms": launch_ms,
-        "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
+        "kernel_share_of_step": {k: kstages[k] / ktot for k in knames},
+        "stage_ms_per_step_serialized": {k: v / ser_steps for k, v in ser_stage.items()},
+        "serialized_frames_per_s": n * ser_steps / (ser_ms * 1e-3),
+        "stage_ms_per_step_overlapped": {k: v / args.steps for k, v in stage.items()},
+        "per_kernel": {k: {"bytes_per_frame": stage_bytes[k], "launch_ms": kstages[k] / chunks,
+                           "achieved_gbs": stage_bytes[k] * frames_per_launch / (kstages[k] / chunks * 1e-3) / 1e9 if kstages[k] > 0 else 0.0}
+                       for k in knames},
         "path_bytes_per_frame": path_bytes,
         "path_achieved": value / world * path_bytes / 1e9, "path_frac": value / world * path_bytes / 1e9 / peak,
-        "note": "stage times are CUDA events on the library's 3 chunk streams; chunks overlap, so each stage time "
-                "includes sharing the GPU with the other streams' kernels",
+        "note": "launch_ms: CUDA events on the launching stream in a pass with the chunks serialised on one stream, run "
+                "right after the timed region on the same batch; in the timed region the chunk streams overlap "
+                "(stage_ms_per_step_overlapped), so those per-stream times include sharing the GPU",
     }
 
     line = {
@@ -391,6 +420,8 @@ def run_ours(args, rank, world, local_rank):
         "wall_ms_per_step": wall_dev_ms / args.steps,
         "roofline": roofline,
     }
+    if hamming is not None:
+        line["hamming"] = hamming
     if world == 1 and not args.no_cpu:
         threads = host_threads()
         sample = max(32, 4 * threads)
@@ -407,6 +438,52 @@ def run_ours(args, rank, world, local_rank):
     return 0
 
 
+def bench_hamming(pkg, torch, dist, rank, world, local_rank, num_keyframes, n_per_kf, reps=3):
+    """All-pairs keyframe matching (BASELINE config 5 shape, K keyframes x n descriptors): every rank holds all
+    descriptors, owns round-robin blocks of the upper-triangular pair list, counts accepted matches per pair
+    (best <= TH_LOW && best < 0.6 * second) and the counts are exchanged with ONE all_gather (NCCL)."""
+    shard = pkg.shard
+    desc = pkg.synth.keyframe_descriptors(num_keyframes, n_per_kf)
+    pairs = shard.all_pairs(num_keyframes)
+    block = 4096
+    mine = np.concatenate([pairs[s:e] for s, e in shard.pair_blocks_of_rank(len(pairs), rank, world, block)] or
+                          [np.zeros((0, 2), np.int32)])
+    m = pkg.ORBmatcher(0.6, True, device=local_rank)
+    d_desc = torch.from_numpy(desc).cuda()
+    m.set_keyframes_device(d_desc.data_ptr(), num_keyframes, n_per_kf)
+    d_pairs = torch.from_numpy(np.ascontiguousarray(mine)).cuda()
+    d_counts = torch.zeros((max(len(mine), 1),), dtype=torch.int32, device="cuda")
+    best_ms, gather_ms, full = None, 0.0, None
+    for _ in range(reps + 1):                                  # first pass = warm-up
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        if len(mine):
+            m.count_pairs_device(d_pairs.data_ptr(), len(mine), d_counts.data_ptr())   # synchronous; kernel on the matcher's stream
+        e1.record()
+        full = shard.gather_pair_counts(d_counts[:len(mine)], len(pairs), rank, world, block, dist=dist, device="cuda")
+        e2.record()
+        torch.cuda.synchronize()
+        k_ms = m.last_kernel_ms() if len(mine) else 0.0
+        g_ms = e1.elapsed_time(e2)
+        t = torch.tensor([k_ms + g_ms, k_ms, g_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tot, k_ms, g_ms = [float(x) for x in t.tolist()]
+        if best_ms is None or tot < best_ms[0]:
+            best_ms = (tot, k_ms, g_ms)
+    m.close()
+    tot, k_ms, g_ms = best_ms
+    npairs = len(pairs)
+    return {"metric": "hamming_query_matches_per_s", "value": npairs * n_per_kf / (tot * 1e-3), "unit": "matches/s",
+            "distance_evals_per_s": npairs * float(n_per_kf) * n_per_kf / (tot * 1e-3), "keyframes": num_keyframes,
+            "descriptors_per_keyframe": n_per_kf, "pairs": npairs, "kernel_ms": k_ms, "gather_ms": g_ms,
+            "gather": "one all_gather of int32 counts (NCCL)" if world > 1 else "none (1 GPU)",
+            "accepted_total": int(full.clamp(min=0).sum().item()), "timing": "best of %d, max over ranks" % reps}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -416,6 +493,7 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_STEP, help="frames per step per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="wall time budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--hamming-keyframes", type=int, default=384, help="keyframes of the all-pairs Hamming leg (0 = skip; 4096 = full config 5)")
     ap.add_argument("--streams", type=int, default=0, help="internal chunk streams; 0 = library default")
     ap.add_argument("--chunk", type=int, default=0, help="max frames per chunk; 0 = library default")
     args = ap.parse_args()
@@ -423,6 +501,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         return run_reference(args, rank)
     if world == 1 and args.gpus > 1:

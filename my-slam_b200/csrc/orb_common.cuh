@@ -18,8 +18,12 @@
 #define ORB_BORDER 16        // EDGE_THRESHOLD - 3: origin of the FAST cell grid, :773
 #define ORB_HALF_PATCH 15    // HALF_PATCH_SIZE, :75
 #define ORB_PATCH 31         // PATCH_SIZE, :74
-#define ORB_BLUR_ROWS 28     // output rows per k_blur thread
+#ifndef ORB_BLUR_ROWS
+#define ORB_BLUR_ROWS 28     // output rows per k_blur thread (multiple of 7)
+#endif
+#ifndef ORB_BLUR_THREADS
 #define ORB_BLUR_THREADS 128 // tasks per k_blur CTA
+#endif
 
 struct OrbLevel {
     int w, h, pitch;             // level size; pitch of pyr/blur rows for this level

@@ -36,8 +36,12 @@ int orb_upload_constants(const int* umax16)
 // (source index, weights) are built on the host in double/float exactly as OpenCV does.
 // One thread = 4 horizontally adjacent output pixels = one aligned 32-bit store.
 // =================================================================================================
+#ifndef RS_ROWS
 #define RS_ROWS 8             // output rows per thread
+#endif
+#ifndef RS_THREADS
 #define RS_THREADS 128
+#endif
 
 // horizontal pass of one source row for this thread's 4 output pixels: H[j] = S[s_j]*a0_j + S[s_j + 1]*a1_j.
 // WORDS: the 4 pixel pairs lie inside three aligned words starting at word wb (byte offsets o_j = s_j - 4wb).
@@ -159,7 +163,9 @@ int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
 // are written in row-major order (warp ballot + popc prefix) to the cell's slot area.
 // =================================================================================================
 #define FAST_TP 64            // shared-memory row pitch of the cell tile (max cell image width is 59)
+#ifndef FAST_WARPS
 #define FAST_WARPS 8
+#endif
 
 __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
 {

@@ -92,8 +92,10 @@ struct orbgpu_extractor {
     Plan plan;
     StreamCtx ctx[NSTREAM];
     bool profiling = false;
-    int nstream = 4;                    // chunk streams a batch call deals its chunks to (1..NSTREAM)
-    int max_chunk = 32;                 // frames per chunk (upper bound; also capped by plan.chunk_cap)
+    // how a batch call is cut up: [0] host-buffer calls (finer chunks pipeline PCIe against the kernels),
+    // [1] device-buffer calls (fewer, larger launches); orbgpu_set_batching overrides both
+    int nstream[2] = {8, 4};            // chunk streams a batch call deals its chunks to (1..NSTREAM)
+    int max_chunk[2] = {32, 64};        // frames per chunk (upper bound; also capped by plan.chunk_cap)
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
@@ -610,11 +612,11 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
     const bool pin_in = is_pinned(frames);
     const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
-    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk), (n + e->nstream - 1) / e->nstream));
+    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk[0]), (n + e->nstream[0] - 1) / e->nstream[0]));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
-        StreamCtx& c = e->ctx[k % e->nstream];
+        StreamCtx& c = e->ctx[k % e->nstream[0]];
         const int m = std::min(chunk, n - i0);
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
@@ -647,11 +649,11 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
     for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
     if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
-    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk), (n + e->nstream - 1) / e->nstream));
+    const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk[1]), (n + e->nstream[1] - 1) / e->nstream[1]));
     int result = ORBGPU_OK, k = 0;
     if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
     for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
-        StreamCtx& c = e->ctx[k % e->nstream];
+        StreamCtx& c = e->ctx[k % e->nstream[1]];
         const int m = std::min(chunk, n - i0);
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
@@ -922,8 +924,8 @@ int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames)
     if (!e || streams < 1 || streams > NSTREAM || max_chunk_frames < 1) return ORBGPU_ERR_ARG;
     for (int s = 0; s < NSTREAM; ++s)
         if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
-    e->nstream = streams;
-    e->max_chunk = max_chunk_frames;
+    e->nstream[0] = e->nstream[1] = streams;
+    e->max_chunk[0] = e->max_chunk[1] = max_chunk_frames;
     return ORBGPU_OK;
 }
 

@@ -71,3 +71,19 @@ CONFIGS = {
 def config_frames(name: str, count: int, start: int = 0) -> np.ndarray:
     w, h, _, base, _ = CONFIGS[name]
     return np.stack([synth(w, h, base + start + i) for i in range(count)])
+
+
+def keyframe_descriptors(num_keyframes: int, n_per_keyframe: int, seed: int = 0x5EED4000) -> np.ndarray:
+    """BASELINE config 5 input (SURVEY.md section 8(d) C5): [K, n, 32] uint8.  A pool of 65 536 base 256-bit words;
+    keyframe k, descriptor j = pool[(977k + 31j) mod 65536] XOR noise, each noise bit the AND of 4 PRNG bits
+    (p = 1/16), so two copies of a base word differ by ~30 bits (< TH_LOW) and unrelated words by ~128."""
+    pool = splitmix64(seed, 0, 65536 * 4).reshape(65536, 4)
+    k = np.arange(num_keyframes, dtype=np.int64)[:, None]
+    j = np.arange(n_per_keyframe, dtype=np.int64)[None, :]
+    base = pool[(977 * k + 31 * j) % 65536]                                   # [K, n, 4] uint64
+    cnt = num_keyframes * n_per_keyframe * 4
+    noise = splitmix64(seed ^ 0xA5A5, 0, cnt)
+    for r in range(1, 4):
+        noise &= splitmix64(seed ^ 0xA5A5, r * cnt, cnt)
+    out = base ^ noise.reshape(num_keyframes, n_per_keyframe, 4)
+    return np.ascontiguousarray(out).view(np.uint8).reshape(num_keyframes, n_per_keyframe, 32)
