@@ -70,13 +70,22 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
                                              int sw, int sh, uint8_t* __restrict__ dst, int wc, int y0, const int s[4],
                                              const int o[4], const unsigned a01[4], int wb, int wlast)
 {
+    // y-axis table entries of all RS_ROWS rows first (independent loads), then the rows
+    int sy[RS_ROWS];
+    unsigned b01[RS_ROWS];
+#pragma unroll
+    for (int k = 0; k < RS_ROWS; ++k) {
+        const int dy = min(y0 + k, D.h - 1);
+        sy[k] = P.rs_ofs[D.yofs_off + dy];
+        b01[k] = *reinterpret_cast<const unsigned*>(P.rs_a + 2 * (D.yofs_off + dy));
+    }
     int Ha[4], Hb[4], ya = -1, yb = -1;                        // cached horizontal rows (source row indices ya, yb)
-    const int yend = min(y0 + RS_ROWS, D.h);
-    for (int dy = y0; dy < yend; ++dy) {
-        const int sy = P.rs_ofs[D.yofs_off + dy];
-        const unsigned b01 = *reinterpret_cast<const unsigned*>(P.rs_a + 2 * (D.yofs_off + dy));
-        const int b0 = (int)(b01 & 0xFFFFu), b1 = (int)(b01 >> 16);
-        const int r0 = min(max(sy, 0), sh - 1), r1 = min(max(sy + 1, 0), sh - 1);
+#pragma unroll
+    for (int k = 0; k < RS_ROWS; ++k) {
+        const int dy = y0 + k;
+        if (dy >= D.h) break;
+        const int b0 = (int)(b01[k] & 0xFFFFu), b1 = (int)(b01[k] >> 16);
+        const int r0 = min(max(sy[k], 0), sh - 1), r1 = min(max(sy[k] + 1, 0), sh - 1);
         if (r0 == yb) {                                        // the usual step: last row's lower line is this row's upper line
 #pragma unroll
             for (int j = 0; j < 4; ++j) Ha[j] = Hb[j];
@@ -263,8 +272,14 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
 
     const int cs = 3 + sh, ce = cs + iw;                       // interior tile columns [cs, ce), rows [3, 3 + ih)
     const int w0 = cs >> 2, nwi = ((ce - 1) >> 2) - w0 + 1;    // words of a row that hold interior pixels
-    const int ntask = ih * nwi;
-    const float inv_nwi = 1.0f / (float)nwi, inv_iw = 1.0f / (float)iw;
+    const float inv_iw = 1.0f / (float)iw;
+    // pass-1 lane layout, fixed for the cell: rpi = 32 / nwi rows per iteration, lane -> (row lrow, word w0 + lcol)
+    const int rpi = 32 / nwi, lrow = lane / nwi, lcol = lane - lrow * nwi;
+    const bool lrow_ok = lrow < rpi;
+    const int loff = (3 + lrow) * FAST_TP + 4 * (w0 + lcol);   // tile offset of the lane's word in the first iteration
+    unsigned lmask = 0x80808080u;                              // flag bits of the word's bytes that are interior pixels
+    if (4 * (w0 + lcol) < cs) lmask &= 0xFFFFFFFFu << (8 * (cs - 4 * (w0 + lcol)));
+    if (4 * (w0 + lcol) + 4 > ce) lmask &= 0xFFFFFFFFu >> (8 * (4 * (w0 + lcol) + 4 - ce));
     uint16_t* q = s_queue[warp];
     uint16_t* cl = s_corner[warp];
     uint32_t* slot = P.slots + (long long)frame * P.slot_frame_words + P.lv[l].slot_off + cell.slot_off;
@@ -296,19 +311,14 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
 
         if (th <= 126) {
             const unsigned K = (unsigned)(127 - th) * 0x01010101u;
-            for (int base = 0; base < ntask; base += 32) {
-                const int t = base + lane;
+            for (int y0 = 0; y0 < ih; y0 += rpi) {             // rpi rows of nwi words per iteration
                 unsigned f = 0;
-                int off = 0;
-                if (t < ntask) {
-                    const int yi = __float2int_rd(((float)t + 0.5f) * inv_nwi), wi = w0 + t - yi * nwi;
-                    off = (yi + 3) * FAST_TP + 4 * wi;
+                const int off = loff + y0 * FAST_TP;
+                if (lrow_ok && y0 + lrow < ih) {
                     const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off);
                     const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
                     const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
-                    f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & 0x80808080u;
-                    if (4 * wi < cs) f &= 0xFFFFFFFFu << (8 * (cs - 4 * wi));
-                    if (4 * wi + 4 > ce) f &= 0xFFFFFFFFu >> (8 * (4 * wi + 4 - ce));
+                    f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
                 }
                 if (__ballot_sync(0xffffffffu, f != 0) == 0) continue;
                 // queue order is irrelevant (results are keyed by position): exclusive prefix of the per-lane counts

@@ -28,16 +28,32 @@ void orbgpu_internal_set_error(const char* s);   // orbgpu_extractor.cu (thread-
         }                                                                                             \
     } while (0)
 
+// 256-bit Hamming distance.  POPC issues at a quarter of the ALU rate, so the 8 XOR words are first folded
+// by three carry-save adders (sum = a^b^c, carry = maj(a,b,c), one LOP3 each): 8 words -> 2 sum words + 3 carry
+// words, d = popc(s1) + popc(s2) + 2 (popc(c0) + popc(c1) + popc(c2)): 5 POPC instead of 8.
+__device__ __forceinline__ unsigned csa_sum(unsigned a, unsigned b, unsigned c) { return a ^ b ^ c; }
+__device__ __forceinline__ unsigned csa_carry(unsigned a, unsigned b, unsigned c) { return (a & b) | (c & (a | b)); }
+
 __device__ __forceinline__ int hamming256(const uint4& q0, const uint4& q1, const uint4& c0, const uint4& c1)
 {
-    return __popc(q0.x ^ c0.x) + __popc(q0.y ^ c0.y) + __popc(q0.z ^ c0.z) + __popc(q0.w ^ c0.w) +
-           __popc(q1.x ^ c1.x) + __popc(q1.y ^ c1.y) + __popc(q1.z ^ c1.z) + __popc(q1.w ^ c1.w);
+    const unsigned x0 = q0.x ^ c0.x, x1 = q0.y ^ c0.y, x2 = q0.z ^ c0.z, x3 = q0.w ^ c0.w;
+    const unsigned x4 = q1.x ^ c1.x, x5 = q1.y ^ c1.y, x6 = q1.z ^ c1.z, x7 = q1.w ^ c1.w;
+    const unsigned s0 = csa_sum(x0, x1, x2), k0 = csa_carry(x0, x1, x2);
+    const unsigned s1 = csa_sum(x3, x4, x5), k1 = csa_carry(x3, x4, x5);
+    const unsigned s2 = csa_sum(x6, x7, s0), k2 = csa_carry(x6, x7, s0);
+    return __popc(s1) + __popc(s2) + 2 * (__popc(k0) + __popc(k1) + __popc(k2));
 }
+
+// (distance, index) packed as d << 22 | j: min over the packed value is the lowest distance and, among equal
+// distances, the lowest index -- the strict '<' update of src/ORBmatcher.cc:201-226.  Needs j < 2^22.
+#define MATCH_IDX_BITS 22
+#define MATCH_INIT ((256u << MATCH_IDX_BITS) | ((1u << MATCH_IDX_BITS) - 1u))
 
 // scan all nB candidates (index order) for this thread's query; the CTA cooperates on staging
 __device__ __forceinline__ void scan_candidates(const uint4* __restrict__ B, int nB, bool active, const uint4& q0,
                                                 const uint4& q1, uint4* s_tile, int& best, int& second, int& best_idx)
 {
+    unsigned pb = MATCH_INIT, ps = MATCH_INIT;                 // best and second-best packed values
     for (int t0 = 0; t0 < nB; t0 += MATCH_TILE) {
         const int tn = min(MATCH_TILE, nB - t0);
         __syncthreads();
@@ -46,12 +62,17 @@ __device__ __forceinline__ void scan_candidates(const uint4* __restrict__ B, int
         if (active) {
 #pragma unroll 4
             for (int j = 0; j < tn; ++j) {
-                const int d = hamming256(q0, q1, s_tile[2 * j], s_tile[2 * j + 1]);
-                if (d < best) { second = best; best = d; best_idx = t0 + j; }
-                else if (d < second) second = d;
+                const unsigned cur = ((unsigned)hamming256(q0, q1, s_tile[2 * j], s_tile[2 * j + 1]) << MATCH_IDX_BITS) | (unsigned)(t0 + j);
+                const unsigned hi = max(pb, cur);
+                pb = min(pb, cur);
+                ps = min(ps, hi);
             }
         }
     }
+    best = (int)(pb >> MATCH_IDX_BITS);
+    second = (int)(ps >> MATCH_IDX_BITS);
+    best_idx = pb == MATCH_INIT ? -1 : (int)(pb & ((1u << MATCH_IDX_BITS) - 1u));
+    if (nB == 0) best_idx = -1;
 }
 
 __global__ void __launch_bounds__(MATCH_THREADS) k_match_bruteforce(const uint4* __restrict__ A, int nA,
@@ -112,6 +133,7 @@ int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t*
                             int32_t* best_idx, uint16_t* best, uint16_t* second)
 {
     if (!A || !B || !best_idx || !best || !second || nA < 1 || nB < 0) return ORBGPU_ERR_ARG;
+    if (nB >= (1 << 22) - 1) return ORBGPU_ERR_UNSUPPORTED;   // candidate index is packed into 22 bits
     CUM(cudaSetDevice(device));
     uint4 *dA = nullptr, *dB = nullptr; int32_t* di = nullptr; uint16_t *d1 = nullptr, *d2 = nullptr;
     CUM(cudaMalloc(&dA, 32 * (size_t)nA));
@@ -161,6 +183,7 @@ void orbgpu_matcher_destroy(orbgpu_matcher* m)
 int orbgpu_matcher_set_keyframes(orbgpu_matcher* m, const uint8_t* desc, int num_keyframes, int n_per_keyframe)
 {
     if (!m || !desc || num_keyframes < 1 || n_per_keyframe < 1) return ORBGPU_ERR_ARG;
+    if (n_per_keyframe >= (1 << 22) - 1) return ORBGPU_ERR_UNSUPPORTED;
     CUM(cudaSetDevice(m->device));
     if (m->own_desc) cudaFree(m->d_desc);
     m->d_desc = nullptr; m->own_desc = false;
@@ -175,6 +198,7 @@ int orbgpu_matcher_set_keyframes(orbgpu_matcher* m, const uint8_t* desc, int num
 int orbgpu_matcher_set_keyframes_device(orbgpu_matcher* m, const uint8_t* d_desc, int num_keyframes, int n_per_keyframe)
 {
     if (!m || !d_desc || num_keyframes < 1 || n_per_keyframe < 1 || ((uintptr_t)d_desc & 15)) return ORBGPU_ERR_ARG;
+    if (n_per_keyframe >= (1 << 22) - 1) return ORBGPU_ERR_UNSUPPORTED;
     CUM(cudaSetDevice(m->device));
     if (m->own_desc) cudaFree(m->d_desc);
     m->d_desc = reinterpret_cast<uint4*>(const_cast<uint8_t*>(d_desc));
