@@ -383,10 +383,18 @@ def run_ours(args, rank, world, local_rank):
     launch_ms = kstages[dom] / chunks
     achieved = stage_bytes[dom] * frames_per_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
     ktot = sum(kstages.values())
+    traffic, traffic_src = None, None
+    try:                                                      # dram bytes of that kernel from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        traffic = tj["dram_bytes_per_frame"][dom] * frames_per_launch
+        traffic_src = tj["source"]
+    except Exception:
+        pass
     roofline = {
         "bound": "hbm", "kernel": {"pyramid": "k_resize_level (x%d levels)" % (p["nlevels"] - 1), "fast_cells": "k_fast_cells",
                                    "octree": "k_octree", "blur": "k_blur", "describe": "k_describe"}[dom],
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+        "traffic_source": traffic_src, "algorithmic_bytes_per_launch": stage_bytes[dom] * frames_per_launch,
         "peak_source": peak_src, "bytes_per_frame": stage_bytes[dom], "frames_per_launch": frames_per_launch,
         "launch_ms": launch_ms,
         "kernel_share_of_step": {k: kstages[k] / ktot for k in knames},
