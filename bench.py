@@ -239,6 +239,25 @@ def run_reference(args, rank):
     return 0
 
 
+def bind_to_gpu_cpus(index):
+    """Pins this process to the CPUs local to GPU `index` (NVML's ideal affinity), so the pinned frame buffers are
+    first-touched on the NUMA node next to the GPU's PCIe root.  Plumbing only; returns a note for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        allowed = os.sched_getaffinity(0)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(allowed) // 64) + 1)
+        ideal = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1}
+        use = ideal & allowed
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            return "bound to %d of %d allowed CPUs (NVML ideal affinity of GPU %d)" % (len(use), len(allowed), index)
+        return "no narrower GPU-local CPU set (%d allowed CPUs)" % len(allowed)
+    except Exception as e:                                    # containers may forbid it: measured anyway
+        return "affinity not set: %s" % type(e).__name__
+
+
 # ---------------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------------
@@ -250,6 +269,8 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available() or pkg.device_count() < 1:
         raise RuntimeError("bench.py: no CUDA device visible; the orbgpu path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_cpus(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -419,7 +440,7 @@ def run_ours(args, rank, world, local_rank):
                    "ini_th": p["ini_th"], "min_th": p["min_th"], "width": w, "height": h,
                    "frames_per_step_per_gpu": n, "parallelism": "frames sharded %d-way, no data-path collective" % world,
                    "l2": "inputs larger than L2: %.0f MB of frames per step vs %.0f MB L2" % (n * w * h / 1e6, L2_BYTES / 1e6),
-                   "keypoints_per_step_per_gpu": nkp_dev},
+                   "keypoints_per_step_per_gpu": nkp_dev, "host_affinity": numa},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * w * h * world,
                 "d2h_bytes_per_step": (n * cap * 60 + 4 * n) * world,
@@ -430,6 +451,7 @@ def run_ours(args, rank, world, local_rank):
     }
     if hamming is not None:
         line["hamming"] = hamming
+    os.sched_setaffinity(0, all_cpus)                         # the CPU legs use every host core again
     if world == 1 and not args.no_cpu:
         threads = host_threads()
         sample = max(32, 4 * threads)
