@@ -398,7 +398,7 @@ def run_ours(args, rank, world, local_rank):
     knames = ("pyramid", "fast_cells", "octree", "blur", "describe")
     kstages = {k: ser_stage[k] for k in knames}
     dom = max(kstages, key=kstages.get)
-    per_chunk_launches = (p["nlevels"] - 1) + 4
+    per_chunk_launches = (p["nlevels"] - 1) + 4 + (1 if w % 16 else 0)   # + k_repitch when rows are not 16-byte multiples
     chunks = max(1, int(round(ser_launches / per_chunk_launches)))
     frames_per_launch = n * ser_steps / chunks
     launch_ms = kstages[dom] / chunks
@@ -526,7 +526,15 @@ def main():
     ap.add_argument("--hamming-keyframes", type=int, default=384, help="keyframes of the all-pairs Hamming leg (0 = skip; 4096 = full config 5)")
     ap.add_argument("--streams", type=int, default=0, help="internal chunk streams; 0 = library default")
     ap.add_argument("--chunk", type=int, default=0, help="max frames per chunk; 0 = library default")
+    ap.add_argument("--workload", default="C1", choices=["C1", "C2", "C3", "C4"],
+                    help="BASELINE.json extraction config (default C1 = the shape the metric is quoted on)")
     args = ap.parse_args()
+    global WORKLOAD, METRIC
+    WORKLOAD = {"C1": "C1_tum_640x480_nf1000", "C2": "C2_kitti_1241x376_nf2000", "C3": "C3_euroc_752x480_nf1000",
+                "C4": "C4_hd_1920x1080_nf4000"}[args.workload]
+    PARAMS["nfeatures"] = {"C1": 1000, "C2": 2000, "C3": 1000, "C4": 4000}[args.workload]
+    if args.workload != "C1":
+        METRIC = "orb_extract_frames_per_s_" + WORKLOAD.split("_", 1)[1]
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -31,6 +31,32 @@ int orb_upload_constants(const int* umax16)
 }
 
 // =================================================================================================
+// Level 0 whose rows are not 4-byte aligned (dense 1241-px KITTI frames ...) is copied once into a buffer
+// with a 16-byte-multiple pitch, so that every other kernel stays on its aligned word path.
+// =================================================================================================
+__global__ void __launch_bounds__(256) k_repitch(const uint8_t* __restrict__ src, long long src_frame_stride, int src_pitch,
+                                                 uint8_t* __restrict__ dst, int dst_pitch, int w, int h)
+{
+    const int wpr = dst_pitch >> 2;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int y = t / wpr, x4 = (t - y * wpr) * 4;
+    if (y >= h) return;
+    const uint8_t* __restrict__ r = src + (long long)blockIdx.y * src_frame_stride + (long long)y * src_pitch;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v |= (uint32_t)__ldg(r + min(x4 + k, w - 1)) << (8 * k);
+    *reinterpret_cast<uint32_t*>(dst + ((long long)blockIdx.y * h + y) * dst_pitch + x4) = v;
+}
+
+int orb_launch_repitch(const uint8_t* src, long long src_frame_stride, int src_pitch, uint8_t* dst, int dst_pitch, int w, int h,
+                       int nframes, cudaStream_t st)
+{
+    const int ntask = (dst_pitch >> 2) * h;
+    k_repitch<<<dim3((ntask + 255) / 256, nframes), 256, 0, st>>>(src, src_frame_stride, src_pitch, dst, dst_pitch, w, h);
+    return 1;
+}
+
+// =================================================================================================
 // Pyramid: level l from level l-1, OpenCV's fixed-point bilinear (11-bit weights; horizontal pass in
 // int32, vertical pass ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.  The per-axis tables
 // (source index, weights) are built on the host in double/float exactly as OpenCV does.

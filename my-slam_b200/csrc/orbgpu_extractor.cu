@@ -48,7 +48,8 @@ struct Plan {
     int ntiles = 0;
     int fast_smem = 0, key_smem_cap = 0, node_smem_cap = 0;
     int kmax = 0;                      // max keypoints per frame
-    size_t in_frame_bytes = 0;         // dense upload buffer, pitch = w
+    size_t in_pitch = 0;               // row pitch of the upload buffer d_in: w rounded up to 16 B (aligned word loads)
+    size_t in_frame_bytes = 0;         // in_pitch * h
     size_t bytes_per_frame = 0;
     int chunk_cap = 1;
     void free_dev()
@@ -63,6 +64,7 @@ struct StreamCtx {
     cudaEvent_t ev[EV_COUNT] = {};
     cudaEvent_t done = nullptr;
     int cap = 0;                       // frames the buffers below can hold
+    uint8_t* d_raw = nullptr; size_t raw_bytes = 0;   // dense copy of unaligned frames before k_repitch (lazily allocated)
     uint8_t *d_in = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_scratch = nullptr, *d_desc = nullptr;
     uint32_t *d_cellcnt = nullptr, *d_slots = nullptr, *d_sel = nullptr;
     int *d_selcnt = nullptr, *d_candcnt = nullptr, *d_nout = nullptr;
@@ -281,7 +283,8 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
     if (np.fast_smem < 0 || np.fast_smem > 200 * 1024) return ORBGPU_ERR_UNSUPPORTED;
     np.key_smem_cap = std::min(std::max(8 * D.lv[0].nfeat, 1024), 6144);
     np.node_smem_cap = std::min(max_node_cap, 1024);
-    np.in_frame_bytes = (size_t)w * h;
+    np.in_pitch = align_up((size_t)w, 16);
+    np.in_frame_bytes = np.in_pitch * h;
     np.bytes_per_frame = np.in_frame_bytes + (size_t)D.pyr_frame_bytes + (size_t)D.blur_frame_bytes +
                          (size_t)D.slot_frame_words * 4 + (size_t)D.scratch_frame_bytes + (size_t)D.ncells * 4 +
                          (size_t)sel_total * 4 + (size_t)np.kmax * 60 + 256;
@@ -305,6 +308,7 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
 
 static void ctx_free_buffers(StreamCtx& c)
 {
+    cudaFree(c.d_raw); c.d_raw = nullptr; c.raw_bytes = 0;
     cudaFree(c.d_in); cudaFree(c.d_pyr); cudaFree(c.d_blur); cudaFree(c.d_scratch); cudaFree(c.d_desc);
     cudaFree(c.d_cellcnt); cudaFree(c.d_slots); cudaFree(c.d_sel); cudaFree(c.d_selcnt); cudaFree(c.d_candcnt);
     cudaFree(c.d_nout); cudaFree(c.d_kps);
@@ -336,7 +340,7 @@ static int ctx_reserve(orbgpu_extractor* e, StreamCtx& c, int frames, int plan_w
     CU(cudaMalloc(&c.d_nout, n * 4));
     CU(cudaMalloc(&c.d_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint)));
     CU(cudaMalloc(&c.d_desc, n * (size_t)std::max(pl.kmax, 1) * 32));
-    CU(cudaHostAlloc(&c.h_in, n * pl.in_frame_bytes + 64, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&c.h_in, n * (size_t)pl.w * pl.h + 64, cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint), cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_desc, n * (size_t)std::max(pl.kmax, 1) * 32, cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_nout, n * 4, cudaHostAllocDefault));
@@ -419,25 +423,44 @@ static int use_device(orbgpu_extractor* e)
     return ORBGPU_OK;
 }
 
-// upload `m` frames starting at host pointer `src` into c.d_in (dense, pitch = w)
+static int reserve_raw(StreamCtx& c, size_t bytes)
+{
+    if (c.raw_bytes >= bytes) return ORBGPU_OK;
+    cudaFree(c.d_raw); c.d_raw = nullptr; c.raw_bytes = 0;
+    CU(cudaMalloc(&c.d_raw, bytes + 64));
+    c.raw_bytes = bytes;
+    return ORBGPU_OK;
+}
+
+// upload `m` frames starting at host pointer `src` into c.d_in (row pitch plan.in_pitch, frames in_pitch * h apart).
+// PCIe copies are always plain 1-D copies of dense frames; when the pitched layout differs from the dense one
+// (w not a multiple of 16) the frames land in d_raw and k_repitch lays them out.
 static int upload_frames(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, int m, int w, int h,
                          size_t row_stride, size_t frame_stride, bool pinned)
 {
-    const size_t fb = (size_t)w * h;
+    const size_t fb = (size_t)w * h, dp = e->plan.in_pitch;
+    const bool repitch = dp != (size_t)w;
+    int rc;
+    if (repitch && (rc = reserve_raw(c, fb * m)) != ORBGPU_OK) return rc;
+    uint8_t* dense = repitch ? c.d_raw : c.d_in;
     if (pinned && row_stride == (size_t)w && frame_stride == fb) {
-        CU(cudaMemcpyAsync(c.d_in, src, fb * m, cudaMemcpyHostToDevice, c.st));
-    } else if (pinned && frame_stride == row_stride * h) {
-        CU(cudaMemcpy2DAsync(c.d_in, (size_t)w, src, row_stride, (size_t)w, (size_t)h * m, cudaMemcpyHostToDevice, c.st));
-    } else {
+        CU(cudaMemcpyAsync(dense, src, fb * m, cudaMemcpyHostToDevice, c.st));
+    } else if (pinned && row_stride == (size_t)w) {
+        for (int i = 0; i < m; ++i)
+            CU(cudaMemcpyAsync(dense + (size_t)i * fb, src + (size_t)i * frame_stride, fb, cudaMemcpyHostToDevice, c.st));
+    } else {                                               // strided rows or pageable memory: gather into the pinned staging buffer
         for (int i = 0; i < m; ++i) {
             const uint8_t* f = src + (size_t)i * frame_stride;
             uint8_t* d = c.h_in + (size_t)i * fb;
             if (row_stride == (size_t)w) memcpy(d, f, fb);
             else for (int y = 0; y < h; ++y) memcpy(d + (size_t)y * w, f + (size_t)y * row_stride, (size_t)w);
         }
-        CU(cudaMemcpyAsync(c.d_in, c.h_in, fb * m, cudaMemcpyHostToDevice, c.st));
+        CU(cudaMemcpyAsync(dense, c.h_in, fb * m, cudaMemcpyHostToDevice, c.st));
     }
-    (void)e;
+    if (repitch) {
+        if (orb_launch_repitch(c.d_raw, (long long)fb, w, c.d_in, (int)dp, w, h, m, c.st) < 0) return ORBGPU_ERR_CUDA;
+        e->launches += 1;
+    }
     return ORBGPU_OK;
 }
 
@@ -472,7 +495,7 @@ static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, i
     if (prof) CU(cudaEventRecord(c.ev[EV_BEGIN], c.st));
     if ((rc = upload_frames(e, c, src, m, w, h, row_stride, frame_stride, pinned_in)) != ORBGPU_OK) return rc;
     if (prof) CU(cudaEventRecord(c.ev[EV_UP], c.st));
-    if ((rc = enqueue_kernels(e, c, c.d_in, (long long)w * h, w, m, c.d_kps, c.d_desc, c.d_nout, e->plan.kmax)) != ORBGPU_OK) return rc;
+    if ((rc = enqueue_kernels(e, c, c.d_in, (long long)(e->plan.in_pitch * h), (int)e->plan.in_pitch, m, c.d_kps, c.d_desc, c.d_nout, e->plan.kmax)) != ORBGPU_OK) return rc;
     if ((rc = download_results(e, c, m, kps, desc, n_out, capacity, pinned_out)) != ORBGPU_OK) return rc;
     if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
     CU(cudaEventRecord(c.done, c.st));
@@ -659,7 +682,18 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
         const bool prof = e->profiling;
         if (prof) { CU(cudaEventRecord(c.ev[EV_BEGIN], c.st)); CU(cudaEventRecord(c.ev[EV_UP], c.st)); }
-        rc = enqueue_kernels(e, c, d_frames + (size_t)i0 * frame_stride, (long long)frame_stride, (int)row_stride, m,
+        const uint8_t* lvl0 = d_frames + (size_t)i0 * frame_stride;
+        long long lvl0_frame = (long long)frame_stride;
+        int lvl0_pitch = (int)row_stride;
+        if ((row_stride & 3) || (frame_stride & 3) || (reinterpret_cast<uintptr_t>(d_frames) & 3)) {
+            // rows not 4-byte aligned (e.g. 1241-px KITTI frames, dense): one device-to-device 2-D copy into the
+            // pitched buffer keeps every kernel on its aligned word path
+            const size_t dp = e->plan.in_pitch;
+            if (orb_launch_repitch(lvl0, (long long)frame_stride, (int)row_stride, c.d_in, (int)dp, w, h, m, c.st) < 0) return ORBGPU_ERR_CUDA;
+            e->launches += 1;
+            lvl0 = c.d_in; lvl0_frame = (long long)(dp * h); lvl0_pitch = (int)dp;
+        }
+        rc = enqueue_kernels(e, c, lvl0, lvl0_frame, lvl0_pitch, m,
                              d_kps + (size_t)i0 * capacity, d_desc + (size_t)i0 * capacity * 32, d_n_out + i0, capacity);
         if (rc != ORBGPU_OK) { result = rc; break; }
         if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
@@ -736,7 +770,7 @@ int orbgpu_pyramid_level(orbgpu_extractor* e, int level, uint8_t* dst, size_t ds
     if (h) *h = L.h;
     if (!dst) return ORBGPU_OK;
     if (dst_stride < (size_t)L.w) return ORBGPU_ERR_ARG;
-    if (level == 0) CU(cudaMemcpy2D(dst, dst_stride, c->d_in, (size_t)e->plan.w, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+    if (level == 0) CU(cudaMemcpy2D(dst, dst_stride, c->d_in, e->plan.in_pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
     else CU(cudaMemcpy2D(dst, dst_stride, c->d_pyr + L.pyr_off, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
     return ORBGPU_OK;
 }
