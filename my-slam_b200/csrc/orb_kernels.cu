@@ -71,17 +71,20 @@ int orb_launch_repitch(const uint8_t* src, long long src_frame_stride, int src_p
 
 // horizontal pass of one source row for this thread's 4 output pixels: H[j] = S[s_j]*a0_j + S[s_j + 1]*a1_j.
 // WORDS: the 4 pixel pairs lie inside three aligned words starting at word wb (byte offsets o_j = s_j - 4wb).
+// horizontal pass of one source row for this thread's 4 output pixels: H[j] = S[s_j]*a0_j + S[s_j + 1]*a1_j.
+// WORDS: the 4 pixel pairs lie inside three aligned words starting at word wb.  Pixel j's pair (bytes o_j, o_j + 1
+// of the 12-byte window) is cut out by one PRMT whose selector sel[j] was fixed at thread start; lowpair[j] tells
+// whether it lies in words (0,1) or (1,2).
 template <bool WORDS>
-__device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int wb, int wlast, const int s[4], const int o[4],
-                                            const unsigned a01[4], int sw, int H[4])
+__device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int wb, int wlast, const int s[4], const unsigned sel[4],
+                                            const bool lowpair[4], const unsigned a01[4], int sw, int H[4])
 {
     if (WORDS) {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(row);
         const unsigned w0 = __ldg(p + wb), w1 = __ldg(p + min(wb + 1, wlast)), w2 = __ldg(p + min(wb + 2, wlast));
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const unsigned pair = o[j] < 4 ? __funnelshift_r(w0, w1, 8 * o[j])
-                                  : o[j] < 8 ? __funnelshift_r(w1, w2, 8 * (o[j] - 4)) : w2 >> (8 * (o[j] - 8));
+            const unsigned pair = __byte_perm(lowpair[j] ? w0 : w1, lowpair[j] ? w1 : w2, sel[j]);
             H[j] = (int)__dp2a_lo(a01[j], pair, 0u);           // a0 * byte0 + a1 * byte1
         }
     } else {
@@ -91,12 +94,15 @@ __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int
     }
 }
 
+#define RS_SRC_ROWS 12        // source rows one strip of RS_ROWS output rows may touch on the shared-memory path
+
 template <bool WORDS>
 __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel& D, const uint8_t* __restrict__ src, int sp,
                                              int sw, int sh, uint8_t* __restrict__ dst, int wc, int y0, const int s[4],
-                                             const int o[4], const unsigned a01[4], int wb, int wlast)
+                                             const unsigned sel[4], const bool lowpair[4], const unsigned a01[4], int wb,
+                                             int wlast, uint2* s_h)
 {
-    // y-axis table entries of all RS_ROWS rows first (independent loads), then the rows
+    // y-axis table entries of all RS_ROWS rows first (independent loads)
     int sy[RS_ROWS];
     unsigned b01[RS_ROWS];
 #pragma unroll
@@ -105,19 +111,50 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
         sy[k] = P.rs_ofs[D.yofs_off + dy];
         b01[k] = *reinterpret_cast<const unsigned*>(P.rs_a + 2 * (D.yofs_off + dy));
     }
-    int Ha[4], Hb[4], ya = -1, yb = -1;                        // cached horizontal rows (source row indices ya, yb)
+    const int rfirst = min(max(sy[0], 0), sh - 1), rlast = min(max(sy[RS_ROWS - 1] + 1, 0), sh - 1);
+    if (rlast - rfirst < RS_SRC_ROWS) {
+        // every source row of the strip exactly once: H rows go to this thread's private shared-memory column
+        // (no reuse logic, no divergence, all row loads independent), then the vertical pass reads two of them
+        uint2* hcol = s_h + threadIdx.x;                       // H >> 4 <= 32640: two 16-bit values per word
+#pragma unroll
+        for (int i = 0; i < RS_SRC_ROWS; ++i) {
+            if (rfirst + i <= rlast) {
+                int H[4];
+                resize_hrow<WORDS>(src + (size_t)(rfirst + i) * sp, wb, wlast, s, sel, lowpair, a01, sw, H);
+                hcol[i * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < RS_ROWS; ++k) {
+            const int dy = y0 + k;
+            if (dy < D.h) {
+                const int b0 = (int)(b01[k] & 0xFFFFu), b1 = (int)(b01[k] >> 16);
+                const uint2 A = hcol[(min(max(sy[k], 0), sh - 1) - rfirst) * RS_THREADS];
+                const uint2 B = hcol[(min(max(sy[k] + 1, 0), sh - 1) - rfirst) * RS_THREADS];
+                const int v0 = (((b0 * (int)(A.x & 0xFFFFu)) >> 16) + ((b1 * (int)(B.x & 0xFFFFu)) >> 16) + 2) >> 2;
+                const int v1 = (((b0 * (int)(A.x >> 16)) >> 16) + ((b1 * (int)(B.x >> 16)) >> 16) + 2) >> 2;
+                const int v2 = (((b0 * (int)(A.y & 0xFFFFu)) >> 16) + ((b1 * (int)(B.y & 0xFFFFu)) >> 16) + 2) >> 2;
+                const int v3 = (((b0 * (int)(A.y >> 16)) >> 16) + ((b1 * (int)(B.y >> 16)) >> 16) + 2) >> 2;
+                *reinterpret_cast<uint32_t*>(dst + (size_t)dy * D.pitch + 4 * wc) =
+                    __byte_perm(__byte_perm(v0, v1, 0x0040), __byte_perm(v2, v3, 0x0040), 0x5410);
+            }
+        }
+        return;
+    }
+    // steep scale factors (more than RS_SRC_ROWS source rows per strip): row by row with a two-row cache
+    int Ha[4], Hb[4], ya = -1, yb = -1;
 #pragma unroll
     for (int k = 0; k < RS_ROWS; ++k) {
         const int dy = y0 + k;
         if (dy >= D.h) break;
         const int b0 = (int)(b01[k] & 0xFFFFu), b1 = (int)(b01[k] >> 16);
         const int r0 = min(max(sy[k], 0), sh - 1), r1 = min(max(sy[k] + 1, 0), sh - 1);
-        if (r0 == yb) {                                        // the usual step: last row's lower line is this row's upper line
+        if (r0 == yb) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) Ha[j] = Hb[j];
             ya = yb;
         } else if (r0 != ya) {
-            resize_hrow<WORDS>(src + (size_t)r0 * sp, wb, wlast, s, o, a01, sw, Ha);
+            resize_hrow<WORDS>(src + (size_t)r0 * sp, wb, wlast, s, sel, lowpair, a01, sw, Ha);
             ya = r0;
         }
         if (r1 == ya) {
@@ -125,7 +162,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
             for (int j = 0; j < 4; ++j) Hb[j] = Ha[j];
             yb = ya;
         } else if (r1 != yb) {
-            resize_hrow<WORDS>(src + (size_t)r1 * sp, wb, wlast, s, o, a01, sw, Hb);
+            resize_hrow<WORDS>(src + (size_t)r1 * sp, wb, wlast, s, sel, lowpair, a01, sw, Hb);
             yb = r1;
         }
         uint32_t packed = 0;
@@ -143,6 +180,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
 // four IDP.2A dot products, and is reused when consecutive output rows share it.
 __global__ void __launch_bounds__(RS_THREADS) k_resize_level(OrbPlanDev P, int l)
 {
+    __shared__ uint2 s_h[RS_SRC_ROWS * RS_THREADS];            // [source row][thread]: H >> 4 of the thread's 4 pixels, 16 bits each
     const OrbLevel& D = P.lv[l];
     const int frame = blockIdx.y;
     const int nwc = (D.w + 3) >> 2;
@@ -155,7 +193,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize_level(OrbPlanDev P, int l
     const int sp = orb_level_pitch(P, l - 1);
     uint8_t* __restrict__ dst = P.pyr + (long long)frame * P.pyr_frame_bytes + D.pyr_off;
 
-    int s[4], o[4];
+    int s[4];
     unsigned a01[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -165,15 +203,22 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize_level(OrbPlanDev P, int l
     }
     const int smin = min(min(s[0], s[1]), min(s[2], s[3])), smax = max(max(s[0], s[1]), max(s[2], s[3]));
     const int wb = smin >> 2;
+    unsigned sel[4];
+    bool lowpair[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) o[j] = s[j] - 4 * wb;
+    for (int j = 0; j < 4; ++j) {
+        const int o = s[j] - 4 * wb;                           // byte offset of the pair inside the 12-byte window
+        lowpair[j] = o <= 6;
+        const int q = lowpair[j] ? o : o - 4;
+        sel[j] = (unsigned)q | ((unsigned)(q + 1) << 4);
+    }
     // word path: rows 4-byte aligned and every (s_j, s_j + 1) pair inside words wb .. wb + 2 (clamped to the
     // last word that lies inside the pitch; a pair byte beyond the row only ever meets weight a1 = 0)
     const int wlast = (sp >> 2) - 1;
     const bool words = ((sp & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 3) == 0) && (smax + 1 - 4 * wb <= 11) &&
                        (wb + 2 <= wlast || 4 * wlast + 3 >= min(smax + 1, sw - 1));
-    if (words) resize_strip<true>(P, D, src, sp, sw, sh, dst, wc, y0, s, o, a01, wb, wlast);
-    else resize_strip<false>(P, D, src, sp, sw, sh, dst, wc, y0, s, o, a01, wb, wlast);
+    if (words) resize_strip<true>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
+    else resize_strip<false>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
 }
 
 int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
@@ -467,7 +512,9 @@ int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream
 // Selection (:743-762): per node the key with the highest response, first in input order on ties.
 // Keys and node tables live in shared memory when they fit, else in a global scratch area.
 // =================================================================================================
+#ifndef OCT_THREADS
 #define OCT_THREADS 256
+#endif
 #define OCT_NODE_BYTES 64     // per-node bytes in the node pool (see carve below)
 
 struct OctPools {
