@@ -78,6 +78,18 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
                          size_t row_stride, size_t frame_stride,
                          orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
 
+/* Asynchronous form of orbgpu_extract_batch for a continuous stream of batches: enqueues the batch on the
+ * internal streams and returns (it only blocks while all stream contexts are still busy with earlier chunks:
+ * back-pressure), so the upload of batch k+1 overlaps the kernels of batch k and the pipeline never drains.
+ * Every buffer must stay valid and untouched until orbgpu_wait returns.  orbgpu_wait blocks until everything
+ * enqueued since the previous wait has completed, delivers staged (pageable) outputs and returns the first
+ * error; orbgpu_last_batch_ms then covers the whole window.  The synchronous calls, the frame queue and
+ * shape changes return ORBGPU_ERR_STATE while a window is open. */
+int orbgpu_extract_batch_async(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h,
+                               size_t row_stride, size_t frame_stride,
+                               orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
+int orbgpu_wait(orbgpu_extractor* e);
+
 /* Same, with every buffer already resident in device memory (frames, kps, desc, n_out are device
  * pointers of this extractor's device).  Returns after the work has completed. */
 int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, int n, int w, int h,

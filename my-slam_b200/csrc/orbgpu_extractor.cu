@@ -101,6 +101,8 @@ struct orbgpu_extractor {
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
+    bool async_open = false;           // orbgpu_extract_batch_async batches outstanding (closed by orbgpu_wait)
+    int next_ctx = 0;                  // next chunk stream of the host-batch round-robin
     cudaEvent_t ev_batch0 = nullptr, ev_batch1 = nullptr;   // bracket the most recent batch call on ctx[0].st
     double last_batch_ms = 0;
     int last_ctx = -1;                 // context holding the most recent single frame (pyramid / debug views)
@@ -624,22 +626,19 @@ int orbgpu_max_keypoints(orbgpu_extractor* e, int w, int h)
     return e->plan.kmax;
 }
 
-int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
-                         size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+// enqueue one host-buffer batch on the chunk streams; with `rotate` the chunk -> stream assignment continues
+// where the previous batch stopped, so back-to-back asynchronous batches keep every stream fed
+static int enqueue_host_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
+                              size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
 {
-    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
     int rc;
-    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
-    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
-    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
-    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
     const bool pin_in = is_pinned(frames);
     const bool pin_out = is_pinned(kps) && is_pinned(desc) && is_pinned(n_out);
     const int chunk = std::max(1, std::min(std::min(e->plan.chunk_cap, e->max_chunk[0]), (n + e->nstream[0] - 1) / e->nstream[0]));
-    int result = ORBGPU_OK, k = 0;
-    if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
-    for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
-        StreamCtx& c = e->ctx[k % e->nstream[0]];
+    int result = ORBGPU_OK;
+    for (int i0 = 0; i0 < n; i0 += chunk) {
+        StreamCtx& c = e->ctx[e->next_ctx % e->nstream[0]];
+        e->next_ctx = (e->next_ctx + 1) % e->nstream[0];
         const int m = std::min(chunk, n - i0);
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
@@ -647,12 +646,63 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
                           kps + (size_t)i0 * capacity, desc + (size_t)i0 * capacity * 32, n_out + i0, capacity, pin_out);
         if (rc != ORBGPU_OK) { result = rc; break; }
     }
+    return result;
+}
+
+static int finish_all(orbgpu_extractor* e, int result)
+{
+    int rc;
     if (result == ORBGPU_OK) result = batch_end(e);
     for (int s = 0; s < NSTREAM; ++s)
         if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) result = rc;
     batch_collect_ms(e);
+    e->async_open = false;
+    return result;
+}
+
+int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
+                         size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if (e->async_open) return ORBGPU_ERR_STATE;                // orbgpu_wait first
+    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
+    e->next_ctx = 0;
+    const int result = finish_all(e, enqueue_host_batch(e, frames, n, w, h, row_stride, frame_stride, kps, desc, capacity, n_out));
     e->last_ctx = (n == 1 && result == ORBGPU_OK) ? 0 : -1;
     return result;
+}
+
+int orbgpu_extract_batch_async(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
+                               size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if (e->async_open && (w != e->plan.w || h != e->plan.h)) return ORBGPU_ERR_STATE;   // one shape per open window
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    if (!e->async_open) {
+        if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
+        e->async_open = true;
+        e->next_ctx = 0;
+    }
+    e->last_ctx = -1;
+    return enqueue_host_batch(e, frames, n, w, h, row_stride, frame_stride, kps, desc, capacity, n_out);
+}
+
+int orbgpu_wait(orbgpu_extractor* e)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if (!e->async_open) return ORBGPU_OK;
+    return finish_all(e, ORBGPU_OK);
 }
 
 int orbgpu_extract(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride,
@@ -669,6 +719,7 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
     if (!e || !d_frames || !d_kps || !d_desc || !d_n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if (e->async_open) return ORBGPU_ERR_STATE;
     for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
     if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
     if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
@@ -716,6 +767,7 @@ int orbgpu_submit(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t 
     if (!e || !img || !ticket || w < 1 || h < 1 || stride < (size_t)w) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if (e->async_open) return ORBGPU_ERR_STATE;
     if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
     const uint64_t t = e->next_ticket;
     StreamCtx& c = e->ctx[t % NSTREAM];

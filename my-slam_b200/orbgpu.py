@@ -42,6 +42,8 @@ def lib():
         "orbgpu_extract": (i32, [vp, vp, i32, i32, sz, vp, vp, i32, pi]),
         "orbgpu_extract_batch": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
+        "orbgpu_extract_batch_async": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
+        "orbgpu_wait": (i32, [vp]),
         "orbgpu_submit": (i32, [vp, vp, i32, i32, sz, C.POINTER(u64)]),
         "orbgpu_collect": (i32, [vp, u64, vp, vp, i32, pi]),
         "orbgpu_queue_depth": (i32, [vp]),
@@ -166,6 +168,12 @@ class ORBextractor:
     def extract_batch_ptr(self, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr, device=False):
         f = self._L.orbgpu_extract_batch_device if device else self._L.orbgpu_extract_batch
         _check(f(self._h, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr))
+
+    def extract_batch_async_ptr(self, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr):
+        _check(self._L.orbgpu_extract_batch_async(self._h, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr))
+
+    def wait(self):
+        _check(self._L.orbgpu_wait(self._h))
 
     def submit(self, image):
         image = np.ascontiguousarray(image, np.uint8)

@@ -261,3 +261,32 @@ def test_launches_are_counted(pkg):
     before = ex.launch_count()
     ex(pkg.synth.synth(640, 480, 2))
     assert ex.launch_count() - before == 7 + 4       # 7 resize levels + FAST + octree + blur + describe
+
+
+def test_async_batches_equal_synchronous_results(pkg):
+    """orbgpu_extract_batch_async + orbgpu_wait: several batches in flight, pinned and pageable buffers."""
+    import ctypes as C
+    synth = pkg.synth
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    w, h = 640, 480
+    cap = ex.max_keypoints(w, h)
+    batches = [np.stack([synth.synth(w, h, 9000 + 10 * b + i) for i in range(5 + b)]) for b in range(3)]
+    want = [ex.extract_batch(f) for f in batches]
+    outs = []
+    for f in batches:
+        n = len(f)
+        outs.append((np.zeros((n, cap), pkg.KP_DTYPE), np.zeros((n, cap, 32), np.uint8), np.full(n, -7, np.int32)))
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for f, (k, d, c) in zip(batches, outs):
+        ex.extract_batch_async_ptr(p(f), len(f), w, h, w, w * h, p(k), p(d), cap, p(c))
+    with pytest.raises(pkg.OrbGpuError):
+        ex.extract_batch(batches[0])                            # synchronous calls are refused while a window is open
+    ex.wait()
+    ex.wait()                                                   # idempotent
+    for (k, d, c), (wk, wd, wc) in zip(outs, want):
+        assert np.array_equal(c, wc)
+        for i in range(len(c)):
+            assert k[i, :c[i]].tobytes() == wk[i, :wc[i]].tobytes() and np.array_equal(d[i, :c[i]], wd[i, :wc[i]])
+    assert ex.last_batch_ms() > 0
+    kps, desc = ex(batches[0][0])                               # the handle is usable synchronously again
+    assert len(kps) == want[0][2][0]
