@@ -96,6 +96,13 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
                                 size_t row_stride, size_t frame_stride,
                                 orbgpu_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out);
 
+/* Input pixel format of the frames handed to every extraction entry point of this handle: 1 (gray, default),
+ * 3 or 4 interleaved 8-bit channels; rgb_order != 0 means R,G,B[,A], else B,G,R[,A].  Colour frames are converted
+ * on the device exactly as Tracking::GrabImageMonocular does on the host before it constructs the Frame
+ * (cv::cvtColor CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY, src/Tracking.cc:244-257; OpenCV 4.13 fixed point);
+ * strides are in bytes.  orbgpu_pyramid_level(0) then returns the gray image (mImGray). */
+int orbgpu_set_input_format(orbgpu_extractor* e, int channels, int rgb_order);
+
 /* The pinned-memory frame queue for Frame construction (north_star): submit copies the image into
  * a pinned ring slot and enqueues upload + kernels + download without blocking; collect blocks on
  * that frame only.  Frame::Frame (src/Frame.cc:174-228) or Tracking::GrabImage* one frame ahead

@@ -109,6 +109,8 @@ int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N,
                              int key_smem_cap, int node_smem_cap, cudaStream_t st);
 int orb_launch_repitch(const uint8_t* src, long long src_frame_stride, int src_pitch, uint8_t* dst, int dst_pitch, int w, int h,
                        int nframes, cudaStream_t st);
+int orb_launch_cvt_gray(const uint8_t* src, long long src_frame_stride, int src_pitch, int channels, int rgb_order, uint8_t* dst,
+                        int dst_pitch, int w, int h, int nframes, cudaStream_t st);
 int orb_upload_constants(const int* umax16);
 int orb_fast_smem_bytes(int max_cw, int max_ch);
 int orb_debug_atan2(const float* d_y, const float* d_x, int n, float* d_out, cudaStream_t st);

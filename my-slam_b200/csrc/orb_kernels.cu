@@ -48,6 +48,36 @@ __global__ void __launch_bounds__(256) k_repitch(const uint8_t* __restrict__ src
     *reinterpret_cast<uint32_t*>(dst + ((long long)blockIdx.y * h + y) * dst_pitch + x4) = v;
 }
 
+// cv::cvtColor(..., CV_BGR2GRAY / RGB2GRAY / BGRA2GRAY / RGBA2GRAY) on 8-bit pixels as Tracking::GrabImage* applies it
+// before the extractor (src/Tracking.cc:244-257), in OpenCV 4.13's fixed point (pinned against cv2, tests/golden):
+// gray = (c0*k0 + c1*19235 + c2*k2 + 2^14) >> 15 with (k0, k2) = (3735, 9798) for B,G,R order and swapped for R,G,B.
+__global__ void __launch_bounds__(256) k_cvt_gray(const uint8_t* __restrict__ src, long long src_frame_stride, int src_pitch, int bpp,
+                                                  int k0, int k2, uint8_t* __restrict__ dst, int dst_pitch, int w, int h)
+{
+    const int wpr = dst_pitch >> 2;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int y = t / wpr, x4 = (t - y * wpr) * 4;
+    if (y >= h) return;
+    const uint8_t* __restrict__ r = src + (long long)blockIdx.y * src_frame_stride + (long long)y * src_pitch;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint8_t* px = r + (long long)min(x4 + k, w - 1) * bpp;
+        const int g = ((int)__ldg(px) * k0 + (int)__ldg(px + 1) * 19235 + (int)__ldg(px + 2) * k2 + (1 << 14)) >> 15;
+        v |= (uint32_t)g << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(dst + ((long long)blockIdx.y * h + y) * dst_pitch + x4) = v;
+}
+
+int orb_launch_cvt_gray(const uint8_t* src, long long src_frame_stride, int src_pitch, int channels, int rgb_order, uint8_t* dst,
+                        int dst_pitch, int w, int h, int nframes, cudaStream_t st)
+{
+    const int ntask = (dst_pitch >> 2) * h;
+    k_cvt_gray<<<dim3((ntask + 255) / 256, nframes), 256, 0, st>>>(src, src_frame_stride, src_pitch, channels, rgb_order ? 9798 : 3735,
+                                                                    rgb_order ? 3735 : 9798, dst, dst_pitch, w, h);
+    return 1;
+}
+
 int orb_launch_repitch(const uint8_t* src, long long src_frame_stride, int src_pitch, uint8_t* dst, int dst_pitch, int w, int h,
                        int nframes, cudaStream_t st)
 {

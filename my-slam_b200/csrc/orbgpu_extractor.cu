@@ -101,6 +101,7 @@ struct orbgpu_extractor {
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
+    int in_channels = 1, in_rgb = 0;   // input pixel format of host/device frames (orbgpu_set_input_format)
     bool async_open = false;           // orbgpu_extract_batch_async batches outstanding (closed by orbgpu_wait)
     int next_ctx = 0;                  // next chunk stream of the host-batch round-robin
     cudaEvent_t ev_batch0 = nullptr, ev_batch1 = nullptr;   // bracket the most recent batch call on ctx[0].st
@@ -342,7 +343,7 @@ static int ctx_reserve(orbgpu_extractor* e, StreamCtx& c, int frames, int plan_w
     CU(cudaMalloc(&c.d_nout, n * 4));
     CU(cudaMalloc(&c.d_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint)));
     CU(cudaMalloc(&c.d_desc, n * (size_t)std::max(pl.kmax, 1) * 32));
-    CU(cudaHostAlloc(&c.h_in, n * (size_t)pl.w * pl.h + 64, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&c.h_in, n * (size_t)pl.w * pl.h * e->in_channels + 64, cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_kps, n * (size_t)std::max(pl.kmax, 1) * sizeof(orbgpu_keypoint), cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_desc, n * (size_t)std::max(pl.kmax, 1) * 32, cudaHostAllocDefault));
     CU(cudaHostAlloc(&c.h_nout, n * 4, cudaHostAllocDefault));
@@ -435,32 +436,35 @@ static int reserve_raw(StreamCtx& c, size_t bytes)
 }
 
 // upload `m` frames starting at host pointer `src` into c.d_in (row pitch plan.in_pitch, frames in_pitch * h apart).
-// PCIe copies are always plain 1-D copies of dense frames; when the pitched layout differs from the dense one
-// (w not a multiple of 16) the frames land in d_raw and k_repitch lays them out.
+// PCIe copies are always plain 1-D copies of dense frames; when the device layout differs from the dense one
+// (w not a multiple of 16, or 3/4-channel input) the frames land in d_raw and k_repitch / k_cvt_gray lays them out.
 static int upload_frames(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, int m, int w, int h,
                          size_t row_stride, size_t frame_stride, bool pinned)
 {
-    const size_t fb = (size_t)w * h, dp = e->plan.in_pitch;
-    const bool repitch = dp != (size_t)w;
+    const int bpp = e->in_channels;
+    const size_t rb = (size_t)w * bpp, fb = rb * h, dp = e->plan.in_pitch;
+    const bool relayout = dp != (size_t)w || bpp != 1;
     int rc;
-    if (repitch && (rc = reserve_raw(c, fb * m)) != ORBGPU_OK) return rc;
-    uint8_t* dense = repitch ? c.d_raw : c.d_in;
-    if (pinned && row_stride == (size_t)w && frame_stride == fb) {
+    if (relayout && (rc = reserve_raw(c, fb * m)) != ORBGPU_OK) return rc;
+    uint8_t* dense = relayout ? c.d_raw : c.d_in;
+    if (pinned && row_stride == rb && frame_stride == fb) {
         CU(cudaMemcpyAsync(dense, src, fb * m, cudaMemcpyHostToDevice, c.st));
-    } else if (pinned && row_stride == (size_t)w) {
+    } else if (pinned && row_stride == rb) {
         for (int i = 0; i < m; ++i)
             CU(cudaMemcpyAsync(dense + (size_t)i * fb, src + (size_t)i * frame_stride, fb, cudaMemcpyHostToDevice, c.st));
     } else {                                               // strided rows or pageable memory: gather into the pinned staging buffer
         for (int i = 0; i < m; ++i) {
             const uint8_t* f = src + (size_t)i * frame_stride;
             uint8_t* d = c.h_in + (size_t)i * fb;
-            if (row_stride == (size_t)w) memcpy(d, f, fb);
-            else for (int y = 0; y < h; ++y) memcpy(d + (size_t)y * w, f + (size_t)y * row_stride, (size_t)w);
+            if (row_stride == rb) memcpy(d, f, fb);
+            else for (int y = 0; y < h; ++y) memcpy(d + (size_t)y * rb, f + (size_t)y * row_stride, rb);
         }
         CU(cudaMemcpyAsync(dense, c.h_in, fb * m, cudaMemcpyHostToDevice, c.st));
     }
-    if (repitch) {
-        if (orb_launch_repitch(c.d_raw, (long long)fb, w, c.d_in, (int)dp, w, h, m, c.st) < 0) return ORBGPU_ERR_CUDA;
+    if (relayout) {
+        const int n = bpp == 1 ? orb_launch_repitch(c.d_raw, (long long)fb, w, c.d_in, (int)dp, w, h, m, c.st)
+                               : orb_launch_cvt_gray(c.d_raw, (long long)fb, (int)rb, bpp, e->in_rgb, c.d_in, (int)dp, w, h, m, c.st);
+        if (n < 0) return ORBGPU_ERR_CUDA;
         e->launches += 1;
     }
     return ORBGPU_OK;
@@ -663,7 +667,7 @@ static int finish_all(orbgpu_extractor* e, int result)
 int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
                          size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
 {
-    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w * e->in_channels) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
     if (e->async_open) return ORBGPU_ERR_STATE;                // orbgpu_wait first
@@ -680,7 +684,7 @@ int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int 
 int orbgpu_extract_batch_async(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h, size_t row_stride,
                                size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
 {
-    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    if (!e || !frames || !kps || !desc || !n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w * e->in_channels) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
     for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
@@ -716,7 +720,7 @@ int orbgpu_extract(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t
 int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, int n, int w, int h, size_t row_stride,
                                 size_t frame_stride, orbgpu_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out)
 {
-    if (!e || !d_frames || !d_kps || !d_desc || !d_n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w) return ORBGPU_ERR_ARG;
+    if (!e || !d_frames || !d_kps || !d_desc || !d_n_out || n < 1 || w < 1 || h < 1 || row_stride < (size_t)w * e->in_channels) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
     if (e->async_open) return ORBGPU_ERR_STATE;
@@ -736,11 +740,15 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
         const uint8_t* lvl0 = d_frames + (size_t)i0 * frame_stride;
         long long lvl0_frame = (long long)frame_stride;
         int lvl0_pitch = (int)row_stride;
-        if ((row_stride & 3) || (frame_stride & 3) || (reinterpret_cast<uintptr_t>(d_frames) & 3)) {
-            // rows not 4-byte aligned (e.g. 1241-px KITTI frames, dense): one device-to-device 2-D copy into the
-            // pitched buffer keeps every kernel on its aligned word path
+        if (e->in_channels != 1 || (row_stride & 3) || (frame_stride & 3) || (reinterpret_cast<uintptr_t>(d_frames) & 3)) {
+            // colour input, or rows not 4-byte aligned (e.g. 1241-px KITTI frames, dense): one pass into the pitched
+            // gray buffer keeps every kernel on its aligned word path
             const size_t dp = e->plan.in_pitch;
-            if (orb_launch_repitch(lvl0, (long long)frame_stride, (int)row_stride, c.d_in, (int)dp, w, h, m, c.st) < 0) return ORBGPU_ERR_CUDA;
+            const int nl = e->in_channels == 1
+                               ? orb_launch_repitch(lvl0, (long long)frame_stride, (int)row_stride, c.d_in, (int)dp, w, h, m, c.st)
+                               : orb_launch_cvt_gray(lvl0, (long long)frame_stride, (int)row_stride, e->in_channels, e->in_rgb, c.d_in,
+                                                     (int)dp, w, h, m, c.st);
+            if (nl < 0) return ORBGPU_ERR_CUDA;
             e->launches += 1;
             lvl0 = c.d_in; lvl0_frame = (long long)(dp * h); lvl0_pitch = (int)dp;
         }
@@ -764,7 +772,7 @@ int orbgpu_queue_depth(orbgpu_extractor* e) { return e ? NSTREAM : ORBGPU_ERR_AR
 
 int orbgpu_submit(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride, uint64_t* ticket)
 {
-    if (!e || !img || !ticket || w < 1 || h < 1 || stride < (size_t)w) return ORBGPU_ERR_ARG;
+    if (!e || !img || !ticket || w < 1 || h < 1 || stride < (size_t)w * e->in_channels) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
     if (e->async_open) return ORBGPU_ERR_STATE;
@@ -1004,6 +1012,20 @@ int orbgpu_get_stage_ms(orbgpu_extractor* e, double* ms, int n, int reset)
 }
 
 uint64_t orbgpu_launch_count(orbgpu_extractor* e) { return e ? e->launches : 0; }
+
+int orbgpu_set_input_format(orbgpu_extractor* e, int channels, int rgb_order)
+{
+    if (!e || (channels != 1 && channels != 3 && channels != 4)) return ORBGPU_ERR_ARG;
+    if (e->async_open) return ORBGPU_ERR_STATE;
+    for (int s = 0; s < NSTREAM; ++s)
+        if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if (cudaSetDevice(e->device) != cudaSuccess) return ORBGPU_ERR_CUDA;
+    if (channels != e->in_channels)
+        for (int s = 0; s < NSTREAM; ++s) ctx_free_buffers(e->ctx[s]);     // the pinned staging buffers are sized per format
+    e->in_channels = channels; e->in_rgb = rgb_order != 0;
+    e->last_ctx = -1;
+    return ORBGPU_OK;
+}
 
 int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames)
 {

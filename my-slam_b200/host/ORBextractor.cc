@@ -21,7 +21,7 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST, int cudaDevice)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
-      mpHandle(0), mbDownloadPyramid(false), mLastError("ok"), mLastW(0), mLastH(0)
+      mpHandle(0), mbDownloadPyramid(false), mLastError("ok"), mLastW(0), mLastH(0), mChannels(1)
 {
     const int rc = orbgpu_create(&mpHandle, cudaDevice, _nfeatures, _scaleFactor, _nlevels, _iniThFAST, _minThFAST);
     if (rc != ORBGPU_OK)      // the reference has no failure path here; there is no CPU path to fall back to
@@ -58,7 +58,7 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
 {
     if (_image.empty()) return;                            // :1048-1049: outputs untouched
     cv::Mat image = _image.getMat();
-    assert(image.type() == CV_8UC1);                       // :1052
+    assert(image.type() == (mChannels == 1 ? CV_8UC1 : mChannels == 3 ? CV_8UC3 : CV_8UC4));   // :1052 (CV_8UC1 in the reference)
     const int w = image.cols, h = image.rows;
     const int cap = orbgpu_max_keypoints(mpHandle, w, h);
     if (cap < 0) { mLastError = orbgpu_strerror(cap); throw std::runtime_error(std::string("ORBextractor: ") + mLastError); }
@@ -73,11 +73,28 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     if (mbDownloadPyramid) FillPyramid();
 }
 
+bool ORBextractor::SetColorInput(int channels, bool rgbOrder)
+{
+    const int rc = orbgpu_set_input_format(mpHandle, channels, rgbOrder ? 1 : 0);
+    if (rc != ORBGPU_OK) { mLastError = orbgpu_strerror(rc); return false; }
+    mChannels = channels;
+    return true;
+}
+
+cv::Mat ORBextractor::GrayImage()
+{
+    int w = 0, h = 0;
+    if (orbgpu_pyramid_level(mpHandle, 0, 0, 0, &w, &h) != ORBGPU_OK) return cv::Mat();
+    cv::Mat g(h, w, CV_8UC1);
+    orbgpu_pyramid_level(mpHandle, 0, g.ptr(0), (size_t)g.step, &w, &h);
+    return g;
+}
+
 uint64_t ORBextractor::Submit(cv::InputArray _image)
 {
     if (_image.empty()) return 0;
     cv::Mat image = _image.getMat();
-    assert(image.type() == CV_8UC1);
+    assert(image.channels() == mChannels);
     uint64_t ticket = 0;
     const int rc = orbgpu_submit(mpHandle, image.ptr(0), image.cols, image.rows, (size_t)image.step, &ticket);
     if (rc != ORBGPU_OK) { mLastError = orbgpu_strerror(rc); return 0; }

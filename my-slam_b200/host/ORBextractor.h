@@ -44,6 +44,11 @@ public:
 
     // ---- additions ----
     void SetPyramidDownload(bool on) { mbDownloadPyramid = on; }
+    // Accept the camera image as it arrives (3 or 4 interleaved 8-bit channels, R,G,B or B,G,R order) and do the
+    // cv::cvtColor(..., CV_*2GRAY) of Tracking::GrabImage* (src/Tracking.cc:244-257) on the device; channels = 1 restores
+    // the reference contract (CV_8UC1).  GrayImage() returns what mImGray would hold after the host conversion.
+    bool SetColorInput(int channels, bool rgbOrder);
+    cv::Mat GrayImage();
     // asynchronous pair: returns a ticket (0 = failed / queue full); Collect blocks on that frame only
     uint64_t Submit(cv::InputArray image);
     bool Collect(uint64_t ticket, std::vector<cv::KeyPoint>& keypoints, cv::OutputArray descriptors);
@@ -76,6 +81,7 @@ protected:
     const char* mLastError;
     std::vector<unsigned char> mKpScratch, mDescScratch;   // staging for the C ABI (caller-owned buffers)
     int mLastW, mLastH;
+    int mChannels;
 
 private:
     ORBextractor(const ORBextractor&);

@@ -20,6 +20,8 @@
 #ifndef CV_8U
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_8UC3 16
+#define CV_8UC4 24
 #endif
 
 namespace cv {
@@ -46,18 +48,20 @@ public:
     Mat() : rows(0), cols(0), data(0), step(0), type_(CV_8UC1) {}
     Mat(int r, int c, int type) : rows(0), cols(0), data(0), step(0), type_(type) { create(r, c, type); }
     Mat(int r, int c, int type, void* ext, size_t ext_step = 0)   // wraps caller memory, no ownership
-        : rows(r), cols(c), data((unsigned char*)ext), step(ext_step ? ext_step : (size_t)c), type_(type) {}
+        : rows(r), cols(c), data((unsigned char*)ext), step(ext_step ? ext_step : (size_t)c * ((type >> 3) + 1)), type_(type) {}
     void create(int r, int c, int type)
     {
-        if (r == rows && c == cols && type == type_ && buf_ && step == (size_t)c) return;
-        rows = r; cols = c; type_ = type; step = (size_t)c;
-        buf_.reset(new std::vector<unsigned char>((size_t)r * c + 1));
+        const size_t rb = (size_t)c * ((type >> 3) + 1);
+        if (r == rows && c == cols && type == type_ && buf_ && step == rb) return;
+        rows = r; cols = c; type_ = type; step = rb;
+        buf_.reset(new std::vector<unsigned char>((size_t)r * rb + 1));
         data = buf_->data();
     }
     void release() { buf_.reset(); data = 0; rows = cols = 0; step = 0; }
     bool empty() const { return data == 0 || rows == 0 || cols == 0; }
     int type() const { return type_; }
-    bool isContinuous() const { return step == (size_t)cols; }
+    int channels() const { return (type_ >> 3) + 1; }
+    bool isContinuous() const { return step == (size_t)cols * channels(); }
     unsigned char* ptr(int r = 0) { return data + (size_t)r * step; }
     const unsigned char* ptr(int r = 0) const { return data + (size_t)r * step; }
     template <typename T> T* ptr(int r = 0) { return (T*)(data + (size_t)r * step); }
@@ -67,13 +71,13 @@ public:
     Mat operator()(const Rect& q) const
     {
         Mat m(*this);
-        m.data = data + (size_t)q.y * step + q.x; m.rows = q.height; m.cols = q.width;
+        m.data = data + (size_t)q.y * step + (size_t)q.x * channels(); m.rows = q.height; m.cols = q.width;
         return m;
     }
     Mat clone() const
     {
         Mat m(rows, cols, type_);
-        for (int r = 0; r < rows; ++r) std::memcpy(m.ptr(r), ptr(r), (size_t)cols);
+        for (int r = 0; r < rows; ++r) std::memcpy(m.ptr(r), ptr(r), (size_t)cols * channels());
         return m;
     }
 private:

@@ -44,6 +44,7 @@ def lib():
         "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_extract_batch_async": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_wait": (i32, [vp]),
+        "orbgpu_set_input_format": (i32, [vp, i32, i32]),
         "orbgpu_submit": (i32, [vp, vp, i32, i32, sz, C.POINTER(u64)]),
         "orbgpu_collect": (i32, [vp, u64, vp, vp, i32, pi]),
         "orbgpu_queue_depth": (i32, [vp]),
@@ -143,11 +144,12 @@ class ORBextractor:
         (the reference returns without touching its outputs, src/ORBextractor.cc:1048-1049)."""
         if image is None or image.size == 0:
             return None, None
-        if image.dtype != np.uint8 or image.ndim != 2:
-            raise ValueError("image must be CV_8UC1 (2-D uint8)")    # reference: assert, src/ORBextractor.cc:1052
-        if image.strides[1] != 1:
+        ch = getattr(self, "_channels", 1)
+        if image.dtype != np.uint8 or image.ndim != (2 if ch == 1 else 3) or (ch != 1 and image.shape[2] != ch):
+            raise ValueError("image must be CV_8UC%d" % ch)          # reference: assert, src/ORBextractor.cc:1052
+        if image.strides[-1] != 1 or (ch != 1 and image.strides[1] != ch):
             image = np.ascontiguousarray(image)
-        h, w = image.shape
+        h, w = image.shape[:2]
         cap = self.max_keypoints(w, h)
         kps = np.zeros(cap, KP_DTYPE)
         desc = np.zeros((cap, 32), np.uint8)
@@ -171,6 +173,10 @@ class ORBextractor:
 
     def extract_batch_async_ptr(self, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr):
         _check(self._L.orbgpu_extract_batch_async(self._h, frames_ptr, n, w, h, row_stride, frame_stride, kps_ptr, desc_ptr, cap, nout_ptr))
+
+    def set_input_format(self, channels, rgb_order=False):
+        _check(self._L.orbgpu_set_input_format(self._h, int(channels), int(bool(rgb_order))))
+        self._channels = int(channels)
 
     def wait(self):
         _check(self._L.orbgpu_wait(self._h))

@@ -9,7 +9,7 @@ Sources of truth (nothing here comes from our own code):
   * the UNMODIFIED reference extractor (oracle/_ref/liborbref.so = /root/reference/src/ORBextractor.cc
     compiled against oracle/cvshim, ascending-arena tie-break pin) for whole-frame results and for
     DistributeOctTree on random candidate sets.
-Outputs: prims_golden.npz, extract_golden.json, octree_golden.npz.
+Outputs: prims_golden.npz, extract_golden.json, octree_golden.npz, gray_golden.npz (`make_golden.py gray` alone).
 """
 import ctypes
 import hashlib
@@ -166,7 +166,30 @@ def make_octree():
     print("octree_golden.npz:", k, "cases")
 
 
+def make_gray():
+    """cv2.cvtColor to gray, the conversion Tracking::GrabImage* applies before the extractor (src/Tracking.cc:244-257)."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(77)
+    c3 = rng.integers(0, 256, (45, 67, 3), dtype=np.uint8)
+    c4 = rng.integers(0, 256, (33, 52, 4), dtype=np.uint8)
+    # every value of each channel against extreme values of the others (rounding corners of the fixed point)
+    ramp = np.zeros((6, 256, 3), np.uint8)
+    for ch in range(3):
+        ramp[2 * ch, :, ch] = np.arange(256); ramp[2 * ch + 1, :, ch] = np.arange(256)
+        ramp[2 * ch + 1, :, (ch + 1) % 3] = 255; ramp[2 * ch + 1, :, (ch + 2) % 3] = 131
+    out = {"c3": c3, "c4": c4, "ramp": ramp,
+           "c3_bgr": cv2.cvtColor(c3, cv2.COLOR_BGR2GRAY), "c3_rgb": cv2.cvtColor(c3, cv2.COLOR_RGB2GRAY),
+           "c4_bgra": cv2.cvtColor(c4, cv2.COLOR_BGRA2GRAY), "c4_rgba": cv2.cvtColor(c4, cv2.COLOR_RGBA2GRAY),
+           "ramp_bgr": cv2.cvtColor(ramp, cv2.COLOR_BGR2GRAY), "ramp_rgb": cv2.cvtColor(ramp, cv2.COLOR_RGB2GRAY)}
+    np.savez_compressed(os.path.join(HERE, "gray_golden.npz"), **out)
+    print("gray_golden.npz written")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "gray":
+        make_gray()
+        sys.exit(0)
     make_prims()
     make_extract()
     make_octree()
