@@ -119,6 +119,14 @@ int orbgpu_queue_depth(orbgpu_extractor* e);
  * rebuilt on the host by the C++ wrapper. */
 int orbgpu_pyramid_level(orbgpu_extractor* e, int level, uint8_t* dst, size_t dst_stride, int* w, int* h);
 
+/* Frame::ComputeStereoMatches (src/Frame.cc:466-640) between the most recent frame of `left` and of `right`
+ * (two extractor handles on one device, each after its own orbgpu_extract / orbgpu_collect, as the stereo Frame
+ * constructor runs them, src/Frame.cc:78-81).  Pyramids, keypoints and descriptors are used where they lie in HBM:
+ * nothing is uploaded and mvImagePyramid need not be downloaded.  bf = mbf, b = mb.  Outputs for the n_left left
+ * keypoints: u_right = mvuRight, depth = mvDepth (-1 where unmatched), after the median-SAD outlier rejection. */
+int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float bf, float b,
+                        float* u_right, float* depth, int capacity, int* n_left);
+
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),
  * FAST candidates in list order (:791-831) and octree survivors in list order (:541-765); x, y are

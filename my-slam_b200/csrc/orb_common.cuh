@@ -97,6 +97,27 @@ __host__ __device__ inline int orb_level_pitch(const OrbPlanDev& P, int l) { ret
 #define ORB_PY(p) ((int)(((p) >> 12) & 0xFFFu))
 #define ORB_PS(p) ((int)((p) >> 24))
 
+// Frame::ComputeStereoMatches on the device (src/Frame.cc:466-640): the unblurred pyramids, keypoints and
+// descriptors of the most recent left / right frame stay where the two extractors left them in HBM.
+struct OrbStereoSide {
+    const uint8_t* lvl[ORB_MAX_LEVELS];      // level l, row 0 (frame 0 of the context that holds the frame)
+    int pitch[ORB_MAX_LEVELS], w[ORB_MAX_LEVELS], h[ORB_MAX_LEVELS];
+    const void* kps;                         // orbgpu_keypoint[n]
+    const uint8_t* desc;                     // [n][32]
+    int n;
+};
+struct OrbStereoArgs {
+    OrbStereoSide L, R;
+    int nlevels;
+    float scale[ORB_MAX_LEVELS], inv_scale[ORB_MAX_LEVELS];
+    float bf, b;                             // mbf, mb
+    int th_orb_dist, th_high;                // (TH_HIGH + TH_LOW) / 2, TH_HIGH  (src/Frame.cc:471, :522)
+    float* u_right;                          // [L.n] mvuRight before the median filter (-1 = no match)
+    float* depth;                            // [L.n] mvDepth
+    int* sad;                                // [L.n] best SAD of the sub-pixel search (-1 = no match)
+};
+int orb_launch_stereo(const OrbStereoArgs& A, cudaStream_t st);
+
 // kernel launchers (orb_kernels.cu); every one enqueues on `st` and returns the launch count
 int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st);
 int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream_t st);

@@ -946,6 +946,74 @@ int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* 
     return count;
 }
 
+// ---- Frame::ComputeStereoMatches (src/Frame.cc:466-640) --------------------------------------------------------
+static int stereo_side(orbgpu_extractor* e, OrbStereoSide& S)
+{
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    const Plan& pl = e->plan;
+    for (int l = 0; l < e->nlevels; ++l) {
+        const OrbLevel& L = pl.dev.lv[l];
+        S.lvl[l] = l == 0 ? c->d_in : c->d_pyr + L.pyr_off;
+        S.pitch[l] = l == 0 ? (int)pl.in_pitch : L.pitch;
+        S.w[l] = L.w; S.h[l] = L.h;
+    }
+    S.kps = c->d_kps; S.desc = c->d_desc;
+    CU(cudaMemcpy(&S.n, c->d_nout, sizeof(int), cudaMemcpyDeviceToHost));   // count of the frame this context extracted last
+    return S.n < 0 ? ORBGPU_ERR_STATE : ORBGPU_OK;
+}
+
+int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float bf, float b, float* u_right, float* depth,
+                        int capacity, int* n_left)
+{
+    if (!left || !right || !u_right || !depth || !n_left || !(b > 0.f)) return ORBGPU_ERR_ARG;
+    if (left->device != right->device || left->nlevels != right->nlevels) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(left)) != ORBGPU_OK) return rc;
+    OrbStereoArgs A;
+    memset(&A, 0, sizeof(A));
+    if ((rc = stereo_side(left, A.L)) != ORBGPU_OK || (rc = stereo_side(right, A.R)) != ORBGPU_OK) return rc;
+    for (int l = 0; l < left->nlevels; ++l)
+        if (A.L.w[l] != A.R.w[l] || A.L.h[l] != A.R.h[l] || left->scale[l] != right->scale[l]) return ORBGPU_ERR_ARG;
+    const int N = A.L.n;
+    *n_left = N;
+    if (capacity < N) return ORBGPU_ERR_CAPACITY;
+    if (A.R.n >= 65535) return ORBGPU_ERR_UNSUPPORTED;        // right index is packed into 16 bits
+    if (N == 0) return ORBGPU_OK;
+    A.nlevels = left->nlevels;
+    for (int l = 0; l < left->nlevels; ++l) { A.scale[l] = left->scale[l]; A.inv_scale[l] = left->inv_scale[l]; }
+    A.bf = bf; A.b = b;
+    A.th_high = 100; A.th_orb_dist = (100 + 50) / 2;           // ORBmatcher::TH_HIGH, TH_LOW (src/ORBmatcher.cc:37-38)
+    float* d_out = nullptr;
+    CU(cudaMalloc(&d_out, 3 * sizeof(float) * (size_t)N));
+    A.u_right = d_out; A.depth = d_out + N; A.sad = reinterpret_cast<int*>(d_out + 2 * (size_t)N);
+    cudaStream_t st = left->ctx[0].st;
+    // the right handle's work was synchronised by its own extract call; same device, so a plain launch suffices
+    if (orb_launch_stereo(A, st) < 0) { cudaFree(d_out); return ORBGPU_ERR_CUDA; }
+    left->launches += 1;
+    std::vector<int> sad((size_t)N);
+    cudaError_t ce = cudaMemcpyAsync(u_right, A.u_right, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(depth, A.depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(sad.data(), A.sad, sizeof(int) * (size_t)N, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+    cudaFree(d_out);
+    CU(ce);
+    // outlier rejection by the median SAD (:626-639): accepted matches sorted by (SAD, left index)
+    std::vector<std::pair<int, int> > v;
+    for (int i = 0; i < N; ++i) if (sad[i] >= 0) v.push_back(std::make_pair(sad[i], i));
+    if (!v.empty()) {                                          // (the reference indexes an empty vector here when nothing matched)
+        std::sort(v.begin(), v.end());
+        const float median = (float)v[v.size() / 2].first;
+        const float thDist = 1.5f * 1.4f * median;
+        for (int i = (int)v.size() - 1; i >= 0; --i) {
+            if ((float)v[i].first < thDist) break;
+            u_right[v[i].second] = -1.f;
+            depth[v[i].second] = -1.f;
+        }
+    }
+    return ORBGPU_OK;
+}
+
 // ---- float-step test hooks ------------------------------------------------------------------------
 int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg)
 {

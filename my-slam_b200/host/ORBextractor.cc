@@ -150,6 +150,21 @@ bool ORBextractor::ExtractBatch(const std::vector<cv::Mat>& frames, std::vector<
     return true;
 }
 
+bool ORBextractor::ComputeStereoMatches(ORBextractor& left, ORBextractor& right, float bf, float b,
+                                        std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+{
+    const int cap = orbgpu_max_keypoints(left.mpHandle, left.mLastW, left.mLastH);
+    if (cap < 0) { left.mLastError = orbgpu_strerror(cap); return false; }
+    mvuRight.assign((size_t)(cap > 0 ? cap : 1), -1.0f);
+    mvDepth.assign((size_t)(cap > 0 ? cap : 1), -1.0f);
+    int n = 0;
+    const int rc = orbgpu_stereo_match(left.mpHandle, right.mpHandle, bf, b, mvuRight.data(), mvDepth.data(), cap, &n);
+    if (rc != ORBGPU_OK) { left.mLastError = orbgpu_strerror(rc); mvuRight.clear(); mvDepth.clear(); return false; }
+    mvuRight.resize((size_t)n);
+    mvDepth.resize((size_t)n);
+    return true;
+}
+
 static inline int reflect101(int i, int n)
 {
     if (n == 1) return 0;

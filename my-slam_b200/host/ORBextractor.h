@@ -56,6 +56,10 @@ public:
     // same-shape batch (frames[i] all w x h): one upload / launch set / download per chunk
     bool ExtractBatch(const std::vector<cv::Mat>& frames, std::vector<std::vector<cv::KeyPoint> >& keypoints,
                       std::vector<cv::Mat>& descriptors);
+    // Frame::ComputeStereoMatches (src/Frame.cc:466-640) between the frames the two extractors processed last: fills
+    // mvuRight / mvDepth (size = left keypoint count, -1 where unmatched) without downloading either pyramid.
+    static bool ComputeStereoMatches(ORBextractor& left, ORBextractor& right, float bf, float b,
+                                     std::vector<float>& mvuRight, std::vector<float>& mvDepth);
     const char* LastError() const { return mLastError; }
     orbgpu_extractor* Handle() { return mpHandle; }
 

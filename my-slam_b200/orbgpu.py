@@ -44,6 +44,7 @@ def lib():
         "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_extract_batch_async": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_wait": (i32, [vp]),
+        "orbgpu_stereo_match": (i32, [vp, vp, f32, f32, vp, vp, i32, pi]),
         "orbgpu_set_input_format": (i32, [vp, i32, i32]),
         "orbgpu_submit": (i32, [vp, vp, i32, i32, sz, C.POINTER(u64)]),
         "orbgpu_collect": (i32, [vp, u64, vp, vp, i32, pi]),
@@ -258,6 +259,14 @@ class ORBextractor:
     def set_batching(self, streams, max_chunk_frames): _check(self._L.orbgpu_set_batching(self._h, int(streams), int(max_chunk_frames)))
 
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
+
+
+def stereo_match(left, right, bf, b):
+    """Frame::ComputeStereoMatches between the last frames of two ORBextractor handles -> (mvuRight, mvDepth)."""
+    cap = 1 << 16
+    u = np.zeros(cap, np.float32); d = np.zeros(cap, np.float32); n = C.c_int(0)
+    _check(lib().orbgpu_stereo_match(left._h, right._h, bf, b, _p(u), _p(d), cap, C.byref(n)))
+    return u[:n.value].copy(), d[:n.value].copy()
 
 
 class ORBmatcher:

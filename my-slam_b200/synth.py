@@ -47,6 +47,23 @@ def synth(w: int, h: int, seed: int, rect_div: int = 1, noise_amp: int = 8) -> n
     return _box3(np.clip(img + noise, 0, 255).astype(np.uint8))
 
 
+def stereo_pair(w: int, h: int, seed: int, disparities=(6, 14, 27), noise_amp: int = 3):
+    """A rectified left/right pair: horizontal bands of one scene, band k seen with disparity disparities[k]
+    (uR = uL - d), plus independent per-pixel noise in the right image."""
+    pad = max(disparities) + 1
+    scene = synth(w + pad, h, seed)
+    left = scene[:, :w].copy()
+    right = np.empty_like(left)
+    nb = len(disparities)
+    for k, d in enumerate(disparities):
+        y0, y1 = h * k // nb, h * (k + 1) // nb
+        right[y0:y1] = scene[y0:y1, d:d + w]
+    r = splitmix64(seed ^ 0x57E2E0, 0, w * h)
+    nz = (r % np.uint64(2 * noise_amp + 1)).astype(np.int32).reshape(h, w) - noise_amp
+    right = np.clip(right.astype(np.int32) + nz, 0, 255).astype(np.uint8)
+    return left, right
+
+
 def flat(w: int, h: int, value: int = 128) -> np.ndarray:
     return np.full((h, w), value, np.uint8)
 

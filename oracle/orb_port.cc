@@ -5,6 +5,7 @@
 #include "orb_pattern.h"   // the 512-point rBRIEF table (data constant, my-slam_b200/csrc)
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -413,3 +414,105 @@ int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int 
 }
 
 }  // extern "C"
+
+
+// ---- Frame::ComputeStereoMatches, src/Frame.cc:466-640 (PARITY UNPINNED: restatement only, see orb_port.h) --------
+namespace {
+inline int refl101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = i < 0 ? -i : 2 * (n - 1) - i;
+    return i;
+}
+inline float lvl_px(const uint8_t* lvl, int w, int h, int x, int y) { return (float)lvl[(size_t)refl101(y, h) * w + refl101(x, w)]; }
+}  // namespace
+
+extern "C" void orbport_stereo_matches(const orbport_keypoint* kL, const uint8_t* dL, int nL, const orbport_keypoint* kR,
+                                       const uint8_t* dR, int nR, const uint8_t* const* lvlL, const uint8_t* const* lvlR,
+                                       const int* w, const int* h, const float* scale, const float* inv_scale, float bf, float b,
+                                       float* u_right, float* depth)
+{
+    const int TH_HIGH = 100, TH_LOW = 50;                      // src/ORBmatcher.cc:37-38
+    for (int i = 0; i < nL; ++i) { u_right[i] = -1.0f; depth[i] = -1.0f; }        // :468-469
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;              // :471
+    const int nRows = h[0];                                    // :473
+    std::vector<std::vector<size_t> > rows((size_t)nRows);     // :476-495 right keypoints per image row
+    for (int iR = 0; iR < nR; ++iR) {
+        const float kpY = kR[iR].y;
+        const float r = 2.0f * scale[kR[iR].octave];
+        const int maxr = (int)std::ceil(kpY + r), minr = (int)std::floor(kpY - r);
+        for (int yi = minr; yi <= maxr; ++yi)
+            if (yi >= 0 && yi < nRows) rows[(size_t)yi].push_back((size_t)iR);      // (the reference does not guard yi)
+    }
+    const float minZ = b, minD = 0, maxD = bf / minZ;          // :497-499
+    std::vector<std::pair<int, int> > vDistIdx;
+    for (int iL = 0; iL < nL; ++iL) {
+        const orbport_keypoint& kpL = kL[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y, uL = kpL.x;
+        const std::vector<size_t>& cand = rows[(size_t)vL];    // :512 float -> index
+        if (cand.empty()) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        size_t bestIdxR = 0;
+        for (size_t iC = 0; iC < cand.size(); ++iC) {          // :528-549
+            const size_t iR = cand[iC];
+            const orbport_keypoint& kpR = kR[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = orbport_hamming256(dL + 32 * (size_t)iL, dR + 32 * iR);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {                            // :552 sub-pixel match by correlation
+            const float uR0 = kR[bestIdxR].x;
+            const float sf = inv_scale[levelL];
+            const float scaleduL = std::round(kpL.x * sf), scaledvL = std::round(kpL.y * sf), scaleduR0 = std::round(uR0 * sf);
+            const int wdw = 5, L = 5;
+            const int cxL = (int)scaleduL, cy = (int)scaledvL, cxR = (int)scaleduR0;
+            const uint8_t* PL = lvlL[levelL]; const uint8_t* PR = lvlR[levelL];
+            const int lw = w[levelL], lh = h[levelL];
+            int bestSad = INT_MAX, bestincR = 0;
+            float vDists[2 * 5 + 1];
+            const float iniu = scaleduR0 + L - wdw, endu = scaleduR0 + L + wdw + 1;
+            if (iniu < 0 || endu >= lw) continue;              // :572-575
+            const float cL = lvl_px(PL, lw, lh, cxL, cy);
+            for (int incR = -L; incR <= L; ++incR) {           // :577-592
+                const float cR = lvl_px(PR, lw, lh, cxR + incR, cy);
+                double acc = 0;                                // cv::norm(NORM_L1) accumulates in double
+                for (int dy = -wdw; dy <= wdw; ++dy)
+                    for (int dx = -wdw; dx <= wdw; ++dx) {
+                        const float a = lvl_px(PL, lw, lh, cxL + dx, cy + dy) - cL;
+                        const float bb = lvl_px(PR, lw, lh, cxR + incR + dx, cy + dy) - cR;
+                        acc += std::fabs(a - bb);
+                    }
+                const float dist = (float)acc;
+                if (dist < bestSad) { bestSad = (int)dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;     // :594
+            const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));     // :602
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = scale[levelL] * ((float)scaleduR0 + (float)bestincR + deltaR);       // :608
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {       // :612-622
+                if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+                depth[iL] = bf / disparity;
+                u_right[iL] = bestuR;
+                vDistIdx.push_back(std::pair<int, int>(bestSad, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return;                              // (the reference indexes the empty vector, :627)
+    std::sort(vDistIdx.begin(), vDistIdx.end());               // :626-639
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; --i) {
+        if (vDistIdx[i].first < thDist) break;
+        u_right[vDistIdx[i].second] = -1;
+        depth[vDistIdx[i].second] = -1;
+    }
+}

@@ -50,6 +50,16 @@ void orbport_match_bruteforce(const uint8_t* A, int nA, const uint8_t* B, int nB
 /* accepted-match count of one keyframe pair: best <= th_low && float(best) < ratio*float(second) */
 int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int th_low, float ratio);
 
+/* Frame::ComputeStereoMatches (src/Frame.cc:466-640).  PARITY UNPINNED for this function: src/Frame.cc needs
+ * the whole ORB-SLAM2 header set (DBoW2 vocabulary templates, KeyFrame, MapPoint, cv::undistortPoints ...) and cannot
+ * be compiled here, and the reference has no test for it; this is a line-by-line restatement only.
+ * lvlL/lvlR[l] = dense unblurred level l (w[l] x h[l], pitch w[l]) of the left / right pyramid; pixels outside a
+ * level are its REFLECT_101 continuation (the 19-px frame of mvImagePyramid).  Outputs mvuRight / mvDepth [nL]. */
+void orbport_stereo_matches(const orbport_keypoint* kL, const uint8_t* dL, int nL, const orbport_keypoint* kR,
+                            const uint8_t* dR, int nR, const uint8_t* const* lvlL, const uint8_t* const* lvlR,
+                            const int* w, const int* h, const float* scale, const float* inv_scale, float bf, float b,
+                            float* u_right, float* depth);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,9 @@ class OraclePort:
         L.orbport_match_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                                C.c_void_p, C.c_void_p]
         L.orbport_match_count.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float]
+        L.orbport_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
 
@@ -129,6 +132,21 @@ class OraclePort:
         bi = np.zeros(len(A), np.int32); b1 = np.zeros(len(A), np.uint16); b2 = np.zeros(len(A), np.uint16)
         self.L.orbport_match_bruteforce(_ptr(A), len(A), _ptr(B), len(B), _ptr(bi), _ptr(b1), _ptr(b2))
         return bi, b1, b2
+
+    def stereo_matches(self, kL, dL, kR, dR, lvlL, lvlR, bf, b):
+        """Frame::ComputeStereoMatches restated (parity unpinned, oracle/orb_port.h) -> (mvuRight, mvDepth)."""
+        nl = self.nlevels
+        lvlL = [np.ascontiguousarray(a, np.uint8) for a in lvlL]; lvlR = [np.ascontiguousarray(a, np.uint8) for a in lvlR]
+        pl = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlL]); pr = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlR])
+        w = np.array([a.shape[1] for a in lvlL], np.int32); h = np.array([a.shape[0] for a in lvlL], np.int32)
+        s4 = self.tables()[0]
+        sc = np.ascontiguousarray(s4[0]); isc = np.ascontiguousarray(s4[1])
+        kL = np.ascontiguousarray(kL); kR = np.ascontiguousarray(kR)
+        dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+        u = np.zeros(max(len(kL), 1), np.float32); d = np.zeros(max(len(kL), 1), np.float32)
+        self.L.orbport_stereo_matches(_ptr(kL), _ptr(dL), len(kL), _ptr(kR), _ptr(dR), len(kR), pl, pr, _ptr(w), _ptr(h),
+                                      _ptr(sc), _ptr(isc), bf, b, _ptr(u), _ptr(d))
+        return u[:len(kL)].copy(), d[:len(kL)].copy()
 
     def match_count(self, A, B, th_low=50, ratio=0.6):
         A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)
