@@ -127,6 +127,57 @@ int orbgpu_pyramid_level(orbgpu_extractor* e, int level, uint8_t* dst, size_t ds
 int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float bf, float b,
                         float* u_right, float* depth, int capacity, int* n_left);
 
+/* Frame::UndistortKeyPoints (src/Frame.cc:404-435): the keypoints of the most recent frame of `e`, read where they
+ * lie in HBM, with pt replaced by cv::undistortPoints(pt, K, D, noArray(), K) (OpenCV 4.13: 5 iterations in double);
+ * the other fields are copied.  K4 = fx, fy, cx, cy of mK; dist = k1, k2, p1, p2[, k3] of mDistCoef (ndist = 4 or 5,
+ * up to 12 accepted).  dist[0] == 0 returns the keypoints unchanged, as the reference does. */
+int orbgpu_undistort_keypoints(orbgpu_extractor* e, const float* K4, const float* dist, int ndist,
+                               orbgpu_keypoint* kps_un, int capacity, int* n_out);
+
+/* cv::undistortPoints(xy, K, D, noArray(), K) on n arbitrary points (host buffers, x0 y0 x1 y1 ...): the four image
+ * corners of Frame::ComputeImageBounds (src/Frame.cc:437-463), or any point list. */
+int orbgpu_undistort_points(int device, const float* xy, int n, const float* K4, const float* dist, int ndist, float* out_xy);
+
+/* ---- grid-gated searches between two frames ------------------------------------------
+ * Plain-array snapshots of what the reference reads through Frame / MapPoint getters.  bounds4 = mnMinX, mnMaxX,
+ * mnMinY, mnMaxY of the searched frame (its 64 x 48 grid, src/Frame.cc:230-245, is rebuilt on the device). */
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:405-520).
+ * keys*_un = mvKeysUn, desc* = mDescriptors; prev_matched (n1 x 2, in/out) = vbPrevMatched; matches12[n1] = vnMatches12;
+ * *nmatches = the return value.  nnratio / check_orientation = the matcher's mfNNratio / mbCheckOrientation. */
+int orbgpu_search_for_initialization(int device, const orbgpu_keypoint* keys1_un, const uint8_t* desc1, int n1,
+                                     const orbgpu_keypoint* keys2_un, const uint8_t* desc2, int n2, const float* bounds4,
+                                     float* prev_matched, int window_size, float nnratio, int check_orientation,
+                                     int32_t* matches12, int* nmatches);
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1328-1470). */
+typedef struct orbgpu_projection_args {
+    int32_t n_last;
+    const float* world_pos;        /* n_last x 3: pMP->GetWorldPos() */
+    const uint8_t* mp_desc;        /* n_last x 32: pMP->GetDescriptor() */
+    const uint8_t* mp_valid;       /* LastFrame.mvpMapPoints[i] && !LastFrame.mvbOutlier[i] */
+    const uint8_t* mp_observed;    /* pMP->Observations() > 0 */
+    const int32_t* last_octave;    /* LastFrame.mvKeys[i].octave */
+    const float* last_angle;       /* LastFrame.mvKeysUn[i].angle */
+    const float* Tcw_last;         /* LastFrame.mTcw, 4 x 4 row-major */
+    int32_t n_cur;
+    const orbgpu_keypoint* cur_keys_un;   /* CurrentFrame.mvKeysUn */
+    const uint8_t* cur_desc;       /* CurrentFrame.mDescriptors */
+    const float* cur_u_right;      /* CurrentFrame.mvuRight */
+    const uint8_t* cur_occupied;   /* CurrentFrame.mvpMapPoints[i2] && ->Observations() > 0, on entry */
+    const float* Tcw_cur;          /* CurrentFrame.mTcw */
+    float fx, fy, cx, cy, bf, b;   /* CurrentFrame.fx .. mbf, mb */
+    float bounds[4];               /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;    /* CurrentFrame.mvScaleFactors[nlevels] */
+    int32_t nlevels;
+    float th;
+    int32_t mono;                  /* bMono */
+    int32_t check_orientation;     /* mbCheckOrientation */
+} orbgpu_projection_args;
+/* cur_match[n_cur]: what the call did to CurrentFrame.mvpMapPoints[i2]: -1 untouched, i >= 0 set to the map point of
+ * last-frame keypoint i, -2 set and then reset to NULL by the rotation-consistency check.  *nmatches = return value. */
+int orbgpu_search_by_projection(int device, const orbgpu_projection_args* args, int32_t* cur_match, int* nmatches);
+
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),
  * FAST candidates in list order (:791-831) and octree survivors in list order (:541-765); x, y are

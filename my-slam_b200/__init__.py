@@ -5,5 +5,6 @@ classes in host/.  This package is the thin ctypes binding used by the tests and
 directory name has a hyphen, so import it through __graft_entry__.load_package() (module name
 `my_slam_b200`).
 """
-from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path, stereo_match)  # noqa: F401
+from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path, stereo_match, undistort_points,
+                     ProjectionArgs, projection_args, search_for_initialization, search_by_projection)  # noqa: F401
 from . import shard, synth  # noqa: F401

@@ -117,6 +117,10 @@ struct OrbStereoArgs {
     int* sad;                                // [L.n] best SAD of the sub-pixel search (-1 = no match)
 };
 int orb_launch_stereo(const OrbStereoArgs& A, cudaStream_t st);
+// orb_frame.cu: K4 = fx, fy, cx, cy; dist = k1, k2, p1, p2[, k3 ...] (ndist <= 12), both host pointers
+int orb_launch_undistort_points(const float* K4, const float* dist, int ndist, const float* d_src, float* d_dst, int n, cudaStream_t st);
+int orb_launch_undistort_keypoints(const float* K4, const float* dist, int ndist, const void* d_kps, void* d_kps_un, const int* d_n,
+                                   int capacity, cudaStream_t st);
 
 // kernel launchers (orb_kernels.cu); every one enqueues on `st` and returns the launch count
 int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st);

@@ -1014,6 +1014,47 @@ int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float b
     return ORBGPU_OK;
 }
 
+// ---- Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cc:404-463) -------------------------
+int orbgpu_undistort_keypoints(orbgpu_extractor* e, const float* K4, const float* dist, int ndist, orbgpu_keypoint* kps_un,
+                               int capacity, int* n_out)
+{
+    if (!e || !K4 || !dist || !kps_un || !n_out || ndist < 4 || ndist > 12) return ORBGPU_ERR_ARG;
+    StreamCtx* c = last_frame_ctx(e);
+    if (!c) return ORBGPU_ERR_STATE;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    int n = 0;
+    CU(cudaMemcpy(&n, c->d_nout, sizeof(int), cudaMemcpyDeviceToHost));
+    if (n < 0) return ORBGPU_ERR_STATE;
+    *n_out = n;
+    if (capacity < n) return ORBGPU_ERR_CAPACITY;
+    if (n == 0) return ORBGPU_OK;
+    void* d_un = nullptr;
+    CU(cudaMalloc(&d_un, sizeof(orbgpu_keypoint) * (size_t)n));
+    cudaStream_t st = c->st;
+    orb_launch_undistort_keypoints(K4, dist, ndist, c->d_kps, d_un, c->d_nout, n, st);
+    e->launches += 1;
+    cudaError_t ce = cudaMemcpyAsync(kps_un, d_un, sizeof(orbgpu_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+    cudaFree(d_un);
+    CU(ce);
+    return ORBGPU_OK;
+}
+
+int orbgpu_undistort_points(int device, const float* xy, int n, const float* K4, const float* dist, int ndist, float* out_xy)
+{
+    if (!xy || !K4 || !dist || !out_xy || n < 0 || ndist < 4 || ndist > 12) return ORBGPU_ERR_ARG;
+    if (n == 0) return ORBGPU_OK;
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return ORBGPU_ERR_CUDA; }
+    float* d = nullptr;
+    if (cudaMalloc(&d, 4 * sizeof(float) * (size_t)n) != cudaSuccess) { cudaGetLastError(); return ORBGPU_ERR_CUDA; }
+    cudaError_t ce = cudaMemcpy(d, xy, 2 * sizeof(float) * (size_t)n, cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) { orb_launch_undistort_points(K4, dist, ndist, d, d + 2 * (size_t)n, n, 0); ce = cudaGetLastError(); }
+    if (ce == cudaSuccess) ce = cudaMemcpy(out_xy, d + 2 * (size_t)n, 2 * sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return ce == cudaSuccess ? ORBGPU_OK : ORBGPU_ERR_CUDA;
+}
+
 // ---- float-step test hooks ------------------------------------------------------------------------
 int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg)
 {

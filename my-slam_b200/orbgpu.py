@@ -16,6 +16,39 @@ class OrbGpuError(RuntimeError):
     pass
 
 
+class ProjectionArgs(C.Structure):
+    """orbgpu_projection_args (include/orbgpu.h): the snapshot ORBmatcher::SearchByProjection(Frame, Frame) reads."""
+    _fields_ = [("n_last", C.c_int32), ("world_pos", C.c_void_p), ("mp_desc", C.c_void_p), ("mp_valid", C.c_void_p),
+                ("mp_observed", C.c_void_p), ("last_octave", C.c_void_p), ("last_angle", C.c_void_p), ("Tcw_last", C.c_void_p),
+                ("n_cur", C.c_int32), ("cur_keys_un", C.c_void_p), ("cur_desc", C.c_void_p), ("cur_u_right", C.c_void_p),
+                ("cur_occupied", C.c_void_p), ("Tcw_cur", C.c_void_p),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float), ("b", C.c_float),
+                ("bounds", C.c_float * 4), ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("th", C.c_float),
+                ("mono", C.c_int32), ("check_orientation", C.c_int32)]
+
+
+def projection_args(world_pos, mp_desc, mp_valid, mp_observed, last_octave, last_angle, Tcw_last, cur_keys_un, cur_desc,
+                    cur_u_right, cur_occupied, Tcw_cur, cam, bf, b, bounds, scale_factors, th, mono, check_orientation=True):
+    """Builds a ProjectionArgs; returns (struct, keepalive list of the arrays it points into)."""
+    f32, u8, i32 = np.float32, np.uint8, np.int32
+    arrs = dict(world_pos=np.ascontiguousarray(world_pos, f32), mp_desc=np.ascontiguousarray(mp_desc, u8),
+                mp_valid=np.ascontiguousarray(mp_valid, u8), mp_observed=np.ascontiguousarray(mp_observed, u8),
+                last_octave=np.ascontiguousarray(last_octave, i32), last_angle=np.ascontiguousarray(last_angle, f32),
+                Tcw_last=np.ascontiguousarray(Tcw_last, f32), cur_keys_un=np.ascontiguousarray(cur_keys_un),
+                cur_desc=np.ascontiguousarray(cur_desc, u8), cur_u_right=np.ascontiguousarray(cur_u_right, f32),
+                cur_occupied=np.ascontiguousarray(cur_occupied, u8), Tcw_cur=np.ascontiguousarray(Tcw_cur, f32),
+                scale_factors=np.ascontiguousarray(scale_factors, f32))
+    a = ProjectionArgs()
+    for k, v in arrs.items():
+        setattr(a, k, v.ctypes.data)
+    a.n_last = len(arrs["last_octave"]); a.n_cur = len(arrs["cur_keys_un"])
+    a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+    a.bf, a.b, a.th = float(bf), float(b), float(th)
+    a.bounds = (C.c_float * 4)(*[float(v) for v in bounds])
+    a.nlevels = len(arrs["scale_factors"]); a.mono = int(mono); a.check_orientation = int(check_orientation)
+    return a, arrs
+
+
 def lib_path():
     return os.path.join(_HERE, "liborbgpu.so")
 
@@ -62,6 +95,10 @@ def lib():
         "orbgpu_launch_count": (u64, [vp]),
         "orbgpu_last_batch_ms": (C.c_double, [vp]),
         "orbgpu_set_batching": (i32, [vp, i32, i32]),
+        "orbgpu_undistort_keypoints": (i32, [vp, vp, vp, i32, vp, i32, pi]),
+        "orbgpu_undistort_points": (i32, [i32, vp, i32, vp, vp, i32, vp]),
+        "orbgpu_search_for_initialization": (i32, [i32, vp, vp, i32, vp, vp, i32, vp, vp, i32, f32, i32, vp, pi]),
+        "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
@@ -197,6 +234,14 @@ class ORBextractor:
     def queue_depth(self):
         return _check(self._L.orbgpu_queue_depth(self._h))
 
+    # Frame::UndistortKeyPoints, src/Frame.cc:404-435
+    def undistort_keypoints(self, K4, dist):
+        K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+        cap = 1 << 16
+        kps = np.zeros(cap, KP_DTYPE); n = C.c_int(0)
+        _check(self._L.orbgpu_undistort_keypoints(self._h, _p(K4), _p(dist), len(dist), _p(kps), cap, C.byref(n)))
+        return kps[:n.value].copy()
+
     # mvImagePyramid, include/ORBextractor.h:85
     def pyramid_level(self, level, bordered=False):
         w, h = C.c_int(), C.c_int()
@@ -259,6 +304,36 @@ class ORBextractor:
     def set_batching(self, streams, max_chunk_frames): _check(self._L.orbgpu_set_batching(self._h, int(streams), int(max_chunk_frames)))
 
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
+
+
+def undistort_points(xy, K4, dist, device=0):
+    """cv::undistortPoints(xy, K, D, noArray(), K) (src/Frame.cc:404-463); K4 = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(xy)
+    _check(lib().orbgpu_undistort_points(device, _p(xy), len(xy), _p(K4), _p(dist), len(dist), _p(out)))
+    return out
+
+
+def search_for_initialization(keys1_un, desc1, keys2_un, desc2, bounds, prev_matched, window_size=100, nnratio=0.9,
+                              check_orientation=True, device=0):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) -> (nmatches, vnMatches12, updated vbPrevMatched)."""
+    k1 = np.ascontiguousarray(keys1_un); k2 = np.ascontiguousarray(keys2_un)
+    d1 = np.ascontiguousarray(desc1, np.uint8); d2 = np.ascontiguousarray(desc2, np.uint8)
+    b4 = np.ascontiguousarray(bounds, np.float32)
+    pm = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.zeros(max(len(k1), 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_for_initialization(device, _p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), _p(b4), _p(pm),
+                                                  int(window_size), float(nnratio), int(check_orientation), _p(m12), C.byref(nm)))
+    return nm.value, m12[:len(k1)].copy(), pm
+
+
+def search_by_projection(args, device=0):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1328-1470) on a
+    ProjectionArgs snapshot -> (nmatches, cur_match[n_cur])."""
+    cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_by_projection(device, C.byref(args), _p(cm), C.byref(nm)))
+    return nm.value, cm[:args.n_cur].copy()
 
 
 def stereo_match(left, right, bf, b):

@@ -1,0 +1,233 @@
+// frame_port.cc -- TEST INFRASTRUCTURE (oracle), PARITY UNPINNED; see frame_port.h.
+#include "frame_port.h"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <vector>
+
+namespace {
+
+const int GRID_ROWS = 48, GRID_COLS = 64;                     // include/Frame.h:37-38
+const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:37-39
+
+struct Grid {                                                 // Frame::mGrid + the members GetFeaturesInArea reads
+    std::vector<size_t> cell[GRID_COLS][GRID_ROWS];
+    float minX, maxX, minY, maxY, invW, invH;
+    const orbport_keypoint* keys;
+    int N;
+};
+
+// src/Frame.cc:383-391 + :230-245; grid element sizes as src/Frame.cc:155-156
+void build_grid(Grid& g, const orbport_keypoint* keys, int n, const float* b)
+{
+    g.minX = b[0]; g.maxX = b[1]; g.minY = b[2]; g.maxY = b[3];
+    g.invW = static_cast<float>(GRID_COLS) / static_cast<float>(g.maxX - g.minX);
+    g.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(g.maxY - g.minY);
+    g.keys = keys; g.N = n;
+    for (int i = 0; i < n; ++i) {
+        const int posX = std::round((keys[i].x - g.minX) * g.invW);
+        const int posY = std::round((keys[i].y - g.minY) * g.invH);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        g.cell[posX][posY].push_back((size_t)i);
+    }
+}
+
+// src/Frame.cc:327-380
+std::vector<size_t> features_in_area(const Grid& g, float x, float y, float r, int minLevel, int maxLevel)
+{
+    std::vector<size_t> v;
+    const int nMinCellX = std::max(0, (int)std::floor((x - g.minX - r) * g.invW));
+    if (nMinCellX >= GRID_COLS) return v;
+    const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - g.minX + r) * g.invW));
+    if (nMaxCellX < 0) return v;
+    const int nMinCellY = std::max(0, (int)std::floor((y - g.minY - r) * g.invH));
+    if (nMinCellY >= GRID_ROWS) return v;
+    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - g.minY + r) * g.invH));
+    if (nMaxCellY < 0) return v;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ++ix)
+        for (int iy = nMinCellY; iy <= nMaxCellY; ++iy) {
+            const std::vector<size_t>& c = g.cell[ix][iy];
+            for (size_t j = 0; j < c.size(); ++j) {
+                const orbport_keypoint& kp = g.keys[c[j]];
+                if (bCheckLevels) {
+                    if (kp.octave < minLevel) continue;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                }
+                const float distx = kp.x - x, disty = kp.y - y;
+                if (std::fabs(distx) < r && std::fabs(disty) < r) v.push_back(c[j]);
+            }
+        }
+    return v;
+}
+
+// src/ORBmatcher.cc:1601-1642
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; ++i) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+inline int rot_bin(float a1, float a2)                        // src/ORBmatcher.cc:474-480, :1432-1438
+{
+    const float factor = 1.0f / HISTO_LENGTH;
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = std::round(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+// cv::Mat "A*x + c" for 3x3 * 3x1 CV_32F = cv::gemm's small-matrix case: float products summed left to right,
+// then (float)(t*alpha + c*beta) with alpha = beta = 1.0 as doubles
+inline void mat3_mul_add(const float* A, int astep, const float* x, const float* c, float* d)
+{
+    for (int i = 0; i < 3; ++i) {
+        const float* a = A + i * astep;
+        const float t = a[0] * x[0] + a[1] * x[1] + a[2] * x[2];
+        d[i] = (float)((double)t * 1.0 + (double)c[i] * 1.0);
+    }
+}
+
+}  // namespace
+
+extern "C" int frameport_features_in_area(const orbport_keypoint* keys_un, int n, const float* bounds4, float x, float y, float r,
+                                          int min_level, int max_level, int* out, int cap)
+{
+    Grid* g = new Grid;
+    build_grid(*g, keys_un, n, bounds4);
+    const std::vector<size_t> v = features_in_area(*g, x, y, r, min_level, max_level);
+    delete g;
+    for (size_t i = 0; i < v.size() && (int)i < cap; ++i) out[i] = (int)v[i];
+    return (int)v.size();
+}
+
+extern "C" int frameport_search_for_initialization(const orbport_keypoint* k1, const uint8_t* d1, int n1, const orbport_keypoint* k2,
+                                                   const uint8_t* d2, int n2, const float* bounds4, float* prev_matched,
+                                                   int window_size, float nnratio, int check_orientation, int* matches12)
+{
+    Grid* g = new Grid;
+    build_grid(*g, k2, n2, bounds4);
+    int nmatches = 0;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance((size_t)n2, INT_MAX), vnMatches21((size_t)n2, -1);
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int level1 = k1[i1].octave;
+        if (level1 > 0) continue;
+        const std::vector<size_t> vIndices2 = features_in_area(*g, prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, level1, level1);
+        if (vIndices2.empty()) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (size_t c = 0; c < vIndices2.size(); ++c) {
+            const size_t i2 = vIndices2[c];
+            const int dist = orbport_hamming256(d1 + 32 * (size_t)i1, d2 + 32 * i2);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = (int)i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                matches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (check_orientation) rotHist[rot_bin(k1[i1].angle, k2[bestIdx2].angle)].push_back(i1);
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); ++j) {
+                const int idx1 = rotHist[i][j];
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; ++i1)
+        if (matches12[i1] >= 0) { prev_matched[2 * i1] = k2[matches12[i1]].x; prev_matched[2 * i1 + 1] = k2[matches12[i1]].y; }
+    delete g;
+    return nmatches;
+}
+
+extern "C" int frameport_search_by_projection(const frameport_projection_args* a, int* cur_match)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->cur_keys_un, a->n_cur, a->bounds);
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float* Tc = a->Tcw_cur; const float* Tl = a->Tcw_last;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]}, tlw[3] = {Tl[3], Tl[7], Tl[11]};
+    // twc = -Rcw.t() * tcw: cv::gemm with GEMM_1_T takes the generic path (double accumulation, alpha = -1)
+    float twc[3];
+    for (int i = 0; i < 3; ++i) {
+        double s = 0;
+        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        twc[i] = (float)(s * -1.0);
+    }
+    float tlc[3];
+    mat3_mul_add(Tl, 4, twc, tlw, tlc);                       // :1347
+    const bool bForward = tlc[2] > a->b && !a->mono;
+    const bool bBackward = -tlc[2] > a->b && !a->mono;
+    std::vector<int> holder((size_t)a->n_cur, -1);            // index of the last-frame point now in mvpMapPoints[i2]
+    std::vector<uint8_t> occupied(a->cur_occupied, a->cur_occupied + a->n_cur);
+    for (int i = 0; i < a->n_cur; ++i) cur_match[i] = -1;
+    for (int i = 0; i < a->n_last; ++i) {
+        if (!a->mp_valid[i]) continue;
+        float x3Dc[3];
+        mat3_mul_add(Tc, 4, a->world_pos + 3 * (size_t)i, tcw, x3Dc);
+        const float xc = x3Dc[0], yc = x3Dc[1];
+        const float invzc = 1.0 / x3Dc[2];
+        if (invzc < 0) continue;
+        const float u = a->fx * xc * invzc + a->cx;
+        const float v = a->fy * yc * invzc + a->cy;
+        if (u < a->bounds[0] || u > a->bounds[1]) continue;
+        if (v < a->bounds[2] || v > a->bounds[3]) continue;
+        const int nLastOctave = a->last_octave[i];
+        const float radius = a->th * a->scale_factors[nLastOctave];
+        std::vector<size_t> vIndices2;
+        if (bForward) vIndices2 = features_in_area(*g, u, v, radius, nLastOctave, -1);
+        else if (bBackward) vIndices2 = features_in_area(*g, u, v, radius, 0, nLastOctave);
+        else vIndices2 = features_in_area(*g, u, v, radius, nLastOctave - 1, nLastOctave + 1);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t c = 0; c < vIndices2.size(); ++c) {
+            const size_t i2 = vIndices2[c];
+            if (occupied[i2]) continue;
+            if (a->cur_u_right[i2] > 0) {
+                const float ur = u - a->bf * invzc;
+                const float er = std::fabs(ur - a->cur_u_right[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)i, a->cur_desc + 32 * i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = (int)i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            holder[bestIdx2] = i;
+            occupied[bestIdx2] = a->mp_observed[i];
+            cur_match[bestIdx2] = i;
+            nmatches++;
+            if (a->check_orientation) rotHist[rot_bin(a->last_angle[i], a->cur_keys_un[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (a->check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (size_t j = 0; j < rotHist[i].size(); ++j) { cur_match[rotHist[i][j]] = -2; nmatches--; }
+    }
+    delete g;
+    return nmatches;
+}

@@ -1,0 +1,56 @@
+/* frame_port.h -- TEST INFRASTRUCTURE (oracle).  CPU restatement of the grid-gated searches of SURVEY.md section 8(f2):
+ *   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:230-245, 327-391
+ *   ORBmatcher::SearchForInitialization                           src/ORBmatcher.cc:405-520
+ *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono) src/ORBmatcher.cc:1328-1470
+ *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
+ * PARITY UNPINNED: src/Frame.cc and src/ORBmatcher.cc need the whole ORB-SLAM2 header set (DBoW2, g2o, Eigen,
+ * MapPoint/KeyFrame) and cannot be compiled here, and the reference has no tests for them.  The one library
+ * arithmetic on this path -- cv::Mat "Rcw*x3Dw+tcw" = cv::gemm's 3x3 float special case -- was checked bit-equal
+ * against cv2 4.13.0 (20 000 random cases).  Only tests/ may use this file; the product never does. */
+#ifndef ORACLE_FRAME_PORT_H
+#define ORACLE_FRAME_PORT_H
+#include <stdint.h>
+#include "orb_port.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* same layout as orbgpu_projection_args (include/orbgpu.h) */
+typedef struct frameport_projection_args {
+    int32_t n_last;
+    const float* world_pos;        /* n_last x 3: pMP->GetWorldPos() */
+    const uint8_t* mp_desc;        /* n_last x 32: pMP->GetDescriptor() */
+    const uint8_t* mp_valid;       /* LastFrame.mvpMapPoints[i] && !LastFrame.mvbOutlier[i] */
+    const uint8_t* mp_observed;    /* pMP->Observations() > 0 */
+    const int32_t* last_octave;    /* LastFrame.mvKeys[i].octave */
+    const float* last_angle;       /* LastFrame.mvKeysUn[i].angle */
+    const float* Tcw_last;         /* 4 x 4 row-major */
+    int32_t n_cur;
+    const orbport_keypoint* cur_keys_un;
+    const uint8_t* cur_desc;
+    const float* cur_u_right;      /* CurrentFrame.mvuRight */
+    const uint8_t* cur_occupied;   /* CurrentFrame.mvpMapPoints[i2] && ->Observations() > 0 on entry */
+    const float* Tcw_cur;
+    float fx, fy, cx, cy, bf, b;
+    float bounds[4];               /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;
+    int32_t nlevels;
+    float th;
+    int32_t mono;
+    int32_t check_orientation;
+} frameport_projection_args;
+
+/* ordered index list of GetFeaturesInArea on a grid built from keys_un; returns the count */
+int frameport_features_in_area(const orbport_keypoint* keys_un, int n, const float* bounds4, float x, float y, float r,
+                               int min_level, int max_level, int* out, int cap);
+/* returns nmatches; matches12[n1]; prev_matched (n1 x 2) updated in place */
+int frameport_search_for_initialization(const orbport_keypoint* k1, const uint8_t* d1, int n1, const orbport_keypoint* k2,
+                                        const uint8_t* d2, int n2, const float* bounds4, float* prev_matched, int window_size,
+                                        float nnratio, int check_orientation, int* matches12);
+/* returns nmatches; cur_match[n_cur]: -1 untouched, -2 reset to NULL by the rotation check, >= 0 index into the last frame */
+int frameport_search_by_projection(const frameport_projection_args* a, int* cur_match);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

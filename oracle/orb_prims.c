@@ -300,3 +300,33 @@ uint64_t orbo_sincos_checksum(uint32_t first, uint32_t count, uint32_t step, int
     }
     return sum;
 }
+
+
+/* ---- cv::undistortPoints, OpenCV 4.13 (see orb_prims.h) ------------------------------------------------- */
+void orbo_undistort_points(const float* xy, int n, const float* K4, const float* dist, int ndist, float* out)
+{
+    double k[14] = {0};
+    const double fx = K4[0], fy = K4[1], cx = K4[2], cy = K4[3];
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < ndist && i < 14; ++i) k[i] = dist[i];
+    for (int i = 0; i < n; ++i) {
+        const double u = xy[2 * i], v = xy[2 * i + 1];
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; ++j) {                       /* TermCriteria(MAX_ITER, 5, 0.01): count only */
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        /* RR = P * I with P = K */
+        const double xx = fx * x + 0. * y + cx;
+        const double yy = 0. * x + fy * y + cy;
+        const double ww = 1. / (0. * x + 0. * y + 1.);
+        out[2 * i] = (float)(xx * ww);
+        out[2 * i + 1] = (float)(yy * ww);
+    }
+}

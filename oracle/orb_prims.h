@@ -64,6 +64,12 @@ void orbo_sincosf(float x, float* s, float* c);
 /* checksum of (x, sin x, cos x) over float bit patterns; which = 0 restatement, 1 host glibc */
 uint64_t orbo_sincos_checksum(uint32_t first, uint32_t count, uint32_t step, int which);
 
+/* cv::undistortPoints(src, dst, K, D, noArray(), K) of OpenCV 4.13 (calib3d undistort: 5 fixed-point iterations in
+ * double, then re-projection with P = K), as Frame::UndistortKeyPoints / ComputeImageBounds call it
+ * (src/Frame.cc:404-463).  K4 = fx, fy, cx, cy and dist = k1, k2, p1, p2[, k3] are the float values of mK / mDistCoef.
+ * Pinned: bit-equal to cv2 4.13.0 on tests/golden/undistort_golden.npz. */
+void orbo_undistort_points(const float* xy, int n, const float* K4, const float* dist, int ndist, float* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -186,9 +186,39 @@ def make_gray():
     print("gray_golden.npz written")
 
 
+UNDISTORT_CAMERAS = [    # (fx, fy, cx, cy), (k1, k2, p1, p2[, k3]): Examples/Monocular/TUM1.yaml, EuRoC.yaml, TUM2.yaml, a strong barrel
+    ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+    ((458.654, 457.296, 367.215, 248.375), (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05)),
+    ((520.908620, 521.007327, 325.141442, 249.701764), (0.231222, -0.784899, -0.003257, -0.000105, 0.917205)),
+    ((300.0, 305.0, 320.0, 240.0), (-0.9, 0.35, 0.01, -0.02, 1.9)),
+]
+
+
+def make_undistort():
+    """cv2.undistortPoints(pts, K, D, None, K), what Frame::UndistortKeyPoints / ComputeImageBounds call (src/Frame.cc:404-463)."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(4041)
+    out = {"count": np.int32(len(UNDISTORT_CAMERAS))}
+    for c, (K, D) in enumerate(UNDISTORT_CAMERAS):
+        pts = (rng.random((3000, 2)) * np.array([752.0, 480.0])).astype(np.float32)
+        pts[:4] = [[0, 0], [752, 0], [0, 480], [752, 480]]                # the image-bounds corners
+        pts[4:8] = [[K[2], K[3]], [-50.5, 20.25], [900.0, 700.0], [1e4, -1e4]]   # principal point, outside the image, far outside
+        Km = np.array([[K[0], 0, K[2]], [0, K[1], K[3]], [0, 0, 1]], np.float32)
+        Dm = np.array(D, np.float32).reshape(-1, 1)
+        und = cv2.undistortPoints(pts.reshape(-1, 1, 2), Km, Dm, None, Km).reshape(-1, 2)
+        out["K_%d" % c] = np.array(K, np.float32); out["D_%d" % c] = np.array(D, np.float32)
+        out["pts_%d" % c] = pts; out["und_%d" % c] = und.astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "undistort_golden.npz"), **out)
+    print("undistort_golden.npz written")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "gray":
         make_gray()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "undistort":
+        make_undistort()
         sys.exit(0)
     make_prims()
     make_extract()

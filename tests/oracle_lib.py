@@ -58,6 +58,11 @@ class OraclePort:
         L.orbport_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.frameport_features_in_area.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int,
+                                                 C.c_int, C.c_void_p, C.c_int]
+        L.frameport_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                          C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.frameport_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
 
@@ -147,6 +152,29 @@ class OraclePort:
         self.L.orbport_stereo_matches(_ptr(kL), _ptr(dL), len(kL), _ptr(kR), _ptr(dR), len(kR), pl, pr, _ptr(w), _ptr(h),
                                       _ptr(sc), _ptr(isc), bf, b, _ptr(u), _ptr(d))
         return u[:len(kL)].copy(), d[:len(kL)].copy()
+
+    # ---- frame_port.cc (parity unpinned restatements of src/Frame.cc / src/ORBmatcher.cc searches) ----
+    def features_in_area(self, keys_un, bounds, x, y, r, min_level=-1, max_level=-1):
+        k = np.ascontiguousarray(keys_un); b4 = np.ascontiguousarray(bounds, np.float32)
+        out = _i32(len(k))
+        n = self.L.frameport_features_in_area(_ptr(k), len(k), _ptr(b4), x, y, r, min_level, max_level, _ptr(out), len(out))
+        return out[:n].copy()
+
+    def search_for_initialization(self, k1, d1, k2, d2, bounds, prev_matched, window_size=100, nnratio=0.9, check_orientation=True):
+        k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+        d1 = np.ascontiguousarray(d1, np.uint8); d2 = np.ascontiguousarray(d2, np.uint8)
+        b4 = np.ascontiguousarray(bounds, np.float32)
+        pm = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+        m12 = _i32(len(k1))
+        nm = self.L.frameport_search_for_initialization(_ptr(k1), _ptr(d1), len(k1), _ptr(k2), _ptr(d2), len(k2), _ptr(b4),
+                                                        _ptr(pm), window_size, nnratio, int(check_orientation), _ptr(m12))
+        return nm, m12[:len(k1)].copy(), pm
+
+    def search_by_projection(self, args):
+        """args: the product's ProjectionArgs ctypes struct (same layout as frameport_projection_args)."""
+        cm = _i32(args.n_cur)
+        nm = self.L.frameport_search_by_projection(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
 
     def match_count(self, A, B, th_low=50, ratio=0.6):
         A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)

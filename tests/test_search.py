@@ -1,0 +1,186 @@
+"""Grid-gated searches between two frames: Frame::GetFeaturesInArea (src/Frame.cc:327-380),
+ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520), ORBmatcher::SearchByProjection(Frame, Frame)
+(src/ORBmatcher.cc:1328-1470).  The oracle (oracle/frame_port.cc) is PARITY UNPINNED (the reference files cannot be
+compiled here and have no tests): CPU tests check it against the geometry of a synthetic two-view scene and a
+brute-force window search, GPU tests check the device path bit-for-bit against it."""
+import numpy as np
+import pytest
+
+SHIFT = (12, -7)              # frame 2 = frame 1's scene moved by this many pixels
+
+
+def two_frames(pkg, extract, w=640, h=480, seed=0x2F2A3E, nf=1000):
+    """Two views of one synthetic scene: the second is the first shifted by SHIFT, with fresh pixel noise."""
+    pad = 32
+    scene = pkg.synth.synth(w + 2 * pad, h + 2 * pad, seed)
+    f1 = np.ascontiguousarray(scene[pad:pad + h, pad:pad + w])
+    f2 = scene[pad - SHIFT[1]:pad - SHIFT[1] + h, pad - SHIFT[0]:pad - SHIFT[0] + w].astype(np.int32)
+    nz = (pkg.synth.splitmix64(seed ^ 0xABCD, 0, w * h) % np.uint64(7)).astype(np.int32).reshape(h, w) - 3
+    f2 = np.clip(f2 + nz, 0, 255).astype(np.uint8)
+    k1, d1 = extract(f1, nf)
+    k2, d2 = extract(f2, nf)
+    return (k1, d1), (k2, d2), (0.0, float(w), 0.0, float(h))
+
+
+def oracle_extract(oracle):
+    def run(img, nf):
+        return oracle.OraclePort(nf, 1.2, 8, 20, 7).extract(img)
+    return run
+
+
+def device_extract(pkg):
+    def run(img, nf):
+        return pkg.ORBextractor(nf, 1.2, 8, 20, 7)(img)
+    return run
+
+
+def projection_scene(pkg, oracle, F1, F2, bounds, motion, mono, seed=7):
+    """Last frame = F1 with map points at depth ~Z; current frame = F2 seen after a camera translation that moves the
+    projections by about SHIFT (plus `motion` along z for the forward / backward branches)."""
+    (k1, d1), (k2, d2) = F1, F2
+    rng = np.random.default_rng(seed)
+    fx, fy, cx, cy = 517.3, 516.5, 318.6, 255.3
+    bf, b = 40.0, 40.0 / fx
+    Z = 25.0
+    n1, n2 = len(k1), len(k2)
+    z = (Z + rng.uniform(-0.4, 0.4, n1)).astype(np.float32)
+    Tl = np.eye(4, dtype=np.float32)
+    Tl[:3, 3] = [0.3, -0.2, 0.1]
+    ang = 0.002
+    Tl[:3, :3] = np.array([[np.cos(ang), -np.sin(ang), 0], [np.sin(ang), np.cos(ang), 0], [0, 0, 1]], np.float32)
+    # points in the last camera, then in the world
+    pc = np.stack([(k1["x"] - cx) * z / fx, (k1["y"] - cy) * z / fy, z], 1).astype(np.float64)
+    Rl = Tl[:3, :3].astype(np.float64); tl = Tl[:3, 3].astype(np.float64)
+    pw = ((pc - tl) @ Rl).astype(np.float32)                  # Rl^T (pc - tl)
+    Tc = Tl.copy()
+    Tc[:3, 3] += np.array([SHIFT[0] * Z / fx, SHIFT[1] * Z / fy, motion], np.float32)
+    s4 = oracle.OraclePort(1000, 1.2, 8, 20, 7).tables()[0]
+    valid = (rng.random(n1) < 0.85).astype(np.uint8)
+    observed = (rng.random(n1) < 0.7).astype(np.uint8)
+    occupied = (rng.random(n2) < 0.05).astype(np.uint8)
+    ur = np.where(rng.random(n2) < 0.6, k2["x"] - bf / Z + rng.normal(0, 3.0, n2), -1.0).astype(np.float32)
+    if mono:
+        ur[:] = -1.0
+    args, keep = pkg.projection_args(pw, d1, valid, observed, k1["octave"], k1["angle"], Tl, k2, d2, ur, occupied, Tc,
+                                     (fx, fy, cx, cy), bf, b, bounds, s4[0], 15.0 if mono else 7.0, mono)
+    return args, keep
+
+
+# ---------------------------------------------------------------------------------------------------------- CPU: oracle
+def test_oracle_features_in_area_equals_window_scan_as_a_set(pkg, oracle):
+    (k1, d1), _, bounds = two_frames(pkg, oracle_extract(oracle))
+    po = oracle.OraclePort()
+    rng = np.random.default_rng(1)
+    for _ in range(60):
+        x, y = float(rng.uniform(-20, 660)), float(rng.uniform(-20, 500))
+        r = float(rng.choice([7.0, 15.0, 43.2, 100.0]))
+        lo, hi = [(-1, -1), (0, 0), (1, 3), (2, -1), (0, 4)][int(rng.integers(5))]
+        got = po.features_in_area(k1, bounds, x, y, r, lo, hi)
+        inside = (np.abs(k1["x"] - np.float32(x)) < r) & (np.abs(k1["y"] - np.float32(y)) < r)
+        if lo > 0 or hi >= 0:
+            inside &= k1["octave"] >= lo
+            if hi >= 0:
+                inside &= k1["octave"] <= hi
+        # the grid only bounds the scan; every keypoint of the open window is returned (a window may not reach
+        # past the cells it touches, so the result is exactly the window content)
+        assert sorted(got.tolist()) == np.nonzero(inside)[0].tolist()
+        assert len(set(got.tolist())) == len(got)
+
+
+def test_oracle_initialization_matches_follow_the_shift(pkg, oracle):
+    (k1, d1), (k2, d2), bounds = two_frames(pkg, oracle_extract(oracle))
+    po = oracle.OraclePort()
+    pm0 = np.stack([k1["x"], k1["y"]], 1)
+    nm, m12, pm = po.search_for_initialization(k1, d1, k2, d2, bounds, pm0)
+    ok = m12 >= 0
+    assert nm == ok.sum() and nm > 60
+    assert (k1["octave"][ok] == 0).all() and (k2["octave"][m12[ok]] == 0).all()
+    assert len(set(m12[ok].tolist())) == ok.sum()             # vnMatches21 keeps matches one-to-one
+    dx = k2["x"][m12[ok]] - k1["x"][ok]; dy = k2["y"][m12[ok]] - k1["y"][ok]
+    assert (np.abs(dx - SHIFT[0]) < 2).mean() > 0.9 and (np.abs(dy - SHIFT[1]) < 2).mean() > 0.9
+    assert np.array_equal(pm[ok], np.stack([k2["x"][m12[ok]], k2["y"][m12[ok]]], 1)) and np.array_equal(pm[~ok], pm0[~ok])
+
+
+def test_oracle_projection_matches_follow_the_motion(pkg, oracle):
+    F1, F2, bounds = two_frames(pkg, oracle_extract(oracle))
+    po = oracle.OraclePort()
+    for motion, mono in [(0.0, True), (0.0, False), (0.5, False), (-0.5, False)]:
+        args, keep = projection_scene(pkg, oracle, F1, F2, bounds, motion, mono)
+        nm, cm = po.search_by_projection(args)
+        got = cm >= 0
+        assert got.sum() > 150 and nm >= got.sum() - 5
+        assert not (got & (keep["cur_occupied"] > 0)).any()   # occupied features are never taken
+        assert keep["mp_valid"][cm[got]].all()
+        k1, k2 = F1[0], F2[0]
+        dx = k2["x"][got] - k1["x"][cm[got]]; dy = k2["y"][got] - k1["y"][cm[got]]
+        assert (np.abs(dx - SHIFT[0]) < 3).mean() > 0.85 and (np.abs(dy - SHIFT[1]) < 3).mean() > 0.85
+
+
+# ------------------------------------------------------------------------------------------------- GPU: device == oracle
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [(640, 480, 1000, 100, 0.9, True), (640, 480, 2000, 100, 0.9, True), (752, 480, 1000, 30, 0.6, False),
+                                 (333, 217, 700, 100, 0.9, True)])
+def test_device_search_for_initialization_equals_oracle(pkg, oracle, cfg):
+    w, h, nf, win, ratio, ori = cfg
+    (k1, d1), (k2, d2), bounds = two_frames(pkg, device_extract(pkg), w, h, 0x2F2A3E + nf, nf)
+    po = oracle.OraclePort()
+    pm = np.stack([k1["x"], k1["y"]], 1)
+    for _ in range(2):                                        # second round starts from the updated vbPrevMatched
+        onm, om12, opm = po.search_for_initialization(k1, d1, k2, d2, bounds, pm, win, ratio, ori)
+        nm, m12, npm = pkg.search_for_initialization(k1, d1, k2, d2, bounds, pm, win, ratio, ori)
+        assert nm == onm and np.array_equal(m12, om12) and npm.tobytes() == opm.tobytes()
+        pm = npm
+    assert nm > 30
+
+
+@pytest.mark.gpu
+def test_device_search_for_initialization_with_duplicates_steals_like_the_reference(pkg, oracle):
+    """Many identical descriptors in F1 competing for the same F2 feature: exercises vMatchedDistance / vnMatches21."""
+    (k1, d1), (k2, d2), bounds = two_frames(pkg, device_extract(pkg))
+    rng = np.random.default_rng(9)
+    lvl0 = np.nonzero(k1["octave"] == 0)[0]
+    d1 = d1.copy(); k1 = k1.copy()
+    for i in lvl0[::3]:                                        # every third level-0 keypoint becomes a near copy of a neighbour
+        j = lvl0[int(rng.integers(len(lvl0)))]
+        d1[i] = d1[j]; d1[i, int(rng.integers(32))] ^= np.uint8(1 << int(rng.integers(8)))
+        k1["x"][i] = k1["x"][j] + np.float32(rng.integers(-3, 4)); k1["y"][i] = k1["y"][j]
+    pm = np.stack([k1["x"], k1["y"]], 1)
+    po = oracle.OraclePort()
+    for ori in (True, False):
+        onm, om12, opm = po.search_for_initialization(k1, d1, k2, d2, bounds, pm, 100, 0.9, ori)
+        nm, m12, npm = pkg.search_for_initialization(k1, d1, k2, d2, bounds, pm, 100, 0.9, ori)
+        assert nm == onm and np.array_equal(m12, om12) and npm.tobytes() == opm.tobytes()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [(0.0, True), (0.0, False), (0.5, False), (-0.5, False)], ids=["mono", "stereo", "forward", "backward"])
+def test_device_search_by_projection_equals_oracle(pkg, oracle, case):
+    motion, mono = case
+    F1, F2, bounds = two_frames(pkg, device_extract(pkg))
+    po = oracle.OraclePort()
+    for seed in (7, 8):
+        args, keep = projection_scene(pkg, oracle, F1, F2, bounds, motion, mono, seed)
+        onm, ocm = po.search_by_projection(args)
+        nm, cm = pkg.search_by_projection(args)
+        assert nm == onm and np.array_equal(cm, ocm)
+        args.check_orientation = 0
+        onm, ocm = po.search_by_projection(args)
+        nm, cm = pkg.search_by_projection(args)
+        assert nm == onm and np.array_equal(cm, ocm)
+    assert (cm >= 0).sum() > 150
+
+
+@pytest.mark.gpu
+def test_device_search_edge_cases(pkg, oracle):
+    (k1, d1), (k2, d2), bounds = two_frames(pkg, device_extract(pkg), 333, 217, 5, 500)
+    pm = np.stack([k1["x"], k1["y"]], 1)
+    nm, m12, _ = pkg.search_for_initialization(k1, d1, k2[:0], d2[:0], bounds, pm)          # empty F2
+    assert nm == 0 and (m12 == -1).all()
+    nm, m12, _ = pkg.search_for_initialization(k1[:0], d1[:0], k2, d2, bounds, pm[:0])      # empty F1
+    assert nm == 0 and len(m12) == 0
+    far = pm + np.float32(5000)                                                            # windows outside the grid
+    nm, m12, _ = pkg.search_for_initialization(k1, d1, k2, d2, bounds, far)
+    onm, om12, _ = oracle.OraclePort().search_for_initialization(k1, d1, k2, d2, bounds, far)
+    assert nm == onm == 0 and np.array_equal(m12, om12)
+    with pytest.raises(RuntimeError):
+        pkg.search_for_initialization(k1, d1, k2, d2, (0, 0, 0, 217), pm)                  # degenerate bounds
