@@ -368,11 +368,12 @@ def run_ours(args, rank, world, local_rank):
     wall_e2e_ms = (time.perf_counter() - t0) * 1e3
     # the same through the synchronous call (pipeline fills and drains every step)
     barrier()
+    t0 = time.perf_counter()
     sync_ms = 0.0
     for _ in range(args.steps):
         sync_ms += step_host()
     barrier()
-    sync_ms = max_over_ranks(sync_ms)
+    sync_ms = max(max_over_ranks(sync_ms), max_over_ranks((time.perf_counter() - t0) * 1e3))   # slower of events and wall
     clocks = sampler.stop()
     e2e_ms = max_over_ranks(e2e_ms)
     wall_e2e_ms = max_over_ranks(wall_e2e_ms)
@@ -403,7 +404,11 @@ def run_ours(args, rank, world, local_rank):
 
     total_frames = n * world * args.steps
     value = total_frames / (dev_ms * 1e-3)
-    e2e_value = total_frames / (max(e2e_ms, wall_e2e_ms) * 1e-3)      # the slower of device events and host wall clock
+    async_value = total_frames / (max(e2e_ms, wall_e2e_ms) * 1e-3)    # the slower of device events and host wall clock
+    sync_value = total_frames / (sync_ms * 1e-3)
+    # both are complete end-to-end runs of the same work through a public entry point; the line reports the better one
+    # (with few host threads per GPU the one-call-per-step form can win) and names it
+    e2e_value = max(async_value, sync_value)
 
     if rank != 0:
         if world > 1:
@@ -463,8 +468,9 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * w * h * world,
                 "d2h_bytes_per_step": (n * cap * 60 + 4 * n) * world,
                 "ms_per_step_events": e2e_ms / args.steps, "ms_per_step_wall": wall_e2e_ms / args.steps,
-                "api": "orbgpu_extract_batch_async x steps + orbgpu_wait (pinned host buffers)",
-                "synchronous_call_value": total_frames / (sync_ms * 1e-3)},
+                "api": ("orbgpu_extract_batch_async x steps + orbgpu_wait" if async_value >= sync_value
+                        else "orbgpu_extract_batch, one synchronous call per step") + " (pinned host buffers)",
+                "async_api_value": async_value, "synchronous_call_value": sync_value},
         "gpu_launches": int(total_launches),
         "wall_ms_per_step": wall_dev_ms / args.steps,
         "roofline": roofline,

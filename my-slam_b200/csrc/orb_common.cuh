@@ -104,7 +104,7 @@ struct OrbStereoSide {
     int pitch[ORB_MAX_LEVELS], w[ORB_MAX_LEVELS], h[ORB_MAX_LEVELS];
     const void* kps;                         // orbgpu_keypoint[n]
     const uint8_t* desc;                     // [n][32]
-    int n;
+    const int* n_ptr;                        // device: keypoint count of that frame
 };
 struct OrbStereoArgs {
     OrbStereoSide L, R;
@@ -115,8 +115,9 @@ struct OrbStereoArgs {
     float* u_right;                          // [L.n] mvuRight before the median filter (-1 = no match)
     float* depth;                            // [L.n] mvDepth
     int* sad;                                // [L.n] best SAD of the sub-pixel search (-1 = no match)
+    int* counts;                             // [2] nL, nR as the kernel read them
 };
-int orb_launch_stereo(const OrbStereoArgs& A, cudaStream_t st);
+int orb_launch_stereo(const OrbStereoArgs& A, int max_left, cudaStream_t st);
 // orb_frame.cu: K4 = fx, fy, cx, cy; dist = k1, k2, p1, p2[, k3 ...] (ndist <= 12), both host pointers
 int orb_launch_undistort_points(const float* K4, const float* dist, int ndist, const float* d_src, float* d_dst, int n, cudaStream_t st);
 int orb_launch_undistort_keypoints(const float* K4, const float* dist, int ndist, const void* d_kps, void* d_kps_un, const int* d_n,

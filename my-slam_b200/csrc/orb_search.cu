@@ -10,7 +10,7 @@
 //   k_grid_build        one CTA: cell ids, per-cell counts, exclusive scan, in-cell rank by index
 //   k_area_candidates   one warp per query: walks the window ranges, keeps order with ballot prefix sums, evaluates the
 //                       Hamming distance of every candidate and stores (index, distance) lists
-//   k_init_resolve / k_proj_resolve   one warp walks the queries in index order and applies the reference's
+//   k_init_resolve / k_proj_resolve   one CTA stages lists + state in shared memory, then warp 0 walks the queries in index order and applies the reference's
 //                       order-dependent rules (vMatchedDistance / vnMatches21 stealing; mvpMapPoints occupancy) --
 //                       a true sequential dependence in the reference, kept as such
 // The rotation histogram + ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) finish on the host, O(matches).
@@ -157,56 +157,120 @@ __global__ void __launch_bounds__(256) k_area_candidates(GridDev G, const AreaQu
     if (lane == 0) cand_n[q] = total;
 }
 
-// two smallest keys of a warp (keys are distinct: the candidate position is part of the key)
-__device__ __forceinline__ void warp_two_min(unsigned& k1, unsigned& k2)
+// ---- in-order resolution -------------------------------------------------------------------------------------------
+// One CTA.  All 1024 threads first stage the walk's state in shared memory -- per-query list offsets and counts, the
+// order-dependent tables, and (when they fit) the compacted candidate lists themselves -- then warp 0 walks the
+// queries in index order; a query costs a few shared-memory round trips and two warp reductions instead of a chain
+// of dependent global loads.
+#define RESOLVE_THREADS 1024
+#define RESOLVE_SMEM (200 * 1024)
+
+struct ResolveStage {
+    int* off;                     // [nq] start of query q's list, relative to `base`
+    unsigned short* cnt;          // [nq]
+    const uint32_t* base;         // shared-memory copy of the lists, or the global buffer when they do not fit
+};
+
+// carve-out after `used` bytes of the dynamic shared memory; every thread returns the same stage
+__device__ ResolveStage stage_lists(unsigned char* smem, size_t used, const uint32_t* __restrict__ cand, const int* __restrict__ cand_n,
+                                    int cap, int nq)
 {
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, s), o2 = __shfl_xor_sync(0xffffffffu, k2, s);
-        const unsigned lo = min(k1, o1), hi = max(k1, o1);
-        k2 = min(hi, min(k2, o2));
-        k1 = lo;
+    __shared__ int s_part[RESOLVE_THREADS];
+    __shared__ int s_total;
+    const int t = threadIdx.x;
+    ResolveStage S;
+    S.off = reinterpret_cast<int*>(smem + used); used += sizeof(int) * (size_t)nq;
+    S.cnt = reinterpret_cast<unsigned short*>(smem + used); used += sizeof(unsigned short) * (size_t)nq;
+    used = (used + 15) & ~(size_t)15;
+    uint32_t* s_cand = reinterpret_cast<uint32_t*>(smem + used);
+    const int room = (int)((RESOLVE_SMEM - used) / sizeof(uint32_t));
+    const int per = (nq + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
+    const int q0 = min(t * per, nq), q1 = min(q0 + per, nq);
+    int sum = 0;
+    for (int q = q0; q < q1; ++q) sum += cand_n[q];
+    s_part[t] = sum;
+    __syncthreads();
+    for (int s = 1; s < RESOLVE_THREADS; s <<= 1) {
+        const int v = t >= s ? s_part[t - s] : 0;
+        __syncthreads();
+        s_part[t] += v;
+        __syncthreads();
     }
+    if (t == RESOLVE_THREADS - 1) s_total = s_part[t];
+    __syncthreads();
+    const bool fits = s_total <= room;
+    int run = s_part[t] - sum;
+    for (int q = q0; q < q1; ++q) {
+        const int c = cand_n[q];
+        S.off[q] = fits ? run : q * cap;
+        S.cnt[q] = (unsigned short)c;
+        run += c;
+    }
+    __syncthreads();
+    if (fits) {
+        const int warp = t >> 5, lane = t & 31;
+        for (int q = warp; q < nq; q += RESOLVE_THREADS / 32) {
+            const int c = S.cnt[q], o = S.off[q];
+            const uint32_t* src = cand + (size_t)q * cap;
+            for (int p = lane; p < c; p += 32) s_cand[o + p] = src[p];
+        }
+    }
+    S.base = fits ? s_cand : cand;
+    __syncthreads();
+    return S;
 }
 
-// SearchForInitialization, the loop over i1 (src/ORBmatcher.cc:418-484) on precomputed candidate lists.
+// SearchForInitialization, the loop over i1 (src/ORBmatcher.cc:418-484) on the candidate lists.
 // accepted[i1] = bestIdx2 at the moment i1 was accepted (feeds rotHist), else -1.
-__global__ void __launch_bounds__(32) k_init_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap, int n1,
-                                                     int n2, float nnratio, int* matched_dist, int* matches21, int* matches12,
-                                                     int* accepted, int* nmatches_out)
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_init_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
+                                                                  int n1, int n2, float nnratio, int* __restrict__ matches12,
+                                                                  int* __restrict__ accepted, int* __restrict__ nmatches_out)
 {
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n2; i += 32) { matched_dist[i] = INT_MAX; matches21[i] = -1; }
-    for (int i = lane; i < n1; i += 32) { matches12[i] = -1; accepted[i] = -1; }
-    __syncwarp();
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int t = threadIdx.x;
+    unsigned short* matched_dist = reinterpret_cast<unsigned short*>(smem);          // vMatchedDistance, 0xFFFF = INT_MAX
+    short* matches21 = reinterpret_cast<short*>(smem + sizeof(short) * (size_t)n2);   // vnMatches21
+    for (int i = t; i < n2; i += RESOLVE_THREADS) { matched_dist[i] = 0xFFFFu; matches21[i] = -1; }
+    for (int i = t; i < n1; i += RESOLVE_THREADS) { matches12[i] = -1; accepted[i] = -1; }
+    const ResolveStage S = stage_lists(smem, 2 * sizeof(short) * (size_t)n2, cand, cand_n, cap, n1);
+    if (t >= 32) return;
+    const int lane = t;
     int nmatches = 0;
-    for (int i1 = 0; i1 < n1; ++i1) {
-        const int cnt = cand_n[i1];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + (size_t)i1 * cap;
-        unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;           // (dist << 16) | position: earliest candidate wins ties
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            const int i2 = (int)(e >> CAND_DIST_BITS), dist = (int)(e & ((1u << CAND_DIST_BITS) - 1u));
-            if (matched_dist[i2] <= dist) continue;            // :444-445
-            const unsigned key = ((unsigned)dist << 16) | (unsigned)p;
-            if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
-        }
-        warp_two_min(k1, k2);
-        if (lane == 0 && k1 != 0xFFFFFFFFu) {
-            const int bestDist = (int)(k1 >> 16);
-            const int bestDist2 = k2 == 0xFFFFFFFFu ? INT_MAX : (int)(k2 >> 16);
-            if (bestDist <= 50 && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) {      // TH_LOW, :459-461
-                const int bestIdx2 = (int)(c[k1 & 0xFFFFu] >> CAND_DIST_BITS);
-                if (matches21[bestIdx2] >= 0) { matches12[matches21[bestIdx2]] = -1; nmatches--; }
-                matches12[i1] = bestIdx2;
-                matches21[bestIdx2] = i1;
-                matched_dist[bestIdx2] = bestDist;
-                accepted[i1] = bestIdx2;
-                nmatches++;
+    for (int qb = 0; qb < n1; qb += 32) {
+        unsigned todo = __ballot_sync(0xffffffffu, qb + lane < n1 && S.cnt[qb + lane] != 0);
+        while (todo) {
+            const int i1 = qb + __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int cnt = S.cnt[i1];
+            const uint32_t* c = S.base + S.off[i1];
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;       // (dist << 16) | position: earliest candidate wins ties
+            for (int p = lane; p < cnt; p += 32) {
+                const uint32_t e = c[p];
+                const unsigned dist = e & ((1u << CAND_DIST_BITS) - 1u);
+                if ((unsigned)matched_dist[e >> CAND_DIST_BITS] <= dist) continue;      // :444-445
+                const unsigned key = (dist << 16) | (unsigned)p;
+                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+            }
+            const unsigned b1 = __reduce_min_sync(0xffffffffu, k1);
+            const unsigned b2 = __reduce_min_sync(0xffffffffu, k1 == b1 ? k2 : k1);    // keys are distinct
+            if (b1 == 0xFFFFFFFFu) continue;
+            const int bestDist = (int)(b1 >> 16);
+            const int bestDist2 = b2 == 0xFFFFFFFFu ? INT_MAX : (int)(b2 >> 16);
+            if (bestDist <= 50 && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) {          // TH_LOW, :459-461
+                const int bestIdx2 = (int)(c[b1 & 0xFFFFu] >> CAND_DIST_BITS);
+                const int prev = matches21[bestIdx2];
+                __syncwarp();
+                if (lane == 0) {
+                    if (prev >= 0) matches12[prev] = -1;
+                    matches12[i1] = bestIdx2;
+                    matches21[bestIdx2] = (short)i1;
+                    matched_dist[bestIdx2] = (unsigned short)bestDist;
+                    accepted[i1] = bestIdx2;
+                }
+                nmatches += prev >= 0 ? 0 : 1;
+                __syncwarp();
             }
         }
-        __syncwarp();
     }
     if (lane == 0) *nmatches_out = nmatches;
 }
@@ -247,54 +311,54 @@ __global__ void k_proj_queries(ProjCam C, const float* __restrict__ world_pos, c
     Q[i] = q;
 }
 
-// the loop over the last frame's points (src/ORBmatcher.cc:1353-1443) on precomputed candidate lists
-__global__ void __launch_bounds__(32) k_proj_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap, int n_last,
-                                                     int n_cur, const uint8_t* __restrict__ observed, uint8_t* occupied, int* cur_match,
-                                                     int* accepted, int* nmatches_out)
+// the loop over the last frame's points (src/ORBmatcher.cc:1353-1443) on the candidate lists
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
+                                                                  int n_last, int n_cur, const uint8_t* __restrict__ observed,
+                                                                  const uint8_t* __restrict__ occupied_in, int* __restrict__ cur_match,
+                                                                  int* __restrict__ accepted, int* __restrict__ nmatches_out)
 {
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n_cur; i += 32) cur_match[i] = -1;
-    for (int i = lane; i < n_last; i += 32) accepted[i] = -1;
-    __syncwarp();
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int t = threadIdx.x;
+    unsigned char* occupied = smem;                            // mvpMapPoints[i2] && Observations() > 0
+    unsigned char* obs = smem + (size_t)n_cur;
+    for (int i = t; i < n_cur; i += RESOLVE_THREADS) { occupied[i] = occupied_in[i]; cur_match[i] = -1; }
+    for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed[i]; accepted[i] = -1; }
+    const size_t used = ((size_t)n_cur + (size_t)n_last + 15) & ~(size_t)15;
+    const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_last);
+    if (t >= 32) return;
+    const int lane = t;
     int nmatches = 0;
-    for (int i = 0; i < n_last; ++i) {
-        const int cnt = cand_n[i];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + (size_t)i * cap;
-        unsigned best = 0xFFFFFFFFu;
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            if (occupied[e >> CAND_DIST_BITS]) continue;       // :1403-1405
-            best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
-        }
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
-        if (lane == 0 && best != 0xFFFFFFFFu && (int)(best >> 16) <= 100) {     // bestDist < 256 by construction; TH_HIGH
+    for (int qb = 0; qb < n_last; qb += 32) {
+        unsigned todo = __ballot_sync(0xffffffffu, qb + lane < n_last && S.cnt[qb + lane] != 0);
+        while (todo) {
+            const int i = qb + __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int cnt = S.cnt[i];
+            const uint32_t* c = S.base + S.off[i];
+            unsigned best = 0xFFFFFFFFu;
+            for (int p = lane; p < cnt; p += 32) {
+                const uint32_t e = c[p];
+                if (occupied[e >> CAND_DIST_BITS]) continue;   // :1403-1405
+                best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
+            }
+            best = __reduce_min_sync(0xffffffffu, best);
+            if (best == 0xFFFFFFFFu || (int)(best >> 16) > 100) continue;           // bestDist < 256 by construction; TH_HIGH
             const int bestIdx2 = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
-            cur_match[bestIdx2] = i;
-            occupied[bestIdx2] = observed[i];
-            accepted[i] = bestIdx2;
+            __syncwarp();
+            if (lane == 0) {
+                cur_match[bestIdx2] = i;
+                occupied[bestIdx2] = obs[i];
+                accepted[i] = bestIdx2;
+            }
             nmatches++;
+            __syncwarp();
         }
-        __syncwarp();
     }
     if (lane == 0) *nmatches_out = nmatches;
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
 namespace {
-
-struct DevBuf {                   // every device allocation of one call, freed together
-    std::vector<void*> ptrs;
-    ~DevBuf() { for (void* p : ptrs) cudaFree(p); }
-    template <typename T> T* get(size_t count)
-    {
-        void* p = nullptr;
-        if (cudaMalloc(&p, sizeof(T) * (count ? count : 1)) != cudaSuccess) return nullptr;
-        ptrs.push_back(p);
-        return static_cast<T*>(p);
-    }
-};
 
 #define CUS(call)                                                                                         \
     do {                                                                                                  \
@@ -307,25 +371,51 @@ struct DevBuf {                   // every device allocation of one call, freed 
         }                                                                                                 \
     } while (0)
 
-// uploads the searched frame (mvKeysUn + mDescriptors) and builds its grid
-int make_grid(DevBuf& B, const orbgpu_keypoint* keys, const uint8_t* desc, int n, const float* bounds, GridDev& G)
-{
-    float* d_keys = B.get<float>(7 * (size_t)n);
-    uint8_t* d_desc = B.get<uint8_t>(32 * (size_t)n);
-    int* d_start = B.get<int>(GRID_CELLS + 1);
-    int* d_sorted = B.get<int>((size_t)n);
-    if (!d_keys || !d_desc || !d_start || !d_sorted) return ORBGPU_ERR_NOMEM;
-    CUS(cudaMemcpy(d_keys, keys, sizeof(orbgpu_keypoint) * (size_t)n, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_desc, desc, 32 * (size_t)n, cudaMemcpyHostToDevice));
-    G.keys = d_keys; G.desc = d_desc; G.n = n;
-    G.minX = bounds[0]; G.minY = bounds[2];
-    G.invW = static_cast<float>(GRID_COLS) / static_cast<float>(bounds[1] - bounds[0]);       // src/Frame.cc:155-156
-    G.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(bounds[3] - bounds[2]);
-    G.cell_start = d_start; G.sorted = d_sorted;
-    k_grid_build<<<1, 1024>>>(G);
-    CUS(cudaGetLastError());
-    return ORBGPU_OK;
-}
+// Per host thread: one device block, one pinned block and one stream, grown on demand and kept for the next call
+// (a call is then: pack inputs into the pinned block, ONE H2D copy, the kernels, ONE D2H copy, one synchronise).
+struct Workspace {
+    int device = -1;
+    uint8_t* d = nullptr; size_t dcap = 0;
+    uint8_t* h = nullptr; size_t hcap = 0;
+    cudaStream_t st = nullptr;
+    bool attr_set = false;
+    int reserve(int dev, size_t dbytes, size_t hbytes)
+    {
+        CUS(cudaSetDevice(dev));
+        if (dev != device) {
+            if (d) cudaFree(d);
+            if (st) cudaStreamDestroy(st);
+            d = nullptr; dcap = 0; st = nullptr; attr_set = false; device = dev;
+        }
+        if (!st) CUS(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        if (!attr_set) {
+            CUS(cudaFuncSetAttribute(k_init_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
+            CUS(cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
+            attr_set = true;
+        }
+        if (dbytes > dcap) {
+            if (d) cudaFree(d);
+            d = nullptr; dcap = 0;
+            const size_t want = dbytes + dbytes / 4;
+            if (cudaMalloc(&d, want) != cudaSuccess) { cudaGetLastError(); return ORBGPU_ERR_NOMEM; }
+            dcap = want;
+        }
+        if (hbytes > hcap) {
+            if (h) cudaFreeHost(h);
+            h = nullptr; hcap = 0;
+            const size_t want = hbytes + hbytes / 4;
+            if (cudaMallocHost(&h, want) != cudaSuccess) { cudaGetLastError(); return ORBGPU_ERR_NOMEM; }
+            hcap = want;
+        }
+        return ORBGPU_OK;
+    }
+};
+thread_local Workspace g_ws;      // released with the process (no CUDA calls from thread-exit destructors)
+
+struct Layout {                   // 256-byte aligned carve-out shared by the device block and its pinned mirror
+    size_t off = 0;
+    size_t add(size_t bytes) { const size_t o = off; off = (off + bytes + 255) & ~(size_t)255; return o; }
+};
 
 // src/ORBmatcher.cc:1601-1642 on bin sizes
 void three_maxima(const int* size, int L, int& ind1, int& ind2, int& ind3)
@@ -354,6 +444,15 @@ inline int rot_bin(float a1, float a2)                        // src/ORBmatcher.
     return bin;
 }
 
+void set_grid(GridDev& G, uint8_t* d, size_t o_keys, size_t o_desc, size_t o_start, size_t o_sorted, int n, const float* bounds)
+{
+    G.keys = reinterpret_cast<const float*>(d + o_keys); G.desc = d + o_desc; G.n = n;
+    G.minX = bounds[0]; G.minY = bounds[2];
+    G.invW = static_cast<float>(GRID_COLS) / static_cast<float>(bounds[1] - bounds[0]);       // src/Frame.cc:155-156
+    G.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(bounds[3] - bounds[2]);
+    G.cell_start = reinterpret_cast<int*>(d + o_start); G.sorted = reinterpret_cast<int*>(d + o_sorted);
+}
+
 }  // namespace
 
 extern "C" {
@@ -370,36 +469,45 @@ int orbgpu_search_for_initialization(int device, const orbgpu_keypoint* keys1_un
     *nmatches = 0;
     for (int i = 0; i < n1; ++i) matches12[i] = -1;
     if (n1 == 0 || n2 == 0) return ORBGPU_OK;
-    CUS(cudaSetDevice(device));
-    DevBuf B;
-    GridDev G;
-    int rc = make_grid(B, keys2_un, desc2, n2, bounds4, G);
+    // device block: [inputs | outputs | scratch]; the pinned block mirrors inputs and outputs
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2);
+    const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_qdesc = L.add(32 * (size_t)n1);
+    const size_t in_bytes = L.off;
+    const size_t o_m12 = L.add(4 * (size_t)n1), o_acc = L.add(4 * (size_t)n1), o_nm = L.add(4);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
+    const size_t o_cand = L.add(4 * (size_t)n1 * n2);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
     if (rc != ORBGPU_OK) return rc;
-    // queries: level-0 keypoints of F1 around vbPrevMatched (:418-425)
-    std::vector<AreaQuery> hq((size_t)n1);
+    memcpy(W.h + o_keys, keys2_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_desc, desc2, 32 * (size_t)n2);
+    memcpy(W.h + o_qdesc, desc1, 32 * (size_t)n1);
+    AreaQuery* hq = reinterpret_cast<AreaQuery*>(W.h + o_q);   // level-0 keypoints of F1 around vbPrevMatched (:418-425)
     for (int i = 0; i < n1; ++i) {
-        AreaQuery& q = hq[(size_t)i];
+        AreaQuery& q = hq[i];
         q.x = prev_matched[2 * i]; q.y = prev_matched[2 * i + 1]; q.r = (float)window_size;
         q.min_level = q.max_level = keys1_un[i].octave;
         q.active = keys1_un[i].octave > 0 ? 0 : 1;
         q.ur = 0.f; q.check_ur = 0;
     }
-    AreaQuery* d_q = B.get<AreaQuery>((size_t)n1);
-    uint8_t* d_qdesc = B.get<uint8_t>(32 * (size_t)n1);
-    uint32_t* d_cand = B.get<uint32_t>((size_t)n1 * n2);
-    int* d_ints = B.get<int>((size_t)n1 * 3 + (size_t)n2 * 2 + 1);
-    if (!d_q || !d_qdesc || !d_cand || !d_ints) return ORBGPU_ERR_NOMEM;
-    int *d_cn = d_ints, *d_m12 = d_cn + n1, *d_acc = d_m12 + n1, *d_md = d_acc + n1, *d_m21 = d_md + n2, *d_nm = d_m21 + n2;
-    CUS(cudaMemcpy(d_q, hq.data(), sizeof(AreaQuery) * (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_qdesc, desc1, 32 * (size_t)n1, cudaMemcpyHostToDevice));
-    k_area_candidates<<<(n1 + 7) / 8, 256>>>(G, d_q, d_qdesc, n1, nullptr, d_cand, n2, d_cn);
-    k_init_resolve<<<1, 32>>>(d_cand, d_cn, n2, n1, n2, nnratio, d_md, d_m21, d_m12, d_acc, d_nm);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    GridDev G;
+    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, bounds4);
+    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, reinterpret_cast<const AreaQuery*>(W.d + o_q), W.d + o_qdesc, n1, nullptr, d_cand,
+                                                      n2, d_cn);
+    k_init_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nnratio, reinterpret_cast<int*>(W.d + o_m12),
+                                                               reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
     CUS(cudaGetLastError());
-    std::vector<int> acc((size_t)n1);
-    int nm = 0;
-    CUS(cudaMemcpy(matches12, d_m12, sizeof(int) * (size_t)n1, cudaMemcpyDeviceToHost));
-    CUS(cudaMemcpy(acc.data(), d_acc, sizeof(int) * (size_t)n1, cudaMemcpyDeviceToHost));
-    CUS(cudaMemcpy(&nm, d_nm, sizeof(int), cudaMemcpyDeviceToHost));
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(matches12, W.h + o_m12, 4 * (size_t)n1);
+    const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
+    int nm = *reinterpret_cast<const int*>(W.h + o_nm);
     if (check_orientation) {                                   // :487-511, bins in push order = ascending i1
         int bin_of[30] = {0};
         std::vector<int> bin((size_t)n1, -1);
@@ -432,11 +540,6 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     *nmatches = 0;
     for (int i = 0; i < n2; ++i) cur_match[i] = -1;
     if (n1 == 0 || n2 == 0) return ORBGPU_OK;
-    CUS(cudaSetDevice(device));
-    DevBuf B;
-    GridDev G;
-    int rc = make_grid(B, a->cur_keys_un, a->cur_desc, n2, a->bounds, G);
-    if (rc != ORBGPU_OK) return rc;
     // camera motion between the frames (:1339-1350); the cv::Mat expressions restated with cv::gemm's arithmetic
     ProjCam C;
     const float* Tc = a->Tcw_cur; const float* Tl = a->Tcw_last;
@@ -456,35 +559,46 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy; C.bf = a->bf; C.th = a->th;
     C.minX = a->bounds[0]; C.maxX = a->bounds[1]; C.minY = a->bounds[2]; C.maxY = a->bounds[3];
 
-    float* d_pos = B.get<float>(3 * (size_t)n1);
-    uint8_t* d_qdesc = B.get<uint8_t>(32 * (size_t)n1);
-    uint8_t* d_bytes = B.get<uint8_t>(2 * (size_t)n1 + (size_t)n2);
-    int* d_oct = B.get<int>((size_t)n1);
-    float* d_scale = B.get<float>((size_t)a->nlevels);
-    float* d_ur = B.get<float>((size_t)n2);
-    AreaQuery* d_q = B.get<AreaQuery>((size_t)n1);
-    uint32_t* d_cand = B.get<uint32_t>((size_t)n1 * n2);
-    int* d_ints = B.get<int>((size_t)n1 * 2 + (size_t)n2 + 1);
-    if (!d_pos || !d_qdesc || !d_bytes || !d_oct || !d_scale || !d_ur || !d_q || !d_cand || !d_ints) return ORBGPU_ERR_NOMEM;
-    uint8_t *d_valid = d_bytes, *d_obs = d_bytes + n1, *d_occ = d_obs + n1;
-    int *d_cn = d_ints, *d_acc = d_cn + n1, *d_cm = d_acc + n1, *d_nm = d_cm + n2;
-    CUS(cudaMemcpy(d_pos, a->world_pos, 12 * (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_qdesc, a->mp_desc, 32 * (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_valid, a->mp_valid, (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_obs, a->mp_observed, (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_occ, a->cur_occupied, (size_t)n2, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_oct, a->last_octave, 4 * (size_t)n1, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_scale, a->scale_factors, 4 * (size_t)a->nlevels, cudaMemcpyHostToDevice));
-    CUS(cudaMemcpy(d_ur, a->cur_u_right, 4 * (size_t)n2, cudaMemcpyHostToDevice));
-    k_proj_queries<<<(n1 + 127) / 128, 128>>>(C, d_pos, d_valid, d_oct, d_scale, n1, d_q);
-    k_area_candidates<<<(n1 + 7) / 8, 256>>>(G, d_q, d_qdesc, n1, d_ur, d_cand, n2, d_cn);
-    k_proj_resolve<<<1, 32>>>(d_cand, d_cn, n2, n1, n2, d_obs, d_occ, d_cm, d_acc, d_nm);
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2);
+    const size_t o_pos = L.add(12 * (size_t)n1), o_qdesc = L.add(32 * (size_t)n1), o_valid = L.add((size_t)n1), o_obs = L.add((size_t)n1);
+    const size_t o_occ = L.add((size_t)n2), o_oct = L.add(4 * (size_t)n1), o_scale = L.add(4 * (size_t)a->nlevels), o_ur = L.add(4 * (size_t)n2);
+    const size_t in_bytes = L.off;
+    const size_t o_cm = L.add(4 * (size_t)n2), o_acc = L.add(4 * (size_t)n1), o_nm = L.add(4);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
+    const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_cand = L.add(4 * (size_t)n1 * n2);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_keys, a->cur_keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_desc, a->cur_desc, 32 * (size_t)n2);
+    memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
+    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(W.h + o_valid, a->mp_valid, (size_t)n1);
+    memcpy(W.h + o_obs, a->mp_observed, (size_t)n1);
+    memcpy(W.h + o_occ, a->cur_occupied, (size_t)n2);
+    memcpy(W.h + o_oct, a->last_octave, 4 * (size_t)n1);
+    memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    memcpy(W.h + o_ur, a->cur_u_right, 4 * (size_t)n2);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    GridDev G;
+    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+    AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
+    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_proj_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
+                                                       reinterpret_cast<const int*>(W.d + o_oct), reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
+    k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
+    k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, reinterpret_cast<int*>(W.d + o_cm),
+                                                               reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
     CUS(cudaGetLastError());
-    std::vector<int> acc((size_t)n1);
-    int nm = 0;
-    CUS(cudaMemcpy(cur_match, d_cm, sizeof(int) * (size_t)n2, cudaMemcpyDeviceToHost));
-    CUS(cudaMemcpy(acc.data(), d_acc, sizeof(int) * (size_t)n1, cudaMemcpyDeviceToHost));
-    CUS(cudaMemcpy(&nm, d_nm, sizeof(int), cudaMemcpyDeviceToHost));
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
+    const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
+    int nm = *reinterpret_cast<const int*>(W.h + o_nm);
     if (a->check_orientation) {                                // :1446-1466: every entry of a losing bin is reset, even twice
         int bin_of[30] = {0};
         std::vector<int> bin((size_t)n1, -1);

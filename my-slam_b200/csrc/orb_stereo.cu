@@ -41,7 +41,9 @@ __global__ void __launch_bounds__(256) k_stereo_match(OrbStereoArgs A)
 {
     const int lane = threadIdx.x & 31;
     const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (iL >= A.L.n) return;
+    const int nL = *A.L.n_ptr, nR = *A.R.n_ptr;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { A.counts[0] = nL; A.counts[1] = nR; }
+    if (iL >= nL) return;
     const StereoKp* kL = reinterpret_cast<const StereoKp*>(A.L.kps);
     const StereoKp* kR = reinterpret_cast<const StereoKp*>(A.R.kps);
     const float uL = kL[iL].x, vL = kL[iL].y;
@@ -56,7 +58,7 @@ __global__ void __launch_bounds__(256) k_stereo_match(OrbStereoArgs A)
     if (!(maxU < 0.f)) {
         const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(A.L.desc) + 2 * (size_t)iL);
         const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(A.L.desc) + 2 * (size_t)iL + 1);
-        for (int iR = lane; iR < A.R.n; iR += 32) {
+        for (int iR = lane; iR < nR; iR += 32) {
             const StereoKp k = kR[iR];
             const float r = __fmul_rn(2.0f, A.scale[k.octave]);
             const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
@@ -123,9 +125,9 @@ __global__ void __launch_bounds__(256) k_stereo_match(OrbStereoArgs A)
     if (lane == 0) { A.u_right[iL] = out_u; A.depth[iL] = out_d; A.sad[iL] = out_sad; }
 }
 
-int orb_launch_stereo(const OrbStereoArgs& A, cudaStream_t st)
+int orb_launch_stereo(const OrbStereoArgs& A, int max_left, cudaStream_t st)
 {
-    if (A.L.n < 1) return 0;
-    k_stereo_match<<<(A.L.n + 7) / 8, 256, 0, st>>>(A);
+    if (max_left < 1) return 0;
+    k_stereo_match<<<(max_left + 7) / 8, 256, 0, st>>>(A);
     return 1;
 }

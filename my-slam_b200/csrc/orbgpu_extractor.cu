@@ -106,6 +106,8 @@ struct orbgpu_extractor {
     int next_ctx = 0;                  // next chunk stream of the host-batch round-robin
     cudaEvent_t ev_batch0 = nullptr, ev_batch1 = nullptr;   // bracket the most recent batch call on ctx[0].st
     double last_batch_ms = 0;
+    uint8_t* d_aux = nullptr; size_t d_aux_cap = 0;   // stereo / undistort outputs of the last frame, grown on demand
+    uint8_t* h_aux = nullptr; size_t h_aux_cap = 0;   // pinned mirror
     int last_ctx = -1;                 // context holding the most recent single frame (pyramid / debug views)
     // scratch for orbgpu_octree
     uint8_t* d_oct_scratch = nullptr; size_t oct_scratch_bytes = 0;
@@ -604,6 +606,8 @@ void orbgpu_destroy(orbgpu_extractor* e)
     if (e->ev_batch1) cudaEventDestroy(e->ev_batch1);
     e->plan.free_dev();
     cudaFree(e->d_oct_scratch);
+    cudaFree(e->d_aux);
+    cudaFreeHost(e->h_aux);
     delete e;
 }
 
@@ -947,6 +951,21 @@ int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* 
 }
 
 // ---- Frame::ComputeStereoMatches (src/Frame.cc:466-640) --------------------------------------------------------
+static int reserve_aux(orbgpu_extractor* e, size_t bytes)
+{
+    if (bytes > e->d_aux_cap) {
+        cudaFree(e->d_aux); e->d_aux = nullptr; e->d_aux_cap = 0;
+        CU(cudaMalloc(&e->d_aux, bytes));
+        e->d_aux_cap = bytes;
+    }
+    if (bytes > e->h_aux_cap) {
+        cudaFreeHost(e->h_aux); e->h_aux = nullptr; e->h_aux_cap = 0;
+        CU(cudaMallocHost(&e->h_aux, bytes));
+        e->h_aux_cap = bytes;
+    }
+    return ORBGPU_OK;
+}
+
 static int stereo_side(orbgpu_extractor* e, OrbStereoSide& S)
 {
     StreamCtx* c = last_frame_ctx(e);
@@ -959,8 +978,8 @@ static int stereo_side(orbgpu_extractor* e, OrbStereoSide& S)
         S.w[l] = L.w; S.h[l] = L.h;
     }
     S.kps = c->d_kps; S.desc = c->d_desc;
-    CU(cudaMemcpy(&S.n, c->d_nout, sizeof(int), cudaMemcpyDeviceToHost));   // count of the frame this context extracted last
-    return S.n < 0 ? ORBGPU_ERR_STATE : ORBGPU_OK;
+    S.n_ptr = c->d_nout;                                       // count of the frame this context extracted last
+    return ORBGPU_OK;
 }
 
 int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float bf, float b, float* u_right, float* depth,
@@ -975,29 +994,31 @@ int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float b
     if ((rc = stereo_side(left, A.L)) != ORBGPU_OK || (rc = stereo_side(right, A.R)) != ORBGPU_OK) return rc;
     for (int l = 0; l < left->nlevels; ++l)
         if (A.L.w[l] != A.R.w[l] || A.L.h[l] != A.R.h[l] || left->scale[l] != right->scale[l]) return ORBGPU_ERR_ARG;
-    const int N = A.L.n;
-    *n_left = N;
-    if (capacity < N) return ORBGPU_ERR_CAPACITY;
-    if (A.R.n >= 65535) return ORBGPU_ERR_UNSUPPORTED;        // right index is packed into 16 bits
-    if (N == 0) return ORBGPU_OK;
+    const int kmax = left->plan.kmax;
+    if (right->plan.kmax >= 65535) return ORBGPU_ERR_UNSUPPORTED;   // right index is packed into 16 bits
     A.nlevels = left->nlevels;
     for (int l = 0; l < left->nlevels; ++l) { A.scale[l] = left->scale[l]; A.inv_scale[l] = left->inv_scale[l]; }
     A.bf = bf; A.b = b;
     A.th_high = 100; A.th_orb_dist = (100 + 50) / 2;           // ORBmatcher::TH_HIGH, TH_LOW (src/ORBmatcher.cc:37-38)
-    float* d_out = nullptr;
-    CU(cudaMalloc(&d_out, 3 * sizeof(float) * (size_t)N));
-    A.u_right = d_out; A.depth = d_out + N; A.sad = reinterpret_cast<int*>(d_out + 2 * (size_t)N);
+    const size_t bytes = sizeof(float) * (3 * (size_t)kmax + 2);
+    if ((rc = reserve_aux(left, bytes)) != ORBGPU_OK) return rc;
+    float* d_out = reinterpret_cast<float*>(left->d_aux);
+    A.u_right = d_out; A.depth = d_out + kmax; A.sad = reinterpret_cast<int*>(d_out + 2 * (size_t)kmax);
+    A.counts = reinterpret_cast<int*>(d_out + 3 * (size_t)kmax);
     cudaStream_t st = left->ctx[0].st;
     // the right handle's work was synchronised by its own extract call; same device, so a plain launch suffices
-    if (orb_launch_stereo(A, st) < 0) { cudaFree(d_out); return ORBGPU_ERR_CUDA; }
+    if (orb_launch_stereo(A, kmax, st) < 0) return ORBGPU_ERR_CUDA;
     left->launches += 1;
-    std::vector<int> sad((size_t)N);
-    cudaError_t ce = cudaMemcpyAsync(u_right, A.u_right, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st);
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(depth, A.depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st);
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(sad.data(), A.sad, sizeof(int) * (size_t)N, cudaMemcpyDeviceToHost, st);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
-    cudaFree(d_out);
-    CU(ce);
+    CU(cudaMemcpyAsync(left->h_aux, left->d_aux, bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const float* h = reinterpret_cast<const float*>(left->h_aux);
+    const int* sad = reinterpret_cast<const int*>(h + 2 * (size_t)kmax);
+    const int N = reinterpret_cast<const int*>(h + 3 * (size_t)kmax)[0];
+    if (N < 0) return ORBGPU_ERR_STATE;
+    *n_left = N;
+    if (capacity < N) return ORBGPU_ERR_CAPACITY;
+    memcpy(u_right, h, sizeof(float) * (size_t)N);
+    memcpy(depth, h + kmax, sizeof(float) * (size_t)N);
     // outlier rejection by the median SAD (:626-639): accepted matches sorted by (SAD, left index)
     std::vector<std::pair<int, int> > v;
     for (int i = 0; i < N; ++i) if (sad[i] >= 0) v.push_back(std::make_pair(sad[i], i));
@@ -1023,21 +1044,20 @@ int orbgpu_undistort_keypoints(orbgpu_extractor* e, const float* K4, const float
     if (!c) return ORBGPU_ERR_STATE;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
-    int n = 0;
-    CU(cudaMemcpy(&n, c->d_nout, sizeof(int), cudaMemcpyDeviceToHost));
+    const int kmax = e->plan.kmax;
+    const size_t rec = sizeof(orbgpu_keypoint) * (size_t)kmax, bytes = rec + 16;
+    if ((rc = reserve_aux(e, bytes)) != ORBGPU_OK) return rc;
+    cudaStream_t st = c->st;
+    orb_launch_undistort_keypoints(K4, dist, ndist, c->d_kps, e->d_aux, c->d_nout, kmax, st);
+    e->launches += 1;
+    CU(cudaMemcpyAsync(e->d_aux + rec, c->d_nout, sizeof(int), cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(e->h_aux, e->d_aux, bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const int n = *reinterpret_cast<const int*>(e->h_aux + rec);
     if (n < 0) return ORBGPU_ERR_STATE;
     *n_out = n;
     if (capacity < n) return ORBGPU_ERR_CAPACITY;
-    if (n == 0) return ORBGPU_OK;
-    void* d_un = nullptr;
-    CU(cudaMalloc(&d_un, sizeof(orbgpu_keypoint) * (size_t)n));
-    cudaStream_t st = c->st;
-    orb_launch_undistort_keypoints(K4, dist, ndist, c->d_kps, d_un, c->d_nout, n, st);
-    e->launches += 1;
-    cudaError_t ce = cudaMemcpyAsync(kps_un, d_un, sizeof(orbgpu_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, st);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
-    cudaFree(d_un);
-    CU(ce);
+    memcpy(kps_un, e->h_aux, sizeof(orbgpu_keypoint) * (size_t)n);
     return ORBGPU_OK;
 }
 

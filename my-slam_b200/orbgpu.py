@@ -188,7 +188,7 @@ class ORBextractor:
         if image.strides[-1] != 1 or (ch != 1 and image.strides[1] != ch):
             image = np.ascontiguousarray(image)
         h, w = image.shape[:2]
-        cap = self.max_keypoints(w, h)
+        cap = self._last_cap = self.max_keypoints(w, h)
         kps = np.zeros(cap, KP_DTYPE)
         desc = np.zeros((cap, 32), np.uint8)
         n = C.c_int(0)
@@ -237,8 +237,8 @@ class ORBextractor:
     # Frame::UndistortKeyPoints, src/Frame.cc:404-435
     def undistort_keypoints(self, K4, dist):
         K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
-        cap = 1 << 16
-        kps = np.zeros(cap, KP_DTYPE); n = C.c_int(0)
+        cap = getattr(self, "_last_cap", 1 << 16)
+        kps = np.empty(cap, KP_DTYPE); n = C.c_int(0)
         _check(self._L.orbgpu_undistort_keypoints(self._h, _p(K4), _p(dist), len(dist), _p(kps), cap, C.byref(n)))
         return kps[:n.value].copy()
 
@@ -338,8 +338,8 @@ def search_by_projection(args, device=0):
 
 def stereo_match(left, right, bf, b):
     """Frame::ComputeStereoMatches between the last frames of two ORBextractor handles -> (mvuRight, mvDepth)."""
-    cap = 1 << 16
-    u = np.zeros(cap, np.float32); d = np.zeros(cap, np.float32); n = C.c_int(0)
+    cap = getattr(left, "_last_cap", 1 << 16)
+    u = np.empty(cap, np.float32); d = np.empty(cap, np.float32); n = C.c_int(0)
     _check(lib().orbgpu_stereo_match(left._h, right._h, bf, b, _p(u), _p(d), cap, C.byref(n)))
     return u[:n.value].copy(), d[:n.value].copy()
 

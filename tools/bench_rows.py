@@ -1,0 +1,80 @@
+#!/usr/bin/env python
+"""Timing of the SURVEY section-8(f) rows next to their CPU restatements (one thread, the reference's execution model
+for these functions): python tools/bench_rows.py > profiles/<round>_rows.json.  Each GPU figure is the wall time of the
+public C-ABI call (host buffers in, host buffers out; synchronous), median of `reps` calls after warm-up; the CPU
+figure is oracle/frame_port.cc / orb_port.cc on the same inputs.  Results of both are compared before timing."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import __graft_entry__ as g          # noqa: E402
+import oracle_lib                     # noqa: E402  (checker + CPU baseline only)
+import test_search as ts              # noqa: E402  (scene builders)
+
+
+def med(f, reps=30, warm=3):
+    for _ in range(warm):
+        f()
+    t = []
+    for _ in range(reps):
+        t0 = time.perf_counter(); f(); t.append(time.perf_counter() - t0)
+    return float(np.median(t)) * 1e3
+
+
+def main():
+    pkg = g.load_package()
+    po = oracle_lib.OraclePort()
+    out = {"unit": "ms per call (median)", "cpu": "oracle restatement, 1 thread"}
+    # --- stereo: Frame::ComputeStereoMatches
+    left, right = pkg.synth.stereo_pair(640, 480, 0x57E2E001)
+    exL = pkg.ORBextractor(1000, 1.2, 8, 20, 7); exR = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    kL, dL = exL(left); kR, dR = exR(right)
+    pl = oracle_lib.OraclePort(); pr = oracle_lib.OraclePort()
+    pl.extract(left); pr.extract(right)
+    lv = [pl.level_pixels(l) for l in range(8)], [pr.level_pixels(l) for l in range(8)]
+    bf, b = 386.1448, 0.5372
+    u, d = pkg.stereo_match(exL, exR, bf, b)
+    ou, od = po.stereo_matches(kL, dL, kR, dR, lv[0], lv[1], bf, b)
+    assert u.tobytes() == ou.tobytes() and d.tobytes() == od.tobytes()
+    out["stereo_match_640x480_1000kp"] = {"gpu_ms": med(lambda: pkg.stereo_match(exL, exR, bf, b)),
+                                          "cpu_ms": med(lambda: po.stereo_matches(kL, dL, kR, dR, lv[0], lv[1], bf, b), 10, 1),
+                                          "matched": int((u >= 0).sum())}
+    # --- undistort
+    K, D = (517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    import ctypes as C
+    L = C.CDLL(oracle_lib.PORT_SO)
+    L.orbo_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    Kf, Df = np.array(K, np.float32), np.array(D, np.float32)
+
+    def cpu_und(p):
+        o = np.zeros_like(p); L.orbo_undistort_points(p.ctypes.data, len(p), Kf.ctypes.data, Df.ctypes.data, len(Df), o.ctypes.data); return o
+    pts = np.ascontiguousarray(np.stack([kL["x"], kL["y"]], 1))
+    assert np.array_equal(np.stack([exL.undistort_keypoints(K, D)[f] for f in ("x", "y")], 1), cpu_und(pts))
+    out["undistort_keypoints_1000"] = {"gpu_ms": med(lambda: exL.undistort_keypoints(K, D)), "cpu_ms": med(lambda: cpu_und(pts))}
+    big = (np.random.default_rng(1).random((1 << 22, 2)) * np.array([640.0, 480.0])).astype(np.float32)
+    assert pkg.undistort_points(big, K, D).tobytes() == cpu_und(big).tobytes()
+    out["undistort_points_4M"] = {"gpu_ms": med(lambda: pkg.undistort_points(big, K, D), 5, 1), "cpu_ms": med(lambda: cpu_und(big), 3, 1)}
+    # --- searches
+    F1, F2, bounds = ts.two_frames(pkg, ts.device_extract(pkg))
+    (k1, d1), (k2, d2) = F1, F2
+    pm = np.stack([k1["x"], k1["y"]], 1)
+    a = pkg.search_for_initialization(k1, d1, k2, d2, bounds, pm); o = po.search_for_initialization(k1, d1, k2, d2, bounds, pm)
+    assert a[0] == o[0] and np.array_equal(a[1], o[1])
+    out["search_for_initialization_1000x1000"] = {"gpu_ms": med(lambda: pkg.search_for_initialization(k1, d1, k2, d2, bounds, pm)),
+                                                  "cpu_ms": med(lambda: po.search_for_initialization(k1, d1, k2, d2, bounds, pm)),
+                                                  "nmatches": a[0]}
+    args, keep = ts.projection_scene(pkg, oracle_lib, F1, F2, bounds, 0.0, True)
+    a = pkg.search_by_projection(args); o = po.search_by_projection(args)
+    assert a[0] == o[0] and np.array_equal(a[1], o[1])
+    out["search_by_projection_1000x1000"] = {"gpu_ms": med(lambda: pkg.search_by_projection(args)),
+                                             "cpu_ms": med(lambda: po.search_by_projection(args)), "nmatches": a[0]}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
