@@ -860,11 +860,11 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-// horizontal pass of one input row for the 4 pixels of word column wc: h[p] = sum_i k_i * I(4wc + p + i - 3).
-// WORDS: three aligned 32-bit loads (the whole 10-byte window lies inside the row); otherwise byte loads
-// with REFLECT_101 (row ends, or rows that are not 4-byte aligned).
+// The 12-byte window (wl, wm, wr) of one input row around word column wc: bytes I(4wc - 4 .. 4wc + 7).
+// WORDS: three aligned 32-bit loads (the whole window lies inside the row); otherwise byte loads with
+// REFLECT_101 (row ends, or rows that are not 4-byte aligned).
 template <bool WORDS>
-__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ rowp, int wc, int w, unsigned h[4])
+__device__ __forceinline__ uint3 blur_load(const uint8_t* __restrict__ rowp, int wc, int w)
 {
     unsigned wl, wm, wr;
     if (WORDS) {
@@ -881,43 +881,65 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ rowp, int 
             if (k < 4) wl |= v << (8 * k); else if (k < 8) wm |= v << (8 * (k - 4)); else wr |= v << (8 * (k - 8));
         }
     }
-    unsigned b[10];
-    b[0] = (wl >> 8) & 0xFF; b[1] = (wl >> 16) & 0xFF; b[2] = wl >> 24;
-    b[3] = wm & 0xFF; b[4] = (wm >> 8) & 0xFF; b[5] = (wm >> 16) & 0xFF; b[6] = wm >> 24;
-    b[7] = wr & 0xFF; b[8] = (wr >> 8) & 0xFF; b[9] = (wr >> 16) & 0xFF;
-#pragma unroll
-    for (int p = 0; p < 4; ++p)
-        h[p] = 18u * (b[p] + b[p + 6]) + 34u * (b[p + 1] + b[p + 5]) + 48u * (b[p + 2] + b[p + 4]) + 56u * b[p + 3];
+    return make_uint3(wl, wm, wr);
+}
+
+// horizontal pass for the 4 pixels of the word column: h[p] = sum_i k_i * I(4wc + p + i - 3).
+// window bytes b[k] = I(4wc - 3 + k): a_p = b[p..p+3], c_p = b[p+4..p+7]; taps (18,34,48,56 | 48,34,18,0) by IDP.4A
+__device__ __forceinline__ void blur_hsum(const uint3 r, unsigned h[4])
+{
+    const unsigned K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
+    h[0] = __dp4a(__funnelshift_r(r.x, r.y, 8), K0, __dp4a(__funnelshift_r(r.y, r.z, 8), K1, 0u));
+    h[1] = __dp4a(__funnelshift_r(r.x, r.y, 16), K0, __dp4a(__funnelshift_r(r.y, r.z, 16), K1, 0u));
+    h[2] = __dp4a(__funnelshift_r(r.x, r.y, 24), K0, __dp4a(__funnelshift_r(r.y, r.z, 24), K1, 0u));
+    h[3] = __dp4a(r.y, K0, __dp4a(r.z, K1, 0u));
 }
 
 // One thread = one 4-pixel word column x BLUR_R output rows.  The horizontal sums of the last 7 input rows
 // live in registers (28 values); every new input row costs three aligned 32-bit loads (L1 serves the
-// overlap with the neighbouring threads), every output row one aligned 32-bit store.  No shared memory.
+// overlap with the neighbouring threads), issued BLUR_AHEAD rows before their use; every output row is one
+// aligned 32-bit store.  No shared memory.
+#ifndef BLUR_AHEAD
+#define BLUR_AHEAD 1
+#endif
 template <bool WORDS>
 __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int sp, uint8_t* __restrict__ dst, int dp,
                                            int w, int hgt, int wc, int y0)
 {
     // input row y0 - 3 + k; rows are REFLECT_101-mapped only in the first / last strip
-    const bool inner = y0 >= 3 && y0 + BLUR_R + 3 <= hgt;
+    const bool inner = y0 >= 3 && y0 + BLUR_R + 3 + BLUR_AHEAD <= hgt;
     unsigned ring[7][4];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
         const int yy = inner ? y0 - 3 + k : reflect101(y0 - 3 + k, hgt);
-        blur_hrow<WORDS>(src + (size_t)yy * sp, wc, w, ring[k]);
+        blur_hsum(blur_load<WORDS>(src + (size_t)yy * sp, wc, w), ring[k]);
+    }
+    uint3 ahead[BLUR_AHEAD];                                   // rows y0 + 3 .. y0 + 3 + BLUR_AHEAD - 1, in flight
+#pragma unroll
+    for (int a = 0; a < BLUR_AHEAD; ++a) {
+        const int yy = inner ? y0 + 3 + a : reflect101(y0 + 3 + a, hgt);
+        ahead[a] = blur_load<WORDS>(src + (size_t)yy * sp, wc, w);
     }
     for (int yb = 0; yb < BLUR_R; yb += 7) {
 #pragma unroll
         for (int j = 0; j < 7; ++j) {
             const int y = y0 + yb + j;
-            const int yy = inner ? y + 3 : reflect101(y + 3, hgt);
-            blur_hrow<WORDS>(src + (size_t)yy * sp, wc, w, ring[(j + 6) % 7]);
-            uint32_t out = 0;
+            const uint3 cur = ahead[0];
 #pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                const unsigned v = 18u * (ring[j % 7][p] + ring[(j + 6) % 7][p]) + 34u * (ring[(j + 1) % 7][p] + ring[(j + 5) % 7][p]) +
-                                   48u * (ring[(j + 2) % 7][p] + ring[(j + 4) % 7][p]) + 56u * ring[(j + 3) % 7][p] + 32768u;
-                out |= (v >> 16) << (8 * p);
+            for (int a = 0; a + 1 < BLUR_AHEAD; ++a) ahead[a] = ahead[a + 1];
+            {
+                const int yn = y + 3 + BLUR_AHEAD;             // rows past the strip are loaded but never used
+                const int yy = inner ? yn : reflect101(yn, hgt);
+                ahead[BLUR_AHEAD - 1] = blur_load<WORDS>(src + (size_t)yy * sp, wc, w);
             }
+            blur_hsum(cur, ring[(j + 6) % 7]);
+            unsigned v[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+                v[p] = 18u * (ring[j % 7][p] + ring[(j + 6) % 7][p]) + 34u * (ring[(j + 1) % 7][p] + ring[(j + 5) % 7][p]) +
+                       48u * (ring[(j + 2) % 7][p] + ring[(j + 4) % 7][p]) + 56u * ring[(j + 3) % 7][p] + 32768u;
+            // byte 2 of each sum = (v + 2^15) >> 16 (v < 2^24)
+            const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
             if (y < hgt) *reinterpret_cast<uint32_t*>(dst + (size_t)y * dp + 4 * wc) = out;
         }
     }
