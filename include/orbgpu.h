@@ -178,6 +178,21 @@ typedef struct orbgpu_projection_args {
  * last-frame keypoint i, -2 set and then reset to NULL by the rotation-consistency check.  *nmatches = return value. */
 int orbgpu_search_by_projection(int device, const orbgpu_projection_args* args, int32_t* cur_match, int* nmatches);
 
+/* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
+ * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
+ * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order
+ * (DBoW2 itself stays on the reference path).  valid = map point present and not bad (all 1 for a Frame); angle =
+ * keypoint angles.  strict_th_low: 0 = "bestDist1 <= TH_LOW" (:241), 1 = "bestDist1 < TH_LOW" (:600).
+ * match12[n1] / match21[n2] = the accepted pairs after the rotation check, -1 elsewhere: overload 1 sets
+ * vpMapPointMatches[idx2] to the map point of keyframe feature match21[idx2]; overload 2 sets vpMatches12[idx1] to the
+ * map point of feature match12[idx1] of pKF2.  *nmatches = the return value. */
+typedef struct orbgpu_bow_side {
+    const uint8_t* desc; int32_t n; const uint8_t* valid; const float* angle;
+    const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;
+} orbgpu_bow_side;
+int orbgpu_search_by_bow(int device, const orbgpu_bow_side* side1, const orbgpu_bow_side* side2, float nnratio,
+                         int check_orientation, int strict_th_low, int32_t* match12, int32_t* match21, int* nmatches);
+
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),
  * FAST candidates in list order (:791-831) and octree survivors in list order (:541-765); x, y are

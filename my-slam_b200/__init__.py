@@ -6,5 +6,6 @@ directory name has a hyphen, so import it through __graft_entry__.load_package()
 `my_slam_b200`).
 """
 from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path, stereo_match, undistort_points,
-                     ProjectionArgs, projection_args, search_for_initialization, search_by_projection)  # noqa: F401
+                     ProjectionArgs, projection_args, search_for_initialization, search_by_projection,
+                     BowSide, bow_side, search_by_bow)  # noqa: F401
 from . import shard, synth  # noqa: F401

@@ -357,6 +357,79 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t
     if (lane == 0) *nmatches_out = nmatches;
 }
 
+// ---- SearchByBoW (src/ORBmatcher.cc:159-288, :522-655) -----------------------------------------------------------
+// A query = one valid feature of side 1 inside a vocabulary node both sides share; its candidates = the features of
+// side 2 in that node, in the FeatureVector's order.  Queries are listed by the host in the reference's visiting
+// order (nodes ascending, then the node's index list).
+struct BowQuery { int idx1, start, len; };                    // candidates = indices2[start .. start + len)
+
+__global__ void __launch_bounds__(256) k_bow_candidates(const BowQuery* __restrict__ Q, int nq, const uint8_t* __restrict__ desc1,
+                                                        const uint8_t* __restrict__ desc2, const uint32_t* __restrict__ indices2,
+                                                        uint32_t* __restrict__ cand, int cap, int* __restrict__ cand_n)
+{
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const BowQuery B = Q[q];
+    const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1);
+    const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1 + 1);
+    for (int p = lane; p < B.len; p += 32) {
+        const uint32_t i2 = indices2[B.start + p];
+        const int d = hamming_regs(a0, a1, reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2);
+        cand[(size_t)q * cap + p] = (i2 << CAND_DIST_BITS) | (uint32_t)d;
+    }
+    if (lane == 0) cand_n[q] = B.len;
+}
+
+// the in-order part: vbMatched2 / vpMapPointMatches exclusion, best + second, TH_LOW and ratio tests.  The exclusion
+// only couples queries of the same vocabulary node (a feature lies in one node), so each warp of the CTA walks the
+// queries of its own nodes in order: group g = queries [gstart[g], gstart[g + 1]).
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_bow_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
+                                                                 int nq, int n2, const uint8_t* __restrict__ valid2,
+                                                                 const int* __restrict__ gstart, int ngroups, float nnratio,
+                                                                 int th_low_excl, int* __restrict__ accepted, int* __restrict__ nmatches_out)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_nmatches;
+    const int t = threadIdx.x;
+    unsigned char* blocked = smem;                             // vbMatched2[idx2] || no usable map point
+    for (int i = t; i < n2; i += RESOLVE_THREADS) blocked[i] = valid2[i] ? 0 : 1;
+    for (int i = t; i < nq; i += RESOLVE_THREADS) accepted[i] = -1;
+    if (t == 0) s_nmatches = 0;
+    const ResolveStage S = stage_lists(smem, ((size_t)n2 + 15) & ~(size_t)15, cand, cand_n, cap, nq);
+    const int lane = t & 31, warp = t >> 5;
+    int nmatches = 0;
+    for (int g = warp; g < ngroups; g += RESOLVE_THREADS / 32) {
+        const int q1 = gstart[g + 1];
+        for (int q = gstart[g]; q < q1; ++q) {
+            const int cnt = S.cnt[q];
+            const uint32_t* c = S.base + S.off[q];
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
+            for (int p = lane; p < cnt; p += 32) {
+                const uint32_t e = c[p];
+                if (blocked[e >> CAND_DIST_BITS]) continue;
+                const unsigned key = ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p;
+                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+            }
+            const unsigned b1 = __reduce_min_sync(0xffffffffu, k1);
+            const unsigned b2 = __reduce_min_sync(0xffffffffu, k1 == b1 ? k2 : k1);
+            // bestDist1 / bestDist2 start at 256 and only take smaller values (:199-201)
+            const int bestDist1 = b1 == 0xFFFFFFFFu ? 256 : min((int)(b1 >> 16), 256);
+            const int bestDist2 = b2 == 0xFFFFFFFFu ? 256 : min((int)(b2 >> 16), 256);
+            if (bestDist1 < th_low_excl && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) {
+                const int bestIdx2 = (int)(c[b1 & 0xFFFFu] >> CAND_DIST_BITS);
+                __syncwarp();
+                if (lane == 0) { blocked[bestIdx2] = 1; accepted[q] = bestIdx2; }
+                nmatches++;
+                __syncwarp();
+            }
+        }
+    }
+    if (lane == 0 && nmatches) atomicAdd(&s_nmatches, nmatches);
+    __syncthreads();
+    if (t == 0) *nmatches_out = s_nmatches;
+}
+
 // ---- host side ---------------------------------------------------------------------------------------------------
 namespace {
 
@@ -391,6 +464,7 @@ struct Workspace {
         if (!attr_set) {
             CUS(cudaFuncSetAttribute(k_init_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
+            CUS(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             attr_set = true;
         }
         if (dbytes > dcap) {
@@ -609,6 +683,100 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
         for (int i = 0; i < n1; ++i) {
             if (bin[i] < 0 || bin[i] == ind1 || bin[i] == ind2 || bin[i] == ind3) continue;
             cur_match[acc[i]] = -2;
+            nm--;
+        }
+    }
+    *nmatches = nm;
+    return ORBGPU_OK;
+}
+
+int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow_side* s2, float nnratio, int check_orientation,
+                         int strict_th_low, int32_t* match12, int32_t* match21, int* nmatches)
+{
+    if (!s1 || !s2 || !match12 || !match21 || !nmatches) return ORBGPU_ERR_ARG;
+    const orbgpu_bow_side* S[2] = {s1, s2};
+    for (int k = 0; k < 2; ++k) {
+        const orbgpu_bow_side* s = S[k];
+        if (s->n < 0 || s->n_nodes < 0 || (s->n > 0 && (!s->desc || !s->valid || !s->angle)) ||
+            (s->n_nodes > 0 && (!s->node_ids || !s->node_start || !s->indices))) return ORBGPU_ERR_ARG;
+        if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+        for (int i = 0; i < s->n_nodes; ++i) {
+            if (s->node_start[i] > s->node_start[i + 1] || (i && s->node_ids[i - 1] >= s->node_ids[i])) return ORBGPU_ERR_ARG;
+            for (int a = s->node_start[i]; a < s->node_start[i + 1]; ++a) if (s->indices[a] >= (uint32_t)s->n) return ORBGPU_ERR_ARG;
+        }
+    }
+    const int n1 = s1->n, n2 = s2->n;
+    *nmatches = 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    for (int i = 0; i < n2; ++i) match21[i] = -1;
+    // the merge walk over the two FeatureVectors (:176-180, :254-266) -> queries in visiting order
+    std::vector<BowQuery> hq;
+    std::vector<int> gstart;                                   // query ranges per shared node
+    int cap = 0, it1 = 0, it2 = 0;
+    while (it1 != s1->n_nodes && it2 != s2->n_nodes) {
+        if (s1->node_ids[it1] == s2->node_ids[it2]) {
+            const int st = s2->node_start[it2], len = s2->node_start[it2 + 1] - st;
+            gstart.push_back((int)hq.size());
+            for (int a = s1->node_start[it1]; a < s1->node_start[it1 + 1]; ++a) {
+                const int idx1 = (int)s1->indices[a];
+                if (!s1->valid[idx1] || len == 0) continue;
+                BowQuery q; q.idx1 = idx1; q.start = st; q.len = len;
+                hq.push_back(q);
+                cap = len > cap ? len : cap;
+            }
+            ++it1; ++it2;
+        } else if (s1->node_ids[it1] < s2->node_ids[it2]) {
+            while (it1 != s1->n_nodes && s1->node_ids[it1] < s2->node_ids[it2]) ++it1;
+        } else {
+            while (it2 != s2->n_nodes && s2->node_ids[it2] < s1->node_ids[it1]) ++it2;
+        }
+    }
+    const int nq = (int)hq.size(), ngroups = (int)gstart.size();
+    gstart.push_back(nq);
+    if (nq == 0) return ORBGPU_OK;
+    if (nq > GRID_MAX_KEYS || (size_t)nq * (size_t)cap > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
+    const int nidx2 = s2->node_start[s2->n_nodes];
+    Layout L;
+    const size_t o_d1 = L.add(32 * (size_t)n1), o_d2 = L.add(32 * (size_t)n2), o_v2 = L.add((size_t)n2);
+    const size_t o_i2 = L.add(4 * (size_t)nidx2), o_q = L.add(sizeof(BowQuery) * (size_t)nq), o_g = L.add(4 * (size_t)(ngroups + 1));
+    const size_t in_bytes = L.off;
+    const size_t o_acc = L.add(4 * (size_t)nq), o_nm = L.add(4);
+    const size_t io_bytes = L.off;
+    const size_t o_cn = L.add(4 * (size_t)nq), o_cand = L.add(4 * (size_t)nq * cap);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_d1, s1->desc, 32 * (size_t)n1);
+    memcpy(W.h + o_d2, s2->desc, 32 * (size_t)n2);
+    memcpy(W.h + o_v2, s2->valid, (size_t)n2);
+    memcpy(W.h + o_i2, s2->indices, 4 * (size_t)nidx2);
+    memcpy(W.h + o_q, hq.data(), sizeof(BowQuery) * (size_t)nq);
+    memcpy(W.h + o_g, gstart.data(), 4 * (size_t)(ngroups + 1));
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+    k_bow_candidates<<<(nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), nq, W.d + o_d1, W.d + o_d2,
+                                                     reinterpret_cast<const uint32_t*>(W.d + o_i2), d_cand, cap, d_cn);
+    k_bow_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, cap, nq, n2, W.d + o_v2, reinterpret_cast<const int*>(W.d + o_g),
+                                                              ngroups, nnratio, strict_th_low ? 50 : 51,
+                                                              reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
+    int nm = *reinterpret_cast<const int*>(W.h + o_nm);
+    for (int q = 0; q < nq; ++q)
+        if (acc[q] >= 0) { match12[hq[q].idx1] = acc[q]; match21[acc[q]] = hq[q].idx1; }
+    if (check_orientation) {                                   // :268-285, :628-652
+        int bin_of[30] = {0};
+        std::vector<int> bin((size_t)nq, -1);
+        for (int q = 0; q < nq; ++q)
+            if (acc[q] >= 0) { bin[q] = rot_bin(s1->angle[hq[q].idx1], s2->angle[acc[q]]); bin_of[bin[q]]++; }
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(bin_of, 30, ind1, ind2, ind3);
+        for (int q = 0; q < nq; ++q) {
+            if (bin[q] < 0 || bin[q] == ind1 || bin[q] == ind2 || bin[q] == ind3) continue;
+            match12[hq[q].idx1] = -1; match21[acc[q]] = -1;
             nm--;
         }
     }

@@ -27,6 +27,32 @@ class ProjectionArgs(C.Structure):
                 ("mono", C.c_int32), ("check_orientation", C.c_int32)]
 
 
+class BowSide(C.Structure):
+    """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
+    _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
+                ("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p), ("n_nodes", C.c_int32)]
+
+
+def bow_side(desc, valid, angle, node_ids, node_start, indices):
+    """Builds a BowSide; returns (struct, keepalive dict)."""
+    arrs = dict(desc=np.ascontiguousarray(desc, np.uint8), valid=np.ascontiguousarray(valid, np.uint8),
+                angle=np.ascontiguousarray(angle, np.float32), node_ids=np.ascontiguousarray(node_ids, np.uint32),
+                node_start=np.ascontiguousarray(node_start, np.int32), indices=np.ascontiguousarray(indices, np.uint32))
+    s = BowSide()
+    for k, v in arrs.items():
+        setattr(s, k, v.ctypes.data)
+    s.n = len(arrs["valid"]); s.n_nodes = len(arrs["node_ids"])
+    return s, arrs
+
+
+def search_by_bow(side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False, device=0):
+    """ORBmatcher::SearchByBoW (src/ORBmatcher.cc:159-288, 522-655) -> (nmatches, match12[n1], match21[n2])."""
+    m12 = np.zeros(max(side1.n, 1), np.int32); m21 = np.zeros(max(side2.n, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_by_bow(device, C.byref(side1), C.byref(side2), float(nnratio), int(check_orientation),
+                                      int(strict_th_low), _p(m12), _p(m21), C.byref(nm)))
+    return nm.value, m12[:side1.n].copy(), m21[:side2.n].copy()
+
+
 def projection_args(world_pos, mp_desc, mp_valid, mp_observed, last_octave, last_angle, Tcw_last, cur_keys_un, cur_desc,
                     cur_u_right, cur_occupied, Tcw_cur, cam, bf, b, bounds, scale_factors, th, mono, check_orientation=True):
     """Builds a ProjectionArgs; returns (struct, keepalive list of the arrays it points into)."""
@@ -99,6 +125,7 @@ def lib():
         "orbgpu_undistort_points": (i32, [i32, vp, i32, vp, vp, i32, vp]),
         "orbgpu_search_for_initialization": (i32, [i32, vp, vp, i32, vp, vp, i32, vp, vp, i32, f32, i32, vp, pi]),
         "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
+        "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),

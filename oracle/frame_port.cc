@@ -231,3 +231,59 @@ extern "C" int frameport_search_by_projection(const frameport_projection_args* a
     delete g;
     return nmatches;
 }
+
+// src/ORBmatcher.cc:159-288 and :522-655 (the two overloads differ in which side carries validity and in <= / < TH_LOW)
+extern "C" int frameport_search_by_bow(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
+                                       int strict_th_low, int* match12, int* match21)
+{
+    for (int i = 0; i < s1->n; ++i) match12[i] = -1;
+    for (int i = 0; i < s2->n; ++i) match21[i] = -1;
+    std::vector<bool> vbMatched2((size_t)s2->n, false);
+    std::vector<int> rotHist[HISTO_LENGTH];                    // holds idx1; the pair's idx2 is match12[idx1]
+    int nmatches = 0;
+    int it1 = 0, it2 = 0;
+    while (it1 != s1->n_nodes && it2 != s2->n_nodes) {
+        if (s1->node_ids[it1] == s2->node_ids[it2]) {
+            for (int a = s1->node_start[it1]; a < s1->node_start[it1 + 1]; ++a) {
+                const unsigned idx1 = s1->indices[a];
+                if (!s1->valid[idx1]) continue;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int c = s2->node_start[it2]; c < s2->node_start[it2 + 1]; ++c) {
+                    const unsigned idx2 = s2->indices[c];
+                    if (vbMatched2[idx2] || !s2->valid[idx2]) continue;
+                    const int dist = orbport_hamming256(s1->desc + 32 * (size_t)idx1, s2->desc + 32 * (size_t)idx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = (int)idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (strict_th_low ? bestDist1 < TH_LOW : bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {
+                        match12[idx1] = bestIdx2;
+                        match21[bestIdx2] = (int)idx1;
+                        vbMatched2[bestIdx2] = true;
+                        if (check_orientation) rotHist[rot_bin(s1->angle[idx1], s2->angle[bestIdx2])].push_back((int)idx1);
+                        nmatches++;
+                    }
+                }
+            }
+            ++it1; ++it2;
+        } else if (s1->node_ids[it1] < s2->node_ids[it2]) {
+            while (it1 != s1->n_nodes && s1->node_ids[it1] < s2->node_ids[it2]) ++it1;       // lower_bound
+        } else {
+            while (it2 != s2->n_nodes && s2->node_ids[it2] < s1->node_ids[it1]) ++it2;
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); ++j) {
+                const int idx1 = rotHist[i][j];
+                match21[match12[idx1]] = -1;
+                match12[idx1] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}

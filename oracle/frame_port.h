@@ -2,6 +2,7 @@
  *   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:230-245, 327-391
  *   ORBmatcher::SearchForInitialization                           src/ORBmatcher.cc:405-520
  *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono) src/ORBmatcher.cc:1328-1470
+ *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
  * PARITY UNPINNED: src/Frame.cc and src/ORBmatcher.cc need the whole ORB-SLAM2 header set (DBoW2, g2o, Eigen,
  * MapPoint/KeyFrame) and cannot be compiled here, and the reference has no tests for them.  The one library
@@ -49,6 +50,20 @@ int frameport_search_for_initialization(const orbport_keypoint* k1, const uint8_
                                         float nnratio, int check_orientation, int* matches12);
 /* returns nmatches; cur_match[n_cur]: -1 untouched, -2 reset to NULL by the rotation check, >= 0 index into the last frame */
 int frameport_search_by_projection(const frameport_projection_args* a, int* cur_match);
+
+/* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
+ * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
+ * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order.
+ * valid = map point present and not bad (all 1 for a Frame).  strict_th_low: 0 = "bestDist1 <= TH_LOW" (:241),
+ * 1 = "bestDist1 < TH_LOW" (:600).  match12[n1] / match21[n2] = the accepted pairs after the rotation check
+ * (-1 elsewhere): overload 1 fills vpMapPointMatches[idx2] = map point of match21[idx2], overload 2 fills
+ * vpMatches12[idx1] = map point of match12[idx1].  Same layout as orbgpu_bow_side (include/orbgpu.h). */
+typedef struct frameport_bow_side {
+    const uint8_t* desc; int32_t n; const uint8_t* valid; const float* angle;
+    const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;
+} frameport_bow_side;
+int frameport_search_by_bow(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
+                            int strict_th_low, int* match12, int* match21);
 
 #ifdef __cplusplus
 }

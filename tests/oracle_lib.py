@@ -63,6 +63,7 @@ class OraclePort:
         L.frameport_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                                           C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.frameport_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
 
@@ -175,6 +176,13 @@ class OraclePort:
         cm = _i32(args.n_cur)
         nm = self.L.frameport_search_by_projection(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
+
+    def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
+        """sides: the product's BowSide ctypes structs (same layout as frameport_bow_side)."""
+        m12 = _i32(side1.n); m21 = _i32(side2.n)
+        nm = self.L.frameport_search_by_bow(C.byref(side1), C.byref(side2), nnratio, int(check_orientation), int(strict_th_low),
+                                            _ptr(m12), _ptr(m21))
+        return nm, m12[:side1.n].copy(), m21[:side2.n].copy()
 
     def match_count(self, A, B, th_low=50, ratio=0.6):
         A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)

@@ -184,3 +184,69 @@ def test_device_search_edge_cases(pkg, oracle):
     assert nm == onm == 0 and np.array_equal(m12, om12)
     with pytest.raises(RuntimeError):
         pkg.search_for_initialization(k1, d1, k2, d2, (0, 0, 0, 217), pm)                  # degenerate bounds
+
+
+# ------------------------------------------------------------------------------------------------ SearchByBoW (f3)
+def feature_vector(desc, n_words):
+    """A stand-in for DBoW2's FeatureVector (the vocabulary tree stays on the reference path): node id = a few leading
+    descriptor bits + a coarse hash, features listed per node in index order, nodes ascending -- the layout of
+    std::map<NodeId, std::vector<unsigned>>."""
+    level_bits = 3 if n_words <= 32 else 5
+    node = ((desc[:, 0].astype(np.uint32) >> (8 - level_bits)) * 7 + (desc[:, 5].astype(np.uint32) >> 6)) % np.uint32(n_words)
+    ids = np.unique(node)
+    start, idx = [0], []
+    for i in ids:
+        members = np.nonzero(node == i)[0]
+        idx.extend(members.tolist()); start.append(len(idx))
+    return ids.astype(np.uint32), np.array(start, np.int32), np.array(idx, np.uint32)
+
+
+def bow_sides(pkg, F1, F2, seed, kf_kf, n_words=24):
+    (k1, d1), (k2, d2) = F1, F2
+    rng = np.random.default_rng(seed)
+    v1 = (rng.random(len(k1)) < 0.8).astype(np.uint8)
+    v2 = (rng.random(len(k2)) < 0.8).astype(np.uint8) if kf_kf else np.ones(len(k2), np.uint8)
+    s1, keep1 = pkg.bow_side(d1, v1, k1["angle"], *feature_vector(d1, n_words))
+    s2, keep2 = pkg.bow_side(d2, v2, k2["angle"], *feature_vector(d2, n_words))
+    return s1, s2, (keep1, keep2)
+
+
+def test_oracle_bow_matches_are_one_to_one_and_follow_the_shift(pkg, oracle):
+    F1, F2, _ = two_frames(pkg, oracle_extract(oracle))
+    po = oracle.OraclePort()
+    for kf_kf in (False, True):
+        s1, s2, keep = bow_sides(pkg, F1, F2, 3, kf_kf)
+        nm, m12, m21 = po.search_by_bow(s1, s2, 0.7, True, kf_kf)
+        ok = m12 >= 0
+        assert nm == ok.sum() == (m21 >= 0).sum() and nm > 100
+        assert np.array_equal(m21[m12[ok]], np.nonzero(ok)[0])             # the two views of the pair list agree
+        assert keep[0]["valid"][ok].all() and keep[1]["valid"][m12[ok]].all()
+        k1, k2 = F1[0], F2[0]
+        dx = k2["x"][m12[ok]] / 1.0 - k1["x"][ok]; dy = k2["y"][m12[ok]] - k1["y"][ok]
+        assert (np.abs(dx - SHIFT[0]) < 4).mean() > 0.8 and (np.abs(dy - SHIFT[1]) < 4).mean() > 0.8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kf_kf", [False, True], ids=["keyframe-frame", "keyframe-keyframe"])
+def test_device_search_by_bow_equals_oracle(pkg, oracle, kf_kf):
+    po = oracle.OraclePort()
+    for nf, seed in [(1000, 3), (2000, 4)]:
+        F1, F2, _ = two_frames(pkg, device_extract(pkg), 640, 480, 0xB0B0 + nf, nf)
+        s1, s2, keep = bow_sides(pkg, F1, F2, seed, kf_kf, 24 if nf == 1000 else 100)
+        for ratio, ori in [(0.7, True), (0.9, False), (0.6, True)]:
+            onm, om12, om21 = po.search_by_bow(s1, s2, ratio, ori, kf_kf)
+            nm, m12, m21 = pkg.search_by_bow(s1, s2, ratio, ori, kf_kf)
+            assert nm == onm and np.array_equal(m12, om12) and np.array_equal(m21, om21)
+    assert nm > 80
+    # a single shared node (every feature against every feature) and disjoint vocabularies
+    (k1, d1), (k2, d2) = F1, F2
+    one = (np.array([5], np.uint32), np.array([0, len(k1)], np.int32), np.arange(len(k1), dtype=np.uint32))
+    two = (np.array([5], np.uint32), np.array([0, len(k2)], np.int32), np.arange(len(k2), dtype=np.uint32))
+    a, ka = pkg.bow_side(d1, np.ones(len(k1), np.uint8), k1["angle"], *one)
+    b, kb = pkg.bow_side(d2, np.ones(len(k2), np.uint8), k2["angle"], *two)
+    got, want = pkg.search_by_bow(a, b), po.search_by_bow(a, b)
+    assert got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+    two = (np.array([9], np.uint32), two[1], two[2])
+    b, kb = pkg.bow_side(d2, np.ones(len(k2), np.uint8), k2["angle"], *two)
+    nm, m12, m21 = pkg.search_by_bow(a, b)
+    assert nm == 0 and (m12 == -1).all() and (m21 == -1).all()

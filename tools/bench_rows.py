@@ -73,6 +73,11 @@ def main():
     assert a[0] == o[0] and np.array_equal(a[1], o[1])
     out["search_by_projection_1000x1000"] = {"gpu_ms": med(lambda: pkg.search_by_projection(args)),
                                              "cpu_ms": med(lambda: po.search_by_projection(args)), "nmatches": a[0]}
+    s1, s2, keep = ts.bow_sides(pkg, F1, F2, 3, False, 100)
+    a = pkg.search_by_bow(s1, s2); o = po.search_by_bow(s1, s2)
+    assert a[0] == o[0] and np.array_equal(a[1], o[1])
+    out["search_by_bow_1000x1000_100nodes"] = {"gpu_ms": med(lambda: pkg.search_by_bow(s1, s2)), "cpu_ms": med(lambda: po.search_by_bow(s1, s2)),
+                                              "nmatches": a[0]}
     print(json.dumps(out, indent=1))
 
 
