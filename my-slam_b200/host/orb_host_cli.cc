@@ -7,11 +7,15 @@
 //   orb_host_cli match <A.bin> <nA> <B.bin> <nB> <out.bin>      -> int32 best idx / dist / second per row,
 //       then int32 accepted count of SearchBruteForce and one DescriptorDistance(A0, B0)
 //   orb_host_cli maxima  (reads histogram sizes from stdin)     -> prints ind1 ind2 ind3
+//   orb_host_cli stereo <left.gray> <right.gray> <w> <h> <nfeatures> <bf> <b> <out.bin>
+//       two extractors on two threads as the stereo Frame constructor runs them (src/Frame.cc:78-81), then
+//       ORBextractor::ComputeStereoMatches -> int32 N, N x float mvuRight, N x float mvDepth
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "FrameQueue.h"
@@ -108,6 +112,34 @@ static int cmd_match(int argc, char** argv)
     return 0;
 }
 
+static int cmd_stereo(int argc, char** argv)
+{
+    if (argc < 10) return 2;
+    const int w = atoi(argv[4]), h = atoi(argv[5]), nf = atoi(argv[6]);
+    std::vector<unsigned char> rawL, rawR;
+    if (!read_file(argv[2], rawL, (size_t)w * h) || !read_file(argv[3], rawR, (size_t)w * h)) return 2;
+    ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);
+    cv::Mat imL(h, w, CV_8UC1, rawL.data(), (size_t)w), imR(h, w, CV_8UC1, rawR.data(), (size_t)w);
+    std::vector<cv::KeyPoint> kL, kR;
+    cv::Mat dL, dR;
+    std::thread tl([&] { exL(imL, cv::Mat(), kL, dL); });
+    std::thread tr([&] { exR(imR, cv::Mat(), kR, dR); });
+    tl.join(); tr.join();
+    std::vector<float> uR, depth;
+    if (!ORBextractor::ComputeStereoMatches(exL, exR, (float)atof(argv[7]), (float)atof(argv[8]), uR, depth)) {
+        fprintf(stderr, "ComputeStereoMatches: %s\n", exL.LastError());
+        return 3;
+    }
+    FILE* out = fopen(argv[9], "wb");
+    if (!out) return 2;
+    const int n = (int)uR.size();
+    fwrite(&n, 4, 1, out);
+    fwrite(uR.data(), 4, (size_t)n, out); fwrite(depth.data(), 4, (size_t)n, out);
+    fclose(out);
+    printf("%d %d\n", (int)kL.size(), (int)kR.size());
+    return 0;
+}
+
 static int cmd_maxima()
 {
     std::vector<std::vector<int> > histo;
@@ -126,10 +158,11 @@ int main(int argc, char** argv)
         if (argc >= 2 && !strcmp(argv[1], "extract")) return cmd_extract(argc, argv);
         if (argc >= 2 && !strcmp(argv[1], "match")) return cmd_match(argc, argv);
         if (argc >= 2 && !strcmp(argv[1], "maxima")) return cmd_maxima();
+        if (argc >= 2 && !strcmp(argv[1], "stereo")) return cmd_stereo(argc, argv);
     } catch (const std::exception& e) {
         fprintf(stderr, "orb_host_cli: %s\n", e.what());     // e.g. no CUDA device: there is no CPU path
         return 3;
     }
-    fprintf(stderr, "usage: orb_host_cli extract|match|maxima ...\n");
+    fprintf(stderr, "usage: orb_host_cli extract|match|maxima|stereo ...\n");
     return 2;
 }

@@ -86,3 +86,23 @@ def test_cpp_matcher_matches_oracle(cli, pkg, oracle, tmp_path):
     assert acc == int(ok.sum()) == port.match_count(A, B, 50, 0.6) and acc >= 90
     assert np.array_equal(m12, np.where(ok, oi, -1))
     assert d00 == port.hamming(A[0], B[0])
+
+
+def test_cpp_stereo_matches_equal_oracle(cli, pkg, oracle, tmp_path):
+    """Two ORBextractor instances on two threads (src/Frame.cc:78-81), then the device ComputeStereoMatches."""
+    left, right = pkg.synth.stereo_pair(640, 480, 0x57E2E0AA)
+    (tmp_path / "l.gray").write_bytes(left.tobytes()); (tmp_path / "r.gray").write_bytes(right.tobytes())
+    out = tmp_path / "stereo.bin"
+    bf, b = 386.1448, 0.5372
+    r = subprocess.run([cli, "stereo", str(tmp_path / "l.gray"), str(tmp_path / "r.gray"), "640", "480", "1000", repr(bf), repr(b), str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = out.read_bytes()
+    n = int(np.frombuffer(buf, np.int32, 1)[0])
+    u = np.frombuffer(buf, np.float32, n, 4); d = np.frombuffer(buf, np.float32, n, 4 + 4 * n)
+    pl = oracle.OraclePort(1000, 1.2, 8, 20, 7); pr = oracle.OraclePort(1000, 1.2, 8, 20, 7)
+    kL, dL = pl.extract(left); kR, dR = pr.extract(right)
+    ou, od = pl.stereo_matches(kL, dL, kR, dR, [pl.level_pixels(l) for l in range(8)], [pr.level_pixels(l) for l in range(8)],
+                               np.float32(bf), np.float32(b))
+    assert n == len(kL) and u.tobytes() == ou.tobytes() and d.tobytes() == od.tobytes()
+    assert (u >= 0).sum() > 300
