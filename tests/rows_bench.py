@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Timing of the SURVEY section-8(f) rows next to their CPU restatements (one thread, the reference's execution model
-for these functions): python tools/bench_rows.py > profiles/<round>_rows.json.  Each GPU figure is the wall time of the
+for these functions): python tests/rows_bench.py > profiles/<round>_rows.json (lives under tests/ because it uses the oracle as checker and CPU baseline).  Each GPU figure is the wall time of the
 public C-ABI call (host buffers in, host buffers out; synchronous), median of `reps` calls after warm-up; the CPU
 figure is oracle/frame_port.cc / orb_port.cc on the same inputs.  Results of both are compared before timing."""
 import json
@@ -11,7 +11,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))   # this file's own directory
 import __graft_entry__ as g          # noqa: E402
 import oracle_lib                     # noqa: E402  (checker + CPU baseline only)
 import test_search as ts              # noqa: E402  (scene builders)
