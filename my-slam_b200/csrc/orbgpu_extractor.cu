@@ -61,6 +61,8 @@ struct Plan {
 
 struct StreamCtx {
     cudaStream_t st = nullptr;
+    cudaStream_t st_side = nullptr;    // blur runs here, beside FAST + octree of the same chunk (both only need the pyramid)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
     cudaEvent_t done = nullptr;
     int cap = 0;                       // frames the buffers below can hold
@@ -370,11 +372,22 @@ static int enqueue_kernels(orbgpu_extractor* e, StreamCtx& c, const uint8_t* d_s
     int n, total = 0;
     if ((n = orb_launch_pyramid(P, nframes, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
     if (prof) CU(cudaEventRecord(c.ev[EV_PYR], c.st));
+    // blur only needs the pyramid: it runs on the side stream next to FAST + octree of the same chunk and joins before
+    // describe (throughput of a busy GPU is unchanged, a single frame's latency drops by the blur time); the profiling
+    // mode keeps everything on one stream so that the stage events bracket one kernel each
+    const bool side = !prof && c.st_side;
+    if (side) {
+        CU(cudaEventRecord(c.ev_fork, c.st));
+        CU(cudaStreamWaitEvent(c.st_side, c.ev_fork, 0));
+        if ((n = orb_launch_blur(P, nframes, pl.d_tiles, pl.ntiles, c.st_side)) < 0) return ORBGPU_ERR_CUDA; total += n;
+        CU(cudaEventRecord(c.ev_join, c.st_side));
+    }
     if (P.ncells > 0) { if ((n = orb_launch_fast(P, nframes, pl.fast_smem, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n; }
     if (prof) CU(cudaEventRecord(c.ev[EV_FAST], c.st));
     if ((n = orb_launch_octree(P, nframes, pl.key_smem_cap, pl.node_smem_cap, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
     if (prof) CU(cudaEventRecord(c.ev[EV_OCT], c.st));
-    if ((n = orb_launch_blur(P, nframes, pl.d_tiles, pl.ntiles, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
+    if (side) CU(cudaStreamWaitEvent(c.st, c.ev_join, 0));
+    else { if ((n = orb_launch_blur(P, nframes, pl.d_tiles, pl.ntiles, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n; }
     if (prof) CU(cudaEventRecord(c.ev[EV_BLUR], c.st));
     if ((n = orb_launch_describe(P, nframes, c.st)) < 0) return ORBGPU_ERR_CUDA; total += n;
     if (prof) CU(cudaEventRecord(c.ev[EV_DESC], c.st));
@@ -582,6 +595,9 @@ int orbgpu_create(orbgpu_extractor** out, int device, int nfeatures, float scale
     for (int s = 0; s < NSTREAM; ++s) {
         StreamCtx& c = e->ctx[s];
         if (cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking) != cudaSuccess) { delete e; return ORBGPU_ERR_CUDA; }
+        if (cudaStreamCreateWithFlags(&c.st_side, cudaStreamNonBlocking) != cudaSuccess) { delete e; return ORBGPU_ERR_CUDA; }
+        cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming);
         for (int k = 0; k < EV_COUNT; ++k) cudaEventCreate(&c.ev[k]);
         cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming);
     }
@@ -600,6 +616,9 @@ void orbgpu_destroy(orbgpu_extractor* e)
         ctx_free_buffers(c);
         for (int k = 0; k < EV_COUNT; ++k) if (c.ev[k]) cudaEventDestroy(c.ev[k]);
         if (c.done) cudaEventDestroy(c.done);
+        if (c.ev_fork) cudaEventDestroy(c.ev_fork);
+        if (c.ev_join) cudaEventDestroy(c.ev_join);
+        if (c.st_side) cudaStreamDestroy(c.st_side);
         if (c.st) cudaStreamDestroy(c.st);
     }
     if (e->ev_batch0) cudaEventDestroy(e->ev_batch0);
