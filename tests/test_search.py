@@ -250,3 +250,63 @@ def test_device_search_by_bow_equals_oracle(pkg, oracle, kf_kf):
     b, kb = pkg.bow_side(d2, np.ones(len(k2), np.uint8), k2["angle"], *two)
     nm, m12, m21 = pkg.search_by_bow(a, b)
     assert nm == 0 and (m12 == -1).all() and (m21 == -1).all()
+
+
+# --------------------------------------------------------------------------------------------- randomised stress
+def random_frame(rng, n, w, h, pool):
+    """Keypoints anywhere in and slightly outside the image bounds (undistortion can push them out, src/Frame.cc:387),
+    all octaves, descriptors drawn from a small pool with a few flipped bits (many ties and competing queries)."""
+    KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+    k = np.zeros(n, KP)
+    k["x"] = rng.uniform(-12, w + 12, n).astype(np.float32); k["y"] = rng.uniform(-12, h + 12, n).astype(np.float32)
+    k["octave"] = rng.integers(0, 8, n); k["angle"] = rng.uniform(0, 360, n).astype(np.float32)
+    k["size"] = 31; k["response"] = rng.integers(7, 200, n); k["class_id"] = -1
+    d = pool[rng.integers(0, len(pool), n)].copy()
+    flips = rng.integers(0, 4, n)
+    for i in range(n):
+        for _ in range(int(flips[i])):
+            d[i, int(rng.integers(32))] ^= np.uint8(1 << int(rng.integers(8)))
+    return k, d
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [11, 12, 13])
+def test_device_searches_equal_oracle_on_random_frames(pkg, oracle, seed):
+    rng = np.random.default_rng(seed)
+    w, h = 640, 480
+    pool = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+    n1, n2 = int(rng.integers(300, 1500)), int(rng.integers(300, 1500))
+    k1, d1 = random_frame(rng, n1, w, h, pool); k2, d2 = random_frame(rng, n2, w, h, pool)
+    k1["octave"][rng.random(n1) < 0.6] = 0                    # SearchForInitialization only uses level 0
+    bounds = (-8.5, w + 7.25, -6.0, h + 9.5)                  # undistorted image bounds need not be the pixel grid
+    po = oracle.OraclePort()
+    pm = np.stack([k1["x"], k1["y"]], 1) + rng.normal(0, 20, (n1, 2)).astype(np.float32)
+    for win, ratio, ori in [(100, 0.9, True), (37, 0.75, False)]:
+        want = po.search_for_initialization(k1, d1, k2, d2, bounds, pm, win, ratio, ori)
+        got = pkg.search_for_initialization(k1, d1, k2, d2, bounds, pm, win, ratio, ori)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]) and got[2].tobytes() == want[2].tobytes()
+    # projection: random world points in front of / behind the camera, random validity, occupancy and stereo coordinates
+    s4 = po.tables()[0]
+    for mono, motion in [(True, 0.0), (False, 0.3), (False, -0.3), (False, 0.0)]:
+        Tl = np.eye(4, dtype=np.float32); Tc = np.eye(4, dtype=np.float32)
+        Tc[:3, 3] = [0.05, -0.02, motion]
+        z = rng.uniform(-2, 12, n1).astype(np.float32); z[np.abs(z) < 0.2] = 0.5
+        fx, fy, cx, cy = 500.0, 505.0, 320.0, 240.0
+        pw = np.stack([(k1["x"] - cx) * z / fx, (k1["y"] - cy) * z / fy, z], 1).astype(np.float32)
+        ur = np.where(rng.random(n2) < 0.5, k2["x"] - rng.uniform(0, 30, n2), -1.0).astype(np.float32)
+        args, keep = pkg.projection_args(pw, d1, rng.random(n1) < 0.8, rng.random(n1) < 0.6, k1["octave"], k1["angle"], Tl, k2, d2, ur,
+                                         rng.random(n2) < 0.1, Tc, (fx, fy, cx, cy), 40.0, 0.08, bounds, s4[0], 15.0 if mono else 7.0, mono)
+        want = po.search_by_projection(args); got = pkg.search_by_projection(args)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1])
+    # BoW: random vocabulary words, validity on both sides
+    def fv(n, words):
+        node = rng.integers(0, words, n)
+        ids = np.unique(node); start = [0]; idx = []
+        for i in ids:
+            idx.extend(np.nonzero(node == i)[0].tolist()); start.append(len(idx))
+        return ids.astype(np.uint32), np.array(start, np.int32), np.array(idx, np.uint32)
+    for words, strict in [(7, False), (90, True)]:
+        s1, keep1 = pkg.bow_side(d1, rng.random(n1) < 0.7, k1["angle"], *fv(n1, words))
+        s2, keep2 = pkg.bow_side(d2, rng.random(n2) < 0.7, k2["angle"], *fv(n2, words))
+        want = po.search_by_bow(s1, s2, 0.8, True, strict); got = pkg.search_by_bow(s1, s2, 0.8, True, strict)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
