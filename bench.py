@@ -433,7 +433,16 @@ def run_ours(args, rank, world, local_rank):
         traffic = tj["dram_bytes_per_frame"][dom] * frames_per_launch
         traffic_src = tj["source"]
     except Exception:
-        pass
+        tj = None
+    issue = None
+    if tj and "warp_instructions_per_frame" in tj and WORKLOAD.startswith("C1"):
+        # the bound this integer path actually runs against: executed warp instructions per frame (ncu, same capture)
+        # against the SMs' issue rate at the clock sampled during the timed region
+        wi = sum(tj["warp_instructions_per_frame"].values())
+        peak_issue = 148 * 4 * (clocks.get("sm_mhz") or 1965) * 1e6
+        issue = {"warp_instructions_per_frame": wi, "issue_peak_per_s": peak_issue,
+                 "achieved_per_s": value / world * wi, "frac": value / world * wi / peak_issue,
+                 "per_kernel": tj["warp_instructions_per_frame"], "source": tj["source"]}
     roofline = {
         "bound": "hbm", "kernel": {"pyramid": "k_resize_level (x%d levels)" % (p["nlevels"] - 1), "fast_cells": "k_fast_cells",
                                    "octree": "k_octree", "blur": "k_blur", "describe": "k_describe"}[dom],
@@ -448,6 +457,7 @@ def run_ours(args, rank, world, local_rank):
         "per_kernel": {k: {"bytes_per_frame": stage_bytes[k], "launch_ms": kstages[k] / chunks,
                            "achieved_gbs": stage_bytes[k] * frames_per_launch / (kstages[k] / chunks * 1e-3) / 1e9 if kstages[k] > 0 else 0.0}
                        for k in knames},
+        "issue_rate": issue,
         "path_bytes_per_frame": path_bytes,
         "path_achieved": value / world * path_bytes / 1e9, "path_frac": value / world * path_bytes / 1e9 / peak,
         "note": "launch_ms: CUDA events on the launching stream in a pass with the chunks serialised on one stream, run "
