@@ -619,10 +619,11 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     const float* Tc = a->Tcw_cur; const float* Tl = a->Tcw_last;
     for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = Tc[4 * r + c]; C.t[r] = Tc[4 * r + 3]; }
     float twc[3], tlc[3];
-    for (int i = 0; i < 3; ++i) {                              // -Rcw.t() * tcw: generic gemm path, double accumulation
-        double s = 0;
-        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + i] * (double)C.t[k];
-        twc[i] = (float)(s * -1.0);
+    for (int i = 0; i < 3; ++i) {                              // -Rcw.t() * tcw: cv::MatExpr negates a transposed COPY,
+        volatile float t = Tc[i] * C.t[0];                     // so this is gemm's 3x3 float case with alpha = -1
+        t = t + Tc[4 + i] * C.t[1];                            // (volatile: keep the host compiler from contracting)
+        t = t + Tc[8 + i] * C.t[2];
+        twc[i] = (float)((double)t * -1.0);
     }
     for (int i = 0; i < 3; ++i) {                              // Rlw * twc + tlw: 3x3 float case
         const float t = Tl[4 * i] * twc[0] + Tl[4 * i + 1] * twc[1] + Tl[4 * i + 2] * twc[2];

@@ -1,0 +1,2 @@
+// oracle/cvshim2 forwarding header -- TEST INFRASTRUCTURE (see opencv2/core/core.hpp)
+#include "opencv2/core/core.hpp"

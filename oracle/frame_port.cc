@@ -1,4 +1,4 @@
-// frame_port.cc -- TEST INFRASTRUCTURE (oracle), PARITY UNPINNED; see frame_port.h.
+// frame_port.cc -- TEST INFRASTRUCTURE (oracle); pinned against the reference's own code, see frame_port.h.
 #include "frame_port.h"
 
 #include <algorithm>
@@ -169,12 +169,14 @@ extern "C" int frameport_search_by_projection(const frameport_projection_args* a
     std::vector<int> rotHist[HISTO_LENGTH];
     const float* Tc = a->Tcw_cur; const float* Tl = a->Tcw_last;
     const float tcw[3] = {Tc[3], Tc[7], Tc[11]}, tlw[3] = {Tl[3], Tl[7], Tl[11]};
-    // twc = -Rcw.t() * tcw: cv::gemm with GEMM_1_T takes the generic path (double accumulation, alpha = -1)
+    // twc = -Rcw.t() * tcw (:1341): cv::operator-(MatExpr) materialises the transpose (MatOp::subtract has no MatOp_T
+    // override) and leaves "-1 * copy", so the product is cv::gemm(copy, tcw, alpha = -1, flags = 0): the small-matrix
+    // case, float products summed left to right, then (float)(t * -1.0).  Not a GEMM_1_T call (which would accumulate in
+    // double); pinned by tests/test_ref_frame.py against the reference's own code on a knife-edge pose.
     float twc[3];
     for (int i = 0; i < 3; ++i) {
-        double s = 0;
-        for (int k = 0; k < 3; ++k) s += (double)Tc[4 * k + i] * (double)tcw[k];
-        twc[i] = (float)(s * -1.0);
+        const float t = Tc[i] * tcw[0] + Tc[4 + i] * tcw[1] + Tc[8 + i] * tcw[2];
+        twc[i] = (float)((double)t * -1.0);
     }
     float tlc[3];
     mat3_mul_add(Tl, 4, twc, tlw, tlc);                       // :1347

@@ -4,10 +4,14 @@
  *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono) src/ORBmatcher.cc:1328-1470
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
- * PARITY UNPINNED: src/Frame.cc and src/ORBmatcher.cc need the whole ORB-SLAM2 header set (DBoW2, g2o, Eigen,
- * MapPoint/KeyFrame) and cannot be compiled here, and the reference has no tests for them.  The one library
- * arithmetic on this path -- cv::Mat "Rcw*x3Dw+tcw" = cv::gemm's 3x3 float special case -- was checked bit-equal
- * against cv2 4.13.0 (20 000 random cases).  Only tests/ may use this file; the product never does. */
+ * PINNED: the reference's own src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc and src/MapPoint.cc compile unchanged
+ * against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc, recipe in oracle/Makefile), and
+ * tests/test_ref_frame.py checks every function here bit-for-bit against them (real two-view scenes, randomised frames
+ * with ties / validity / occupancy, and a knife-edge pose for the bForward flag).  The one library arithmetic on this
+ * path -- the cv::Mat expressions "Rcw*x3Dw+tcw" and "-Rcw.t()*tcw" = cv::gemm's 3x3 float special case -- is pinned to
+ * cv2 4.13.0 golden vectors (tests/golden/gemm_golden.npz); how cv::MatExpr lowers "-R.t()*t" (a transposed COPY times
+ * -1, not GEMM_1_T) is restated from OpenCV's matrix_expressions.cpp, which cv2 cannot execute.
+ * Only tests/ may use this file; the product never does. */
 #ifndef ORACLE_FRAME_PORT_H
 #define ORACLE_FRAME_PORT_H
 #include <stdint.h>

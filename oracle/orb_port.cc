@@ -416,7 +416,7 @@ int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int 
 }  // extern "C"
 
 
-// ---- Frame::ComputeStereoMatches, src/Frame.cc:466-640 (PARITY UNPINNED: restatement only, see orb_port.h) --------
+// ---- Frame::ComputeStereoMatches, src/Frame.cc:466-640 (pinned by oracle/_ref/libframeref.so, see orb_port.h) --------
 namespace {
 inline int refl101(int i, int n)
 {

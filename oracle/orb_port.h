@@ -50,9 +50,9 @@ void orbport_match_bruteforce(const uint8_t* A, int nA, const uint8_t* B, int nB
 /* accepted-match count of one keyframe pair: best <= th_low && float(best) < ratio*float(second) */
 int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int th_low, float ratio);
 
-/* Frame::ComputeStereoMatches (src/Frame.cc:466-640).  PARITY UNPINNED for this function: src/Frame.cc needs
- * the whole ORB-SLAM2 header set (DBoW2 vocabulary templates, KeyFrame, MapPoint, cv::undistortPoints ...) and cannot
- * be compiled here, and the reference has no test for it; this is a line-by-line restatement only.
+/* Frame::ComputeStereoMatches (src/Frame.cc:466-640).  PINNED: the reference's own src/Frame.cc compiles
+ * unchanged against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc) and
+ * tests/test_ref_frame.py checks this restatement bit-for-bit against Frame::ComputeStereoMatches executed there.
  * lvlL/lvlR[l] = dense unblurred level l (w[l] x h[l], pitch w[l]) of the left / right pyramid; pixels outside a
  * level are its REFLECT_101 continuation (the 19-px frame of mvImagePyramid).  Outputs mvuRight / mvDepth [nL]. */
 void orbport_stereo_matches(const orbport_keypoint* kL, const uint8_t* dL, int nL, const orbport_keypoint* kR,

@@ -1,0 +1,403 @@
+// oracle/ref_frame_wrap.cc -- TEST INFRASTRUCTURE, not product code.
+//
+// C entry points around the UNMODIFIED reference translation units src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc,
+// src/MapPoint.cc, src/ORBextractor.cc and Thirdparty/DBoW2/DBoW2/{FeatureVector,BowVector}.cpp, which oracle/Makefile
+// compiles from where they lie under /root/reference against oracle/cvshim2 into oracle/_ref/libframeref.so.
+// This is what pins the SURVEY section-8(f) rows: the restatements in oracle/frame_port.cc / orb_port.cc and the CUDA
+// path are compared with what the reference's own code returns on the same inputs.
+//
+// The wrapper only builds the objects the reference functions expect (Frame / KeyFrame / MapPoint with their members
+// filled from plain arrays -- the same arrays the C ABI takes, include/orbgpu.h) and reads the results back:
+//   frameref_stereo_matches               Frame::ComputeStereoMatches                     src/Frame.cc:466-640
+//   frameref_features_in_area             Frame::AssignFeaturesToGrid + GetFeaturesInArea src/Frame.cc:230-245, 327-380
+//   frameref_search_for_initialization    ORBmatcher::SearchForInitialization             src/ORBmatcher.cc:405-520
+//   frameref_search_by_projection         ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  :1328-1470
+//   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
+//   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
+//   frameref_descriptor_distance / frameref_three_maxima   ORBmatcher::DescriptorDistance :1647-1663, ComputeThreeMaxima :1601-1642
+//   frameref_gemm3 / frameref_neg_rt_t    the shim's cv::gemm and "-R.t()*t" evaluation (golden-vector check)
+// Signatures mirror oracle/frame_port.h / orb_port.h so the tests run the same cases through both.
+// Symbols of the reference that none of these paths reaches (Map, KeyFrameDatabase, Converter) are defined here as
+// aborting stand-ins.  "private"/"protected" are opened for the reference headers in THIS file only (class layout is
+// unchanged) so the harness can fill members such as MapPoint::mDescriptor without running the whole SLAM system.
+#include <opencv2/core/core.hpp>
+#include <cstdio>
+#include <map>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#define private public
+#define protected public
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "KeyFrameDatabase.h"
+#include "Map.h"
+#include "MapPoint.h"
+#include "ORBmatcher.h"
+#include "ORBextractor.h"
+#undef private
+#undef protected
+
+#include "frame_port.h"
+
+using namespace ORB_SLAM2;
+
+namespace {
+[[noreturn]] void never(const char* what)
+{
+    std::fprintf(stderr, "oracle/ref_frame_wrap: %s is outside the tested paths\n", what);
+    std::abort();
+}
+}  // namespace
+
+// ---- reference symbols outside the tested paths ------------------------------------------------------------------------
+namespace ORB_SLAM2 {
+Map::Map() : mnMaxKFid(0), mnBigChangeIdx(0) {}
+void Map::EraseMapPoint(MapPoint*) { never("Map::EraseMapPoint"); }
+void Map::EraseKeyFrame(KeyFrame*) { never("Map::EraseKeyFrame"); }
+void KeyFrameDatabase::erase(KeyFrame*) { never("KeyFrameDatabase::erase"); }
+}  // namespace ORB_SLAM2
+#include "Converter.h"
+std::vector<cv::Mat> ORB_SLAM2::Converter::toDescriptorVector(const cv::Mat&) { never("Converter::toDescriptorVector"); }
+
+namespace {
+
+typedef orbport_keypoint KP;   // 28-byte cv::KeyPoint layout
+
+std::vector<cv::KeyPoint> to_keys(const KP* k, int n)
+{
+    std::vector<cv::KeyPoint> v((size_t)n);
+    static_assert(sizeof(cv::KeyPoint) == sizeof(KP), "cv::KeyPoint is a 28-byte POD");
+    if (n) std::memcpy((void*)v.data(), k, sizeof(KP) * (size_t)n);
+    return v;
+}
+
+cv::Mat desc_mat(const uint8_t* d, int n)
+{
+    cv::Mat m(n > 0 ? n : 1, 32, CV_8U);
+    if (n > 0) std::memcpy(m.data, d, (size_t)n * 32);
+    return n > 0 ? m : m.rowRange(0, 0);
+}
+
+cv::Mat pose_mat(const float* T16)
+{
+    cv::Mat m(4, 4, CV_32F);
+    std::memcpy(m.data, T16, 16 * sizeof(float));
+    return m;
+}
+
+// the static members Frame's constructors compute once (src/Frame.cc:96-115)
+void set_frame_statics(const float* bounds4, float fx, float fy, float cx, float cy)
+{
+    Frame::mnMinX = bounds4[0]; Frame::mnMaxX = bounds4[1]; Frame::mnMinY = bounds4[2]; Frame::mnMaxY = bounds4[3];
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+    Frame::fx = fx; Frame::fy = fy; Frame::cx = cx; Frame::cy = cy;
+    Frame::invfx = 1.0f / fx; Frame::invfy = 1.0f / fy;
+    Frame::mbInitialComputations = false;
+}
+
+// a Frame as its constructor leaves it, from plain arrays
+void fill_frame(Frame& F, const KP* keys_un, const uint8_t* desc, int n)
+{
+    F.N = n;
+    F.mvKeysUn = to_keys(keys_un, n);
+    F.mvKeys = F.mvKeysUn;
+    if (desc) F.mDescriptors = desc_mat(desc, n);
+    F.mvuRight.assign((size_t)n, -1.f);
+    F.mvDepth.assign((size_t)n, -1.f);
+    F.mvpMapPoints.assign((size_t)n, static_cast<MapPoint*>(NULL));
+    F.mvbOutlier.assign((size_t)n, false);
+    F.AssignFeaturesToGrid();
+}
+
+void set_scale_tables(Frame& F, const float* scale_factors, int nlevels)
+{
+    F.mnScaleLevels = nlevels;
+    F.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    F.mvInvScaleFactors.resize((size_t)nlevels);
+    F.mvLevelSigma2.resize((size_t)nlevels);
+    F.mvInvLevelSigma2.resize((size_t)nlevels);
+    for (int i = 0; i < nlevels; ++i) {
+        F.mvInvScaleFactors[i] = 1.0f / scale_factors[i];
+        F.mvLevelSigma2[i] = scale_factors[i] * scale_factors[i];
+        F.mvInvLevelSigma2[i] = 1.0f / F.mvLevelSigma2[i];
+    }
+    F.mfScaleFactor = nlevels > 1 ? scale_factors[1] : 1.2f;
+    F.mfLogScaleFactor = std::log(F.mfScaleFactor);
+}
+
+struct World {           // owns the MapPoints / KeyFrames of one call
+    Map map;
+    Frame anchor;        // reference frame handed to KeyFrame's constructor for the map points
+    KeyFrame* anchor_kf;
+    std::vector<MapPoint*> points;
+    std::vector<KeyFrame*> keyframes;
+    World() : anchor_kf(0)
+    {
+        anchor.N = 0;
+        anchor.mTcw = cv::Mat::eye(4, 4, CV_32F);
+        anchor.mnId = 0;
+        anchor.mbf = 1.f; anchor.mb = 1.f; anchor.mThDepth = 1.f; anchor.mTimeStamp = 0;
+        anchor.mnScaleLevels = 1; anchor.mfScaleFactor = 1.2f; anchor.mfLogScaleFactor = std::log(1.2f);
+        anchor_kf = new KeyFrame(anchor, &map, static_cast<KeyFrameDatabase*>(NULL));
+        keyframes.push_back(anchor_kf);
+    }
+    MapPoint* point(const float* xyz, const uint8_t* desc, int observations, bool bad)
+    {
+        cv::Mat pos(3, 1, CV_32F);
+        const float zero[3] = {0, 0, 0};
+        std::memcpy(pos.data, xyz ? xyz : zero, 3 * sizeof(float));
+        MapPoint* p = new MapPoint(pos, anchor_kf, &map);      // src/MapPoint.cc:32-44
+        if (desc) {
+            cv::Mat d(1, 32, CV_8U);
+            std::memcpy(d.data, desc, 32);
+            p->mDescriptor = d;                                   // what ComputeDistinctiveDescriptors would leave
+        }
+        p->nObs = observations;
+        p->mbBad = bad;
+        points.push_back(p);
+        return p;
+    }
+    ~World()
+    {
+        for (size_t i = 0; i < points.size(); ++i) delete points[i];
+        for (size_t i = 0; i < keyframes.size(); ++i) delete keyframes[i];
+    }
+};
+
+void fill_feature_vector(DBoW2::FeatureVector& fv, const frameport_bow_side* s)
+{
+    fv.clear();
+    for (int n = 0; n < s->n_nodes; ++n)
+        for (int k = s->node_start[n]; k < s->node_start[n + 1]; ++k) fv.addFeature(s->node_ids[n], s->indices[k]);
+}
+
+}  // namespace
+
+extern "C" {
+
+// d = alpha * op(A) * x + beta * c through the shim's cv::gemm (A 3x3, x and c 3x1, float); c may be NULL
+void frameref_gemm3(const float* A, const float* x, const float* c, double alpha, double beta, int flags, float* d)
+{
+    cv::Mat mA(3, 3, CV_32F, (void*)A), mx(3, 1, CV_32F, (void*)x), mc, out;
+    if (c) mc = cv::Mat(3, 1, CV_32F, (void*)c);
+    cv::cv_gemm32f(mA, mx, alpha, c ? &mc : 0, beta, out, flags);
+    for (int i = 0; i < 3; ++i) d[i] = out.at<float>(i);
+}
+
+// "-Rcw.t()*tcw" and "Rlw*twc+tlw" exactly as src/ORBmatcher.cc:1338-1346 writes them, through the shim's MatExpr
+void frameref_neg_rt_t(const float* Tcw16, const float* Tlw16, float* twc3, float* tlc3)
+{
+    const cv::Mat Tc = pose_mat(Tcw16), Tl = pose_mat(Tlw16);
+    const cv::Mat Rcw = Tc.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tcw = Tc.rowRange(0, 3).col(3);
+    const cv::Mat twc = -Rcw.t() * tcw;
+    const cv::Mat Rlw = Tl.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tlw = Tl.rowRange(0, 3).col(3);
+    const cv::Mat tlc = Rlw * twc + tlw;
+    for (int i = 0; i < 3; ++i) { twc3[i] = twc.at<float>(i); tlc3[i] = tlc.at<float>(i); }
+}
+
+int frameref_features_in_area(const KP* keys_un, int n, const float* bounds4, float x, float y, float r, int min_level,
+                              int max_level, int* out, int cap)
+{
+    set_frame_statics(bounds4, 1.f, 1.f, 0.f, 0.f);
+    Frame F;
+    fill_frame(F, keys_un, 0, n);
+    const std::vector<size_t> v = F.GetFeaturesInArea(x, y, r, min_level, max_level);
+    for (size_t i = 0; i < v.size() && (int)i < cap; ++i) out[i] = (int)v[i];
+    return (int)v.size();
+}
+
+int frameref_search_for_initialization(const KP* k1, const uint8_t* d1, int n1, const KP* k2, const uint8_t* d2, int n2,
+                                       const float* bounds4, float* prev_matched, int window_size, float nnratio,
+                                       int check_orientation, int* matches12)
+{
+    set_frame_statics(bounds4, 1.f, 1.f, 0.f, 0.f);
+    Frame F1, F2;
+    fill_frame(F1, k1, d1, n1);
+    fill_frame(F2, k2, d2, n2);
+    std::vector<cv::Point2f> prev((size_t)n1);
+    for (int i = 0; i < n1; ++i) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    const int nm = matcher.SearchForInitialization(F1, F2, prev, m12, window_size);
+    for (int i = 0; i < n1; ++i) {
+        matches12[i] = m12[i];
+        prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
+    }
+    return nm;
+}
+
+// cur_match: index of the last-frame map point CurrentFrame.mvpMapPoints[i2] ends up with, -1 where it is NULL or still
+// the entry's own (occupied) map point.  (The restatement's extra "-2 = reset by the rotation check" is not observable.)
+int frameref_search_by_projection(const frameport_projection_args* a, int* cur_match)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame Last, Cur;
+    set_scale_tables(Last, a->scale_factors, a->nlevels);
+    set_scale_tables(Cur, a->scale_factors, a->nlevels);
+
+    // LastFrame: N, mvpMapPoints, mvbOutlier, mvKeys[i].octave, mvKeysUn[i].angle, mTcw
+    Last.N = a->n_last;
+    Last.mvKeys.assign((size_t)a->n_last, cv::KeyPoint());
+    for (int i = 0; i < a->n_last; ++i) { Last.mvKeys[i].octave = a->last_octave[i]; Last.mvKeys[i].angle = a->last_angle[i]; }
+    Last.mvKeysUn = Last.mvKeys;
+    Last.mvpMapPoints.assign((size_t)a->n_last, static_cast<MapPoint*>(NULL));
+    Last.mvbOutlier.assign((size_t)a->n_last, false);
+    std::map<MapPoint*, int> index_of;
+    for (int i = 0; i < a->n_last; ++i) {
+        // mp_valid = map point present and not an outlier: alternate the two ways of being invalid
+        MapPoint* p = world.point(a->world_pos + 3 * i, a->mp_desc + 32 * i, a->mp_observed[i] ? 1 : 0, false);
+        index_of[p] = i;
+        if (a->mp_valid[i]) Last.mvpMapPoints[i] = p;
+        else if (i & 1) { Last.mvpMapPoints[i] = p; Last.mvbOutlier[i] = true; }
+    }
+    Last.SetPose(pose_mat(a->Tcw_last));
+
+    fill_frame(Cur, a->cur_keys_un, a->cur_desc, a->n_cur);
+    Cur.mvuRight.assign(a->cur_u_right, a->cur_u_right + a->n_cur);
+    Cur.mbf = a->bf; Cur.mb = a->b;
+    Last.mbf = a->bf; Last.mb = a->b;
+    const float origin[3] = {0, 0, 0};
+    for (int i = 0; i < a->n_cur; ++i)
+        if (a->cur_occupied[i]) Cur.mvpMapPoints[i] = world.point(origin, 0, 1, false);
+    Cur.SetPose(pose_mat(a->Tcw_cur));
+
+    ORBmatcher matcher(0.9f, a->check_orientation != 0);
+    const int nm = matcher.SearchByProjection(Cur, Last, a->th, a->mono != 0);
+    for (int i = 0; i < a->n_cur; ++i) {
+        MapPoint* p = Cur.mvpMapPoints[i];
+        std::map<MapPoint*, int>::const_iterator it = p ? index_of.find(p) : index_of.end();
+        cur_match[i] = it == index_of.end() ? -1 : it->second;
+    }
+    return nm;
+}
+
+// strict_th_low = 0: SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches)   (side 1 = pKF, side 2 = F)
+// strict_th_low = 1: SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12)
+int frameref_search_by_bow(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
+                           int strict_th_low, int* match12, int* match21)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, 1.f, 1.f, 0.f, 0.f);
+    World world;
+    const float origin[3] = {0, 0, 0};
+    const frameport_bow_side* sides[2] = {s1, s2};
+    Frame F[2];
+    KeyFrame* KF[2] = {0, 0};
+    std::map<MapPoint*, int> index_of[2];
+    for (int s = 0; s < 2; ++s) {
+        const frameport_bow_side* sd = sides[s];
+        std::vector<KP> keys((size_t)sd->n);
+        for (int i = 0; i < sd->n; ++i) {
+            std::memset(&keys[i], 0, sizeof(KP));
+            keys[i].x = 10.f + (float)(i % 600); keys[i].y = 10.f + (float)(i % 400);
+            keys[i].angle = sd->angle[i];
+        }
+        fill_frame(F[s], keys.data(), sd->desc, sd->n);
+        F[s].mTcw = cv::Mat::eye(4, 4, CV_32F);
+        F[s].mbf = 1.f; F[s].mb = 1.f; F[s].mThDepth = 1.f; F[s].mTimeStamp = 0; F[s].mnId = (unsigned long)(s + 1);
+        F[s].mnScaleLevels = 1; F[s].mfScaleFactor = 1.2f; F[s].mfLogScaleFactor = std::log(1.2f);
+        fill_feature_vector(F[s].mFeatVec, sd);
+        const bool as_keyframe = s == 0 || strict_th_low;
+        if (!as_keyframe) continue;
+        for (int i = 0; i < sd->n; ++i) {
+            // valid = map point present and not bad: alternate the two ways of being invalid
+            const bool valid = !sd->valid || sd->valid[i];
+            if (valid || (i & 1)) {
+                MapPoint* p = world.point(origin, sd->desc + 32 * (size_t)i, 1, !valid);
+                F[s].mvpMapPoints[i] = p;
+                index_of[s][p] = i;
+            }
+        }
+        KF[s] = new KeyFrame(F[s], &world.map, static_cast<KeyFrameDatabase*>(NULL));   // src/KeyFrame.cc:34-60
+        world.keyframes.push_back(KF[s]);
+    }
+    for (int i = 0; i < s1->n; ++i) match12[i] = -1;
+    for (int i = 0; i < s2->n; ++i) match21[i] = -1;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    int nm;
+    if (!strict_th_low) {
+        std::vector<MapPoint*> matches;
+        nm = matcher.SearchByBoW(KF[0], F[1], matches);
+        for (int i2 = 0; i2 < s2->n; ++i2)
+            if (matches[i2]) { const int i1 = index_of[0][matches[i2]]; match21[i2] = i1; match12[i1] = i2; }
+    } else {
+        std::vector<MapPoint*> matches;
+        nm = matcher.SearchByBoW(KF[0], KF[1], matches);
+        for (int i1 = 0; i1 < s1->n; ++i1)
+            if (matches[i1]) { const int i2 = index_of[1][matches[i1]]; match12[i1] = i2; match21[i2] = i1; }
+    }
+    return nm;
+}
+
+// Frame::ComputeStereoMatches on caller-provided keypoints, descriptors and UNBLURRED pyramid levels (dense rows).
+// nlevels = number of entries of lvlL / lvlR / w / h / scale / inv_scale.
+void frameref_stereo_matches(const KP* kL, const uint8_t* dL, int nL, const KP* kR, const uint8_t* dR, int nR,
+                             const uint8_t* const* lvlL, const uint8_t* const* lvlR, const int* w, const int* h,
+                             const float* scale, const float* inv_scale, int nlevels, float bf, float b, float* u_right,
+                             float* depth)
+{
+    ORBextractor exL(1000, scale[nlevels > 1 ? 1 : 0], nlevels, 20, 7), exR(1000, scale[nlevels > 1 ? 1 : 0], nlevels, 20, 7);
+    exL.mvImagePyramid.resize((size_t)nlevels);
+    exR.mvImagePyramid.resize((size_t)nlevels);
+    for (int l = 0; l < nlevels; ++l) {
+        exL.mvImagePyramid[l] = cv::Mat(h[l], w[l], CV_8U, (void*)lvlL[l]);
+        exR.mvImagePyramid[l] = cv::Mat(h[l], w[l], CV_8U, (void*)lvlR[l]);
+    }
+    Frame F;
+    F.mpORBextractorLeft = &exL; F.mpORBextractorRight = &exR;
+    F.N = nL;
+    F.mvKeys = to_keys(kL, nL);
+    F.mvKeysRight = to_keys(kR, nR);
+    F.mDescriptors = desc_mat(dL, nL);
+    F.mDescriptorsRight = desc_mat(dR, nR);
+    F.mvScaleFactors.assign(scale, scale + nlevels);
+    F.mvInvScaleFactors.assign(inv_scale, inv_scale + nlevels);
+    F.mbf = bf; F.mb = b;
+    F.ComputeStereoMatches();
+    for (int i = 0; i < nL; ++i) { u_right[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+}
+
+// ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663) on two 32-byte descriptors
+int frameref_descriptor_distance(const uint8_t* a, const uint8_t* b)
+{
+    cv::Mat ma(1, 32, CV_8U, (void*)a), mb(1, 32, CV_8U, (void*)b);
+    return ORBmatcher::DescriptorDistance(ma, mb);
+}
+
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) on a histogram given by its bin sizes
+void frameref_three_maxima(const int* bin_sizes, int L, int* ind3)
+{
+    std::vector<std::vector<int> > histo((size_t)L);
+    for (int i = 0; i < L; ++i) histo[i].assign((size_t)bin_sizes[i], 0);
+    ORBmatcher matcher(0.6f, true);
+    ind3[0] = ind3[1] = ind3[2] = -1;
+    matcher.ComputeThreeMaxima(histo.data(), L, ind3[0], ind3[1], ind3[2]);
+}
+
+// Frame::UndistortKeyPoints (and, with bounds4 != NULL, Frame::ComputeImageBounds on a w x h image)
+void frameref_undistort_keypoints(const KP* keys, int n, const float* K4, const float* dist, int ndist, int w, int h,
+                                  KP* keys_un, float* bounds4)
+{
+    Frame F;
+    F.N = n;
+    F.mvKeys = to_keys(keys, n);
+    F.mK = cv::Mat::eye(3, 3, CV_32F);
+    F.mK.at<float>(0, 0) = K4[0]; F.mK.at<float>(1, 1) = K4[1]; F.mK.at<float>(0, 2) = K4[2]; F.mK.at<float>(1, 2) = K4[3];
+    F.mDistCoef = cv::Mat(ndist, 1, CV_32F);
+    for (int i = 0; i < ndist; ++i) F.mDistCoef.at<float>(i) = dist[i];
+    F.UndistortKeyPoints();
+    if (n) std::memcpy(keys_un, F.mvKeysUn.data(), sizeof(KP) * (size_t)n);
+    if (bounds4) {
+        cv::Mat im(h, w, CV_8U);
+        F.ComputeImageBounds(im);
+        bounds4[0] = Frame::mnMinX; bounds4[1] = Frame::mnMaxX; bounds4[2] = Frame::mnMinY; bounds4[3] = Frame::mnMaxY;
+    }
+}
+
+}  // extern "C"

@@ -213,7 +213,35 @@ def make_undistort():
     print("undistort_golden.npz written")
 
 
+def make_gemm():
+    """cv2.gemm on 3x3 * 3x1 CV_32F, the shapes of the pose arithmetic in ORBmatcher::SearchByProjection
+    (src/ORBmatcher.cc:1338-1361: Rcw*x3Dw+tcw, -Rcw.t()*tcw): alpha*A*x + beta*c with and without GEMM_1_T."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(777)
+    n = 4000
+    A = rng.normal(0, 1, (n, 3, 3)).astype(np.float32)
+    for i in range(0, n, 2):                                             # half of them near-rotations, as in a pose
+        q, _ = np.linalg.qr(rng.normal(0, 1, (3, 3)))
+        A[i] = (q + rng.normal(0, 1e-4, (3, 3))).astype(np.float32)
+    x = (rng.normal(0, 1, (n, 3)) * rng.choice([0.01, 1.0, 30.0], (n, 1))).astype(np.float32)
+    c = (rng.normal(0, 1, (n, 3)) * rng.choice([0.01, 1.0, 30.0], (n, 1))).astype(np.float32)
+    out = {"A": A, "x": x, "c": c}
+    for key, alpha, beta, flags in [("ax_plus_c", 1.0, 1.0, 0), ("neg_ax", -1.0, 0.0, 0), ("neg_atx", -1.0, 0.0, cv2.GEMM_1_T),
+                                    ("atx_plus_c", 1.0, 1.0, cv2.GEMM_1_T)]:
+        r = np.zeros((n, 3), np.float32)
+        for i in range(n):
+            cc = c[i].reshape(3, 1) if beta != 0 else None
+            r[i] = cv2.gemm(A[i], x[i].reshape(3, 1), alpha, cc, beta, flags=flags).reshape(3)
+        out[key] = r
+    np.savez_compressed(os.path.join(HERE, "gemm_golden.npz"), **out)
+    print("gemm_golden.npz written")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "gemm":
+        make_gemm()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gray":
         make_gray()
         sys.exit(0)

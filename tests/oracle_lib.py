@@ -3,6 +3,9 @@
 OraclePort  -> oracle/_build/liborbport.so  (our restatement, always buildable)
 OracleRef   -> oracle/_ref/liborbref.so     (the unmodified reference extractor; built in the dev
                                              container where /root/reference exists, travels prebuilt)
+OracleFrameRef -> oracle/_ref/libframeref.so (the unmodified reference Frame.cc / ORBmatcher.cc / KeyFrame.cc /
+                                             MapPoint.cc behind oracle/ref_frame_wrap.cc; same methods as the
+                                             frame-side restatements of OraclePort)
 """
 import ctypes as C
 import os
@@ -14,6 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE = os.path.join(ROOT, "oracle")
 PORT_SO = os.path.join(ORACLE, "_build", "liborbport.so")
 REF_SO = os.path.join(ORACLE, "_ref", "liborbref.so")
+FRAME_REF_SO = os.path.join(ORACLE, "_ref", "libframeref.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
@@ -140,7 +144,7 @@ class OraclePort:
         return bi, b1, b2
 
     def stereo_matches(self, kL, dL, kR, dR, lvlL, lvlR, bf, b):
-        """Frame::ComputeStereoMatches restated (parity unpinned, oracle/orb_port.h) -> (mvuRight, mvDepth)."""
+        """Frame::ComputeStereoMatches restated (oracle/orb_port.h; pinned by tests/test_ref_frame.py) -> (mvuRight, mvDepth)."""
         nl = self.nlevels
         lvlL = [np.ascontiguousarray(a, np.uint8) for a in lvlL]; lvlR = [np.ascontiguousarray(a, np.uint8) for a in lvlR]
         pl = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlL]); pr = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlR])
@@ -154,7 +158,7 @@ class OraclePort:
                                       _ptr(sc), _ptr(isc), bf, b, _ptr(u), _ptr(d))
         return u[:len(kL)].copy(), d[:len(kL)].copy()
 
-    # ---- frame_port.cc (parity unpinned restatements of src/Frame.cc / src/ORBmatcher.cc searches) ----
+    # ---- frame_port.cc (restatements of src/Frame.cc / src/ORBmatcher.cc searches; pinned by tests/test_ref_frame.py) ----
     def features_in_area(self, keys_un, bounds, x, y, r, min_level=-1, max_level=-1):
         k = np.ascontiguousarray(keys_un); b4 = np.ascontiguousarray(bounds, np.float32)
         out = _i32(len(k))
@@ -278,3 +282,103 @@ class OracleRef:
         sec = self.L.orbref_bench(_ptr(frames), n, w, h, frames.strides[0], nf, sc, nl, ini, mn, threads, reps,
                                   C.byref(tot))
         return sec, tot.value
+
+
+def have_frame_ref():
+    return os.path.exists(FRAME_REF_SO)
+
+
+class OracleFrameRef:
+    """The unmodified reference Frame / ORBmatcher code (oracle/ref_frame_wrap.cc).  Method names and results follow the
+    frame-side methods of OraclePort so a test can run one case through both."""
+
+    def __init__(self, scale_tables=None):
+        L = self.L = C.CDLL(FRAME_REF_SO)
+        L.frameref_gemm3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_void_p]
+        L.frameref_neg_rt_t.argtypes = [C.c_void_p] * 4
+        L.frameref_features_in_area.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int,
+                                                C.c_int, C.c_void_p, C.c_int]
+        L.frameref_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                         C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.frameref_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.frameref_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                                   C.c_void_p, C.c_void_p]
+        L.frameref_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameref_three_maxima.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        self.scale_tables = scale_tables     # (scale, inv_scale) float32 arrays, for stereo_matches
+
+    def descriptor_distance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return self.L.frameref_descriptor_distance(_ptr(a), _ptr(b))
+
+    def three_maxima(self, sizes):
+        s = np.ascontiguousarray(sizes, np.int32); out = _i32(3)
+        self.L.frameref_three_maxima(_ptr(s), len(s), _ptr(out))
+        return tuple(int(v) for v in out)
+
+    def gemm3(self, A, x, c=None, alpha=1.0, beta=1.0, flags=0):
+        A = np.ascontiguousarray(A, np.float32); x = np.ascontiguousarray(x, np.float32)
+        c = None if c is None else np.ascontiguousarray(c, np.float32)
+        d = np.zeros(3, np.float32)
+        self.L.frameref_gemm3(_ptr(A), _ptr(x), None if c is None else _ptr(c), alpha, beta, flags, _ptr(d))
+        return d
+
+    def neg_rt_t(self, Tcw, Tlw):
+        Tcw = np.ascontiguousarray(Tcw, np.float32); Tlw = np.ascontiguousarray(Tlw, np.float32)
+        twc = np.zeros(3, np.float32); tlc = np.zeros(3, np.float32)
+        self.L.frameref_neg_rt_t(_ptr(Tcw), _ptr(Tlw), _ptr(twc), _ptr(tlc))
+        return twc, tlc
+
+    def features_in_area(self, keys_un, bounds, x, y, r, min_level=-1, max_level=-1):
+        k = np.ascontiguousarray(keys_un); b4 = np.ascontiguousarray(bounds, np.float32)
+        out = _i32(len(k))
+        n = self.L.frameref_features_in_area(_ptr(k), len(k), _ptr(b4), x, y, r, min_level, max_level, _ptr(out), len(out))
+        return out[:n].copy()
+
+    def search_for_initialization(self, k1, d1, k2, d2, bounds, prev_matched, window_size=100, nnratio=0.9, check_orientation=True):
+        k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+        d1 = np.ascontiguousarray(d1, np.uint8); d2 = np.ascontiguousarray(d2, np.uint8)
+        b4 = np.ascontiguousarray(bounds, np.float32)
+        pm = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+        m12 = _i32(len(k1))
+        nm = self.L.frameref_search_for_initialization(_ptr(k1), _ptr(d1), len(k1), _ptr(k2), _ptr(d2), len(k2), _ptr(b4),
+                                                       _ptr(pm), window_size, nnratio, int(check_orientation), _ptr(m12))
+        return nm, m12[:len(k1)].copy(), pm
+
+    def search_by_projection(self, args):
+        """-> (nmatches, cur_match) with cur_match[i2] = last-frame index or -1 (the restatement's -2 reads as -1 here)."""
+        cm = _i32(args.n_cur)
+        nm = self.L.frameref_search_by_projection(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
+
+    def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
+        m12 = _i32(side1.n); m21 = _i32(side2.n)
+        nm = self.L.frameref_search_by_bow(C.byref(side1), C.byref(side2), nnratio, int(check_orientation), int(strict_th_low),
+                                           _ptr(m12), _ptr(m21))
+        return nm, m12[:side1.n].copy(), m21[:side2.n].copy()
+
+    def stereo_matches(self, kL, dL, kR, dR, lvlL, lvlR, bf, b):
+        nl = len(lvlL)
+        lvlL = [np.ascontiguousarray(a, np.uint8) for a in lvlL]; lvlR = [np.ascontiguousarray(a, np.uint8) for a in lvlR]
+        pl = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlL]); pr = (C.c_void_p * nl)(*[a.ctypes.data for a in lvlR])
+        w = np.array([a.shape[1] for a in lvlL], np.int32); h = np.array([a.shape[0] for a in lvlL], np.int32)
+        sc = np.ascontiguousarray(self.scale_tables[0], np.float32); isc = np.ascontiguousarray(self.scale_tables[1], np.float32)
+        kL = np.ascontiguousarray(kL); kR = np.ascontiguousarray(kR)
+        dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+        u = np.zeros(max(len(kL), 1), np.float32); d = np.zeros(max(len(kL), 1), np.float32)
+        self.L.frameref_stereo_matches(_ptr(kL), _ptr(dL), len(kL), _ptr(kR), _ptr(dR), len(kR), pl, pr, _ptr(w), _ptr(h),
+                                       _ptr(sc), _ptr(isc), nl, bf, b, _ptr(u), _ptr(d))
+        return u[:len(kL)].copy(), d[:len(kL)].copy()
+
+    def undistort_keypoints(self, keys, K4, dist, w=0, h=0):
+        """Frame::UndistortKeyPoints (+ ComputeImageBounds when w, h > 0) -> (mvKeysUn, bounds or None)."""
+        k = np.ascontiguousarray(keys); out = k.copy()
+        K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+        b4 = np.zeros(4, np.float32)
+        self.L.frameref_undistort_keypoints(_ptr(k), len(k), _ptr(K4), _ptr(dist), len(dist), w, h, _ptr(out),
+                                            _ptr(b4) if w > 0 else None)
+        return out, (b4 if w > 0 else None)

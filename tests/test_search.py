@@ -1,8 +1,8 @@
 """Grid-gated searches between two frames: Frame::GetFeaturesInArea (src/Frame.cc:327-380),
 ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520), ORBmatcher::SearchByProjection(Frame, Frame)
-(src/ORBmatcher.cc:1328-1470).  The oracle (oracle/frame_port.cc) is PARITY UNPINNED (the reference files cannot be
-compiled here and have no tests): CPU tests check it against the geometry of a synthetic two-view scene and a
-brute-force window search, GPU tests check the device path bit-for-bit against it."""
+(src/ORBmatcher.cc:1328-1470).  The oracle restatement (oracle/frame_port.cc) is pinned bit-for-bit against the reference's
+own code in tests/test_ref_frame.py (oracle/_ref/libframeref.so); the CPU tests here check it against the geometry of a
+synthetic two-view scene and a brute-force window search, the GPU tests check the device path bit-for-bit against it."""
 import numpy as np
 import pytest
 
@@ -253,6 +253,55 @@ def test_device_search_by_bow_equals_oracle(pkg, oracle, kf_kf):
 
 
 # --------------------------------------------------------------------------------------------- randomised stress
+def knife_edge_projection_args(pkg, port):
+    """A pair of poses whose tlc.z differs in the last bit between the float evaluation of "-Rcw.t()*tcw" (what
+    cv::MatExpr does, src/ORBmatcher.cc:1341) and a double-accumulating one; the baseline b is set to the smaller value so
+    that bForward = tlc.z > b holds for one evaluation only.  -> (args, keepalive, (Tcw_cur, Tcw_last, tlc.z in float))"""
+    f32 = np.float32
+    rng = np.random.default_rng(2024)
+    for _ in range(20000):
+        q, _ = np.linalg.qr(rng.normal(0, 1, (3, 3)))
+        Tc = np.eye(4, dtype=f32); Tc[:3, :3] = q.astype(f32); Tc[:3, 3] = rng.normal(0, 0.5, 3).astype(f32)
+        q2, _ = np.linalg.qr(rng.normal(0, 1, (3, 3)))
+        Tl = np.eye(4, dtype=f32); Tl[:3, :3] = q2.astype(f32); Tl[:3, 3] = rng.normal(0, 0.5, 3).astype(f32)
+        R, t = Tc[:3, :3], Tc[:3, 3]
+        twc_f = np.array([-f32(f32(f32(R[0, i] * t[0]) + f32(R[1, i] * t[1])) + f32(R[2, i] * t[2])) for i in range(3)], f32)
+        twc_d = (-(R.astype(np.float64).T @ t.astype(np.float64))).astype(f32)
+
+        def tlc_z(twc):
+            r = Tl[2, :3]
+            s = f32(f32(f32(r[0] * twc[0]) + f32(r[1] * twc[1])) + f32(r[2] * twc[2]))
+            return f32(np.float64(s) + np.float64(Tl[2, 3]))
+        zf, zd = tlc_z(twc_f), tlc_z(twc_d)
+        if zf != zd and min(zf, zd) > 0.05:
+            break
+    else:
+        raise AssertionError("no knife-edge pose found")
+    b = float(min(zf, zd))
+    rng = np.random.default_rng(3)
+    pool = rng.integers(0, 256, (30, 32), dtype=np.uint8)
+    n1, n2 = 1200, 1200
+    k1, d1 = random_frame(rng, n1, 640, 480, pool); k2, d2 = random_frame(rng, n2, 640, 480, pool)
+    fx, fy, cx, cy = 500.0, 505.0, 320.0, 240.0
+    z = rng.uniform(2, 12, n1)                    # world points that project into the current image
+    pc = np.stack([(k1["x"] - cx) * z / fx, (k1["y"] - cy) * z / fy, z], 1)
+    pw = ((pc - Tc[:3, 3].astype(np.float64)) @ Tc[:3, :3].astype(np.float64)).astype(f32)
+    s4 = port.tables()[0]
+    args, keep = pkg.projection_args(pw, d1, np.ones(n1, bool), np.ones(n1, bool), k1["octave"], k1["angle"], Tl, k2, d2,
+                                     -np.ones(n2, f32), np.zeros(n2, bool), Tc, (fx, fy, cx, cy), 40.0, b,
+                                     (0.0, 640.0, 0.0, 480.0), s4[0], 15.0, False)
+    return args, keep, (Tc, Tl, zf)
+
+
+@pytest.mark.gpu
+def test_device_search_by_projection_forward_flag_on_a_knife_edge(pkg, oracle):
+    """The host side of orbgpu_search_by_projection forms tlc with cv::MatExpr's arithmetic (float "-R.t()*t")."""
+    po = oracle.OraclePort()
+    args, keep, _ = knife_edge_projection_args(pkg, po)
+    want = po.search_by_projection(args); got = pkg.search_by_projection(args)
+    assert want[0] > 20 and got[0] == want[0] and np.array_equal(got[1], want[1])
+
+
 def random_frame(rng, n, w, h, pool):
     """Keypoints anywhere in and slightly outside the image bounds (undistortion can push them out, src/Frame.cc:387),
     all octaves, descriptors drawn from a small pool with a few flipped bits (many ties and competing queries)."""

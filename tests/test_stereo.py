@@ -1,7 +1,7 @@
 """Frame::ComputeStereoMatches (reference src/Frame.cc:466-640), SURVEY.md section 8(f) first "next" row.
-The oracle restatement is PARITY UNPINNED (src/Frame.cc cannot be compiled here and the reference has no test
-for it): the CPU test checks the restatement against the geometry of a synthetic rectified pair, the GPU test
-checks the device kernel bit-for-bit against the restatement."""
+The oracle restatement is pinned bit-for-bit against the reference's own Frame::ComputeStereoMatches in
+tests/test_ref_frame.py (oracle/_ref/libframeref.so); the CPU test here checks it against the geometry of a synthetic
+rectified pair, the GPU test checks the device kernel bit-for-bit against the restatement."""
 import numpy as np
 import pytest
 
