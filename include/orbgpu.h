@@ -178,6 +178,33 @@ typedef struct orbgpu_projection_args {
  * last-frame keypoint i, -2 set and then reset to NULL by the rotation-consistency check.  *nmatches = return value. */
 int orbgpu_search_by_projection(int device, const orbgpu_projection_args* args, int32_t* cur_match, int* nmatches);
 
+/* ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th) (src/ORBmatcher.cc:44-125): the
+ * local-map search of Tracking::SearchLocalPoints (src/Tracking.cc:1150-1200), run on every tracked frame.  The map
+ * points arrive as the plain arrays Frame::isInFrustum (src/Frame.cc:269-325, stays host) left in them. */
+typedef struct orbgpu_local_points_args {
+    int32_t n_points;
+    const uint8_t* in_view;        /* pMP->mbTrackInView && !pMP->isBad() */
+    const float* proj_x;           /* pMP->mTrackProjX */
+    const float* proj_y;           /* pMP->mTrackProjY */
+    const float* proj_xr;          /* pMP->mTrackProjXR */
+    const int32_t* scale_level;    /* pMP->mnTrackScaleLevel, 0 <= level < nlevels where in_view */
+    const float* view_cos;         /* pMP->mTrackViewCos */
+    const uint8_t* mp_desc;        /* n_points x 32: pMP->GetDescriptor() */
+    const uint8_t* mp_observed;    /* pMP->Observations() > 0 */
+    int32_t n_cur;
+    const orbgpu_keypoint* cur_keys_un;   /* F.mvKeysUn */
+    const uint8_t* cur_desc;       /* F.mDescriptors */
+    const float* cur_u_right;      /* F.mvuRight */
+    const uint8_t* cur_occupied;   /* F.mvpMapPoints[idx] && ->Observations() > 0, on entry */
+    float bounds[4];               /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;    /* F.mvScaleFactors[nlevels] */
+    int32_t nlevels;
+    float th;
+    float nnratio;                 /* mfNNratio */
+} orbgpu_local_points_args;
+/* cur_match[n_cur]: -1 untouched, i >= 0: F.mvpMapPoints[idx] was set to vpMapPoints[i].  *nmatches = return value. */
+int orbgpu_search_local_points(int device, const orbgpu_local_points_args* args, int32_t* cur_match, int* nmatches);
+
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
  * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order

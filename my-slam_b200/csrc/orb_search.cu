@@ -2,6 +2,7 @@
 //   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea     src/Frame.cc:230-245, 327-391
 //   ORBmatcher::SearchForInitialization                             src/ORBmatcher.cc:405-520
 //   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  src/ORBmatcher.cc:1328-1470
+//   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)  src/ORBmatcher.cc:44-125 (local-map search)
 //
 // Device layout.  The 64 x 48 grid of the searched frame is a counting sort of its keypoint indices by cell id
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
@@ -83,13 +84,39 @@ __global__ void __launch_bounds__(1024) k_grid_build(GridDev G)
     G.cell_start[3 * t] = base; G.cell_start[3 * t + 1] = base + c0; G.cell_start[3 * t + 2] = base + c0 + c1;
     if (t == 1023) G.cell_start[GRID_CELLS] = s_part[1023];
     __syncthreads();
-    // position inside the cell = number of earlier keypoints of the same cell (keeps the push_back order)
+    // Order inside a cell = index order (the push_back order of AssignFeaturesToGrid).  Keys are dropped into their
+    // cell's range in arrival order, then every short range is put in index order by one thread; a range too long for
+    // that takes, per key, its rank = number of earlier keys of the same cell.
     for (int i = t; i < G.n; i += 1024) {
         const int c = s_cell[i];
-        if (c < 0) continue;
-        int rank = 0;
-        for (int j = 0; j < i; ++j) rank += s_cell[j] == c;
-        G.sorted[s_cnt[c] + rank] = i;
+        if (c >= 0) G.sorted[atomicAdd(&s_cnt[c], 1)] = i;       // s_cnt[c] runs from the cell's start to its end
+    }
+    __syncthreads();
+    const int len3[3] = {c0, c1, c2};
+    bool any_long = false;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int len = len3[k], start = s_cnt[3 * t + k] - len;
+        if (len < 2) continue;
+        if (len > 48) { any_long = true; continue; }
+        int* a = G.sorted + start;
+        for (int x = 1; x < len; ++x) {                          // insertion sort of a handful of indices
+            const int v = a[x];
+            int y = x - 1;
+            for (; y >= 0 && a[y] > v; --y) a[y + 1] = a[y];
+            a[y + 1] = v;
+        }
+    }
+    if (__syncthreads_or(any_long)) {
+        for (int i = t; i < G.n; i += 1024) {
+            const int c = s_cell[i];
+            if (c < 0) continue;
+            const int end = s_cnt[c], start = G.cell_start[c];
+            if (end - start <= 48) continue;
+            int rank = 0;
+            for (int j = 0; j < i; ++j) rank += s_cell[j] == c;
+            G.sorted[start + rank] = i;
+        }
     }
 }
 
@@ -220,6 +247,27 @@ __device__ ResolveStage stage_lists(unsigned char* smem, size_t used, const uint
     return S;
 }
 
+// ---- the speculative in-order walk ---------------------------------------------------------------------------------
+// The reference visits the queries strictly in index order because an accepted match changes what later queries may
+// take (vMatchedDistance / mvpMapPoints occupancy).  Warp 0 keeps that order exactly but works on 32 consecutive queries
+// at a time, one per lane: every lane scans its own candidate list against the committed state and decides; the
+// features the deciding lanes would take are posted in `taker` (lowest lane per feature, found with match.any, so a byte
+// per feature and no atomics).  Taking a feature only ever removes it from later queries' eligible sets, and a query's
+// decision depends on its eligible set only through its best and second-best candidate, so a lane may have decided on
+// stale state -- and is invalid -- only when an EARLIER lane posted its best or its second-best feature.  The lanes
+// before the first invalid one are committed together (their scans saw exactly the state the sequential loop would have
+// shown them), and the window restarts at the first invalid query.  Lane 0 is never invalid, so every pass commits at
+// least one query; scenes without contention commit 32 per pass.
+#define TAKER_NONE 64
+
+// posts `lane` in taker[take] for the lowest lane among those that want the same feature
+__device__ __forceinline__ void post_taker(unsigned char* taker, bool wants, int take, int lane)
+{
+    const unsigned same = __match_any_sync(0xffffffffu, wants ? take : -1 - lane);
+    if (wants && (same & ((1u << lane) - 1u)) == 0) taker[take] = (unsigned char)lane;
+    __syncwarp();
+}
+
 // SearchForInitialization, the loop over i1 (src/ORBmatcher.cc:418-484) on the candidate lists.
 // accepted[i1] = bestIdx2 at the moment i1 was accepted (feeds rotHist), else -1.
 __global__ void __launch_bounds__(RESOLVE_THREADS) k_init_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
@@ -228,49 +276,59 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_init_resolve(const uint32_t
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int t = threadIdx.x;
-    unsigned short* matched_dist = reinterpret_cast<unsigned short*>(smem);          // vMatchedDistance, 0xFFFF = INT_MAX
-    short* matches21 = reinterpret_cast<short*>(smem + sizeof(short) * (size_t)n2);   // vnMatches21
-    for (int i = t; i < n2; i += RESOLVE_THREADS) { matched_dist[i] = 0xFFFFu; matches21[i] = -1; }
+    unsigned short* matched_dist = reinterpret_cast<unsigned short*>(smem);                            // vMatchedDistance, 0xFFFF = INT_MAX
+    short* matches21 = reinterpret_cast<short*>(smem + 2 * (size_t)n2);                                // vnMatches21
+    unsigned char* taker = smem + 4 * (size_t)n2;
+    for (int i = t; i < n2; i += RESOLVE_THREADS) { taker[i] = TAKER_NONE; matched_dist[i] = 0xFFFFu; matches21[i] = -1; }
     for (int i = t; i < n1; i += RESOLVE_THREADS) { matches12[i] = -1; accepted[i] = -1; }
-    const ResolveStage S = stage_lists(smem, 2 * sizeof(short) * (size_t)n2, cand, cand_n, cap, n1);
+    const ResolveStage S = stage_lists(smem, (5 * (size_t)n2 + 15) & ~(size_t)15, cand, cand_n, cap, n1);
     if (t >= 32) return;
     const int lane = t;
     int nmatches = 0;
-    for (int qb = 0; qb < n1; qb += 32) {
-        unsigned todo = __ballot_sync(0xffffffffu, qb + lane < n1 && S.cnt[qb + lane] != 0);
-        while (todo) {
-            const int i1 = qb + __ffs(todo) - 1;
-            todo &= todo - 1;
-            const int cnt = S.cnt[i1];
-            const uint32_t* c = S.base + S.off[i1];
-            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;       // (dist << 16) | position: earliest candidate wins ties
-            for (int p = lane; p < cnt; p += 32) {
-                const uint32_t e = c[p];
-                const unsigned dist = e & ((1u << CAND_DIST_BITS) - 1u);
-                if ((unsigned)matched_dist[e >> CAND_DIST_BITS] <= dist) continue;      // :444-445
-                const unsigned key = (dist << 16) | (unsigned)p;
-                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
-            }
-            const unsigned b1 = __reduce_min_sync(0xffffffffu, k1);
-            const unsigned b2 = __reduce_min_sync(0xffffffffu, k1 == b1 ? k2 : k1);    // keys are distinct
-            if (b1 == 0xFFFFFFFFu) continue;
-            const int bestDist = (int)(b1 >> 16);
-            const int bestDist2 = b2 == 0xFFFFFFFFu ? INT_MAX : (int)(b2 >> 16);
-            if (bestDist <= 50 && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) {          // TH_LOW, :459-461
-                const int bestIdx2 = (int)(c[b1 & 0xFFFFu] >> CAND_DIST_BITS);
-                const int prev = matches21[bestIdx2];
-                __syncwarp();
-                if (lane == 0) {
-                    if (prev >= 0) matches12[prev] = -1;
-                    matches12[i1] = bestIdx2;
-                    matches21[bestIdx2] = (short)i1;
-                    matched_dist[bestIdx2] = (unsigned short)bestDist;
-                    accepted[i1] = bestIdx2;
-                }
-                nmatches += prev >= 0 ? 0 : 1;
-                __syncwarp();
-            }
+    for (int qb = 0; qb < n1;) {
+        const int i1 = qb + lane;
+        const int cnt = i1 < n1 ? S.cnt[i1] : 0;
+        const uint32_t* c = S.base + (i1 < n1 ? S.off[i1] : 0);
+        unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;           // (dist << 16) | position: earliest candidate wins ties
+        for (int p = 0; p < cnt; ++p) {
+            const uint32_t e = c[p];
+            const unsigned dist = e & ((1u << CAND_DIST_BITS) - 1u);
+            if ((unsigned)matched_dist[e >> CAND_DIST_BITS] <= dist) continue;      // :444-445
+            const unsigned key = (dist << 16) | (unsigned)p;
+            if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
         }
+        int take = -1, bestDist = 0;
+        if (k1 != 0xFFFFFFFFu) {
+            bestDist = (int)(k1 >> 16);
+            const int bestDist2 = k2 == 0xFFFFFFFFu ? INT_MAX : (int)(k2 >> 16);
+            if (bestDist <= 50 && (float)bestDist < __fmul_rn((float)bestDist2, nnratio))             // TH_LOW, :459-461
+                take = (int)(c[k1 & 0xFFFFu] >> CAND_DIST_BITS);
+        }
+        const unsigned takers = __ballot_sync(0xffffffffu, take >= 0);
+        int ncommit = 32;
+        if (takers) {                                          // later lanes may have decided on stale state
+            post_taker(taker, take >= 0, take, lane);
+            bool invalid = false;
+            if (k1 != 0xFFFFFFFFu) invalid = taker[c[k1 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
+            if (k2 != 0xFFFFFFFFu) invalid = invalid || taker[c[k2 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
+            const unsigned inv = __ballot_sync(0xffffffffu, invalid);
+            if (inv) ncommit = __ffs(inv) - 1;
+            if (take >= 0) taker[take] = TAKER_NONE;
+        }
+        const bool commit = take >= 0 && lane < ncommit;
+        bool fresh = false;
+        if (commit) {                                          // committed lanes hold distinct features
+            const int prev = matches21[take];
+            if (prev >= 0) matches12[prev] = -1;               // :463-468: the earlier owner loses the feature
+            else fresh = true;
+            matches12[i1] = take;
+            matches21[take] = (short)i1;
+            matched_dist[take] = (unsigned short)bestDist;
+            accepted[i1] = take;
+        }
+        nmatches += __popc(__ballot_sync(0xffffffffu, fresh));
+        __syncwarp();
+        qb += ncommit;
     }
     if (lane == 0) *nmatches_out = nmatches;
 }
@@ -319,40 +377,113 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int t = threadIdx.x;
-    unsigned char* occupied = smem;                            // mvpMapPoints[i2] && Observations() > 0
-    unsigned char* obs = smem + (size_t)n_cur;
-    for (int i = t; i < n_cur; i += RESOLVE_THREADS) { occupied[i] = occupied_in[i]; cur_match[i] = -1; }
+    unsigned char* taker = smem;
+    unsigned char* occupied = smem + (size_t)n_cur;            // mvpMapPoints[i2] && Observations() > 0
+    unsigned char* obs = smem + 2 * (size_t)n_cur;
+    for (int i = t; i < n_cur; i += RESOLVE_THREADS) { taker[i] = TAKER_NONE; occupied[i] = occupied_in[i]; cur_match[i] = -1; }
     for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed[i]; accepted[i] = -1; }
-    const size_t used = ((size_t)n_cur + (size_t)n_last + 15) & ~(size_t)15;
+    const size_t used = (2 * (size_t)n_cur + (size_t)n_last + 15) & ~(size_t)15;
     const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_last);
     if (t >= 32) return;
     const int lane = t;
     int nmatches = 0;
-    for (int qb = 0; qb < n_last; qb += 32) {
-        unsigned todo = __ballot_sync(0xffffffffu, qb + lane < n_last && S.cnt[qb + lane] != 0);
-        while (todo) {
-            const int i = qb + __ffs(todo) - 1;
-            todo &= todo - 1;
-            const int cnt = S.cnt[i];
-            const uint32_t* c = S.base + S.off[i];
-            unsigned best = 0xFFFFFFFFu;
-            for (int p = lane; p < cnt; p += 32) {
-                const uint32_t e = c[p];
-                if (occupied[e >> CAND_DIST_BITS]) continue;   // :1403-1405
-                best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
-            }
-            best = __reduce_min_sync(0xffffffffu, best);
-            if (best == 0xFFFFFFFFu || (int)(best >> 16) > 100) continue;           // bestDist < 256 by construction; TH_HIGH
-            const int bestIdx2 = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
-            __syncwarp();
-            if (lane == 0) {
-                cur_match[bestIdx2] = i;
-                occupied[bestIdx2] = obs[i];
-                accepted[i] = bestIdx2;
-            }
-            nmatches++;
-            __syncwarp();
+    for (int qb = 0; qb < n_last;) {
+        const int i = qb + lane;
+        const int cnt = i < n_last ? S.cnt[i] : 0;
+        const uint32_t* c = S.base + (i < n_last ? S.off[i] : 0);
+        unsigned best = 0xFFFFFFFFu;
+        for (int p = 0; p < cnt; ++p) {
+            const uint32_t e = c[p];
+            if (occupied[e >> CAND_DIST_BITS]) continue;       // :1403-1405
+            best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
         }
+        int take = -1;                                         // bestDist < 256 by construction; TH_HIGH
+        if (best != 0xFFFFFFFFu && (int)(best >> 16) <= 100) take = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
+        const bool blocks = take >= 0 && obs[i];               // an unobserved point leaves the feature free (:1431)
+        const unsigned blockers = __ballot_sync(0xffffffffu, blocks);
+        int ncommit = 32;
+        if (blockers) {                                        // later lanes may have decided on stale state
+            post_taker(taker, blocks, take, lane);
+            const bool invalid = take >= 0 && taker[take] < lane;     // no second best here: only the best can go stale
+            const unsigned inv = __ballot_sync(0xffffffffu, invalid);
+            if (inv) ncommit = __ffs(inv) - 1;
+            if (blocks) taker[take] = TAKER_NONE;
+        }
+        const bool commit = take >= 0 && lane < ncommit;
+        if (commit) {
+            atomicMax(&cur_match[take], i);                    // the last point in index order keeps the feature
+            if (blocks) occupied[take] = 1;
+            accepted[i] = take;
+        }
+        nmatches += __popc(__ballot_sync(0xffffffffu, commit));
+        __syncwarp();
+        qb += ncommit;
+    }
+    if (lane == 0) *nmatches_out = nmatches;
+}
+
+// SearchByProjection(Frame, vector<MapPoint*>): the loop over the local map points (src/ORBmatcher.cc:50-122) on the
+// candidate lists.  Best and second best keep the octave of the keypoint they came from (bestLevel / bestLevel2); the
+// sequential scan's second best is the minimum of (distance, position) over everything but the best.
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_local_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
+                                                                   int n_points, int n_cur, const uint8_t* __restrict__ observed,
+                                                                   const uint8_t* __restrict__ occupied_in, const float* __restrict__ keys,
+                                                                   float nnratio, int* __restrict__ cur_match, int* __restrict__ nmatches_out)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int t = threadIdx.x;
+    unsigned char* taker = smem;
+    unsigned char* occupied = smem + (size_t)n_cur;            // F.mvpMapPoints[idx] && Observations() > 0 (:89-91)
+    unsigned char* oct = smem + 2 * (size_t)n_cur;             // F.mvKeysUn[idx].octave
+    unsigned char* obs = smem + 3 * (size_t)n_cur;
+    for (int i = t; i < n_cur; i += RESOLVE_THREADS) {
+        taker[i] = TAKER_NONE; occupied[i] = occupied_in[i]; oct[i] = (unsigned char)key_octave(keys, i); cur_match[i] = -1;
+    }
+    for (int i = t; i < n_points; i += RESOLVE_THREADS) obs[i] = observed[i];
+    const size_t used = (3 * (size_t)n_cur + (size_t)n_points + 15) & ~(size_t)15;
+    const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_points);
+    if (t >= 32) return;
+    const int lane = t;
+    int nmatches = 0;
+    for (int qb = 0; qb < n_points;) {
+        const int i = qb + lane;
+        const int cnt = i < n_points ? S.cnt[i] : 0;
+        const uint32_t* c = S.base + (i < n_points ? S.off[i] : 0);
+        unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
+        for (int p = 0; p < cnt; ++p) {
+            const uint32_t e = c[p];
+            if (occupied[e >> CAND_DIST_BITS]) continue;
+            const unsigned key = ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p;
+            if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+        }
+        int take = -1;
+        if (k1 != 0xFFFFFFFFu && (int)(k1 >> 16) <= 100) {     // TH_HIGH (:113); a distance of 256 never replaces the initial 256
+            const int bestDist = (int)(k1 >> 16);
+            const int bestIdx = (int)(c[k1 & 0xFFFFu] >> CAND_DIST_BITS);
+            int bestDist2 = 256, bestLevel2 = -1;
+            if (k2 != 0xFFFFFFFFu && (int)(k2 >> 16) < 256) { bestDist2 = (int)(k2 >> 16); bestLevel2 = oct[c[k2 & 0xFFFFu] >> CAND_DIST_BITS]; }
+            if (!((int)oct[bestIdx] == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2))) take = bestIdx;    // :115-116
+        }
+        const bool blocks = take >= 0 && obs[i];               // an unobserved point does not reserve its feature (:89-91)
+        const unsigned blockers = __ballot_sync(0xffffffffu, blocks);
+        int ncommit = 32;
+        if (blockers) {                                        // later lanes may have decided on stale state
+            post_taker(taker, blocks, take, lane);
+            bool invalid = false;
+            if (k1 != 0xFFFFFFFFu) invalid = taker[c[k1 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
+            if (k2 != 0xFFFFFFFFu) invalid = invalid || taker[c[k2 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
+            const unsigned inv = __ballot_sync(0xffffffffu, invalid);
+            if (inv) ncommit = __ffs(inv) - 1;
+            if (blocks) taker[take] = TAKER_NONE;
+        }
+        const bool commit = take >= 0 && lane < ncommit;
+        if (commit) {
+            atomicMax(&cur_match[take], i);                    // the last point in index order keeps the feature
+            if (blocks) occupied[take] = 1;
+        }
+        nmatches += __popc(__ballot_sync(0xffffffffu, commit));
+        __syncwarp();
+        qb += ncommit;
     }
     if (lane == 0) *nmatches_out = nmatches;
 }
@@ -465,6 +596,7 @@ struct Workspace {
             CUS(cudaFuncSetAttribute(k_init_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
+            CUS(cudaFuncSetAttribute(k_local_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             attr_set = true;
         }
         if (dbytes > dcap) {
@@ -688,6 +820,72 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
         }
     }
     *nmatches = nm;
+    return ORBGPU_OK;
+}
+
+int orbgpu_search_local_points(int device, const orbgpu_local_points_args* a, int32_t* cur_match, int* nmatches)
+{
+    if (!a || !cur_match || !nmatches || a->n_points < 0 || a->n_cur < 0 || a->nlevels < 1 || a->nlevels > 255) return ORBGPU_ERR_ARG;
+    if (!a->in_view || !a->proj_x || !a->proj_y || !a->proj_xr || !a->scale_level || !a->view_cos || !a->mp_desc || !a->mp_observed ||
+        !a->cur_keys_un || !a->cur_desc || !a->cur_u_right || !a->cur_occupied || !a->scale_factors) return ORBGPU_ERR_ARG;
+    if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
+    const int n1 = a->n_points, n2 = a->n_cur;
+    if (n1 > GRID_MAX_KEYS || n2 > GRID_MAX_KEYS || (size_t)n1 * (size_t)n2 > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
+    for (int i = 0; i < n1; ++i)
+        if (a->in_view[i] && (a->scale_level[i] < 0 || a->scale_level[i] >= a->nlevels)) return ORBGPU_ERR_ARG;
+    for (int i = 0; i < n2; ++i)
+        if (a->cur_keys_un[i].octave < 0 || a->cur_keys_un[i].octave > 255) return ORBGPU_ERR_ARG;
+    *nmatches = 0;
+    for (int i = 0; i < n2; ++i) cur_match[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBGPU_OK;
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2);
+    const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_qdesc = L.add(32 * (size_t)n1), o_obs = L.add((size_t)n1);
+    const size_t o_occ = L.add((size_t)n2), o_ur = L.add(4 * (size_t)n2);
+    const size_t in_bytes = L.off;
+    const size_t o_cm = L.add(4 * (size_t)n2), o_nm = L.add(4);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
+    const size_t o_cand = L.add(4 * (size_t)n1 * n2);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_keys, a->cur_keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_desc, a->cur_desc, 32 * (size_t)n2);
+    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(W.h + o_obs, a->mp_observed, (size_t)n1);
+    memcpy(W.h + o_occ, a->cur_occupied, (size_t)n2);
+    memcpy(W.h + o_ur, a->cur_u_right, 4 * (size_t)n2);
+    AreaQuery* hq = reinterpret_cast<AreaQuery*>(W.h + o_q);
+    const bool bFactor = a->th != 1.0;                         // :48
+    for (int i = 0; i < n1; ++i) {
+        AreaQuery& q = hq[i];
+        q.x = q.y = q.r = q.ur = 0.f; q.min_level = q.max_level = -1; q.active = 0; q.check_ur = 1;
+        if (!a->in_view[i]) continue;                          // :53-57
+        const int lvl = a->scale_level[i];
+        volatile float r = (double)a->view_cos[i] > 0.998 ? 2.5f : 4.0f;        // RadiusByViewingCos (:127-133)
+        if (bFactor) r = r * a->th;
+        r = r * a->scale_factors[lvl];                         // the window of :67 and the stereo gate of :96
+        q.x = a->proj_x[i]; q.y = a->proj_y[i]; q.r = r;
+        q.min_level = lvl - 1; q.max_level = lvl;
+        q.ur = a->proj_xr[i];
+        q.active = 1;
+    }
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    GridDev G;
+    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, reinterpret_cast<const AreaQuery*>(W.d + o_q), W.d + o_qdesc, n1,
+                                                      reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
+    k_local_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, G.keys, a->nnratio,
+                                                                reinterpret_cast<int*>(W.d + o_cm), reinterpret_cast<int*>(W.d + o_nm));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
+    *nmatches = *reinterpret_cast<const int*>(W.h + o_nm);
     return ORBGPU_OK;
 }
 

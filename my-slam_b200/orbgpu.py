@@ -27,6 +27,35 @@ class ProjectionArgs(C.Structure):
                 ("mono", C.c_int32), ("check_orientation", C.c_int32)]
 
 
+class LocalPointsArgs(C.Structure):
+    """orbgpu_local_points_args (include/orbgpu.h): what ORBmatcher::SearchByProjection(Frame, vector<MapPoint*>, th) reads."""
+    _fields_ = [("n_points", C.c_int32), ("in_view", C.c_void_p), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p),
+                ("proj_xr", C.c_void_p), ("scale_level", C.c_void_p), ("view_cos", C.c_void_p), ("mp_desc", C.c_void_p),
+                ("mp_observed", C.c_void_p), ("n_cur", C.c_int32), ("cur_keys_un", C.c_void_p), ("cur_desc", C.c_void_p),
+                ("cur_u_right", C.c_void_p), ("cur_occupied", C.c_void_p), ("bounds", C.c_float * 4),
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("th", C.c_float), ("nnratio", C.c_float)]
+
+
+def local_points_args(in_view, proj_x, proj_y, proj_xr, scale_level, view_cos, mp_desc, mp_observed, cur_keys_un, cur_desc,
+                      cur_u_right, cur_occupied, bounds, scale_factors, th, nnratio=0.8):
+    """Builds a LocalPointsArgs; returns (struct, keepalive dict of the arrays it points into)."""
+    f32, u8, i32 = np.float32, np.uint8, np.int32
+    arrs = dict(in_view=np.ascontiguousarray(in_view, u8), proj_x=np.ascontiguousarray(proj_x, f32),
+                proj_y=np.ascontiguousarray(proj_y, f32), proj_xr=np.ascontiguousarray(proj_xr, f32),
+                scale_level=np.ascontiguousarray(scale_level, i32), view_cos=np.ascontiguousarray(view_cos, f32),
+                mp_desc=np.ascontiguousarray(mp_desc, u8), mp_observed=np.ascontiguousarray(mp_observed, u8),
+                cur_keys_un=np.ascontiguousarray(cur_keys_un), cur_desc=np.ascontiguousarray(cur_desc, u8),
+                cur_u_right=np.ascontiguousarray(cur_u_right, f32), cur_occupied=np.ascontiguousarray(cur_occupied, u8),
+                scale_factors=np.ascontiguousarray(scale_factors, f32))
+    a = LocalPointsArgs()
+    for k, v in arrs.items():
+        setattr(a, k, v.ctypes.data)
+    a.n_points = len(arrs["in_view"]); a.n_cur = len(arrs["cur_keys_un"])
+    a.bounds = (C.c_float * 4)(*[float(v) for v in bounds])
+    a.nlevels = len(arrs["scale_factors"]); a.th = float(th); a.nnratio = float(nnratio)
+    return a, arrs
+
+
 class BowSide(C.Structure):
     """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
     _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
@@ -125,6 +154,7 @@ def lib():
         "orbgpu_undistort_points": (i32, [i32, vp, i32, vp, vp, i32, vp]),
         "orbgpu_search_for_initialization": (i32, [i32, vp, vp, i32, vp, vp, i32, vp, vp, i32, f32, i32, vp, pi]),
         "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
+        "orbgpu_search_local_points": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
@@ -360,6 +390,14 @@ def search_by_projection(args, device=0):
     ProjectionArgs snapshot -> (nmatches, cur_match[n_cur])."""
     cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
     _check(lib().orbgpu_search_by_projection(device, C.byref(args), _p(cm), C.byref(nm)))
+    return nm.value, cm[:args.n_cur].copy()
+
+
+def search_local_points(args, device=0):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:44-125) on a LocalPointsArgs snapshot
+    -> (nmatches, cur_match[n_cur]): cur_match[idx] = i where F.mvpMapPoints[idx] was set to vpMapPoints[i], else -1."""
+    cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_local_points(device, C.byref(args), _p(cm), C.byref(nm)))
     return nm.value, cm[:args.n_cur].copy()
 
 

@@ -234,6 +234,59 @@ extern "C" int frameport_search_by_projection(const frameport_projection_args* a
     return nmatches;
 }
 
+// src/ORBmatcher.cc:127-133
+static float radius_by_viewing_cos(const float& viewCos)
+{
+    if (viewCos > 0.998) return 2.5;
+    else return 4.0;
+}
+
+// src/ORBmatcher.cc:44-125
+extern "C" int frameport_search_local_points(const frameport_local_points_args* a, int* cur_match)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->cur_keys_un, a->n_cur, a->bounds);
+    int nmatches = 0;
+    const bool bFactor = a->th != 1.0;
+    std::vector<uint8_t> occupied(a->cur_occupied, a->cur_occupied + a->n_cur);
+    for (int i = 0; i < a->n_cur; ++i) cur_match[i] = -1;
+    for (int iMP = 0; iMP < a->n_points; ++iMP) {
+        if (!a->in_view[iMP]) continue;                       // !mbTrackInView || isBad()
+        const int nPredictedLevel = a->scale_level[iMP];
+        float r = radius_by_viewing_cos(a->view_cos[iMP]);
+        if (bFactor) r *= a->th;
+        const std::vector<size_t> vIndices = features_in_area(*g, a->proj_x[iMP], a->proj_y[iMP], r * a->scale_factors[nPredictedLevel],
+                                                              nPredictedLevel - 1, nPredictedLevel);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (size_t c = 0; c < vIndices.size(); ++c) {
+            const size_t idx = vIndices[c];
+            if (occupied[idx]) continue;
+            if (a->cur_u_right[idx] > 0) {
+                const float er = std::fabs(a->proj_xr[iMP] - a->cur_u_right[idx]);
+                if (er > r * a->scale_factors[nPredictedLevel]) continue;
+            }
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)iMP, a->cur_desc + 32 * idx);
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist;
+                bestLevel2 = bestLevel; bestLevel = a->cur_keys_un[idx].octave;
+                bestIdx = (int)idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = a->cur_keys_un[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > a->nnratio * bestDist2) continue;
+            cur_match[bestIdx] = iMP;
+            occupied[bestIdx] = a->mp_observed[iMP];
+            nmatches++;
+        }
+    }
+    delete g;
+    return nmatches;
+}
+
 // src/ORBmatcher.cc:159-288 and :522-655 (the two overloads differ in which side carries validity and in <= / < TH_LOW)
 extern "C" int frameport_search_by_bow(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
                                        int strict_th_low, int* match12, int* match21)

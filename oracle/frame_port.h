@@ -2,6 +2,7 @@
  *   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:230-245, 327-391
  *   ORBmatcher::SearchForInitialization                           src/ORBmatcher.cc:405-520
  *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono) src/ORBmatcher.cc:1328-1470
+ *   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) src/ORBmatcher.cc:44-133 (local-map search)
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
  * PINNED: the reference's own src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc and src/MapPoint.cc compile unchanged
@@ -54,6 +55,32 @@ int frameport_search_for_initialization(const orbport_keypoint* k1, const uint8_
                                         float nnratio, int check_orientation, int* matches12);
 /* returns nmatches; cur_match[n_cur]: -1 untouched, -2 reset to NULL by the rotation check, >= 0 index into the last frame */
 int frameport_search_by_projection(const frameport_projection_args* a, int* cur_match);
+
+/* same layout as orbgpu_local_points_args (include/orbgpu.h): ORBmatcher::SearchByProjection(Frame&, const
+ * vector<MapPoint*>&, th) (src/ORBmatcher.cc:44-125) on the fields Frame::isInFrustum left in the map points */
+typedef struct frameport_local_points_args {
+    int32_t n_points;
+    const uint8_t* in_view;        /* pMP->mbTrackInView && !pMP->isBad() */
+    const float* proj_x;
+    const float* proj_y;
+    const float* proj_xr;
+    const int32_t* scale_level;
+    const float* view_cos;
+    const uint8_t* mp_desc;
+    const uint8_t* mp_observed;    /* pMP->Observations() > 0 */
+    int32_t n_cur;
+    const orbport_keypoint* cur_keys_un;
+    const uint8_t* cur_desc;
+    const float* cur_u_right;
+    const uint8_t* cur_occupied;
+    float bounds[4];
+    const float* scale_factors;
+    int32_t nlevels;
+    float th;
+    float nnratio;
+} frameport_local_points_args;
+/* returns nmatches; cur_match[n_cur]: -1 untouched, i >= 0 = F.mvpMapPoints[idx] set to vpMapPoints[i] */
+int frameport_search_local_points(const frameport_local_points_args* a, int* cur_match);
 
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2

@@ -12,6 +12,7 @@
 //   frameref_features_in_area             Frame::AssignFeaturesToGrid + GetFeaturesInArea src/Frame.cc:230-245, 327-380
 //   frameref_search_for_initialization    ORBmatcher::SearchForInitialization             src/ORBmatcher.cc:405-520
 //   frameref_search_by_projection         ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  :1328-1470
+//   frameref_search_local_points          ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  :44-125
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
 //   frameref_descriptor_distance / frameref_three_maxima   ORBmatcher::DescriptorDistance :1647-1663, ComputeThreeMaxima :1601-1642
@@ -271,6 +272,41 @@ int frameref_search_by_projection(const frameport_projection_args* a, int* cur_m
     const int nm = matcher.SearchByProjection(Cur, Last, a->th, a->mono != 0);
     for (int i = 0; i < a->n_cur; ++i) {
         MapPoint* p = Cur.mvpMapPoints[i];
+        std::map<MapPoint*, int>::const_iterator it = p ? index_of.find(p) : index_of.end();
+        cur_match[i] = it == index_of.end() ? -1 : it->second;
+    }
+    return nm;
+}
+
+// The local-map search.  Map points carry what Frame::isInFrustum would have left in them; in_view = 0 alternates between
+// the two ways the reference skips a point (mbTrackInView false, or a bad point still flagged in view).
+int frameref_search_local_points(const frameport_local_points_args* a, int* cur_match)
+{
+    set_frame_statics(a->bounds, 1.f, 1.f, 0.f, 0.f);
+    World world;
+    Frame F;
+    set_scale_tables(F, a->scale_factors, a->nlevels);
+    fill_frame(F, a->cur_keys_un, a->cur_desc, a->n_cur);
+    F.mvuRight.assign(a->cur_u_right, a->cur_u_right + a->n_cur);
+    const float origin[3] = {0, 0, 0};
+    for (int i = 0; i < a->n_cur; ++i)
+        if (a->cur_occupied[i]) F.mvpMapPoints[i] = world.point(origin, 0, 1, false);
+        else if (i % 7 == 3) F.mvpMapPoints[i] = world.point(origin, 0, 0, false);       // present but unobserved: not skipped (:89-91)
+    std::vector<MapPoint*> vp((size_t)a->n_points);
+    std::map<MapPoint*, int> index_of;
+    for (int i = 0; i < a->n_points; ++i) {
+        const bool bad = !a->in_view[i] && (i & 1);
+        MapPoint* p = world.point(origin, a->mp_desc + 32 * i, a->mp_observed[i] ? 2 : 0, bad);
+        p->mbTrackInView = a->in_view[i] || bad;
+        p->mTrackProjX = a->proj_x[i]; p->mTrackProjY = a->proj_y[i]; p->mTrackProjXR = a->proj_xr[i];
+        p->mnTrackScaleLevel = a->scale_level[i];
+        p->mTrackViewCos = a->view_cos[i];
+        vp[i] = p; index_of[p] = i;
+    }
+    ORBmatcher matcher(a->nnratio, true);
+    const int nm = matcher.SearchByProjection(F, vp, a->th);
+    for (int i = 0; i < a->n_cur; ++i) {
+        MapPoint* p = F.mvpMapPoints[i];
         std::map<MapPoint*, int>::const_iterator it = p ? index_of.find(p) : index_of.end();
         cur_match[i] = it == index_of.end() ? -1 : it->second;
     }

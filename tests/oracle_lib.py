@@ -67,6 +67,7 @@ class OraclePort:
         L.frameport_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                                           C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.frameport_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
@@ -179,6 +180,12 @@ class OraclePort:
         """args: the product's ProjectionArgs ctypes struct (same layout as frameport_projection_args)."""
         cm = _i32(args.n_cur)
         nm = self.L.frameport_search_by_projection(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
+
+    def search_local_points(self, args):
+        """args: the product's LocalPointsArgs ctypes struct (same layout as frameport_local_points_args)."""
+        cm = _i32(args.n_cur)
+        nm = self.L.frameport_search_local_points(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
@@ -301,6 +308,7 @@ class OracleFrameRef:
         L.frameref_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                                          C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.frameref_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameref_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -353,6 +361,12 @@ class OracleFrameRef:
         """-> (nmatches, cur_match) with cur_match[i2] = last-frame index or -1 (the restatement's -2 reads as -1 here)."""
         cm = _i32(args.n_cur)
         nm = self.L.frameref_search_by_projection(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
+
+    def search_local_points(self, args):
+        """ORBmatcher::SearchByProjection(F, vpMapPoints, th) executed by the reference -> (nmatches, cur_match)."""
+        cm = _i32(args.n_cur)
+        nm = self.L.frameref_search_local_points(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):

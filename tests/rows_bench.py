@@ -78,6 +78,15 @@ def main():
     assert a[0] == o[0] and np.array_equal(a[1], o[1])
     out["search_by_bow_1000x1000_100nodes"] = {"gpu_ms": med(lambda: pkg.search_by_bow(s1, s2)), "cpu_ms": med(lambda: po.search_by_bow(s1, s2)),
                                               "nmatches": a[0]}
+    # --- local-map search: SearchByProjection(Frame, vector<MapPoint*>, th), 1000 and 4000 map points against 1000 features
+    import test_local_points as tl
+    for rep, th in [(1, 1.0), (4, 3.0)]:
+        G1 = (np.concatenate([k1] * rep), np.concatenate([d1] * rep))
+        args, keep = tl.local_scene(pkg, po, G1, F2, bounds, th, 1)
+        a = pkg.search_local_points(args); o = po.search_local_points(args)
+        assert a[0] == o[0] and np.array_equal(a[1], o[1])
+        out["search_local_points_%dx%d_th%d" % (len(G1[0]), len(k2), int(th))] = {
+            "gpu_ms": med(lambda: pkg.search_local_points(args)), "cpu_ms": med(lambda: po.search_local_points(args)), "nmatches": a[0]}
     print(json.dumps(out, indent=1))
 
 
