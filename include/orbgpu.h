@@ -220,6 +220,34 @@ typedef struct orbgpu_bow_side {
 int orbgpu_search_by_bow(int device, const orbgpu_bow_side* side1, const orbgpu_bow_side* side2, float nnratio,
                          int check_orientation, int strict_th_low, int32_t* match12, int32_t* match21, int* nmatches);
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) + CheckDistEpipolarLine
+ * (src/ORBmatcher.cc:657-820, :140-157): the BoW-gated, epipolar-checked search LocalMapping::CreateNewMapPoints runs
+ * against every neighbouring keyframe.  FeatureVectors flattened as for orbgpu_search_by_bow; F12 is computed by the
+ * caller (LocalMapping::ComputeF12 stays host). */
+typedef struct orbgpu_triangulation_side {
+    const orbgpu_keypoint* keys_un;  /* pKF->mvKeysUn */
+    const uint8_t* desc;             /* pKF->mDescriptors */
+    int32_t n;                       /* pKF->N */
+    const uint8_t* has_map_point;    /* pKF->GetMapPoint(idx) != NULL */
+    const float* u_right;            /* pKF->mvuRight */
+    const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;   /* pKF->mFeatVec */
+} orbgpu_triangulation_side;
+typedef struct orbgpu_triangulation_args {
+    orbgpu_triangulation_side kf1, kf2;
+    float F12[9];                    /* row-major 3 x 3 */
+    float Cw1[3];                    /* pKF1->GetCameraCenter() */
+    float T2w[16];                   /* pose of pKF2, 4 x 4 row-major (GetRotation / GetTranslation) */
+    float fx, fy, cx, cy;            /* pKF2->fx .. cy */
+    const float* scale_factors2;     /* pKF2->mvScaleFactors[nlevels] */
+    const float* level_sigma2;       /* pKF2->mvLevelSigma2[nlevels] */
+    int32_t nlevels;
+    int32_t only_stereo;             /* bOnlyStereo */
+    int32_t check_orientation;       /* mbCheckOrientation */
+} orbgpu_triangulation_args;
+/* matches12[kf1.n] = vMatches12 after the rotation check (vMatchedPairs = the pairs (i, matches12[i]) with matches12[i]
+ * >= 0, ascending i); *nmatches = the return value. */
+int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* args, int32_t* matches12, int* nmatches);
+
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),
  * FAST candidates in list order (:791-831) and octree survivors in list order (:541-765); x, y are

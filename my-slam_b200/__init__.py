@@ -8,5 +8,6 @@ directory name has a hyphen, so import it through __graft_entry__.load_package()
 from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_count, lib, lib_path, stereo_match, undistort_points,
                      ProjectionArgs, projection_args, search_for_initialization, search_by_projection,
                      BowSide, bow_side, search_by_bow,
-                     LocalPointsArgs, local_points_args, search_local_points)  # noqa: F401
+                     LocalPointsArgs, local_points_args, search_local_points,
+                     TriangulationArgs, triangulation_args, search_for_triangulation)  # noqa: F401
 from . import shard, synth  # noqa: F401

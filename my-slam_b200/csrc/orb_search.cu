@@ -3,6 +3,7 @@
 //   ORBmatcher::SearchForInitialization                             src/ORBmatcher.cc:405-520
 //   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  src/ORBmatcher.cc:1328-1470
 //   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)  src/ORBmatcher.cc:44-125 (local-map search)
+//   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine      src/ORBmatcher.cc:657-820, 140-157
 //
 // Device layout.  The 64 x 48 grid of the searched frame is a counting sort of its keypoint indices by cell id
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
@@ -561,6 +562,58 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_bow_resolve(const uint32_t*
     if (t == 0) *nmatches_out = s_nmatches;
 }
 
+// ---- SearchForTriangulation (src/ORBmatcher.cc:657-820) -----------------------------------------------------------
+// Queries as for SearchByBoW: the features of pKF1 without a map point inside a vocabulary node both keyframes share.
+// vbMatched2 is never set in the reference (:680, :722), so the queries are independent: one warp per query scans the
+// node's features of pKF2 and keeps, among those that pass the static tests (no map point, stereo flag, distance <=
+// TH_LOW, distance to the epipole, CheckDistEpipolarLine), the smallest distance -- the LAST one on ties, because the
+// reference's running test is "dist > bestDist -> skip" (:734).
+struct TriCam { float F[9]; float ex, ey; int only_stereo; };
+
+__global__ void __launch_bounds__(256) k_tri_match(const BowQuery* __restrict__ Q, int nq, TriCam C, const float* __restrict__ keys1,
+                                                   const uint8_t* __restrict__ desc1, const float* __restrict__ ur1,
+                                                   const float* __restrict__ keys2, const uint8_t* __restrict__ desc2,
+                                                   const float* __restrict__ ur2, const uint8_t* __restrict__ has_mp2,
+                                                   const uint32_t* __restrict__ indices2, const float* __restrict__ scale2,
+                                                   const float* __restrict__ sigma2, int* __restrict__ matches12)
+{
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const BowQuery B = Q[q];
+    const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1);
+    const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1 + 1);
+    const float x1 = keys1[7 * (size_t)B.idx1], y1 = keys1[7 * (size_t)B.idx1 + 1];
+    const bool stereo1 = ur1[B.idx1] >= 0.f;
+    // epipolar line l = x1' F12 (:143-145), float products summed left to right
+    const float la = __fadd_rn(__fadd_rn(__fmul_rn(x1, C.F[0]), __fmul_rn(y1, C.F[3])), C.F[6]);
+    const float lb = __fadd_rn(__fadd_rn(__fmul_rn(x1, C.F[1]), __fmul_rn(y1, C.F[4])), C.F[7]);
+    const float lc = __fadd_rn(__fadd_rn(__fmul_rn(x1, C.F[2]), __fmul_rn(y1, C.F[5])), C.F[8]);
+    const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+    unsigned best = 0xFFFFFFFFu;
+    for (int p = lane; p < B.len; p += 32) {
+        const uint32_t i2 = indices2[B.start + p];
+        if (has_mp2[i2]) continue;                             // :722
+        const bool stereo2 = ur2[i2] >= 0.f;
+        if (C.only_stereo && !stereo2) continue;
+        const int d = hamming_regs(a0, a1, reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2);
+        if (d > 50) continue;                                  // TH_LOW (:734)
+        const float x2 = keys2[7 * (size_t)i2], y2 = keys2[7 * (size_t)i2 + 1];
+        const int oct = __float_as_int(keys2[7 * (size_t)i2 + 5]);
+        if (!stereo1 && !stereo2) {                            // :739-745: too close to the epipole
+            const float dx = __fsub_rn(C.ex, x2), dy = __fsub_rn(C.ey, y2);
+            if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, scale2[oct])) continue;
+        }
+        if (den == 0.f) continue;                              // CheckDistEpipolarLine (:147-156)
+        const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if (!((double)dsqr < __dmul_rn(3.84, (double)sigma2[oct]))) continue;
+        best = min(best, ((unsigned)d << 16) | (unsigned)(0xFFFF - p));
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (lane == 0 && best != 0xFFFFFFFFu) matches12[B.idx1] = (int)indices2[B.start + (0xFFFF - (int)(best & 0xFFFFu))];
+}
+
 // ---- host side ---------------------------------------------------------------------------------------------------
 namespace {
 
@@ -886,6 +939,122 @@ int orbgpu_search_local_points(int device, const orbgpu_local_points_args* a, in
     CUS(cudaStreamSynchronize(W.st));
     memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
     *nmatches = *reinterpret_cast<const int*>(W.h + o_nm);
+    return ORBGPU_OK;
+}
+
+int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* a, int32_t* matches12, int* nmatches)
+{
+    if (!a || !matches12 || !nmatches || a->nlevels < 1 || !a->scale_factors2 || !a->level_sigma2) return ORBGPU_ERR_ARG;
+    const orbgpu_triangulation_side* S[2] = {&a->kf1, &a->kf2};
+    for (int k = 0; k < 2; ++k) {
+        const orbgpu_triangulation_side* s = S[k];
+        if (s->n < 0 || s->n_nodes < 0 || (s->n > 0 && (!s->keys_un || !s->desc || !s->has_map_point || !s->u_right)) ||
+            (s->n_nodes > 0 && (!s->node_ids || !s->node_start || !s->indices))) return ORBGPU_ERR_ARG;
+        if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+        for (int i = 0; i < s->n_nodes; ++i) {
+            if (s->node_start[i] > s->node_start[i + 1] || (i && s->node_ids[i - 1] >= s->node_ids[i])) return ORBGPU_ERR_ARG;
+            for (int c = s->node_start[i]; c < s->node_start[i + 1]; ++c) if (s->indices[c] >= (uint32_t)s->n) return ORBGPU_ERR_ARG;
+        }
+    }
+    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
+    const int n1 = s1.n, n2 = s2.n;
+    for (int i = 0; i < n2; ++i)
+        if (s2.keys_un[i].octave < 0 || s2.keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
+    *nmatches = 0;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    // the merge walk over the two FeatureVectors (:689-696, :782-789) -> queries in visiting order
+    std::vector<BowQuery> hq;
+    int it1 = 0, it2 = 0;
+    while (it1 != s1.n_nodes && it2 != s2.n_nodes) {
+        if (s1.node_ids[it1] == s2.node_ids[it2]) {
+            const int st = s2.node_start[it2], len = s2.node_start[it2 + 1] - st;
+            for (int c = s1.node_start[it1]; c < s1.node_start[it1 + 1]; ++c) {
+                const int idx1 = (int)s1.indices[c];
+                if (s1.has_map_point[idx1] || len == 0) continue;                      // :703-706
+                if (a->only_stereo && !(s1.u_right[idx1] >= 0)) continue;              // :708-712
+                BowQuery q; q.idx1 = idx1; q.start = st; q.len = len;
+                hq.push_back(q);
+            }
+            ++it1; ++it2;
+        } else if (s1.node_ids[it1] < s2.node_ids[it2]) {
+            while (it1 != s1.n_nodes && s1.node_ids[it1] < s2.node_ids[it2]) ++it1;
+        } else {
+            while (it2 != s2.n_nodes && s2.node_ids[it2] < s1.node_ids[it1]) ++it2;
+        }
+    }
+    const int nq = (int)hq.size();
+    if (nq == 0) return ORBGPU_OK;
+    const int nidx2 = s2.node_start[s2.n_nodes];
+    if (nidx2 > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;
+    // epipole of pKF1's centre in pKF2 (:664-670): C2 = R2w*Cw + t2w is cv::gemm's 3x3 float case
+    TriCam C;
+    float C2[3];
+    for (int r = 0; r < 3; ++r) {
+        volatile float t = a->T2w[4 * r] * a->Cw1[0];          // (volatile: keep the host compiler from contracting)
+        t = t + a->T2w[4 * r + 1] * a->Cw1[1];
+        t = t + a->T2w[4 * r + 2] * a->Cw1[2];
+        C2[r] = (float)((double)t * 1.0 + (double)a->T2w[4 * r + 3] * 1.0);
+    }
+    {
+        const float invz = 1.0f / C2[2];
+        volatile float px = a->fx * C2[0]; px = px * invz; px = px + a->cx;
+        volatile float py = a->fy * C2[1]; py = py * invz; py = py + a->cy;
+        C.ex = px; C.ey = py;
+    }
+    for (int i = 0; i < 9; ++i) C.F[i] = a->F12[i];
+    C.only_stereo = a->only_stereo ? 1 : 0;
+
+    Layout L;
+    const size_t o_k1 = L.add(sizeof(orbgpu_keypoint) * (size_t)n1), o_d1 = L.add(32 * (size_t)n1), o_u1 = L.add(4 * (size_t)n1);
+    const size_t o_k2 = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_d2 = L.add(32 * (size_t)n2), o_u2 = L.add(4 * (size_t)n2);
+    const size_t o_m2 = L.add((size_t)n2), o_i2 = L.add(4 * (size_t)nidx2), o_q = L.add(sizeof(BowQuery) * (size_t)nq);
+    const size_t o_sc = L.add(4 * (size_t)a->nlevels), o_sg = L.add(4 * (size_t)a->nlevels);
+    const size_t in_bytes = L.off;
+    const size_t o_m12 = L.add(4 * (size_t)n1);
+    const size_t io_bytes = L.off;
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_k1, s1.keys_un, sizeof(orbgpu_keypoint) * (size_t)n1);
+    memcpy(W.h + o_d1, s1.desc, 32 * (size_t)n1);
+    memcpy(W.h + o_u1, s1.u_right, 4 * (size_t)n1);
+    memcpy(W.h + o_k2, s2.keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_d2, s2.desc, 32 * (size_t)n2);
+    memcpy(W.h + o_u2, s2.u_right, 4 * (size_t)n2);
+    memcpy(W.h + o_m2, s2.has_map_point, (size_t)n2);
+    memcpy(W.h + o_i2, s2.indices, 4 * (size_t)nidx2);
+    memcpy(W.h + o_q, hq.data(), sizeof(BowQuery) * (size_t)nq);
+    memcpy(W.h + o_sc, a->scale_factors2, 4 * (size_t)a->nlevels);
+    memcpy(W.h + o_sg, a->level_sigma2, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    CUS(cudaMemsetAsync(W.d + o_m12, 0xFF, 4 * (size_t)n1, W.st));
+    k_tri_match<<<(nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), nq, C, reinterpret_cast<const float*>(W.d + o_k1),
+                                                W.d + o_d1, reinterpret_cast<const float*>(W.d + o_u1), reinterpret_cast<const float*>(W.d + o_k2),
+                                                W.d + o_d2, reinterpret_cast<const float*>(W.d + o_u2), W.d + o_m2,
+                                                reinterpret_cast<const uint32_t*>(W.d + o_i2), reinterpret_cast<const float*>(W.d + o_sc),
+                                                reinterpret_cast<const float*>(W.d + o_sg), reinterpret_cast<int*>(W.d + o_m12));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + o_m12, W.d + o_m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(matches12, W.h + o_m12, 4 * (size_t)n1);
+    int nm = 0;
+    for (int q = 0; q < nq; ++q) nm += matches12[hq[q].idx1] >= 0;
+    if (a->check_orientation) {                                // :760-776, :794-813
+        int bin_of[30] = {0};
+        std::vector<int> bin((size_t)nq, -1);
+        for (int q = 0; q < nq; ++q) {
+            const int i1 = hq[q].idx1;
+            if (matches12[i1] >= 0) { bin[q] = rot_bin(s1.keys_un[i1].angle, s2.keys_un[matches12[i1]].angle); bin_of[bin[q]]++; }
+        }
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(bin_of, 30, ind1, ind2, ind3);
+        for (int q = 0; q < nq; ++q) {
+            if (bin[q] < 0 || bin[q] == ind1 || bin[q] == ind2 || bin[q] == ind3) continue;
+            matches12[hq[q].idx1] = -1;
+            nm--;
+        }
+    }
+    *nmatches = nm;
     return ORBGPU_OK;
 }
 

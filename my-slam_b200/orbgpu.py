@@ -56,6 +56,43 @@ def local_points_args(in_view, proj_x, proj_y, proj_xr, scale_level, view_cos, m
     return a, arrs
 
 
+class TriangulationSide(C.Structure):
+    """orbgpu_triangulation_side (include/orbgpu.h)."""
+    _fields_ = [("keys_un", C.c_void_p), ("desc", C.c_void_p), ("n", C.c_int32), ("has_map_point", C.c_void_p),
+                ("u_right", C.c_void_p), ("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p),
+                ("n_nodes", C.c_int32)]
+
+
+class TriangulationArgs(C.Structure):
+    """orbgpu_triangulation_args (include/orbgpu.h): what ORBmatcher::SearchForTriangulation reads."""
+    _fields_ = [("kf1", TriangulationSide), ("kf2", TriangulationSide), ("F12", C.c_float * 9), ("Cw1", C.c_float * 3),
+                ("T2w", C.c_float * 16), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("scale_factors2", C.c_void_p), ("level_sigma2", C.c_void_p), ("nlevels", C.c_int32),
+                ("only_stereo", C.c_int32), ("check_orientation", C.c_int32)]
+
+
+def triangulation_args(side1, side2, F12, Cw1, T2w, cam, scale_factors2, level_sigma2, only_stereo=False, check_orientation=True):
+    """side = (keys_un, desc, has_map_point, u_right, node_ids, node_start, indices); returns (struct, keepalive list)."""
+    f32, u8 = np.float32, np.uint8
+    a = TriangulationArgs(); keep = []
+    for dst, sd in ((a.kf1, side1), (a.kf2, side2)):
+        arrs = [np.ascontiguousarray(sd[0]), np.ascontiguousarray(sd[1], u8), np.ascontiguousarray(sd[2], u8),
+                np.ascontiguousarray(sd[3], f32), np.ascontiguousarray(sd[4], np.uint32), np.ascontiguousarray(sd[5], np.int32),
+                np.ascontiguousarray(sd[6], np.uint32)]
+        keep.append(arrs)
+        dst.keys_un, dst.desc, dst.has_map_point, dst.u_right, dst.node_ids, dst.node_start, dst.indices = [v.ctypes.data for v in arrs]
+        dst.n = len(arrs[0]); dst.n_nodes = len(arrs[4])
+    a.F12 = (C.c_float * 9)(*[float(v) for v in np.asarray(F12, f32).reshape(9)])
+    a.Cw1 = (C.c_float * 3)(*[float(v) for v in np.asarray(Cw1, f32).reshape(3)])
+    a.T2w = (C.c_float * 16)(*[float(v) for v in np.asarray(T2w, f32).reshape(16)])
+    a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+    sc = np.ascontiguousarray(scale_factors2, f32); sg = np.ascontiguousarray(level_sigma2, f32)
+    keep.append([sc, sg])
+    a.scale_factors2 = sc.ctypes.data; a.level_sigma2 = sg.ctypes.data; a.nlevels = len(sc)
+    a.only_stereo = int(only_stereo); a.check_orientation = int(check_orientation)
+    return a, keep
+
+
 class BowSide(C.Structure):
     """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
     _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
@@ -156,6 +193,7 @@ def lib():
         "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_local_points": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
+        "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
@@ -399,6 +437,14 @@ def search_local_points(args, device=0):
     cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
     _check(lib().orbgpu_search_local_points(device, C.byref(args), _p(cm), C.byref(nm)))
     return nm.value, cm[:args.n_cur].copy()
+
+
+def search_for_triangulation(args, device=0):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-820) on a TriangulationArgs snapshot
+    -> (nmatches, vMatches12[kf1.n])."""
+    m12 = np.zeros(max(args.kf1.n, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_for_triangulation(device, C.byref(args), _p(m12), C.byref(nm)))
+    return nm.value, m12[:args.kf1.n].copy()
 
 
 def stereo_match(left, right, bf, b):

@@ -342,3 +342,80 @@ extern "C" int frameport_search_by_bow(const frameport_bow_side* s1, const frame
     }
     return nmatches;
 }
+
+// src/ORBmatcher.cc:140-157
+static bool check_dist_epipolar_line(const orbport_keypoint& kp1, const orbport_keypoint& kp2, const float* F12, const float* level_sigma2)
+{
+    const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+    const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+    const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+    const float num = a * kp2.x + b * kp2.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * level_sigma2[kp2.octave];
+}
+
+// src/ORBmatcher.cc:657-820
+extern "C" int frameport_search_for_triangulation(const frameport_triangulation_args* a, int* matches12)
+{
+    const frameport_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
+    // epipole in the second image (:664-670): R2w*Cw+t2w through cv::gemm's 3x3 float case
+    const float t2w[3] = {a->T2w[3], a->T2w[7], a->T2w[11]};
+    float C2[3];
+    mat3_mul_add(a->T2w, 4, a->Cw1, t2w, C2);
+    const float invz = 1.0f / C2[2];
+    const float ex = a->fx * C2[0] * invz + a->cx;
+    const float ey = a->fy * C2[1] * invz + a->cy;
+    int nmatches = 0;
+    std::vector<bool> vbMatched2((size_t)s2.n, false);         // never set in the reference either
+    for (int i = 0; i < s1.n; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int it1 = 0, it2 = 0;
+    while (it1 != s1.n_nodes && it2 != s2.n_nodes) {
+        if (s1.node_ids[it1] == s2.node_ids[it2]) {
+            for (int c1 = s1.node_start[it1]; c1 < s1.node_start[it1 + 1]; ++c1) {
+                const size_t idx1 = s1.indices[c1];
+                if (s1.has_map_point[idx1]) continue;
+                const bool bStereo1 = s1.u_right[idx1] >= 0;
+                if (a->only_stereo) if (!bStereo1) continue;
+                const orbport_keypoint& kp1 = s1.keys_un[idx1];
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (int c2 = s2.node_start[it2]; c2 < s2.node_start[it2 + 1]; ++c2) {
+                    const size_t idx2 = s2.indices[c2];
+                    if (vbMatched2[idx2] || s2.has_map_point[idx2]) continue;
+                    const bool bStereo2 = s2.u_right[idx2] >= 0;
+                    if (a->only_stereo) if (!bStereo2) continue;
+                    const int dist = orbport_hamming256(s1.desc + 32 * idx1, s2.desc + 32 * idx2);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const orbport_keypoint& kp2 = s2.keys_un[idx2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - kp2.x;
+                        const float distey = ey - kp2.y;
+                        if (distex * distex + distey * distey < 100 * a->scale_factors2[kp2.octave]) continue;
+                    }
+                    if (check_dist_epipolar_line(kp1, kp2, a->F12, a->level_sigma2)) { bestIdx2 = (int)idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    matches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (a->check_orientation) rotHist[rot_bin(kp1.angle, s2.keys_un[bestIdx2].angle)].push_back((int)idx1);
+                }
+            }
+            ++it1; ++it2;
+        } else if (s1.node_ids[it1] < s2.node_ids[it2]) {
+            while (it1 != s1.n_nodes && s1.node_ids[it1] < s2.node_ids[it2]) ++it1;
+        } else {
+            while (it2 != s2.n_nodes && s2.node_ids[it2] < s1.node_ids[it1]) ++it2;
+        }
+    }
+    if (a->check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); ++j) { matches12[rotHist[i][j]] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}

@@ -4,6 +4,7 @@
  *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono) src/ORBmatcher.cc:1328-1470
  *   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) src/ORBmatcher.cc:44-133 (local-map search)
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
+ *   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine    src/ORBmatcher.cc:657-820, 140-157
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
  * PINNED: the reference's own src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc and src/MapPoint.cc compile unchanged
  * against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc, recipe in oracle/Makefile), and
@@ -95,6 +96,20 @@ typedef struct frameport_bow_side {
 } frameport_bow_side;
 int frameport_search_by_bow(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
                             int strict_th_low, int* match12, int* match21);
+
+/* same layout as orbgpu_triangulation_side / orbgpu_triangulation_args (include/orbgpu.h):
+ * ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-820) with CheckDistEpipolarLine (:140-157) */
+typedef struct frameport_triangulation_side {
+    const orbport_keypoint* keys_un; const uint8_t* desc; int32_t n; const uint8_t* has_map_point; const float* u_right;
+    const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;
+} frameport_triangulation_side;
+typedef struct frameport_triangulation_args {
+    frameport_triangulation_side kf1, kf2;
+    float F12[9]; float Cw1[3]; float T2w[16]; float fx, fy, cx, cy;
+    const float* scale_factors2; const float* level_sigma2; int32_t nlevels; int32_t only_stereo; int32_t check_orientation;
+} frameport_triangulation_args;
+/* returns nmatches; matches12[kf1.n] = vMatches12 after the rotation check */
+int frameport_search_for_triangulation(const frameport_triangulation_args* a, int* matches12);
 
 #ifdef __cplusplus
 }

@@ -14,6 +14,7 @@
 //   frameref_search_by_projection         ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  :1328-1470
 //   frameref_search_local_points          ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  :44-125
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
+//   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
 //   frameref_descriptor_distance / frameref_three_maxima   ORBmatcher::DescriptorDistance :1647-1663, ComputeThreeMaxima :1601-1642
 //   frameref_gemm3 / frameref_neg_rt_t    the shim's cv::gemm and "-R.t()*t" evaluation (golden-vector check)
@@ -367,6 +368,51 @@ int frameref_search_by_bow(const frameport_bow_side* s1, const frameport_bow_sid
         nm = matcher.SearchByBoW(KF[0], KF[1], matches);
         for (int i1 = 0; i1 < s1->n; ++i1)
             if (matches[i1]) { const int i2 = index_of[1][matches[i1]]; match12[i1] = i2; match21[i2] = i1; }
+    }
+    return nm;
+}
+
+// SearchForTriangulation between two KeyFrames built by the reference's constructor from plain arrays.  T1w is the pose
+// of pKF1; the camera centre the reference derives from it (KeyFrame::SetPose, GetCameraCenter) is returned in cw1_out so
+// the restatement can be given exactly the value the reference used (a->Cw1 is ignored here).
+int frameref_search_for_triangulation(const frameport_triangulation_args* a, const float* T1w, int* matches12, float* cw1_out)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    const float origin[3] = {0, 0, 0};
+    const frameport_triangulation_side* sides[2] = {&a->kf1, &a->kf2};
+    Frame F[2];
+    KeyFrame* KF[2] = {0, 0};
+    for (int s = 0; s < 2; ++s) {
+        const frameport_triangulation_side* sd = sides[s];
+        set_scale_tables(F[s], a->scale_factors2, a->nlevels);
+        F[s].mvLevelSigma2.assign(a->level_sigma2, a->level_sigma2 + a->nlevels);
+        fill_frame(F[s], sd->keys_un, sd->desc, sd->n);
+        F[s].mvuRight.assign(sd->u_right, sd->u_right + sd->n);
+        F[s].mTcw = pose_mat(s == 0 ? T1w : a->T2w);
+        F[s].mbf = 1.f; F[s].mb = 1.f; F[s].mThDepth = 1.f; F[s].mTimeStamp = 0; F[s].mnId = (unsigned long)(s + 1);
+        frameport_bow_side fv; std::memset(&fv, 0, sizeof(fv));
+        fv.node_ids = sd->node_ids; fv.node_start = sd->node_start; fv.indices = sd->indices; fv.n_nodes = sd->n_nodes;
+        fill_feature_vector(F[s].mFeatVec, &fv);
+        for (int i = 0; i < sd->n; ++i)
+            if (sd->has_map_point[i]) F[s].mvpMapPoints[i] = world.point(origin, sd->desc + 32 * (size_t)i, 1, false);
+        KF[s] = new KeyFrame(F[s], &world.map, static_cast<KeyFrameDatabase*>(NULL));   // src/KeyFrame.cc:34-60
+        world.keyframes.push_back(KF[s]);
+    }
+    const cv::Mat Cw = KF[0]->GetCameraCenter();
+    for (int i = 0; i < 3; ++i) cw1_out[i] = Cw.at<float>(i);
+    cv::Mat F12(3, 3, CV_32F);
+    std::memcpy(F12.data, a->F12, 9 * sizeof(float));
+    std::vector<std::pair<size_t, size_t> > pairs;
+    ORBmatcher matcher(0.6f, a->check_orientation != 0);
+    const int nm = matcher.SearchForTriangulation(KF[0], KF[1], F12, pairs, a->only_stereo != 0);
+    for (int i = 0; i < a->kf1.n; ++i) matches12[i] = -1;
+    size_t last = 0;
+    for (size_t k = 0; k < pairs.size(); ++k) {
+        if (k && pairs[k].first <= last) never("vMatchedPairs not ascending");
+        last = pairs[k].first;
+        matches12[pairs[k].first] = (int)pairs[k].second;
     }
     return nm;
 }

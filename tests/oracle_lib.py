@@ -68,6 +68,7 @@ class OraclePort:
                                                           C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.frameport_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
@@ -187,6 +188,12 @@ class OraclePort:
         cm = _i32(args.n_cur)
         nm = self.L.frameport_search_local_points(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
+
+    def search_for_triangulation(self, args):
+        """args: the product's TriangulationArgs ctypes struct (same layout as frameport_triangulation_args)."""
+        m12 = _i32(args.kf1.n)
+        nm = self.L.frameport_search_for_triangulation(C.byref(args), _ptr(m12))
+        return nm, m12[:args.kf1.n].copy()
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
         """sides: the product's BowSide ctypes structs (same layout as frameport_bow_side)."""
@@ -309,6 +316,7 @@ class OracleFrameRef:
                                                          C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.frameref_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -368,6 +376,14 @@ class OracleFrameRef:
         cm = _i32(args.n_cur)
         nm = self.L.frameref_search_local_points(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
+
+    def search_for_triangulation(self, args, T1w):
+        """ORBmatcher::SearchForTriangulation executed by the reference on KeyFrames posed at T1w / args.T2w
+        -> (nmatches, vMatches12, the camera centre of pKF1 the reference derived from T1w)."""
+        m12 = _i32(args.kf1.n); cw = np.zeros(3, np.float32)
+        T1 = np.ascontiguousarray(T1w, np.float32)
+        nm = self.L.frameref_search_for_triangulation(C.byref(args), _ptr(T1), _ptr(m12), _ptr(cw))
+        return nm, m12[:args.kf1.n].copy(), cw
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
         m12 = _i32(side1.n); m21 = _i32(side2.n)

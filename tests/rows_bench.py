@@ -87,6 +87,15 @@ def main():
         assert a[0] == o[0] and np.array_equal(a[1], o[1])
         out["search_local_points_%dx%d_th%d" % (len(G1[0]), len(k2), int(th))] = {
             "gpu_ms": med(lambda: pkg.search_local_points(args)), "cpu_ms": med(lambda: po.search_local_points(args)), "nmatches": a[0]}
+    # --- SearchForTriangulation: 1000 x 1000 and 2000 x 2000 features in 100 vocabulary nodes
+    import test_triangulation as tt
+    for nf in (1000, 2000):
+        G1, G2, _ = ts.two_frames(pkg, ts.device_extract(pkg), 640, 480, 0x7A1A + nf, nf)
+        args, keep, T1 = tt.tri_scene(pkg, po, G1, G2, 4, 100, False, True, 0.5)
+        a = pkg.search_for_triangulation(args); o = po.search_for_triangulation(args)
+        assert a[0] == o[0] and np.array_equal(a[1], o[1])
+        out["search_for_triangulation_%dx%d_100nodes" % (len(G1[0]), len(G2[0]))] = {
+            "gpu_ms": med(lambda: pkg.search_for_triangulation(args)), "cpu_ms": med(lambda: po.search_for_triangulation(args)), "nmatches": a[0]}
     print(json.dumps(out, indent=1))
 
 
