@@ -205,6 +205,48 @@ typedef struct orbgpu_local_points_args {
 /* cur_match[n_cur]: -1 untouched, i >= 0: F.mvpMapPoints[idx] was set to vpMapPoints[i].  *nmatches = return value. */
 int orbgpu_search_local_points(int device, const orbgpu_local_points_args* args, int32_t* cur_match, int* nmatches);
 
+/* Tracking::SearchLocalPoints (src/Tracking.cc:1150-1200) in one call: Frame::isInFrustum (src/Frame.cc:269-325, with
+ * MapPoint::PredictScale, src/MapPoint.cc:402-417) for every candidate local map point, then
+ * ORBmatcher::SearchByProjection(F, vpLocalMapPoints, th) (src/ORBmatcher.cc:44-125) on what it left in the points. */
+typedef struct orbgpu_local_map_args {
+    int32_t n_points;
+    const uint8_t* candidate;      /* pMP->mnLastFrameSeen != F.mnId && !pMP->isBad() (src/Tracking.cc:1177-1180) */
+    const float* world_pos;        /* n_points x 3: pMP->GetWorldPos() */
+    const float* normal;           /* n_points x 3: pMP->GetNormal() */
+    const float* max_distance;     /* pMP->mfMaxDistance ( = GetMaxDistanceInvariance() / 1.2f ) */
+    const float* min_distance;     /* pMP->mfMinDistance */
+    const uint8_t* mp_desc;        /* n_points x 32: pMP->GetDescriptor() */
+    const uint8_t* mp_observed;    /* pMP->Observations() > 0 */
+    const float* Tcw;              /* F.mTcw, 4 x 4 row-major */
+    float fx, fy, cx, cy, bf;      /* F.fx .. F.mbf */
+    float viewing_cos_limit;       /* 0.5 at src/Tracking.cc:1182 */
+    float log_scale_factor;        /* F.mfLogScaleFactor */
+    int32_t n_cur;
+    const orbgpu_keypoint* cur_keys_un;   /* F.mvKeysUn */
+    const uint8_t* cur_desc;       /* F.mDescriptors */
+    const float* cur_u_right;      /* F.mvuRight */
+    const uint8_t* cur_occupied;   /* F.mvpMapPoints[idx] && ->Observations() > 0, on entry */
+    float bounds[4];               /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;    /* F.mvScaleFactors[nlevels] */
+    int32_t nlevels;
+    float th;
+    float nnratio;                 /* mfNNratio (0.8 at src/Tracking.cc:1191) */
+} orbgpu_local_map_args;
+/* what isInFrustum leaves in each map point (arrays of n_points); where in_view = 0 the reference leaves the members
+ * untouched and the other five entries are 0 */
+typedef struct orbgpu_track_fields {
+    uint8_t* in_view;              /* mbTrackInView = the return value of isInFrustum (caller: IncreaseVisible()) */
+    float* proj_x;                 /* mTrackProjX */
+    float* proj_y;                 /* mTrackProjY */
+    float* proj_xr;                /* mTrackProjXR */
+    int32_t* scale_level;          /* mnTrackScaleLevel */
+    float* view_cos;               /* mTrackViewCos */
+} orbgpu_track_fields;
+/* *n_in_view = nToMatch; the search runs when it is > 0 (src/Tracking.cc:1189); cur_match / *nmatches as for
+ * orbgpu_search_local_points.  n_cur == 0 makes this a batched isInFrustum. */
+int orbgpu_search_local_map(int device, const orbgpu_local_map_args* args, const orbgpu_track_fields* out, int* n_in_view,
+                            int32_t* cur_match, int* nmatches);
+
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
  * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order
@@ -270,6 +312,10 @@ int orbgpu_octree(orbgpu_extractor* e, const int* xs, const int* ys, const int* 
 int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg);
 int orbgpu_debug_sincosf(orbgpu_extractor* e, const float* rad, int n, float* out_sin, float* out_cos);
 int orbgpu_debug_sincos_checksum(orbgpu_extractor* e, uint32_t first_bits, uint32_t count, uint32_t step, uint64_t* checksum);
+
+/* Test hook for the float step that decides MapPoint::PredictScale (src/MapPoint.cc:410): glibc's logf exactly as
+ * k_frustum evaluates it.  Host arrays. */
+int orbgpu_debug_logf(int device, const float* x, int n, float* out);
 
 /* Profiling: with profiling on, CUDA events bracket every stage of each chunk on its stream.
  * orbgpu_get_stage_ms returns accumulated milliseconds per stage since the last reset:

@@ -9,5 +9,6 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      ProjectionArgs, projection_args, search_for_initialization, search_by_projection,
                      BowSide, bow_side, search_by_bow,
                      LocalPointsArgs, local_points_args, search_local_points,
-                     TriangulationArgs, triangulation_args, search_for_triangulation)  # noqa: F401
+                     TriangulationArgs, triangulation_args, search_for_triangulation,
+                     LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf)  # noqa: F401
 from . import shard, synth  # noqa: F401

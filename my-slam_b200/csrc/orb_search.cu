@@ -4,6 +4,7 @@
 //   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  src/ORBmatcher.cc:1328-1470
 //   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)  src/ORBmatcher.cc:44-125 (local-map search)
 //   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine      src/ORBmatcher.cc:657-820, 140-157
+//   Frame::isInFrustum + MapPoint::PredictScale                     src/Frame.cc:269-325, src/MapPoint.cc:402-417
 //
 // Device layout.  The 64 x 48 grid of the searched frame is a counting sort of its keypoint indices by cell id
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
@@ -562,6 +563,126 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_bow_resolve(const uint32_t*
     if (t == 0) *nmatches_out = s_nmatches;
 }
 
+// ---- Frame::isInFrustum (src/Frame.cc:269-325) ---------------------------------------------------------------------
+// glibc 2.39 logf (sysdeps/ieee754/flt-32/e_logf.c, the routine the reference object calls from MapPoint::PredictScale)
+// followed operation by operation in double; tests/test_local_map.py sweeps float bit patterns against the host's logf
+// (the rounding to float absorbs whether the host build contracts the multiply-adds, checked over every normal float).
+__constant__ double c_logf_tab[32] = {
+    0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2, 0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2,
+    0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3, 0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3,
+    0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4, 0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5,
+    0x1p+0, 0x0p+0, 0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4,
+    0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3, 0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2,
+    0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2};
+
+__device__ __forceinline__ float orb_logf(float x)
+{
+    uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {       // x < 0x1p-126, inf or nan
+        if (ix * 2 == 0) return __int_as_float(0xff800000);    // log(0) = -inf
+        if (ix == 0x7f800000u) return x;                       // log(inf) = inf
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return __int_as_float(0x7fc00000);
+        ix = __float_as_uint(__fmul_rn(x, 0x1p23f));           // subnormal: normalise
+        ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (int)((tmp >> 19) & 15u);
+    const int k = (int)tmp >> 23;
+    const uint32_t iz = ix - (tmp & (0x1ffu << 23));
+    const double invc = c_logf_tab[2 * i], logc = c_logf_tab[2 * i + 1];
+    const double z = (double)__uint_as_float(iz);
+    const double r = __dadd_rn(__dmul_rn(z, invc), -1.0);
+    const double y0 = __dadd_rn(logc, __dmul_rn((double)k, 0x1.62e42fefa39efp-1));
+    const double r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(0x1.5575b0be00b6ap-2, r), -0x1.ffffef20a4123p-2);
+    y = __dadd_rn(__dmul_rn(-0x1.00ea348b88334p-2, r2), y);
+    y = __dadd_rn(__dmul_rn(y, r2), __dadd_rn(y0, r));
+    return (float)y;
+}
+
+__global__ void k_debug_logf(const float* __restrict__ x, int n, float* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = orb_logf(x[i]);
+}
+
+struct FrustumCam { float R[9], t[3], Ow[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, cos_limit, log_scale, th; int nlevels; };
+struct TrackOut { uint8_t* in_view; float *proj_x, *proj_y, *proj_xr, *view_cos; int* scale_level; };
+
+__global__ void k_frustum(FrustumCam C, const uint8_t* __restrict__ candidate, const float* __restrict__ world_pos,
+                          const float* __restrict__ normal, const float* __restrict__ max_distance, const float* __restrict__ min_distance,
+                          const float* __restrict__ scale, int n, TrackOut T, AreaQuery* __restrict__ Q, int* __restrict__ n_in_view)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool in = false;
+    if (i < n) {
+        AreaQuery q;
+        q.x = q.y = q.r = q.ur = 0.f; q.min_level = q.max_level = -1; q.active = 0; q.check_ur = 1;
+        float u = 0.f, v = 0.f, ur = 0.f, viewCos = 0.f;
+        int level = 0;
+        if (candidate[i]) {
+            const float P[3] = {world_pos[3 * (size_t)i], world_pos[3 * (size_t)i + 1], world_pos[3 * (size_t)i + 2]};
+            float Pc[3];
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {                      // mRcw*P+mtcw: cv::gemm's 3x3 float case (:277)
+                const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.R[3 * r], P[0]), __fmul_rn(C.R[3 * r + 1], P[1])), __fmul_rn(C.R[3 * r + 2], P[2]));
+                Pc[r] = (float)__dadd_rn(__dmul_rn((double)t, 1.0), __dmul_rn((double)C.t[r], 1.0));
+            }
+            if (!(Pc[2] < 0.0f)) {                             // :283
+                const float invz = __fdiv_rn(1.0f, Pc[2]);
+                u = __fadd_rn(__fmul_rn(__fmul_rn(C.fx, Pc[0]), invz), C.cx);
+                v = __fadd_rn(__fmul_rn(__fmul_rn(C.fy, Pc[1]), invz), C.cy);
+                if (!(u < C.minX || u > C.maxX) && !(v < C.minY || v > C.maxY)) {
+                    const float maxDistance = __fmul_rn(1.2f, max_distance[i]);        // src/MapPoint.cc:373-383
+                    const float minDistance = __fmul_rn(0.8f, min_distance[i]);
+                    const float PO[3] = {__fsub_rn(P[0], C.Ow[0]), __fsub_rn(P[1], C.Ow[1]), __fsub_rn(P[2], C.Ow[2])};
+                    // cv::norm: squares summed in double, sqrt in double, narrowed by "const float dist" (:299)
+                    double s2 = __dmul_rn((double)PO[0], (double)PO[0]);
+                    s2 = __dadd_rn(s2, __dmul_rn((double)PO[1], (double)PO[1]));
+                    s2 = __dadd_rn(s2, __dmul_rn((double)PO[2], (double)PO[2]));
+                    const float dist = (float)__dsqrt_rn(s2);
+                    if (!(dist < minDistance || dist > maxDistance)) {
+                        // cv::Mat::dot: products summed in double; "/dist" divides in double (:307)
+                        double d = __dmul_rn((double)PO[0], (double)normal[3 * (size_t)i]);
+                        d = __dadd_rn(d, __dmul_rn((double)PO[1], (double)normal[3 * (size_t)i + 1]));
+                        d = __dadd_rn(d, __dmul_rn((double)PO[2], (double)normal[3 * (size_t)i + 2]));
+                        viewCos = (float)__ddiv_rn(d, (double)dist);
+                        if (!(viewCos < C.cos_limit)) {
+                            // MapPoint::PredictScale (src/MapPoint.cc:402-417)
+                            const float ratio = __fdiv_rn(max_distance[i], dist);
+                            const float c = ceilf(__fdiv_rn(orb_logf(ratio), C.log_scale));
+                            int nScale = (fabsf(c) < 2147483648.f) ? (int)c : INT_MIN;     // cvttss2si of inf / nan
+                            if (nScale < 0) nScale = 0;
+                            else if (nScale >= C.nlevels) nScale = C.nlevels - 1;
+                            level = nScale;
+                            ur = __fsub_rn(u, __fmul_rn(C.bf, invz));
+                            in = true;
+                        }
+                    }
+                }
+            }
+        }
+        if (!in) { u = v = ur = viewCos = 0.f; level = 0; }     // the reference leaves the members of such a point untouched
+        // a point on the camera plane or at the camera centre yields 0*inf or 0/0; x86 writes its default NaN (sign set)
+        if (u != u) u = __int_as_float(0xffc00000);
+        if (v != v) v = __int_as_float(0xffc00000);
+        if (ur != ur) ur = __int_as_float(0xffc00000);
+        if (viewCos != viewCos) viewCos = __int_as_float(0xffc00000);
+        T.in_view[i] = in ? 1 : 0;
+        T.proj_x[i] = u; T.proj_y[i] = v; T.proj_xr[i] = ur; T.view_cos[i] = viewCos; T.scale_level[i] = level;
+        if (in) {                                              // the window of src/ORBmatcher.cc:62-67
+            float r = (double)viewCos > 0.998 ? 2.5f : 4.0f;
+            if (C.th != 1.0f) r = __fmul_rn(r, C.th);
+            q.x = u; q.y = v; q.r = __fmul_rn(r, scale[level]);
+            q.min_level = level - 1; q.max_level = level; q.ur = ur; q.active = 1;
+        }
+        Q[i] = q;
+    }
+    const int cnt = __syncthreads_count(in);
+    if (threadIdx.x == 0 && cnt) atomicAdd(n_in_view, cnt);
+}
+
 // ---- SearchForTriangulation (src/ORBmatcher.cc:657-820) -----------------------------------------------------------
 // Queries as for SearchByBoW: the features of pKF1 without a map point inside a vocabulary node both keyframes share.
 // vbMatched2 is never set in the reference (:680, :722), so the queries are independent: one warp per query scans the
@@ -939,6 +1060,120 @@ int orbgpu_search_local_points(int device, const orbgpu_local_points_args* a, in
     CUS(cudaStreamSynchronize(W.st));
     memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
     *nmatches = *reinterpret_cast<const int*>(W.h + o_nm);
+    return ORBGPU_OK;
+}
+
+int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const orbgpu_track_fields* out, int* n_in_view,
+                            int32_t* cur_match, int* nmatches)
+{
+    if (!a || !out || !n_in_view || !cur_match || !nmatches || a->n_points < 0 || a->n_cur < 0 || a->nlevels < 1 || a->nlevels > 255)
+        return ORBGPU_ERR_ARG;
+    if (!a->candidate || !a->world_pos || !a->normal || !a->max_distance || !a->min_distance || !a->mp_desc || !a->mp_observed || !a->Tcw ||
+        !a->scale_factors || !out->in_view || !out->proj_x || !out->proj_y || !out->proj_xr || !out->scale_level || !out->view_cos)
+        return ORBGPU_ERR_ARG;
+    if (a->n_cur > 0 && (!a->cur_keys_un || !a->cur_desc || !a->cur_u_right || !a->cur_occupied)) return ORBGPU_ERR_ARG;
+    if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
+    const int n1 = a->n_points, n2 = a->n_cur;
+    if (n1 > GRID_MAX_KEYS || n2 > GRID_MAX_KEYS || (size_t)n1 * (size_t)n2 > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
+    for (int i = 0; i < n2; ++i)
+        if (a->cur_keys_un[i].octave < 0 || a->cur_keys_un[i].octave > 255) return ORBGPU_ERR_ARG;
+    *nmatches = 0; *n_in_view = 0;
+    for (int i = 0; i < n2; ++i) cur_match[i] = -1;
+    if (n1 == 0) return ORBGPU_OK;
+    // pose matrices as Frame::UpdatePoseMatrices leaves them (src/Frame.cc:261-267); mOw = -mRcw.t()*mtcw is the same
+    // cv::MatExpr as at src/ORBmatcher.cc:1341: gemm of a transposed copy with alpha = -1 (float products, float sums)
+    FrustumCam C;
+    const float* Tc = a->Tcw;
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = Tc[4 * r + c]; C.t[r] = Tc[4 * r + 3]; }
+    for (int i = 0; i < 3; ++i) {
+        volatile float t = Tc[i] * C.t[0];
+        t = t + Tc[4 + i] * C.t[1];
+        t = t + Tc[8 + i] * C.t[2];
+        C.Ow[i] = (float)((double)t * -1.0);
+    }
+    C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy; C.bf = a->bf;
+    C.minX = a->bounds[0]; C.maxX = a->bounds[1]; C.minY = a->bounds[2]; C.maxY = a->bounds[3];
+    C.cos_limit = a->viewing_cos_limit; C.log_scale = a->log_scale_factor; C.th = a->th; C.nlevels = a->nlevels;
+
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2);
+    const size_t o_qdesc = L.add(32 * (size_t)n1), o_obs = L.add((size_t)n1), o_occ = L.add((size_t)n2), o_ur = L.add(4 * (size_t)n2);
+    const size_t o_cand = L.add((size_t)n1), o_pos = L.add(12 * (size_t)n1), o_nrm = L.add(12 * (size_t)n1);
+    const size_t o_maxd = L.add(4 * (size_t)n1), o_mind = L.add(4 * (size_t)n1), o_scale = L.add(4 * (size_t)a->nlevels);
+    const size_t in_bytes = L.off;
+    const size_t o_cm = L.add(4 * (size_t)n2), o_nm = L.add(8);
+    const size_t o_iv = L.add((size_t)n1), o_px = L.add(4 * (size_t)n1), o_py = L.add(4 * (size_t)n1), o_pxr = L.add(4 * (size_t)n1);
+    const size_t o_vc = L.add(4 * (size_t)n1), o_lvl = L.add(4 * (size_t)n1);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
+    const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_cl = L.add(4 * (size_t)n1 * (size_t)(n2 > 0 ? n2 : 1));
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    if (n2) {
+        memcpy(W.h + o_keys, a->cur_keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+        memcpy(W.h + o_desc, a->cur_desc, 32 * (size_t)n2);
+        memcpy(W.h + o_occ, a->cur_occupied, (size_t)n2);
+        memcpy(W.h + o_ur, a->cur_u_right, 4 * (size_t)n2);
+    }
+    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(W.h + o_obs, a->mp_observed, (size_t)n1);
+    memcpy(W.h + o_cand, a->candidate, (size_t)n1);
+    memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
+    memcpy(W.h + o_nrm, a->normal, 12 * (size_t)n1);
+    memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    CUS(cudaMemsetAsync(W.d + o_nm, 0, 8, W.st));
+    TrackOut T;
+    T.in_view = W.d + o_iv; T.proj_x = reinterpret_cast<float*>(W.d + o_px); T.proj_y = reinterpret_cast<float*>(W.d + o_py);
+    T.proj_xr = reinterpret_cast<float*>(W.d + o_pxr); T.view_cos = reinterpret_cast<float*>(W.d + o_vc);
+    T.scale_level = reinterpret_cast<int*>(W.d + o_lvl);
+    AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
+    int* d_nm = reinterpret_cast<int*>(W.d + o_nm);
+    k_frustum<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_cand, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
+                                                  reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
+                                                  reinterpret_cast<const float*>(W.d + o_scale), n1, T, d_q, d_nm + 1);
+    if (n2) {
+        GridDev G;
+        set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+        uint32_t* d_cl = reinterpret_cast<uint32_t*>(W.d + o_cl);
+        int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+        k_grid_build<<<1, 1024, 0, W.st>>>(G);
+        k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cl, n2, d_cn);
+        k_local_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cl, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, G.keys, a->nnratio,
+                                                                    reinterpret_cast<int*>(W.d + o_cm), d_nm);
+    }
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    if (n2) memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
+    *nmatches = reinterpret_cast<const int*>(W.h + o_nm)[0];
+    *n_in_view = reinterpret_cast<const int*>(W.h + o_nm)[1];
+    memcpy(out->in_view, W.h + o_iv, (size_t)n1);
+    memcpy(out->proj_x, W.h + o_px, 4 * (size_t)n1);
+    memcpy(out->proj_y, W.h + o_py, 4 * (size_t)n1);
+    memcpy(out->proj_xr, W.h + o_pxr, 4 * (size_t)n1);
+    memcpy(out->view_cos, W.h + o_vc, 4 * (size_t)n1);
+    memcpy(out->scale_level, W.h + o_lvl, 4 * (size_t)n1);
+    return ORBGPU_OK;
+}
+
+/* test hook: the device logf of MapPoint::PredictScale on host arrays */
+int orbgpu_debug_logf(int device, const float* x, int n, float* out)
+{
+    if (!x || !out || n < 0) return ORBGPU_ERR_ARG;
+    if (n == 0) return ORBGPU_OK;
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, 8 * (size_t)n, 16);
+    if (rc != ORBGPU_OK) return rc;
+    float* d_x = reinterpret_cast<float*>(W.d); float* d_o = d_x + n;
+    CUS(cudaMemcpyAsync(d_x, x, 4 * (size_t)n, cudaMemcpyHostToDevice, W.st));
+    k_debug_logf<<<(n + 255) / 256, 256, 0, W.st>>>(d_x, n, d_o);
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(out, d_o, 4 * (size_t)n, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
     return ORBGPU_OK;
 }
 

@@ -93,6 +93,56 @@ def triangulation_args(side1, side2, F12, Cw1, T2w, cam, scale_factors2, level_s
     return a, keep
 
 
+class LocalMapArgs(C.Structure):
+    """orbgpu_local_map_args (include/orbgpu.h): Frame::isInFrustum per candidate point + the local-map search."""
+    _fields_ = [("n_points", C.c_int32), ("candidate", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
+                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("mp_desc", C.c_void_p), ("mp_observed", C.c_void_p),
+                ("Tcw", C.c_void_p), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("viewing_cos_limit", C.c_float), ("log_scale_factor", C.c_float),
+                ("n_cur", C.c_int32), ("cur_keys_un", C.c_void_p), ("cur_desc", C.c_void_p), ("cur_u_right", C.c_void_p),
+                ("cur_occupied", C.c_void_p), ("bounds", C.c_float * 4), ("scale_factors", C.c_void_p), ("nlevels", C.c_int32),
+                ("th", C.c_float), ("nnratio", C.c_float)]
+
+
+class TrackFields(C.Structure):
+    """orbgpu_track_fields (include/orbgpu.h)."""
+    _fields_ = [("in_view", C.c_void_p), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p),
+                ("scale_level", C.c_void_p), ("view_cos", C.c_void_p)]
+
+
+def track_fields(n):
+    """Output arrays for n map points -> (struct, dict of numpy arrays)."""
+    n = max(int(n), 1)
+    arrs = dict(in_view=np.zeros(n, np.uint8), proj_x=np.zeros(n, np.float32), proj_y=np.zeros(n, np.float32),
+                proj_xr=np.zeros(n, np.float32), scale_level=np.zeros(n, np.int32), view_cos=np.zeros(n, np.float32))
+    t = TrackFields()
+    for k, v in arrs.items():
+        setattr(t, k, v.ctypes.data)
+    return t, arrs
+
+
+def local_map_args(candidate, world_pos, normal, max_distance, min_distance, mp_desc, mp_observed, Tcw, cam, bf, cur_keys_un, cur_desc,
+                   cur_u_right, cur_occupied, bounds, scale_factors, log_scale_factor, th, nnratio=0.8, viewing_cos_limit=0.5):
+    """Builds a LocalMapArgs; returns (struct, keepalive dict of the arrays it points into)."""
+    f32, u8 = np.float32, np.uint8
+    arrs = dict(candidate=np.ascontiguousarray(candidate, u8), world_pos=np.ascontiguousarray(world_pos, f32),
+                normal=np.ascontiguousarray(normal, f32), max_distance=np.ascontiguousarray(max_distance, f32),
+                min_distance=np.ascontiguousarray(min_distance, f32), mp_desc=np.ascontiguousarray(mp_desc, u8),
+                mp_observed=np.ascontiguousarray(mp_observed, u8), Tcw=np.ascontiguousarray(Tcw, f32),
+                cur_keys_un=np.ascontiguousarray(cur_keys_un), cur_desc=np.ascontiguousarray(cur_desc, u8),
+                cur_u_right=np.ascontiguousarray(cur_u_right, f32), cur_occupied=np.ascontiguousarray(cur_occupied, u8),
+                scale_factors=np.ascontiguousarray(scale_factors, f32))
+    a = LocalMapArgs()
+    for k, v in arrs.items():
+        setattr(a, k, v.ctypes.data)
+    a.n_points = len(arrs["candidate"]); a.n_cur = len(arrs["cur_keys_un"])
+    a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+    a.bf = float(bf); a.viewing_cos_limit = float(viewing_cos_limit); a.log_scale_factor = float(log_scale_factor)
+    a.bounds = (C.c_float * 4)(*[float(v) for v in bounds])
+    a.nlevels = len(arrs["scale_factors"]); a.th = float(th); a.nnratio = float(nnratio)
+    return a, arrs
+
+
 class BowSide(C.Structure):
     """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
     _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
@@ -193,6 +243,8 @@ def lib():
         "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_local_points": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
+        "orbgpu_search_local_map": (i32, [i32, vp, vp, pi, vp, pi]),
+        "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
@@ -445,6 +497,22 @@ def search_for_triangulation(args, device=0):
     m12 = np.zeros(max(args.kf1.n, 1), np.int32); nm = C.c_int(0)
     _check(lib().orbgpu_search_for_triangulation(device, C.byref(args), _p(m12), C.byref(nm)))
     return nm.value, m12[:args.kf1.n].copy()
+
+
+def search_local_map(args, device=0):
+    """Tracking::SearchLocalPoints (src/Tracking.cc:1150-1200): isInFrustum for the candidate points + the local-map search
+    -> (nmatches, cur_match[n_cur], n_in_view, dict of the mTrack* arrays)."""
+    t, arrs = track_fields(args.n_points)
+    cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0); nv = C.c_int(0)
+    _check(lib().orbgpu_search_local_map(device, C.byref(args), C.byref(t), C.byref(nv), _p(cm), C.byref(nm)))
+    return nm.value, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+
+def debug_logf(x, device=0):
+    """glibc logf as the device evaluates it in MapPoint::PredictScale (test hook)."""
+    x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x)
+    _check(lib().orbgpu_debug_logf(device, _p(x), len(x), _p(out)))
+    return out
 
 
 def stereo_match(left, right, bf, b):

@@ -419,3 +419,67 @@ extern "C" int frameport_search_for_triangulation(const frameport_triangulation_
     }
     return nmatches;
 }
+
+extern "C" void frameport_logf_array(const float* x, int n, float* out)
+{
+    for (int i = 0; i < n; ++i) out[i] = logf(x[i]);
+}
+
+// src/Tracking.cc:1173-1199: isInFrustum (src/Frame.cc:269-325) for the candidate points, then the search when nToMatch > 0
+extern "C" int frameport_search_local_map(const frameport_local_map_args* a, const frameport_track_fields* out, int* n_in_view, int* cur_match)
+{
+    const float* Tc = a->Tcw;
+    const float mtcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float mOw[3];                                             // Frame::UpdatePoseMatrices: mOw = -mRcw.t()*mtcw (src/Frame.cc:266),
+    for (int i = 0; i < 3; ++i) {                             // the cv::MatExpr of src/ORBmatcher.cc:1341 (see above)
+        const float t = Tc[i] * mtcw[0] + Tc[4 + i] * mtcw[1] + Tc[8 + i] * mtcw[2];
+        mOw[i] = (float)((double)t * -1.0);
+    }
+    int nToMatch = 0;
+    for (int i = 0; i < a->n_points; ++i) {
+        out->in_view[i] = 0; out->proj_x[i] = out->proj_y[i] = out->proj_xr[i] = out->view_cos[i] = 0.f; out->scale_level[i] = 0;
+        if (!a->candidate[i]) continue;
+        const float* P = a->world_pos + 3 * (size_t)i;
+        float Pc[3];
+        mat3_mul_add(Tc, 4, P, mtcw, Pc);
+        const float PcX = Pc[0], PcY = Pc[1], PcZ = Pc[2];
+        if (PcZ < 0.0f) continue;
+        const float invz = 1.0f / PcZ;
+        const float u = a->fx * PcX * invz + a->cx;
+        const float v = a->fy * PcY * invz + a->cy;
+        if (u < a->bounds[0] || u > a->bounds[1]) continue;
+        if (v < a->bounds[2] || v > a->bounds[3]) continue;
+        const float maxDistance = 1.2f * a->max_distance[i];
+        const float minDistance = 0.8f * a->min_distance[i];
+        const float PO[3] = {P[0] - mOw[0], P[1] - mOw[1], P[2] - mOw[2]};
+        double s2 = 0;                                        // cv::norm(PO): double accumulation, sqrt in double
+        for (int k = 0; k < 3; ++k) s2 += (double)PO[k] * (double)PO[k];
+        const float dist = std::sqrt(s2);
+        if (dist < minDistance || dist > maxDistance) continue;
+        const float* Pn = a->normal + 3 * (size_t)i;
+        double dot = 0;                                       // cv::Mat::dot: double accumulation
+        for (int k = 0; k < 3; ++k) dot += (double)PO[k] * (double)Pn[k];
+        const float viewCos = dot / dist;
+        if (viewCos < a->viewing_cos_limit) continue;
+        // MapPoint::PredictScale (src/MapPoint.cc:402-417); the reference object calls logf
+        const float ratio = a->max_distance[i] / dist;
+        int nScale = ceil(logf(ratio) / a->log_scale_factor);
+        if (nScale < 0) nScale = 0;
+        else if (nScale >= a->nlevels) nScale = a->nlevels - 1;
+        out->in_view[i] = 1;                                  // "Data used by the tracking" (src/Frame.cc:316-322)
+        out->proj_x[i] = u; out->proj_y[i] = v; out->view_cos[i] = viewCos;
+        out->proj_xr[i] = u - a->bf * invz;
+        out->scale_level[i] = nScale;
+        nToMatch++;
+    }
+    *n_in_view = nToMatch;
+    for (int i = 0; i < a->n_cur; ++i) cur_match[i] = -1;
+    if (a->n_cur == 0) return 0;
+    frameport_local_points_args s;
+    s.n_points = a->n_points; s.in_view = out->in_view; s.proj_x = out->proj_x; s.proj_y = out->proj_y; s.proj_xr = out->proj_xr;
+    s.scale_level = out->scale_level; s.view_cos = out->view_cos; s.mp_desc = a->mp_desc; s.mp_observed = a->mp_observed;
+    s.n_cur = a->n_cur; s.cur_keys_un = a->cur_keys_un; s.cur_desc = a->cur_desc; s.cur_u_right = a->cur_u_right; s.cur_occupied = a->cur_occupied;
+    for (int k = 0; k < 4; ++k) s.bounds[k] = a->bounds[k];
+    s.scale_factors = a->scale_factors; s.nlevels = a->nlevels; s.th = a->th; s.nnratio = a->nnratio;
+    return frameport_search_local_points(&s, cur_match);
+}

@@ -5,6 +5,7 @@
  *   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) src/ORBmatcher.cc:44-133 (local-map search)
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine    src/ORBmatcher.cc:657-820, 140-157
+ *   Frame::isInFrustum + MapPoint::PredictScale (Tracking::SearchLocalPoints)  src/Frame.cc:269-325, src/MapPoint.cc:402-417
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
  * PINNED: the reference's own src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc and src/MapPoint.cc compile unchanged
  * against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc, recipe in oracle/Makefile), and
@@ -110,6 +111,24 @@ typedef struct frameport_triangulation_args {
 } frameport_triangulation_args;
 /* returns nmatches; matches12[kf1.n] = vMatches12 after the rotation check */
 int frameport_search_for_triangulation(const frameport_triangulation_args* a, int* matches12);
+
+/* same layout as orbgpu_local_map_args / orbgpu_track_fields (include/orbgpu.h): Tracking::SearchLocalPoints
+ * (src/Tracking.cc:1150-1200) = Frame::isInFrustum per candidate point, then the local-map SearchByProjection */
+typedef struct frameport_local_map_args {
+    int32_t n_points;
+    const uint8_t* candidate; const float* world_pos; const float* normal; const float* max_distance; const float* min_distance;
+    const uint8_t* mp_desc; const uint8_t* mp_observed;
+    const float* Tcw; float fx, fy, cx, cy, bf; float viewing_cos_limit; float log_scale_factor;
+    int32_t n_cur; const orbport_keypoint* cur_keys_un; const uint8_t* cur_desc; const float* cur_u_right; const uint8_t* cur_occupied;
+    float bounds[4]; const float* scale_factors; int32_t nlevels; float th; float nnratio;
+} frameport_local_map_args;
+typedef struct frameport_track_fields {
+    uint8_t* in_view; float* proj_x; float* proj_y; float* proj_xr; int32_t* scale_level; float* view_cos;
+} frameport_track_fields;
+/* returns nmatches; *n_in_view = nToMatch */
+int frameport_search_local_map(const frameport_local_map_args* a, const frameport_track_fields* out, int* n_in_view, int* cur_match);
+/* glibc logf on an array (what MapPoint::PredictScale calls), for the device logf test */
+void frameport_logf_array(const float* x, int n, float* out);
 
 #ifdef __cplusplus
 }

@@ -13,6 +13,7 @@
 //   frameref_search_for_initialization    ORBmatcher::SearchForInitialization             src/ORBmatcher.cc:405-520
 //   frameref_search_by_projection         ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  :1328-1470
 //   frameref_search_local_points          ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  :44-125
+//   frameref_search_local_map             Frame::isInFrustum (src/Frame.cc:269-325) per point + that search, as Tracking::SearchLocalPoints
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
 //   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
@@ -304,6 +305,62 @@ int frameref_search_local_points(const frameport_local_points_args* a, int* cur_
         p->mTrackViewCos = a->view_cos[i];
         vp[i] = p; index_of[p] = i;
     }
+    ORBmatcher matcher(a->nnratio, true);
+    const int nm = matcher.SearchByProjection(F, vp, a->th);
+    for (int i = 0; i < a->n_cur; ++i) {
+        MapPoint* p = F.mvpMapPoints[i];
+        std::map<MapPoint*, int>::const_iterator it = p ? index_of.find(p) : index_of.end();
+        cur_match[i] = it == index_of.end() ? -1 : it->second;
+    }
+    return nm;
+}
+
+// The second half of Tracking::SearchLocalPoints (src/Tracking.cc:1171-1199) on a Frame posed by SetPose and MapPoints
+// carrying world position, normal and the scale-invariance distances.
+int frameref_search_local_map(const frameport_local_map_args* a, const frameport_track_fields* out, int* n_in_view, int* cur_match)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame F;
+    set_scale_tables(F, a->scale_factors, a->nlevels);
+    F.mfLogScaleFactor = a->log_scale_factor;
+    fill_frame(F, a->cur_keys_un, a->cur_desc, a->n_cur);
+    if (a->n_cur) F.mvuRight.assign(a->cur_u_right, a->cur_u_right + a->n_cur);
+    F.mbf = a->bf; F.mb = 1.f; F.mnId = 77;
+    F.SetPose(pose_mat(a->Tcw));                               // UpdatePoseMatrices: mRcw, mtcw, mOw
+    const float origin[3] = {0, 0, 0};
+    for (int i = 0; i < a->n_cur; ++i)
+        if (a->cur_occupied[i]) F.mvpMapPoints[i] = world.point(origin, 0, 1, false);
+    std::vector<MapPoint*> vp((size_t)a->n_points);
+    std::map<MapPoint*, int> index_of;
+    for (int i = 0; i < a->n_points; ++i) {
+        // candidate = 0: alternately a bad point and one already seen in this frame (src/Tracking.cc:1177-1180)
+        const bool bad = !a->candidate[i] && (i & 1);
+        MapPoint* p = world.point(a->world_pos + 3 * i, a->mp_desc + 32 * i, a->mp_observed[i] ? 2 : 0, bad);
+        cv::Mat nrm(3, 1, CV_32F);
+        std::memcpy(nrm.data, a->normal + 3 * i, 3 * sizeof(float));
+        p->mNormalVector = nrm;
+        p->mfMaxDistance = a->max_distance[i]; p->mfMinDistance = a->min_distance[i];
+        p->mnLastFrameSeen = (!a->candidate[i] && !bad) ? F.mnId : 0;
+        p->mbTrackInView = false;
+        vp[i] = p; index_of[p] = i;
+    }
+    int nToMatch = 0;
+    for (int i = 0; i < a->n_points; ++i) {
+        MapPoint* pMP = vp[i];
+        out->in_view[i] = 0; out->proj_x[i] = out->proj_y[i] = out->proj_xr[i] = out->view_cos[i] = 0.f; out->scale_level[i] = 0;
+        if (pMP->mnLastFrameSeen == F.mnId) continue;
+        if (pMP->isBad()) continue;
+        if (F.isInFrustum(pMP, a->viewing_cos_limit)) {
+            nToMatch++;
+            out->in_view[i] = pMP->mbTrackInView ? 1 : 0;
+            out->proj_x[i] = pMP->mTrackProjX; out->proj_y[i] = pMP->mTrackProjY; out->proj_xr[i] = pMP->mTrackProjXR;
+            out->scale_level[i] = pMP->mnTrackScaleLevel; out->view_cos[i] = pMP->mTrackViewCos;
+        }
+    }
+    *n_in_view = nToMatch;
+    for (int i = 0; i < a->n_cur; ++i) cur_match[i] = -1;
+    if (nToMatch == 0 || a->n_cur == 0) return 0;
     ORBmatcher matcher(a->nnratio, true);
     const int nm = matcher.SearchByProjection(F, vp, a->th);
     for (int i = 0; i < a->n_cur; ++i) {

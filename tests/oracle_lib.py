@@ -69,6 +69,9 @@ class OraclePort:
         L.frameport_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameport_logf_array.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.frameport_logf_array.restype = None
         L.frameport_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
@@ -195,6 +198,19 @@ class OraclePort:
         nm = self.L.frameport_search_for_triangulation(C.byref(args), _ptr(m12))
         return nm, m12[:args.kf1.n].copy()
 
+    def search_local_map(self, args, track_fields):
+        """args: the product's LocalMapArgs; track_fields: its track_fields(n) factory -> (nmatches, cur_match, n_in_view, fields)."""
+        t, arrs = track_fields(args.n_points)
+        cm = _i32(args.n_cur); nv = C.c_int(0)
+        nm = self.L.frameport_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
+        return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+    def logf(self, x):
+        """glibc logf (the call MapPoint::PredictScale makes) on a float32 array."""
+        x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x)
+        self.L.frameport_logf_array(_ptr(x), len(x), _ptr(out))
+        return out
+
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
         """sides: the product's BowSide ctypes structs (same layout as frameport_bow_side)."""
         m12 = _i32(side1.n); m21 = _i32(side2.n)
@@ -317,6 +333,7 @@ class OracleFrameRef:
         L.frameref_search_by_projection.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -384,6 +401,13 @@ class OracleFrameRef:
         T1 = np.ascontiguousarray(T1w, np.float32)
         nm = self.L.frameref_search_for_triangulation(C.byref(args), _ptr(T1), _ptr(m12), _ptr(cw))
         return nm, m12[:args.kf1.n].copy(), cw
+
+    def search_local_map(self, args, track_fields):
+        """args: the product's LocalMapArgs; track_fields: its track_fields(n) factory -> (nmatches, cur_match, n_in_view, fields)."""
+        t, arrs = track_fields(args.n_points)
+        cm = _i32(args.n_cur); nv = C.c_int(0)
+        nm = self.L.frameref_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
+        return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
         m12 = _i32(side1.n); m21 = _i32(side2.n)

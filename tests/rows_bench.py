@@ -96,6 +96,15 @@ def main():
         assert a[0] == o[0] and np.array_equal(a[1], o[1])
         out["search_for_triangulation_%dx%d_100nodes" % (len(G1[0]), len(G2[0]))] = {
             "gpu_ms": med(lambda: pkg.search_for_triangulation(args)), "cpu_ms": med(lambda: po.search_for_triangulation(args)), "nmatches": a[0]}
+    # --- Tracking::SearchLocalPoints in one call: isInFrustum for 4000 local map points + the search against 1000 features
+    import test_local_map as tm
+    G1 = (np.concatenate([k1] * 4), np.concatenate([d1] * 4))
+    args, keep = tm.local_map_scene(pkg, po, G1, F2, bounds, 1.0, 1)
+    a = pkg.search_local_map(args); o = po.search_local_map(args, pkg.track_fields)
+    assert tm.same(a, o)
+    out["search_local_map_%dx%d_th1" % (len(G1[0]), len(k2))] = {
+        "gpu_ms": med(lambda: pkg.search_local_map(args)), "cpu_ms": med(lambda: po.search_local_map(args, pkg.track_fields)),
+        "in_view": a[2], "nmatches": a[0]}
     print(json.dumps(out, indent=1))
 
 
