@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 namespace {
@@ -482,4 +483,55 @@ extern "C" int frameport_search_local_map(const frameport_local_map_args* a, con
     for (int k = 0; k < 4; ++k) s.bounds[k] = a->bounds[k];
     s.scale_factors = a->scale_factors; s.nlevels = a->nlevels; s.th = a->th; s.nnratio = a->nnratio;
     return frameport_search_local_points(&s, cur_match);
+}
+
+// glibc 2.39 logf (sysdeps/ieee754/flt-32/e_logf.c, data e_logf_data.c) restated operation by operation -- the form
+// k_frustum evaluates on the device (separate multiplies and adds).  frameport_logf_port_mismatches counts the float
+// bit patterns first, first + step, ... (count of them) on which it differs from the host's logf.
+static const double kLogfTab[32] = {
+    0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2, 0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2,
+    0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3, 0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3,
+    0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4, 0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5,
+    0x1p+0, 0x0p+0, 0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4,
+    0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3, 0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2,
+    0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2};
+
+static float logf_port(float x)
+{
+    uint32_t ix; memcpy(&ix, &x, 4);
+    if (ix == 0x3f800000u) return 0.f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return -INFINITY;
+        if (ix == 0x7f800000u) return x;
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return NAN;
+        const float xs = x * 0x1p23f;
+        memcpy(&ix, &xs, 4);
+        ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (int)((tmp >> 19) & 15u);
+    const int k = (int32_t)tmp >> 23;
+    const uint32_t iz = ix - (tmp & (0x1ffu << 23));
+    float zf; memcpy(&zf, &iz, 4);
+    const double invc = kLogfTab[2 * i], logc = kLogfTab[2 * i + 1], z = zf;
+    volatile double m;                                         // volatile: no contraction, as __dmul_rn / __dadd_rn on the device
+    m = z * invc; const double r = m + -1.0;
+    m = (double)k * 0x1.62e42fefa39efp-1; const double y0 = logc + m;
+    m = r * r; const double r2 = m;
+    m = 0x1.5575b0be00b6ap-2 * r; double y = m + -0x1.ffffef20a4123p-2;
+    m = -0x1.00ea348b88334p-2 * r2; y = m + y;
+    m = y * r2; y = m + (y0 + r);
+    return (float)y;
+}
+
+extern "C" long long frameport_logf_port_mismatches(uint32_t first, uint32_t count, uint32_t step)
+{
+    long long bad = 0;
+    for (uint32_t n = 0; n < count; ++n) {
+        const uint32_t b = first + n * step;
+        float x; memcpy(&x, &b, 4);
+        const float a = logf(x), p = logf_port(x);
+        if (std::isnan(a) ? !std::isnan(p) : memcmp(&a, &p, 4) != 0) ++bad;
+    }
+    return bad;
 }

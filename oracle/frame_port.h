@@ -129,6 +129,8 @@ typedef struct frameport_track_fields {
 int frameport_search_local_map(const frameport_local_map_args* a, const frameport_track_fields* out, int* n_in_view, int* cur_match);
 /* glibc logf on an array (what MapPoint::PredictScale calls), for the device logf test */
 void frameport_logf_array(const float* x, int n, float* out);
+/* the device's logf algorithm restated on the CPU vs the host's logf over float bit patterns first + k*step, k < count */
+long long frameport_logf_port_mismatches(uint32_t first, uint32_t count, uint32_t step);
 
 #ifdef __cplusplus
 }

@@ -72,6 +72,8 @@ class OraclePort:
         L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameport_logf_array.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.frameport_logf_array.restype = None
+        L.frameport_logf_port_mismatches.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+        L.frameport_logf_port_mismatches.restype = C.c_longlong
         L.frameport_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         self.nlevels = nlevels
         self.h = L.orbport_create(nfeatures, scale, nlevels, ini_th, min_th)
@@ -204,6 +206,9 @@ class OraclePort:
         cm = _i32(args.n_cur); nv = C.c_int(0)
         nm = self.L.frameport_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
         return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+    def logf_port_mismatches(self, first, count, step):
+        return int(self.L.frameport_logf_port_mismatches(first, count, step))
 
     def logf(self, x):
         """glibc logf (the call MapPoint::PredictScale makes) on a float32 array."""
