@@ -247,6 +247,37 @@ typedef struct orbgpu_track_fields {
 int orbgpu_search_local_map(int device, const orbgpu_local_map_args* args, const orbgpu_track_fields* out, int* n_in_view,
                             int32_t* cur_match, int* nmatches);
 
+/* The search inside ORBmatcher::Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, th) (src/ORBmatcher.cc:825-957,
+ * LocalMapping::SearchInNeighbors): projection into pKF, image / distance / viewing-angle tests, PredictScale,
+ * KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:569-608) and the chi-square gated best-descriptor scan (:892-940) for every
+ * map point at once.  best_idx[i] = the keypoint of pKF map point i fuses with (bestDist <= TH_LOW), else -1.  The map
+ * surgery that follows (:943-961: Replace / AddObservation / AddMapPoint) and the entry tests that depend on it
+ * (isBad(), IsInKeyFrame(pKF), :850-851) stay host and run in index order over best_idx. */
+typedef struct orbgpu_fuse_args {
+    int32_t n_points;
+    const uint8_t* present;        /* vpMapPoints[i] != NULL */
+    const float* world_pos;        /* n_points x 3: GetWorldPos() */
+    const float* normal;           /* n_points x 3: GetNormal() */
+    const float* max_distance;     /* mfMaxDistance */
+    const float* min_distance;     /* mfMinDistance */
+    const uint8_t* mp_desc;        /* n_points x 32: GetDescriptor() */
+    const float* Tcw;              /* pKF pose, 4 x 4 row-major (GetRotation / GetTranslation) */
+    float Ow[3];                   /* pKF->GetCameraCenter() */
+    float fx, fy, cx, cy, bf;      /* pKF->fx .. mbf */
+    float log_scale_factor;        /* pKF->mfLogScaleFactor */
+    int32_t n_kf;                  /* pKF->N */
+    const orbgpu_keypoint* keys_un;/* pKF->mvKeysUn */
+    const uint8_t* desc;           /* pKF->mDescriptors */
+    const float* u_right;          /* pKF->mvuRight */
+    float bounds[4];               /* Frame::mnMinX, mnMaxX, mnMinY, mnMaxY the keyframe's grid was built with; the keyframe
+                                      itself keeps them truncated to int (include/KeyFrame.h:185-188), as the window does */
+    const float* scale_factors;    /* pKF->mvScaleFactors[nlevels] */
+    const float* inv_level_sigma2; /* pKF->mvInvLevelSigma2[nlevels] */
+    int32_t nlevels;
+    float th;
+} orbgpu_fuse_args;
+int orbgpu_fuse_search(int device, const orbgpu_fuse_args* args, int32_t* best_idx);
+
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
  * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order

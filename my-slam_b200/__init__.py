@@ -10,5 +10,6 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      BowSide, bow_side, search_by_bow,
                      LocalPointsArgs, local_points_args, search_local_points,
                      TriangulationArgs, triangulation_args, search_for_triangulation,
-                     LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf)  # noqa: F401
+                     LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf,
+                     FuseArgs, fuse_args, fuse_search)  # noqa: F401
 from . import shard, synth  # noqa: F401

@@ -5,6 +5,7 @@
 //   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)  src/ORBmatcher.cc:44-125 (local-map search)
 //   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine      src/ORBmatcher.cc:657-820, 140-157
 //   Frame::isInFrustum + MapPoint::PredictScale                     src/Frame.cc:269-325, src/MapPoint.cc:402-417
+//   the search of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) src/ORBmatcher.cc:825-957, src/KeyFrame.cc:569-613
 //
 // Device layout.  The 64 x 48 grid of the searched frame is a counting sort of its keypoint indices by cell id
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
@@ -39,6 +40,7 @@ struct GridDev {
     const uint8_t* desc;
     int n;
     float minX, minY, invW, invH;
+    float winX, winY;             // origin the search window is measured from: minX, minY for a Frame, their int truncation for a KeyFrame
     int* cell_start;              // GRID_CELLS + 1
     int* sorted;                  // n
 };
@@ -142,10 +144,10 @@ __global__ void __launch_bounds__(256) k_area_candidates(GridDev G, const AreaQu
     int total = 0;
     if (A.active) {
         const float x = A.x, y = A.y, r = A.r;
-        const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, G.minX), r), G.invW)));
-        const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, G.minX), r), G.invW)));
-        const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, G.minY), r), G.invH)));
-        const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, G.minY), r), G.invH)));
+        const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, G.winX), r), G.invW)));
+        const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, G.winX), r), G.invW)));
+        const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, G.winY), r), G.invH)));
+        const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, G.winY), r), G.invH)));
         if (nMinCellX < GRID_COLS && nMaxCellX >= 0 && nMinCellY < GRID_ROWS && nMaxCellY >= 0) {
             const bool bCheckLevels = (A.min_level > 0) || (A.max_level >= 0);
             const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(qdesc) + 2 * (size_t)q);
@@ -683,6 +685,113 @@ __global__ void k_frustum(FrustumCam C, const uint8_t* __restrict__ candidate, c
     if (threadIdx.x == 0 && cnt) atomicAdd(n_in_view, cnt);
 }
 
+// ---- the search of ORBmatcher::Fuse (src/ORBmatcher.cc:825-957) -----------------------------------------------------
+struct FuseCam { float R[9], t[3], Ow[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, log_scale, th; int nlevels; };
+struct FuseQuery { float u, v, ur, r; int level; int active; };
+
+__global__ void k_fuse_queries(FuseCam C, const uint8_t* __restrict__ present, const float* __restrict__ world_pos,
+                               const float* __restrict__ normal, const float* __restrict__ max_distance,
+                               const float* __restrict__ min_distance, const float* __restrict__ scale, int n, FuseQuery* __restrict__ Q)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    FuseQuery q;
+    q.u = q.v = q.ur = q.r = 0.f; q.level = 0; q.active = 0;
+    if (present[i]) {
+        const float P[3] = {world_pos[3 * (size_t)i], world_pos[3 * (size_t)i + 1], world_pos[3 * (size_t)i + 2]};
+        float Pc[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {                          // Rcw*p3Dw + tcw: cv::gemm's 3x3 float case (:854)
+            const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.R[3 * r], P[0]), __fmul_rn(C.R[3 * r + 1], P[1])), __fmul_rn(C.R[3 * r + 2], P[2]));
+            Pc[r] = (float)__dadd_rn(__dmul_rn((double)t, 1.0), __dmul_rn((double)C.t[r], 1.0));
+        }
+        if (!(Pc[2] < 0.0f)) {                                 // :857
+            const float invz = __fdiv_rn(1.0f, Pc[2]);
+            const float x = __fmul_rn(Pc[0], invz), y = __fmul_rn(Pc[1], invz);
+            const float u = __fadd_rn(__fmul_rn(C.fx, x), C.cx), v = __fadd_rn(__fmul_rn(C.fy, y), C.cy);
+            if (u >= C.minX && u < C.maxX && v >= C.minY && v < C.maxY) {             // KeyFrame::IsInImage, int bounds
+                const float maxDistance = __fmul_rn(1.2f, max_distance[i]);
+                const float minDistance = __fmul_rn(0.8f, min_distance[i]);
+                const float PO[3] = {__fsub_rn(P[0], C.Ow[0]), __fsub_rn(P[1], C.Ow[1]), __fsub_rn(P[2], C.Ow[2])};
+                double s2 = __dmul_rn((double)PO[0], (double)PO[0]);
+                s2 = __dadd_rn(s2, __dmul_rn((double)PO[1], (double)PO[1]));
+                s2 = __dadd_rn(s2, __dmul_rn((double)PO[2], (double)PO[2]));
+                const float dist3D = (float)__dsqrt_rn(s2);
+                if (!(dist3D < minDistance || dist3D > maxDistance)) {
+                    double d = __dmul_rn((double)PO[0], (double)normal[3 * (size_t)i]);
+                    d = __dadd_rn(d, __dmul_rn((double)PO[1], (double)normal[3 * (size_t)i + 1]));
+                    d = __dadd_rn(d, __dmul_rn((double)PO[2], (double)normal[3 * (size_t)i + 2]));
+                    if (!(d < __dmul_rn(0.5, (double)dist3D))) {                       // :883
+                        const float ratio = __fdiv_rn(max_distance[i], dist3D);        // PredictScale(dist3D, pKF), src/MapPoint.cc:385-400
+                        const float c = ceilf(__fdiv_rn(orb_logf(ratio), C.log_scale));
+                        int nScale = (fabsf(c) < 2147483648.f) ? (int)c : INT_MIN;
+                        if (nScale < 0) nScale = 0;
+                        else if (nScale >= C.nlevels) nScale = C.nlevels - 1;
+                        q.u = u; q.v = v; q.ur = __fsub_rn(u, __fmul_rn(C.bf, invz));
+                        q.r = __fmul_rn(C.th, scale[nScale]);
+                        q.level = nScale; q.active = 1;
+                    }
+                }
+            }
+        }
+    }
+    Q[i] = q;
+}
+
+// one warp per map point: KeyFrame::GetFeaturesInArea's visiting order (columns of the window, cells top to bottom, index
+// order inside a cell) with the level and chi-square gates of :897-928; the smallest distance wins, the first one on ties
+__global__ void __launch_bounds__(256) k_fuse_match(GridDev G, const FuseQuery* __restrict__ Q, const uint8_t* __restrict__ qdesc, int nq,
+                                                    const float* __restrict__ u_right, const float* __restrict__ inv_sigma2,
+                                                    int* __restrict__ best_idx)
+{
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const FuseQuery A = Q[q];
+    unsigned long long best = ~0ull;                           // (dist << 40) | (visit position << 16) | ... the index rides below
+    if (A.active) {
+        const float x = A.u, y = A.v, r = A.r;
+        const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, G.winX), r), G.invW)));
+        const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, G.winX), r), G.invW)));
+        const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, G.winY), r), G.invH)));
+        const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, G.winY), r), G.invH)));
+        if (nMinCellX < GRID_COLS && nMaxCellX >= 0 && nMinCellY < GRID_ROWS && nMaxCellY >= 0 && nMinCellY <= nMaxCellY) {
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(qdesc) + 2 * (size_t)q);
+            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(qdesc) + 2 * (size_t)q + 1);
+            int visited = 0;
+            for (int ix = nMinCellX; ix <= nMaxCellX; ++ix) {
+                const int p0 = G.cell_start[ix * GRID_ROWS + nMinCellY], p1 = G.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
+                for (int pb = p0; pb < p1; pb += 32) {
+                    const int p = pb + lane;
+                    if (p < p1) {
+                        const int i2 = G.sorted[p];
+                        const float kx = G.keys[7 * (size_t)i2], ky = G.keys[7 * (size_t)i2 + 1];
+                        const int oct = key_octave(G.keys, i2);
+                        bool ok = fabsf(__fsub_rn(kx, x)) < r && fabsf(__fsub_rn(ky, y)) < r;       // src/KeyFrame.cc:598-602
+                        if (oct < A.level - 1 || oct > A.level) ok = false;                           // :901-902
+                        if (ok) {
+                            const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky);
+                            const float kr = u_right[i2];
+                            float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                            double lim = 5.99;
+                            if (kr >= 0.f) { const float er = __fsub_rn(A.ur, kr); e2 = __fadd_rn(e2, __fmul_rn(er, er)); lim = 7.8; }
+                            if ((double)__fmul_rn(e2, inv_sigma2[oct]) > lim) ok = false;            // :914, :926
+                        }
+                        if (ok) {
+                            const unsigned d = (unsigned)hamming_regs(a0, a1, reinterpret_cast<const uint4*>(G.desc) + 2 * (size_t)i2);
+                            best = min(best, ((unsigned long long)d << 40) | ((unsigned long long)(unsigned)(visited + p - pb) << 16) | (unsigned)i2);
+                        }
+                    }
+                    visited += 32;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) best_idx[q] = (best != ~0ull && (unsigned)(best >> 40) <= 50u) ? (int)(best & 0xFFFFu) : -1;   // TH_LOW (:943)
+}
+
 // ---- SearchForTriangulation (src/ORBmatcher.cc:657-820) -----------------------------------------------------------
 // Queries as for SearchByBoW: the features of pKF1 without a map point inside a vocabulary node both keyframes share.
 // vbMatched2 is never set in the reference (:680, :722), so the queries are independent: one warp per query scans the
@@ -828,6 +937,7 @@ void set_grid(GridDev& G, uint8_t* d, size_t o_keys, size_t o_desc, size_t o_sta
 {
     G.keys = reinterpret_cast<const float*>(d + o_keys); G.desc = d + o_desc; G.n = n;
     G.minX = bounds[0]; G.minY = bounds[2];
+    G.winX = bounds[0]; G.winY = bounds[2];
     G.invW = static_cast<float>(GRID_COLS) / static_cast<float>(bounds[1] - bounds[0]);       // src/Frame.cc:155-156
     G.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(bounds[3] - bounds[2]);
     G.cell_start = reinterpret_cast<int*>(d + o_start); G.sorted = reinterpret_cast<int*>(d + o_sorted);
@@ -1174,6 +1284,67 @@ int orbgpu_debug_logf(int device, const float* x, int n, float* out)
     CUS(cudaGetLastError());
     CUS(cudaMemcpyAsync(out, d_o, 4 * (size_t)n, cudaMemcpyDeviceToHost, W.st));
     CUS(cudaStreamSynchronize(W.st));
+    return ORBGPU_OK;
+}
+
+int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
+{
+    if (!a || !best_idx || a->n_points < 0 || a->n_kf < 0 || a->nlevels < 1) return ORBGPU_ERR_ARG;
+    if (!a->present || !a->world_pos || !a->normal || !a->max_distance || !a->min_distance || !a->mp_desc || !a->Tcw || !a->scale_factors ||
+        !a->inv_level_sigma2) return ORBGPU_ERR_ARG;
+    if (a->n_kf > 0 && (!a->keys_un || !a->desc || !a->u_right)) return ORBGPU_ERR_ARG;
+    if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
+    const int n1 = a->n_points, n2 = a->n_kf;
+    if (n1 > (1 << 20) || n2 > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+    for (int i = 0; i < n2; ++i)
+        if (a->keys_un[i].octave < 0 || a->keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
+    for (int i = 0; i < n1; ++i) best_idx[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBGPU_OK;
+    FuseCam C;
+    const float* Tc = a->Tcw;
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = Tc[4 * r + c]; C.t[r] = Tc[4 * r + 3]; C.Ow[r] = a->Ow[r]; }
+    C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy; C.bf = a->bf;
+    // the keyframe holds the image bounds as ints (include/KeyFrame.h:185-188, src/KeyFrame.cc:42-43)
+    C.minX = (float)(int)a->bounds[0]; C.maxX = (float)(int)a->bounds[1]; C.minY = (float)(int)a->bounds[2]; C.maxY = (float)(int)a->bounds[3];
+    C.log_scale = a->log_scale_factor; C.th = a->th; C.nlevels = a->nlevels;
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2), o_ur = L.add(4 * (size_t)n2);
+    const size_t o_qdesc = L.add(32 * (size_t)n1), o_pres = L.add((size_t)n1), o_pos = L.add(12 * (size_t)n1), o_nrm = L.add(12 * (size_t)n1);
+    const size_t o_maxd = L.add(4 * (size_t)n1), o_mind = L.add(4 * (size_t)n1);
+    const size_t o_scale = L.add(4 * (size_t)a->nlevels), o_sig = L.add(4 * (size_t)a->nlevels);
+    const size_t in_bytes = L.off;
+    const size_t o_best = L.add(4 * (size_t)n1);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_q = L.add(sizeof(FuseQuery) * (size_t)n1);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_keys, a->keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_desc, a->desc, 32 * (size_t)n2);
+    memcpy(W.h + o_ur, a->u_right, 4 * (size_t)n2);
+    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(W.h + o_pres, a->present, (size_t)n1);
+    memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
+    memcpy(W.h + o_nrm, a->normal, 12 * (size_t)n1);
+    memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    memcpy(W.h + o_sig, a->inv_level_sigma2, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    GridDev G;
+    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    G.winX = C.minX; G.winY = C.minY;                          // src/KeyFrame.cc:574-586 subtract the int members
+    FuseQuery* d_q = reinterpret_cast<FuseQuery*>(W.d + o_q);
+    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_fuse_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_pres, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
+                                                       reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
+                                                       reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
+    k_fuse_match<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur),
+                                                 reinterpret_cast<const float*>(W.d + o_sig), reinterpret_cast<int*>(W.d + o_best));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + o_best, W.d + o_best, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(best_idx, W.h + o_best, 4 * (size_t)n1);
     return ORBGPU_OK;
 }
 

@@ -143,6 +143,38 @@ def local_map_args(candidate, world_pos, normal, max_distance, min_distance, mp_
     return a, arrs
 
 
+class FuseArgs(C.Structure):
+    """orbgpu_fuse_args (include/orbgpu.h): what the loop body of ORBmatcher::Fuse(pKF, vpMapPoints, th) reads."""
+    _fields_ = [("n_points", C.c_int32), ("present", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
+                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("mp_desc", C.c_void_p), ("Tcw", C.c_void_p),
+                ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("log_scale_factor", C.c_float), ("n_kf", C.c_int32), ("keys_un", C.c_void_p), ("desc", C.c_void_p),
+                ("u_right", C.c_void_p), ("bounds", C.c_float * 4), ("scale_factors", C.c_void_p), ("inv_level_sigma2", C.c_void_p),
+                ("nlevels", C.c_int32), ("th", C.c_float)]
+
+
+def fuse_args(present, world_pos, normal, max_distance, min_distance, mp_desc, Tcw, Ow, cam, bf, keys_un, desc, u_right, bounds,
+              scale_factors, inv_level_sigma2, log_scale_factor, th=3.0):
+    """Builds a FuseArgs; returns (struct, keepalive dict of the arrays it points into)."""
+    f32, u8 = np.float32, np.uint8
+    arrs = dict(present=np.ascontiguousarray(present, u8), world_pos=np.ascontiguousarray(world_pos, f32),
+                normal=np.ascontiguousarray(normal, f32), max_distance=np.ascontiguousarray(max_distance, f32),
+                min_distance=np.ascontiguousarray(min_distance, f32), mp_desc=np.ascontiguousarray(mp_desc, u8),
+                Tcw=np.ascontiguousarray(Tcw, f32), keys_un=np.ascontiguousarray(keys_un), desc=np.ascontiguousarray(desc, u8),
+                u_right=np.ascontiguousarray(u_right, f32), scale_factors=np.ascontiguousarray(scale_factors, f32),
+                inv_level_sigma2=np.ascontiguousarray(inv_level_sigma2, f32))
+    a = FuseArgs()
+    for k, v in arrs.items():
+        setattr(a, k, v.ctypes.data)
+    a.n_points = len(arrs["present"]); a.n_kf = len(arrs["keys_un"])
+    a.Ow = (C.c_float * 3)(*[float(v) for v in np.asarray(Ow, f32).reshape(3)])
+    a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+    a.bf = float(bf); a.log_scale_factor = float(log_scale_factor)
+    a.bounds = (C.c_float * 4)(*[float(v) for v in bounds])
+    a.nlevels = len(arrs["scale_factors"]); a.th = float(th)
+    return a, arrs
+
+
 class BowSide(C.Structure):
     """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
     _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
@@ -244,6 +276,7 @@ def lib():
         "orbgpu_search_local_points": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
         "orbgpu_search_local_map": (i32, [i32, vp, vp, pi, vp, pi]),
+        "orbgpu_fuse_search": (i32, [i32, vp, vp]),
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
@@ -513,6 +546,14 @@ def debug_logf(x, device=0):
     x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x)
     _check(lib().orbgpu_debug_logf(device, _p(x), len(x), _p(out)))
     return out
+
+
+def fuse_search(args, device=0):
+    """The search of ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-957) for every map point at once
+    -> best_idx[n_points]: the keypoint of pKF each point fuses with, or -1."""
+    best = np.zeros(max(args.n_points, 1), np.int32)
+    _check(lib().orbgpu_fuse_search(device, C.byref(args), _p(best)))
+    return best[:args.n_points].copy()
 
 
 def stereo_match(left, right, bf, b):

@@ -535,3 +535,86 @@ extern "C" long long frameport_logf_port_mismatches(uint32_t first, uint32_t cou
     }
     return bad;
 }
+
+// the loop body of ORBmatcher::Fuse up to the decision (src/ORBmatcher.cc:845-943) with KeyFrame::GetFeaturesInArea
+// (src/KeyFrame.cc:569-608: the grid was filled by the Frame with its float bounds, the window subtracts the keyframe's
+// int-truncated copies) and KeyFrame::IsInImage (:610-613)
+extern "C" void frameport_fuse_search(const frameport_fuse_args* a, int* best_idx)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->keys_un, a->n_kf, a->bounds);
+    const int mnMinX = (int)a->bounds[0], mnMaxX = (int)a->bounds[1], mnMinY = (int)a->bounds[2], mnMaxY = (int)a->bounds[3];
+    const float* Tc = a->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    for (int i = 0; i < a->n_points; ++i) {
+        best_idx[i] = -1;
+        if (!a->present[i]) continue;
+        const float* p3Dw = a->world_pos + 3 * (size_t)i;
+        float p3Dc[3];
+        mat3_mul_add(Tc, 4, p3Dw, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) continue;
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz;
+        const float y = p3Dc[1] * invz;
+        const float u = a->fx * x + a->cx;
+        const float v = a->fy * y + a->cy;
+        if (!(u >= mnMinX && u < mnMaxX && v >= mnMinY && v < mnMaxY)) continue;
+        const float ur = u - a->bf * invz;
+        const float maxDistance = 1.2f * a->max_distance[i];
+        const float minDistance = 0.8f * a->min_distance[i];
+        const float PO[3] = {p3Dw[0] - a->Ow[0], p3Dw[1] - a->Ow[1], p3Dw[2] - a->Ow[2]};
+        double s2 = 0;
+        for (int k = 0; k < 3; ++k) s2 += (double)PO[k] * (double)PO[k];
+        const float dist3D = std::sqrt(s2);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const float* Pn = a->normal + 3 * (size_t)i;
+        double dot = 0;
+        for (int k = 0; k < 3; ++k) dot += (double)PO[k] * (double)Pn[k];
+        if (dot < 0.5 * dist3D) continue;
+        const float ratio = a->max_distance[i] / dist3D;       // PredictScale(dist3D, pKF)
+        int nPredictedLevel = ceil(logf(ratio) / a->log_scale_factor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= a->nlevels) nPredictedLevel = a->nlevels - 1;
+        const float radius = a->th * a->scale_factors[nPredictedLevel];
+        // KeyFrame::GetFeaturesInArea(u, v, radius)
+        std::vector<size_t> vIndices;
+        {
+            const float r = radius;
+            const int nMinCellX = std::max(0, (int)floor((u - mnMinX - r) * g->invW));
+            const int nMaxCellX = std::min(GRID_COLS - 1, (int)ceil((u - mnMinX + r) * g->invW));
+            const int nMinCellY = std::max(0, (int)floor((v - mnMinY - r) * g->invH));
+            const int nMaxCellY = std::min(GRID_ROWS - 1, (int)ceil((v - mnMinY + r) * g->invH));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0))
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                        const std::vector<size_t>& vCell = g->cell[ix][iy];
+                        for (size_t j = 0; j < vCell.size(); j++) {
+                            const orbport_keypoint& kpUn = a->keys_un[vCell[j]];
+                            const float distx = kpUn.x - u, disty = kpUn.y - v;
+                            if (std::fabs(distx) < r && std::fabs(disty) < r) vIndices.push_back(vCell[j]);
+                        }
+                    }
+        }
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t c = 0; c < vIndices.size(); ++c) {
+            const size_t idx = vIndices[c];
+            const orbport_keypoint& kp = a->keys_un[idx];
+            const int kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (a->u_right[idx] >= 0) {
+                const float ex = u - kp.x, ey = v - kp.y, er = ur - a->u_right[idx];
+                const float e2 = ex * ex + ey * ey + er * er;
+                if (e2 * a->inv_level_sigma2[kpLevel] > 7.8) continue;
+            } else {
+                const float ex = u - kp.x, ey = v - kp.y;
+                const float e2 = ex * ex + ey * ey;
+                if (e2 * a->inv_level_sigma2[kpLevel] > 5.99) continue;
+            }
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)i, a->desc + 32 * idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) best_idx[i] = bestIdx;
+    }
+    delete g;
+}

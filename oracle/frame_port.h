@@ -6,6 +6,8 @@
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine    src/ORBmatcher.cc:657-820, 140-157
  *   Frame::isInFrustum + MapPoint::PredictScale (Tracking::SearchLocalPoints)  src/Frame.cc:269-325, src/MapPoint.cc:402-417
+ *   the search of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) + KeyFrame::GetFeaturesInArea / IsInImage
+ *                                                                 src/ORBmatcher.cc:825-957, src/KeyFrame.cc:569-613
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
  * PINNED: the reference's own src/Frame.cc, src/ORBmatcher.cc, src/KeyFrame.cc and src/MapPoint.cc compile unchanged
  * against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc, recipe in oracle/Makefile), and
@@ -131,6 +133,16 @@ int frameport_search_local_map(const frameport_local_map_args* a, const framepor
 void frameport_logf_array(const float* x, int n, float* out);
 /* the device's logf algorithm restated on the CPU vs the host's logf over float bit patterns first + k*step, k < count */
 long long frameport_logf_port_mismatches(uint32_t first, uint32_t count, uint32_t step);
+
+/* same layout as orbgpu_fuse_args (include/orbgpu.h): per map point, the keypoint of pKF the loop body of ORBmatcher::Fuse
+ * (src/ORBmatcher.cc:845-957) would fuse it with, or -1 */
+typedef struct frameport_fuse_args {
+    int32_t n_points; const uint8_t* present; const float* world_pos; const float* normal; const float* max_distance;
+    const float* min_distance; const uint8_t* mp_desc; const float* Tcw; float Ow[3]; float fx, fy, cx, cy, bf; float log_scale_factor;
+    int32_t n_kf; const orbport_keypoint* keys_un; const uint8_t* desc; const float* u_right; float bounds[4];
+    const float* scale_factors; const float* inv_level_sigma2; int32_t nlevels; float th;
+} frameport_fuse_args;
+void frameport_fuse_search(const frameport_fuse_args* a, int* best_idx);
 
 #ifdef __cplusplus
 }

@@ -14,6 +14,7 @@
 //   frameref_search_by_projection         ORBmatcher::SearchByProjection(Frame&, const Frame&, th, mono)  :1328-1470
 //   frameref_search_local_points          ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  :44-125
 //   frameref_search_local_map             Frame::isInFrustum (src/Frame.cc:269-325) per point + that search, as Tracking::SearchLocalPoints
+//   frameref_fuse_search                  ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) :825-957, one map point per call
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
 //   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
@@ -57,7 +58,7 @@ namespace {
 // ---- reference symbols outside the tested paths ------------------------------------------------------------------------
 namespace ORB_SLAM2 {
 Map::Map() : mnMaxKFid(0), mnBigChangeIdx(0) {}
-void Map::EraseMapPoint(MapPoint*) { never("Map::EraseMapPoint"); }
+void Map::EraseMapPoint(MapPoint*) {}     // reached from MapPoint::Replace under Fuse; the harness owns the points
 void Map::EraseKeyFrame(KeyFrame*) { never("Map::EraseKeyFrame"); }
 void KeyFrameDatabase::erase(KeyFrame*) { never("KeyFrameDatabase::erase"); }
 }  // namespace ORB_SLAM2
@@ -369,6 +370,42 @@ int frameref_search_local_map(const frameport_local_map_args* a, const frameport
         cur_match[i] = it == index_of.end() ? -1 : it->second;
     }
     return nm;
+}
+
+// ORBmatcher::Fuse on a KeyFrame built by the reference's constructor.  Fuse's map surgery makes its per-point decisions
+// observable only through the map, so the harness runs the reference's Fuse once per map point (a one-element vector) on
+// a keyframe without map points, reads which keypoint the point was attached to, and detaches it again.
+void frameref_fuse_search(const frameport_fuse_args* a, int* best_idx, float* ow_out)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame F;
+    set_scale_tables(F, a->scale_factors, a->nlevels);
+    F.mvInvLevelSigma2.assign(a->inv_level_sigma2, a->inv_level_sigma2 + a->nlevels);
+    F.mfLogScaleFactor = a->log_scale_factor;
+    fill_frame(F, a->keys_un, a->desc, a->n_kf);
+    if (a->n_kf) F.mvuRight.assign(a->u_right, a->u_right + a->n_kf);
+    F.mbf = a->bf; F.mb = 1.f; F.mThDepth = 1.f; F.mTimeStamp = 0; F.mnId = 5;
+    F.mTcw = pose_mat(a->Tcw);
+    KeyFrame* pKF = new KeyFrame(F, &world.map, static_cast<KeyFrameDatabase*>(NULL));
+    world.keyframes.push_back(pKF);
+    const cv::Mat Ow = pKF->GetCameraCenter();
+    for (int i = 0; i < 3; ++i) ow_out[i] = Ow.at<float>(i);
+    ORBmatcher matcher(0.6f, true);
+    for (int i = 0; i < a->n_points; ++i) {
+        best_idx[i] = -1;
+        if (!a->present[i]) continue;
+        MapPoint* p = world.point(a->world_pos + 3 * i, a->mp_desc + 32 * i, 3, false);
+        cv::Mat nrm(3, 1, CV_32F);
+        std::memcpy(nrm.data, a->normal + 3 * i, 3 * sizeof(float));
+        p->mNormalVector = nrm;
+        p->mfMaxDistance = a->max_distance[i]; p->mfMinDistance = a->min_distance[i];
+        std::vector<MapPoint*> one(1, p);
+        const int nf = matcher.Fuse(pKF, one, a->th);
+        const int idx = p->GetIndexInKeyFrame(pKF);
+        if ((nf == 1) != (idx >= 0)) never("Fuse: return value and observation disagree");
+        if (idx >= 0) { best_idx[i] = idx; pKF->EraseMapPointMatch((size_t)idx); p->mObservations.erase(pKF); p->nObs = 3; }
+    }
 }
 
 // strict_th_low = 0: SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches)   (side 1 = pKF, side 2 = F)

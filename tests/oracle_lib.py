@@ -70,6 +70,8 @@ class OraclePort:
         L.frameport_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameport_fuse_search.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_fuse_search.restype = None
         L.frameport_logf_array.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.frameport_logf_array.restype = None
         L.frameport_logf_port_mismatches.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
@@ -207,6 +209,12 @@ class OraclePort:
         nm = self.L.frameport_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
         return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
 
+    def fuse_search(self, args):
+        """args: the product's FuseArgs ctypes struct (same layout as frameport_fuse_args) -> best_idx[n_points]."""
+        best = _i32(args.n_points)
+        self.L.frameport_fuse_search(C.byref(args), _ptr(best))
+        return best[:args.n_points].copy()
+
     def logf_port_mismatches(self, first, count, step):
         return int(self.L.frameport_logf_port_mismatches(first, count, step))
 
@@ -339,6 +347,8 @@ class OracleFrameRef:
         L.frameref_search_local_points.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_fuse_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_fuse_search.restype = None
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -413,6 +423,12 @@ class OracleFrameRef:
         cm = _i32(args.n_cur); nv = C.c_int(0)
         nm = self.L.frameref_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
         return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+    def fuse_search(self, args):
+        """The reference's ORBmatcher::Fuse, one map point per call -> (best_idx[n_points], the camera centre it used)."""
+        best = _i32(args.n_points); ow = np.zeros(3, np.float32)
+        self.L.frameref_fuse_search(C.byref(args), _ptr(best), _ptr(ow))
+        return best[:args.n_points].copy(), ow
 
     def search_by_bow(self, side1, side2, nnratio=0.7, check_orientation=True, strict_th_low=False):
         m12 = _i32(side1.n); m21 = _i32(side2.n)

@@ -105,6 +105,13 @@ def main():
     out["search_local_map_%dx%d_th1" % (len(G1[0]), len(k2))] = {
         "gpu_ms": med(lambda: pkg.search_local_map(args)), "cpu_ms": med(lambda: po.search_local_map(args, pkg.track_fields)),
         "in_view": a[2], "nmatches": a[0]}
+    # --- the search of ORBmatcher::Fuse: 4000 map points into a 1000-feature keyframe
+    import test_fuse as tf
+    fa, fkeep = tf.fuse_from_local_map(pkg, po, keep, 3.0, bounds)
+    a = pkg.fuse_search(fa); o = po.fuse_search(fa)
+    assert np.array_equal(a, o)
+    out["fuse_search_%dx%d_th3" % (fa.n_points, fa.n_kf)] = {
+        "gpu_ms": med(lambda: pkg.fuse_search(fa)), "cpu_ms": med(lambda: po.fuse_search(fa)), "fused": int((a >= 0).sum())}
     print(json.dumps(out, indent=1))
 
 
