@@ -278,6 +278,34 @@ typedef struct orbgpu_fuse_args {
 } orbgpu_fuse_args;
 int orbgpu_fuse_search(int device, const orbgpu_fuse_args* args, int32_t* best_idx);
 
+/* ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
+ * (src/ORBmatcher.cc:1472-1597), the guided search of Tracking::Relocalization (src/Tracking.cc:1459, :1473). */
+typedef struct orbgpu_reloc_projection_args {
+    int32_t n_kf;                  /* pKF->GetMapPointMatches().size() */
+    const uint8_t* mp_valid;       /* pMP && !pMP->isBad() && !sAlreadyFound.count(pMP) */
+    const float* world_pos;        /* n_kf x 3: pMP->GetWorldPos() */
+    const float* max_distance;     /* pMP->mfMaxDistance */
+    const float* min_distance;     /* pMP->mfMinDistance */
+    const uint8_t* mp_desc;        /* n_kf x 32: pMP->GetDescriptor() */
+    const float* kf_angle;         /* pKF->mvKeysUn[i].angle */
+    int32_t n_cur;
+    const orbgpu_keypoint* cur_keys_un;   /* CurrentFrame.mvKeysUn */
+    const uint8_t* cur_desc;       /* CurrentFrame.mDescriptors */
+    const uint8_t* cur_occupied;   /* CurrentFrame.mvpMapPoints[i2] != NULL, on entry */
+    const float* Tcw_cur;          /* CurrentFrame.mTcw, 4 x 4 row-major */
+    float fx, fy, cx, cy;          /* CurrentFrame.fx .. cy */
+    float bounds[4];               /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;    /* CurrentFrame.mvScaleFactors[nlevels] */
+    float log_scale_factor;        /* CurrentFrame.mfLogScaleFactor */
+    int32_t nlevels;
+    float th;
+    int32_t orb_dist;              /* ORBdist */
+    int32_t check_orientation;     /* mbCheckOrientation */
+} orbgpu_reloc_projection_args;
+/* cur_match[n_cur]: -1 untouched, i >= 0 set to the map point of keyframe feature i, -2 set and then reset to NULL by the
+ * rotation-consistency check.  *nmatches = return value. */
+int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projection_args* args, int32_t* cur_match, int* nmatches);
+
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
  * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order

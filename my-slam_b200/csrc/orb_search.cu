@@ -6,6 +6,7 @@
 //   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine      src/ORBmatcher.cc:657-820, 140-157
 //   Frame::isInFrustum + MapPoint::PredictScale                     src/Frame.cc:269-325, src/MapPoint.cc:402-417
 //   the search of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) src/ORBmatcher.cc:825-957, src/KeyFrame.cc:569-613
+//   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1472-1597 (relocalisation)
 //
 // Device layout.  The 64 x 48 grid of the searched frame is a counting sort of its keypoint indices by cell id
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
@@ -376,8 +377,9 @@ __global__ void k_proj_queries(ProjCam C, const float* __restrict__ world_pos, c
 // the loop over the last frame's points (src/ORBmatcher.cc:1353-1443) on the candidate lists
 __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
                                                                   int n_last, int n_cur, const uint8_t* __restrict__ observed,
-                                                                  const uint8_t* __restrict__ occupied_in, int* __restrict__ cur_match,
-                                                                  int* __restrict__ accepted, int* __restrict__ nmatches_out)
+                                                                  const uint8_t* __restrict__ occupied_in, int max_dist,
+                                                                  int* __restrict__ cur_match, int* __restrict__ accepted,
+                                                                  int* __restrict__ nmatches_out)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int t = threadIdx.x;
@@ -385,7 +387,7 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t
     unsigned char* occupied = smem + (size_t)n_cur;            // mvpMapPoints[i2] && Observations() > 0
     unsigned char* obs = smem + 2 * (size_t)n_cur;
     for (int i = t; i < n_cur; i += RESOLVE_THREADS) { taker[i] = TAKER_NONE; occupied[i] = occupied_in[i]; cur_match[i] = -1; }
-    for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed[i]; accepted[i] = -1; }
+    for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed ? observed[i] : 1; accepted[i] = -1; }
     const size_t used = (2 * (size_t)n_cur + (size_t)n_last + 15) & ~(size_t)15;
     const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_last);
     if (t >= 32) return;
@@ -401,8 +403,8 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t
             if (occupied[e >> CAND_DIST_BITS]) continue;       // :1403-1405
             best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
         }
-        int take = -1;                                         // bestDist < 256 by construction; TH_HIGH
-        if (best != 0xFFFFFFFFu && (int)(best >> 16) <= 100) take = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
+        int take = -1;                                         // bestDist < 256 by construction; max_dist = TH_HIGH or ORBdist
+        if (best != 0xFFFFFFFFu && (int)(best >> 16) <= max_dist) take = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
         const bool blocks = take >= 0 && obs[i];               // an unobserved point leaves the feature free (:1431)
         const unsigned blockers = __ballot_sync(0xffffffffu, blocks);
         int ncommit = 32;
@@ -792,6 +794,52 @@ __global__ void __launch_bounds__(256) k_fuse_match(GridDev G, const FuseQuery* 
     if (lane == 0) best_idx[q] = (best != ~0ull && (unsigned)(best >> 40) <= 50u) ? (int)(best & 0xFFFFu) : -1;   // TH_LOW (:943)
 }
 
+// SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist): the projection of the keyframe's map points
+// (src/ORBmatcher.cc:1496-1528).  No depth-sign test here, and "1.0/z" is a double division (:1503).
+struct RelocCam { float R[9], t[3], Ow[3], fx, fy, cx, cy, minX, maxX, minY, maxY, log_scale, th; int nlevels; };
+
+__global__ void k_reloc_queries(RelocCam C, const uint8_t* __restrict__ valid, const float* __restrict__ world_pos,
+                                const float* __restrict__ max_distance, const float* __restrict__ min_distance,
+                                const float* __restrict__ scale, int n, AreaQuery* __restrict__ Q)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    AreaQuery q;
+    q.x = q.y = q.r = q.ur = 0.f; q.min_level = q.max_level = -1; q.active = 0; q.check_ur = 0;
+    if (valid[i]) {
+        const float P[3] = {world_pos[3 * (size_t)i], world_pos[3 * (size_t)i + 1], world_pos[3 * (size_t)i + 2]};
+        float c[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.R[3 * r], P[0]), __fmul_rn(C.R[3 * r + 1], P[1])), __fmul_rn(C.R[3 * r + 2], P[2]));
+            c[r] = (float)__dadd_rn(__dmul_rn((double)t, 1.0), __dmul_rn((double)C.t[r], 1.0));
+        }
+        const float invzc = (float)__ddiv_rn(1.0, (double)c[2]);
+        const float u = __fadd_rn(__fmul_rn(__fmul_rn(C.fx, c[0]), invzc), C.cx);
+        const float v = __fadd_rn(__fmul_rn(__fmul_rn(C.fy, c[1]), invzc), C.cy);
+        if (!(u < C.minX || u > C.maxX) && !(v < C.minY || v > C.maxY)) {
+            const float PO[3] = {__fsub_rn(P[0], C.Ow[0]), __fsub_rn(P[1], C.Ow[1]), __fsub_rn(P[2], C.Ow[2])};
+            double s2 = __dmul_rn((double)PO[0], (double)PO[0]);
+            s2 = __dadd_rn(s2, __dmul_rn((double)PO[1], (double)PO[1]));
+            s2 = __dadd_rn(s2, __dmul_rn((double)PO[2], (double)PO[2]));
+            const float dist3D = (float)__dsqrt_rn(s2);
+            const float maxDistance = __fmul_rn(1.2f, max_distance[i]);
+            const float minDistance = __fmul_rn(0.8f, min_distance[i]);
+            if (!(dist3D < minDistance || dist3D > maxDistance)) {
+                const float ratio = __fdiv_rn(max_distance[i], dist3D);
+                const float cl = ceilf(__fdiv_rn(orb_logf(ratio), C.log_scale));
+                int nScale = (fabsf(cl) < 2147483648.f) ? (int)cl : INT_MIN;
+                if (nScale < 0) nScale = 0;
+                else if (nScale >= C.nlevels) nScale = C.nlevels - 1;
+                q.x = u; q.y = v; q.r = __fmul_rn(C.th, scale[nScale]);
+                q.min_level = nScale - 1; q.max_level = nScale + 1;
+                q.active = 1;
+            }
+        }
+    }
+    Q[i] = q;
+}
+
 // ---- SearchForTriangulation (src/ORBmatcher.cc:657-820) -----------------------------------------------------------
 // Queries as for SearchByBoW: the features of pKF1 without a map point inside a vocabulary node both keyframes share.
 // vbMatched2 is never set in the reference (:680, :722), so the queries are independent: one warp per query scans the
@@ -1082,7 +1130,7 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     k_proj_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
                                                        reinterpret_cast<const int*>(W.d + o_oct), reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
     k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
-    k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, reinterpret_cast<int*>(W.d + o_cm),
+    k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, 100, reinterpret_cast<int*>(W.d + o_cm),
                                                                reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
     CUS(cudaGetLastError());
     CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
@@ -1345,6 +1393,88 @@ int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
     CUS(cudaMemcpyAsync(W.h + o_best, W.d + o_best, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
     CUS(cudaStreamSynchronize(W.st));
     memcpy(best_idx, W.h + o_best, 4 * (size_t)n1);
+    return ORBGPU_OK;
+}
+
+int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projection_args* a, int32_t* cur_match, int* nmatches)
+{
+    if (!a || !cur_match || !nmatches || a->n_kf < 0 || a->n_cur < 0 || a->nlevels < 1) return ORBGPU_ERR_ARG;
+    if (!a->mp_valid || !a->world_pos || !a->max_distance || !a->min_distance || !a->mp_desc || !a->kf_angle || !a->cur_keys_un ||
+        !a->cur_desc || !a->cur_occupied || !a->Tcw_cur || !a->scale_factors) return ORBGPU_ERR_ARG;
+    if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
+    const int n1 = a->n_kf, n2 = a->n_cur;
+    if (n1 > GRID_MAX_KEYS || n2 > GRID_MAX_KEYS || (size_t)n1 * (size_t)n2 > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
+    *nmatches = 0;
+    for (int i = 0; i < n2; ++i) cur_match[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBGPU_OK;
+    RelocCam C;
+    const float* Tc = a->Tcw_cur;
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = Tc[4 * r + c]; C.t[r] = Tc[4 * r + 3]; }
+    for (int i = 0; i < 3; ++i) {                              // Ow = -Rcw.t()*tcw (:1478), the cv::MatExpr of :1341
+        volatile float t = Tc[i] * C.t[0];
+        t = t + Tc[4 + i] * C.t[1];
+        t = t + Tc[8 + i] * C.t[2];
+        C.Ow[i] = (float)((double)t * -1.0);
+    }
+    C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy;
+    C.minX = a->bounds[0]; C.maxX = a->bounds[1]; C.minY = a->bounds[2]; C.maxY = a->bounds[3];
+    C.log_scale = a->log_scale_factor; C.th = a->th; C.nlevels = a->nlevels;
+    Layout L;
+    const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2), o_occ = L.add((size_t)n2);
+    const size_t o_pos = L.add(12 * (size_t)n1), o_qdesc = L.add(32 * (size_t)n1), o_valid = L.add((size_t)n1);
+    const size_t o_maxd = L.add(4 * (size_t)n1), o_mind = L.add(4 * (size_t)n1), o_scale = L.add(4 * (size_t)a->nlevels);
+    const size_t in_bytes = L.off;
+    const size_t o_cm = L.add(4 * (size_t)n2), o_acc = L.add(4 * (size_t)n1), o_nm = L.add(4);
+    const size_t io_bytes = L.off;
+    const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
+    const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_cand = L.add(4 * (size_t)n1 * n2);
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, L.off, io_bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(W.h + o_keys, a->cur_keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(W.h + o_desc, a->cur_desc, 32 * (size_t)n2);
+    memcpy(W.h + o_occ, a->cur_occupied, (size_t)n2);
+    memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
+    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(W.h + o_valid, a->mp_valid, (size_t)n1);
+    memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
+    memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    GridDev G;
+    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+    AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
+    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_reloc_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_valid, reinterpret_cast<const float*>(W.d + o_pos),
+                                                        reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
+                                                        reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
+    k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, nullptr, d_cand, n2, d_cn);
+    // every assigned feature holds a map point afterwards (:1545-1546): "observed" is all ones
+    k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nullptr, W.d + o_occ, a->orb_dist < 255 ? a->orb_dist : 255,
+                                                               reinterpret_cast<int*>(W.d + o_cm), reinterpret_cast<int*>(W.d + o_acc),
+                                                               reinterpret_cast<int*>(W.d + o_nm));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaStreamSynchronize(W.st));
+    memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
+    const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
+    int nm = *reinterpret_cast<const int*>(W.h + o_nm);
+    if (a->check_orientation) {                                // :1566-1587
+        int bin_of[30] = {0};
+        std::vector<int> bin((size_t)n1, -1);
+        for (int i = 0; i < n1; ++i)
+            if (acc[i] >= 0) { bin[i] = rot_bin(a->kf_angle[i], a->cur_keys_un[acc[i]].angle); bin_of[bin[i]]++; }
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(bin_of, 30, ind1, ind2, ind3);
+        for (int i = 0; i < n1; ++i) {
+            if (bin[i] < 0 || bin[i] == ind1 || bin[i] == ind2 || bin[i] == ind3) continue;
+            cur_match[acc[i]] = -2;
+            nm--;
+        }
+    }
+    *nmatches = nm;
     return ORBGPU_OK;
 }
 

@@ -175,6 +175,37 @@ def fuse_args(present, world_pos, normal, max_distance, min_distance, mp_desc, T
     return a, arrs
 
 
+class RelocProjectionArgs(C.Structure):
+    """orbgpu_reloc_projection_args (include/orbgpu.h): SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)."""
+    _fields_ = [("n_kf", C.c_int32), ("mp_valid", C.c_void_p), ("world_pos", C.c_void_p), ("max_distance", C.c_void_p),
+                ("min_distance", C.c_void_p), ("mp_desc", C.c_void_p), ("kf_angle", C.c_void_p),
+                ("n_cur", C.c_int32), ("cur_keys_un", C.c_void_p), ("cur_desc", C.c_void_p), ("cur_occupied", C.c_void_p),
+                ("Tcw_cur", C.c_void_p), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("bounds", C.c_float * 4), ("scale_factors", C.c_void_p), ("log_scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("th", C.c_float), ("orb_dist", C.c_int32), ("check_orientation", C.c_int32)]
+
+
+def reloc_projection_args(mp_valid, world_pos, max_distance, min_distance, mp_desc, kf_angle, cur_keys_un, cur_desc, cur_occupied,
+                          Tcw_cur, cam, bounds, scale_factors, log_scale_factor, th, orb_dist, check_orientation=True):
+    """Builds a RelocProjectionArgs; returns (struct, keepalive dict)."""
+    f32, u8 = np.float32, np.uint8
+    arrs = dict(mp_valid=np.ascontiguousarray(mp_valid, u8), world_pos=np.ascontiguousarray(world_pos, f32),
+                max_distance=np.ascontiguousarray(max_distance, f32), min_distance=np.ascontiguousarray(min_distance, f32),
+                mp_desc=np.ascontiguousarray(mp_desc, u8), kf_angle=np.ascontiguousarray(kf_angle, f32),
+                cur_keys_un=np.ascontiguousarray(cur_keys_un), cur_desc=np.ascontiguousarray(cur_desc, u8),
+                cur_occupied=np.ascontiguousarray(cur_occupied, u8), Tcw_cur=np.ascontiguousarray(Tcw_cur, f32),
+                scale_factors=np.ascontiguousarray(scale_factors, f32))
+    a = RelocProjectionArgs()
+    for k, v in arrs.items():
+        setattr(a, k, v.ctypes.data)
+    a.n_kf = len(arrs["mp_valid"]); a.n_cur = len(arrs["cur_keys_un"])
+    a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+    a.bounds = (C.c_float * 4)(*[float(v) for v in bounds])
+    a.log_scale_factor = float(log_scale_factor); a.nlevels = len(arrs["scale_factors"]); a.th = float(th)
+    a.orb_dist = int(orb_dist); a.check_orientation = int(check_orientation)
+    return a, arrs
+
+
 class BowSide(C.Structure):
     """orbgpu_bow_side (include/orbgpu.h): descriptors, validity, angles and the flattened DBoW2 FeatureVector of one side."""
     _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("valid", C.c_void_p), ("angle", C.c_void_p),
@@ -277,6 +308,7 @@ def lib():
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
         "orbgpu_search_local_map": (i32, [i32, vp, vp, pi, vp, pi]),
         "orbgpu_fuse_search": (i32, [i32, vp, vp]),
+        "orbgpu_search_by_projection_keyframe": (i32, [i32, vp, vp, pi]),
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
@@ -554,6 +586,14 @@ def fuse_search(args, device=0):
     best = np.zeros(max(args.n_points, 1), np.int32)
     _check(lib().orbgpu_fuse_search(device, C.byref(args), _p(best)))
     return best[:args.n_points].copy()
+
+
+def search_by_projection_keyframe(args, device=0):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1472-1597)
+    -> (nmatches, cur_match[n_cur])."""
+    cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_by_projection_keyframe(device, C.byref(args), _p(cm), C.byref(nm)))
+    return nm.value, cm[:args.n_cur].copy()
 
 
 def stereo_match(left, right, bf, b):

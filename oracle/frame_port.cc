@@ -618,3 +618,69 @@ extern "C" void frameport_fuse_search(const frameport_fuse_args* a, int* best_id
     }
     delete g;
 }
+
+// src/ORBmatcher.cc:1472-1597
+extern "C" int frameport_search_by_projection_keyframe(const frameport_reloc_projection_args* a, int* cur_match)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->cur_keys_un, a->n_cur, a->bounds);
+    int nmatches = 0;
+    const float* Tc = a->Tcw_cur;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float Ow[3];                                              // -Rcw.t()*tcw (:1478), lowered as at :1341
+    for (int i = 0; i < 3; ++i) {
+        const float t = Tc[i] * tcw[0] + Tc[4 + i] * tcw[1] + Tc[8 + i] * tcw[2];
+        Ow[i] = (float)((double)t * -1.0);
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<uint8_t> occupied(a->cur_occupied, a->cur_occupied + a->n_cur);
+    for (int i = 0; i < a->n_cur; ++i) cur_match[i] = -1;
+    for (int i = 0; i < a->n_kf; ++i) {
+        if (!a->mp_valid[i]) continue;
+        const float* x3Dw = a->world_pos + 3 * (size_t)i;
+        float x3Dc[3];
+        mat3_mul_add(Tc, 4, x3Dw, tcw, x3Dc);
+        const float xc = x3Dc[0], yc = x3Dc[1];
+        const float invzc = 1.0 / x3Dc[2];
+        const float u = a->fx * xc * invzc + a->cx;
+        const float v = a->fy * yc * invzc + a->cy;
+        if (u < a->bounds[0] || u > a->bounds[1]) continue;
+        if (v < a->bounds[2] || v > a->bounds[3]) continue;
+        const float PO[3] = {x3Dw[0] - Ow[0], x3Dw[1] - Ow[1], x3Dw[2] - Ow[2]};
+        double s2 = 0;
+        for (int k = 0; k < 3; ++k) s2 += (double)PO[k] * (double)PO[k];
+        float dist3D = std::sqrt(s2);
+        const float maxDistance = 1.2f * a->max_distance[i];
+        const float minDistance = 0.8f * a->min_distance[i];
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const float ratio = a->max_distance[i] / dist3D;
+        int nPredictedLevel = ceil(logf(ratio) / a->log_scale_factor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= a->nlevels) nPredictedLevel = a->nlevels - 1;
+        const float radius = a->th * a->scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices2 = features_in_area(*g, u, v, radius, nPredictedLevel - 1, nPredictedLevel + 1);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t c = 0; c < vIndices2.size(); ++c) {
+            const size_t i2 = vIndices2[c];
+            if (occupied[i2]) continue;
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)i, a->cur_desc + 32 * i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = (int)i2; }
+        }
+        if (bestDist <= a->orb_dist) {
+            occupied[bestIdx2] = 1;
+            cur_match[bestIdx2] = i;
+            nmatches++;
+            if (a->check_orientation) rotHist[rot_bin(a->kf_angle[i], a->cur_keys_un[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (a->check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (size_t j = 0; j < rotHist[i].size(); ++j) { cur_match[rotHist[i][j]] = -2; nmatches--; }
+    }
+    delete g;
+    return nmatches;
+}

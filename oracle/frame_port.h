@@ -6,6 +6,7 @@
  *   ORBmatcher::SearchByBoW (both overloads)                      src/ORBmatcher.cc:159-288, 522-655
  *   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine    src/ORBmatcher.cc:657-820, 140-157
  *   Frame::isInFrustum + MapPoint::PredictScale (Tracking::SearchLocalPoints)  src/Frame.cc:269-325, src/MapPoint.cc:402-417
+ *   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1472-1597
  *   the search of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) + KeyFrame::GetFeaturesInArea / IsInImage
  *                                                                 src/ORBmatcher.cc:825-957, src/KeyFrame.cc:569-613
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
@@ -143,6 +144,18 @@ typedef struct frameport_fuse_args {
     const float* scale_factors; const float* inv_level_sigma2; int32_t nlevels; float th;
 } frameport_fuse_args;
 void frameport_fuse_search(const frameport_fuse_args* a, int* best_idx);
+
+/* same layout as orbgpu_reloc_projection_args (include/orbgpu.h): ORBmatcher::SearchByProjection(CurrentFrame, pKF,
+ * sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1472-1597) */
+typedef struct frameport_reloc_projection_args {
+    int32_t n_kf; const uint8_t* mp_valid; const float* world_pos; const float* max_distance; const float* min_distance;
+    const uint8_t* mp_desc; const float* kf_angle;
+    int32_t n_cur; const orbport_keypoint* cur_keys_un; const uint8_t* cur_desc; const uint8_t* cur_occupied; const float* Tcw_cur;
+    float fx, fy, cx, cy; float bounds[4]; const float* scale_factors; float log_scale_factor; int32_t nlevels; float th;
+    int32_t orb_dist; int32_t check_orientation;
+} frameport_reloc_projection_args;
+/* returns nmatches; cur_match[n_cur]: -1 untouched, -2 reset by the rotation check, >= 0 keyframe feature index */
+int frameport_search_by_projection_keyframe(const frameport_reloc_projection_args* a, int* cur_match);
 
 #ifdef __cplusplus
 }

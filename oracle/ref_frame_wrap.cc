@@ -15,6 +15,7 @@
 //   frameref_search_local_points          ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)  :44-125
 //   frameref_search_local_map             Frame::isInFrustum (src/Frame.cc:269-325) per point + that search, as Tracking::SearchLocalPoints
 //   frameref_fuse_search                  ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) :825-957, one map point per call
+//   frameref_search_by_projection_keyframe  ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) :1472-1597
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
 //   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
@@ -27,6 +28,7 @@
 #include <opencv2/core/core.hpp>
 #include <cstdio>
 #include <map>
+#include <set>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -406,6 +408,51 @@ void frameref_fuse_search(const frameport_fuse_args* a, int* best_idx, float* ow
         if ((nf == 1) != (idx >= 0)) never("Fuse: return value and observation disagree");
         if (idx >= 0) { best_idx[i] = idx; pKF->EraseMapPointMatch((size_t)idx); p->mObservations.erase(pKF); p->nObs = 3; }
     }
+}
+
+// The relocalisation search.  mp_valid = 0 cycles through the three ways the reference skips a keyframe feature: no map
+// point, a bad one, one already in sAlreadyFound.
+int frameref_search_by_projection_keyframe(const frameport_reloc_projection_args* a, int* cur_match)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame Cur, Src;
+    set_scale_tables(Cur, a->scale_factors, a->nlevels);
+    Cur.mfLogScaleFactor = a->log_scale_factor;
+    fill_frame(Cur, a->cur_keys_un, a->cur_desc, a->n_cur);
+    const float origin[3] = {0, 0, 0};
+    for (int i = 0; i < a->n_cur; ++i)
+        if (a->cur_occupied[i]) Cur.mvpMapPoints[i] = world.point(origin, 0, (i & 1), false);     // observed or not: any map point blocks
+    Cur.SetPose(pose_mat(a->Tcw_cur));
+    // the keyframe: only its map point matches and keypoint angles are read
+    std::vector<KP> kk((size_t)a->n_kf);
+    for (int i = 0; i < a->n_kf; ++i) { std::memset(&kk[i], 0, sizeof(KP)); kk[i].x = 10.f + (float)(i % 600); kk[i].y = 10.f + (float)(i % 400); kk[i].angle = a->kf_angle[i]; }
+    set_scale_tables(Src, a->scale_factors, a->nlevels);
+    fill_frame(Src, kk.data(), 0, a->n_kf);
+    Src.mDescriptors = cv::Mat(a->n_kf > 0 ? a->n_kf : 1, 32, CV_8U);
+    Src.mTcw = cv::Mat::eye(4, 4, CV_32F);
+    Src.mbf = 1.f; Src.mb = 1.f; Src.mThDepth = 1.f; Src.mTimeStamp = 0; Src.mnId = 9;
+    std::set<MapPoint*> already;
+    std::map<MapPoint*, int> index_of;
+    for (int i = 0; i < a->n_kf; ++i) {
+        const int how = a->mp_valid[i] ? -1 : i % 3;
+        if (how == 0) continue;                                // no map point
+        MapPoint* p = world.point(a->world_pos + 3 * i, a->mp_desc + 32 * i, 2, how == 1);
+        p->mfMaxDistance = a->max_distance[i]; p->mfMinDistance = a->min_distance[i];
+        Src.mvpMapPoints[i] = p;
+        index_of[p] = i;
+        if (how == 2) already.insert(p);
+    }
+    KeyFrame* pKF = new KeyFrame(Src, &world.map, static_cast<KeyFrameDatabase*>(NULL));
+    world.keyframes.push_back(pKF);
+    ORBmatcher matcher(0.9f, a->check_orientation != 0);
+    const int nm = matcher.SearchByProjection(Cur, pKF, already, a->th, a->orb_dist);
+    for (int i = 0; i < a->n_cur; ++i) {
+        MapPoint* p = Cur.mvpMapPoints[i];
+        std::map<MapPoint*, int>::const_iterator it = p ? index_of.find(p) : index_of.end();
+        cur_match[i] = it == index_of.end() ? -1 : it->second;
+    }
+    return nm;
 }
 
 // strict_th_low = 0: SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches)   (side 1 = pKF, side 2 = F)

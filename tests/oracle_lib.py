@@ -71,6 +71,7 @@ class OraclePort:
         L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameport_fuse_search.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_fuse_search.restype = None
         L.frameport_logf_array.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.frameport_logf_array.restype = None
@@ -208,6 +209,11 @@ class OraclePort:
         cm = _i32(args.n_cur); nv = C.c_int(0)
         nm = self.L.frameport_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
         return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+    def search_by_projection_keyframe(self, args):
+        cm = _i32(args.n_cur)
+        nm = self.L.frameport_search_by_projection_keyframe(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
 
     def fuse_search(self, args):
         """args: the product's FuseArgs ctypes struct (same layout as frameport_fuse_args) -> best_idx[n_points]."""
@@ -348,6 +354,7 @@ class OracleFrameRef:
         L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_fuse_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_fuse_search.restype = None
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.frameref_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
@@ -423,6 +430,12 @@ class OracleFrameRef:
         cm = _i32(args.n_cur); nv = C.c_int(0)
         nm = self.L.frameref_search_local_map(C.byref(args), C.byref(t), C.byref(nv), _ptr(cm))
         return nm, cm[:args.n_cur].copy(), nv.value, {k: v[:args.n_points] for k, v in arrs.items()}
+
+    def search_by_projection_keyframe(self, args):
+        """-> (nmatches, cur_match) with cur_match[i2] = keyframe feature index or -1 (the restatement's -2 reads as -1 here)."""
+        cm = _i32(args.n_cur)
+        nm = self.L.frameref_search_by_projection_keyframe(C.byref(args), _ptr(cm))
+        return nm, cm[:args.n_cur].copy()
 
     def fuse_search(self, args):
         """The reference's ORBmatcher::Fuse, one map point per call -> (best_idx[n_points], the camera centre it used)."""
