@@ -202,6 +202,76 @@ def cpu_extractor_fps(frames, threads, target_s):
     return done / sec, "port", sec, done
 
 
+def _cv2_primitives_worker(job):
+    """One process: OpenCV's own SIMD primitives on a few frames, as an extractor built on real OpenCV would call them
+    (src/ORBextractor.cc:1109-1137 resize chain, :1083-1088 blur, :791-831 per-cell FAST); returns seconds per frame."""
+    frames, sizes, ini_th, min_th, per_cell, seconds = job
+    import cv2
+    cv2.setNumThreads(1)
+    fast_ini = cv2.FastFeatureDetector_create(ini_th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    fast_min = cv2.FastFeatureDetector_create(min_th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+
+    def one(img):
+        lv = [img]
+        for (w, h) in sizes[1:]:
+            lv.append(cv2.resize(lv[-1], (w, h), interpolation=cv2.INTER_LINEAR))
+        n = 0
+        for im in lv:
+            if per_cell:                                       # the reference's 30-px cells, iniTh then minTh
+                H, W = im.shape
+                minB, maxBX, maxBY = 16, W - 16, H - 16
+                nC, nR = int((maxBX - minB) / 30.0), int((maxBY - minB) / 30.0)
+                if nC < 1 or nR < 1:
+                    continue
+                wC, hC = -(-(maxBX - minB) // nC), -(-(maxBY - minB) // nR)
+                for i in range(nR):
+                    y0 = minB + i * hC
+                    if y0 >= maxBY - 3:
+                        continue
+                    y1 = min(y0 + hC + 6, maxBY)
+                    for j in range(nC):
+                        x0 = minB + j * wC
+                        if x0 >= maxBX - 6:
+                            continue
+                        cell = im[y0:y1, x0:min(x0 + wC + 6, maxBX)]
+                        k = fast_ini.detect(cell)
+                        if not k:
+                            k = fast_min.detect(cell)
+                        n += len(k)
+            else:                                              # one call per level at iniTh: less work than the cells need
+                n += len(fast_ini.detect(im))
+            cv2.GaussianBlur(im, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+        return n
+    one(frames[0])
+    t0 = time.perf_counter(); done = 0
+    while time.perf_counter() - t0 < seconds:
+        for f in frames:
+            one(f); done += 1
+    return (time.perf_counter() - t0) / done
+
+
+def cv2_primitives(frames, sizes, threads, seconds=2.0):
+    """A second CPU figure: the time OpenCV's hand-vectorised resize / FAST / GaussianBlur take on this
+    box's cores for one frame's worth of calls -- a floor under ANY CPU extractor built on OpenCV (octree, orientation
+    and descriptors come on top), so the speed-up quoted against the shim-backed reference is not the only yardstick."""
+    try:
+        import cv2
+        import multiprocessing as mp
+    except Exception as e:                                     # cv2 is optional
+        return {"unavailable": str(e)}
+    p = PARAMS
+    out = {"opencv": cv2.__version__,
+           "covers": "7 cv2.resize + 8 cv2.GaussianBlur + cv2.FAST per frame; no octree, orientation, descriptors"}
+    ctx = mp.get_context("fork")
+    for name, per_cell in (("per_level_fast", False), ("per_cell_fast_python_loop", True)):
+        job = (frames[:8], sizes, p["ini_th"], p["min_th"], per_cell, seconds)
+        s1 = _cv2_primitives_worker(job)
+        with ctx.Pool(threads) as pool:
+            sN = pool.map(_cv2_primitives_worker, [job] * threads)
+        out[name] = {"frames_per_s_1_thread": 1.0 / s1, "frames_per_s_%d_processes" % threads: float(sum(1.0 / x for x in sN))}
+    return out
+
+
 def run_reference(args, rank):
     """Reference arm: the reference's own CPU implementation of the path, all host threads."""
     if rank != 0:
@@ -498,6 +568,7 @@ def run_ours(args, rank, world, local_rank):
         if kind == "reference":
             fps1, _, sec1, done1 = cpu_extractor_fps(make_frames(pkg, 16, 0), 1, min(args.cpu_seconds, 5.0))
             line["cpu_baseline"]["single_thread_value"] = fps1
+        line["cpu_baseline"]["opencv_primitives"] = cv2_primitives(make_frames(pkg, 8, 0), level_sizes(w, h, PARAMS["nlevels"], PARAMS["scale"]), threads)
     if world > 1:
         dist.destroy_process_group()
     print(json.dumps(line), flush=True)
