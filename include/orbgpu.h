@@ -422,6 +422,15 @@ int orbgpu_matcher_count_pairs_device(orbgpu_matcher* m, const int32_t* d_pairs,
 /* milliseconds of the most recent count_pairs kernel (CUDA events on its stream) */
 double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-303), batched over map points: LocalMapping calls it for
+ * every map point a new keyframe touches (src/LocalMapping.cc ProcessNewKeyFrame / CreateNewMapPoints / SearchInNeighbors),
+ * each call an N x N table of DescriptorDistance (:281) and a median per row.  Group g = the descriptors
+ * desc[group_start[g] .. group_start[g + 1]) of one map point's observations, in the order the reference collects them
+ * (its std::map<KeyFrame*, size_t> iteration, bad keyframes left out).  best_idx[g] = BestIdx: the row with the smallest
+ * median distance (element int(0.5 * (N - 1)) of the sorted row, the row's own 0 included), the first one on ties; -1 for
+ * an empty group (the reference returns without touching mDescriptor). */
+int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* group_start, int n_groups, int32_t* best_idx);
+
 /* ---- misc ---------------------------------------------------------------------------------- */
 const char* orbgpu_strerror(int code);
 const char* orbgpu_last_cuda_error(void);   /* thread-local text of the last CUDA failure */

@@ -109,6 +109,40 @@ __global__ void __launch_bounds__(MATCH_THREADS) k_match_count_pairs(const uint4
     if (threadIdx.x == 0 && c) atomicAdd(&counts[blockIdx.y], c);
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-303), one warp per map point.  Lane r owns rows r, r + 32, ...:
+// the row's N distances go into the lane's own 257-bin histogram (distances are 0..256; layout [bin][lane] so the lanes of
+// a warp never collide), the median is the first bin whose running count exceeds k = int(0.5 (N - 1)).  The best row is
+// the minimum of (median << 16 | row): strict '<' in row order = the first row among equal medians (:296-300).
+#define DD_WARPS 4
+#define DD_BINS 257
+
+__global__ void __launch_bounds__(DD_WARPS * 32) k_distinctive(const uint4* __restrict__ desc, const int* __restrict__ group_start,
+                                                                int n_groups, int* __restrict__ best_idx)
+{
+    extern __shared__ unsigned short dd_hist[];                // [DD_WARPS][DD_BINS][32]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = blockIdx.x * DD_WARPS + warp;
+    if (g >= n_groups) return;
+    const int s0 = group_start[g], N = group_start[g + 1] - s0;
+    if (N <= 0) { if (lane == 0) best_idx[g] = -1; return; }
+    unsigned short* h = dd_hist + (size_t)warp * DD_BINS * 32 + lane;
+    const int k = (N - 1) >> 1;                                // vDists[0.5 * (N - 1)]
+    unsigned best = 0xFFFFFFFFu;
+    for (int r = lane; r < N; r += 32) {
+        for (int b = 0; b < DD_BINS; ++b) h[b * 32] = 0;
+        const uint4 q0 = __ldg(desc + 2 * (size_t)(s0 + r)), q1 = __ldg(desc + 2 * (size_t)(s0 + r) + 1);
+        for (int j = 0; j < N; ++j) {
+            const uint4 c0 = __ldg(desc + 2 * (size_t)(s0 + j)), c1 = __ldg(desc + 2 * (size_t)(s0 + j) + 1);
+            h[hamming256(q0, q1, c0, c1) * 32]++;              // j == r gives Distances[i][i] = 0
+        }
+        int run = 0, med = 0;
+        for (int b = 0; b < DD_BINS; ++b) { run += h[b * 32]; if (run > k) { med = b; break; } }
+        best = min(best, ((unsigned)med << 16) | (unsigned)r);
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (lane == 0) best_idx[g] = (int)(best & 0xFFFFu);
+}
+
 struct orbgpu_matcher {
     int device = 0;
     cudaStream_t st = nullptr;
@@ -147,6 +181,47 @@ int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t*
     CUM(cudaMemcpy(best, d1, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
     CUM(cudaMemcpy(second, d2, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
     cudaFree(dA); cudaFree(dB); cudaFree(di); cudaFree(d1); cudaFree(d2);
+    return ORBGPU_OK;
+}
+
+int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* group_start, int n_groups, int32_t* best_idx)
+{
+    if (!group_start || !best_idx || n_groups < 0) return ORBGPU_ERR_ARG;
+    if (n_groups == 0) return ORBGPU_OK;
+    const int total = group_start[n_groups];
+    if (group_start[0] != 0 || total < 0 || (total > 0 && !desc)) return ORBGPU_ERR_ARG;
+    for (int g = 0; g < n_groups; ++g) {
+        if (group_start[g + 1] < group_start[g]) return ORBGPU_ERR_ARG;
+        if (group_start[g + 1] - group_start[g] > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;     // row index rides in 16 bits
+    }
+    CUM(cudaSetDevice(device));
+    static thread_local bool attr_set = false;
+    const size_t smem = (size_t)DD_WARPS * DD_BINS * 32 * sizeof(unsigned short);
+    if (!attr_set) {
+        CUM(cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    uint8_t* d = nullptr;
+    const size_t b_desc = ((size_t)32 * (size_t)(total > 0 ? total : 1) + 255) & ~(size_t)255;
+    const size_t b_gs = ((size_t)4 * (size_t)(n_groups + 1) + 255) & ~(size_t)255, b_out = (size_t)4 * (size_t)n_groups;
+    CUM(cudaMalloc(&d, b_desc + b_gs + b_out));
+    cudaError_t e = cudaSuccess;
+    if (total > 0) e = cudaMemcpy(d, desc, (size_t)32 * total, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d + b_desc, group_start, (size_t)4 * (n_groups + 1), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_distinctive<<<(n_groups + DD_WARPS - 1) / DD_WARPS, DD_WARPS * 32, smem>>>(reinterpret_cast<const uint4*>(d),
+                                                                                     reinterpret_cast<const int*>(d + b_desc), n_groups,
+                                                                                     reinterpret_cast<int*>(d + b_desc + b_gs));
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(best_idx, d + b_desc + b_gs, b_out, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) {
+        char b[256];
+        snprintf(b, sizeof(b), "orbgpu_distinctive_descriptors: %s", cudaGetErrorString(e));
+        orbgpu_internal_set_error(b);
+        return ORBGPU_ERR_CUDA;
+    }
     return ORBGPU_OK;
 }
 

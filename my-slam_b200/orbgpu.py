@@ -312,6 +312,7 @@ def lib():
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
+        "orbgpu_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
@@ -594,6 +595,15 @@ def search_by_projection_keyframe(args, device=0):
     cm = np.zeros(max(args.n_cur, 1), np.int32); nm = C.c_int(0)
     _check(lib().orbgpu_search_by_projection_keyframe(device, C.byref(args), _p(cm), C.byref(nm)))
     return nm.value, cm[:args.n_cur].copy()
+
+
+def distinctive_descriptors(desc, group_start, device=0):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-303) for many map points at once: desc (total x 32),
+    group_start (n_groups + 1) -> BestIdx per group (-1 for an empty group)."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); gs = np.ascontiguousarray(group_start, np.int32)
+    out = np.zeros(max(len(gs) - 1, 1), np.int32)
+    _check(lib().orbgpu_distinctive_descriptors(device, _p(d) if len(d) else None, _p(gs), len(gs) - 1, _p(out)))
+    return out[:len(gs) - 1].copy()
 
 
 def stereo_match(left, right, bf, b):

@@ -684,3 +684,31 @@ extern "C" int frameport_search_by_projection_keyframe(const frameport_reloc_pro
     delete g;
     return nmatches;
 }
+
+// src/MapPoint.cc:272-303
+extern "C" void frameport_distinctive_descriptors(const uint8_t* desc, const int32_t* group_start, int n_groups, int* best_idx)
+{
+    for (int g = 0; g < n_groups; ++g) {
+        const uint8_t* d = desc + 32 * (size_t)group_start[g];
+        const size_t N = (size_t)(group_start[g + 1] - group_start[g]);
+        best_idx[g] = -1;
+        if (N == 0) continue;
+        std::vector<float> Distances(N * N);
+        for (size_t i = 0; i < N; i++) {
+            Distances[i * N + i] = 0;
+            for (size_t j = i + 1; j < N; j++) {
+                const int distij = orbport_hamming256(d + 32 * i, d + 32 * j);
+                Distances[i * N + j] = distij;
+                Distances[j * N + i] = distij;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (size_t i = 0; i < N; i++) {
+            std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + (i + 1) * N);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[0.5 * (N - 1)];
+            if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+        }
+        best_idx[g] = BestIdx;
+    }
+}

@@ -157,6 +157,10 @@ typedef struct frameport_reloc_projection_args {
 /* returns nmatches; cur_match[n_cur]: -1 untouched, -2 reset by the rotation check, >= 0 keyframe feature index */
 int frameport_search_by_projection_keyframe(const frameport_reloc_projection_args* a, int* cur_match);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-303) on groups of descriptors given in the order the
+ * reference collects them; best_idx[g] = BestIdx, -1 for an empty group */
+void frameport_distinctive_descriptors(const uint8_t* desc, const int32_t* group_start, int n_groups, int* best_idx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,6 +17,7 @@
 //   frameref_fuse_search                  ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) :825-957, one map point per call
 //   frameref_search_by_projection_keyframe  ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) :1472-1597
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
+//   frameref_distinctive_descriptors      MapPoint::ComputeDistinctiveDescriptors         src/MapPoint.cc:242-303
 //   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
 //   frameref_undistort_keypoints          Frame::UndistortKeyPoints + ComputeImageBounds  src/Frame.cc:404-463
 //   frameref_descriptor_distance / frameref_three_maxima   ORBmatcher::DescriptorDistance :1647-1663, ComputeThreeMaxima :1601-1642
@@ -26,6 +27,7 @@
 // aborting stand-ins.  "private"/"protected" are opened for the reference headers in THIS file only (class layout is
 // unchanged) so the harness can fill members such as MapPoint::mDescriptor without running the whole SLAM system.
 #include <opencv2/core/core.hpp>
+#include <algorithm>
 #include <cstdio>
 #include <map>
 #include <set>
@@ -556,6 +558,50 @@ int frameref_search_for_triangulation(const frameport_triangulation_args* a, con
         matches12[pairs[k].first] = (int)pairs[k].second;
     }
     return nm;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors on groups of descriptors.  The reference walks std::map<KeyFrame*, size_t>, i.e.
+// the observing keyframes in ADDRESS order: a pool of keyframes sorted by address carries the group's descriptors in the
+// given order (one one-row mDescriptors each); best_idx[g] = the row whose descriptor the map point ends up with (the
+// first such row when several are equal -- equal rows have equal medians, and the reference keeps the first).
+void frameref_distinctive_descriptors(const uint8_t* desc, const int32_t* group_start, int n_groups, int* best_idx)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, 1.f, 1.f, 0.f, 0.f);
+    World world;
+    int nmax = 0;
+    for (int g = 0; g < n_groups; ++g) nmax = std::max(nmax, group_start[g + 1] - group_start[g]);
+    std::vector<KeyFrame*> pool;
+    for (int j = 0; j < nmax; ++j) {
+        Frame F;
+        F.N = 0; F.mTcw = cv::Mat::eye(4, 4, CV_32F); F.mnId = (unsigned long)(j + 1);
+        F.mbf = 1.f; F.mb = 1.f; F.mThDepth = 1.f; F.mTimeStamp = 0;
+        F.mnScaleLevels = 1; F.mfScaleFactor = 1.2f; F.mfLogScaleFactor = std::log(1.2f);
+        KeyFrame* kf = new KeyFrame(F, &world.map, static_cast<KeyFrameDatabase*>(NULL));
+        world.keyframes.push_back(kf);
+        pool.push_back(kf);
+    }
+    std::sort(pool.begin(), pool.end());
+    const float origin[3] = {0, 0, 0};
+    for (int g = 0; g < n_groups; ++g) {
+        const int N = group_start[g + 1] - group_start[g];
+        const uint8_t* d = desc + 32 * (size_t)group_start[g];
+        best_idx[g] = -1;
+        MapPoint* p = world.point(origin, 0, N, false);
+        p->mDescriptor = cv::Mat();
+        p->mObservations.clear();
+        for (int j = 0; j < N; ++j) {
+            cv::Mat row(1, 32, CV_8U);
+            std::memcpy(row.data, d + 32 * (size_t)j, 32);
+            const_cast<cv::Mat&>(pool[j]->mDescriptors) = row;
+            p->mObservations[pool[j]] = 0;
+        }
+        p->ComputeDistinctiveDescriptors();
+        const cv::Mat out = p->GetDescriptor();
+        if (N == 0) { if (!out.empty()) never("ComputeDistinctiveDescriptors touched an unobserved point"); continue; }
+        for (int j = 0; j < N && best_idx[g] < 0; ++j)
+            if (std::memcmp(out.data, d + 32 * (size_t)j, 32) == 0) best_idx[g] = j;
+    }
 }
 
 // Frame::ComputeStereoMatches on caller-provided keypoints, descriptors and UNBLURRED pyramid levels (dense rows).

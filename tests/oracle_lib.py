@@ -71,6 +71,8 @@ class OraclePort:
         L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameport_fuse_search.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.frameport_distinctive_descriptors.restype = None
         L.frameport_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_fuse_search.restype = None
         L.frameport_logf_array.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -215,6 +217,12 @@ class OraclePort:
         nm = self.L.frameport_search_by_projection_keyframe(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
 
+    def distinctive_descriptors(self, desc, group_start):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); gs = np.ascontiguousarray(group_start, np.int32)
+        out = _i32(len(gs) - 1)
+        self.L.frameport_distinctive_descriptors(_ptr(d), _ptr(gs), len(gs) - 1, _ptr(out))
+        return out[:len(gs) - 1].copy()
+
     def fuse_search(self, args):
         """args: the product's FuseArgs ctypes struct (same layout as frameport_fuse_args) -> best_idx[n_points]."""
         best = _i32(args.n_points)
@@ -354,6 +362,8 @@ class OracleFrameRef:
         L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_fuse_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.frameref_distinctive_descriptors.restype = None
         L.frameref_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
         L.frameref_fuse_search.restype = None
         L.frameref_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -436,6 +446,12 @@ class OracleFrameRef:
         cm = _i32(args.n_cur)
         nm = self.L.frameref_search_by_projection_keyframe(C.byref(args), _ptr(cm))
         return nm, cm[:args.n_cur].copy()
+
+    def distinctive_descriptors(self, desc, group_start):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); gs = np.ascontiguousarray(group_start, np.int32)
+        out = _i32(len(gs) - 1)
+        self.L.frameref_distinctive_descriptors(_ptr(d), _ptr(gs), len(gs) - 1, _ptr(out))
+        return out[:len(gs) - 1].copy()
 
     def fuse_search(self, args):
         """The reference's ORBmatcher::Fuse, one map point per call -> (best_idx[n_points], the camera centre it used)."""

@@ -112,6 +112,13 @@ def main():
     assert np.array_equal(a, o)
     out["fuse_search_%dx%d_th3" % (fa.n_points, fa.n_kf)] = {
         "gpu_ms": med(lambda: pkg.fuse_search(fa)), "cpu_ms": med(lambda: po.fuse_search(fa)), "fused": int((a >= 0).sum())}
+    # --- MapPoint::ComputeDistinctiveDescriptors for the 2000 map points a new keyframe touches (up to 12 observations each)
+    import test_distinctive as td
+    dd, gs = td.groups(1, 2000, 12)
+    a = pkg.distinctive_descriptors(dd, gs); o = po.distinctive_descriptors(dd, gs)
+    assert np.array_equal(a, o)
+    out["distinctive_descriptors_2000_points_%d_observations" % len(dd)] = {
+        "gpu_ms": med(lambda: pkg.distinctive_descriptors(dd, gs)), "cpu_ms": med(lambda: po.distinctive_descriptors(dd, gs), 10, 1)}
     print(json.dumps(out, indent=1))
 
 
