@@ -306,6 +306,23 @@ typedef struct orbgpu_reloc_projection_args {
  * rotation-consistency check.  *nmatches = return value. */
 int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projection_args* args, int32_t* cur_match, int* nmatches);
 
+/* The three Sim3 routines of loop closing, on the same engine and the same orbgpu_fuse_args snapshot (Tcw / Ow / bf /
+ * u_right / inv_level_sigma2 are not read where a Sim3 replaces the pose; th may hold the reference's int th):
+ *  - Fuse(KeyFrame* pKF, cv::Mat Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:969-1097): present[i] = !isBad() &&
+ *    !spAlreadyFound.count(pMP); best_idx[i] = bestIdx where bestDist <= TH_LOW; the branch on pKF->GetMapPoint(bestIdx)
+ *    (:1082-1094) stays host, in index order.
+ *  - SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th) (:290-403): matched_in[idx] = vpMatched[idx] != NULL
+ *    on entry, present[i] = !isBad() && !spAlreadyFound.count(pMP); matched[n_kf] = the point index vpMatched[idx] was set to,
+ *    else -1; *nmatches = return value.
+ *  - SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (:1102-1326): a12 = the map points of pKF1 (present[i] = pMP &&
+ *    !vbAlreadyMatched1[i] && !isBad(); Tcw = pose of pKF1) searched among pKF2's keypoints, a21 the other direction;
+ *    match12[N1] = idx2 of the pairs both directions agree on (vpMatches12[i1] = vpMapPoints2[idx2]); *nfound = return value. */
+int orbgpu_fuse_search_sim3(int device, const orbgpu_fuse_args* args, const float* Scw16, int32_t* best_idx);
+int orbgpu_search_by_projection_sim3(int device, const orbgpu_fuse_args* args, const float* Scw16, const uint8_t* matched_in,
+                                     int32_t* matched, int* nmatches);
+int orbgpu_search_by_sim3(int device, const orbgpu_fuse_args* a12, const orbgpu_fuse_args* a21, float s12, const float* R12,
+                          const float* t12, int32_t* match12, int* nfound);
+
 /* ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:159-288 KeyFrame/Frame, :522-655 KeyFrame/KeyFrame).
  * Side 1 = the keyframe whose features are the queries (pKF / pKF1), side 2 = the searched one (F / pKF2).  A DBoW2
  * FeatureVector is passed flattened: ascending node ids, node_start[n_nodes + 1], feature indices in the map's order

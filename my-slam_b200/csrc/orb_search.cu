@@ -688,12 +688,19 @@ __global__ void k_frustum(FrustumCam C, const uint8_t* __restrict__ candidate, c
 }
 
 // ---- the search of ORBmatcher::Fuse (src/ORBmatcher.cc:825-957) -----------------------------------------------------
-struct FuseCam { float R[9], t[3], Ow[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, log_scale, th; int nlevels; };
+// mode flags: the keyframe-projection loops of ORBmatcher differ in small print only
+//   two_stage   Pc = R2*(R*P + t) + t2                      SearchBySim3 (:1158-1160, :1238-1240)
+//   inv_double  invz = 1.0/z (a double division)             Fuse(KF, Scw) :1018, SearchBySim3 :1166; "1/z" elsewhere
+//   cam_dist    distance = norm(Pc) instead of norm(P - Ow)  SearchBySim3 :1181
+//   view_check  PO.dot(Pn) < 0.5*dist rejects                Fuse :883, Fuse(Scw) :1041, SearchByProjection(KF, Scw) :351
+struct FuseCam { float R[9], t[3], R2[9], t2[3], Ow[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, log_scale, th; int nlevels;
+                 int two_stage, inv_double, cam_dist, view_check; };
 struct FuseQuery { float u, v, ur, r; int level; int active; };
 
 __global__ void k_fuse_queries(FuseCam C, const uint8_t* __restrict__ present, const float* __restrict__ world_pos,
                                const float* __restrict__ normal, const float* __restrict__ max_distance,
-                               const float* __restrict__ min_distance, const float* __restrict__ scale, int n, FuseQuery* __restrict__ Q)
+                               const float* __restrict__ min_distance, const float* __restrict__ scale, int n, FuseQuery* __restrict__ Q,
+                               AreaQuery* __restrict__ AQ)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -707,23 +714,37 @@ __global__ void k_fuse_queries(FuseCam C, const uint8_t* __restrict__ present, c
             const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.R[3 * r], P[0]), __fmul_rn(C.R[3 * r + 1], P[1])), __fmul_rn(C.R[3 * r + 2], P[2]));
             Pc[r] = (float)__dadd_rn(__dmul_rn((double)t, 1.0), __dmul_rn((double)C.t[r], 1.0));
         }
+        if (C.two_stage) {                                     // sR21*p3Dc1 + t21
+            const float A[3] = {Pc[0], Pc[1], Pc[2]};
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.R2[3 * r], A[0]), __fmul_rn(C.R2[3 * r + 1], A[1])), __fmul_rn(C.R2[3 * r + 2], A[2]));
+                Pc[r] = (float)__dadd_rn(__dmul_rn((double)t, 1.0), __dmul_rn((double)C.t2[r], 1.0));
+            }
+        }
         if (!(Pc[2] < 0.0f)) {                                 // :857
-            const float invz = __fdiv_rn(1.0f, Pc[2]);
+            const float invz = C.inv_double ? (float)__ddiv_rn(1.0, (double)Pc[2]) : __fdiv_rn(1.0f, Pc[2]);
             const float x = __fmul_rn(Pc[0], invz), y = __fmul_rn(Pc[1], invz);
             const float u = __fadd_rn(__fmul_rn(C.fx, x), C.cx), v = __fadd_rn(__fmul_rn(C.fy, y), C.cy);
             if (u >= C.minX && u < C.maxX && v >= C.minY && v < C.maxY) {             // KeyFrame::IsInImage, int bounds
                 const float maxDistance = __fmul_rn(1.2f, max_distance[i]);
                 const float minDistance = __fmul_rn(0.8f, min_distance[i]);
-                const float PO[3] = {__fsub_rn(P[0], C.Ow[0]), __fsub_rn(P[1], C.Ow[1]), __fsub_rn(P[2], C.Ow[2])};
+                float PO[3];
+                if (C.cam_dist) { PO[0] = Pc[0]; PO[1] = Pc[1]; PO[2] = Pc[2]; }
+                else { PO[0] = __fsub_rn(P[0], C.Ow[0]); PO[1] = __fsub_rn(P[1], C.Ow[1]); PO[2] = __fsub_rn(P[2], C.Ow[2]); }
                 double s2 = __dmul_rn((double)PO[0], (double)PO[0]);
                 s2 = __dadd_rn(s2, __dmul_rn((double)PO[1], (double)PO[1]));
                 s2 = __dadd_rn(s2, __dmul_rn((double)PO[2], (double)PO[2]));
                 const float dist3D = (float)__dsqrt_rn(s2);
                 if (!(dist3D < minDistance || dist3D > maxDistance)) {
-                    double d = __dmul_rn((double)PO[0], (double)normal[3 * (size_t)i]);
-                    d = __dadd_rn(d, __dmul_rn((double)PO[1], (double)normal[3 * (size_t)i + 1]));
-                    d = __dadd_rn(d, __dmul_rn((double)PO[2], (double)normal[3 * (size_t)i + 2]));
-                    if (!(d < __dmul_rn(0.5, (double)dist3D))) {                       // :883
+                    bool seen = true;
+                    if (C.view_check) {
+                        double d = __dmul_rn((double)PO[0], (double)normal[3 * (size_t)i]);
+                        d = __dadd_rn(d, __dmul_rn((double)PO[1], (double)normal[3 * (size_t)i + 1]));
+                        d = __dadd_rn(d, __dmul_rn((double)PO[2], (double)normal[3 * (size_t)i + 2]));
+                        seen = !(d < __dmul_rn(0.5, (double)dist3D));                  // :883
+                    }
+                    if (seen) {
                         const float ratio = __fdiv_rn(max_distance[i], dist3D);        // PredictScale(dist3D, pKF), src/MapPoint.cc:385-400
                         const float c = ceilf(__fdiv_rn(orb_logf(ratio), C.log_scale));
                         int nScale = (fabsf(c) < 2147483648.f) ? (int)c : INT_MIN;
@@ -738,13 +759,18 @@ __global__ void k_fuse_queries(FuseCam C, const uint8_t* __restrict__ present, c
         }
     }
     Q[i] = q;
+    if (AQ) {                                                  // the same query for k_area_candidates (SearchByProjection(KF, Scw))
+        AreaQuery a;
+        a.x = q.u; a.y = q.v; a.r = q.r; a.min_level = q.level - 1; a.max_level = q.level; a.active = q.active; a.ur = 0.f; a.check_ur = 0;
+        AQ[i] = a;
+    }
 }
 
 // one warp per map point: KeyFrame::GetFeaturesInArea's visiting order (columns of the window, cells top to bottom, index
 // order inside a cell) with the level and chi-square gates of :897-928; the smallest distance wins, the first one on ties
 __global__ void __launch_bounds__(256) k_fuse_match(GridDev G, const FuseQuery* __restrict__ Q, const uint8_t* __restrict__ qdesc, int nq,
                                                     const float* __restrict__ u_right, const float* __restrict__ inv_sigma2,
-                                                    int* __restrict__ best_idx)
+                                                    int chi2_gate, unsigned max_dist, int* __restrict__ best_idx)
 {
     const int lane = threadIdx.x & 31;
     const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -771,7 +797,7 @@ __global__ void __launch_bounds__(256) k_fuse_match(GridDev G, const FuseQuery* 
                         const int oct = key_octave(G.keys, i2);
                         bool ok = fabsf(__fsub_rn(kx, x)) < r && fabsf(__fsub_rn(ky, y)) < r;       // src/KeyFrame.cc:598-602
                         if (oct < A.level - 1 || oct > A.level) ok = false;                           // :901-902
-                        if (ok) {
+                        if (ok && chi2_gate) {
                             const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky);
                             const float kr = u_right[i2];
                             float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
@@ -791,7 +817,7 @@ __global__ void __launch_bounds__(256) k_fuse_match(GridDev G, const FuseQuery* 
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-    if (lane == 0) best_idx[q] = (best != ~0ull && (unsigned)(best >> 40) <= 50u) ? (int)(best & 0xFFFFu) : -1;   // TH_LOW (:943)
+    if (lane == 0) best_idx[q] = (best != ~0ull && (unsigned)(best >> 40) <= max_dist) ? (int)(best & 0xFFFFu) : -1;   // TH_LOW (:943) / TH_HIGH
 }
 
 // SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist): the projection of the keyframe's map points
@@ -1335,22 +1361,26 @@ int orbgpu_debug_logf(int device, const float* x, int n, float* out)
     return ORBGPU_OK;
 }
 
-int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
+// One engine for the keyframe-projection loops (Fuse, Fuse with Sim3, SearchByProjection with Sim3, the two passes of
+// SearchBySim3).  C carries the pose(s) and the mode flags; occupied != NULL switches from "best keypoint per point"
+// (best[n_points]) to the occupancy-ordered assignment of SearchByProjection(KF, Scw) (best[n_kf] = point index).
+static int fuse_run(int device, const orbgpu_fuse_args* a, FuseCam C, int chi2_gate, int max_dist, const uint8_t* occupied,
+                    int32_t* best, int* nmatches)
 {
-    if (!a || !best_idx || a->n_points < 0 || a->n_kf < 0 || a->nlevels < 1) return ORBGPU_ERR_ARG;
-    if (!a->present || !a->world_pos || !a->normal || !a->max_distance || !a->min_distance || !a->mp_desc || !a->Tcw || !a->scale_factors ||
-        !a->inv_level_sigma2) return ORBGPU_ERR_ARG;
-    if (a->n_kf > 0 && (!a->keys_un || !a->desc || !a->u_right)) return ORBGPU_ERR_ARG;
+    if (!a || !best || a->n_points < 0 || a->n_kf < 0 || a->nlevels < 1) return ORBGPU_ERR_ARG;
+    if (!a->present || !a->world_pos || !a->max_distance || !a->min_distance || !a->mp_desc || !a->scale_factors) return ORBGPU_ERR_ARG;
+    if ((C.view_check && !a->normal) || (chi2_gate && !a->inv_level_sigma2)) return ORBGPU_ERR_ARG;
+    if (a->n_kf > 0 && (!a->keys_un || !a->desc || (chi2_gate && !a->u_right))) return ORBGPU_ERR_ARG;
     if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
     const int n1 = a->n_points, n2 = a->n_kf;
     if (n1 > (1 << 20) || n2 > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+    if (occupied && (n1 > GRID_MAX_KEYS || (size_t)n1 * (size_t)n2 > ((size_t)1 << 26))) return ORBGPU_ERR_UNSUPPORTED;
     for (int i = 0; i < n2; ++i)
         if (a->keys_un[i].octave < 0 || a->keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
-    for (int i = 0; i < n1; ++i) best_idx[i] = -1;
+    const int nout = occupied ? n2 : n1;
+    for (int i = 0; i < nout; ++i) best[i] = -1;
+    if (nmatches) *nmatches = 0;
     if (n1 == 0 || n2 == 0) return ORBGPU_OK;
-    FuseCam C;
-    const float* Tc = a->Tcw;
-    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = Tc[4 * r + c]; C.t[r] = Tc[4 * r + 3]; C.Ow[r] = a->Ow[r]; }
     C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy; C.bf = a->bf;
     // the keyframe holds the image bounds as ints (include/KeyFrame.h:185-188, src/KeyFrame.cc:42-43)
     C.minX = (float)(int)a->bounds[0]; C.maxX = (float)(int)a->bounds[1]; C.minY = (float)(int)a->bounds[2]; C.maxY = (float)(int)a->bounds[3];
@@ -1358,41 +1388,157 @@ int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
     Layout L;
     const size_t o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_desc = L.add(32 * (size_t)n2), o_ur = L.add(4 * (size_t)n2);
     const size_t o_qdesc = L.add(32 * (size_t)n1), o_pres = L.add((size_t)n1), o_pos = L.add(12 * (size_t)n1), o_nrm = L.add(12 * (size_t)n1);
-    const size_t o_maxd = L.add(4 * (size_t)n1), o_mind = L.add(4 * (size_t)n1);
+    const size_t o_maxd = L.add(4 * (size_t)n1), o_mind = L.add(4 * (size_t)n1), o_occ = L.add((size_t)n2);
     const size_t o_scale = L.add(4 * (size_t)a->nlevels), o_sig = L.add(4 * (size_t)a->nlevels);
     const size_t in_bytes = L.off;
-    const size_t o_best = L.add(4 * (size_t)n1);
+    const size_t o_best = L.add(4 * (size_t)nout), o_nm = L.add(4);
     const size_t io_bytes = L.off;
     const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_q = L.add(sizeof(FuseQuery) * (size_t)n1);
+    const size_t o_aq = L.add(occupied ? sizeof(AreaQuery) * (size_t)n1 : 0), o_cn = L.add(occupied ? 4 * (size_t)n1 : 0);
+    const size_t o_acc = L.add(occupied ? 4 * (size_t)n1 : 0), o_cand = L.add(occupied ? 4 * (size_t)n1 * n2 : 0);
     Workspace& W = g_ws;
     int rc = W.reserve(device, L.off, io_bytes);
     if (rc != ORBGPU_OK) return rc;
     memcpy(W.h + o_keys, a->keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
     memcpy(W.h + o_desc, a->desc, 32 * (size_t)n2);
-    memcpy(W.h + o_ur, a->u_right, 4 * (size_t)n2);
+    if (a->u_right) memcpy(W.h + o_ur, a->u_right, 4 * (size_t)n2); else memset(W.h + o_ur, 0, 4 * (size_t)n2);
     memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
     memcpy(W.h + o_pres, a->present, (size_t)n1);
     memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
-    memcpy(W.h + o_nrm, a->normal, 12 * (size_t)n1);
+    if (a->normal) memcpy(W.h + o_nrm, a->normal, 12 * (size_t)n1);
     memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
     memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
+    if (occupied) memcpy(W.h + o_occ, occupied, (size_t)n2);
     memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
-    memcpy(W.h + o_sig, a->inv_level_sigma2, 4 * (size_t)a->nlevels);
+    if (a->inv_level_sigma2) memcpy(W.h + o_sig, a->inv_level_sigma2, 4 * (size_t)a->nlevels);
     CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
     GridDev G;
     set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
     G.winX = C.minX; G.winY = C.minY;                          // src/KeyFrame.cc:574-586 subtract the int members
     FuseQuery* d_q = reinterpret_cast<FuseQuery*>(W.d + o_q);
+    AreaQuery* d_aq = occupied ? reinterpret_cast<AreaQuery*>(W.d + o_aq) : nullptr;
     k_grid_build<<<1, 1024, 0, W.st>>>(G);
     k_fuse_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_pres, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
                                                        reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
-                                                       reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
-    k_fuse_match<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur),
-                                                 reinterpret_cast<const float*>(W.d + o_sig), reinterpret_cast<int*>(W.d + o_best));
+                                                       reinterpret_cast<const float*>(W.d + o_scale), n1, d_q, d_aq);
+    if (!occupied) {
+        k_fuse_match<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur),
+                                                     reinterpret_cast<const float*>(W.d + o_sig), chi2_gate, (unsigned)max_dist,
+                                                     reinterpret_cast<int*>(W.d + o_best));
+    } else {                                                   // vpMatched[idx] blocks a keypoint; an assignment blocks it for later points (:375, :397)
+        uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+        int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+        k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_aq, W.d + o_qdesc, n1, nullptr, d_cand, n2, d_cn);
+        k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nullptr, W.d + o_occ, max_dist,
+                                                                   reinterpret_cast<int*>(W.d + o_best), reinterpret_cast<int*>(W.d + o_acc),
+                                                                   reinterpret_cast<int*>(W.d + o_nm));
+    }
     CUS(cudaGetLastError());
-    CUS(cudaMemcpyAsync(W.h + o_best, W.d + o_best, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaMemcpyAsync(W.h + o_best, W.d + o_best, io_bytes - o_best, cudaMemcpyDeviceToHost, W.st));
     CUS(cudaStreamSynchronize(W.st));
-    memcpy(best_idx, W.h + o_best, 4 * (size_t)n1);
+    memcpy(best, W.h + o_best, 4 * (size_t)nout);
+    if (nmatches && occupied) *nmatches = *reinterpret_cast<const int*>(W.h + o_nm);
+    return ORBGPU_OK;
+}
+
+static void cam_from_pose(FuseCam& C, const float* T16)
+{
+    memset(&C, 0, sizeof(C));
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) C.R[3 * r + c] = T16[4 * r + c]; C.t[r] = T16[4 * r + 3]; }
+}
+
+// "Decompose Scw" (src/ORBmatcher.cc:299-303, :979-984): scw = sqrt(row0 . row0) (cv::Mat::dot sums in double), Rcw = sRcw/scw and
+// tcw = t/scw through convertTo with scale 1/scw (each element times (float)(1.0/scw), in float), Ow = -Rcw.t()*tcw
+static void cam_from_sim3(FuseCam& C, const float* S16)
+{
+    memset(&C, 0, sizeof(C));
+    double d = 0;
+    for (int c = 0; c < 3; ++c) d += (double)S16[c] * (double)S16[c];
+    const float scw = (float)sqrt(d);
+    const float inv = (float)(1.0 / (double)scw);
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) { volatile float v = S16[4 * r + c] * inv; C.R[3 * r + c] = v; }
+        volatile float v = S16[4 * r + 3] * inv; C.t[r] = v;
+    }
+    for (int i = 0; i < 3; ++i) {
+        volatile float t = C.R[i] * C.t[0];
+        t = t + C.R[3 + i] * C.t[1];
+        t = t + C.R[6 + i] * C.t[2];
+        C.Ow[i] = (float)((double)t * -1.0);
+    }
+}
+
+int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
+{
+    if (!a || !a->Tcw) return ORBGPU_ERR_ARG;
+    FuseCam C;
+    cam_from_pose(C, a->Tcw);
+    for (int r = 0; r < 3; ++r) C.Ow[r] = a->Ow[r];
+    C.view_check = 1;
+    return fuse_run(device, a, C, 1, 50, nullptr, best_idx, nullptr);
+}
+
+int orbgpu_fuse_search_sim3(int device, const orbgpu_fuse_args* a, const float* Scw, int32_t* best_idx)
+{
+    if (!a || !Scw) return ORBGPU_ERR_ARG;
+    FuseCam C;
+    cam_from_sim3(C, Scw);
+    C.view_check = 1; C.inv_double = 1;
+    return fuse_run(device, a, C, 0, 50, nullptr, best_idx, nullptr);
+}
+
+int orbgpu_search_by_projection_sim3(int device, const orbgpu_fuse_args* a, const float* Scw, const uint8_t* matched_in,
+                                     int32_t* matched, int* nmatches)
+{
+    if (!a || !Scw || !matched_in || !nmatches) return ORBGPU_ERR_ARG;
+    FuseCam C;
+    cam_from_sim3(C, Scw);
+    C.view_check = 1;
+    return fuse_run(device, a, C, 0, 50, matched_in, matched, nmatches);
+}
+
+int orbgpu_search_by_sim3(int device, const orbgpu_fuse_args* a12, const orbgpu_fuse_args* a21, float s12, const float* R12,
+                          const float* t12, int32_t* match12, int* nfound)
+{
+    if (!a12 || !a21 || !R12 || !t12 || !match12 || !nfound || !a12->Tcw || !a21->Tcw) return ORBGPU_ERR_ARG;
+    if (a12->n_points != a21->n_kf || a21->n_points != a12->n_kf) return ORBGPU_ERR_ARG;
+    // "Transformation between cameras" (:1117-1120): sR12 = s12*R12 and sR21 = (1.0/s12)*R12.t() are convertTo with a
+    // scale (element times (float)scale, in float); t21 = -sR21*t12 is gemm's 3x3 float case with alpha = -1
+    float sR12[9], sR21[9], t21[3];
+    const float inv = (float)(1.0 / (double)s12);
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+            volatile float v = R12[3 * r + c] * (float)(double)s12; sR12[3 * r + c] = v;
+            volatile float w = R12[3 * c + r] * inv; sR21[3 * r + c] = w;
+        }
+    for (int i = 0; i < 3; ++i) {
+        volatile float t = sR21[3 * i] * t12[0];
+        t = t + sR21[3 * i + 1] * t12[1];
+        t = t + sR21[3 * i + 2] * t12[2];
+        t21[i] = (float)((double)t * -1.0);
+    }
+    const int N1 = a12->n_points, N2 = a21->n_points;
+    std::vector<int32_t> m1((size_t)(N1 > 0 ? N1 : 1)), m2((size_t)(N2 > 0 ? N2 : 1));
+    FuseCam C;
+    cam_from_pose(C, a12->Tcw);                                // KF1 -> KF2 (:1147-1225)
+    for (int k = 0; k < 9; ++k) C.R2[k] = sR21[k];
+    for (int k = 0; k < 3; ++k) C.t2[k] = t21[k];
+    C.two_stage = 1; C.inv_double = 1; C.cam_dist = 1;
+    int rc = fuse_run(device, a12, C, 0, 100, nullptr, m1.data(), nullptr);
+    if (rc != ORBGPU_OK) return rc;
+    cam_from_pose(C, a21->Tcw);                                // KF2 -> KF1 (:1227-1305)
+    for (int k = 0; k < 9; ++k) C.R2[k] = sR12[k];
+    for (int k = 0; k < 3; ++k) C.t2[k] = t12[k];
+    C.two_stage = 1; C.inv_double = 1; C.cam_dist = 1;
+    rc = fuse_run(device, a21, C, 0, 100, nullptr, m2.data(), nullptr);
+    if (rc != ORBGPU_OK) return rc;
+    int nf = 0;                                                // "Check agreement" (:1307-1323)
+    for (int i1 = 0; i1 < N1; ++i1) {
+        match12[i1] = -1;
+        const int idx2 = m1[i1];
+        if (idx2 >= 0 && m2[idx2] == i1) { match12[i1] = idx2; nf++; }
+    }
+    *nfound = nf;
     return ORBGPU_OK;
 }
 

@@ -308,6 +308,9 @@ def lib():
         "orbgpu_search_by_bow": (i32, [i32, vp, vp, f32, i32, i32, vp, vp, pi]),
         "orbgpu_search_local_map": (i32, [i32, vp, vp, pi, vp, pi]),
         "orbgpu_fuse_search": (i32, [i32, vp, vp]),
+        "orbgpu_fuse_search_sim3": (i32, [i32, vp, vp, vp]),
+        "orbgpu_search_by_projection_sim3": (i32, [i32, vp, vp, vp, vp, pi]),
+        "orbgpu_search_by_sim3": (i32, [i32, vp, vp, f32, vp, vp, vp, pi]),
         "orbgpu_search_by_projection_keyframe": (i32, [i32, vp, vp, pi]),
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
@@ -604,6 +607,29 @@ def distinctive_descriptors(desc, group_start, device=0):
     out = np.zeros(max(len(gs) - 1, 1), np.int32)
     _check(lib().orbgpu_distinctive_descriptors(device, _p(d) if len(d) else None, _p(gs), len(gs) - 1, _p(out)))
     return out[:len(gs) - 1].copy()
+
+
+def fuse_search_sim3(args, Scw, device=0):
+    """The search of ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:969-1097) -> best_idx[n_points]."""
+    S = np.ascontiguousarray(Scw, np.float32).reshape(16); best = np.zeros(max(args.n_points, 1), np.int32)
+    _check(lib().orbgpu_fuse_search_sim3(device, C.byref(args), _p(S), _p(best)))
+    return best[:args.n_points].copy()
+
+
+def search_by_projection_sim3(args, Scw, matched_in, device=0):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403) -> (nmatches, matched[n_kf])."""
+    S = np.ascontiguousarray(Scw, np.float32).reshape(16); mi = np.ascontiguousarray(matched_in, np.uint8)
+    out = np.zeros(max(args.n_kf, 1), np.int32); nm = C.c_int(0)
+    _check(lib().orbgpu_search_by_projection_sim3(device, C.byref(args), _p(S), _p(mi), _p(out), C.byref(nm)))
+    return nm.value, out[:args.n_kf].copy()
+
+
+def search_by_sim3(a12, a21, s12, R12, t12, device=0):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1102-1326) -> (nFound, match12[N1])."""
+    R = np.ascontiguousarray(R12, np.float32).reshape(9); t = np.ascontiguousarray(t12, np.float32).reshape(3)
+    out = np.zeros(max(a12.n_points, 1), np.int32); nf = C.c_int(0)
+    _check(lib().orbgpu_search_by_sim3(device, C.byref(a12), C.byref(a21), float(s12), _p(R), _p(t), _p(out), C.byref(nf)))
+    return nf.value, out[:a12.n_points].copy()
 
 
 def stereo_match(left, right, bf, b):

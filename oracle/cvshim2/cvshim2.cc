@@ -250,7 +250,9 @@ static Mat transpose_of(const Mat& a)
     return o;
 }
 
-// element-wise m*alpha for CV_32F (cv::Mat::convertTo with a scale: float(double(v)*alpha) in the scalar path)
+// element-wise m*alpha for CV_32F = cv::Mat::convertTo with a scale: OpenCV's cvtScale32f narrows the scale to float first
+// and multiplies in float, v * (float)alpha (pinned to cv2 4.13.0: tests/golden/scale_golden.npz, made through
+// cv2.normalize(NORM_INF), which ends in the same convertTo call; float(double(v) * alpha) differs in the last bit often)
 static Mat scaled_of(const Mat& m, double alpha)
 {
     if (alpha == 1) return m;
@@ -258,7 +260,7 @@ static Mat scaled_of(const Mat& m, double alpha)
     Mat o;
     o.create(m.rows, m.cols, m.type());
     for (int y = 0; y < m.rows; ++y)
-        for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = (float)((double)m.at<float>(y, x) * alpha);
+        for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = m.at<float>(y, x) * (float)alpha;
     return o;
 }
 

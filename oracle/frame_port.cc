@@ -712,3 +712,224 @@ extern "C" void frameport_distinctive_descriptors(const uint8_t* desc, const int
         best_idx[g] = BestIdx;
     }
 }
+
+namespace {
+
+// KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:569-608) on the grid the Frame built; the window subtracts the keyframe's
+// int-truncated bounds
+std::vector<size_t> kf_features_in_area(const Grid& g, const orbport_keypoint* keys, int mnMinX, int mnMinY, float x, float y, float r)
+{
+    std::vector<size_t> v;
+    const int nMinCellX = std::max(0, (int)floor((x - mnMinX - r) * g.invW));
+    if (nMinCellX >= GRID_COLS) return v;
+    const int nMaxCellX = std::min(GRID_COLS - 1, (int)ceil((x - mnMinX + r) * g.invW));
+    if (nMaxCellX < 0) return v;
+    const int nMinCellY = std::max(0, (int)floor((y - mnMinY - r) * g.invH));
+    if (nMinCellY >= GRID_ROWS) return v;
+    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)ceil((y - mnMinY + r) * g.invH));
+    if (nMaxCellY < 0) return v;
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+            const std::vector<size_t>& vCell = g.cell[ix][iy];
+            for (size_t j = 0; j < vCell.size(); j++) {
+                const orbport_keypoint& kpUn = keys[vCell[j]];
+                const float distx = kpUn.x - x, disty = kpUn.y - y;
+                if (std::fabs(distx) < r && std::fabs(disty) < r) v.push_back(vCell[j]);
+            }
+        }
+    return v;
+}
+
+// "Decompose Scw" (src/ORBmatcher.cc:299-303, :979-984)
+void decompose_sim3(const float* S, float* Rcw9, float* tcw, float* Ow)
+{
+    double d = 0;                                             // sRcw.row(0).dot(sRcw.row(0)): double accumulation
+    for (int c = 0; c < 3; ++c) d += (double)S[c] * (double)S[c];
+    const float scw = sqrt(d);
+    const float inv = (float)(1.0 / scw);                     // "M / scw" = convertTo with scale 1/scw: element * (float)scale, in float
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) Rcw9[3 * r + c] = S[4 * r + c] * inv;
+        tcw[r] = S[4 * r + 3] * inv;
+    }
+    for (int i = 0; i < 3; ++i) {                             // -Rcw.t()*tcw, lowered as at :1341
+        const float t = Rcw9[i] * tcw[0] + Rcw9[3 + i] * tcw[1] + Rcw9[6 + i] * tcw[2];
+        Ow[i] = (float)((double)t * -1.0);
+    }
+}
+
+int predict_scale(float max_distance, float dist, float log_scale, int nlevels)      // src/MapPoint.cc:385-400
+{
+    const float ratio = max_distance / dist;
+    int nScale = ceil(logf(ratio) / log_scale);
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= nlevels) nScale = nlevels - 1;
+    return nScale;
+}
+
+}  // namespace
+
+// src/ORBmatcher.cc:969-1097 up to the decision
+extern "C" void frameport_fuse_search_sim3(const frameport_fuse_args* a, const float* Scw, int* best_idx)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->keys_un, a->n_kf, a->bounds);
+    const int mnMinX = (int)a->bounds[0], mnMaxX = (int)a->bounds[1], mnMinY = (int)a->bounds[2], mnMaxY = (int)a->bounds[3];
+    float Rcw[9], tcw[3], Ow[3];
+    decompose_sim3(Scw, Rcw, tcw, Ow);
+    for (int iMP = 0; iMP < a->n_points; ++iMP) {
+        best_idx[iMP] = -1;
+        if (!a->present[iMP]) continue;
+        const float* p3Dw = a->world_pos + 3 * (size_t)iMP;
+        float p3Dc[3];
+        mat3_mul_add(Rcw, 3, p3Dw, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) continue;
+        const float invz = 1.0 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        const float u = a->fx * x + a->cx, v = a->fy * y + a->cy;
+        if (!(u >= mnMinX && u < mnMaxX && v >= mnMinY && v < mnMaxY)) continue;
+        const float maxDistance = 1.2f * a->max_distance[iMP], minDistance = 0.8f * a->min_distance[iMP];
+        const float PO[3] = {p3Dw[0] - Ow[0], p3Dw[1] - Ow[1], p3Dw[2] - Ow[2]};
+        double s2 = 0;
+        for (int k = 0; k < 3; ++k) s2 += (double)PO[k] * (double)PO[k];
+        const float dist3D = std::sqrt(s2);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const float* Pn = a->normal + 3 * (size_t)iMP;
+        double dot = 0;
+        for (int k = 0; k < 3; ++k) dot += (double)PO[k] * (double)Pn[k];
+        if (dot < 0.5 * dist3D) continue;
+        const int nPredictedLevel = predict_scale(a->max_distance[iMP], dist3D, a->log_scale_factor, a->nlevels);
+        const float radius = a->th * a->scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices = kf_features_in_area(*g, a->keys_un, mnMinX, mnMinY, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (size_t c = 0; c < vIndices.size(); ++c) {
+            const size_t idx = vIndices[c];
+            const int kpLevel = a->keys_un[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)iMP, a->desc + 32 * idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) best_idx[iMP] = bestIdx;
+    }
+    delete g;
+}
+
+// src/ORBmatcher.cc:290-403
+extern "C" int frameport_search_by_projection_sim3(const frameport_fuse_args* a, const float* Scw, const uint8_t* matched_in, int* matched)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->keys_un, a->n_kf, a->bounds);
+    const int mnMinX = (int)a->bounds[0], mnMaxX = (int)a->bounds[1], mnMinY = (int)a->bounds[2], mnMaxY = (int)a->bounds[3];
+    float Rcw[9], tcw[3], Ow[3];
+    decompose_sim3(Scw, Rcw, tcw, Ow);
+    std::vector<uint8_t> vpMatched(matched_in, matched_in + a->n_kf);
+    for (int i = 0; i < a->n_kf; ++i) matched[i] = -1;
+    int nmatches = 0;
+    for (int iMP = 0; iMP < a->n_points; ++iMP) {
+        if (!a->present[iMP]) continue;
+        const float* p3Dw = a->world_pos + 3 * (size_t)iMP;
+        float p3Dc[3];
+        mat3_mul_add(Rcw, 3, p3Dw, tcw, p3Dc);
+        if (p3Dc[2] < 0.0) continue;
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        const float u = a->fx * x + a->cx, v = a->fy * y + a->cy;
+        if (!(u >= mnMinX && u < mnMaxX && v >= mnMinY && v < mnMaxY)) continue;
+        const float maxDistance = 1.2f * a->max_distance[iMP], minDistance = 0.8f * a->min_distance[iMP];
+        const float PO[3] = {p3Dw[0] - Ow[0], p3Dw[1] - Ow[1], p3Dw[2] - Ow[2]};
+        double s2 = 0;
+        for (int k = 0; k < 3; ++k) s2 += (double)PO[k] * (double)PO[k];
+        const float dist = std::sqrt(s2);
+        if (dist < minDistance || dist > maxDistance) continue;
+        const float* Pn = a->normal + 3 * (size_t)iMP;
+        double dot = 0;
+        for (int k = 0; k < 3; ++k) dot += (double)PO[k] * (double)Pn[k];
+        if (dot < 0.5 * dist) continue;
+        const int nPredictedLevel = predict_scale(a->max_distance[iMP], dist, a->log_scale_factor, a->nlevels);
+        const float radius = (int)a->th * a->scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices = kf_features_in_area(*g, a->keys_un, mnMinX, mnMinY, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t c = 0; c < vIndices.size(); ++c) {
+            const size_t idx = vIndices[c];
+            if (vpMatched[idx]) continue;
+            const int kpLevel = a->keys_un[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int d = orbport_hamming256(a->mp_desc + 32 * (size_t)iMP, a->desc + 32 * idx);
+            if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) { vpMatched[bestIdx] = 1; matched[bestIdx] = iMP; nmatches++; }
+    }
+    delete g;
+    return nmatches;
+}
+
+namespace {
+// one direction of SearchBySim3 (src/ORBmatcher.cc:1147-1225 / :1227-1305)
+void sim3_pass(const frameport_fuse_args* a, const float* sR, const float* tt, std::vector<int>& vnMatch)
+{
+    Grid* g = new Grid;
+    build_grid(*g, a->keys_un, a->n_kf, a->bounds);
+    const int mnMinX = (int)a->bounds[0], mnMaxX = (int)a->bounds[1], mnMinY = (int)a->bounds[2], mnMaxY = (int)a->bounds[3];
+    const float* T = a->Tcw;
+    const float tw[3] = {T[3], T[7], T[11]};
+    vnMatch.assign((size_t)a->n_points, -1);
+    for (int i = 0; i < a->n_points; ++i) {
+        if (!a->present[i]) continue;
+        float pA[3], pB[3];
+        mat3_mul_add(T, 4, a->world_pos + 3 * (size_t)i, tw, pA);
+        mat3_mul_add(sR, 3, pA, tt, pB);
+        if (pB[2] < 0.0) continue;
+        const float invz = 1.0 / pB[2];
+        const float x = pB[0] * invz, y = pB[1] * invz;
+        const float u = a->fx * x + a->cx, v = a->fy * y + a->cy;
+        if (!(u >= mnMinX && u < mnMaxX && v >= mnMinY && v < mnMaxY)) continue;
+        const float maxDistance = 1.2f * a->max_distance[i], minDistance = 0.8f * a->min_distance[i];
+        double s2 = 0;
+        for (int k = 0; k < 3; ++k) s2 += (double)pB[k] * (double)pB[k];
+        const float dist3D = std::sqrt(s2);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const int nPredictedLevel = predict_scale(a->max_distance[i], dist3D, a->log_scale_factor, a->nlevels);
+        const float radius = a->th * a->scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices = kf_features_in_area(*g, a->keys_un, mnMinX, mnMinY, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (size_t c = 0; c < vIndices.size(); ++c) {
+            const size_t idx = vIndices[c];
+            const int oct = a->keys_un[idx].octave;
+            if (oct < nPredictedLevel - 1 || oct > nPredictedLevel) continue;
+            const int dist = orbport_hamming256(a->mp_desc + 32 * (size_t)i, a->desc + 32 * idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_HIGH) vnMatch[i] = bestIdx;
+    }
+    delete g;
+}
+}  // namespace
+
+// src/ORBmatcher.cc:1102-1326
+extern "C" int frameport_search_by_sim3(const frameport_fuse_args* a12, const frameport_fuse_args* a21, float s12, const float* R12,
+                                        const float* t12, int* match12)
+{
+    float sR12[9], sR21[9], t21[3];
+    const float inv = (float)(1.0 / s12);                     // (1.0/s12)*R12.t(): transpose, then convertTo with that scale
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) { sR12[3 * r + c] = R12[3 * r + c] * s12; sR21[3 * r + c] = R12[3 * c + r] * inv; }
+    for (int i = 0; i < 3; ++i) {                             // -sR21*t12: gemm with alpha = -1
+        const float t = sR21[3 * i] * t12[0] + sR21[3 * i + 1] * t12[1] + sR21[3 * i + 2] * t12[2];
+        t21[i] = (float)((double)t * -1.0);
+    }
+    std::vector<int> vnMatch1, vnMatch2;
+    sim3_pass(a12, sR21, t21, vnMatch1);
+    sim3_pass(a21, sR12, t12, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < a12->n_points; ++i1) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) { match12[i1] = idx2; nFound++; }
+        }
+    }
+    return nFound;
+}

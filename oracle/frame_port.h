@@ -7,6 +7,8 @@
  *   ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine    src/ORBmatcher.cc:657-820, 140-157
  *   Frame::isInFrustum + MapPoint::PredictScale (Tracking::SearchLocalPoints)  src/Frame.cc:269-325, src/MapPoint.cc:402-417
  *   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1472-1597
+ *   the Sim3 routines Fuse(KeyFrame*, Scw, ...), SearchByProjection(KeyFrame*, Scw, ...), SearchBySim3
+ *                                                                 src/ORBmatcher.cc:969-1097, 290-403, 1102-1326
  *   the search of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) + KeyFrame::GetFeaturesInArea / IsInImage
  *                                                                 src/ORBmatcher.cc:825-957, src/KeyFrame.cc:569-613
  *   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:1601-1642
@@ -160,6 +162,12 @@ int frameport_search_by_projection_keyframe(const frameport_reloc_projection_arg
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-303) on groups of descriptors given in the order the
  * reference collects them; best_idx[g] = BestIdx, -1 for an empty group */
 void frameport_distinctive_descriptors(const uint8_t* desc, const int32_t* group_start, int n_groups, int* best_idx);
+
+/* the Sim3 routines on the frameport_fuse_args snapshot (see include/orbgpu.h for what each field means there) */
+void frameport_fuse_search_sim3(const frameport_fuse_args* a, const float* Scw16, int* best_idx);
+int frameport_search_by_projection_sim3(const frameport_fuse_args* a, const float* Scw16, const uint8_t* matched_in, int* matched);
+int frameport_search_by_sim3(const frameport_fuse_args* a12, const frameport_fuse_args* a21, float s12, const float* R12,
+                             const float* t12, int* match12);
 
 #ifdef __cplusplus
 }

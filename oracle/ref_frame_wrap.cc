@@ -16,6 +16,7 @@
 //   frameref_search_local_map             Frame::isInFrustum (src/Frame.cc:269-325) per point + that search, as Tracking::SearchLocalPoints
 //   frameref_fuse_search                  ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th) :825-957, one map point per call
 //   frameref_search_by_projection_keyframe  ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) :1472-1597
+//   frameref_fuse_search_sim3 / frameref_search_by_projection_sim3 / frameref_search_by_sim3   the Sim3 routines :969-1097, :290-403, :1102-1326
 //   frameref_search_by_bow                ORBmatcher::SearchByBoW, both overloads         :159-288, :522-655
 //   frameref_distinctive_descriptors      MapPoint::ComputeDistinctiveDescriptors         src/MapPoint.cc:242-303
 //   frameref_search_for_triangulation     ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine  :657-820, :140-157
@@ -206,6 +207,16 @@ void frameref_neg_rt_t(const float* Tcw16, const float* Tlw16, float* twc3, floa
     const cv::Mat tlw = Tl.rowRange(0, 3).col(3);
     const cv::Mat tlc = Rlw * twc + tlw;
     for (int i = 0; i < 3; ++i) { twc3[i] = twc.at<float>(i); tlc3[i] = tlc.at<float>(i); }
+}
+
+// "M / s" for a CV_32F row vector, as the Sim3 routines of src/ORBmatcher.cc form it (:301-302): the shim's MatExpr
+// lowering (convertTo with scale 1/s), checked against cv2 golden vectors
+void frameref_mat_div(const float* v, int n, float s, float* out)
+{
+    cv::Mat M(1, n, CV_32F);
+    std::memcpy(M.data, v, sizeof(float) * (size_t)n);
+    cv::Mat R = M / s;
+    std::memcpy(out, R.data, sizeof(float) * (size_t)n);
 }
 
 int frameref_features_in_area(const KP* keys_un, int n, const float* bounds4, float x, float y, float r, int min_level,
@@ -455,6 +466,162 @@ int frameref_search_by_projection_keyframe(const frameport_reloc_projection_args
         cur_match[i] = it == index_of.end() ? -1 : it->second;
     }
     return nm;
+}
+
+namespace {
+// a KeyFrame carrying the keypoints / descriptors / tables of a frameport_fuse_args snapshot, posed at T16
+KeyFrame* keyframe_of(World& world, const frameport_fuse_args* a, const float* T16, unsigned long id, Frame& F)
+{
+    set_scale_tables(F, a->scale_factors, a->nlevels);
+    if (a->inv_level_sigma2) F.mvInvLevelSigma2.assign(a->inv_level_sigma2, a->inv_level_sigma2 + a->nlevels);
+    F.mfLogScaleFactor = a->log_scale_factor;
+    fill_frame(F, a->keys_un, a->desc, a->n_kf);
+    if (a->n_kf && a->u_right) F.mvuRight.assign(a->u_right, a->u_right + a->n_kf);
+    F.mbf = a->bf; F.mb = 1.f; F.mThDepth = 1.f; F.mTimeStamp = 0; F.mnId = id;
+    F.mTcw = pose_mat(T16);
+    KeyFrame* pKF = new KeyFrame(F, &world.map, static_cast<KeyFrameDatabase*>(NULL));
+    world.keyframes.push_back(pKF);
+    return pKF;
+}
+
+MapPoint* point_of(World& world, const frameport_fuse_args* a, int i, bool bad)
+{
+    MapPoint* p = world.point(a->world_pos + 3 * i, a->mp_desc + 32 * i, 3, bad);
+    if (a->normal) {
+        cv::Mat nrm(3, 1, CV_32F);
+        std::memcpy(nrm.data, a->normal + 3 * i, 3 * sizeof(float));
+        p->mNormalVector = nrm;
+    }
+    p->mfMaxDistance = a->max_distance[i]; p->mfMinDistance = a->min_distance[i];
+    return p;
+}
+
+cv::Mat mat44(const float* S16)
+{
+    cv::Mat m(4, 4, CV_32F);
+    std::memcpy(m.data, S16, 16 * sizeof(float));
+    return m;
+}
+}  // namespace
+
+// Fuse(pKF, Scw, vpPoints, th, vpReplacePoint).  present = 0: alternately a bad point and a point the keyframe already
+// holds (spAlreadyFound).  The keypoint a point was fused with is read back from the map: its own observation of pKF, or
+// the observation of the point it was told to replace.
+int frameref_fuse_search_sim3(const frameport_fuse_args* a, const float* Scw, int* best_idx)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame F;
+    const float eye[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    KeyFrame* pKF = keyframe_of(world, a, eye, 5, F);
+    std::vector<MapPoint*> vp((size_t)a->n_points), repl((size_t)a->n_points, static_cast<MapPoint*>(NULL));
+    int slot = 0;
+    for (int i = 0; i < a->n_points; ++i) {
+        const bool bad = !a->present[i] && (i & 1);
+        vp[i] = point_of(world, a, i, bad);
+        if (!a->present[i] && !bad && a->n_kf > 0) {          // already in the keyframe
+            while (slot < a->n_kf && pKF->GetMapPoint(slot)) ++slot;
+            if (slot < a->n_kf) { pKF->AddMapPoint(vp[i], slot); vp[i]->mObservations[pKF] = slot; }
+            else vp[i]->mbBad = true;
+        }
+    }
+    ORBmatcher matcher(0.8f, true);
+    const int nf = matcher.Fuse(pKF, mat44(Scw), vp, a->th, repl);
+    int seen = 0;
+    for (int i = 0; i < a->n_points; ++i) {
+        best_idx[i] = -1;
+        if (!a->present[i]) continue;
+        best_idx[i] = repl[i] ? repl[i]->GetIndexInKeyFrame(pKF) : vp[i]->GetIndexInKeyFrame(pKF);
+        seen += best_idx[i] >= 0;
+    }
+    if (seen != nf) never("Fuse(Scw): return value and the map disagree");
+    return nf;
+}
+
+// SearchByProjection(pKF, Scw, vpPoints, vpMatched, th).  matched_in marks keypoints that already hold a match; present = 0
+// points are bad or (every third one) sit in vpMatched themselves.
+int frameref_search_by_projection_sim3(const frameport_fuse_args* a, const float* Scw, const uint8_t* matched_in, int* matched)
+{
+    set_frame_statics(a->bounds, a->fx, a->fy, a->cx, a->cy);
+    World world;
+    Frame F;
+    const float eye[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    KeyFrame* pKF = keyframe_of(world, a, eye, 5, F);
+    const float origin[3] = {0, 0, 0};
+    std::vector<MapPoint*> vpMatched((size_t)a->n_kf, static_cast<MapPoint*>(NULL));
+    std::vector<int> occupied;
+    for (int j = 0; j < a->n_kf; ++j)
+        if (matched_in[j]) { vpMatched[j] = world.point(origin, 0, 1, false); occupied.push_back(j); }
+    std::vector<MapPoint*> vp((size_t)a->n_points);
+    std::map<MapPoint*, int> index_of;
+    size_t next = 0;
+    for (int i = 0; i < a->n_points; ++i) {
+        const bool in_matched = !a->present[i] && i % 3 == 0 && next < occupied.size();
+        vp[i] = point_of(world, a, i, !a->present[i] && !in_matched);
+        if (in_matched) vpMatched[occupied[next++]] = vp[i];
+        index_of[vp[i]] = i;
+    }
+    ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(pKF, mat44(Scw), vp, vpMatched, (int)a->th);
+    for (int j = 0; j < a->n_kf; ++j) {
+        matched[j] = -1;
+        if (matched_in[j] || !vpMatched[j]) continue;
+        matched[j] = index_of[vpMatched[j]];
+    }
+    return nm;
+}
+
+// SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th).  a12: the map points of pKF1 (its pose in a12->Tcw) searched in
+// pKF2, whose keypoints a12 carries; a21 the other way round.  present = 0 cycles through: no map point, a bad one, one
+// already matched on entry (vpMatches12 / an observation of pKF2 by a pre-matched point).
+int frameref_search_by_sim3(const frameport_fuse_args* a12, const frameport_fuse_args* a21, float s12, const float* R12,
+                            const float* t12, int* match12)
+{
+    set_frame_statics(a12->bounds, a12->fx, a12->fy, a12->cx, a12->cy);
+    World world;
+    Frame F1, F2;
+    const int N1 = a12->n_points, N2 = a21->n_points;
+    KeyFrame* pKF1 = keyframe_of(world, a21, a12->Tcw, 5, F1);      // pKF1 carries the keypoints a21 searches in
+    KeyFrame* pKF2 = keyframe_of(world, a12, a21->Tcw, 6, F2);
+    const float origin[3] = {0, 0, 0};
+    std::vector<MapPoint*> vpMatches12((size_t)N1, static_cast<MapPoint*>(NULL));
+    std::map<MapPoint*, int> index2;
+    std::vector<uint8_t> pre2((size_t)N2, 0);
+    for (int i = 0; i < N2; ++i) {
+        const int how = a21->present[i] ? -1 : i % 3;
+        if (how == 0) continue;
+        MapPoint* p = point_of(world, a21, i, how == 1);
+        pKF2->AddMapPoint(p, i);
+        index2[p] = i;
+        if (how == 2) pre2[i] = 1;                             // will be reached through a pre-matched point of pKF1, or stays bad
+    }
+    std::vector<int> want2;                                    // keypoints of pKF2 that must read "already matched"
+    for (int i = 0; i < N2; ++i) if (pre2[i]) want2.push_back(i);
+    size_t next = 0;
+    for (int i = 0; i < N1; ++i) {
+        const int how = a12->present[i] ? -1 : i % 3;
+        if (how == 0) continue;
+        MapPoint* p = point_of(world, a12, i, how == 1);
+        pKF1->AddMapPoint(p, i);
+        if (how == 2) {                                        // pre-matched: blocks i1 and, when it observes pKF2, that keypoint
+            MapPoint* m = world.point(origin, 0, 1, false);
+            if (next < want2.size()) m->mObservations[pKF2] = (size_t)want2[next++];
+            vpMatches12[i] = m;
+        }
+    }
+    for (; next < want2.size(); ++next) pKF2->GetMapPoint(want2[next])->mbBad = true;      // leftovers: skipped as bad instead
+    cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+    std::memcpy(R.data, R12, 9 * sizeof(float));
+    std::memcpy(t.data, t12, 3 * sizeof(float));
+    std::vector<MapPoint*> before = vpMatches12;
+    ORBmatcher matcher(0.75f, true);
+    const int nf = matcher.SearchBySim3(pKF1, pKF2, vpMatches12, s12, R, t, a12->th);
+    for (int i = 0; i < N1; ++i) {
+        match12[i] = -1;
+        if (before[i] || !vpMatches12[i]) continue;
+        match12[i] = index2[vpMatches12[i]];
+    }
+    return nf;
 }
 
 // strict_th_low = 0: SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches)   (side 1 = pKF, side 2 = F)

@@ -238,9 +238,30 @@ def make_gemm():
     print("gemm_golden.npz written")
 
 
+def make_scale():
+    """cv::Mat::convertTo with a scale (what "M / s" and "s * M" lower to in the Sim3 routines, src/ORBmatcher.cc:301-302,
+    :1118-1119), reached from Python through cv2.normalize(NORM_INF): scale = alpha / max|src| in double, then
+    src.convertTo(dst, CV_32F, scale, 0).  With alpha = 1 and max|src| = s the call computes src / s."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(4242)
+    n = 4000
+    sc = rng.uniform(0.2, 5.0, n).astype(np.float32)
+    src = np.zeros((n, 13), np.float32); dst = np.zeros((n, 13), np.float32)
+    for i in range(n):
+        v = np.clip((rng.uniform(-1, 1, 12) * sc[i]).astype(np.float32), -sc[i], sc[i])
+        src[i] = np.concatenate([v, [sc[i]]])                             # the last element carries max|src| = s
+        dst[i] = cv2.normalize(src[i].reshape(1, 13), None, 1.0, 0.0, cv2.NORM_INF, dtype=cv2.CV_32F).reshape(13)
+    np.savez_compressed(os.path.join(HERE, "scale_golden.npz"), src=src, s=sc, dst=dst)
+    print("scale_golden.npz written")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "gemm":
         make_gemm()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "scale":
+        make_scale()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gray":
         make_gray()

@@ -71,6 +71,10 @@ class OraclePort:
         L.frameport_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p]
         L.frameport_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameport_fuse_search.argtypes = [C.c_void_p, C.c_void_p]
+        L.frameport_fuse_search_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameport_fuse_search_sim3.restype = None
+        L.frameport_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameport_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameport_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.frameport_distinctive_descriptors.restype = None
         L.frameport_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
@@ -223,6 +227,21 @@ class OraclePort:
         self.L.frameport_distinctive_descriptors(_ptr(d), _ptr(gs), len(gs) - 1, _ptr(out))
         return out[:len(gs) - 1].copy()
 
+    def fuse_search_sim3(self, args, Scw):
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16); best = _i32(args.n_points)
+        self.L.frameport_fuse_search_sim3(C.byref(args), _ptr(S), _ptr(best))
+        return best[:args.n_points].copy()
+
+    def search_by_projection_sim3(self, args, Scw, matched_in):
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16); mi = np.ascontiguousarray(matched_in, np.uint8); out = _i32(args.n_kf)
+        nm = self.L.frameport_search_by_projection_sim3(C.byref(args), _ptr(S), _ptr(mi), _ptr(out))
+        return nm, out[:args.n_kf].copy()
+
+    def search_by_sim3(self, a12, a21, s12, R12, t12):
+        R = np.ascontiguousarray(R12, np.float32).reshape(9); t = np.ascontiguousarray(t12, np.float32).reshape(3); out = _i32(a12.n_points)
+        nf = self.L.frameport_search_by_sim3(C.byref(a12), C.byref(a21), float(s12), _ptr(R), _ptr(t), _ptr(out))
+        return nf, out[:a12.n_points].copy()
+
     def fuse_search(self, args):
         """args: the product's FuseArgs ctypes struct (same layout as frameport_fuse_args) -> best_idx[n_points]."""
         best = _i32(args.n_points)
@@ -362,6 +381,11 @@ class OracleFrameRef:
         L.frameref_search_for_triangulation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_search_local_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frameref_fuse_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_fuse_search_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_search_by_projection_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frameref_mat_div.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_void_p]
+        L.frameref_mat_div.restype = None
         L.frameref_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.frameref_distinctive_descriptors.restype = None
         L.frameref_search_by_projection_keyframe.argtypes = [C.c_void_p, C.c_void_p]
@@ -452,6 +476,27 @@ class OracleFrameRef:
         out = _i32(len(gs) - 1)
         self.L.frameref_distinctive_descriptors(_ptr(d), _ptr(gs), len(gs) - 1, _ptr(out))
         return out[:len(gs) - 1].copy()
+
+    def mat_div(self, v, s):
+        """cv::Mat(v) / s through the shim's MatExpr lowering."""
+        v = np.ascontiguousarray(v, np.float32); out = np.zeros_like(v)
+        self.L.frameref_mat_div(_ptr(v), len(v), float(s), _ptr(out))
+        return out
+
+    def fuse_search_sim3(self, args, Scw):
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16); best = _i32(args.n_points)
+        self.L.frameref_fuse_search_sim3(C.byref(args), _ptr(S), _ptr(best))
+        return best[:args.n_points].copy()
+
+    def search_by_projection_sim3(self, args, Scw, matched_in):
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16); mi = np.ascontiguousarray(matched_in, np.uint8); out = _i32(args.n_kf)
+        nm = self.L.frameref_search_by_projection_sim3(C.byref(args), _ptr(S), _ptr(mi), _ptr(out))
+        return nm, out[:args.n_kf].copy()
+
+    def search_by_sim3(self, a12, a21, s12, R12, t12):
+        R = np.ascontiguousarray(R12, np.float32).reshape(9); t = np.ascontiguousarray(t12, np.float32).reshape(3); out = _i32(a12.n_points)
+        nf = self.L.frameref_search_by_sim3(C.byref(a12), C.byref(a21), float(s12), _ptr(R), _ptr(t), _ptr(out))
+        return nf, out[:a12.n_points].copy()
 
     def fuse_search(self, args):
         """The reference's ORBmatcher::Fuse, one map point per call -> (best_idx[n_points], the camera centre it used)."""

@@ -65,6 +65,19 @@ def test_neg_rt_t_is_the_small_matrix_gemm_of_the_transposed_copy(ref):
     assert differs > 0          # the two evaluations are really different arithmetic
 
 
+def test_shim_mat_div_equals_cv2_golden(ref):
+    """"M / s" (src/ORBmatcher.cc:301-302) = convertTo with scale 1/s: v * (float)(1.0 / s) in float, as cv2 4.13.0 computes it
+    (tests/golden/scale_golden.npz); the double product float(double(v) / s) differs in the last bit for most vectors."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "scale_golden.npz"))
+    other = 0
+    for i in range(len(g["s"])):
+        got = ref.mat_div(g["src"][i], g["s"][i])
+        assert got.tobytes() == g["dst"][i].tobytes()
+        other += (g["src"][i].astype(np.float64) * (1.0 / np.float64(g["s"][i]))).astype(np.float32).tobytes() != g["dst"][i].tobytes()
+    assert other > 1000
+
+
 # ------------------------------------------------------------------------------------------------ M1 / M3: host pieces
 def test_descriptor_distance_and_three_maxima_equal_reference(ref, port):
     """ORBmatcher::DescriptorDistance (the reference's SWAR popcount) and ComputeThreeMaxima executed by the reference,
