@@ -39,11 +39,12 @@ def test_shim_gemm_equals_cv2_golden(ref):
     import os
     g = np.load(os.path.join(os.path.dirname(__file__), "golden", "gemm_golden.npz"))
     A, x, c = g["A"], g["x"], g["c"]
+    g1, g2, g3, g4 = g["ax_plus_c"], g["neg_ax"], g["neg_atx"], g["atx_plus_c"]
     for i in range(len(A)):
-        assert ref.gemm3(A[i], x[i], c[i], 1.0, 1.0, 0).tobytes() == g["ax_plus_c"][i].tobytes()
-        assert ref.gemm3(A[i], x[i], None, -1.0, 0.0, 0).tobytes() == g["neg_ax"][i].tobytes()
-        assert ref.gemm3(A[i], x[i], None, -1.0, 0.0, GEMM_1_T).tobytes() == g["neg_atx"][i].tobytes()
-        assert ref.gemm3(A[i], x[i], c[i], 1.0, 1.0, GEMM_1_T).tobytes() == g["atx_plus_c"][i].tobytes()
+        assert ref.gemm3(A[i], x[i], c[i], 1.0, 1.0, 0).tobytes() == g1[i].tobytes()
+        assert ref.gemm3(A[i], x[i], None, -1.0, 0.0, 0).tobytes() == g2[i].tobytes()
+        assert ref.gemm3(A[i], x[i], None, -1.0, 0.0, GEMM_1_T).tobytes() == g3[i].tobytes()
+        assert ref.gemm3(A[i], x[i], c[i], 1.0, 1.0, GEMM_1_T).tobytes() == g4[i].tobytes()
 
 
 def test_neg_rt_t_is_the_small_matrix_gemm_of_the_transposed_copy(ref):
@@ -70,11 +71,12 @@ def test_shim_mat_div_equals_cv2_golden(ref):
     (tests/golden/scale_golden.npz); the double product float(double(v) / s) differs in the last bit for most vectors."""
     import os
     g = np.load(os.path.join(os.path.dirname(__file__), "golden", "scale_golden.npz"))
+    src, sc, dst = g["src"], g["s"], g["dst"]
     other = 0
-    for i in range(len(g["s"])):
-        got = ref.mat_div(g["src"][i], g["s"][i])
-        assert got.tobytes() == g["dst"][i].tobytes()
-        other += (g["src"][i].astype(np.float64) * (1.0 / np.float64(g["s"][i]))).astype(np.float32).tobytes() != g["dst"][i].tobytes()
+    for i in range(len(sc)):
+        got = ref.mat_div(src[i], sc[i])
+        assert got.tobytes() == dst[i].tobytes()
+        other += (src[i].astype(np.float64) * (1.0 / np.float64(sc[i]))).astype(np.float32).tobytes() != dst[i].tobytes()
     assert other > 1000
 
 
