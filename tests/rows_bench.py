@@ -119,6 +119,25 @@ def main():
     assert np.array_equal(a, o)
     out["distinctive_descriptors_2000_points_%d_observations" % len(dd)] = {
         "gpu_ms": med(lambda: pkg.distinctive_descriptors(dd, gs)), "cpu_ms": med(lambda: po.distinctive_descriptors(dd, gs), 10, 1)}
+    # --- the Sim3 routines of loop closing on the same 4000-point / 1000-feature snapshot, and SearchBySim3 between the two frames
+    import test_sim3 as t3
+    S = t3.sim3_of(keep["Tcw"], 1.1)
+    a = pkg.fuse_search_sim3(fa, S); o = po.fuse_search_sim3(fa, S)
+    assert np.array_equal(a, o)
+    out["fuse_search_sim3_%dx%d" % (fa.n_points, fa.n_kf)] = {
+        "gpu_ms": med(lambda: pkg.fuse_search_sim3(fa, S)), "cpu_ms": med(lambda: po.fuse_search_sim3(fa, S)), "fused": int((a >= 0).sum())}
+    mi = np.zeros(fa.n_kf, np.uint8)
+    a = pkg.search_by_projection_sim3(fa, S, mi); o = po.search_by_projection_sim3(fa, S, mi)
+    assert a[0] == o[0] and np.array_equal(a[1], o[1])
+    out["search_by_projection_sim3_%dx%d" % (fa.n_points, fa.n_kf)] = {
+        "gpu_ms": med(lambda: pkg.search_by_projection_sim3(fa, S, mi)), "cpu_ms": med(lambda: po.search_by_projection_sim3(fa, S, mi)),
+        "nmatches": a[0]}
+    a12, a21, s12, R12, t12, keep3 = t3.sim3_pair(pkg, po, F1, F2, bounds, 7.5, 1)
+    a = pkg.search_by_sim3(a12, a21, s12, R12, t12); o = po.search_by_sim3(a12, a21, s12, R12, t12)
+    assert a[0] == o[0] and np.array_equal(a[1], o[1])
+    out["search_by_sim3_%dx%d" % (a12.n_points, a21.n_points)] = {
+        "gpu_ms": med(lambda: pkg.search_by_sim3(a12, a21, s12, R12, t12)), "cpu_ms": med(lambda: po.search_by_sim3(a12, a21, s12, R12, t12)),
+        "nfound": a[0]}
     print(json.dumps(out, indent=1))
 
 
