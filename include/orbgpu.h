@@ -448,6 +448,49 @@ double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m);
  * an empty group (the reference returns without touching mDescriptor). */
 int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* group_start, int n_groups, int32_t* best_idx);
 
+/* ---- bag of words: the DBoW2 vocabulary tree ----------------------------------------------------
+ * Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:395-402, src/KeyFrame.cc:59-68) call
+ * ORBVocabulary::transform(descriptors, BowVector, FeatureVector, 4)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1194): every descriptor walks the k-ary tree from the root, at each
+ * node to the child with the smallest FORB::distance (FORB.cpp:81-101), the first child on ties (:1237-1250); the leaf's
+ * word id and weight go into the BowVector (BowVector.cpp:34-60), the ancestor `levelsup` levels above the leaves and the
+ * feature index into the FeatureVector (FeatureVector.cpp:29-43); the BowVector is then normalised (BowVector.cpp:64-86).
+ * The tree arrives as flat arrays in node-id order, node 0 = the root (its parent / descriptor / weight are ignored):
+ *   parent[i]   id of the parent (children keep the order in which they appear, as m_nodes[pid].children.push_back does,
+ *               TemplatedVocabulary.h:1389-1390)
+ *   is_leaf[i]  the file's leaf flag: flagged nodes get consecutive word ids in node order (:1407-1414)
+ *   desc[i*32]  node descriptor, weight[i] node weight (double, as parsed)
+ * scoring / weighting are DBoW2's enums (BowVector.h:36-53): weighting 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY; scoring
+ * 0 L1_NORM ... 5 DOT_PRODUCT decides the norm applied by transform (L1, except L2 for L2_NORM and none for DOT_PRODUCT). */
+typedef struct orbgpu_vocabulary orbgpu_vocabulary;
+int orbgpu_vocabulary_create(orbgpu_vocabulary** out, int device, int k, int L, int scoring, int weighting, int n_nodes,
+                             const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight);
+/* TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1338-1425), the ORBvoc.txt format: "k L scoring weighting",
+ * then one line per node "parent is_leaf d0 .. d31 weight".  Same header check (:1358-1362 -> ORBGPU_ERR_ARG).  Empty lines
+ * are skipped: the reference's `while(!f.eof())` turns a trailing newline into one more child of the root whose descriptor
+ * is uninitialised memory (undefined there, not reproduced here). */
+int orbgpu_vocabulary_load_text(orbgpu_vocabulary** out, int device, const char* path);
+void orbgpu_vocabulary_destroy(orbgpu_vocabulary* v);
+/* out6 = k, L, scoring, weighting, number of nodes (root included), number of words */
+int orbgpu_vocabulary_info(const orbgpu_vocabulary* v, int* out6);
+/* transform(features, BowVector, FeatureVector, levelsup) for n descriptors (n x 32 bytes, host).  Outputs, caller-sized:
+ *   words[n], values[n]     the BowVector in ascending word order (std::map iteration order)
+ *   node_ids[n], start[n+1], idx[n]   the FeatureVector in ascending node order, node j owning idx[start[j] .. start[j+1]),
+ *                           feature indices ascending: the layout orbgpu_bow_side takes
+ *   counts3 = BowVector size, FeatureVector size, number of feature indices (features with weight <= 0 are "stopped")
+ * A descriptor whose walk ends on a leaf above the FeatureVector level (an unbalanced tree) leaves `nid` uninitialised in
+ * the reference (:1150-1155); here it gets the leaf's own node id.  n <= 16384, else ORBGPU_ERR_CAPACITY. */
+int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
+                                double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts3);
+/* Vocabulary::score(query, keyframe) for nk keyframes at once (L1Scoring::score, ScoringObject.cpp:25-72): the call
+ * KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates make per candidate keyframe
+ * (src/KeyFrameDatabase.cc:133, :249) and LoopClosing::DetectLoop per covisible keyframe (src/LoopClosing.cc:135).
+ * BowVectors as ascending (word, value) arrays; keyframe k owns kw/kv[kstart[k] .. kstart[k+1]).  The terms
+ * |vi - wi| - |vi| - |wi| of the common words are added in ascending word order, in double.  Only L1_NORM vocabularies
+ * (the one ORB-SLAM2 ships); others return ORBGPU_ERR_UNSUPPORTED. */
+int orbgpu_vocabulary_score(orbgpu_vocabulary* v, const uint32_t* qw, const double* qv, int nq, const uint32_t* kw,
+                            const double* kv, const int32_t* kstart, int nk, double* scores);
+
 /* ---- misc ---------------------------------------------------------------------------------- */
 const char* orbgpu_strerror(int code);
 const char* orbgpu_last_cuda_error(void);   /* thread-local text of the last CUDA failure */

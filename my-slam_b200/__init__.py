@@ -13,5 +13,6 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf,
                      FuseArgs, fuse_args, fuse_search,
                      RelocProjectionArgs, reloc_projection_args, search_by_projection_keyframe, distinctive_descriptors,
-                     fuse_search_sim3, search_by_projection_sim3, search_by_sim3)  # noqa: F401
+                     fuse_search_sim3, search_by_projection_sim3, search_by_sim3,
+                     ORBVocabulary, write_vocabulary_text)  # noqa: F401
 from . import shard, synth  # noqa: F401

@@ -1,0 +1,563 @@
+// orb_vocab.cu -- the DBoW2 vocabulary tree on the device: Frame::ComputeBoW / KeyFrame::ComputeBoW
+// (src/Frame.cc:395-402, src/KeyFrame.cc:59-68) and Vocabulary::score for batches of keyframes.
+//
+// Reference: Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1194 (transform with FeatureVector), :1218-1261 (the walk
+// of one descriptor: strict '<' on FORB::distance, so the first child wins ties), BowVector.cpp:34-86 (addWeight,
+// addIfNotExist, normalize), FeatureVector.cpp:29-43, ScoringObject.cpp:25-72 (L1 score).
+//
+// Layout in HBM: the nodes are renumbered breadth first so that the children of a node are one contiguous block
+// ("position" order): desc[pos] 32 B, child[pos] = (first child position, child count), node_of[pos] = the reference's
+// node id, word_of[pos], weight_of[pos].  ORBvoc.txt (k = 10, L = 6: 1.1 M nodes) takes 62 MB and stays in L2 once warm.
+//
+// Kernels (byte / integer work, no tensor cores):
+//   k_bow_descend   warp = one descriptor; lane = one child of the current node: one coalesced read of the child block,
+//                   256-bit XOR + popcount, warp minimum over (distance << 20 | child index)
+//   k_bow_finalize  one CTA: bitonic sort of (word << 32 | feature) and (node << 32 | feature) in shared memory, run heads
+//                   by prefix scan; a word's value is the leaf weight added once per feature in double (as addWeight
+//                   does); the norm is one thread's in-order sum over the words (the reference's summation order)
+//   k_bow_score     warp = one keyframe: lanes binary-search the query for their words; matching terms are added by lane
+//                   order through shuffles, i.e. in ascending word order as the merge walk of the reference does
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/orbgpu.h"
+
+void orbgpu_internal_set_error(const char* s);   // orbgpu_extractor.cu
+#define CUV(call)                                                                                     \
+    do {                                                                                              \
+        cudaError_t _e = (call);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            char _b[256];                                                                             \
+            snprintf(_b, sizeof(_b), "%s: %s", #call, cudaGetErrorString(_e));                        \
+            orbgpu_internal_set_error(_b);                                                            \
+            return ORBGPU_ERR_CUDA;                                                                   \
+        }                                                                                             \
+    } while (0)
+
+#define BOW_MAX_FEATURES 16384
+#define BOW_FIN_THREADS 1024
+#define BOW_NO_KEY 0xFFFFFFFFFFFFFFFFull
+
+struct VocabDev {
+    const uint4* desc;        // [n_nodes][2]
+    const int2* child;        // [n_nodes] (first child position, count)
+    const uint32_t* node_of;  // [n_nodes]
+    const uint32_t* word_of;  // [n_nodes]
+    const double* weight_of;  // [n_nodes]
+};
+
+// ------------------------------------------------------------------------------------------------ the walk of one descriptor
+__global__ void __launch_bounds__(256) k_bow_descend(VocabDev V, const uint4* __restrict__ feat, int n, int nid_level,
+                                                     uint32_t* __restrict__ f_word, uint32_t* __restrict__ f_node,
+                                                     double* __restrict__ f_weight)
+{
+    const int lane = threadIdx.x & 31;
+    const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (f >= n) return;
+    const uint4 q0 = __ldg(feat + 2 * (size_t)f), q1 = __ldg(feat + 2 * (size_t)f + 1);
+    int pos = 0, level = 0;
+    bool have_nid = nid_level <= 0;
+    uint32_t nid = 0;                                        // root (:1225)
+    for (;;) {
+        const int2 ch = __ldg(V.child + pos);
+        if (ch.y == 0) break;
+        ++level;
+        unsigned best = 0xFFFFFFFFu;
+        for (int c0 = 0; c0 < ch.y; c0 += 32) {
+            const int c = c0 + lane;
+            if (c < ch.y) {
+                const uint4 d0 = __ldg(V.desc + 2 * (size_t)(ch.x + c)), d1 = __ldg(V.desc + 2 * (size_t)(ch.x + c) + 1);
+                const int d = __popc(q0.x ^ d0.x) + __popc(q0.y ^ d0.y) + __popc(q0.z ^ d0.z) + __popc(q0.w ^ d0.w) +
+                              __popc(q1.x ^ d1.x) + __popc(q1.y ^ d1.y) + __popc(q1.z ^ d1.z) + __popc(q1.w ^ d1.w);
+                best = min(best, ((unsigned)d << 20) | (unsigned)c);      // children per node < 2^20
+            }
+        }
+        best = __reduce_min_sync(0xffffffffu, best);
+        pos = ch.x + (int)(best & 0xFFFFFu);
+        if (level == nid_level) { nid = __ldg(V.node_of + pos); have_nid = true; }
+    }
+    if (lane == 0) {
+        f_word[f] = __ldg(V.word_of + pos);
+        f_node[f] = have_nid ? nid : __ldg(V.node_of + pos);
+        f_weight[f] = __ldg(V.weight_of + pos);
+    }
+}
+
+// ------------------------------------------------------------------------------------- BowVector / FeatureVector of one frame
+__device__ __forceinline__ void bitonic_sort_u64(unsigned long long* keys, int n_pad)
+{
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const unsigned long long a = keys[i], b = keys[i | j];
+                if ((a > b) == ((i & k) == 0)) { keys[i] = b; keys[i | j] = a; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// exclusive prefix sum of one int per thread over the CTA (blockDim.x = 1024); *total = the sum
+__device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp, int* total)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();                                     // s_warp may still be read from a previous scan
+    if (lane == 31) s_warp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int x = s_warp[lane], y = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, y, o);
+            if (lane >= o) y += t;
+        }
+        s_warp[lane] = y - x;                            // exclusive warp offsets
+        if (lane == 31) *total = y;
+    }
+    __syncthreads();
+    return s_warp[w] + inc - v;
+}
+
+// norm_mode: 0 none, 1 L1, 2 L2 (GeneralScoring::mustNormalize of the vocabulary's scoring type)
+__global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_pad, const uint32_t* __restrict__ f_word,
+                                                                  const uint32_t* __restrict__ f_node,
+                                                                  const double* __restrict__ f_weight, int weighting, int norm_mode,
+                                                                  uint32_t* out_words, double* out_values, uint32_t* out_node_ids,
+                                                                  int32_t* out_start, uint32_t* out_idx, int* out_counts)
+{
+    extern __shared__ unsigned long long keys[];
+    __shared__ int s_warp[32];
+    __shared__ int s_total;
+    __shared__ double s_norm;
+    const int C = n_pad > BOW_FIN_THREADS ? n_pad / BOW_FIN_THREADS : 1;
+    const int i0 = threadIdx.x * C, i1 = min(i0 + C, n_pad);
+    const bool accumulate = weighting == 0 || weighting == 1;          // TF_IDF, TF: addWeight; IDF, BINARY: addIfNotExist
+
+    // ---- BowVector: words ascending, value = weight added once per feature of the word (:1157-1159)
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x)
+        keys[i] = (i < n && f_weight[i] > 0.0) ? ((unsigned long long)f_word[i] << 32) | (unsigned)i : BOW_NO_KEY;
+    __syncthreads();
+    bitonic_sort_u64(keys, n_pad);
+    int heads = 0;
+    for (int i = i0; i < i1; ++i)
+        heads += keys[i] != BOW_NO_KEY && (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32));
+    int r = block_exclusive_scan(heads, s_warp, &s_total);
+    const int nw = s_total;
+    for (int i = i0; i < i1; ++i) {
+        const unsigned long long key = keys[i];
+        if (key == BOW_NO_KEY || (i != 0 && (keys[i - 1] >> 32) == (key >> 32))) continue;
+        const double w = f_weight[(uint32_t)key];
+        double v = w;
+        if (accumulate)
+            for (int j = i + 1; j < n_pad && (keys[j] >> 32) == (key >> 32); ++j) v = __dadd_rn(v, w);
+        out_words[r] = (uint32_t)(key >> 32);
+        out_values[r] = v;
+        ++r;
+    }
+    __syncthreads();
+    double* vals = reinterpret_cast<double*>(keys);                    // the sorted keys are not needed any more
+    for (int i = threadIdx.x; i < nw; i += blockDim.x) vals[i] = out_values[i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double norm = 0.0;
+        if (norm_mode == 1) {
+            for (int i = 0; i < nw; ++i) norm = __dadd_rn(norm, fabs(vals[i]));               // BowVector.cpp:69-73
+        } else if (norm_mode == 2) {
+            for (int i = 0; i < nw; ++i) norm = __dadd_rn(norm, __dmul_rn(vals[i], vals[i])); // :75-79
+            norm = sqrt(norm);
+        }
+        s_norm = norm;
+    }
+    __syncthreads();
+    if (norm_mode != 0) {
+        const double norm = s_norm;
+        if (norm > 0.0)
+            for (int i = threadIdx.x; i < nw; i += blockDim.x) out_values[i] = vals[i] / norm;
+    } else if (accumulate && nw > 0) {
+        const double nd = (double)nw;                                                         // :1163-1169
+        for (int i = threadIdx.x; i < nw; i += blockDim.x) out_values[i] = vals[i] / nd;
+    }
+    __syncthreads();
+
+    // ---- FeatureVector: nodes ascending, the features of a node in ascending index order (push_back order)
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x)
+        keys[i] = (i < n && f_weight[i] > 0.0) ? ((unsigned long long)f_node[i] << 32) | (unsigned)i : BOW_NO_KEY;
+    __syncthreads();
+    bitonic_sort_u64(keys, n_pad);
+    heads = 0;
+    int valid = 0;
+    for (int i = i0; i < i1; ++i) {
+        heads += keys[i] != BOW_NO_KEY && (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32));
+        valid += keys[i] != BOW_NO_KEY;
+    }
+    r = block_exclusive_scan(heads, s_warp, &s_total);
+    const int nn = s_total;
+    for (int i = i0; i < i1; ++i) {
+        const unsigned long long key = keys[i];
+        if (key == BOW_NO_KEY) continue;
+        out_idx[i] = (uint32_t)key;
+        if (i == 0 || (keys[i - 1] >> 32) != (key >> 32)) {
+            out_node_ids[r] = (uint32_t)(key >> 32);
+            out_start[r] = i;
+            ++r;
+        }
+    }
+    block_exclusive_scan(valid, s_warp, &s_total);
+    if (threadIdx.x == 0) {
+        out_start[nn] = s_total;
+        out_counts[0] = nw; out_counts[1] = nn; out_counts[2] = s_total;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------- L1 score, batched
+__global__ void __launch_bounds__(256) k_bow_score(const uint32_t* __restrict__ qw, const double* __restrict__ qv, int nq,
+                                                   const uint32_t* __restrict__ kw, const double* __restrict__ kv,
+                                                   const int32_t* __restrict__ kstart, int nk, double* __restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (k >= nk) return;
+    const int b = kstart[k], e = kstart[k + 1];
+    double score = 0.0;
+    for (int i0 = b; i0 < e; i0 += 32) {
+        const int i = i0 + lane;
+        bool hit = false;
+        double term = 0.0;
+        if (i < e) {
+            const uint32_t w = __ldg(kw + i);
+            int lo = 0, hi = nq;                                   // first query word >= w
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (__ldg(qw + mid) < w) lo = mid + 1; else hi = mid;
+            }
+            if (lo < nq && __ldg(qw + lo) == w) {
+                const double vi = __ldg(qv + lo), wi = __ldg(kv + i);
+                term = __dsub_rn(__dsub_rn(fabs(__dsub_rn(vi, wi)), fabs(vi)), fabs(wi));   // ScoringObject.cpp:44
+                hit = true;
+            }
+        }
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        while (m) {                                                // ascending word order = the reference's merge walk
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            score = __dadd_rn(score, __shfl_sync(0xffffffffu, term, src));
+        }
+    }
+    if (lane == 0) out[k] = -score / 2.0;                          // :67
+}
+
+// ------------------------------------------------------------------------------------------------------------ host side
+struct orbgpu_vocabulary {
+    int device = 0;
+    int k = 0, L = 0, scoring = 0, weighting = 0, n_nodes = 0, n_words = 0;
+    cudaStream_t st = nullptr;
+    void* d_tree = nullptr;                 // one allocation: desc | child | node_of | word_of | weight_of
+    VocabDev dev{};
+    // per-call scratch, grown on demand
+    int cap = 0;                            // features
+    uint8_t* d_call = nullptr;              // desc | f_word | f_node | f_weight | outputs
+    uint8_t* h_call = nullptr;              // pinned mirror of desc (in) and the outputs (out)
+    size_t score_cap = 0;
+    uint8_t* d_score = nullptr;
+    uint8_t* h_score = nullptr;
+};
+
+namespace {
+
+int norm_mode_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1); }   // ScoringObject.h:74-89
+
+size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct CallLayout {                         // offsets inside d_call / h_call for a capacity of `cap` features
+    size_t desc, f_word, f_node, f_weight, words, values, node_ids, start, idx, counts, total;
+    explicit CallLayout(int cap)
+    {
+        size_t o = 0;
+        desc = o;     o = align256(o + (size_t)cap * 32);
+        f_word = o;   o = align256(o + (size_t)cap * 4);
+        f_node = o;   o = align256(o + (size_t)cap * 4);
+        f_weight = o; o = align256(o + (size_t)cap * 8);
+        words = o;    o = align256(o + (size_t)cap * 4);
+        values = o;   o = align256(o + (size_t)cap * 8);
+        node_ids = o; o = align256(o + (size_t)cap * 4);
+        start = o;    o = align256(o + ((size_t)cap + 1) * 4);
+        idx = o;      o = align256(o + (size_t)cap * 4);
+        counts = o;   o = align256(o + 16);
+        total = o;
+    }
+};
+
+int ensure_call(orbgpu_vocabulary* v, int n)
+{
+    if (n <= v->cap) return ORBGPU_OK;
+    int cap = 2048;
+    while (cap < n) cap <<= 1;
+    if (v->d_call) { cudaFree(v->d_call); v->d_call = nullptr; }
+    if (v->h_call) { cudaFreeHost(v->h_call); v->h_call = nullptr; }
+    v->cap = 0;
+    const CallLayout lay(cap);
+    CUV(cudaMalloc(&v->d_call, lay.total));
+    CUV(cudaHostAlloc(&v->h_call, lay.total, cudaHostAllocDefault));
+    v->cap = cap;
+    return ORBGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbgpu_vocabulary_create(orbgpu_vocabulary** out, int device, int k, int L, int scoring, int weighting, int n_nodes,
+                             const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    if (n_nodes < 1 || scoring < 0 || scoring > 5 || weighting < 0 || weighting > 3) return ORBGPU_ERR_ARG;
+    if (n_nodes > 1 && (!parent || !is_leaf || !desc || !weight)) return ORBGPU_ERR_ARG;
+    for (int i = 1; i < n_nodes; ++i)
+        if (parent[i] < 0 || parent[i] >= i) return ORBGPU_ERR_ARG;     // a node names an earlier node as its parent
+    int ndev = 0;
+    CUV(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(device));
+
+    // children lists in order of appearance (CSR by parent), then breadth-first positions
+    std::vector<int> cstart((size_t)n_nodes + 1, 0), clist((size_t)(n_nodes > 1 ? n_nodes - 1 : 0));
+    for (int i = 1; i < n_nodes; ++i) ++cstart[(size_t)parent[i] + 1];
+    for (int i = 0; i < n_nodes; ++i) cstart[(size_t)i + 1] += cstart[(size_t)i];
+    {
+        std::vector<int> fill(cstart.begin(), cstart.end() - 1);
+        for (int i = 1; i < n_nodes; ++i) clist[(size_t)fill[(size_t)parent[i]]++] = i;
+    }
+    std::vector<uint32_t> word_id((size_t)n_nodes, 0);
+    int n_words = 0;
+    for (int i = 1; i < n_nodes; ++i)
+        if (is_leaf[i]) word_id[(size_t)i] = (uint32_t)n_words++;
+    std::vector<int> order;                                              // order[pos] = node id
+    order.reserve((size_t)n_nodes);
+    order.push_back(0);
+    std::vector<int2> child((size_t)n_nodes);
+    for (size_t head = 0; head < order.size(); ++head) {
+        const int id = order[head];
+        const int nc = cstart[(size_t)id + 1] - cstart[(size_t)id];
+        child[head] = make_int2((int)order.size(), nc);
+        if (nc >= (1 << 20)) return ORBGPU_ERR_UNSUPPORTED;
+        for (int c = 0; c < nc; ++c) order.push_back(clist[(size_t)cstart[(size_t)id] + c]);
+    }
+    if ((int)order.size() != n_nodes) return ORBGPU_ERR_ARG;
+
+    const size_t N = (size_t)n_nodes;
+    const size_t o_desc = 0, o_child = align256(N * 32), o_node = align256(o_child + N * 8), o_word = align256(o_node + N * 4),
+                 o_weight = align256(o_word + N * 4), total = align256(o_weight + N * 8);
+    std::vector<uint8_t> host(total, 0);
+    for (size_t pos = 0; pos < N; ++pos) {
+        const int id = order[pos];
+        if (id != 0) memcpy(&host[o_desc + pos * 32], desc + (size_t)id * 32, 32);
+        memcpy(&host[o_child + pos * 8], &child[pos], 8);
+        const uint32_t nid = (uint32_t)id;
+        memcpy(&host[o_node + pos * 4], &nid, 4);
+        memcpy(&host[o_word + pos * 4], &word_id[(size_t)id], 4);
+        const double w = id != 0 ? weight[id] : 0.0;
+        memcpy(&host[o_weight + pos * 8], &w, 8);
+    }
+    orbgpu_vocabulary* v = new (std::nothrow) orbgpu_vocabulary();
+    if (!v) return ORBGPU_ERR_NOMEM;
+    v->device = device; v->k = k; v->L = L; v->scoring = scoring; v->weighting = weighting;
+    v->n_nodes = n_nodes; v->n_words = n_words;
+    cudaError_t e = cudaStreamCreateWithFlags(&v->st, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&v->d_tree, total);
+    if (e == cudaSuccess) e = cudaMemcpy(v->d_tree, host.data(), total, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bow_finalize, cudaFuncAttributeMaxDynamicSharedMemorySize, BOW_MAX_FEATURES * 8);
+    if (e != cudaSuccess) {
+        char b[256];
+        snprintf(b, sizeof(b), "orbgpu_vocabulary_create: %s", cudaGetErrorString(e));
+        orbgpu_internal_set_error(b);
+        orbgpu_vocabulary_destroy(v);
+        return ORBGPU_ERR_CUDA;
+    }
+    uint8_t* base = static_cast<uint8_t*>(v->d_tree);
+    v->dev.desc = reinterpret_cast<const uint4*>(base + o_desc);
+    v->dev.child = reinterpret_cast<const int2*>(base + o_child);
+    v->dev.node_of = reinterpret_cast<const uint32_t*>(base + o_node);
+    v->dev.word_of = reinterpret_cast<const uint32_t*>(base + o_word);
+    v->dev.weight_of = reinterpret_cast<const double*>(base + o_weight);
+    *out = v;
+    return ORBGPU_OK;
+}
+
+void orbgpu_vocabulary_destroy(orbgpu_vocabulary* v)
+{
+    if (!v) return;
+    cudaSetDevice(v->device);
+    if (v->st) { cudaStreamSynchronize(v->st); cudaStreamDestroy(v->st); }
+    if (v->d_tree) cudaFree(v->d_tree);
+    if (v->d_call) cudaFree(v->d_call);
+    if (v->h_call) cudaFreeHost(v->h_call);
+    if (v->d_score) cudaFree(v->d_score);
+    if (v->h_score) cudaFreeHost(v->h_score);
+    delete v;
+}
+
+int orbgpu_vocabulary_info(const orbgpu_vocabulary* v, int* out6)
+{
+    if (!v || !out6) return ORBGPU_ERR_ARG;
+    out6[0] = v->k; out6[1] = v->L; out6[2] = v->scoring; out6[3] = v->weighting; out6[4] = v->n_nodes; out6[5] = v->n_words;
+    return ORBGPU_OK;
+}
+
+int orbgpu_vocabulary_load_text(orbgpu_vocabulary** out, int device, const char* path)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    if (!path) return ORBGPU_ERR_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) return ORBGPU_ERR_ARG;
+    std::string text;
+    {
+        char buf[1 << 16];
+        size_t got;
+        while ((got = fread(buf, 1, sizeof(buf), f)) > 0) text.append(buf, got);
+    }
+    fclose(f);
+    const char* p = text.c_str();
+    char* q = nullptr;
+    // header line: k L scoring weighting (TemplatedVocabulary.h:1350-1362)
+    const char* eol = strchr(p, '\n');
+    if (!eol) eol = p + text.size();
+    long hdr[4] = {0, 0, 0, 0};
+    for (int i = 0; i < 4; ++i) {
+        const long x = strtol(p, &q, 10);
+        if (q == p || q > eol) return ORBGPU_ERR_ARG;
+        hdr[i] = x; p = q;
+    }
+    if (hdr[0] < 0 || hdr[0] > 20 || hdr[1] < 1 || hdr[1] > 10 || hdr[2] < 0 || hdr[2] > 5 || hdr[3] < 0 || hdr[3] > 3)
+        return ORBGPU_ERR_ARG;
+    p = *eol ? eol + 1 : eol;
+    std::vector<int32_t> parent(1, 0);
+    std::vector<uint8_t> leaf(1, 0), desc(32, 0);
+    std::vector<double> weight(1, 0.0);
+    while (*p) {
+        eol = strchr(p, '\n');
+        if (!eol) eol = text.c_str() + text.size();
+        const char* s = p;
+        while (s < eol && (*s == ' ' || *s == '\t' || *s == '\r')) ++s;
+        if (s < eol) {                                                  // "parent is_leaf d0 .. d31 weight" (:1386-1405)
+            const long pid = strtol(s, &q, 10);
+            if (q == s || q > eol) return ORBGPU_ERR_ARG;
+            s = q;
+            const long isl = strtol(s, &q, 10);
+            if (q == s || q > eol) return ORBGPU_ERR_ARG;
+            s = q;
+            uint8_t d[32];
+            for (int i = 0; i < 32; ++i) {
+                const long x = strtol(s, &q, 10);
+                if (q == s || q > eol) return ORBGPU_ERR_ARG;
+                d[i] = (uint8_t)x; s = q;                                // FORB::fromString: (unsigned char)n
+            }
+            const double w = strtod(s, &q);
+            if (q == s || q > eol) return ORBGPU_ERR_ARG;
+            if (pid < 0 || pid >= (long)parent.size()) return ORBGPU_ERR_ARG;
+            parent.push_back((int32_t)pid);
+            leaf.push_back(isl > 0 ? 1 : 0);
+            desc.insert(desc.end(), d, d + 32);
+            weight.push_back(w);
+        }
+        p = *eol ? eol + 1 : eol;
+    }
+    return orbgpu_vocabulary_create(out, device, (int)hdr[0], (int)hdr[1], (int)hdr[2], (int)hdr[3], (int)parent.size(),
+                                    parent.data(), leaf.data(), desc.data(), weight.data());
+}
+
+int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
+                                double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts3)
+{
+    if (!v || !counts3 || n < 0) return ORBGPU_ERR_ARG;
+    if (n > 0 && (!desc || !words || !values || !node_ids || !start || !idx)) return ORBGPU_ERR_ARG;
+    if (n > BOW_MAX_FEATURES) return ORBGPU_ERR_CAPACITY;
+    counts3[0] = counts3[1] = counts3[2] = 0;
+    if (start) start[0] = 0;
+    CUV(cudaSetDevice(v->device));
+    if (n == 0 || v->n_words == 0) return ORBGPU_OK;                     // v.clear(); fv.clear(); empty() -> return (:1132-1138)
+    const int rc = ensure_call(v, n);
+    if (rc != ORBGPU_OK) return rc;
+    const CallLayout lay(v->cap);
+    memcpy(v->h_call + lay.desc, desc, (size_t)n * 32);
+    CUV(cudaMemcpyAsync(v->d_call + lay.desc, v->h_call + lay.desc, (size_t)n * 32, cudaMemcpyHostToDevice, v->st));
+    uint32_t* f_word = reinterpret_cast<uint32_t*>(v->d_call + lay.f_word);
+    uint32_t* f_node = reinterpret_cast<uint32_t*>(v->d_call + lay.f_node);
+    double* f_weight = reinterpret_cast<double*>(v->d_call + lay.f_weight);
+    k_bow_descend<<<(n + 7) / 8, 256, 0, v->st>>>(v->dev, reinterpret_cast<const uint4*>(v->d_call + lay.desc), n, v->L - levelsup,
+                                                  f_word, f_node, f_weight);
+    int n_pad = 64;
+    while (n_pad < n) n_pad <<= 1;
+    k_bow_finalize<<<1, BOW_FIN_THREADS, (size_t)n_pad * 8, v->st>>>(
+        n, n_pad, f_word, f_node, f_weight, v->weighting, norm_mode_of(v->scoring),
+        reinterpret_cast<uint32_t*>(v->d_call + lay.words), reinterpret_cast<double*>(v->d_call + lay.values),
+        reinterpret_cast<uint32_t*>(v->d_call + lay.node_ids), reinterpret_cast<int32_t*>(v->d_call + lay.start),
+        reinterpret_cast<uint32_t*>(v->d_call + lay.idx), reinterpret_cast<int*>(v->d_call + lay.counts));
+    CUV(cudaGetLastError());
+    // the outputs are one contiguous block [words .. counts] of the layout
+    CUV(cudaMemcpyAsync(v->h_call + lay.words, v->d_call + lay.words, lay.total - lay.words, cudaMemcpyDeviceToHost, v->st));
+    CUV(cudaStreamSynchronize(v->st));
+    const int* c = reinterpret_cast<const int*>(v->h_call + lay.counts);
+    counts3[0] = c[0]; counts3[1] = c[1]; counts3[2] = c[2];
+    memcpy(words, v->h_call + lay.words, (size_t)c[0] * 4);
+    memcpy(values, v->h_call + lay.values, (size_t)c[0] * 8);
+    memcpy(node_ids, v->h_call + lay.node_ids, (size_t)c[1] * 4);
+    memcpy(start, v->h_call + lay.start, ((size_t)c[1] + 1) * 4);
+    memcpy(idx, v->h_call + lay.idx, (size_t)c[2] * 4);
+    return ORBGPU_OK;
+}
+
+int orbgpu_vocabulary_score(orbgpu_vocabulary* v, const uint32_t* qw, const double* qv, int nq, const uint32_t* kw,
+                            const double* kv, const int32_t* kstart, int nk, double* scores)
+{
+    if (!v || nq < 0 || nk < 0) return ORBGPU_ERR_ARG;
+    if (nk == 0) return ORBGPU_OK;
+    if (!kstart || !scores || (nq > 0 && (!qw || !qv))) return ORBGPU_ERR_ARG;
+    if (v->scoring != 0) return ORBGPU_ERR_UNSUPPORTED;
+    const int total = kstart[nk];
+    if (total < 0 || (total > 0 && (!kw || !kv))) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(v->device));
+    const size_t o_qw = 0, o_qv = align256(o_qw + (size_t)nq * 4), o_kw = align256(o_qv + (size_t)nq * 8),
+                 o_kv = align256(o_kw + (size_t)total * 4), o_ks = align256(o_kv + (size_t)total * 8),
+                 o_out = align256(o_ks + ((size_t)nk + 1) * 4), bytes = align256(o_out + (size_t)nk * 8);
+    if (bytes > v->score_cap) {
+        if (v->d_score) { cudaFree(v->d_score); v->d_score = nullptr; }
+        if (v->h_score) { cudaFreeHost(v->h_score); v->h_score = nullptr; }
+        v->score_cap = 0;
+        const size_t cap = bytes + bytes / 2;
+        CUV(cudaMalloc(&v->d_score, cap));
+        CUV(cudaHostAlloc(&v->h_score, cap, cudaHostAllocDefault));
+        v->score_cap = cap;
+    }
+    if (nq) { memcpy(v->h_score + o_qw, qw, (size_t)nq * 4); memcpy(v->h_score + o_qv, qv, (size_t)nq * 8); }
+    if (total) { memcpy(v->h_score + o_kw, kw, (size_t)total * 4); memcpy(v->h_score + o_kv, kv, (size_t)total * 8); }
+    memcpy(v->h_score + o_ks, kstart, ((size_t)nk + 1) * 4);
+    CUV(cudaMemcpyAsync(v->d_score, v->h_score, o_out, cudaMemcpyHostToDevice, v->st));
+    k_bow_score<<<(nk + 7) / 8, 256, 0, v->st>>>(reinterpret_cast<const uint32_t*>(v->d_score + o_qw),
+                                                  reinterpret_cast<const double*>(v->d_score + o_qv), nq,
+                                                  reinterpret_cast<const uint32_t*>(v->d_score + o_kw),
+                                                  reinterpret_cast<const double*>(v->d_score + o_kv),
+                                                  reinterpret_cast<const int32_t*>(v->d_score + o_ks), nk,
+                                                  reinterpret_cast<double*>(v->d_score + o_out));
+    CUV(cudaGetLastError());
+    CUV(cudaMemcpyAsync(v->h_score + o_out, v->d_score + o_out, (size_t)nk * 8, cudaMemcpyDeviceToHost, v->st));
+    CUV(cudaStreamSynchronize(v->st));
+    memcpy(scores, v->h_score + o_out, (size_t)nk * 8);
+    return ORBGPU_OK;
+}
+
+}  // extern "C"

@@ -316,6 +316,12 @@ def lib():
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp]),
+        "orbgpu_vocabulary_create": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
+        "orbgpu_vocabulary_load_text": (i32, [C.POINTER(vp), i32, C.c_char_p]),
+        "orbgpu_vocabulary_destroy": (None, [vp]),
+        "orbgpu_vocabulary_info": (i32, [vp, vp]),
+        "orbgpu_vocabulary_transform": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]),
+        "orbgpu_vocabulary_score": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
@@ -699,3 +705,82 @@ class ORBmatcher:
             self._m = None
 
     __del__ = close
+
+
+class ORBVocabulary:
+    """ORB_SLAM2::ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (include/ORBVocabulary.h:30-31) resident
+    on the device: transform (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1194) as Frame::ComputeBoW / KeyFrame::ComputeBoW
+    call it (src/Frame.cc:395-402, src/KeyFrame.cc:59-68) and score (:1198-1203, L1Scoring) for batches of keyframes.
+    Build it from flat arrays (node 0 = root) or, like loadFromTextFile (:1338-1425), from an ORBvoc.txt-format file."""
+
+    TF_IDF, TF, IDF, BINARY = 0, 1, 2, 3
+    L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = 0, 1, 2, 3, 4, 5
+
+    def __init__(self, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0, device=0):
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); weight = np.ascontiguousarray(weight, np.float64)
+        if not (len(parent) == len(is_leaf) == len(desc) == len(weight)):
+            raise ValueError("parent, is_leaf, desc and weight must have one entry per node (root included)")
+        h = C.c_void_p()
+        _check(lib().orbgpu_vocabulary_create(C.byref(h), device, k, L, scoring, weighting, len(parent), _p(parent), _p(is_leaf),
+                                              _p(desc), _p(weight)))
+        self._h = h
+
+    @classmethod
+    def load_from_text_file(cls, path, device=0):
+        self = cls.__new__(cls)
+        h = C.c_void_p()
+        _check(lib().orbgpu_vocabulary_load_text(C.byref(h), device, os.fsencode(path)))
+        self._h = h
+        return self
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbgpu_vocabulary_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def info(self):
+        """(k, L, scoring, weighting, number of nodes, number of words)"""
+        out = np.zeros(6, np.int32)
+        _check(lib().orbgpu_vocabulary_info(self._h, _p(out)))
+        return tuple(int(x) for x in out)
+
+    def transform(self, desc, levelsup=4):
+        """-> (words, values, node_ids, start, idx): the BowVector as ascending (word id, value) arrays and the FeatureVector
+        as ascending node ids with their feature indices idx[start[j]:start[j + 1]] (the layout ORBmatcher.search_by_bow takes)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d); m = max(n, 1)
+        words = np.zeros(m, np.uint32); values = np.zeros(m, np.float64); nodes = np.zeros(m, np.uint32)
+        start = np.zeros(m + 1, np.int32); idx = np.zeros(m, np.uint32); counts = np.zeros(3, np.int32)
+        _check(lib().orbgpu_vocabulary_transform(self._h, _p(d) if n else None, n, levelsup, _p(words), _p(values), _p(nodes),
+                                                 _p(start), _p(idx), _p(counts)))
+        nw, nn, ni = (int(x) for x in counts)
+        return words[:nw].copy(), values[:nw].copy(), nodes[:nn].copy(), start[:nn + 1].copy(), idx[:ni].copy()
+
+    def score(self, query, keyframes):
+        """query = (words, values); keyframes = list of (words, values) -> scores (float64), one per keyframe."""
+        qw = np.ascontiguousarray(query[0], np.uint32); qv = np.ascontiguousarray(query[1], np.float64)
+        ks = np.zeros(len(keyframes) + 1, np.int32)
+        ks[1:] = np.cumsum([len(k[0]) for k in keyframes])
+        kw = np.ascontiguousarray(np.concatenate([np.asarray(k[0], np.uint32) for k in keyframes]) if keyframes else np.zeros(0, np.uint32))
+        kv = np.ascontiguousarray(np.concatenate([np.asarray(k[1], np.float64) for k in keyframes]) if keyframes else np.zeros(0, np.float64))
+        return self.score_csr(qw, qv, kw, kv, ks)
+
+    def score_csr(self, qw, qv, kw, kv, kstart):
+        out = np.zeros(max(len(kstart) - 1, 1), np.float64)
+        _check(lib().orbgpu_vocabulary_score(self._h, _p(qw) if len(qw) else None, _p(qv) if len(qv) else None, len(qw),
+                                             _p(kw) if len(kw) else None, _p(kv) if len(kv) else None, _p(kstart), len(kstart) - 1, _p(out)))
+        return out[:len(kstart) - 1].copy()
+
+
+def write_vocabulary_text(path, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0, trailing_newline=False):
+    """TemplatedVocabulary::saveToTextFile's format (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1428-1449): what
+    loadFromTextFile reads.  Weights are written with 17 significant digits so that they parse back to the same double."""
+    with open(path, "w") as f:
+        f.write("%d %d %d %d" % (k, L, scoring, weighting))
+        for i in range(1, len(parent)):
+            f.write("\n%d %d %s %.17g" % (parent[i], 1 if is_leaf[i] else 0, " ".join(str(int(b)) for b in desc[i]), weight[i]))
+        if trailing_newline:
+            f.write("\n")

@@ -169,6 +169,17 @@ int frameport_search_by_projection_sim3(const frameport_fuse_args* a, const floa
 int frameport_search_by_sim3(const frameport_fuse_args* a12, const frameport_fuse_args* a21, float s12, const float* R12,
                              const float* t12, int* match12);
 
+/* The DBoW2 vocabulary (oracle/vocab_port.cc): transform(features, BowVector, FeatureVector, levelsup) and the L1 score on
+ * flat arrays; the arguments mean what they mean in include/orbgpu.h (orbgpu_vocabulary_*). */
+typedef struct frameport_vocab frameport_vocab;
+frameport_vocab* frameport_vocab_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t* parent,
+                                        const uint8_t* is_leaf, const uint8_t* desc, const double* weight);
+void frameport_vocab_free(frameport_vocab* v);
+void frameport_vocab_transform(const frameport_vocab* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
+                               double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts);
+void frameport_vocab_score(const uint32_t* qw, const double* qv, int nq, const uint32_t* kw, const double* kv,
+                           const int32_t* kstart, int nk, double* out);
+
 #ifdef __cplusplus
 }
 #endif

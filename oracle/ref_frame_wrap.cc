@@ -68,7 +68,13 @@ void Map::EraseKeyFrame(KeyFrame*) { never("Map::EraseKeyFrame"); }
 void KeyFrameDatabase::erase(KeyFrame*) { never("KeyFrameDatabase::erase"); }
 }  // namespace ORB_SLAM2
 #include "Converter.h"
-std::vector<cv::Mat> ORB_SLAM2::Converter::toDescriptorVector(const cv::Mat&) { never("Converter::toDescriptorVector"); }
+// stand-in for src/Converter.cc:27-35 (that file needs Eigen and g2o): one single-row header per descriptor
+std::vector<cv::Mat> ORB_SLAM2::Converter::toDescriptorVector(const cv::Mat& D)
+{
+    std::vector<cv::Mat> rows((size_t)D.rows);
+    for (int r = 0; r < D.rows; ++r) rows[(size_t)r] = D.row(r);
+    return rows;
+}
 
 namespace {
 

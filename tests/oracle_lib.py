@@ -531,3 +531,106 @@ class OracleFrameRef:
         self.L.frameref_undistort_keypoints(_ptr(k), len(k), _ptr(K4), _ptr(dist), len(dist), w, h, _ptr(out),
                                             _ptr(b4) if w > 0 else None)
         return out, (b4 if w > 0 else None)
+
+
+def _bow_outputs(n):
+    m = max(n, 1)
+    return (np.zeros(m, np.uint32), np.zeros(m, np.float64), np.zeros(m, np.uint32), np.zeros(m + 1, np.int32),
+            np.zeros(m, np.uint32), np.zeros(3, np.int32))
+
+
+def _bow_result(words, values, nodes, start, idx, counts):
+    nw, nn, ni = (int(x) for x in counts)
+    return words[:nw].copy(), values[:nw].copy(), nodes[:nn].copy(), start[:nn + 1].copy(), idx[:ni].copy()
+
+
+class PortVocabulary:
+    """oracle/vocab_port.cc: the restatement of DBoW2's transform / L1 score on flat arrays (same methods as
+    my-slam_b200's ORBVocabulary)."""
+
+    def __init__(self, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0):
+        lib = self.L = C.CDLL(PORT_SO)
+        lib.frameport_vocab_create.restype = C.c_void_p
+        lib.frameport_vocab_create.argtypes = [C.c_int] * 5 + [C.c_void_p] * 4
+        lib.frameport_vocab_free.argtypes = [C.c_void_p]
+        lib.frameport_vocab_free.restype = None
+        lib.frameport_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6
+        lib.frameport_vocab_transform.restype = None
+        lib.frameport_vocab_score.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        lib.frameport_vocab_score.restype = None
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); weight = np.ascontiguousarray(weight, np.float64)
+        self.h = lib.frameport_vocab_create(k, L, scoring, weighting, len(parent), _ptr(parent), _ptr(is_leaf), _ptr(desc), _ptr(weight))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.frameport_vocab_free(self.h)
+            self.h = None
+
+    def transform(self, desc, levelsup=4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        out = _bow_outputs(len(d))
+        self.L.frameport_vocab_transform(self.h, _ptr(d), len(d), levelsup, *[_ptr(a) for a in out])
+        return _bow_result(*out)
+
+    def score_csr(self, qw, qv, kw, kv, kstart):
+        qw = np.ascontiguousarray(qw, np.uint32); qv = np.ascontiguousarray(qv, np.float64)
+        kw = np.ascontiguousarray(kw, np.uint32); kv = np.ascontiguousarray(kv, np.float64)
+        ks = np.ascontiguousarray(kstart, np.int32)
+        out = np.zeros(max(len(ks) - 1, 1), np.float64)
+        self.L.frameport_vocab_score(_ptr(qw), _ptr(qv), len(qw), _ptr(kw), _ptr(kv), _ptr(ks), len(ks) - 1, _ptr(out))
+        return out[:len(ks) - 1].copy()
+
+
+class RefVocabulary:
+    """The reference's own ORBVocabulary (oracle/ref_vocab_wrap.cc in oracle/_ref/libframeref.so), read from a text file by
+    TemplatedVocabulary::loadFromTextFile."""
+
+    def __init__(self, path):
+        lib = self.L = C.CDLL(FRAME_REF_SO)
+        lib.frameref_vocab_load.restype = C.c_void_p
+        lib.frameref_vocab_load.argtypes = [C.c_char_p]
+        lib.frameref_vocab_free.argtypes = [C.c_void_p]
+        lib.frameref_vocab_free.restype = None
+        lib.frameref_vocab_info.argtypes = [C.c_void_p, C.c_void_p]
+        lib.frameref_vocab_info.restype = None
+        for f in (lib.frameref_compute_bow, lib.frameref_vocab_transform):
+            f.restype = None
+        lib.frameref_compute_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 6
+        lib.frameref_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6
+        lib.frameref_vocab_score.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        lib.frameref_vocab_score.restype = None
+        self.h = lib.frameref_vocab_load(os.fsencode(path))
+        if not self.h:
+            raise RuntimeError("loadFromTextFile failed: " + str(path))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.frameref_vocab_free(self.h)
+            self.h = None
+
+    def info(self):
+        out = np.zeros(6, np.int32)
+        self.L.frameref_vocab_info(self.h, _ptr(out))
+        return tuple(int(x) for x in out)
+
+    def compute_bow(self, desc):
+        """Frame::ComputeBoW on a frame holding these descriptors"""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        out = _bow_outputs(len(d))
+        self.L.frameref_compute_bow(self.h, _ptr(d), len(d), *[_ptr(a) for a in out])
+        return _bow_result(*out)
+
+    def transform(self, desc, levelsup=4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        out = _bow_outputs(len(d))
+        self.L.frameref_vocab_transform(self.h, _ptr(d), len(d), levelsup, *[_ptr(a) for a in out])
+        return _bow_result(*out)
+
+    def score_csr(self, qw, qv, kw, kv, kstart):
+        qw = np.ascontiguousarray(qw, np.uint32); qv = np.ascontiguousarray(qv, np.float64)
+        kw = np.ascontiguousarray(kw, np.uint32); kv = np.ascontiguousarray(kv, np.float64)
+        ks = np.ascontiguousarray(kstart, np.int32)
+        out = np.zeros(max(len(ks) - 1, 1), np.float64)
+        self.L.frameref_vocab_score(self.h, _ptr(qw), _ptr(qv), len(qw), _ptr(kw), _ptr(kv), _ptr(ks), len(ks) - 1, _ptr(out))
+        return out[:len(ks) - 1].copy()

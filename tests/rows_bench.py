@@ -138,6 +138,29 @@ def main():
     out["search_by_sim3_%dx%d" % (a12.n_points, a21.n_points)] = {
         "gpu_ms": med(lambda: pkg.search_by_sim3(a12, a21, s12, R12, t12)), "cpu_ms": med(lambda: po.search_by_sim3(a12, a21, s12, R12, t12)),
         "nfound": a[0]}
+    # --- Frame::ComputeBoW on a vocabulary of ORBvoc.txt's shape (k = 10, L = 6: 1 111 111 nodes, 10^6 words), and the L1 score
+    #     of one BowVector against 2000 keyframes (KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates)
+    import test_vocab as tv
+    rng = np.random.default_rng(77)
+    nn = (10 ** 7 - 1) // 9
+    parent = (np.arange(nn, dtype=np.int64) - 1) // 10
+    parent[0] = 0
+    leaf = (np.arange(nn) >= (10 ** 6 - 1) // 9).astype(np.uint8)
+    vdesc = rng.integers(0, 256, (nn, 32), dtype=np.uint8)
+    wts = np.where(leaf > 0, rng.uniform(0.1, 9.0, nn), 0.0)
+    voc = pkg.ORBVocabulary(10, 6, parent.astype(np.int32), leaf, vdesc, wts)
+    pvoc = oracle_lib.PortVocabulary(10, 6, parent.astype(np.int32), leaf, vdesc, wts)
+    for dsc in (dL, np.concatenate([dL, dR, dL[::-1] ^ np.uint8(0x5A), dR[::-1] ^ np.uint8(0xA5)])):
+        assert tv.same_bow(voc.transform(dsc, 4), pvoc.transform(dsc, 4))
+        out["compute_bow_%d_descriptors_1111111_nodes" % len(dsc)] = {
+            "gpu_ms": med(lambda: voc.transform(dsc, 4)), "cpu_ms": med(lambda: pvoc.transform(dsc, 4), 10, 2),
+            "words": len(voc.transform(dsc, 4)[0])}
+    q = tv.random_bow_vectors(rng, 10 ** 6, 1, 500, 900)[0]
+    kw, kv, ks = tv.csr(tv.random_bow_vectors(rng, 10 ** 6, 2000, 500, 900, share=q[0]))
+    a = voc.score_csr(q[0], q[1], kw, kv, ks); o = pvoc.score_csr(q[0], q[1], kw, kv, ks)
+    assert np.array_equal(a.view(np.uint64), o.view(np.uint64))
+    out["bow_score_1_vs_2000_keyframes"] = {"gpu_ms": med(lambda: voc.score_csr(q[0], q[1], kw, kv, ks)),
+                                            "cpu_ms": med(lambda: pvoc.score_csr(q[0], q[1], kw, kv, ks), 10, 2)}
     print(json.dumps(out, indent=1))
 
 
