@@ -491,6 +491,30 @@ int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n
 int orbgpu_vocabulary_score(orbgpu_vocabulary* v, const uint32_t* qw, const double* qv, int nq, const uint32_t* kw,
                             const double* kv, const int32_t* kstart, int nk, double* scores);
 
+/* KeyFrameDatabase (include/KeyFrameDatabase.h:44-75, src/KeyFrameDatabase.cc) with the keyframes' BowVectors resident on the
+ * device.  add (:40-46) appends a BowVector (ascending (word, value) arrays) and returns its slot, slots count up from 0 in
+ * insertion order -- the order in which the reference's inverted-file lists hold the keyframes; erase (:48-67) empties a
+ * slot (its number is not reused); clear (:69-73) forgets everything.
+ * orbgpu_bowdb_query is the data-parallel part of DetectLoopCandidates / DetectRelocalizationCandidates for one query
+ * BowVector, over every slot s (arrays of orbgpu_bowdb_size() entries):
+ *   common_words[s]  words the keyframe shares with the query = mnLoopWords / mnRelocWords after the walk of :86-105 / :207-222
+ *                    (0: the keyframe is not in lKFsSharingWords; erased slots: 0)
+ *   first_common[s]  position in the query of the first shared word (nq if none): the walk meets the keyframes in ascending
+ *                    (first_common, slot) order, which is the order of lKFsSharingWords
+ *   scores[s]        Vocabulary::score(query, keyframe), L1 (ScoringObject.cpp:25-72), for every slot; `float si = score`
+ *                    (:133, :249) narrows it on the host
+ * The connected-keyframe filter, the 0.8 * maxCommonWords and minScore thresholds and the covisibility accumulation
+ * (:107-197, :224-309) walk the keyframe graph and stay with the caller (my-slam_b200/orbgpu.py KeyFrameDatabase). */
+typedef struct orbgpu_bowdb orbgpu_bowdb;
+int orbgpu_bowdb_create(orbgpu_bowdb** out, int device);
+void orbgpu_bowdb_destroy(orbgpu_bowdb* db);
+int orbgpu_bowdb_add(orbgpu_bowdb* db, const uint32_t* words, const double* values, int n, int* slot);
+int orbgpu_bowdb_erase(orbgpu_bowdb* db, int slot);
+int orbgpu_bowdb_clear(orbgpu_bowdb* db);
+int orbgpu_bowdb_size(const orbgpu_bowdb* db);
+int orbgpu_bowdb_query(orbgpu_bowdb* db, const uint32_t* qw, const double* qv, int nq, int32_t* common_words,
+                       int32_t* first_common, double* scores);
+
 /* ---- misc ---------------------------------------------------------------------------------- */
 const char* orbgpu_strerror(int code);
 const char* orbgpu_last_cuda_error(void);   /* thread-local text of the last CUDA failure */

@@ -225,20 +225,23 @@ __global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_p
 // ---------------------------------------------------------------------------------------------------- L1 score, batched
 __global__ void __launch_bounds__(256) k_bow_score(const uint32_t* __restrict__ qw, const double* __restrict__ qv, int nq,
                                                    const uint32_t* __restrict__ kw, const double* __restrict__ kv,
-                                                   const int32_t* __restrict__ kstart, int nk, double* __restrict__ out)
+                                                   const int32_t* __restrict__ kbegin, const int32_t* __restrict__ kend, int nk,
+                                                   double* __restrict__ out, int32_t* __restrict__ common, int32_t* __restrict__ first)
 {
     const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (k >= nk) return;
-    const int b = kstart[k], e = kstart[k + 1];
+    const int b = kbegin[k], e = kend[k];
     double score = 0.0;
+    int ncommon = 0, first_pos = nq;
     for (int i0 = b; i0 < e; i0 += 32) {
         const int i = i0 + lane;
         bool hit = false;
         double term = 0.0;
+        int lo = 0;
         if (i < e) {
             const uint32_t w = __ldg(kw + i);
-            int lo = 0, hi = nq;                                   // first query word >= w
+            int hi = nq;                                           // first query word >= w
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
                 if (__ldg(qw + mid) < w) lo = mid + 1; else hi = mid;
@@ -250,13 +253,19 @@ __global__ void __launch_bounds__(256) k_bow_score(const uint32_t* __restrict__ 
             }
         }
         unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m && ncommon == 0) first_pos = __shfl_sync(0xffffffffu, lo, __ffs(m) - 1);   // words ascend: the first hit
+        ncommon += __popc(m);
         while (m) {                                                // ascending word order = the reference's merge walk
             const int src = __ffs(m) - 1;
             m &= m - 1;
             score = __dadd_rn(score, __shfl_sync(0xffffffffu, term, src));
         }
     }
-    if (lane == 0) out[k] = -score / 2.0;                          // :67
+    if (lane == 0) {
+        out[k] = -score / 2.0;                                     // :67
+        if (common) common[k] = ncommon;
+        if (first) first[k] = first_pos;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------ host side
@@ -551,12 +560,195 @@ int orbgpu_vocabulary_score(orbgpu_vocabulary* v, const uint32_t* qw, const doub
                                                   reinterpret_cast<const double*>(v->d_score + o_qv), nq,
                                                   reinterpret_cast<const uint32_t*>(v->d_score + o_kw),
                                                   reinterpret_cast<const double*>(v->d_score + o_kv),
-                                                  reinterpret_cast<const int32_t*>(v->d_score + o_ks), nk,
-                                                  reinterpret_cast<double*>(v->d_score + o_out));
+                                                  reinterpret_cast<const int32_t*>(v->d_score + o_ks),
+                                                  reinterpret_cast<const int32_t*>(v->d_score + o_ks) + 1, nk,
+                                                  reinterpret_cast<double*>(v->d_score + o_out), nullptr, nullptr);
     CUV(cudaGetLastError());
     CUV(cudaMemcpyAsync(v->h_score + o_out, v->d_score + o_out, (size_t)nk * 8, cudaMemcpyDeviceToHost, v->st));
     CUV(cudaStreamSynchronize(v->st));
     memcpy(scores, v->h_score + o_out, (size_t)nk * 8);
+    return ORBGPU_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------- KeyFrameDatabase: resident BowVectors
+// src/KeyFrameDatabase.cc keeps an inverted file (word -> keyframes) and, per query, walks the lists of the query's words to
+// count the words each keyframe shares (:86-105, :207-222) before scoring the ones above 0.8 * max (:107-139, :224-255).  Here
+// the BowVectors of the keyframes stay in HBM and one launch of k_bow_score gives, for EVERY live keyframe, the number of shared
+// words, the position of the first shared word in the query (the inverted-file walk meets keyframes in that order, then in
+// insertion order) and the L1 score.
+struct orbgpu_bowdb {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    size_t cap = 0, used = 0;                 // entries of the arena
+    uint32_t* d_words = nullptr;
+    double* d_values = nullptr;
+    std::vector<int32_t> begin, end;          // per slot; end == begin for an erased slot
+    bool table_dirty = true;
+    int slot_cap = 0;
+    int32_t* d_begin = nullptr; int32_t* d_end = nullptr;
+    int32_t* d_common = nullptr; int32_t* d_first = nullptr; double* d_score = nullptr;
+    size_t stage_cap = 0;                     // bytes
+    uint8_t* h_stage = nullptr;               // pinned: uploads and results
+    int q_cap = 0;
+    uint32_t* d_qw = nullptr; double* d_qv = nullptr;
+};
+
+namespace {
+int bowdb_stage(orbgpu_bowdb* db, size_t bytes)
+{
+    if (bytes <= db->stage_cap) return ORBGPU_OK;
+    if (db->h_stage) { cudaFreeHost(db->h_stage); db->h_stage = nullptr; db->stage_cap = 0; }
+    const size_t cap = align256(bytes + bytes / 2 + 4096);
+    CUV(cudaHostAlloc(&db->h_stage, cap, cudaHostAllocDefault));
+    db->stage_cap = cap;
+    return ORBGPU_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int orbgpu_bowdb_create(orbgpu_bowdb** out, int device)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    CUV(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(device));
+    orbgpu_bowdb* db = new (std::nothrow) orbgpu_bowdb();
+    if (!db) return ORBGPU_ERR_NOMEM;
+    db->device = device;
+    const cudaError_t e = cudaStreamCreateWithFlags(&db->st, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete db; orbgpu_internal_set_error(cudaGetErrorString(e)); return ORBGPU_ERR_CUDA; }
+    *out = db;
+    return ORBGPU_OK;
+}
+
+void orbgpu_bowdb_destroy(orbgpu_bowdb* db)
+{
+    if (!db) return;
+    cudaSetDevice(db->device);
+    if (db->st) { cudaStreamSynchronize(db->st); cudaStreamDestroy(db->st); }
+    cudaFree(db->d_words); cudaFree(db->d_values); cudaFree(db->d_begin); cudaFree(db->d_end);
+    cudaFree(db->d_common); cudaFree(db->d_first); cudaFree(db->d_score); cudaFree(db->d_qw); cudaFree(db->d_qv);
+    if (db->h_stage) cudaFreeHost(db->h_stage);
+    delete db;
+}
+
+int orbgpu_bowdb_add(orbgpu_bowdb* db, const uint32_t* words, const double* values, int n, int* slot)
+{
+    if (!db || n < 0 || (n > 0 && (!words || !values))) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(db->device));
+    if (db->used + (size_t)n > db->cap) {                             // grow the arena (doubling), keeping what is there
+        size_t cap = db->cap ? db->cap : ((size_t)1 << 20);
+        while (cap < db->used + (size_t)n) cap <<= 1;
+        if (cap > 0x7FFFFFFFull) return ORBGPU_ERR_CAPACITY;
+        uint32_t* nw = nullptr; double* nv = nullptr;
+        CUV(cudaMalloc(&nw, cap * 4));
+        cudaError_t e = cudaMalloc(&nv, cap * 8);
+        if (e != cudaSuccess) { cudaFree(nw); orbgpu_internal_set_error(cudaGetErrorString(e)); return ORBGPU_ERR_CUDA; }
+        CUV(cudaStreamSynchronize(db->st));
+        if (db->used) {
+            CUV(cudaMemcpy(nw, db->d_words, db->used * 4, cudaMemcpyDeviceToDevice));
+            CUV(cudaMemcpy(nv, db->d_values, db->used * 8, cudaMemcpyDeviceToDevice));
+        }
+        cudaFree(db->d_words); cudaFree(db->d_values);
+        db->d_words = nw; db->d_values = nv; db->cap = cap;
+    }
+    if (n > 0) {
+        CUV(cudaStreamSynchronize(db->st));                           // the staging block may still feed an earlier copy
+        const int rc = bowdb_stage(db, (size_t)n * 12 + 256);
+        if (rc != ORBGPU_OK) return rc;
+        const size_t o_v = align256((size_t)n * 4);
+        memcpy(db->h_stage, words, (size_t)n * 4);
+        memcpy(db->h_stage + o_v, values, (size_t)n * 8);
+        CUV(cudaMemcpyAsync(db->d_words + db->used, db->h_stage, (size_t)n * 4, cudaMemcpyHostToDevice, db->st));
+        CUV(cudaMemcpyAsync(db->d_values + db->used, db->h_stage + o_v, (size_t)n * 8, cudaMemcpyHostToDevice, db->st));
+    }
+    db->begin.push_back((int32_t)db->used);
+    db->end.push_back((int32_t)(db->used + (size_t)n));
+    db->used += (size_t)n;
+    db->table_dirty = true;
+    if (slot) *slot = (int)db->begin.size() - 1;
+    return ORBGPU_OK;
+}
+
+int orbgpu_bowdb_erase(orbgpu_bowdb* db, int slot)
+{
+    if (!db || slot < 0 || slot >= (int)db->begin.size()) return ORBGPU_ERR_ARG;
+    db->end[(size_t)slot] = db->begin[(size_t)slot];
+    db->table_dirty = true;
+    return ORBGPU_OK;
+}
+
+int orbgpu_bowdb_clear(orbgpu_bowdb* db)
+{
+    if (!db) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(db->device));
+    CUV(cudaStreamSynchronize(db->st));
+    db->begin.clear(); db->end.clear(); db->used = 0; db->table_dirty = true;
+    return ORBGPU_OK;
+}
+
+int orbgpu_bowdb_size(const orbgpu_bowdb* db) { return db ? (int)db->begin.size() : ORBGPU_ERR_ARG; }
+
+int orbgpu_bowdb_query(orbgpu_bowdb* db, const uint32_t* qw, const double* qv, int nq, int32_t* common_words,
+                       int32_t* first_common, double* scores)
+{
+    if (!db || nq < 0 || (nq > 0 && (!qw || !qv))) return ORBGPU_ERR_ARG;
+    const int ns = (int)db->begin.size();
+    if (ns == 0) return ORBGPU_OK;
+    if (!common_words || !first_common || !scores) return ORBGPU_ERR_ARG;
+    CUV(cudaSetDevice(db->device));
+    CUV(cudaStreamSynchronize(db->st));
+    if (ns > db->slot_cap) {
+        int cap = db->slot_cap ? db->slot_cap : 1024;
+        while (cap < ns) cap <<= 1;
+        cudaFree(db->d_begin); cudaFree(db->d_end); cudaFree(db->d_common); cudaFree(db->d_first); cudaFree(db->d_score);
+        db->d_begin = db->d_end = db->d_common = db->d_first = nullptr; db->d_score = nullptr; db->slot_cap = 0;
+        CUV(cudaMalloc(&db->d_begin, (size_t)cap * 4)); CUV(cudaMalloc(&db->d_end, (size_t)cap * 4));
+        CUV(cudaMalloc(&db->d_common, (size_t)cap * 4)); CUV(cudaMalloc(&db->d_first, (size_t)cap * 4));
+        CUV(cudaMalloc(&db->d_score, (size_t)cap * 8));
+        db->slot_cap = cap; db->table_dirty = true;
+    }
+    if (nq > db->q_cap) {
+        int cap = db->q_cap ? db->q_cap : 4096;
+        while (cap < nq) cap <<= 1;
+        cudaFree(db->d_qw); cudaFree(db->d_qv); db->d_qw = nullptr; db->d_qv = nullptr; db->q_cap = 0;
+        CUV(cudaMalloc(&db->d_qw, (size_t)cap * 4)); CUV(cudaMalloc(&db->d_qv, (size_t)cap * 8));
+        db->q_cap = cap;
+    }
+    // staging: [begin | end] (when dirty) | qw | qv ... results: common | first | score
+    const size_t o_b = 0, o_e = align256((size_t)ns * 4), o_qw = align256(o_e + (size_t)ns * 4), o_qv = align256(o_qw + (size_t)nq * 4),
+                 o_c = align256(o_qv + (size_t)nq * 8), o_f = align256(o_c + (size_t)ns * 4), o_s = align256(o_f + (size_t)ns * 4),
+                 total = align256(o_s + (size_t)ns * 8);
+    const int rc = bowdb_stage(db, total);
+    if (rc != ORBGPU_OK) return rc;
+    if (db->table_dirty) {
+        memcpy(db->h_stage + o_b, db->begin.data(), (size_t)ns * 4);
+        memcpy(db->h_stage + o_e, db->end.data(), (size_t)ns * 4);
+        CUV(cudaMemcpyAsync(db->d_begin, db->h_stage + o_b, (size_t)ns * 4, cudaMemcpyHostToDevice, db->st));
+        CUV(cudaMemcpyAsync(db->d_end, db->h_stage + o_e, (size_t)ns * 4, cudaMemcpyHostToDevice, db->st));
+        db->table_dirty = false;
+    }
+    if (nq) {
+        memcpy(db->h_stage + o_qw, qw, (size_t)nq * 4);
+        memcpy(db->h_stage + o_qv, qv, (size_t)nq * 8);
+        CUV(cudaMemcpyAsync(db->d_qw, db->h_stage + o_qw, (size_t)nq * 4, cudaMemcpyHostToDevice, db->st));
+        CUV(cudaMemcpyAsync(db->d_qv, db->h_stage + o_qv, (size_t)nq * 8, cudaMemcpyHostToDevice, db->st));
+    }
+    k_bow_score<<<(ns + 7) / 8, 256, 0, db->st>>>(db->d_qw, db->d_qv, nq, db->d_words, db->d_values, db->d_begin, db->d_end, ns,
+                                                  db->d_score, db->d_common, db->d_first);
+    CUV(cudaGetLastError());
+    CUV(cudaMemcpyAsync(db->h_stage + o_c, db->d_common, (size_t)ns * 4, cudaMemcpyDeviceToHost, db->st));
+    CUV(cudaMemcpyAsync(db->h_stage + o_f, db->d_first, (size_t)ns * 4, cudaMemcpyDeviceToHost, db->st));
+    CUV(cudaMemcpyAsync(db->h_stage + o_s, db->d_score, (size_t)ns * 8, cudaMemcpyDeviceToHost, db->st));
+    CUV(cudaStreamSynchronize(db->st));
+    memcpy(common_words, db->h_stage + o_c, (size_t)ns * 4);
+    memcpy(first_common, db->h_stage + o_f, (size_t)ns * 4);
+    memcpy(scores, db->h_stage + o_s, (size_t)ns * 8);
     return ORBGPU_OK;
 }
 

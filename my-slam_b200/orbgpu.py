@@ -322,6 +322,13 @@ def lib():
         "orbgpu_vocabulary_info": (i32, [vp, vp]),
         "orbgpu_vocabulary_transform": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]),
         "orbgpu_vocabulary_score": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, vp]),
+        "orbgpu_bowdb_create": (i32, [C.POINTER(vp), i32]),
+        "orbgpu_bowdb_destroy": (None, [vp]),
+        "orbgpu_bowdb_add": (i32, [vp, vp, vp, i32, pi]),
+        "orbgpu_bowdb_erase": (i32, [vp, i32]),
+        "orbgpu_bowdb_clear": (i32, [vp]),
+        "orbgpu_bowdb_size": (i32, [vp]),
+        "orbgpu_bowdb_query": (i32, [vp, vp, vp, i32, vp, vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
@@ -784,3 +791,101 @@ def write_vocabulary_text(path, k, L, parent, is_leaf, desc, weight, scoring=0, 
             f.write("\n%d %d %s %.17g" % (parent[i], 1 if is_leaf[i] else 0, " ".join(str(int(b)) for b in desc[i]), weight[i]))
         if trailing_newline:
             f.write("\n")
+
+
+class KeyFrameDatabase:
+    """ORB_SLAM2::KeyFrameDatabase (include/KeyFrameDatabase.h:44-75, src/KeyFrameDatabase.cc) with the keyframes' BowVectors
+    resident on the device.  Keyframes are known by the slot `add` returns.  The shared-word counts and L1 scores of a query
+    against every keyframe come from one kernel launch (orbgpu_bowdb_query); the thresholds and the covisibility accumulation
+    (:107-197, :224-309) follow on the host, in the reference's float arithmetic and list order.  loop_score / reloc_score keep
+    mLoopScore / mRelocScore between queries, as the KeyFrame members do."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        _check(lib().orbgpu_bowdb_create(C.byref(h), device))
+        self._h = h
+        self.loop_score = []
+        self.reloc_score = []
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbgpu_bowdb_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def add(self, words, values):
+        w = np.ascontiguousarray(words, np.uint32); v = np.ascontiguousarray(values, np.float64)
+        slot = C.c_int(-1)
+        _check(lib().orbgpu_bowdb_add(self._h, _p(w) if len(w) else None, _p(v) if len(v) else None, len(w), C.byref(slot)))
+        self.loop_score.append(np.float32(0)); self.reloc_score.append(np.float32(0))
+        return slot.value
+
+    def erase(self, slot):
+        _check(lib().orbgpu_bowdb_erase(self._h, slot))
+
+    def clear(self):
+        _check(lib().orbgpu_bowdb_clear(self._h))
+        self.loop_score = []; self.reloc_score = []
+
+    def __len__(self):
+        return lib().orbgpu_bowdb_size(self._h)
+
+    def query(self, words, values):
+        """-> (common_words, first_common, scores) for every slot"""
+        w = np.ascontiguousarray(words, np.uint32); v = np.ascontiguousarray(values, np.float64)
+        n = len(self); m = max(n, 1)
+        common = np.zeros(m, np.int32); first = np.zeros(m, np.int32); scores = np.zeros(m, np.float64)
+        _check(lib().orbgpu_bowdb_query(self._h, _p(w) if len(w) else None, _p(v) if len(v) else None, len(w), _p(common), _p(first), _p(scores)))
+        return common[:n], first[:n], scores[:n]
+
+    def _detect(self, query, reloc, connected, neighbours, min_score):
+        common, first, scores = self.query(*query)
+        n = len(common)
+        state = self.reloc_score if reloc else self.loop_score
+        marked = common > 0
+        if not reloc and connected is not None:
+            marked &= ~np.asarray(connected, bool)[:n]
+        words = np.where(marked, common, 0)
+        order = np.nonzero(marked)[0]
+        order = order[np.lexsort((order, first[order]))]          # the inverted-file walk: by first shared word, then insertion
+        if len(order) == 0:
+            return marked, words, []
+        min_common = int(np.float32(int(words[order].max())) * np.float32(0.8))
+        scored = []
+        for k in order:
+            if words[k] > min_common:
+                si = np.float32(scores[k])
+                state[k] = si
+                if reloc or si >= np.float32(min_score):
+                    scored.append((si, int(k)))
+        if not scored:
+            return marked, words, []
+        acc = []
+        best_acc = np.float32(0) if reloc else np.float32(min_score)
+        for si, k in scored:
+            best, total, best_k = si, si, k
+            for k2 in list(neighbours(k))[:10]:
+                if not marked[k2] or (not reloc and not words[k2] > min_common):
+                    continue
+                total = np.float32(total + state[k2])
+                if state[k2] > best:
+                    best_k, best = k2, state[k2]
+            acc.append((total, best_k))
+            if total > best_acc:
+                best_acc = total
+        keep = np.float32(0.75) * best_acc
+        out = []
+        for total, k in acc:
+            if total > keep and k not in out:
+                out.append(k)
+        return marked, words, out
+
+    def detect_loop_candidates(self, query, connected, neighbours, min_score):
+        """DetectLoopCandidates(pKF, minScore) (:76-197): query = pKF's (words, values); connected[slot] = member of
+        pKF->GetConnectedKeyFrames(); neighbours(slot) = that keyframe's ordered covisibility list -> candidate slots"""
+        return self._detect(query, False, connected, neighbours, min_score)[2]
+
+    def detect_relocalization_candidates(self, query, neighbours):
+        """DetectRelocalizationCandidates(F) (:199-309) -> candidate slots"""
+        return self._detect(query, True, None, neighbours, 0.0)[2]

@@ -180,6 +180,23 @@ void frameport_vocab_transform(const frameport_vocab* v, const uint8_t* desc, in
 void frameport_vocab_score(const uint32_t* qw, const double* qv, int nq, const uint32_t* kw, const double* kv,
                            const int32_t* kstart, int nk, double* out);
 
+/* KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates (src/KeyFrameDatabase.cc:76-197, :199-309) on flat
+ * arrays.  Keyframes are numbered in the order they were added to the database. */
+typedef struct {
+    int n_kf;
+    const uint32_t* kw; const double* kv; const int32_t* kstart;   /* the keyframes' BowVectors (CSR, ascending words) */
+    const uint8_t* erased;        /* [n_kf] 1 = KeyFrameDatabase::erase was called for it (it stays in the covisibility graph) */
+    const uint32_t* qw; const double* qv; int nq;                  /* the query's BowVector */
+    const uint8_t* connected;     /* [n_kf] loop detection: member of pKF->GetConnectedKeyFrames() */
+    const int32_t* neigh_start; const int32_t* neigh;              /* mvpOrderedConnectedKeyFrames of every keyframe (CSR) */
+    const float* prev_score;      /* [n_kf] mLoopScore / mRelocScore as an earlier query left it */
+    float min_score;              /* loop detection */
+    int reloc;                    /* 0 DetectLoopCandidates, 1 DetectRelocalizationCandidates */
+} frameport_db_args;
+/* marked[i] = the keyframe was put into lKFsSharingWords; words[i] = mnLoopWords / mnRelocWords (where marked);
+ * score[i] = mLoopScore / mRelocScore after the call; returns the number of candidates written (keyframe numbers, in order) */
+int frameport_db_detect(const frameport_db_args* a, int32_t* marked, int32_t* words, float* score, int32_t* candidates);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,7 +65,6 @@ namespace ORB_SLAM2 {
 Map::Map() : mnMaxKFid(0), mnBigChangeIdx(0) {}
 void Map::EraseMapPoint(MapPoint*) {}     // reached from MapPoint::Replace under Fuse; the harness owns the points
 void Map::EraseKeyFrame(KeyFrame*) { never("Map::EraseKeyFrame"); }
-void KeyFrameDatabase::erase(KeyFrame*) { never("KeyFrameDatabase::erase"); }
 }  // namespace ORB_SLAM2
 #include "Converter.h"
 // stand-in for src/Converter.cc:27-35 (that file needs Eigen and g2o): one single-row header per descriptor
@@ -843,3 +842,61 @@ void frameref_undistort_keypoints(const KP* keys, int n, const float* K4, const 
 }
 
 }  // extern "C"
+
+// The reference's own KeyFrameDatabase (src/KeyFrameDatabase.cc, compiled unchanged): add / erase / DetectLoopCandidates /
+// DetectRelocalizationCandidates on KeyFrames whose BowVectors, covisibility lists and earlier scores come from the caller.
+// `voc` is a vocabulary read by oracle/ref_vocab_wrap.cc (it sizes the inverted file and scores).
+extern "C" int frameref_db_detect(void* voc, const frameport_db_args* a, int32_t* marked, int32_t* words, float* score,
+                                  int32_t* candidates)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, 1.f, 1.f, 0.f, 0.f);
+    const ORBVocabulary* V = static_cast<const ORBVocabulary*>(voc);
+    World world;
+    KeyFrameDatabase db(*V);
+    const int n = a->n_kf;
+    std::vector<KeyFrame*> kfs;
+    for (int k = 0; k < n; ++k) {
+        Frame F;
+        F.N = 0; F.mTcw = cv::Mat::eye(4, 4, CV_32F); F.mnId = (unsigned long)(k + 1);
+        F.mbf = 1.f; F.mb = 1.f; F.mThDepth = 1.f; F.mTimeStamp = 0;
+        F.mnScaleLevels = 1; F.mfScaleFactor = 1.2f; F.mfLogScaleFactor = std::log(1.2f);
+        for (int i = a->kstart[k]; i < a->kstart[k + 1]; ++i) F.mBowVec.insert(F.mBowVec.end(), std::make_pair(a->kw[i], a->kv[i]));
+        KeyFrame* kf = new KeyFrame(F, &world.map, &db);
+        world.keyframes.push_back(kf);
+        kfs.push_back(kf);
+        kf->mLoopScore = a->prev_score[k]; kf->mRelocScore = a->prev_score[k];
+        db.add(kf);
+    }
+    for (int k = 0; k < n; ++k) {
+        for (int j = a->neigh_start[k]; j < a->neigh_start[k + 1]; ++j) kfs[k]->mvpOrderedConnectedKeyFrames.push_back(kfs[a->neigh[j]]);
+        if (a->erased[k]) db.erase(kfs[k]);
+    }
+    // the query: a keyframe outside the database (LoopClosing::DetectLoop adds it afterwards) / the current frame
+    Frame Q;
+    Q.N = 0; Q.mTcw = cv::Mat::eye(4, 4, CV_32F); Q.mnId = (unsigned long)(n + 100);
+    Q.mbf = 1.f; Q.mb = 1.f; Q.mThDepth = 1.f; Q.mTimeStamp = 0;
+    Q.mnScaleLevels = 1; Q.mfScaleFactor = 1.2f; Q.mfLogScaleFactor = std::log(1.2f);
+    for (int i = 0; i < a->nq; ++i) Q.mBowVec.insert(Q.mBowVec.end(), std::make_pair(a->qw[i], a->qv[i]));
+    std::vector<KeyFrame*> got;
+    unsigned long qid;
+    if (a->reloc) {
+        got = db.DetectRelocalizationCandidates(&Q);
+        qid = Q.mnId;
+    } else {
+        KeyFrame* q = new KeyFrame(Q, &world.map, &db);
+        world.keyframes.push_back(q);
+        for (int k = 0; k < n; ++k)
+            if (a->connected[k]) q->mConnectedKeyFrameWeights[kfs[k]] = 20;
+        got = db.DetectLoopCandidates(q, a->min_score);
+        qid = q->mnId;
+    }
+    for (int k = 0; k < n; ++k) {
+        marked[k] = a->reloc ? (kfs[k]->mnRelocQuery == qid) : (kfs[k]->mnLoopQuery == qid);
+        words[k] = a->reloc ? kfs[k]->mnRelocWords : kfs[k]->mnLoopWords;
+        score[k] = a->reloc ? kfs[k]->mRelocScore : kfs[k]->mLoopScore;
+    }
+    for (size_t i = 0; i < got.size(); ++i)
+        candidates[i] = (int32_t)(std::find(kfs.begin(), kfs.end(), got[i]) - kfs.begin());
+    return (int)got.size();
+}

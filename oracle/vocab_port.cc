@@ -6,8 +6,10 @@
 //   BowVector::addWeight / addIfNotExist / normalize                        Thirdparty/DBoW2/DBoW2/BowVector.cpp:34-86
 //   FeatureVector::addFeature                                               Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:29-43
 //   L1Scoring::score                                                        Thirdparty/DBoW2/DBoW2/ScoringObject.cpp:25-72
+//   KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates src/KeyFrameDatabase.cc:76-197, :199-309
 // Pinned by tests/test_vocab.py against the reference's own code (oracle/_ref/libframeref.so: the same vocabulary read by
 // TemplatedVocabulary::loadFromTextFile, the same descriptors through Frame::ComputeBoW and Vocabulary::score).
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -141,3 +143,87 @@ void frameport_vocab_score(const uint32_t* qw, const double* qv, int nq, const u
 }
 
 }  // extern "C"
+
+// KeyFrameDatabase::DetectLoopCandidates (src/KeyFrameDatabase.cc:76-197) / DetectRelocalizationCandidates (:199-309)
+#include <list>
+#include <set>
+#include <utility>
+
+extern "C" int frameport_db_detect(const frameport_db_args* a, int32_t* marked, int32_t* words, float* score, int32_t* candidates)
+{
+    const int n = a->n_kf;
+    // the inverted file as add() leaves it (:40-46), erase() having removed its keyframes (:48-67).  It persists between
+    // queries in the reference, so repeated calls on the same arrays (tests/rows_bench.py timing the query) reuse it.
+    static std::vector<std::vector<int> > inverted;
+    static const void* built_for = NULL;
+    static int built_n = -1, built_total = -1;
+    static uint64_t built_sample = 0;
+    uint64_t sample = 1469598103934665603ull;                      // a strided sample of the words guards a reused address
+    for (int i = 0; i < a->kstart[n]; i += (i < 256 ? 1 : 257)) sample = (sample ^ a->kw[i]) * 1099511628211ull;
+    static std::vector<uint8_t> built_erased;
+    const bool same = built_for == a->kw && built_n == n && built_total == a->kstart[n] && built_sample == sample && built_erased.size() == (size_t)n &&
+                      std::memcmp(built_erased.data(), a->erased, (size_t)n) == 0;
+    if (!same) {
+        uint32_t max_word = 0;
+        for (int i = 0; i < a->kstart[n]; ++i) max_word = std::max(max_word, a->kw[i]);
+        inverted.assign((size_t)max_word + 1, std::vector<int>());
+        for (int k = 0; k < n; ++k)
+            if (!a->erased[k])
+                for (int i = a->kstart[k]; i < a->kstart[k + 1]; ++i) inverted[a->kw[i]].push_back(k);
+        built_for = a->kw; built_sample = sample; built_n = n; built_total = a->kstart[n]; built_erased.assign(a->erased, a->erased + n);
+    }
+    static const std::vector<int> no_keyframes;
+    for (int k = 0; k < n; ++k) { marked[k] = 0; words[k] = 0; score[k] = a->prev_score[k]; }
+    std::list<int> sharing;
+    for (int i = 0; i < a->nq; ++i) {                                              // :86-105 / :207-222
+        const std::vector<int>& l = a->qw[i] < inverted.size() ? inverted[a->qw[i]] : no_keyframes;
+        for (size_t j = 0; j < l.size(); ++j) {
+            const int k = l[j];
+            if (!marked[k]) {
+                words[k] = 0;
+                if (a->reloc || !a->connected[k]) { marked[k] = 1; sharing.push_back(k); }
+            }
+            words[k]++;
+        }
+    }
+    if (sharing.empty()) return 0;
+    int max_common = 0;
+    for (std::list<int>::iterator it = sharing.begin(); it != sharing.end(); ++it) max_common = std::max(max_common, words[*it]);
+    const int min_common = max_common * 0.8f;                                       // :120 / :235
+    std::list<std::pair<float, int> > scored;
+    for (std::list<int>::iterator it = sharing.begin(); it != sharing.end(); ++it) {
+        const int k = *it;
+        if (words[k] > min_common) {
+            double s;
+            const int32_t span[2] = {0, a->kstart[k + 1] - a->kstart[k]};
+            frameport_vocab_score(a->qw, a->qv, a->nq, a->kw + a->kstart[k], a->kv + a->kstart[k], span, 1, &s);
+            const float si = (float)s;
+            score[k] = si;
+            if (a->reloc || si >= a->min_score) scored.push_back(std::make_pair(si, k));
+        }
+    }
+    if (scored.empty()) return 0;
+    std::list<std::pair<float, int> > acc;
+    float best_acc = a->reloc ? 0.f : a->min_score;
+    for (std::list<std::pair<float, int> >::iterator it = scored.begin(); it != scored.end(); ++it) {
+        const int k = it->second;
+        float best = it->first, sum = it->first;
+        int best_k = k;
+        const int nb = std::min(a->neigh_start[k + 1] - a->neigh_start[k], 10);    // GetBestCovisibilityKeyFrames(10)
+        for (int j = 0; j < nb; ++j) {
+            const int k2 = a->neigh[a->neigh_start[k] + j];
+            if (!marked[k2]) continue;
+            if (!a->reloc && !(words[k2] > min_common)) continue;                   // :159 (the relocaliser has no such test, :273-274)
+            sum += score[k2];
+            if (score[k2] > best) { best_k = k2; best = score[k2]; }
+        }
+        acc.push_back(std::make_pair(sum, best_k));
+        if (sum > best_acc) best_acc = sum;
+    }
+    const float keep = 0.75f * best_acc;
+    std::set<int> added;
+    int nc = 0;
+    for (std::list<std::pair<float, int> >::iterator it = acc.begin(); it != acc.end(); ++it)
+        if (it->first > keep && !added.count(it->second)) { candidates[nc++] = it->second; added.insert(it->second); }
+    return nc;
+}

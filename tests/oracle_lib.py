@@ -634,3 +634,47 @@ class RefVocabulary:
         out = np.zeros(max(len(ks) - 1, 1), np.float64)
         self.L.frameref_vocab_score(self.h, _ptr(qw), _ptr(qv), len(qw), _ptr(kw), _ptr(kv), _ptr(ks), len(ks) - 1, _ptr(out))
         return out[:len(ks) - 1].copy()
+
+
+class DbArgs(C.Structure):
+    """frameport_db_args (oracle/frame_port.h)"""
+    _fields_ = [("n_kf", C.c_int), ("kw", C.c_void_p), ("kv", C.c_void_p), ("kstart", C.c_void_p), ("erased", C.c_void_p),
+                ("qw", C.c_void_p), ("qv", C.c_void_p), ("nq", C.c_int), ("connected", C.c_void_p), ("neigh_start", C.c_void_p),
+                ("neigh", C.c_void_p), ("prev_score", C.c_void_p), ("min_score", C.c_float), ("reloc", C.c_int)]
+
+
+def db_args(kfs, erased, query, connected, neighbours, prev_score, min_score, reloc):
+    """kfs: list of (words, values); neighbours: list of lists (ordered covisibility); -> (DbArgs, keep-alive)"""
+    n = len(kfs)
+    ks = np.zeros(n + 1, np.int32); ks[1:] = np.cumsum([len(k[0]) for k in kfs])
+    kw = np.ascontiguousarray(np.concatenate([np.asarray(k[0], np.uint32) for k in kfs] + [np.zeros(0, np.uint32)]))
+    kv = np.ascontiguousarray(np.concatenate([np.asarray(k[1], np.float64) for k in kfs] + [np.zeros(0, np.float64)]))
+    er = np.ascontiguousarray(erased, np.uint8); co = np.ascontiguousarray(connected, np.uint8)
+    qw = np.ascontiguousarray(query[0], np.uint32); qv = np.ascontiguousarray(query[1], np.float64)
+    ns = np.zeros(n + 1, np.int32); ns[1:] = np.cumsum([len(x) for x in neighbours])
+    ne = np.ascontiguousarray(np.concatenate([np.asarray(x, np.int32) for x in neighbours] + [np.zeros(0, np.int32)]).astype(np.int32))
+    ps = np.ascontiguousarray(prev_score, np.float32)
+    keep = (ks, kw, kv, er, co, qw, qv, ns, ne, ps)
+    a = DbArgs(n, kw.ctypes.data, kv.ctypes.data, ks.ctypes.data, er.ctypes.data, qw.ctypes.data, qv.ctypes.data, len(qw),
+               co.ctypes.data, ns.ctypes.data, ne.ctypes.data, ps.ctypes.data, float(min_score), int(reloc))
+    return a, keep
+
+
+def _db_detect(fn, n, *lead):
+    marked = np.zeros(max(n, 1), np.int32); words = np.zeros(max(n, 1), np.int32); score = np.zeros(max(n, 1), np.float32)
+    cand = np.zeros(max(n, 1), np.int32)
+    nc = fn(*lead, _ptr(marked), _ptr(words), _ptr(score), _ptr(cand))
+    return marked[:n].astype(bool), words[:n].copy(), score[:n].copy(), cand[:nc].copy()
+
+
+def port_db_detect(args):
+    lib = C.CDLL(PORT_SO)
+    lib.frameport_db_detect.argtypes = [C.c_void_p] * 5
+    return _db_detect(lib.frameport_db_detect, args.n_kf, C.byref(args))
+
+
+def ref_db_detect(ref_vocab, args):
+    """the reference's own KeyFrameDatabase.cc; ref_vocab: a RefVocabulary (sizes the inverted file, scores)"""
+    lib = ref_vocab.L
+    lib.frameref_db_detect.argtypes = [C.c_void_p] * 6
+    return _db_detect(lib.frameref_db_detect, args.n_kf, ref_vocab.h, C.byref(args))

@@ -161,6 +161,24 @@ def main():
     assert np.array_equal(a.view(np.uint64), o.view(np.uint64))
     out["bow_score_1_vs_2000_keyframes"] = {"gpu_ms": med(lambda: voc.score_csr(q[0], q[1], kw, kv, ks)),
                                             "cpu_ms": med(lambda: pvoc.score_csr(q[0], q[1], kw, kv, ks), 10, 2)}
+    # --- KeyFrameDatabase: 2000 keyframes resident on the device; DetectRelocalizationCandidates for one frame (device query +
+    #     host thresholds / covisibility accumulation) against the restatement (inverted file already built, as in the reference)
+    kfs, erased, qq, connected, neighbours, prev, min_score = tv.db_scene(5, 10 ** 6, n_kf=2000, reloc=True)
+    dargs, dkeep = oracle_lib.db_args(kfs, erased, qq, connected, neighbours, prev, min_score, True)
+    db = pkg.KeyFrameDatabase()
+    for kf in kfs:
+        db.add(*kf)
+    for i in np.nonzero(erased)[0]:
+        db.erase(int(i))
+    db.reloc_score[:] = list(prev)
+    want = oracle_lib.port_db_detect(dargs)
+    got = db.detect_relocalization_candidates(qq, lambda k: neighbours[k])
+    assert got == want[3].tolist()
+    out["keyframe_database_query_2000_keyframes"] = {
+        "gpu_ms_device_query": med(lambda: db.query(*qq)),
+        "gpu_ms_detect_with_python_host_part": med(lambda: db.detect_relocalization_candidates(qq, lambda k: neighbours[k])),
+        "cpu_ms": med(lambda: oracle_lib.port_db_detect(dargs), 10, 2), "candidates": len(got),
+        "sharing_words": int(want[0].sum())}
     print(json.dumps(out, indent=1))
 
 

@@ -255,3 +255,75 @@ def test_device_score_equals_oracle(pkg):
     with pytest.raises(pkg.OrbGpuError):
         other.score_csr(q[0], q[1], kw, kv, ks)                      # only L1_NORM vocabularies are scored on the device
     other.close()
+
+
+# ------------------------------------------------------------------------------------------- KeyFrameDatabase (src/KeyFrameDatabase.cc)
+def db_scene(seed, n_words, n_kf=90, reloc=False):
+    """Keyframes with overlapping BowVectors (a few near-copies of the query), some erased from the database, some connected
+    to the query keyframe, random ordered covisibility lists (more than 10 entries for some), scores left by earlier queries."""
+    rng = np.random.default_rng(seed)
+    q = random_bow_vectors(rng, n_words, 1, 300, 600)[0]
+    kfs = random_bow_vectors(rng, n_words, n_kf, 100, 600, share=q[0])
+    for i in rng.choice(n_kf, 6, replace=False):                      # near-copies: high scores, many common words
+        keep = rng.random(len(q[0])) < 0.9
+        v = q[1][keep] * rng.uniform(0.8, 1.2, int(keep.sum()))
+        kfs[i] = (q[0][keep], v / v.sum())
+    kfs[int(rng.integers(n_kf))] = (np.zeros(0, np.uint32), np.zeros(0))
+    erased = rng.random(n_kf) < 0.1
+    connected = (rng.random(n_kf) < 0.15) & (not reloc)
+    neighbours = [rng.choice(n_kf, int(rng.integers(0, 16)), replace=False).tolist() for _ in range(n_kf)]
+    prev = rng.uniform(0, 0.05, n_kf).astype(np.float32)
+    min_score = float(rng.choice([0.0, 0.01, 0.03]))
+    return kfs, erased, q, connected, neighbours, prev, min_score
+
+
+@needs_ref
+@pytest.mark.parametrize("reloc", [False, True], ids=["loop", "reloc"])
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
+def test_keyframe_database_restatement_equals_reference(pkg, tmp_path, seed, reloc):
+    t = make_tree(1, 10, 4, fixed_k=True)
+    path = tmp_path / "voc.txt"
+    pkg.write_vocabulary_text(path, t["k"], t["L"], t["parent"], t["is_leaf"], t["desc"], t["weight"])
+    ref = oracle_lib.RefVocabulary(path)
+    kfs, erased, q, connected, neighbours, prev, min_score = db_scene(seed, int(t["is_leaf"].sum()), reloc=reloc)
+    args, keep = oracle_lib.db_args(kfs, erased, q, connected, neighbours, prev, min_score, reloc)
+    wm, ww, ws, wc = oracle_lib.ref_db_detect(ref, args)
+    gm, gw, gs, gc = oracle_lib.port_db_detect(args)
+    assert wm.sum() > 20 and len(wc) >= 1
+    assert np.array_equal(gm, wm) and np.array_equal(gw[wm], ww[wm])
+    assert np.array_equal(gs.view(np.uint32), ws.view(np.uint32))
+    assert np.array_equal(gc, wc)
+    assert not wm[erased].any() and not wm[np.asarray(connected, bool)].any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reloc", [False, True], ids=["loop", "reloc"])
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6, 7, 8])
+def test_device_keyframe_database_equals_oracle(pkg, seed, reloc):
+    kfs, erased, q, connected, neighbours, prev, min_score = db_scene(seed, 10000, n_kf=90 if seed < 7 else 1500, reloc=reloc)
+    args, keep = oracle_lib.db_args(kfs, erased, q, connected, neighbours, prev, min_score, reloc)
+    wm, ww, ws, wc = oracle_lib.port_db_detect(args)
+    db = pkg.KeyFrameDatabase()
+    for k in kfs:
+        db.add(*k)
+    for i in np.nonzero(erased)[0]:
+        db.erase(int(i))
+    assert len(db) == len(kfs)
+    # the kernel's three arrays against plain set arithmetic
+    common, first, scores = db.query(*q)
+    for i in (0, 5, len(kfs) - 1):
+        both = np.intersect1d(q[0], kfs[i][0])
+        assert common[i] == (0 if erased[i] else len(both))
+        assert first[i] == (len(q[0]) if erased[i] or len(both) == 0 else int(np.searchsorted(q[0], both[0])))
+    state = db.reloc_score if reloc else db.loop_score
+    state[:] = list(prev)
+    gm, gw, gc = db._detect(q, reloc, connected, lambda k: neighbours[k], min_score)
+    assert np.array_equal(gm, wm) and np.array_equal(gw[wm], ww[wm]) and list(gc) == wc.tolist() and len(wc) >= 1
+    assert np.array_equal(np.array(state, np.float32).view(np.uint32), ws.view(np.uint32))
+    if reloc:
+        assert db.detect_relocalization_candidates(q, lambda k: neighbours[k]) == list(gc)   # scores now left by the first query
+    db.clear()
+    assert len(db) == 0 and db.detect_relocalization_candidates(q, lambda k: []) == []
+    s = db.add(*kfs[0])
+    assert s == 0 and db.query(*kfs[0])[0][0] == len(kfs[0][0])
+    db.close()
