@@ -482,6 +482,14 @@ int orbgpu_vocabulary_info(const orbgpu_vocabulary* v, int* out6);
  * the reference (:1150-1155); here it gets the leaf's own node id.  n <= 16384, else ORBGPU_ERR_CAPACITY. */
 int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
                                 double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts3);
+/* The same for a batch of frames in one call (a frame's ComputeBoW is independent of every other's): frame f owns the
+ * descriptors [frame_start[f], frame_start[f + 1]) of desc (frame_start[0] = 0, at most 16384 per frame); its outputs go to
+ * the same offsets of words / values / node_ids / idx, its start list (count + 1 entries) to start + frame_start[f] + f, so
+ * start needs frame_start[n_frames] + n_frames entries; counts3[3 f .. 3 f + 2] as above.  One descriptor walk over all
+ * frames, then one CTA per frame. */
+int orbgpu_vocabulary_transform_batch(orbgpu_vocabulary* v, const uint8_t* desc, const int32_t* frame_start, int n_frames,
+                                      int levelsup, uint32_t* words, double* values, uint32_t* node_ids, int32_t* start,
+                                      uint32_t* idx, int* counts3);
 /* Vocabulary::score(query, keyframe) for nk keyframes at once (L1Scoring::score, ScoringObject.cpp:25-72): the call
  * KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates make per candidate keyframe
  * (src/KeyFrameDatabase.cc:133, :249) and LoopClosing::DetectLoop per covisible keyframe (src/LoopClosing.cc:135).

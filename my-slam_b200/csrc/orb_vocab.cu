@@ -90,18 +90,33 @@ __global__ void __launch_bounds__(256) k_bow_descend(VocabDev V, const uint4* __
 }
 
 // ------------------------------------------------------------------------------------- BowVector / FeatureVector of one frame
+// Bitonic sort of n_pad (power of two >= 64) keys in shared memory.  Pair t of a stage with distance j is
+// (i, i | j), i = t with a zero inserted at bit log2(j): for j <= 32 the 32 pairs of a warp are exactly its own block of 64
+// consecutive keys, so runs of such stages need only __syncwarp; a CTA barrier is needed around the stages with j >= 64.
+__device__ __forceinline__ void bitonic_stage(unsigned long long* keys, int n_pad, int k, int j)
+{
+    for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const unsigned long long a = keys[i], b = keys[i | j];
+        if ((a > b) == ((i & k) == 0)) { keys[i] = b; keys[i | j] = a; }
+    }
+}
+
 __device__ __forceinline__ void bitonic_sort_u64(unsigned long long* keys, int n_pad)
 {
     for (int k = 2; k <= n_pad; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
-                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                const unsigned long long a = keys[i], b = keys[i | j];
-                if ((a > b) == ((i & k) == 0)) { keys[i] = b; keys[i | j] = a; }
-            }
+        int j = k >> 1;
+        for (; j >= 64; j >>= 1) {
+            bitonic_stage(keys, n_pad, k, j);
             __syncthreads();
         }
+        for (; j > 0; j >>= 1) {
+            bitonic_stage(keys, n_pad, k, j);
+            __syncwarp();
+        }
+        if (k >= 64) __syncthreads();       // the next k starts with a stage that crosses warps (k <= 32: still warp-local)
     }
+    __syncthreads();
 }
 
 // exclusive prefix sum of one int per thread over the CTA (blockDim.x = 1024); *total = the sum
@@ -131,17 +146,34 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp, int* tot
     return s_warp[w] + inc - v;
 }
 
-// norm_mode: 0 none, 1 L1, 2 L2 (GeneralScoring::mustNormalize of the vocabulary's scoring type)
-__global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_pad, const uint32_t* __restrict__ f_word,
-                                                                  const uint32_t* __restrict__ f_node,
-                                                                  const double* __restrict__ f_weight, int weighting, int norm_mode,
-                                                                  uint32_t* out_words, double* out_values, uint32_t* out_node_ids,
-                                                                  int32_t* out_start, uint32_t* out_idx, int* out_counts)
+// norm_mode: 0 none, 1 L1, 2 L2 (GeneralScoring::mustNormalize of the vocabulary's scoring type).
+// CTA = one frame: its descriptors are [frame_start[f], frame_start[f + 1]) of the flat per-descriptor arrays; its outputs go
+// to the same offsets of the flat output arrays (a frame with n descriptors has at most n words / nodes / indices), its
+// `start` list to out_start + frame_start[f] + f (n + 1 entries) and its three counts to out_counts + 3 f.
+__global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(const int32_t* __restrict__ frame_start,
+                                                                  const uint32_t* __restrict__ f_word_all,
+                                                                  const uint32_t* __restrict__ f_node_all,
+                                                                  const double* __restrict__ f_weight_all, int weighting, int norm_mode,
+                                                                  uint32_t* out_words_all, double* out_values_all, uint32_t* out_node_ids_all,
+                                                                  int32_t* out_start_all, uint32_t* out_idx_all, int* out_counts_all)
 {
     extern __shared__ unsigned long long keys[];
     __shared__ int s_warp[32];
     __shared__ int s_total;
     __shared__ double s_norm;
+    const int frame = blockIdx.x;
+    const int base = frame_start[frame], n = frame_start[frame + 1] - base;
+    const uint32_t* f_word = f_word_all + base; const uint32_t* f_node = f_node_all + base; const double* f_weight = f_weight_all + base;
+    uint32_t* out_words = out_words_all + base; double* out_values = out_values_all + base;
+    uint32_t* out_node_ids = out_node_ids_all + base; uint32_t* out_idx = out_idx_all + base;
+    int32_t* out_start = out_start_all + base + frame;
+    int* out_counts = out_counts_all + 3 * frame;
+    if (n == 0) {
+        if (threadIdx.x == 0) { out_start[0] = 0; out_counts[0] = out_counts[1] = out_counts[2] = 0; }
+        return;
+    }
+    int n_pad = 64;
+    while (n_pad < n) n_pad <<= 1;
     const int C = n_pad > BOW_FIN_THREADS ? n_pad / BOW_FIN_THREADS : 1;
     const int i0 = threadIdx.x * C, i1 = min(i0 + C, n_pad);
     const bool accumulate = weighting == 0 || weighting == 1;          // TF_IDF, TF: addWeight; IDF, BINARY: addIfNotExist
@@ -151,21 +183,31 @@ __global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_p
         keys[i] = (i < n && f_weight[i] > 0.0) ? ((unsigned long long)f_word[i] << 32) | (unsigned)i : BOW_NO_KEY;
     __syncthreads();
     bitonic_sort_u64(keys, n_pad);
-    int heads = 0;
-    for (int i = i0; i < i1; ++i)
+    int heads = 0, valid = 0;
+    for (int i = i0; i < i1; ++i) {
         heads += keys[i] != BOW_NO_KEY && (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32));
+        valid += keys[i] != BOW_NO_KEY;
+    }
     int r = block_exclusive_scan(heads, s_warp, &s_total);
     const int nw = s_total;
-    for (int i = i0; i < i1; ++i) {
+    block_exclusive_scan(valid, s_warp, &s_total);
+    const int m = s_total;                                             // features that are not stopped
+    // where each run starts (out_start serves as scratch here; the FeatureVector pass rewrites it): run length = next - this
+    for (int i = i0; i < i1; ++i)
+        if (keys[i] != BOW_NO_KEY && (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32))) out_start[r++] = i;
+    if (threadIdx.x == 0) out_start[nw] = m;
+    __syncthreads();
+    for (int j = threadIdx.x; j < nw; j += blockDim.x) {
+        const int i = out_start[j];
         const unsigned long long key = keys[i];
-        if (key == BOW_NO_KEY || (i != 0 && (keys[i - 1] >> 32) == (key >> 32))) continue;
         const double w = f_weight[(uint32_t)key];
         double v = w;
-        if (accumulate)
-            for (int j = i + 1; j < n_pad && (keys[j] >> 32) == (key >> 32); ++j) v = __dadd_rn(v, w);
-        out_words[r] = (uint32_t)(key >> 32);
-        out_values[r] = v;
-        ++r;
+        if (accumulate) {
+            const int cnt = out_start[j + 1] - i;
+            for (int c = 1; c < cnt; ++c) v = __dadd_rn(v, w);         // addWeight: "+= w" per further feature, in double
+        }
+        out_words[j] = (uint32_t)(key >> 32);
+        out_values[j] = v;
     }
     __syncthreads();
     double* vals = reinterpret_cast<double*>(keys);                    // the sorted keys are not needed any more
@@ -173,11 +215,19 @@ __global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_p
     __syncthreads();
     if (threadIdx.x == 0) {
         double norm = 0.0;
-        if (norm_mode == 1) {
-            for (int i = 0; i < nw; ++i) norm = __dadd_rn(norm, fabs(vals[i]));               // BowVector.cpp:69-73
-        } else if (norm_mode == 2) {
-            for (int i = 0; i < nw; ++i) norm = __dadd_rn(norm, __dmul_rn(vals[i], vals[i])); // :75-79
-            norm = sqrt(norm);
+        // one in-order chain of DADDs (the reference's summation order); the terms of 16 words are fetched and prepared
+        // ahead of the chain so that only the adds are serial
+        if (norm_mode != 0) {
+            int i = 0;
+            for (; i + 16 <= nw; i += 16) {
+                double t[16];
+#pragma unroll
+                for (int u = 0; u < 16; ++u) t[u] = norm_mode == 1 ? fabs(vals[i + u]) : __dmul_rn(vals[i + u], vals[i + u]);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) norm = __dadd_rn(norm, t[u]);                    // BowVector.cpp:69-73, :75-79
+            }
+            for (; i < nw; ++i) norm = __dadd_rn(norm, norm_mode == 1 ? fabs(vals[i]) : __dmul_rn(vals[i], vals[i]));
+            if (norm_mode == 2) norm = sqrt(norm);
         }
         s_norm = norm;
     }
@@ -198,11 +248,8 @@ __global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_p
     __syncthreads();
     bitonic_sort_u64(keys, n_pad);
     heads = 0;
-    int valid = 0;
-    for (int i = i0; i < i1; ++i) {
+    for (int i = i0; i < i1; ++i)
         heads += keys[i] != BOW_NO_KEY && (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32));
-        valid += keys[i] != BOW_NO_KEY;
-    }
     r = block_exclusive_scan(heads, s_warp, &s_total);
     const int nn = s_total;
     for (int i = i0; i < i1; ++i) {
@@ -215,10 +262,9 @@ __global__ void __launch_bounds__(BOW_FIN_THREADS) k_bow_finalize(int n, int n_p
             ++r;
         }
     }
-    block_exclusive_scan(valid, s_warp, &s_total);
     if (threadIdx.x == 0) {
-        out_start[nn] = s_total;
-        out_counts[0] = nw; out_counts[1] = nn; out_counts[2] = s_total;
+        out_start[nn] = m;
+        out_counts[0] = nw; out_counts[1] = nn; out_counts[2] = m;
     }
 }
 
@@ -276,7 +322,7 @@ struct orbgpu_vocabulary {
     void* d_tree = nullptr;                 // one allocation: desc | child | node_of | word_of | weight_of
     VocabDev dev{};
     // per-call scratch, grown on demand
-    int cap = 0;                            // features
+    int cap = 0, fcap = 0;                  // descriptors / frames the per-call scratch holds
     uint8_t* d_call = nullptr;              // desc | f_word | f_node | f_weight | outputs
     uint8_t* h_call = nullptr;              // pinned mirror of desc (in) and the outputs (out)
     size_t score_cap = 0;
@@ -290,11 +336,12 @@ int norm_mode_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1)
 
 size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct CallLayout {                         // offsets inside d_call / h_call for a capacity of `cap` features
-    size_t desc, f_word, f_node, f_weight, words, values, node_ids, start, idx, counts, total;
-    explicit CallLayout(int cap)
+struct CallLayout {                         // offsets inside d_call / h_call for `cap` descriptors in `fcap` frames
+    size_t desc, fstart, f_word, f_node, f_weight, words, values, node_ids, start, idx, counts, total;
+    CallLayout(int cap, int fcap)
     {
         size_t o = 0;
+        fstart = o;   o = align256(o + ((size_t)fcap + 1) * 4);
         desc = o;     o = align256(o + (size_t)cap * 32);
         f_word = o;   o = align256(o + (size_t)cap * 4);
         f_node = o;   o = align256(o + (size_t)cap * 4);
@@ -302,25 +349,26 @@ struct CallLayout {                         // offsets inside d_call / h_call fo
         words = o;    o = align256(o + (size_t)cap * 4);
         values = o;   o = align256(o + (size_t)cap * 8);
         node_ids = o; o = align256(o + (size_t)cap * 4);
-        start = o;    o = align256(o + ((size_t)cap + 1) * 4);
+        start = o;    o = align256(o + ((size_t)cap + (size_t)fcap) * 4);
         idx = o;      o = align256(o + (size_t)cap * 4);
-        counts = o;   o = align256(o + 16);
+        counts = o;   o = align256(o + (size_t)fcap * 12);
         total = o;
     }
 };
 
-int ensure_call(orbgpu_vocabulary* v, int n)
+int ensure_call(orbgpu_vocabulary* v, int n, int frames)
 {
-    if (n <= v->cap) return ORBGPU_OK;
-    int cap = 2048;
+    if (n <= v->cap && frames <= v->fcap) return ORBGPU_OK;
+    int cap = v->cap ? v->cap : 2048, fcap = v->fcap ? v->fcap : 16;
     while (cap < n) cap <<= 1;
+    while (fcap < frames) fcap <<= 1;
     if (v->d_call) { cudaFree(v->d_call); v->d_call = nullptr; }
     if (v->h_call) { cudaFreeHost(v->h_call); v->h_call = nullptr; }
-    v->cap = 0;
-    const CallLayout lay(cap);
+    v->cap = v->fcap = 0;
+    const CallLayout lay(cap, fcap);
     CUV(cudaMalloc(&v->d_call, lay.total));
     CUV(cudaHostAlloc(&v->h_call, lay.total, cudaHostAllocDefault));
-    v->cap = cap;
+    v->cap = cap; v->fcap = fcap;
     return ORBGPU_OK;
 }
 
@@ -489,30 +537,45 @@ int orbgpu_vocabulary_load_text(orbgpu_vocabulary** out, int device, const char*
                                     parent.data(), leaf.data(), desc.data(), weight.data());
 }
 
-int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
-                                double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts3)
+int orbgpu_vocabulary_transform_batch(orbgpu_vocabulary* v, const uint8_t* desc, const int32_t* frame_start, int n_frames,
+                                      int levelsup, uint32_t* words, double* values, uint32_t* node_ids, int32_t* start,
+                                      uint32_t* idx, int* counts3)
 {
-    if (!v || !counts3 || n < 0) return ORBGPU_ERR_ARG;
-    if (n > 0 && (!desc || !words || !values || !node_ids || !start || !idx)) return ORBGPU_ERR_ARG;
-    if (n > BOW_MAX_FEATURES) return ORBGPU_ERR_CAPACITY;
-    counts3[0] = counts3[1] = counts3[2] = 0;
-    if (start) start[0] = 0;
+    if (!v || n_frames < 0) return ORBGPU_ERR_ARG;
+    if (n_frames == 0) return ORBGPU_OK;
+    if (!frame_start || !counts3 || !start || frame_start[0] != 0) return ORBGPU_ERR_ARG;
+    int max_n = 0;
+    for (int f = 0; f < n_frames; ++f) {
+        const int nf = frame_start[f + 1] - frame_start[f];
+        if (nf < 0) return ORBGPU_ERR_ARG;
+        if (nf > BOW_MAX_FEATURES) return ORBGPU_ERR_CAPACITY;
+        max_n = nf > max_n ? nf : max_n;
+    }
+    const int n = frame_start[n_frames];
+    if (n > 0 && (!desc || !words || !values || !node_ids || !idx)) return ORBGPU_ERR_ARG;
+    for (int f = 0; f < n_frames; ++f) {
+        counts3[3 * f] = counts3[3 * f + 1] = counts3[3 * f + 2] = 0;
+        start[frame_start[f] + f] = 0;
+    }
     CUV(cudaSetDevice(v->device));
     if (n == 0 || v->n_words == 0) return ORBGPU_OK;                     // v.clear(); fv.clear(); empty() -> return (:1132-1138)
-    const int rc = ensure_call(v, n);
+    const int rc = ensure_call(v, n, n_frames);
     if (rc != ORBGPU_OK) return rc;
-    const CallLayout lay(v->cap);
+    const CallLayout lay(v->cap, v->fcap);
     memcpy(v->h_call + lay.desc, desc, (size_t)n * 32);
-    CUV(cudaMemcpyAsync(v->d_call + lay.desc, v->h_call + lay.desc, (size_t)n * 32, cudaMemcpyHostToDevice, v->st));
+    memcpy(v->h_call + lay.fstart, frame_start, ((size_t)n_frames + 1) * 4);
+    // frame_start and the descriptors are neighbours in the layout: one upload
+    CUV(cudaMemcpyAsync(v->d_call + lay.fstart, v->h_call + lay.fstart, lay.desc + (size_t)n * 32 - lay.fstart,
+                        cudaMemcpyHostToDevice, v->st));
     uint32_t* f_word = reinterpret_cast<uint32_t*>(v->d_call + lay.f_word);
     uint32_t* f_node = reinterpret_cast<uint32_t*>(v->d_call + lay.f_node);
     double* f_weight = reinterpret_cast<double*>(v->d_call + lay.f_weight);
     k_bow_descend<<<(n + 7) / 8, 256, 0, v->st>>>(v->dev, reinterpret_cast<const uint4*>(v->d_call + lay.desc), n, v->L - levelsup,
                                                   f_word, f_node, f_weight);
     int n_pad = 64;
-    while (n_pad < n) n_pad <<= 1;
-    k_bow_finalize<<<1, BOW_FIN_THREADS, (size_t)n_pad * 8, v->st>>>(
-        n, n_pad, f_word, f_node, f_weight, v->weighting, norm_mode_of(v->scoring),
+    while (n_pad < max_n) n_pad <<= 1;
+    k_bow_finalize<<<n_frames, BOW_FIN_THREADS, (size_t)n_pad * 8, v->st>>>(
+        reinterpret_cast<const int32_t*>(v->d_call + lay.fstart), f_word, f_node, f_weight, v->weighting, norm_mode_of(v->scoring),
         reinterpret_cast<uint32_t*>(v->d_call + lay.words), reinterpret_cast<double*>(v->d_call + lay.values),
         reinterpret_cast<uint32_t*>(v->d_call + lay.node_ids), reinterpret_cast<int32_t*>(v->d_call + lay.start),
         reinterpret_cast<uint32_t*>(v->d_call + lay.idx), reinterpret_cast<int*>(v->d_call + lay.counts));
@@ -521,13 +584,28 @@ int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n
     CUV(cudaMemcpyAsync(v->h_call + lay.words, v->d_call + lay.words, lay.total - lay.words, cudaMemcpyDeviceToHost, v->st));
     CUV(cudaStreamSynchronize(v->st));
     const int* c = reinterpret_cast<const int*>(v->h_call + lay.counts);
-    counts3[0] = c[0]; counts3[1] = c[1]; counts3[2] = c[2];
-    memcpy(words, v->h_call + lay.words, (size_t)c[0] * 4);
-    memcpy(values, v->h_call + lay.values, (size_t)c[0] * 8);
-    memcpy(node_ids, v->h_call + lay.node_ids, (size_t)c[1] * 4);
-    memcpy(start, v->h_call + lay.start, ((size_t)c[1] + 1) * 4);
-    memcpy(idx, v->h_call + lay.idx, (size_t)c[2] * 4);
+    memcpy(counts3, c, (size_t)n_frames * 12);
+    for (int f = 0; f < n_frames; ++f) {                                 // only what each frame produced is copied out
+        const size_t b = (size_t)frame_start[f];
+        memcpy(words + b, v->h_call + lay.words + b * 4, (size_t)c[3 * f] * 4);
+        memcpy(values + b, v->h_call + lay.values + b * 8, (size_t)c[3 * f] * 8);
+        memcpy(node_ids + b, v->h_call + lay.node_ids + b * 4, (size_t)c[3 * f + 1] * 4);
+        memcpy(start + b + f, v->h_call + lay.start + (b + f) * 4, ((size_t)c[3 * f + 1] + 1) * 4);
+        memcpy(idx + b, v->h_call + lay.idx + b * 4, (size_t)c[3 * f + 2] * 4);
+    }
     return ORBGPU_OK;
+}
+
+int orbgpu_vocabulary_transform(orbgpu_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words,
+                                double* values, uint32_t* node_ids, int32_t* start, uint32_t* idx, int* counts3)
+{
+    if (!v || !counts3 || n < 0) return ORBGPU_ERR_ARG;
+    if (n > 0 && (!desc || !words || !values || !node_ids || !start || !idx)) return ORBGPU_ERR_ARG;
+    if (n > BOW_MAX_FEATURES) return ORBGPU_ERR_CAPACITY;
+    int32_t one_start = 0;
+    const int32_t frame_start[2] = {0, n};
+    return orbgpu_vocabulary_transform_batch(v, desc, frame_start, 1, levelsup, words, values, node_ids, start ? start : &one_start,
+                                             idx, counts3);
 }
 
 int orbgpu_vocabulary_score(orbgpu_vocabulary* v, const uint32_t* qw, const double* qv, int nq, const uint32_t* kw,

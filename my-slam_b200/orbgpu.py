@@ -321,6 +321,7 @@ def lib():
         "orbgpu_vocabulary_destroy": (None, [vp]),
         "orbgpu_vocabulary_info": (i32, [vp, vp]),
         "orbgpu_vocabulary_transform": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]),
+        "orbgpu_vocabulary_transform_batch": (i32, [vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]),
         "orbgpu_vocabulary_score": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, vp]),
         "orbgpu_bowdb_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_bowdb_destroy": (None, [vp]),
@@ -765,6 +766,23 @@ class ORBVocabulary:
                                                  _p(start), _p(idx), _p(counts)))
         nw, nn, ni = (int(x) for x in counts)
         return words[:nw].copy(), values[:nw].copy(), nodes[:nn].copy(), start[:nn + 1].copy(), idx[:ni].copy()
+
+    def transform_batch(self, descs, levelsup=4):
+        """ComputeBoW for several frames in one call: descs = list of (n_f x 32) arrays -> list of transform() results"""
+        fs = np.zeros(len(descs) + 1, np.int32)
+        fs[1:] = np.cumsum([len(d) for d in descs])
+        n = int(fs[-1]); m = max(n, 1); nf = len(descs)
+        d = np.ascontiguousarray(np.concatenate([np.asarray(x, np.uint8).reshape(-1, 32) for x in descs] + [np.zeros((0, 32), np.uint8)]))
+        words = np.zeros(m, np.uint32); values = np.zeros(m, np.float64); nodes = np.zeros(m, np.uint32)
+        start = np.zeros(m + nf + 1, np.int32); idx = np.zeros(m, np.uint32); counts = np.zeros(3 * max(nf, 1), np.int32)
+        _check(lib().orbgpu_vocabulary_transform_batch(self._h, _p(d) if n else None, _p(fs), nf, levelsup, _p(words), _p(values),
+                                                       _p(nodes), _p(start), _p(idx), _p(counts)))
+        out = []
+        for f in range(nf):
+            b = int(fs[f]); nw, nn, ni = (int(x) for x in counts[3 * f:3 * f + 3])
+            out.append((words[b:b + nw].copy(), values[b:b + nw].copy(), nodes[b:b + nn].copy(), start[b + f:b + f + nn + 1].copy(),
+                        idx[b:b + ni].copy()))
+        return out
 
     def score(self, query, keyframes):
         """query = (words, values); keyframes = list of (words, values) -> scores (float64), one per keyframe."""

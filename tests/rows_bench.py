@@ -155,6 +155,12 @@ def main():
         out["compute_bow_%d_descriptors_1111111_nodes" % len(dsc)] = {
             "gpu_ms": med(lambda: voc.transform(dsc, 4)), "cpu_ms": med(lambda: pvoc.transform(dsc, 4), 10, 2),
             "words": len(voc.transform(dsc, 4)[0])}
+    batch = [np.roll(dL, i, axis=0) ^ np.uint8(i & 0xFF) for i in range(256)]
+    bb = voc.transform_batch(batch, 4)
+    assert tv.same_bow(bb[17], pvoc.transform(batch[17], 4))
+    out["compute_bow_batch_256_frames_x_%d_descriptors" % len(dL)] = {
+        "gpu_ms_per_frame": med(lambda: voc.transform_batch(batch, 4), 10, 2) / 256,
+        "cpu_ms_per_frame": med(lambda: pvoc.transform(batch[17], 4), 10, 2)}
     q = tv.random_bow_vectors(rng, 10 ** 6, 1, 500, 900)[0]
     kw, kv, ks = tv.csr(tv.random_bow_vectors(rng, 10 ** 6, 2000, 500, 900, share=q[0]))
     a = voc.score_csr(q[0], q[1], kw, kv, ks); o = pvoc.score_csr(q[0], q[1], kw, kv, ks)

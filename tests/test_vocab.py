@@ -226,6 +226,23 @@ def test_device_transform_edge_cases(pkg, tmp_path):
 
 
 @pytest.mark.gpu
+def test_device_transform_batch_equals_per_frame_oracle(pkg):
+    t = make_tree(2, 9, 5, min_leaf_depth=3)
+    port = oracle_lib.PortVocabulary(*vocab_args(t))
+    dev = pkg.ORBVocabulary(*vocab_args(t))
+    sizes = [1000, 0, 1, 2500, 64, 65, 0, 1013] + [1000] * 40
+    descs = [features_for(t, 300 + i, n) if n else np.zeros((0, 32), np.uint8) for i, n in enumerate(sizes)]
+    descs[3][:] = descs[3][0]                                        # 2500 copies of one descriptor: one word, added 2500 times
+    got = dev.transform_batch(descs, 2)
+    assert len(got) == len(sizes)
+    for d, g in zip(descs, got):
+        assert same_bow(g, port.transform(d, 2))
+    assert dev.transform_batch([], 2) == []
+    assert same_bow(dev.transform_batch([descs[0]], 2)[0], got[0])
+    dev.close()
+
+
+@pytest.mark.gpu
 def test_device_score_equals_oracle(pkg):
     t = make_tree(1, 10, 4, fixed_k=True)
     port = oracle_lib.PortVocabulary(*vocab_args(t))
