@@ -21,6 +21,7 @@
 #include "FrameQueue.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 
 using namespace ORB_SLAM2;
 
@@ -152,6 +153,52 @@ static int cmd_maxima()
     return 0;
 }
 
+// bow <voc.txt> <desc.bin> <n> <levelsup> <out.bin>: ORBVocabulary::loadFromTextFile + transform on the descriptor rows, then the
+// BowVector scored against itself and against a BowDatabase holding it.  out.bin: int32 nw, nn, ni | words u32[nw] | values f64[nw]
+// | nodes u32[nn] | per node: int32 count + u32 indices | f64 self score | int32 db common words | f64 db score
+static int cmd_bow(int argc, char** argv)
+{
+    if (argc < 7) return 2;
+    const int n = atoi(argv[4]), levelsup = atoi(argv[5]);
+    std::vector<unsigned char> raw;
+    if (!read_file(argv[3], raw, (size_t)n * 32)) { fprintf(stderr, "cannot read %s\n", argv[3]); return 2; }
+    ORBVocabulary voc;
+    if (!voc.loadFromTextFile(argv[2])) { fprintf(stderr, "cannot load %s\n", argv[2]); return 4; }
+    std::vector<cv::Mat> rows;
+    cv::Mat D(n, 32, CV_8U);
+    if (n) memcpy(D.data, raw.data(), (size_t)n * 32);
+    for (int i = 0; i < n; ++i) rows.push_back(D.row(i));                       // Converter::toDescriptorVector
+    DBoW2::BowVector bv, bv2; DBoW2::FeatureVector fv, fv2;
+    voc.transform(rows, bv, fv, levelsup);
+    voc.transform(D, bv2, fv2, levelsup);
+    if (bv != bv2 || fv != fv2) { fprintf(stderr, "the two transform overloads disagree\n"); return 5; }
+    BowDatabase db;
+    const int slot = db.add(bv);
+    std::vector<int> common, first; std::vector<double> scores;
+    db.query(bv, common, first, scores);
+    FILE* out = fopen(argv[6], "wb");
+    if (!out) return 2;
+    int total = 0;
+    for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) total += (int)it->second.size();
+    const int hdr[3] = {(int)bv.size(), (int)fv.size(), total};
+    fwrite(hdr, 4, 3, out);
+    for (DBoW2::BowVector::const_iterator it = bv.begin(); it != bv.end(); ++it) fwrite(&it->first, 4, 1, out);
+    for (DBoW2::BowVector::const_iterator it = bv.begin(); it != bv.end(); ++it) fwrite(&it->second, 8, 1, out);
+    for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) fwrite(&it->first, 4, 1, out);
+    for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+        const int c = (int)it->second.size();
+        fwrite(&c, 4, 1, out);
+        fwrite(it->second.data(), 4, (size_t)c, out);
+    }
+    const double self = voc.score(bv, bv);
+    fwrite(&self, 8, 1, out);
+    fwrite(&common[(size_t)slot], 4, 1, out);
+    fwrite(&scores[(size_t)slot], 8, 1, out);
+    fclose(out);
+    printf("%u words in the vocabulary, %d in the frame\n", voc.size(), hdr[0]);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     try {
@@ -159,10 +206,11 @@ int main(int argc, char** argv)
         if (argc >= 2 && !strcmp(argv[1], "match")) return cmd_match(argc, argv);
         if (argc >= 2 && !strcmp(argv[1], "maxima")) return cmd_maxima();
         if (argc >= 2 && !strcmp(argv[1], "stereo")) return cmd_stereo(argc, argv);
+        if (argc >= 2 && !strcmp(argv[1], "bow")) return cmd_bow(argc, argv);
     } catch (const std::exception& e) {
         fprintf(stderr, "orb_host_cli: %s\n", e.what());     // e.g. no CUDA device: there is no CPU path
         return 3;
     }
-    fprintf(stderr, "usage: orb_host_cli extract|match|maxima|stereo ...\n");
+    fprintf(stderr, "usage: orb_host_cli extract|match|maxima|stereo|bow ...\n");
     return 2;
 }

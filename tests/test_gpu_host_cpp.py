@@ -106,3 +106,39 @@ def test_cpp_stereo_matches_equal_oracle(cli, pkg, oracle, tmp_path):
                                np.float32(bf), np.float32(b))
     assert n == len(kL) and u.tobytes() == ou.tobytes() and d.tobytes() == od.tobytes()
     assert (u >= 0).sum() > 300
+
+
+@pytest.mark.parametrize("name,levelsup", [("k10-depth4", 2), ("ragged", 2), ("ties", 4)])
+def test_cpp_vocabulary_and_bow_database_match_oracle(cli, pkg, tmp_path, name, levelsup):
+    """ORB_SLAM2::ORBVocabulary (loadFromTextFile, both transform overloads, score) and BowDatabase through the CLI, against the
+    restatement of DBoW2 (oracle/vocab_port.cc)"""
+    import oracle_lib
+    import test_vocab as tv
+    t = tv.make_tree(**tv.TREES[name])
+    path = tmp_path / "voc.txt"
+    pkg.write_vocabulary_text(path, t["k"], t["L"], t["parent"], t["is_leaf"], t["desc"], t["weight"], trailing_newline=True)
+    d = tv.features_for(t, 21, 900)
+    raw = tmp_path / "desc.bin"; raw.write_bytes(d.tobytes())
+    out = tmp_path / "bow.bin"
+    r = subprocess.run([cli, "bow", str(path), str(raw), str(len(d)), str(levelsup), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.startswith("%d words in the vocabulary" % int(t["is_leaf"].sum()))
+    buf = out.read_bytes()
+    nw, nn, ni = np.frombuffer(buf, np.int32, 3, 0); off = 12
+    words = np.frombuffer(buf, np.uint32, nw, off); off += 4 * nw
+    values = np.frombuffer(buf, np.float64, nw, off); off += 8 * nw
+    nodes = np.frombuffer(buf, np.uint32, nn, off); off += 4 * nn
+    start, idx = [0], []
+    for _ in range(nn):
+        c = int(np.frombuffer(buf, np.int32, 1, off)[0]); off += 4
+        idx.extend(np.frombuffer(buf, np.uint32, c, off).tolist()); off += 4 * c
+        start.append(len(idx))
+    self_score = np.frombuffer(buf, np.float64, 1, off)[0]; off += 8
+    common = int(np.frombuffer(buf, np.int32, 1, off)[0]); off += 4
+    db_score = np.frombuffer(buf, np.float64, 1, off)[0]
+    port = oracle_lib.PortVocabulary(*tv.vocab_args(t))
+    want = port.transform(d, levelsup)
+    assert tv.same_bow((words, values, nodes, np.array(start, np.int32), np.array(idx, np.uint32)), want)
+    ks = np.array([0, nw], np.int32)
+    s = port.score_csr(want[0], want[1], want[0], want[1], ks)[0]
+    assert self_score == s == db_score and common == nw and abs(s - 1.0) < 1e-12

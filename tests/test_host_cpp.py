@@ -56,7 +56,11 @@ def test_frontend_library_exports_dropin_symbols(cli):
                 "ORB_SLAM2::ORBextractor::operator()(cv::_InputArray const&, cv::_InputArray const&, std::vector<cv::KeyPoint",
                 "ORB_SLAM2::ORBmatcher::DescriptorDistance(cv::Mat const&, cv::Mat const&)",
                 "ORB_SLAM2::ORBmatcher::ORBmatcher(float, bool)",
-                "ORB_SLAM2::ORBmatcher::TH_LOW", "ORB_SLAM2::ORBmatcher::TH_HIGH", "ORB_SLAM2::ORBmatcher::HISTO_LENGTH"):
+                "ORB_SLAM2::ORBmatcher::TH_LOW", "ORB_SLAM2::ORBmatcher::TH_HIGH", "ORB_SLAM2::ORBmatcher::HISTO_LENGTH",
+                "ORB_SLAM2::ORBVocabulary::loadFromTextFile(std::",
+                "ORB_SLAM2::ORBVocabulary::transform(std::vector<cv::Mat",
+                "ORB_SLAM2::ORBVocabulary::score(DBoW2::BowVector const&, DBoW2::BowVector const&) const",
+                "ORB_SLAM2::BowDatabase::add(DBoW2::BowVector const&)", "ORB_SLAM2::BowDatabase::query("):
         assert sym in out, sym
 
 
@@ -68,3 +72,14 @@ def test_extractor_fails_loudly_without_gpu(cli, pkg, tmp_path):
     r = subprocess.run([cli, "extract", str(raw), "64", "64", "500", "1.2", "8", "20", "7", str(tmp_path / "o.bin")],
                        capture_output=True, text=True)
     assert r.returncode == 3 and "orbgpu_create failed" in r.stderr     # no CPU fallback
+
+
+def test_vocabulary_fails_loudly_without_gpu(cli, pkg, tmp_path):
+    if pkg.device_count() > 0:
+        pytest.skip("a CUDA device is visible")
+    voc = tmp_path / "voc.txt"
+    voc.write_text("10 1 0 0\n0 1 " + " ".join(["7"] * 32) + " 1.5")
+    raw = tmp_path / "d.bin"
+    raw.write_bytes(bytes(64))
+    r = subprocess.run([cli, "bow", str(voc), str(raw), "2", "0", str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode == 3 and "orbgpu_vocabulary_load_text" in r.stderr      # no CPU fallback
