@@ -448,6 +448,18 @@ double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m);
  * an empty group (the reference returns without touching mDescriptor). */
 int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* group_start, int n_groups, int32_t* best_idx);
 
+/* MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371), batched over map points: LocalMapping and Tracking call it next to
+ * ComputeDistinctiveDescriptors for every map point a new keyframe touches.  Point g: world position pos[3 g ..], the camera
+ * centres (KeyFrame::GetCameraCenter) of its observing keyframes centers[3 obs_start[g] .. 3 obs_start[g + 1]) in the order the
+ * reference walks its std::map<KeyFrame*, size_t>, its reference keyframe's centre ref_center[3 g ..], ref_scale[g] =
+ * pRefKF->mvScaleFactors[octave of the point's keypoint there], last_scale[g] = pRefKF->mvScaleFactors[mnScaleLevels - 1].
+ * Out: normal[3 g ..] = mNormalVector, max_dist[g] = mfMaxDistance, min_dist[g] = mfMinDistance; a point without
+ * observations keeps the values the three arrays held on entry (the reference returns early, :345-346).  OpenCV 4.13 arithmetic:
+ * cv::norm in double, "normal + normali / norm" as cv::scaleAdd (a fused multiply-add with the scale narrowed to float). */
+int orbgpu_update_normals_and_depths(int device, const float* pos, const int32_t* obs_start, const float* centers,
+                                     const float* ref_center, const float* ref_scale, const float* last_scale, int n_points,
+                                     float* normal, float* max_dist, float* min_dist);
+
 /* ---- bag of words: the DBoW2 vocabulary tree ----------------------------------------------------
  * Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:395-402, src/KeyFrame.cc:59-68) call
  * ORBVocabulary::transform(descriptors, BowVector, FeatureVector, 4)

@@ -153,6 +153,71 @@ struct orbgpu_matcher {
     double last_ms = 0;
 };
 
+// MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371), one thread per map point: the mean viewing direction is a float
+// accumulation in observation order, so a point's walk stays serial while the points run in parallel.  OpenCV's arithmetic:
+// cv::norm in double, "normal + normali / norm" = cv::scaleAdd = fmaf(v, (float)(1.0 / norm), acc), "normal / n" = v * (float)(1.0 / n).
+__global__ void __launch_bounds__(128) k_update_normals(const float* __restrict__ pos, const int* __restrict__ obs_start,
+                                                        const float* __restrict__ centers, const float* __restrict__ ref_center,
+                                                        const float* __restrict__ ref_scale, const float* __restrict__ last_scale,
+                                                        int n_points, float* __restrict__ normal, float* __restrict__ max_dist,
+                                                        float* __restrict__ min_dist)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_points) return;
+    const int b = obs_start[g], e = obs_start[g + 1];
+    if (e <= b) return;                                                           // observations.empty(): nothing changes (:345-346)
+    const float px = pos[3 * g], py = pos[3 * g + 1], pz = pos[3 * g + 2];
+    float ax = 0.f, ay = 0.f, az = 0.f;
+    for (int j = b; j < e; ++j) {
+        const float vx = __fsub_rn(px, __ldg(centers + 3 * (size_t)j)), vy = __fsub_rn(py, __ldg(centers + 3 * (size_t)j + 1)),
+                    vz = __fsub_rn(pz, __ldg(centers + 3 * (size_t)j + 2));
+        const double nrm = sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)vx, (double)vx), __dmul_rn((double)vy, (double)vy)),
+                                          __dmul_rn((double)vz, (double)vz)));
+        const float a = (float)(1.0 / nrm);
+        ax = __fmaf_rn(vx, a, ax); ay = __fmaf_rn(vy, a, ay); az = __fmaf_rn(vz, a, az);
+    }
+    const float cx = __fsub_rn(px, ref_center[3 * g]), cy = __fsub_rn(py, ref_center[3 * g + 1]), cz = __fsub_rn(pz, ref_center[3 * g + 2]);
+    const float dist = (float)sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)cx, (double)cx), __dmul_rn((double)cy, (double)cy)),
+                                             __dmul_rn((double)cz, (double)cz)));
+    const float mx = __fmul_rn(dist, ref_scale[g]);
+    max_dist[g] = mx;
+    min_dist[g] = __fdiv_rn(mx, last_scale[g]);
+    const float inv_n = (float)(1.0 / (double)(e - b));
+    normal[3 * g] = __fmul_rn(ax, inv_n); normal[3 * g + 1] = __fmul_rn(ay, inv_n); normal[3 * g + 2] = __fmul_rn(az, inv_n);
+}
+
+// Per-thread scratch of the stateless entry points (device block + pinned mirror + stream), grown on demand and kept: no
+// cudaMalloc / cudaFree and no pageable copies on the call path.
+namespace {
+struct MatchScratch {
+    int device = -1;
+    size_t cap = 0;
+    uint8_t* d = nullptr;
+    uint8_t* h = nullptr;
+    cudaStream_t st = nullptr;
+    int ensure(int dev, size_t bytes)
+    {
+        if (dev != device) {
+            if (device >= 0) { cudaSetDevice(device); cudaFree(d); cudaFreeHost(h); if (st) cudaStreamDestroy(st); }
+            d = nullptr; h = nullptr; st = nullptr; cap = 0; device = -1;
+            CUM(cudaSetDevice(dev));
+            CUM(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            device = dev;
+        }
+        CUM(cudaSetDevice(dev));
+        if (bytes <= cap) return ORBGPU_OK;
+        cudaFree(d); cudaFreeHost(h); d = nullptr; h = nullptr; cap = 0;
+        const size_t want = (bytes + bytes / 2 + 65535) & ~(size_t)65535;
+        CUM(cudaMalloc(&d, want));
+        CUM(cudaHostAlloc(&h, want, cudaHostAllocDefault));
+        cap = want;
+        return ORBGPU_OK;
+    }
+};
+thread_local MatchScratch g_scratch;
+inline size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+}  // namespace
+
 extern "C" {
 
 int orbgpu_hamming256(const void* a, const void* b)
@@ -168,19 +233,23 @@ int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t*
 {
     if (!A || !B || !best_idx || !best || !second || nA < 1 || nB < 0) return ORBGPU_ERR_ARG;
     if (nB >= (1 << 22) - 1) return ORBGPU_ERR_UNSUPPORTED;   // candidate index is packed into 22 bits
-    CUM(cudaSetDevice(device));
-    uint4 *dA = nullptr, *dB = nullptr; int32_t* di = nullptr; uint16_t *d1 = nullptr, *d2 = nullptr;
-    CUM(cudaMalloc(&dA, 32 * (size_t)nA));
-    CUM(cudaMalloc(&dB, 32 * (size_t)(nB > 0 ? nB : 1)));
-    CUM(cudaMalloc(&di, 4 * (size_t)nA)); CUM(cudaMalloc(&d1, 2 * (size_t)nA)); CUM(cudaMalloc(&d2, 2 * (size_t)nA));
-    CUM(cudaMemcpy(dA, A, 32 * (size_t)nA, cudaMemcpyHostToDevice));
-    if (nB > 0) CUM(cudaMemcpy(dB, B, 32 * (size_t)nB, cudaMemcpyHostToDevice));
-    k_match_bruteforce<<<(nA + MATCH_THREADS - 1) / MATCH_THREADS, MATCH_THREADS>>>(dA, nA, dB, nB, di, d1, d2);
+    const size_t o_a = 0, o_b = up256(32 * (size_t)nA), o_i = up256(o_b + 32 * (size_t)nB), o_1 = up256(o_i + 4 * (size_t)nA),
+                 o_2 = up256(o_1 + 2 * (size_t)nA), total = up256(o_2 + 2 * (size_t)nA);
+    MatchScratch& S = g_scratch;
+    const int rc = S.ensure(device, total);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(S.h + o_a, A, 32 * (size_t)nA);
+    if (nB > 0) memcpy(S.h + o_b, B, 32 * (size_t)nB);
+    CUM(cudaMemcpyAsync(S.d, S.h, o_b + 32 * (size_t)nB, cudaMemcpyHostToDevice, S.st));
+    k_match_bruteforce<<<(nA + MATCH_THREADS - 1) / MATCH_THREADS, MATCH_THREADS, 0, S.st>>>(
+        reinterpret_cast<const uint4*>(S.d + o_a), nA, reinterpret_cast<const uint4*>(S.d + o_b), nB,
+        reinterpret_cast<int32_t*>(S.d + o_i), reinterpret_cast<uint16_t*>(S.d + o_1), reinterpret_cast<uint16_t*>(S.d + o_2));
     CUM(cudaGetLastError());
-    CUM(cudaMemcpy(best_idx, di, 4 * (size_t)nA, cudaMemcpyDeviceToHost));
-    CUM(cudaMemcpy(best, d1, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
-    CUM(cudaMemcpy(second, d2, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
-    cudaFree(dA); cudaFree(dB); cudaFree(di); cudaFree(d1); cudaFree(d2);
+    CUM(cudaMemcpyAsync(S.h + o_i, S.d + o_i, total - o_i, cudaMemcpyDeviceToHost, S.st));
+    CUM(cudaStreamSynchronize(S.st));
+    memcpy(best_idx, S.h + o_i, 4 * (size_t)nA);
+    memcpy(best, S.h + o_1, 2 * (size_t)nA);
+    memcpy(second, S.h + o_2, 2 * (size_t)nA);
     return ORBGPU_OK;
 }
 
@@ -201,27 +270,57 @@ int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_
         CUM(cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    uint8_t* d = nullptr;
-    const size_t b_desc = ((size_t)32 * (size_t)(total > 0 ? total : 1) + 255) & ~(size_t)255;
-    const size_t b_gs = ((size_t)4 * (size_t)(n_groups + 1) + 255) & ~(size_t)255, b_out = (size_t)4 * (size_t)n_groups;
-    CUM(cudaMalloc(&d, b_desc + b_gs + b_out));
-    cudaError_t e = cudaSuccess;
-    if (total > 0) e = cudaMemcpy(d, desc, (size_t)32 * total, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(d + b_desc, group_start, (size_t)4 * (n_groups + 1), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) {
-        k_distinctive<<<(n_groups + DD_WARPS - 1) / DD_WARPS, DD_WARPS * 32, smem>>>(reinterpret_cast<const uint4*>(d),
-                                                                                     reinterpret_cast<const int*>(d + b_desc), n_groups,
-                                                                                     reinterpret_cast<int*>(d + b_desc + b_gs));
-        e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpy(best_idx, d + b_desc + b_gs, b_out, cudaMemcpyDeviceToHost);
-    cudaFree(d);
-    if (e != cudaSuccess) {
-        char b[256];
-        snprintf(b, sizeof(b), "orbgpu_distinctive_descriptors: %s", cudaGetErrorString(e));
-        orbgpu_internal_set_error(b);
-        return ORBGPU_ERR_CUDA;
-    }
+    const size_t o_gs = up256((size_t)32 * (size_t)total), o_out = up256(o_gs + (size_t)4 * (size_t)(n_groups + 1)),
+                 bytes = up256(o_out + (size_t)4 * (size_t)n_groups);
+    MatchScratch& S = g_scratch;
+    const int rc = S.ensure(device, bytes);
+    if (rc != ORBGPU_OK) return rc;
+    if (total > 0) memcpy(S.h, desc, (size_t)32 * total);
+    memcpy(S.h + o_gs, group_start, (size_t)4 * (n_groups + 1));
+    CUM(cudaMemcpyAsync(S.d, S.h, o_gs + (size_t)4 * (n_groups + 1), cudaMemcpyHostToDevice, S.st));
+    k_distinctive<<<(n_groups + DD_WARPS - 1) / DD_WARPS, DD_WARPS * 32, smem, S.st>>>(reinterpret_cast<const uint4*>(S.d),
+                                                                                       reinterpret_cast<const int*>(S.d + o_gs), n_groups,
+                                                                                       reinterpret_cast<int*>(S.d + o_out));
+    CUM(cudaGetLastError());
+    CUM(cudaMemcpyAsync(S.h + o_out, S.d + o_out, (size_t)4 * n_groups, cudaMemcpyDeviceToHost, S.st));
+    CUM(cudaStreamSynchronize(S.st));
+    memcpy(best_idx, S.h + o_out, (size_t)4 * n_groups);
+    return ORBGPU_OK;
+}
+
+int orbgpu_update_normals_and_depths(int device, const float* pos, const int32_t* obs_start, const float* centers,
+                                     const float* ref_center, const float* ref_scale, const float* last_scale, int n_points,
+                                     float* normal, float* max_dist, float* min_dist)
+{
+    if (n_points < 0) return ORBGPU_ERR_ARG;
+    if (n_points == 0) return ORBGPU_OK;
+    if (!pos || !obs_start || !ref_center || !ref_scale || !last_scale || !normal || !max_dist || !min_dist) return ORBGPU_ERR_ARG;
+    const int total = obs_start[n_points];
+    if (obs_start[0] != 0 || total < 0 || (total > 0 && !centers)) return ORBGPU_ERR_ARG;
+    for (int g = 0; g < n_points; ++g)
+        if (obs_start[g + 1] < obs_start[g]) return ORBGPU_ERR_ARG;
+    const size_t np = (size_t)n_points;
+    // inputs: pos | ref_center | ref_scale | last_scale | obs_start | centers; in/out: normal | max | min
+    const size_t o_pos = 0, o_rc = up256(12 * np), o_rs = up256(o_rc + 12 * np), o_ls = up256(o_rs + 4 * np), o_os = up256(o_ls + 4 * np),
+                 o_c = up256(o_os + 4 * (np + 1)), o_n = up256(o_c + 12 * (size_t)total), o_mx = up256(o_n + 12 * np),
+                 o_mn = up256(o_mx + 4 * np), bytes = up256(o_mn + 4 * np);
+    MatchScratch& S = g_scratch;
+    const int rc = S.ensure(device, bytes);
+    if (rc != ORBGPU_OK) return rc;
+    memcpy(S.h + o_pos, pos, 12 * np); memcpy(S.h + o_rc, ref_center, 12 * np);
+    memcpy(S.h + o_rs, ref_scale, 4 * np); memcpy(S.h + o_ls, last_scale, 4 * np);
+    memcpy(S.h + o_os, obs_start, 4 * (np + 1));
+    if (total > 0) memcpy(S.h + o_c, centers, 12 * (size_t)total);
+    memcpy(S.h + o_n, normal, 12 * np); memcpy(S.h + o_mx, max_dist, 4 * np); memcpy(S.h + o_mn, min_dist, 4 * np);
+    CUM(cudaMemcpyAsync(S.d, S.h, bytes, cudaMemcpyHostToDevice, S.st));
+    k_update_normals<<<(n_points + 127) / 128, 128, 0, S.st>>>(
+        reinterpret_cast<const float*>(S.d + o_pos), reinterpret_cast<const int*>(S.d + o_os), reinterpret_cast<const float*>(S.d + o_c),
+        reinterpret_cast<const float*>(S.d + o_rc), reinterpret_cast<const float*>(S.d + o_rs), reinterpret_cast<const float*>(S.d + o_ls),
+        n_points, reinterpret_cast<float*>(S.d + o_n), reinterpret_cast<float*>(S.d + o_mx), reinterpret_cast<float*>(S.d + o_mn));
+    CUM(cudaGetLastError());
+    CUM(cudaMemcpyAsync(S.h + o_n, S.d + o_n, bytes - o_n, cudaMemcpyDeviceToHost, S.st));
+    CUM(cudaStreamSynchronize(S.st));
+    memcpy(normal, S.h + o_n, 12 * np); memcpy(max_dist, S.h + o_mx, 4 * np); memcpy(min_dist, S.h + o_mn, 4 * np);
     return ORBGPU_OK;
 }
 

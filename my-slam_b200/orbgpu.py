@@ -330,6 +330,7 @@ def lib():
         "orbgpu_bowdb_clear": (i32, [vp]),
         "orbgpu_bowdb_size": (i32, [vp]),
         "orbgpu_bowdb_query": (i32, [vp, vp, vp, i32, vp, vp, vp]),
+        "orbgpu_update_normals_and_depths": (i32, [i32, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
@@ -907,3 +908,16 @@ class KeyFrameDatabase:
     def detect_relocalization_candidates(self, query, neighbours):
         """DetectRelocalizationCandidates(F) (:199-309) -> candidate slots"""
         return self._detect(query, True, None, neighbours, 0.0)[2]
+
+
+def update_normals_and_depths(pos, obs_start, centers, ref_center, ref_scale, last_scale, normal, max_dist, min_dist, device=0):
+    """MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371) for many map points at once -> (normal (n x 3), max_dist, min_dist);
+    the three last inputs are the values before the call (kept for points without observations)."""
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3); n = len(pos)
+    os_ = np.ascontiguousarray(obs_start, np.int32); c = np.ascontiguousarray(centers, np.float32).reshape(-1, 3)
+    rc = np.ascontiguousarray(ref_center, np.float32).reshape(-1, 3)
+    rs = np.ascontiguousarray(ref_scale, np.float32); ls = np.ascontiguousarray(last_scale, np.float32)
+    nv = np.array(normal, np.float32).reshape(-1, 3).copy(); mx = np.array(max_dist, np.float32).copy(); mn = np.array(min_dist, np.float32).copy()
+    _check(lib().orbgpu_update_normals_and_depths(device, _p(pos), _p(os_), _p(c) if len(c) else None, _p(rc), _p(rs), _p(ls), n,
+                                                  _p(nv), _p(mx), _p(mn)))
+    return nv, mx, mn

@@ -3,6 +3,7 @@
 // undistortPoints come from oracle/orb_prims.c (pinned to cv2 4.13.0 golden vectors); cv::gemm / norm / MatExpr
 // evaluation are restated here from OpenCV 4.13 (modules/core/src/matmul.simd.hpp gemmImpl + GEMMSingleMul,
 // matrix_expressions.cpp MatOp_GEMM / MatOp_T / MatOp_AddEx, norm.cpp) and checked against cv2 golden vectors.
+#include <cmath>
 #include "opencv2/core/core.hpp"
 #include "../orb_prims.h"
 #include <cstdio>
@@ -378,6 +379,21 @@ MatExpr operator+(const MatExpr& e, const Mat& m)
     if (e.kind == MatExpr::GEMM && e.c.empty()) {   // MatOp_GEMM::add: alpha*A*B + 1*C
         MatExpr n = e;
         n.c = m; n.beta = 1;
+        return n;
+    }
+    if (e.kind == MatExpr::SCALED && e.alpha != 1 && e.alpha != -1 && !e.a.empty()) {
+        // MatOp::add folds "alpha * A" and a plain matrix into MatOp_AddEx(A, alpha, M, 1); its assign() then calls
+        // cv::scaleAdd(A, alpha, M): alpha narrowed to float, one fused multiply-add per element (OpenCV 4.13.0 as
+        // installed: cv2.scaleAdd golden vectors, tests/golden/scale_add_golden.npz)
+        if (e.a.depth() != CV_32F || m.depth() != CV_32F || e.a.rows != m.rows || e.a.cols != m.cols)
+            unreachable("scaleAdd on mismatching matrices");
+        Mat o;
+        o.create(m.rows, m.cols, m.type());
+        const float af = (float)e.alpha;
+        for (int y = 0; y < m.rows; ++y)
+            for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = std::fmaf(e.a.at<float>(y, x), af, m.at<float>(y, x));
+        MatExpr n;
+        n.kind = MatExpr::SCALED; n.a = o; n.alpha = 1;
         return n;
     }
     MatExpr n;

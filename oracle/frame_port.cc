@@ -933,3 +933,32 @@ extern "C" int frameport_search_by_sim3(const frameport_fuse_args* a12, const fr
     }
     return nFound;
 }
+
+// MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371) in OpenCV's arithmetic: "mWorldPos - Owi" in float; cv::norm
+// accumulates squares in double; "normal + normali / norm" is MatOp_AddEx -> cv::scaleAdd(normali, 1.0 / norm, normal) =
+// fmaf(v, (float)(1.0 / norm), acc) (pinned: tests/golden/scale_add_golden.npz); "normal / n" is v * (float)(1.0 / n).
+extern "C" void frameport_update_normal_and_depth(const float* pos, const int32_t* obs_start, const float* centers,
+                                                  const float* ref_center, const float* ref_scale, const float* last_scale,
+                                                  int n_points, float* normal, float* max_dist, float* min_dist)
+{
+    for (int g = 0; g < n_points; ++g) {
+        const int b = obs_start[g], e = obs_start[g + 1];
+        if (e <= b) continue;                                                     // observations.empty(): return (:345-346)
+        const float* P = pos + 3 * (size_t)g;
+        float acc[3] = {0.f, 0.f, 0.f};
+        for (int j = b; j < e; ++j) {
+            const float* O = centers + 3 * (size_t)j;
+            const float v[3] = {P[0] - O[0], P[1] - O[1], P[2] - O[2]};
+            const double nrm = std::sqrt((double)v[0] * (double)v[0] + (double)v[1] * (double)v[1] + (double)v[2] * (double)v[2]);
+            const float a = (float)(1.0 / nrm);
+            for (int k = 0; k < 3; ++k) acc[k] = std::fmaf(v[k], a, acc[k]);
+        }
+        const float* R = ref_center + 3 * (size_t)g;
+        const float pc[3] = {P[0] - R[0], P[1] - R[1], P[2] - R[2]};
+        const float dist = (float)std::sqrt((double)pc[0] * (double)pc[0] + (double)pc[1] * (double)pc[1] + (double)pc[2] * (double)pc[2]);
+        max_dist[g] = dist * ref_scale[g];
+        min_dist[g] = max_dist[g] / last_scale[g];
+        const float inv_n = (float)(1.0 / (double)(e - b));
+        for (int k = 0; k < 3; ++k) normal[3 * (size_t)g + k] = acc[k] * inv_n;
+    }
+}

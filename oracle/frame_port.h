@@ -197,6 +197,15 @@ typedef struct {
  * score[i] = mLoopScore / mRelocScore after the call; returns the number of candidates written (keyframe numbers, in order) */
 int frameport_db_detect(const frameport_db_args* a, int32_t* marked, int32_t* words, float* score, int32_t* candidates);
 
+/* MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371), batched over map points.  Point g owns the camera centres
+ * centers[3 * obs_start[g] .. 3 * obs_start[g + 1]) of its observing keyframes, in the order the reference walks them (its
+ * std::map<KeyFrame*, size_t>); ref_center / ref_scale / last_scale: the reference keyframe's camera centre,
+ * mvScaleFactors[octave of the point's keypoint there] and mvScaleFactors[mnScaleLevels - 1].  Points without observations
+ * keep normal / max_dist / min_dist as they came in. */
+void frameport_update_normal_and_depth(const float* pos, const int32_t* obs_start, const float* centers, const float* ref_center,
+                                       const float* ref_scale, const float* last_scale, int n_points, float* normal,
+                                       float* max_dist, float* min_dist);
+
 #ifdef __cplusplus
 }
 #endif

@@ -224,6 +224,17 @@ void frameref_mat_div(const float* v, int n, float s, float* out)
     std::memcpy(out, R.data, sizeof(float) * (size_t)n);
 }
 
+// "acc + v / s" for CV_32F vectors, as MapPoint::UpdateNormalAndDepth forms it (src/MapPoint.cc:355): the shim's MatExpr
+// lowering (MatOp_AddEx -> cv::scaleAdd), checked against cv2 golden vectors
+void frameref_mat_add_div(const float* acc, const float* v, int n, double s, float* out)
+{
+    cv::Mat A(n, 1, CV_32F), V(n, 1, CV_32F);
+    std::memcpy(A.data, acc, sizeof(float) * (size_t)n);
+    std::memcpy(V.data, v, sizeof(float) * (size_t)n);
+    cv::Mat R = A + V / s;
+    std::memcpy(out, R.data, sizeof(float) * (size_t)n);
+}
+
 int frameref_features_in_area(const KP* keys_un, int n, const float* bounds4, float x, float y, float r, int min_level,
                               int max_level, int* out, int cap)
 {
@@ -899,4 +910,52 @@ extern "C" int frameref_db_detect(void* voc, const frameport_db_args* a, int32_t
     for (size_t i = 0; i < got.size(); ++i)
         candidates[i] = (int32_t)(std::find(kfs.begin(), kfs.end(), got[i]) - kfs.begin());
     return (int)got.size();
+}
+
+// MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371) executed by the reference on a pool of keyframes sorted by
+// address (the order of its std::map<KeyFrame*, size_t>): keyframe j of a point's walk gets that observation's camera
+// centre, keyframe `ref_slot[g]` of the walk is the point's reference keyframe.
+extern "C" void frameref_update_normal_and_depth(const float* pos, const int32_t* obs_start, const float* centers,
+                                                 const int32_t* ref_slot, const int32_t* ref_level, const float* scale_factors,
+                                                 int n_levels, int n_points, float* normal, float* max_dist, float* min_dist)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, 1.f, 1.f, 0.f, 0.f);
+    World world;
+    int nmax = 0;
+    for (int g = 0; g < n_points; ++g) nmax = std::max(nmax, obs_start[g + 1] - obs_start[g]);
+    std::vector<KeyFrame*> pool;
+    for (int j = 0; j < nmax; ++j) {
+        Frame F;
+        F.N = 0; F.mTcw = cv::Mat::eye(4, 4, CV_32F); F.mnId = (unsigned long)(j + 1);
+        F.mbf = 1.f; F.mb = 1.f; F.mThDepth = 1.f; F.mTimeStamp = 0;
+        F.mnScaleLevels = n_levels; F.mfScaleFactor = scale_factors[1]; F.mfLogScaleFactor = std::log(scale_factors[1]);
+        F.mvScaleFactors.assign(scale_factors, scale_factors + n_levels);
+        F.mvKeysUn.resize(1);
+        KeyFrame* kf = new KeyFrame(F, &world.map, static_cast<KeyFrameDatabase*>(NULL));
+        world.keyframes.push_back(kf);
+        pool.push_back(kf);
+    }
+    std::sort(pool.begin(), pool.end());
+    for (int g = 0; g < n_points; ++g) {
+        const int N = obs_start[g + 1] - obs_start[g];
+        MapPoint* p = world.point(pos + 3 * (size_t)g, 0, N, false);
+        p->mObservations.clear();
+        p->mNormalVector = cv::Mat(3, 1, CV_32F);
+        std::memcpy(p->mNormalVector.data, normal + 3 * (size_t)g, 12);
+        p->mfMaxDistance = max_dist[g]; p->mfMinDistance = min_dist[g];
+        for (int j = 0; j < N; ++j) {
+            cv::Mat ow(3, 1, CV_32F);
+            std::memcpy(ow.data, centers + 3 * (size_t)(obs_start[g] + j), 12);
+            pool[j]->Ow = ow;
+            p->mObservations[pool[j]] = 0;
+        }
+        if (N > 0) {
+            p->mpRefKF = pool[ref_slot[g]];
+            const_cast<std::vector<cv::KeyPoint>&>(p->mpRefKF->mvKeysUn)[0].octave = ref_level[g];
+        }
+        p->UpdateNormalAndDepth();
+        std::memcpy(normal + 3 * (size_t)g, p->mNormalVector.data, 12);
+        max_dist[g] = p->mfMaxDistance; min_dist[g] = p->mfMinDistance;
+    }
 }

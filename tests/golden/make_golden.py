@@ -256,7 +256,27 @@ def make_scale():
     print("scale_golden.npz written")
 
 
+def make_scale_add():
+    """cv::scaleAdd(v, 1 / s, acc) on CV_32F vectors: what "acc + v / s" lowers to in MapPoint::UpdateNormalAndDepth
+    (src/MapPoint.cc:355, through MatOp_AddEx::assign).  s is a double (cv::norm's result there)."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(777)
+    n = 4000
+    v = rng.normal(0, 3, (n, 3)).astype(np.float32); acc = rng.normal(0, 2, (n, 3)).astype(np.float32)
+    s = np.sqrt((v.astype(np.float64) ** 2).sum(1))
+    s[::7] = rng.uniform(0.3, 9.0, len(s[::7]))
+    out = np.zeros((n, 3), np.float32)
+    for i in range(n):
+        out[i] = cv2.scaleAdd(v[i].reshape(3, 1), 1.0 / s[i], acc[i].reshape(3, 1)).reshape(3)
+    np.savez_compressed(os.path.join(HERE, "scale_add_golden.npz"), v=v, acc=acc, s=s, out=out)
+    print("scale_add_golden.npz written")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "scale_add":
+        make_scale_add()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gemm":
         make_gemm()
         sys.exit(0)

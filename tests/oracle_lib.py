@@ -483,6 +483,26 @@ class OracleFrameRef:
         self.L.frameref_mat_div(_ptr(v), len(v), float(s), _ptr(out))
         return out
 
+    def mat_add_div(self, acc, v, s):
+        """cv::Mat(acc) + cv::Mat(v) / s (s a double) through the shim's MatExpr lowering (cv::scaleAdd)."""
+        acc = np.ascontiguousarray(acc, np.float32); v = np.ascontiguousarray(v, np.float32); out = np.zeros_like(v)
+        self.L.frameref_mat_add_div.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p]
+        self.L.frameref_mat_add_div.restype = None
+        self.L.frameref_mat_add_div(_ptr(acc), _ptr(v), len(v), float(s), _ptr(out))
+        return out
+
+    def update_normal_and_depth(self, pos, obs_start, centers, ref_slot, ref_level, scale_factors, normal, max_dist, min_dist):
+        """MapPoint::UpdateNormalAndDepth executed by the reference, point by point"""
+        pos = np.ascontiguousarray(pos, np.float32); os_ = np.ascontiguousarray(obs_start, np.int32)
+        c = np.ascontiguousarray(centers, np.float32); rs = np.ascontiguousarray(ref_slot, np.int32); rl = np.ascontiguousarray(ref_level, np.int32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        nv = np.array(normal, np.float32).copy(); mx = np.array(max_dist, np.float32).copy(); mn = np.array(min_dist, np.float32).copy()
+        f = self.L.frameref_update_normal_and_depth
+        f.argtypes = [C.c_void_p] * 6 + [C.c_int, C.c_int] + [C.c_void_p] * 3
+        f.restype = None
+        f(_ptr(pos), _ptr(os_), _ptr(c), _ptr(rs), _ptr(rl), _ptr(sf), len(sf), len(os_) - 1, _ptr(nv), _ptr(mx), _ptr(mn))
+        return nv, mx, mn
+
     def fuse_search_sim3(self, args, Scw):
         S = np.ascontiguousarray(Scw, np.float32).reshape(16); best = _i32(args.n_points)
         self.L.frameref_fuse_search_sim3(C.byref(args), _ptr(S), _ptr(best))
@@ -678,3 +698,17 @@ def ref_db_detect(ref_vocab, args):
     lib = ref_vocab.L
     lib.frameref_db_detect.argtypes = [C.c_void_p] * 6
     return _db_detect(lib.frameref_db_detect, args.n_kf, ref_vocab.h, C.byref(args))
+
+
+def port_update_normal_and_depth(pos, obs_start, centers, ref_center, ref_scale, last_scale, normal, max_dist, min_dist):
+    """oracle/frame_port.cc:frameport_update_normal_and_depth"""
+    lib = C.CDLL(PORT_SO)
+    f = lib.frameport_update_normal_and_depth
+    f.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 3
+    f.restype = None
+    pos = np.ascontiguousarray(pos, np.float32); os_ = np.ascontiguousarray(obs_start, np.int32)
+    c = np.ascontiguousarray(centers, np.float32); rc = np.ascontiguousarray(ref_center, np.float32)
+    rs = np.ascontiguousarray(ref_scale, np.float32); ls = np.ascontiguousarray(last_scale, np.float32)
+    nv = np.array(normal, np.float32).copy(); mx = np.array(max_dist, np.float32).copy(); mn = np.array(min_dist, np.float32).copy()
+    f(_ptr(pos), _ptr(os_), _ptr(c), _ptr(rc), _ptr(rs), _ptr(ls), len(os_) - 1, _ptr(nv), _ptr(mx), _ptr(mn))
+    return nv, mx, mn

@@ -138,6 +138,13 @@ def main():
     out["search_by_sim3_%dx%d" % (a12.n_points, a21.n_points)] = {
         "gpu_ms": med(lambda: pkg.search_by_sim3(a12, a21, s12, R12, t12)), "cpu_ms": med(lambda: po.search_by_sim3(a12, a21, s12, R12, t12)),
         "nfound": a[0]}
+    # --- MapPoint::UpdateNormalAndDepth for 2000 map points (about 10 observations each)
+    import test_normals as tn
+    sn = tn.scene(3, 2000, 20)
+    nargs = (sn["pos"], sn["start"], sn["centers"], sn["ref_center"], sn["ref_scale"], sn["last_scale"], sn["normal"], sn["maxd"], sn["mind"])
+    assert tn.same(pkg.update_normals_and_depths(*nargs), oracle_lib.port_update_normal_and_depth(*nargs))
+    out["update_normal_and_depth_2000_points_%d_observations" % int(sn["start"][-1])] = {
+        "gpu_ms": med(lambda: pkg.update_normals_and_depths(*nargs)), "cpu_ms": med(lambda: oracle_lib.port_update_normal_and_depth(*nargs), 10, 1)}
     # --- Frame::ComputeBoW on a vocabulary of ORBvoc.txt's shape (k = 10, L = 6: 1 111 111 nodes, 10^6 words), and the L1 score
     #     of one BowVector against 2000 keyframes (KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates)
     import test_vocab as tv

@@ -80,6 +80,20 @@ def test_shim_mat_div_equals_cv2_golden(ref):
     assert other > 1000
 
 
+def test_shim_mat_add_div_equals_cv2_golden(ref):
+    """"acc + v / s" (src/MapPoint.cc:355) = cv::scaleAdd(v, 1 / s, acc): fmaf(v, (float)(1.0 / s), acc), as cv2 4.13.0
+    computes it (tests/golden/scale_add_golden.npz); an unfused multiply-then-add differs for about half of the vectors."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "scale_add_golden.npz"))
+    v, acc, s, out = g["v"], g["acc"], g["s"], g["out"]
+    other = 0
+    for i in range(len(s)):
+        got = ref.mat_add_div(acc[i], v[i], s[i])
+        assert got.tobytes() == out[i].tobytes()
+        other += (v[i] * np.float32(1.0 / s[i]) + acc[i]).astype(np.float32).tobytes() != out[i].tobytes()
+    assert other > 1000
+
+
 # ------------------------------------------------------------------------------------------------ M1 / M3: host pieces
 def test_descriptor_distance_and_three_maxima_equal_reference(ref, port):
     """ORBmatcher::DescriptorDistance (the reference's SWAR popcount) and ComputeThreeMaxima executed by the reference,
