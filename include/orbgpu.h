@@ -365,6 +365,12 @@ typedef struct orbgpu_triangulation_args {
 /* matches12[kf1.n] = vMatches12 after the rotation check (vMatchedPairs = the pairs (i, matches12[i]) with matches12[i]
  * >= 0, ascending i); *nmatches = the return value. */
 int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* args, int32_t* matches12, int* nmatches);
+/* The same for n_pairs keyframe pairs in one call: LocalMapping::CreateNewMapPoints runs the search once per neighbouring
+ * keyframe (src/LocalMapping.cc:215-252), each an independent problem.  Uploads, kernels and downloads of all pairs are
+ * enqueued back to back and waited for once.  Pair p writes kf1.n entries of matches12 right after those of pair p - 1
+ * and nmatches[p]. */
+int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation_args* args, int n_pairs, int32_t* matches12,
+                                          int* nmatches);
 
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),

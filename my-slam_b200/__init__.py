@@ -9,7 +9,7 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      ProjectionArgs, projection_args, search_for_initialization, search_by_projection,
                      BowSide, bow_side, search_by_bow,
                      LocalPointsArgs, local_points_args, search_local_points,
-                     TriangulationArgs, triangulation_args, search_for_triangulation,
+                     TriangulationArgs, triangulation_args, search_for_triangulation, search_for_triangulation_batch,
                      LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf,
                      FuseArgs, fuse_args, fuse_search,
                      RelocProjectionArgs, reloc_projection_args, search_by_projection_keyframe, distinctive_descriptors,

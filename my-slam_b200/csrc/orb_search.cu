@@ -1624,8 +1624,22 @@ int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projecti
     return ORBGPU_OK;
 }
 
-int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* a, int32_t* matches12, int* nmatches)
+// One SearchForTriangulation problem, split so that several (LocalMapping::CreateNewMapPoints runs one per neighbouring
+// keyframe, src/LocalMapping.cc:215-252) can be enqueued back to back on the workspace stream and waited for once.
+struct TriJob {
+    const orbgpu_triangulation_args* a = nullptr;
+    std::vector<BowQuery> hq;
+    TriCam C;
+    int nq = 0;
+    size_t base = 0, bytes = 0, in_bytes = 0;        // region inside the workspace
+    size_t o_k1, o_d1, o_u1, o_k2, o_d2, o_u2, o_m2, o_i2, o_q, o_sc, o_sg, o_m12;
+};
+
+// validation, the merge walk over the two FeatureVectors, the epipole; lays the job's region out
+static int tri_prepare(TriJob& J, int32_t* matches12, int* nmatches)
 {
+    const orbgpu_triangulation_args* a = J.a;
+    std::vector<BowQuery>& hq = J.hq;
     if (!a || !matches12 || !nmatches || a->nlevels < 1 || !a->scale_factors2 || !a->level_sigma2) return ORBGPU_ERR_ARG;
     const orbgpu_triangulation_side* S[2] = {&a->kf1, &a->kf2};
     for (int k = 0; k < 2; ++k) {
@@ -1645,7 +1659,6 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
     *nmatches = 0;
     for (int i = 0; i < n1; ++i) matches12[i] = -1;
     // the merge walk over the two FeatureVectors (:689-696, :782-789) -> queries in visiting order
-    std::vector<BowQuery> hq;
     int it1 = 0, it2 = 0;
     while (it1 != s1.n_nodes && it2 != s2.n_nodes) {
         if (s1.node_ids[it1] == s2.node_ids[it2]) {
@@ -1664,12 +1677,12 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
             while (it2 != s2.n_nodes && s2.node_ids[it2] < s1.node_ids[it1]) ++it2;
         }
     }
-    const int nq = (int)hq.size();
-    if (nq == 0) return ORBGPU_OK;
+    J.nq = (int)hq.size();
+    if (J.nq == 0) return ORBGPU_OK;
     const int nidx2 = s2.node_start[s2.n_nodes];
     if (nidx2 > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;
+    TriCam& C = J.C;
     // epipole of pKF1's centre in pKF2 (:664-670): C2 = R2w*Cw + t2w is cv::gemm's 3x3 float case
-    TriCam C;
     float C2[3];
     for (int r = 0; r < 3; ++r) {
         volatile float t = a->T2w[4 * r] * a->Cw1[0];          // (volatile: keep the host compiler from contracting)
@@ -1687,38 +1700,57 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
     C.only_stereo = a->only_stereo ? 1 : 0;
 
     Layout L;
-    const size_t o_k1 = L.add(sizeof(orbgpu_keypoint) * (size_t)n1), o_d1 = L.add(32 * (size_t)n1), o_u1 = L.add(4 * (size_t)n1);
-    const size_t o_k2 = L.add(sizeof(orbgpu_keypoint) * (size_t)n2), o_d2 = L.add(32 * (size_t)n2), o_u2 = L.add(4 * (size_t)n2);
-    const size_t o_m2 = L.add((size_t)n2), o_i2 = L.add(4 * (size_t)nidx2), o_q = L.add(sizeof(BowQuery) * (size_t)nq);
-    const size_t o_sc = L.add(4 * (size_t)a->nlevels), o_sg = L.add(4 * (size_t)a->nlevels);
-    const size_t in_bytes = L.off;
-    const size_t o_m12 = L.add(4 * (size_t)n1);
-    const size_t io_bytes = L.off;
-    Workspace& W = g_ws;
-    int rc = W.reserve(device, L.off, io_bytes);
-    if (rc != ORBGPU_OK) return rc;
-    memcpy(W.h + o_k1, s1.keys_un, sizeof(orbgpu_keypoint) * (size_t)n1);
-    memcpy(W.h + o_d1, s1.desc, 32 * (size_t)n1);
-    memcpy(W.h + o_u1, s1.u_right, 4 * (size_t)n1);
-    memcpy(W.h + o_k2, s2.keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
-    memcpy(W.h + o_d2, s2.desc, 32 * (size_t)n2);
-    memcpy(W.h + o_u2, s2.u_right, 4 * (size_t)n2);
-    memcpy(W.h + o_m2, s2.has_map_point, (size_t)n2);
-    memcpy(W.h + o_i2, s2.indices, 4 * (size_t)nidx2);
-    memcpy(W.h + o_q, hq.data(), sizeof(BowQuery) * (size_t)nq);
-    memcpy(W.h + o_sc, a->scale_factors2, 4 * (size_t)a->nlevels);
-    memcpy(W.h + o_sg, a->level_sigma2, 4 * (size_t)a->nlevels);
-    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
-    CUS(cudaMemsetAsync(W.d + o_m12, 0xFF, 4 * (size_t)n1, W.st));
-    k_tri_match<<<(nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), nq, C, reinterpret_cast<const float*>(W.d + o_k1),
-                                                W.d + o_d1, reinterpret_cast<const float*>(W.d + o_u1), reinterpret_cast<const float*>(W.d + o_k2),
-                                                W.d + o_d2, reinterpret_cast<const float*>(W.d + o_u2), W.d + o_m2,
-                                                reinterpret_cast<const uint32_t*>(W.d + o_i2), reinterpret_cast<const float*>(W.d + o_sc),
-                                                reinterpret_cast<const float*>(W.d + o_sg), reinterpret_cast<int*>(W.d + o_m12));
+    J.o_k1 = L.add(sizeof(orbgpu_keypoint) * (size_t)n1); J.o_d1 = L.add(32 * (size_t)n1); J.o_u1 = L.add(4 * (size_t)n1);
+    J.o_k2 = L.add(sizeof(orbgpu_keypoint) * (size_t)n2); J.o_d2 = L.add(32 * (size_t)n2); J.o_u2 = L.add(4 * (size_t)n2);
+    J.o_m2 = L.add((size_t)n2); J.o_i2 = L.add(4 * (size_t)nidx2); J.o_q = L.add(sizeof(BowQuery) * (size_t)J.nq);
+    J.o_sc = L.add(4 * (size_t)a->nlevels); J.o_sg = L.add(4 * (size_t)a->nlevels);
+    J.in_bytes = L.off;
+    J.o_m12 = L.add(4 * (size_t)n1);
+    J.bytes = L.off;
+    return ORBGPU_OK;
+}
+
+// stage the inputs in the pinned mirror, upload, launch, download: all asynchronous on the workspace stream
+static int tri_enqueue(Workspace& W, const TriJob& J)
+{
+    if (J.nq == 0) return ORBGPU_OK;
+    const orbgpu_triangulation_args* a = J.a;
+    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
+    const int n1 = s1.n, n2 = s2.n, nidx2 = s2.node_start[s2.n_nodes];
+    uint8_t* h = W.h + J.base;
+    uint8_t* d = W.d + J.base;
+    memcpy(h + J.o_k1, s1.keys_un, sizeof(orbgpu_keypoint) * (size_t)n1);
+    memcpy(h + J.o_d1, s1.desc, 32 * (size_t)n1);
+    memcpy(h + J.o_u1, s1.u_right, 4 * (size_t)n1);
+    memcpy(h + J.o_k2, s2.keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(h + J.o_d2, s2.desc, 32 * (size_t)n2);
+    memcpy(h + J.o_u2, s2.u_right, 4 * (size_t)n2);
+    memcpy(h + J.o_m2, s2.has_map_point, (size_t)n2);
+    memcpy(h + J.o_i2, s2.indices, 4 * (size_t)nidx2);
+    memcpy(h + J.o_q, J.hq.data(), sizeof(BowQuery) * (size_t)J.nq);
+    memcpy(h + J.o_sc, a->scale_factors2, 4 * (size_t)a->nlevels);
+    memcpy(h + J.o_sg, a->level_sigma2, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(d, h, J.in_bytes, cudaMemcpyHostToDevice, W.st));
+    CUS(cudaMemsetAsync(d + J.o_m12, 0xFF, 4 * (size_t)n1, W.st));
+    k_tri_match<<<(J.nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(d + J.o_q), J.nq, J.C, reinterpret_cast<const float*>(d + J.o_k1),
+                                                  d + J.o_d1, reinterpret_cast<const float*>(d + J.o_u1), reinterpret_cast<const float*>(d + J.o_k2),
+                                                  d + J.o_d2, reinterpret_cast<const float*>(d + J.o_u2), d + J.o_m2,
+                                                  reinterpret_cast<const uint32_t*>(d + J.o_i2), reinterpret_cast<const float*>(d + J.o_sc),
+                                                  reinterpret_cast<const float*>(d + J.o_sg), reinterpret_cast<int*>(d + J.o_m12));
     CUS(cudaGetLastError());
-    CUS(cudaMemcpyAsync(W.h + o_m12, W.d + o_m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
-    CUS(cudaStreamSynchronize(W.st));
-    memcpy(matches12, W.h + o_m12, 4 * (size_t)n1);
+    CUS(cudaMemcpyAsync(h + J.o_m12, d + J.o_m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
+    return ORBGPU_OK;
+}
+
+// after the stream has drained: results out of the mirror, the rotation histogram on the host
+static void tri_finish(const Workspace& W, const TriJob& J, int32_t* matches12, int* nmatches)
+{
+    if (J.nq == 0) return;
+    const orbgpu_triangulation_args* a = J.a;
+    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
+    const std::vector<BowQuery>& hq = J.hq;
+    const int nq = J.nq;
+    memcpy(matches12, W.h + J.base + J.o_m12, 4 * (size_t)s1.n);
     int nm = 0;
     for (int q = 0; q < nq; ++q) nm += matches12[hq[q].idx1] >= 0;
     if (a->check_orientation) {                                // :760-776, :794-813
@@ -1737,7 +1769,43 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
         }
     }
     *nmatches = nm;
+}
+
+int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation_args* args, int n_pairs, int32_t* matches12,
+                                          int* nmatches)
+{
+    if (n_pairs < 0) return ORBGPU_ERR_ARG;
+    if (n_pairs == 0) return ORBGPU_OK;
+    if (!args || !matches12 || !nmatches) return ORBGPU_ERR_ARG;
+    std::vector<TriJob> jobs((size_t)n_pairs);
+    std::vector<size_t> out_off((size_t)n_pairs);
+    size_t total = 0, out = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+        TriJob& J = jobs[(size_t)p];
+        J.a = args + p;
+        out_off[(size_t)p] = out;
+        const int rc = tri_prepare(J, matches12 + out, nmatches + p);
+        if (rc != ORBGPU_OK) return rc;
+        out += (size_t)(args[p].kf1.n > 0 ? args[p].kf1.n : 0);
+        J.base = total;
+        total += J.bytes;
+    }
+    if (total == 0) return ORBGPU_OK;
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, total, total);
+    if (rc != ORBGPU_OK) return rc;
+    for (int p = 0; p < n_pairs; ++p) {
+        rc = tri_enqueue(W, jobs[(size_t)p]);
+        if (rc != ORBGPU_OK) { cudaStreamSynchronize(W.st); return rc; }
+    }
+    CUS(cudaStreamSynchronize(W.st));
+    for (int p = 0; p < n_pairs; ++p) tri_finish(W, jobs[(size_t)p], matches12 + out_off[(size_t)p], nmatches + p);
     return ORBGPU_OK;
+}
+
+int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* a, int32_t* matches12, int* nmatches)
+{
+    return orbgpu_search_for_triangulation_batch(device, a, a ? 1 : 0, matches12, nmatches);
 }
 
 int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow_side* s2, float nnratio, int check_orientation,

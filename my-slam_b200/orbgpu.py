@@ -314,6 +314,7 @@ def lib():
         "orbgpu_search_by_projection_keyframe": (i32, [i32, vp, vp, pi]),
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
+        "orbgpu_search_for_triangulation_batch": (i32, [i32, vp, i32, vp, vp]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp]),
         "orbgpu_vocabulary_create": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
@@ -581,6 +582,22 @@ def search_for_triangulation(args, device=0):
     m12 = np.zeros(max(args.kf1.n, 1), np.int32); nm = C.c_int(0)
     _check(lib().orbgpu_search_for_triangulation(device, C.byref(args), _p(m12), C.byref(nm)))
     return nm.value, m12[:args.kf1.n].copy()
+
+
+def search_for_triangulation_batch(args_list, device=0):
+    """SearchForTriangulation for several keyframe pairs in one call (LocalMapping::CreateNewMapPoints: one per neighbour)
+    -> list of (nmatches, vMatches12)."""
+    n = len(args_list)
+    if n == 0:
+        return []
+    arr = (TriangulationArgs * n)(*args_list)
+    sizes = [a.kf1.n for a in args_list]
+    m12 = np.zeros(max(sum(sizes), 1), np.int32); nm = np.zeros(n, np.int32)
+    _check(lib().orbgpu_search_for_triangulation_batch(device, C.cast(arr, C.c_void_p), n, _p(m12), _p(nm)))
+    out, o = [], 0
+    for k, sz in enumerate(sizes):
+        out.append((int(nm[k]), m12[o:o + sz].copy())); o += sz
+    return out
 
 
 def search_local_map(args, device=0):

@@ -96,6 +96,14 @@ def main():
         assert a[0] == o[0] and np.array_equal(a[1], o[1])
         out["search_for_triangulation_%dx%d_100nodes" % (len(G1[0]), len(G2[0]))] = {
             "gpu_ms": med(lambda: pkg.search_for_triangulation(args)), "cpu_ms": med(lambda: po.search_for_triangulation(args)), "nmatches": a[0]}
+        if nf == 1000:          # one keyframe against 20 neighbours in one call (CreateNewMapPoints), per pair
+            many = [tt.tri_scene(pkg, po, G1, G2, 4 + i, 100, False, True, 0.5) for i in range(20)]
+            bl = [m[0] for m in many]
+            got = pkg.search_for_triangulation_batch(bl)
+            assert all(g[0] == po.search_for_triangulation(b)[0] for g, b in zip(got, bl))
+            out["search_for_triangulation_batch_20_pairs_%dx%d_per_pair" % (len(G1[0]), len(G2[0]))] = {
+                "gpu_ms": med(lambda: pkg.search_for_triangulation_batch(bl)) / 20,
+                "cpu_ms": med(lambda: [po.search_for_triangulation(b) for b in bl], 10, 1) / 20}
     # --- Tracking::SearchLocalPoints in one call: isInFrustum for 4000 local map points + the search against 1000 features
     import test_local_map as tm
     G1 = (np.concatenate([k1] * 4), np.concatenate([d1] * 4))

@@ -184,6 +184,30 @@ def test_device_triangulation_equals_oracle_on_random_frames(pkg, port, seed):
 
 
 @pytest.mark.gpu
+def test_device_triangulation_batch_equals_oracle(pkg, port):
+    """One keyframe against its neighbours in one call, as CreateNewMapPoints visits them (src/LocalMapping.cc:215-252)"""
+    jobs = [random_tri_args(pkg, port, seed) for seed in range(50, 62)]
+    F1, F2, _ = two_frames(pkg, device_extract(pkg), 640, 480, 0x7A1A + 1000, 1000)
+    jobs += [tri_scene(pkg, port, F1, F2, seed, 24, False, True, mz) for seed, mz in [(3, 0.0), (4, 0.5), (5, -0.4)]]
+    rng = np.random.default_rng(3)
+    k1, d1 = random_frame(rng, 50, 640, 480, rng.integers(0, 256, (3, 32), dtype=np.uint8))
+    empty = (np.zeros(0, np.uint32), np.zeros(1, np.int32), np.zeros(0, np.uint32))
+    s = port.tables()[0][0]
+    T1, T2 = poses(0.3)
+    side = (k1, d1, np.zeros(50, bool), np.full(50, -1.0, np.float32))
+    jobs.insert(4, pkg.triangulation_args(side + empty, side + empty, compute_f12(T1, T2, CAM), camera_center(T1), T2, CAM, s,
+                                          (s * s).astype(np.float32), False, True) + (T1,))     # nothing shared: no queries
+    got = pkg.search_for_triangulation_batch([j[0] for j in jobs])
+    assert len(got) == len(jobs)
+    total = 0
+    for j, g in zip(jobs, got):
+        want = port.search_for_triangulation(j[0])
+        assert g[0] == want[0] and np.array_equal(g[1], want[1])
+        total += want[0]
+    assert total > 300 and pkg.search_for_triangulation_batch([]) == []
+
+
+@pytest.mark.gpu
 def test_device_triangulation_edge_cases(pkg, port):
     rng = np.random.default_rng(9)
     pool = rng.integers(0, 256, (3, 32), dtype=np.uint8)
