@@ -277,6 +277,10 @@ typedef struct orbgpu_fuse_args {
     float th;
 } orbgpu_fuse_args;
 int orbgpu_fuse_search(int device, const orbgpu_fuse_args* args, int32_t* best_idx);
+/* The same for n_jobs (keyframe, point set) problems in one call: LocalMapping::SearchInNeighbors runs Fuse once per target
+ * keyframe and once back per neighbour (src/LocalMapping.cc:485-492), each an independent search.  All jobs are enqueued back
+ * to back and waited for once; job p writes n_points entries of best_idx right after those of job p - 1. */
+int orbgpu_fuse_search_batch(int device, const orbgpu_fuse_args* args, int n_jobs, int32_t* best_idx);
 
 /* ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
  * (src/ORBmatcher.cc:1472-1597), the guided search of Tracking::Relocalization (src/Tracking.cc:1459, :1473). */
@@ -366,7 +370,7 @@ typedef struct orbgpu_triangulation_args {
  * >= 0, ascending i); *nmatches = the return value. */
 int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* args, int32_t* matches12, int* nmatches);
 /* The same for n_pairs keyframe pairs in one call: LocalMapping::CreateNewMapPoints runs the search once per neighbouring
- * keyframe (src/LocalMapping.cc:215-252), each an independent problem.  Uploads, kernels and downloads of all pairs are
+ * keyframe (src/LocalMapping.cc:239-270), each an independent problem.  Uploads, kernels and downloads of all pairs are
  * enqueued back to back and waited for once.  Pair p writes kf1.n entries of matches12 right after those of pair p - 1
  * and nmatches[p]. */
 int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation_args* args, int n_pairs, int32_t* matches12,

@@ -11,7 +11,7 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      LocalPointsArgs, local_points_args, search_local_points,
                      TriangulationArgs, triangulation_args, search_for_triangulation, search_for_triangulation_batch,
                      LocalMapArgs, TrackFields, track_fields, local_map_args, search_local_map, debug_logf,
-                     FuseArgs, fuse_args, fuse_search,
+                     FuseArgs, fuse_args, fuse_search, fuse_search_batch,
                      RelocProjectionArgs, reloc_projection_args, search_by_projection_keyframe, distinctive_descriptors,
                      fuse_search_sim3, search_by_projection_sim3, search_by_sim3,
                      ORBVocabulary, write_vocabulary_text, KeyFrameDatabase, update_normals_and_depths)  # noqa: F401

@@ -1364,8 +1364,17 @@ int orbgpu_debug_logf(int device, const float* x, int n, float* out)
 // One engine for the keyframe-projection loops (Fuse, Fuse with Sim3, SearchByProjection with Sim3, the two passes of
 // SearchBySim3).  C carries the pose(s) and the mode flags; occupied != NULL switches from "best keypoint per point"
 // (best[n_points]) to the occupancy-ordered assignment of SearchByProjection(KF, Scw) (best[n_kf] = point index).
+// One keyframe-projection problem.  Alone (job == nullptr) it reserves the workspace, runs and waits.  As part of a batch it is
+// called twice: phase 1 validates, presets the outputs and sizes the job's region; phase 2 stages and enqueues it at job->base
+// without waiting (the caller has reserved the workspace for all jobs and collects the results after one stream wait).
+struct FuseJob {
+    size_t base = 0, bytes = 0, o_best = 0;
+    int nout = 0;
+    bool active = false;
+};
+
 static int fuse_run(int device, const orbgpu_fuse_args* a, FuseCam C, int chi2_gate, int max_dist, const uint8_t* occupied,
-                    int32_t* best, int* nmatches)
+                    int32_t* best, int* nmatches, FuseJob* job = nullptr, int phase = 0)
 {
     if (!a || !best || a->n_points < 0 || a->n_kf < 0 || a->nlevels < 1) return ORBGPU_ERR_ARG;
     if (!a->present || !a->world_pos || !a->max_distance || !a->min_distance || !a->mp_desc || !a->scale_factors) return ORBGPU_ERR_ARG;
@@ -1378,8 +1387,10 @@ static int fuse_run(int device, const orbgpu_fuse_args* a, FuseCam C, int chi2_g
     for (int i = 0; i < n2; ++i)
         if (a->keys_un[i].octave < 0 || a->keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
     const int nout = occupied ? n2 : n1;
-    for (int i = 0; i < nout; ++i) best[i] = -1;
-    if (nmatches) *nmatches = 0;
+    if (phase != 2) {
+        for (int i = 0; i < nout; ++i) best[i] = -1;
+        if (nmatches) *nmatches = 0;
+    }
     if (n1 == 0 || n2 == 0) return ORBGPU_OK;
     C.fx = a->fx; C.fy = a->fy; C.cx = a->cx; C.cy = a->cy; C.bf = a->bf;
     // the keyframe holds the image bounds as ints (include/KeyFrame.h:185-188, src/KeyFrame.cc:42-43)
@@ -1397,47 +1408,53 @@ static int fuse_run(int device, const orbgpu_fuse_args* a, FuseCam C, int chi2_g
     const size_t o_aq = L.add(occupied ? sizeof(AreaQuery) * (size_t)n1 : 0), o_cn = L.add(occupied ? 4 * (size_t)n1 : 0);
     const size_t o_acc = L.add(occupied ? 4 * (size_t)n1 : 0), o_cand = L.add(occupied ? 4 * (size_t)n1 * n2 : 0);
     Workspace& W = g_ws;
-    int rc = W.reserve(device, L.off, io_bytes);
-    if (rc != ORBGPU_OK) return rc;
-    memcpy(W.h + o_keys, a->keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
-    memcpy(W.h + o_desc, a->desc, 32 * (size_t)n2);
-    if (a->u_right) memcpy(W.h + o_ur, a->u_right, 4 * (size_t)n2); else memset(W.h + o_ur, 0, 4 * (size_t)n2);
-    memcpy(W.h + o_qdesc, a->mp_desc, 32 * (size_t)n1);
-    memcpy(W.h + o_pres, a->present, (size_t)n1);
-    memcpy(W.h + o_pos, a->world_pos, 12 * (size_t)n1);
-    if (a->normal) memcpy(W.h + o_nrm, a->normal, 12 * (size_t)n1);
-    memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
-    memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
-    if (occupied) memcpy(W.h + o_occ, occupied, (size_t)n2);
-    memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
-    if (a->inv_level_sigma2) memcpy(W.h + o_sig, a->inv_level_sigma2, 4 * (size_t)a->nlevels);
-    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    if (job && phase == 1) { job->bytes = L.off; job->o_best = o_best; job->nout = nout; job->active = true; return ORBGPU_OK; }
+    if (!job) {
+        const int rc = W.reserve(device, L.off, io_bytes);
+        if (rc != ORBGPU_OK) return rc;
+    }
+    uint8_t* const D = W.d + (job ? job->base : 0);
+    uint8_t* const H = W.h + (job ? job->base : 0);
+    memcpy(H + o_keys, a->keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
+    memcpy(H + o_desc, a->desc, 32 * (size_t)n2);
+    if (a->u_right) memcpy(H + o_ur, a->u_right, 4 * (size_t)n2); else memset(H + o_ur, 0, 4 * (size_t)n2);
+    memcpy(H + o_qdesc, a->mp_desc, 32 * (size_t)n1);
+    memcpy(H + o_pres, a->present, (size_t)n1);
+    memcpy(H + o_pos, a->world_pos, 12 * (size_t)n1);
+    if (a->normal) memcpy(H + o_nrm, a->normal, 12 * (size_t)n1);
+    memcpy(H + o_maxd, a->max_distance, 4 * (size_t)n1);
+    memcpy(H + o_mind, a->min_distance, 4 * (size_t)n1);
+    if (occupied) memcpy(H + o_occ, occupied, (size_t)n2);
+    memcpy(H + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    if (a->inv_level_sigma2) memcpy(H + o_sig, a->inv_level_sigma2, 4 * (size_t)a->nlevels);
+    CUS(cudaMemcpyAsync(D, H, in_bytes, cudaMemcpyHostToDevice, W.st));
     GridDev G;
-    set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    set_grid(G, D, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
     G.winX = C.minX; G.winY = C.minY;                          // src/KeyFrame.cc:574-586 subtract the int members
-    FuseQuery* d_q = reinterpret_cast<FuseQuery*>(W.d + o_q);
-    AreaQuery* d_aq = occupied ? reinterpret_cast<AreaQuery*>(W.d + o_aq) : nullptr;
+    FuseQuery* d_q = reinterpret_cast<FuseQuery*>(D + o_q);
+    AreaQuery* d_aq = occupied ? reinterpret_cast<AreaQuery*>(D + o_aq) : nullptr;
     k_grid_build<<<1, 1024, 0, W.st>>>(G);
-    k_fuse_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_pres, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
-                                                       reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
-                                                       reinterpret_cast<const float*>(W.d + o_scale), n1, d_q, d_aq);
+    k_fuse_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, D + o_pres, reinterpret_cast<const float*>(D + o_pos), reinterpret_cast<const float*>(D + o_nrm),
+                                                       reinterpret_cast<const float*>(D + o_maxd), reinterpret_cast<const float*>(D + o_mind),
+                                                       reinterpret_cast<const float*>(D + o_scale), n1, d_q, d_aq);
     if (!occupied) {
-        k_fuse_match<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur),
-                                                     reinterpret_cast<const float*>(W.d + o_sig), chi2_gate, (unsigned)max_dist,
-                                                     reinterpret_cast<int*>(W.d + o_best));
+        k_fuse_match<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, D + o_qdesc, n1, reinterpret_cast<const float*>(D + o_ur),
+                                                     reinterpret_cast<const float*>(D + o_sig), chi2_gate, (unsigned)max_dist,
+                                                     reinterpret_cast<int*>(D + o_best));
     } else {                                                   // vpMatched[idx] blocks a keypoint; an assignment blocks it for later points (:375, :397)
-        uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
-        int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
-        k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_aq, W.d + o_qdesc, n1, nullptr, d_cand, n2, d_cn);
-        k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nullptr, W.d + o_occ, max_dist,
-                                                                   reinterpret_cast<int*>(W.d + o_best), reinterpret_cast<int*>(W.d + o_acc),
-                                                                   reinterpret_cast<int*>(W.d + o_nm));
+        uint32_t* d_cand = reinterpret_cast<uint32_t*>(D + o_cand);
+        int* d_cn = reinterpret_cast<int*>(D + o_cn);
+        k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_aq, D + o_qdesc, n1, nullptr, d_cand, n2, d_cn);
+        k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nullptr, D + o_occ, max_dist,
+                                                                   reinterpret_cast<int*>(D + o_best), reinterpret_cast<int*>(D + o_acc),
+                                                                   reinterpret_cast<int*>(D + o_nm));
     }
     CUS(cudaGetLastError());
-    CUS(cudaMemcpyAsync(W.h + o_best, W.d + o_best, io_bytes - o_best, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaMemcpyAsync(H + o_best, D + o_best, io_bytes - o_best, cudaMemcpyDeviceToHost, W.st));
+    if (job) return ORBGPU_OK;
     CUS(cudaStreamSynchronize(W.st));
-    memcpy(best, W.h + o_best, 4 * (size_t)nout);
-    if (nmatches && occupied) *nmatches = *reinterpret_cast<const int*>(W.h + o_nm);
+    memcpy(best, H + o_best, 4 * (size_t)nout);
+    if (nmatches && occupied) *nmatches = *reinterpret_cast<const int*>(H + o_nm);
     return ORBGPU_OK;
 }
 
@@ -1476,6 +1493,45 @@ int orbgpu_fuse_search(int device, const orbgpu_fuse_args* a, int32_t* best_idx)
     for (int r = 0; r < 3; ++r) C.Ow[r] = a->Ow[r];
     C.view_check = 1;
     return fuse_run(device, a, C, 1, 50, nullptr, best_idx, nullptr);
+}
+
+int orbgpu_fuse_search_batch(int device, const orbgpu_fuse_args* args, int n_jobs, int32_t* best_idx)
+{
+    if (n_jobs < 0) return ORBGPU_ERR_ARG;
+    if (n_jobs == 0) return ORBGPU_OK;
+    if (!args || !best_idx) return ORBGPU_ERR_ARG;
+    std::vector<FuseJob> jobs((size_t)n_jobs);
+    std::vector<FuseCam> cams((size_t)n_jobs);
+    std::vector<size_t> out_off((size_t)n_jobs);
+    size_t total = 0, out = 0;
+    for (int p = 0; p < n_jobs; ++p) {
+        const orbgpu_fuse_args* a = args + p;
+        if (!a->Tcw || a->n_points < 0) return ORBGPU_ERR_ARG;
+        FuseCam& C = cams[(size_t)p];
+        cam_from_pose(C, a->Tcw);
+        for (int r = 0; r < 3; ++r) C.Ow[r] = a->Ow[r];
+        C.view_check = 1;
+        out_off[(size_t)p] = out;
+        const int rc = fuse_run(device, a, C, 1, 50, nullptr, best_idx + out, nullptr, &jobs[(size_t)p], 1);
+        if (rc != ORBGPU_OK) return rc;
+        out += (size_t)a->n_points;
+        jobs[(size_t)p].base = total;
+        total += jobs[(size_t)p].bytes;
+    }
+    if (total == 0) return ORBGPU_OK;
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, total, total);
+    if (rc != ORBGPU_OK) return rc;
+    for (int p = 0; p < n_jobs; ++p) {
+        if (!jobs[(size_t)p].active) continue;
+        rc = fuse_run(device, args + p, cams[(size_t)p], 1, 50, nullptr, best_idx + out_off[(size_t)p], nullptr, &jobs[(size_t)p], 2);
+        if (rc != ORBGPU_OK) { cudaStreamSynchronize(W.st); return rc; }
+    }
+    CUS(cudaStreamSynchronize(W.st));
+    for (int p = 0; p < n_jobs; ++p)
+        if (jobs[(size_t)p].active)
+            memcpy(best_idx + out_off[(size_t)p], W.h + jobs[(size_t)p].base + jobs[(size_t)p].o_best, 4 * (size_t)jobs[(size_t)p].nout);
+    return ORBGPU_OK;
 }
 
 int orbgpu_fuse_search_sim3(int device, const orbgpu_fuse_args* a, const float* Scw, int32_t* best_idx)
@@ -1625,7 +1681,7 @@ int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projecti
 }
 
 // One SearchForTriangulation problem, split so that several (LocalMapping::CreateNewMapPoints runs one per neighbouring
-// keyframe, src/LocalMapping.cc:215-252) can be enqueued back to back on the workspace stream and waited for once.
+// keyframe, src/LocalMapping.cc:239-270) can be enqueued back to back on the workspace stream and waited for once.
 struct TriJob {
     const orbgpu_triangulation_args* a = nullptr;
     std::vector<BowQuery> hq;

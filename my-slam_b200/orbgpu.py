@@ -315,6 +315,7 @@ def lib():
         "orbgpu_debug_logf": (i32, [i32, vp, i32, vp]),
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_for_triangulation_batch": (i32, [i32, vp, i32, vp, vp]),
+        "orbgpu_fuse_search_batch": (i32, [i32, vp, i32, vp]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp]),
         "orbgpu_vocabulary_create": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
@@ -622,6 +623,22 @@ def fuse_search(args, device=0):
     best = np.zeros(max(args.n_points, 1), np.int32)
     _check(lib().orbgpu_fuse_search(device, C.byref(args), _p(best)))
     return best[:args.n_points].copy()
+
+
+def fuse_search_batch(args_list, device=0):
+    """The search of Fuse for several (keyframe, point set) problems in one call (LocalMapping::SearchInNeighbors)
+    -> list of best_idx arrays."""
+    n = len(args_list)
+    if n == 0:
+        return []
+    arr = (FuseArgs * n)(*args_list)
+    sizes = [a.n_points for a in args_list]
+    best = np.zeros(max(sum(sizes), 1), np.int32)
+    _check(lib().orbgpu_fuse_search_batch(device, C.cast(arr, C.c_void_p), n, _p(best)))
+    out, o = [], 0
+    for sz in sizes:
+        out.append(best[o:o + sz].copy()); o += sz
+    return out
 
 
 def search_by_projection_keyframe(args, device=0):

@@ -120,6 +120,10 @@ def main():
     assert np.array_equal(a, o)
     out["fuse_search_%dx%d_th3" % (fa.n_points, fa.n_kf)] = {
         "gpu_ms": med(lambda: pkg.fuse_search(fa)), "cpu_ms": med(lambda: po.fuse_search(fa)), "fused": int((a >= 0).sum())}
+    fl = [fa] * 20               # 20 target keyframes in one call (SearchInNeighbors), per keyframe
+    assert all(np.array_equal(g, o) for g in pkg.fuse_search_batch(fl))
+    out["fuse_search_batch_20_keyframes_%dx%d_per_keyframe" % (fa.n_points, fa.n_kf)] = {
+        "gpu_ms": med(lambda: pkg.fuse_search_batch(fl)) / 20, "cpu_ms": med(lambda: [po.fuse_search(x) for x in fl], 10, 1) / 20}
     # --- MapPoint::ComputeDistinctiveDescriptors for the 2000 map points a new keyframe touches (up to 12 observations each)
     import test_distinctive as td
     dd, gs = td.groups(1, 2000, 12)

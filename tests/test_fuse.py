@@ -114,6 +114,25 @@ def test_device_fuse_equals_oracle_on_random_points(pkg, port, seed):
 
 
 @pytest.mark.gpu
+def test_device_fuse_batch_equals_oracle(pkg, port):
+    """Several target keyframes in one call, as SearchInNeighbors visits them (src/LocalMapping.cc:485-492)"""
+    bounds = (-8.5, 647.25, -6.0, 489.5)
+    jobs = []
+    for seed in range(70, 80):
+        _, keep = random_local_map_args(pkg, port, seed, n_cur=0 if seed == 73 else None)     # one keyframe without features
+        jobs.append(fuse_from_local_map(pkg, port, keep, 3.0, bounds, 30.0, seed=seed))
+    jobs[5][1]["present"][:] = 0                                                               # one job without points to fuse
+    got = pkg.fuse_search_batch([j[0] for j in jobs])
+    assert len(got) == len(jobs) and pkg.fuse_search_batch([]) == []
+    fused = 0
+    for j, g in zip(jobs, got):
+        want = port.fuse_search(j[0])
+        assert np.array_equal(g, want)
+        fused += int((want >= 0).sum())
+    assert fused > 200
+
+
+@pytest.mark.gpu
 def test_device_fuse_edge_cases(pkg, port):
     _, keep = random_local_map_args(pkg, port, 59)
     bounds = (0.0, 640.0, 0.0, 480.0)

@@ -185,7 +185,7 @@ def test_device_triangulation_equals_oracle_on_random_frames(pkg, port, seed):
 
 @pytest.mark.gpu
 def test_device_triangulation_batch_equals_oracle(pkg, port):
-    """One keyframe against its neighbours in one call, as CreateNewMapPoints visits them (src/LocalMapping.cc:215-252)"""
+    """One keyframe against its neighbours in one call, as CreateNewMapPoints visits them (src/LocalMapping.cc:239-270)"""
     jobs = [random_tri_args(pkg, port, seed) for seed in range(50, 62)]
     F1, F2, _ = two_frames(pkg, device_extract(pkg), 640, 480, 0x7A1A + 1000, 1000)
     jobs += [tri_scene(pkg, port, F1, F2, seed, 24, False, True, mz) for seed, mz in [(3, 0.0), (4, 0.5), (5, -0.4)]]
