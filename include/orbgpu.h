@@ -278,7 +278,7 @@ typedef struct orbgpu_fuse_args {
 } orbgpu_fuse_args;
 int orbgpu_fuse_search(int device, const orbgpu_fuse_args* args, int32_t* best_idx);
 /* The same for n_jobs (keyframe, point set) problems in one call: LocalMapping::SearchInNeighbors runs Fuse once per target
- * keyframe and once back per neighbour (src/LocalMapping.cc:485-492), each an independent search.  All jobs are enqueued back
+ * keyframe (src/LocalMapping.cc:485-492; the call back into the current keyframe, :516, is one more job), each an independent search.  All jobs are enqueued back
  * to back and waited for once; job p writes n_points entries of best_idx right after those of job p - 1. */
 int orbgpu_fuse_search_batch(int device, const orbgpu_fuse_args* args, int n_jobs, int32_t* best_idx);
 
