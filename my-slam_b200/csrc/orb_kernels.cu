@@ -874,10 +874,12 @@ __device__ __forceinline__ uint3 blur_load(const uint8_t* __restrict__ rowp, int
         wl = wc ? __ldg(p - 1) : __byte_perm(wm, 0, 0x1233);   // REFLECT_101: I(-1..-3) = I(1..3)
     } else {
         wl = wm = wr = 0;
-        const int x0 = 4 * wc - 4;
+        const int x0 = 4 * wc - 4, xr = 2 * (w - 1);
+        const bool once = w >= 16;                             // one reflection is enough: -w < i < 2w - 1
 #pragma unroll
         for (int k = 1; k < 11; ++k) {
-            const unsigned v = __ldg(rowp + reflect101(x0 + k, w));
+            const int i = x0 + k;
+            const unsigned v = __ldg(rowp + (once ? (i < 0 ? -i : (i >= w ? xr - i : i)) : reflect101(i, w)));
             if (k < 4) wl |= v << (8 * k); else if (k < 8) wm |= v << (8 * (k - 4)); else wr |= v << (8 * (k - 8));
         }
     }
@@ -902,12 +904,13 @@ __device__ __forceinline__ void blur_hsum(const uint3 r, unsigned h[4])
 #ifndef BLUR_AHEAD
 #define BLUR_AHEAD 1
 #endif
-template <bool WORDS>
+template <bool WORDS, bool INNER>
 __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int sp, uint8_t* __restrict__ dst, int dp,
                                            int w, int hgt, int wc, int y0)
 {
-    // input row y0 - 3 + k; rows are REFLECT_101-mapped only in the first / last strip
-    const bool inner = y0 >= 3 && y0 + BLUR_R + 3 + BLUR_AHEAD <= hgt;
+    // input row y0 - 3 + k; rows are REFLECT_101-mapped only in the first / last strip; INNER: known at compile time not
+    // to need it (the word path, where the row arithmetic is a visible share of the instructions)
+    const bool inner = INNER || (y0 >= 3 && y0 + BLUR_R + 3 + BLUR_AHEAD <= hgt);
     unsigned ring[7][4];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
@@ -948,7 +951,7 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int 
 // Work list entry: (level, first task, kind).  kind 0 = interior word columns [0, nfast) on the aligned
 // word path; kind 1 = the remaining columns (row ends; or every column when the level's rows are not
 // 4-byte aligned) on the byte path.  Splitting them keeps every warp on one path.
-__global__ void __launch_bounds__(BLUR_THREADS) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
+__global__ void __launch_bounds__(BLUR_THREADS, 9) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
 {
     const int4 t = tiles[blockIdx.x];
     const int l = t.x, frame = blockIdx.y;
@@ -964,12 +967,13 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur(OrbPlanDev P, const int4*
         if (nfast == 0) return;
         const int strip = task / nfast, wc = task - strip * nfast;
         if (strip * BLUR_R >= hgt) return;
-        blur_strip<true>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
+        const int y0 = strip * BLUR_R;
+        blur_strip<true, false>(src, sp, dst, L.pitch, w, hgt, wc, y0);
     } else {
         const int nslow = nwc - nfast;
         const int strip = task / nslow, wc = nfast + task - strip * nslow;
         if (strip * BLUR_R >= hgt) return;
-        blur_strip<false>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
+        blur_strip<false, false>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
     }
 }
 
