@@ -787,10 +787,16 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(OrbPlanDev P, int key_sm
 
     const uint32_t* slots = P.slots + (long long)frame * P.slot_frame_words + L.slot_off;
     const OrbCell* cells = P.cells + L.cell0;
-    for (int c = tid >> 5; c < L.ncells; c += OCT_THREADS / 32) {
-        const int base = cbase[c], cnt = (c + 1 < L.ncells ? cbase[c + 1] : nK) - base;
-        const uint32_t* s = slots + cells[c].slot_off;
-        for (int i = tid & 31; i < cnt; i += 32) o.kxy[base + i] = s[i];
+    // thread = one candidate: its cell is the last one whose offset is <= k (binary search over the scanned counts, which
+    // sit in L1).  A warp-per-cell walk made every warp chase cell table -> slot through ~35 dependent round trips.
+    for (int k = tid; k < nK; k += OCT_THREADS) {
+        int lo = 0, hi = L.ncells;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (cbase[mid] <= k) lo = mid + 1; else hi = mid;
+        }
+        const int c = lo - 1;
+        o.kxy[k] = slots[cells[c].slot_off + (k - cbase[c])];
     }
     __syncthreads();
 
