@@ -146,12 +146,37 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
         // every source row of the strip exactly once: H rows go to this thread's private shared-memory column
         // (no reuse logic, no divergence, all row loads independent), then the vertical pass reads two of them
         uint2* hcol = s_h + threadIdx.x;                       // H >> 4 <= 32640: two 16-bit values per word
+        if (WORDS) {
+            // six rows at a time: their 18 word loads are issued before the first use (row indices clamped to the last
+            // needed row instead of a branch per row, which kept each row's loads behind the previous row's arithmetic)
+            const int wb1 = min(wb + 1, wlast), wb2 = min(wb + 2, wlast);
 #pragma unroll
-        for (int i = 0; i < RS_SRC_ROWS; ++i) {
-            if (rfirst + i <= rlast) {
-                int H[4];
-                resize_hrow<WORDS>(src + (size_t)(rfirst + i) * sp, wb, wlast, s, sel, lowpair, a01, sw, H);
-                hcol[i * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+            for (int h = 0; h < RS_SRC_ROWS; h += 6) {
+                unsigned w0[6], w1[6], w2[6];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)min(rfirst + h + i, rlast) * sp);
+                    w0[i] = __ldg(p + wb); w1[i] = __ldg(p + wb1); w2[i] = __ldg(p + wb2);
+                }
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    int H[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const unsigned pair = __byte_perm(lowpair[j] ? w0[i] : w1[i], lowpair[j] ? w1[i] : w2[i], sel[j]);
+                        H[j] = (int)__dp2a_lo(a01[j], pair, 0u);
+                    }
+                    hcol[(h + i) * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < RS_SRC_ROWS; ++i) {
+                if (rfirst + i <= rlast) {
+                    int H[4];
+                    resize_hrow<WORDS>(src + (size_t)(rfirst + i) * sp, wb, wlast, s, sel, lowpair, a01, sw, H);
+                    hcol[i * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+                }
             }
         }
 #pragma unroll
@@ -208,7 +233,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
 // One thread = 4 horizontally adjacent output pixels (one aligned 32-bit store per row) x RS_ROWS rows.  The
 // x-axis table entries of the 4 pixels stay in registers; a source row costs three aligned word loads and
 // four IDP.2A dot products, and is reused when consecutive output rows share it.
-__global__ void __launch_bounds__(RS_THREADS) k_resize_level(OrbPlanDev P, int l)
+__global__ void __launch_bounds__(RS_THREADS, 8) k_resize_level(OrbPlanDev P, int l)
 {
     __shared__ uint2 s_h[RS_SRC_ROWS * RS_THREADS];            // [source row][thread]: H >> 4 of the thread's 4 pixels, 16 bits each
     const OrbLevel& D = P.lv[l];
