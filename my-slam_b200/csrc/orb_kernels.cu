@@ -943,17 +943,19 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int 
     // to need it (the word path, where the row arithmetic is a visible share of the instructions)
     const bool inner = INNER || (y0 >= 3 && y0 + BLUR_R + 3 + BLUR_AHEAD <= hgt);
     unsigned ring[7][4];
+    // the row numbers of the 6 + BLUR_AHEAD start-up rows first (reflect101 is a loop: computed between the loads it put a
+    // branch after every row and serialised their round trips), then all their loads, then the sums
+    int yy0[6 + BLUR_AHEAD];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        const int yy = inner ? y0 - 3 + k : reflect101(y0 - 3 + k, hgt);
-        blur_hsum(blur_load<WORDS>(src + (size_t)yy * sp, wc, w), ring[k]);
-    }
+    for (int k = 0; k < 6 + BLUR_AHEAD; ++k) yy0[k] = inner ? y0 - 3 + k : reflect101(y0 - 3 + k, hgt);
+    uint3 first[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) first[k] = blur_load<WORDS>(src + (size_t)yy0[k] * sp, wc, w);
     uint3 ahead[BLUR_AHEAD];                                   // rows y0 + 3 .. y0 + 3 + BLUR_AHEAD - 1, in flight
 #pragma unroll
-    for (int a = 0; a < BLUR_AHEAD; ++a) {
-        const int yy = inner ? y0 + 3 + a : reflect101(y0 + 3 + a, hgt);
-        ahead[a] = blur_load<WORDS>(src + (size_t)yy * sp, wc, w);
-    }
+    for (int a = 0; a < BLUR_AHEAD; ++a) ahead[a] = blur_load<WORDS>(src + (size_t)yy0[6 + a] * sp, wc, w);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) blur_hsum(first[k], ring[k]);
     for (int yb = 0; yb < BLUR_R; yb += 7) {
 #pragma unroll
         for (int j = 0; j < 7; ++j) {
