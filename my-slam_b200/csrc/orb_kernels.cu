@@ -907,11 +907,24 @@ __device__ __forceinline__ uint3 blur_load(const uint8_t* __restrict__ rowp, int
         wl = wm = wr = 0;
         const int x0 = 4 * wc - 4, xr = 2 * (w - 1);
         const bool once = w >= 16;                             // one reflection is enough: -w < i < 2w - 1
+        // five column numbers, then their five loads together, twice (a branch between two loads serialises them; ten at
+        // once cost the word path two spilled registers)
 #pragma unroll
-        for (int k = 1; k < 11; ++k) {
-            const int i = x0 + k;
-            const unsigned v = __ldg(rowp + (once ? (i < 0 ? -i : (i >= w ? xr - i : i)) : reflect101(i, w)));
-            if (k < 4) wl |= v << (8 * k); else if (k < 8) wm |= v << (8 * (k - 4)); else wr |= v << (8 * (k - 8));
+        for (int g = 0; g < 2; ++g) {
+            int xi[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                const int i = x0 + 1 + 5 * g + k;
+                xi[k] = once ? (i < 0 ? -i : (i >= w ? xr - i : i)) : reflect101(i, w);
+            }
+            unsigned v[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) v[k] = __ldg(rowp + xi[k]);
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                const int kk = 1 + 5 * g + k;
+                if (kk < 4) wl |= v[k] << (8 * kk); else if (kk < 8) wm |= v[k] << (8 * (kk - 4)); else wr |= v[k] << (8 * (kk - 8));
+            }
         }
     }
     return make_uint3(wl, wm, wr);
