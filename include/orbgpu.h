@@ -433,6 +433,20 @@ int orbgpu_hamming256(const void* a, const void* b);
 int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t* B, int nB,
                             int32_t* best_idx, uint16_t* best, uint16_t* second);
 
+/* orbgpu_match_bruteforce without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same kernel and bit-identical results as orbgpu_match_bruteforce, but the device
+ * staging area is a fixed file-scope __device__ array of the library (288 KB, held by every GPU that loads the
+ * library until exit) instead of scratch grown with cudaMalloc / cudaHostAlloc: the call makes no cudaMalloc,
+ * cudaFree, cudaHostAlloc, stream / event creation or other allocating call; copies are plain cudaMemcpy on the
+ * legacy default stream.  Limit: nA and nB at most ORBGPU_NOALLOC_MAX_DESCRIPTORS each, beyond it the call returns
+ * ORBGPU_ERR_CAPACITY (text in orbgpu_last_cuda_error()) and touches nothing.  0 <= device < 64.  All calls on
+ * one device share the array, which keeps the previous call's contents (every byte a call reads is written by that
+ * call first); calls on the same device that overlap in time (two host threads) race on it -- serialise them. */
+#define ORBGPU_NOALLOC_MAX_DESCRIPTORS 4096
+int orbgpu_match_bruteforce_noalloc(int device, const uint8_t* A, int nA, const uint8_t* B, int nB,
+                                    int32_t* best_idx, uint16_t* best, uint16_t* second);
+
 /* All-pairs keyframe matching (BASELINE config 5).  A matcher holds K keyframes x n descriptors
  * resident in HBM; pair p = (a[p], b[p]) yields counts[p] = number of rows of keyframe a whose best
  * match in keyframe b passes best <= th_low && float(best) < ratio*float(second)

@@ -9,6 +9,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 #include <new>
 
 #include "../../include/orbgpu.h"
@@ -218,6 +219,33 @@ thread_local MatchScratch g_scratch;
 inline size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
 }  // namespace
 
+// Scratch of orbgpu_match_bruteforce_noalloc: a fixed device array that every GPU loading the library holds until
+// exit (both descriptor sets and the three result arrays of the largest accepted call, each region 256-byte aligned).
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device with that device current (noalloc_scratch_ptr).
+#define NOALLOC_MAX ORBGPU_NOALLOC_MAX_DESCRIPTORS
+#define NOALLOC_BYTES (2 * 32 * NOALLOC_MAX + 4 * NOALLOC_MAX + 2 * 2 * NOALLOC_MAX)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+namespace {
+#define NOALLOC_MAX_DEVICES 64
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];     // device address of g_noalloc_scratch, per device ordinal
+
+// `device` must be current.  Returns ORBGPU_OK and the device's own copy of the array.
+int noalloc_scratch_ptr(int device, unsigned char** out)
+{
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        CUM(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return ORBGPU_OK;
+}
+}  // namespace
+
 extern "C" {
 
 int orbgpu_hamming256(const void* a, const void* b)
@@ -250,6 +278,45 @@ int orbgpu_match_bruteforce(int device, const uint8_t* A, int nA, const uint8_t*
     memcpy(best_idx, S.h + o_i, 4 * (size_t)nA);
     memcpy(best, S.h + o_1, 2 * (size_t)nA);
     memcpy(second, S.h + o_2, 2 * (size_t)nA);
+    return ORBGPU_OK;
+}
+
+// The allocation-free variant (include/orbgpu.h): same kernel, same results, the staging area is g_noalloc_scratch
+// instead of the grown-on-demand MatchScratch; plain cudaMemcpy on the legacy default stream, so no stream, event,
+// pinned or device allocation is made here.  Nothing in the array has to start at zero: the two descriptor regions
+// are overwritten by this call's uploads before the kernel reads them, and the kernel writes all nA entries of the
+// three result regions before they are copied back; bytes beyond nA / nB keep the previous call's contents and are
+// never read.
+int orbgpu_match_bruteforce_noalloc(int device, const uint8_t* A, int nA, const uint8_t* B, int nB,
+                                    int32_t* best_idx, uint16_t* best, uint16_t* second)
+{
+    if (!A || !B || !best_idx || !best || !second || nA < 1 || nB < 0) return ORBGPU_ERR_ARG;
+    if (nA > NOALLOC_MAX || nB > NOALLOC_MAX) {
+        char b[160];
+        snprintf(b, sizeof(b), "orbgpu_match_bruteforce_noalloc: nA = %d / nB = %d exceed the fixed scratch (at most %d descriptors per set)",
+                 nA, nB, NOALLOC_MAX);
+        orbgpu_internal_set_error(b);
+        return ORBGPU_ERR_CAPACITY;
+    }
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(device));
+    unsigned char* d = nullptr;
+    const int rc = noalloc_scratch_ptr(device, &d);
+    if (rc != ORBGPU_OK) return rc;
+    unsigned char* d_a = d;
+    unsigned char* d_b = d_a + 32 * (size_t)NOALLOC_MAX;
+    unsigned char* d_i = d_b + 32 * (size_t)NOALLOC_MAX;
+    unsigned char* d_1 = d_i + 4 * (size_t)NOALLOC_MAX;
+    unsigned char* d_2 = d_1 + 2 * (size_t)NOALLOC_MAX;
+    CUM(cudaMemcpy(d_a, A, 32 * (size_t)nA, cudaMemcpyHostToDevice));
+    if (nB > 0) CUM(cudaMemcpy(d_b, B, 32 * (size_t)nB, cudaMemcpyHostToDevice));
+    k_match_bruteforce<<<(nA + MATCH_THREADS - 1) / MATCH_THREADS, MATCH_THREADS>>>(
+        reinterpret_cast<const uint4*>(d_a), nA, reinterpret_cast<const uint4*>(d_b), nB,
+        reinterpret_cast<int32_t*>(d_i), reinterpret_cast<uint16_t*>(d_1), reinterpret_cast<uint16_t*>(d_2));
+    CUM(cudaGetLastError());
+    CUM(cudaMemcpy(best_idx, d_i, 4 * (size_t)nA, cudaMemcpyDeviceToHost));
+    CUM(cudaMemcpy(best, d_1, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
+    CUM(cudaMemcpy(second, d_2, 2 * (size_t)nA, cudaMemcpyDeviceToHost));
     return ORBGPU_OK;
 }
 

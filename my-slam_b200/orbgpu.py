@@ -334,6 +334,7 @@ def lib():
         "orbgpu_bowdb_query": (i32, [vp, vp, vp, i32, vp, vp, vp]),
         "orbgpu_update_normals_and_depths": (i32, [i32, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
+        "orbgpu_match_bruteforce_noalloc": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
         "orbgpu_matcher_set_keyframes": (i32, [vp, vp, i32, i32]),
