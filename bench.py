@@ -34,6 +34,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+def _load_synth():
+    """my-slam_b200/synth.py on its own (numpy only): frame generators and the BASELINE config table, without touching CUDA."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_orb_synth", os.path.join(ROOT, "my-slam_b200", "synth.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+SYNTH = _load_synth()
+SYNTH_CONFIGS = SYNTH.CONFIGS
 WORKLOAD = "C1_tum_640x480_nf1000"
 PARAMS = dict(nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7)
 FRAMES_PER_STEP = 512            # per GPU: 512 x 307200 B = 157 MB of input per step > 126 MB L2
@@ -298,9 +309,8 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(args.steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "nfeatures": nf, "nlevels": PARAMS["nlevels"], "scale": PARAMS["scale"],
-                   "ini_th": PARAMS["ini_th"], "min_th": PARAMS["min_th"], "width": w, "height": h,
-                   "note": "host CPU only; does not scale with --gpus"},
+        "config": config_of(WORKLOAD, nf, w, h, args.frames),
+        "run": {"note": "host CPU only; does not scale with --gpus; frames_per_step_per_gpu is the other arm's batch, this arm's sample is in cpu_baseline"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample_txt},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -331,199 +341,250 @@ def bind_to_gpu_cpus(index):
 # ---------------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------------
-def run_ours(args, rank, world, local_rank):
-    import torch
-    import torch.distributed as dist
-    import __graft_entry__ as g
-    pkg = g.load_package()
-    if not torch.cuda.is_available() or pkg.device_count() < 1:
-        raise RuntimeError("bench.py: no CUDA device visible; the orbgpu path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    all_cpus = os.sched_getaffinity(0)
-    numa = bind_to_gpu_cpus(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+WORKLOADS = {"C1": ("C1_tum_640x480_nf1000", 1000), "C2": ("C2_kitti_1241x376_nf2000", 2000),
+             "C3": ("C3_euroc_752x480_nf1000", 1000), "C4": ("C4_hd_1920x1080_nf4000", 4000)}
+# frames per step per GPU of the secondary workload lines: each batch is larger than L2 (132 MB)
+SECONDARY_FRAMES = {"C2": 288, "C3": 1024, "C4": 72}
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
-    def max_over_ranks(x):
-        if world == 1:
+def config_of(workload, nfeatures, w, h, frames):
+    """The `config` object: a function of the workload and the command line only, so that both arms print the same keys."""
+    return {"workload": workload, "nfeatures": nfeatures, "nlevels": PARAMS["nlevels"], "scale": PARAMS["scale"],
+            "ini_th": PARAMS["ini_th"], "min_th": PARAMS["min_th"], "width": w, "height": h,
+            "frames_per_step_per_gpu": frames,
+            "l2": "inputs larger than L2: %.0f MB of frames per step vs %.0f MB L2" % (frames * w * h / 1e6, L2_BYTES / 1e6)}
+
+
+def _synth_job(job):
+    w, h, seed = job
+    return SYNTH.synth(w, h, seed)
+
+
+def make_frames_parallel(requests, procs):
+    """requests: {tag: (workload name, [frame numbers])} -> {tag: uint8 [n, h, w]}.  Frame k of a workload is
+    synth(w, h, seed base + k).  Generated by a fork pool BEFORE anything touches CUDA."""
+    import multiprocessing as mp
+    spec = {}
+    jobs = []
+    for tag, (name, idx) in requests.items():
+        w, h, _, base, _ = SYNTH_CONFIGS[name]
+        spec[tag] = (len(jobs), len(idx), w, h)
+        jobs += [(w, h, base + int(k)) for k in idx]
+    if procs > 1 and len(jobs) > 8:
+        with mp.get_context("fork").Pool(procs) as pool:
+            imgs = pool.map(_synth_job, jobs, chunksize=max(1, len(jobs) // (procs * 8)))
+    else:
+        imgs = [_synth_job(j) for j in jobs]
+    out = {}
+    for tag, (o, n, w, h) in spec.items():
+        out[tag] = np.stack(imgs[o:o + n]) if n else np.zeros((0, h, w), np.uint8)
+    return out
+
+
+class Ctx:
+    def __init__(self, torch, dist, rank, world, local_rank):
+        self.torch, self.dist, self.rank, self.world, self.local_rank = torch, dist, rank, world, local_rank
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def _red(self, x, op):
+        if self.world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=op)
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    def max(self, x):
+        return self._red(x, self.dist.ReduceOp.MAX) if self.world > 1 else x
 
+    def sum(self, x):
+        return self._red(x, self.dist.ReduceOp.SUM) if self.world > 1 else x
+
+
+def measure_extraction(ctx, pkg, frames_np, nfeatures, steps, warmup, args, serial_pass=True, sustained_s=0.0,
+                       copy_probe=True, keep_results=False):
+    """One workload on this rank's GPU.  Returns raw times (already max over ranks) and counts:
+    device-resident steps (`value`), end to end from pinned host memory (async API and synchronous call), the pass with
+    the chunks serialised on one stream (per-kernel times, rank 0), an optional sustained loop and the raw copy ceiling."""
+    torch = ctx.torch
     p = PARAMS
-    w, h, nf, _, _ = pkg.synth.CONFIGS[WORKLOAD]
-    n = args.frames
-    ex = pkg.ORBextractor(p["nfeatures"], p["scale"], p["nlevels"], p["ini_th"], p["min_th"], device=local_rank)
+    n, h, w = frames_np.shape
+    ex = pkg.ORBextractor(nfeatures, p["scale"], p["nlevels"], p["ini_th"], p["min_th"], device=ctx.local_rank)
     cap = ex.max_keypoints(w, h)
     if args.streams or args.chunk:
         ex.set_batching(args.streams or 4, args.chunk or 64)
-
-    # synthetic frames: every rank owns its own batch (weak scaling)
     h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
-    h_frames.numpy()[:] = make_frames(pkg, n, rank * n)
+    h_frames.numpy()[:] = frames_np
     d_frames = h_frames.cuda()
     d_kps = torch.empty((n, cap, 28), dtype=torch.uint8, device="cuda")
     d_desc = torch.empty((n, cap, 32), dtype=torch.uint8, device="cuda")
     d_nout = torch.empty((n,), dtype=torch.int32, device="cuda")
-    h_kps = torch.empty((n, cap, 28), dtype=torch.uint8, pin_memory=True)
-    h_desc = torch.empty((n, cap, 32), dtype=torch.uint8, pin_memory=True)
-    h_nout = torch.empty((n,), dtype=torch.int32, pin_memory=True)
+    outs = [(torch.empty((n, cap, 28), dtype=torch.uint8, pin_memory=True), torch.empty((n, cap, 32), dtype=torch.uint8, pin_memory=True),
+             torch.empty((n,), dtype=torch.int32, pin_memory=True)) for _ in range(2)]
+    row, frm = w, w * h                                       # dense rows; the library re-pitches on the device when w % 16 != 0
 
     def step_device():
-        ex.extract_batch_ptr(d_frames.data_ptr(), n, w, h, w, w * h, d_kps.data_ptr(), d_desc.data_ptr(), cap,
-                             d_nout.data_ptr(), device=True)
+        ex.extract_batch_ptr(d_frames.data_ptr(), n, w, h, row, frm, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_nout.data_ptr(), device=True)
         return ex.last_batch_ms()
 
     def step_host():
-        ex.extract_batch_ptr(h_frames.data_ptr(), n, w, h, w, w * h, h_kps.data_ptr(), h_desc.data_ptr(), cap,
-                             h_nout.data_ptr(), device=False)
+        ok, od, on = outs[0]
+        ex.extract_batch_ptr(h_frames.data_ptr(), n, w, h, row, frm, ok.data_ptr(), od.data_ptr(), cap, on.data_ptr(), device=False)
         return ex.last_batch_ms()
-
-    sampler = ClockSampler(local_rank)
-
-    # ---- device-resident: `value`
-    for _ in range(args.warmup):
-        step_device()
-    ex.set_profiling(True)
-    ex.stage_ms(reset=True)
-    barrier()
-    sampler.start()
-    l0 = ex.launch_count()
-    t0 = time.perf_counter()
-    dev_ms = 0.0
-    for _ in range(args.steps):
-        dev_ms += step_device()
-    barrier()
-    wall_dev_ms = (time.perf_counter() - t0) * 1e3
-    launches = ex.launch_count() - l0
-    stage = ex.stage_ms(reset=True)
-    ex.set_profiling(False)
-    dev_ms = max_over_ranks(dev_ms)
-    wall_dev_ms = max_over_ranks(wall_dev_ms)
-    nkp_dev = int(d_nout.sum().item())
-
-    # ---- end to end from pinned host memory: `e2e`.  Batches are streamed through the asynchronous entry point
-    #      (orbgpu_extract_batch_async, results alternate between two pinned output sets, orbgpu_wait at the end) so
-    #      that the upload of step k+1 overlaps the kernels of step k; every step's H2D and D2H lies inside the region
-    h_kps2, h_desc2, h_nout2 = torch.empty_like(h_kps), torch.empty_like(h_desc), torch.empty_like(h_nout)
-    outs = [(h_kps, h_desc, h_nout), (h_kps2, h_desc2, h_nout2)]
 
     def run_host_steps(k):
         for i in range(k):
             ok, od, on = outs[i % 2]
-            ex.extract_batch_async_ptr(h_frames.data_ptr(), n, w, h, w, w * h, ok.data_ptr(), od.data_ptr(), cap, on.data_ptr())
+            ex.extract_batch_async_ptr(h_frames.data_ptr(), n, w, h, row, frm, ok.data_ptr(), od.data_ptr(), cap, on.data_ptr())
         ex.wait()
         return ex.last_batch_ms()
 
-    for _ in range(args.warmup):
+    R = {"n": n, "w": w, "h": h, "cap": cap, "nfeatures": nfeatures}
+    # ---- device-resident: `value`
+    for _ in range(warmup):
+        step_device()
+    ex.set_profiling(True)
+    ex.stage_ms(reset=True)
+    ctx.barrier()
+    l0 = ex.launch_count()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(steps):
+        dev_ms += step_device()
+    ctx.barrier()
+    R["wall_dev_ms"] = ctx.max((time.perf_counter() - t0) * 1e3)
+    R["launches"] = ctx.sum(float(ex.launch_count() - l0))
+    R["stage"] = ex.stage_ms(reset=True)
+    ex.set_profiling(False)
+    R["dev_ms"] = ctx.max(dev_ms)
+    nout_dev = d_nout.cpu().numpy().copy()
+    R["nkp"] = int(nout_dev.sum())
+    if keep_results:
+        R["kps"], R["desc"], R["nout"] = d_kps.cpu().numpy(), d_desc.cpu().numpy(), nout_dev
+
+    # ---- sustained: the same step repeated for at least sustained_s seconds (power / thermal behaviour)
+    if sustained_s > 0:
+        sm = ClockSampler(ctx.local_rank); sm.start()
+        ctx.barrier()
+        t0 = time.perf_counter(); k = 0; ms = 0.0
+        while time.perf_counter() - t0 < sustained_s:         # every rank runs for the same time; steps are counted per rank
+            ms += step_device(); k += 1
+        own = (time.perf_counter() - t0) * 1e3
+        ctx.barrier()
+        wall = ctx.max(max(own, ms))
+        R["sustained"] = {"frames_per_s": n * ctx.sum(float(k)) / (wall * 1e-3), "seconds": wall * 1e-3, "steps_per_gpu": k,
+                          "clocks": sm.stop(), "timing": "frames of all ranks / the slower of summed CUDA-event step times and host wall clock, max over ranks"}
+
+    # ---- end to end from pinned host memory.  Primary API: orbgpu_extract_batch_async x steps + orbgpu_wait (results
+    #      alternate between two pinned output sets); every step's H2D and D2H lies inside the timed region
+    for _ in range(warmup):
         step_host()
     run_host_steps(2)
-    barrier()
+    ctx.barrier()
     t0 = time.perf_counter()
-    e2e_ms = run_host_steps(args.steps)
-    barrier()
-    wall_e2e_ms = (time.perf_counter() - t0) * 1e3
-    # the same through the synchronous call (pipeline fills and drains every step)
-    barrier()
+    ev = run_host_steps(steps)
+    ctx.barrier()
+    R["async_wall_ms"] = ctx.max((time.perf_counter() - t0) * 1e3)
+    R["async_ms"] = ctx.max(ev)
+    ctx.barrier()
     t0 = time.perf_counter()
     sync_ms = 0.0
-    for _ in range(args.steps):
+    for _ in range(steps):
         sync_ms += step_host()
-    barrier()
-    sync_ms = max(max_over_ranks(sync_ms), max_over_ranks((time.perf_counter() - t0) * 1e3))   # slower of events and wall
-    clocks = sampler.stop()
-    e2e_ms = max_over_ranks(e2e_ms)
-    wall_e2e_ms = max_over_ranks(wall_e2e_ms)
-    nkp_host = int(h_nout.numpy().sum())
-    if nkp_host != nkp_dev or not np.array_equal(h_nout.numpy(), d_nout.cpu().numpy()) or not np.array_equal(h_nout2.numpy(), h_nout.numpy()):
-        raise RuntimeError("host-buffer and device-buffer paths disagree on keypoint counts")
-    total_launches = sum_over_ranks(float(launches))
+    ctx.barrier()
+    R["sync_ms"] = max(ctx.max(sync_ms), ctx.max((time.perf_counter() - t0) * 1e3))
+    for (_, _, on) in outs[:2 if steps > 1 else 1]:
+        if not np.array_equal(on.numpy(), nout_dev):
+            raise RuntimeError("host-buffer and device-buffer paths disagree on keypoint counts")
+    R["h2d_bytes"] = n * w * h
+    R["d2h_bytes"] = n * cap * 60 + 4 * n
 
-    # ---- per-kernel durations with each kernel running alone: the same batch, chunks serialised on one stream
-    #      (in the timed region above the chunk streams overlap, which inflates every per-stream stage time)
-    ser_stage, ser_launches, ser_ms = None, 0, 0.0
-    if rank == 0:
+    # ---- raw copy ceiling of this box at this rank count: the same bytes per step, H2D and D2H on two streams at once,
+    #      no kernels (every rank at the same time: the host side is shared)
+    if copy_probe:
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        def copies(k):
+            for _ in range(k):
+                with torch.cuda.stream(s1):
+                    d_frames.copy_(h_frames, non_blocking=True)
+                with torch.cuda.stream(s2):
+                    outs[0][0].copy_(d_kps, non_blocking=True); outs[0][1].copy_(d_desc, non_blocking=True); outs[0][2].copy_(d_nout, non_blocking=True)
+            s1.synchronize(); s2.synchronize()
+        copies(2)
+        ctx.barrier()
+        t0 = time.perf_counter()
+        copies(steps)
+        ctx.barrier()
+        cms = ctx.max((time.perf_counter() - t0) * 1e3)
+        R["copy_ms"] = cms
+        step_device()                                         # d_kps / d_desc were overwritten with stale host data by the probe
+
+    # ---- per-kernel durations with each kernel running alone: chunks serialised on one stream (rank 0)
+    if serial_pass and ctx.rank == 0:
         ex.set_batching(1, args.chunk or 64)
+        R["ser_chunk"] = min(args.chunk or 64, ex.chunk_capacity(w, h))
         step_device()
         ex.set_profiling(True)
         ex.stage_ms(reset=True)
         l1 = ex.launch_count()
-        for _ in range(min(args.steps, 3)):
+        ser_ms = 0.0
+        R["ser_steps"] = min(steps, 3)
+        for _ in range(R["ser_steps"]):
             ser_ms += step_device()
-        ser_launches = ex.launch_count() - l1
-        ser_stage = ex.stage_ms(reset=True)
+        R["ser_launches"] = ex.launch_count() - l1
+        R["ser_stage"] = ex.stage_ms(reset=True)
+        R["ser_ms"] = ser_ms
         ex.set_profiling(False)
-        ex.set_batching(args.streams or 4, args.chunk or 64)
-    ser_steps = min(args.steps, 3)
-    hamming = None
-    if args.hamming_keyframes >= 2:
-        hamming = bench_hamming(pkg, torch, dist, rank, world, local_rank, args.hamming_keyframes, 1000)
+    ex.close()
+    del d_frames, d_kps, d_desc, d_nout, h_frames, outs
+    torch.cuda.empty_cache()
+    return R
 
-    total_frames = n * world * args.steps
-    value = total_frames / (dev_ms * 1e-3)
-    async_value = total_frames / (max(e2e_ms, wall_e2e_ms) * 1e-3)    # the slower of device events and host wall clock
-    sync_value = total_frames / (sync_ms * 1e-3)
-    # both are complete end-to-end runs of the same work through a public entry point; the line reports the better one
-    # (with few host threads per GPU the one-call-per-step form can win) and names it
-    e2e_value = max(async_value, sync_value)
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
-
-    # ---- roofline of the dominant kernel (rank 0): CUDA events on the launching stream, serialised pass
+def roofline_of(R, workload, steps, world, value, clocks, with_issue):
+    """Roofline object of the dominant kernel from the serialised pass of measure_extraction (rank 0)."""
+    p = PARAMS
     peak, peak_src = load_peaks()
-    path_bytes, stage_bytes = algorithmic_bytes(w, h, p["nfeatures"], p["nlevels"], p["scale"])
+    w, h, n = R["w"], R["h"], R["n"]
+    path_bytes, stage_bytes = algorithmic_bytes(w, h, R["nfeatures"], p["nlevels"], p["scale"])
     knames = ("pyramid", "fast_cells", "octree", "blur", "describe")
+    ser_stage, ser_steps = R["ser_stage"], R["ser_steps"]
     kstages = {k: ser_stage[k] for k in knames}
     dom = max(kstages, key=kstages.get)
-    per_chunk_launches = (p["nlevels"] - 1) + 4 + (1 if w % 16 else 0)   # + k_repitch when rows are not 16-byte multiples
-    chunks = max(1, int(round(ser_launches / per_chunk_launches)))
+    chunks = ser_steps * -(-n // R["ser_chunk"])               # the serialised pass cuts the batch into chunks of ser_chunk frames
     frames_per_launch = n * ser_steps / chunks
     launch_ms = kstages[dom] / chunks
     achieved = stage_bytes[dom] * frames_per_launch / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
     ktot = sum(kstages.values())
-    traffic, traffic_src = None, None
-    try:                                                      # dram bytes of that kernel from the committed ncu --set full capture
-        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = tj["dram_bytes_per_frame"][dom] * frames_per_launch
-        traffic_src = tj["source"]
-    except Exception:
-        tj = None
+    traffic, traffic_src, tj = None, None, None
+    if workload.startswith("C1"):
+        try:                                                  # dram bytes of that kernel from the committed ncu --set full capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            traffic = tj["dram_bytes_per_frame"][dom] * frames_per_launch
+            traffic_src = tj["source"]
+        except Exception:
+            tj = None
     issue = None
-    if tj and "warp_instructions_per_frame" in tj and WORKLOAD.startswith("C1"):
-        # the bound this integer path actually runs against: executed warp instructions per frame (ncu, same capture)
-        # against the SMs' issue rate at the clock sampled during the timed region
+    if with_issue and tj and "warp_instructions_per_frame" in tj:
         wi = sum(tj["warp_instructions_per_frame"].values())
-        peak_issue = 148 * 4 * (clocks.get("sm_mhz") or 1965) * 1e6
+        peak_issue = 148 * 4 * ((clocks or {}).get("sm_mhz") or 1965) * 1e6
         issue = {"warp_instructions_per_frame": wi, "issue_peak_per_s": peak_issue,
                  "achieved_per_s": value / world * wi, "frac": value / world * wi / peak_issue,
                  "per_kernel": tj["warp_instructions_per_frame"], "source": tj["source"]}
-    roofline = {
-        "bound": "hbm", "kernel": {"pyramid": "k_resize_level (x%d levels)" % (p["nlevels"] - 1), "fast_cells": "k_fast_cells",
+    return {
+        "bound": "hbm", "kernel": {"pyramid": "k_resize_level / k_resize_tail", "fast_cells": "k_fast_cells",
                                    "octree": "k_octree", "blur": "k_blur", "describe": "k_describe"}[dom],
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "traffic_source": traffic_src, "algorithmic_bytes_per_launch": stage_bytes[dom] * frames_per_launch,
         "peak_source": peak_src, "bytes_per_frame": stage_bytes[dom], "frames_per_launch": frames_per_launch,
-        "launch_ms": launch_ms,
+        "launch_ms": launch_ms, "launches_per_chunk": R["ser_launches"] / chunks,
         "kernel_share_of_step": {k: kstages[k] / ktot for k in knames},
         "stage_ms_per_step_serialized": {k: v / ser_steps for k, v in ser_stage.items()},
-        "serialized_frames_per_s": n * ser_steps / (ser_ms * 1e-3),
-        "stage_ms_per_step_overlapped": {k: v / args.steps for k, v in stage.items()},
+        "serialized_frames_per_s": n * ser_steps / (R["ser_ms"] * 1e-3),
+        "stage_ms_per_step_overlapped": {k: v / steps for k, v in R["stage"].items()},
         "per_kernel": {k: {"bytes_per_frame": stage_bytes[k], "launch_ms": kstages[k] / chunks,
                            "achieved_gbs": stage_bytes[k] * frames_per_launch / (kstages[k] / chunks * 1e-3) / 1e9 if kstages[k] > 0 else 0.0}
                        for k in knames},
@@ -535,90 +596,304 @@ def run_ours(args, rank, world, local_rank):
                 "(stage_ms_per_step_overlapped), so those per-stream times include sharing the GPU",
     }
 
+
+def e2e_of(R, steps, world):
+    frames = R["n"] * world * steps
+    async_value = frames / (max(R["async_ms"], R["async_wall_ms"]) * 1e-3)     # the slower of device events and host wall clock
+    sync_value = frames / (R["sync_ms"] * 1e-3)
+    out = {"value": async_value, "unit": UNIT, "h2d_bytes_per_step": R["h2d_bytes"] * world, "d2h_bytes_per_step": R["d2h_bytes"] * world,
+           "ms_per_step_events": R["async_ms"] / steps, "ms_per_step_wall": R["async_wall_ms"] / steps,
+           "api": "orbgpu_extract_batch_async x steps + orbgpu_wait (pinned host buffers)",
+           "synchronous_call_value": sync_value,
+           "synchronous_call_api": "orbgpu_extract_batch, one blocking call per step (reported beside the primary API, not used for `value`)"}
+    if "copy_ms" in R:
+        sec = R["copy_ms"] * 1e-3
+        out["copy_ceiling"] = {"frames_per_s": frames / sec, "h2d_gbs": R["h2d_bytes"] * world * steps / sec / 1e9,
+                               "d2h_gbs": R["d2h_bytes"] * world * steps / sec / 1e9,
+                               "what": "the same H2D and D2H bytes per step as plain cudaMemcpyAsync on two streams per GPU, no kernels, "
+                                       "all %d ranks at once; host wall clock, max over ranks" % world}
+        out["frac_of_copy_ceiling"] = async_value / out["copy_ceiling"]["frames_per_s"]
+    return out
+
+
+def frame_digests(kps, desc, nout):
+    """SHA-256 per frame over its keypoint records and descriptors (only the n_out valid ones)."""
+    import hashlib
+    out = np.empty((len(nout), 32), np.uint8)
+    for i, k in enumerate(nout):
+        hsh = hashlib.sha256(kps[i, :k].tobytes()); hsh.update(desc[i, :k].tobytes())
+        out[i] = np.frombuffer(hsh.digest(), np.uint8)
+    return out
+
+
+def run_c3_sequence(ctx, pkg, shard_frames, total, args, steps, warmup):
+    """BASELINE config 3 as written: ONE 752x480 sequence of `total` frames, frame i on rank i mod G (strong scaling: the
+    per-GPU batch shrinks with G).  Per-frame SHA-256 digests are all-gathered and folded in frame order; rank 0 then
+    extracts the whole sequence alone (G = 1) and the two hashes must agree."""
+    import hashlib
+    torch, dist = ctx.torch, ctx.dist
+    R = measure_extraction(ctx, pkg, shard_frames, 1000, steps, warmup, args, serial_pass=False, copy_probe=False, keep_results=True)
+    dig = frame_digests(R["kps"], R["desc"], R["nout"])
+    w, h = R["w"], R["h"]
+    if ctx.world > 1:
+        per = total // ctx.world
+        t = torch.from_numpy(dig).cuda()
+        allg = torch.empty((ctx.world, per, 32), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(allg, t)
+        ordered = allg.permute(1, 0, 2).contiguous().cpu().numpy()            # frame i = (i // G)-th frame of rank i % G
+        fr = torch.from_numpy(np.ascontiguousarray(shard_frames)).cuda()
+        allf = torch.empty((ctx.world,) + tuple(fr.shape), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(allf, fr)
+        seq_hash = hashlib.sha256(ordered.tobytes()).hexdigest()
+        g1_hash = None
+        if ctx.rank == 0:
+            full = allf.permute(1, 0, 2, 3).contiguous()                       # the sequence in frame order, on rank 0's GPU
+            ex = pkg.ORBextractor(1000, PARAMS["scale"], PARAMS["nlevels"], PARAMS["ini_th"], PARAMS["min_th"], device=ctx.local_rank)
+            cap = ex.max_keypoints(w, h)
+            k = torch.empty((total, cap, 28), dtype=torch.uint8, device="cuda"); d = torch.empty((total, cap, 32), dtype=torch.uint8, device="cuda")
+            no = torch.empty((total,), dtype=torch.int32, device="cuda")
+            ex.extract_batch_ptr(full.data_ptr(), total, w, h, w, w * h, k.data_ptr(), d.data_ptr(), cap, no.data_ptr(), device=True)
+            g1 = frame_digests(k.cpu().numpy(), d.cpu().numpy(), no.cpu().numpy())
+            g1_hash = hashlib.sha256(g1.tobytes()).hexdigest()
+            ex.close()
+        del allf
+    else:
+        seq_hash = hashlib.sha256(dig.tobytes()).hexdigest()
+        g1_hash = seq_hash
+    frames = total * steps
+    out = {"workload": WORKLOADS["C3"][0], "sequence_frames": total, "sharding": "frame i -> rank i mod %d, no data-path collective" % ctx.world,
+           "scaling": "strong", "value": frames / (R["dev_ms"] * 1e-3), "unit": UNIT, "ms_per_step": R["dev_ms"] / steps,
+           "e2e": {"value": frames / (max(R["async_ms"], R["async_wall_ms"]) * 1e-3), "unit": UNIT,
+                   "h2d_bytes_per_step": R["h2d_bytes"] * ctx.world, "d2h_bytes_per_step": R["d2h_bytes"] * ctx.world},
+           "keypoints": int(ctx.sum(float(R["nkp"]))), "sha256_frames_in_order": seq_hash, "sha256_one_gpu": g1_hash,
+           "parity_vs_one_gpu": (seq_hash == g1_hash) if g1_hash is not None else None}
+    if ctx.rank == 0 and g1_hash is not None and seq_hash != g1_hash:
+        raise RuntimeError("C3: the sharded sequence differs from the one-GPU extraction")
+    return out, R
+
+
+def run_ours(args, rank, world, local_rank):
+    # ---- synthetic inputs first (fork pool, nothing has touched CUDA yet)
+    wl_name, nf = WORKLOADS[args.workload]
+    n = args.frames
+    procs = max(1, host_threads() // max(world, 1))
+    req = {"main": (wl_name, range(rank * n, rank * n + n))}
+    c3_total = SECONDARY_FRAMES["C3"]
+    secondary = args.workload == "C1" and not args.no_workloads
+    if secondary:
+        req["C3"] = (WORKLOADS["C3"][0], range(rank, c3_total, world))
+        if world == 1:
+            for k in ("C2", "C4"):
+                req[k] = (WORKLOADS[k][0], range(SECONDARY_FRAMES[k]))
+    frames = make_frames_parallel(req, procs)
+
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    pkg = g.load_package()
+    if not torch.cuda.is_available() or pkg.device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device visible; the orbgpu path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_cpus(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = Ctx(torch, dist, rank, world, local_rank)
+    w, h = SYNTH_CONFIGS[wl_name][0], SYNTH_CONFIGS[wl_name][1]
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    R = measure_extraction(ctx, pkg, frames.pop("main"), nf, args.steps, args.warmup, args, serial_pass=True,
+                           sustained_s=args.sustained_seconds)
+    clocks = sampler.stop()
+    total_frames = n * world * args.steps
+    value = total_frames / (R["dev_ms"] * 1e-3)
+
+    workloads = {}
+    if secondary:
+        c3, R3 = run_c3_sequence(ctx, pkg, frames.pop("C3"), c3_total, args, max(3, min(args.steps, 5)), 3)
+        workloads["C3"] = c3
+        if world == 1:
+            for k in ("C2", "C4"):
+                name, nfk = WORKLOADS[k]
+                st = max(3, min(args.steps, 5))
+                Rk = measure_extraction(ctx, pkg, frames.pop(k), nfk, st, 3, args, serial_pass=True, copy_probe=False)
+                vk = Rk["n"] * st / (Rk["dev_ms"] * 1e-3)
+                rk = roofline_of(Rk, name, st, 1, vk, clocks, False)
+                workloads[k] = {"workload": name, "config": config_of(name, nfk, Rk["w"], Rk["h"], Rk["n"]), "value": vk, "unit": UNIT,
+                                "ms_per_step": Rk["dev_ms"] / st, "steps": st, "e2e": e2e_of(Rk, st, 1), "keypoints_per_step": Rk["nkp"],
+                                "roofline": {kk: rk[kk] for kk in ("bound", "kernel", "achieved", "peak", "unit", "frac", "traffic", "bytes_per_frame",
+                                                                   "frames_per_launch", "launch_ms", "kernel_share_of_step", "path_achieved", "path_frac")}}
+
+    hamming = None
+    if args.hamming_keyframes != 0:
+        kf = args.hamming_keyframes if args.hamming_keyframes > 0 else (4096 if world >= 8 else 1024)
+        hamming = bench_hamming(pkg, ctx, kf, 1000, cpu=(world == 1 and not args.no_cpu))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": R["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "nfeatures": nf, "nlevels": p["nlevels"], "scale": p["scale"],
-                   "ini_th": p["ini_th"], "min_th": p["min_th"], "width": w, "height": h,
-                   "frames_per_step_per_gpu": n, "parallelism": "frames sharded %d-way, no data-path collective" % world,
-                   "l2": "inputs larger than L2: %.0f MB of frames per step vs %.0f MB L2" % (n * w * h / 1e6, L2_BYTES / 1e6),
-                   "keypoints_per_step_per_gpu": nkp_dev, "host_affinity": numa},
+        "config": config_of(wl_name, nf, w, h, n),
+        "run": {"parallelism": "frames sharded %d-way, no data-path collective" % world,
+                "keypoints_per_step_per_gpu": R["nkp"], "host_affinity": numa, "host_threads": len(all_cpus)},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * w * h * world,
-                "d2h_bytes_per_step": (n * cap * 60 + 4 * n) * world,
-                "ms_per_step_events": e2e_ms / args.steps, "ms_per_step_wall": wall_e2e_ms / args.steps,
-                "api": ("orbgpu_extract_batch_async x steps + orbgpu_wait" if async_value >= sync_value
-                        else "orbgpu_extract_batch, one synchronous call per step") + " (pinned host buffers)",
-                "async_api_value": async_value, "synchronous_call_value": sync_value},
-        "gpu_launches": int(total_launches),
-        "wall_ms_per_step": wall_dev_ms / args.steps,
-        "roofline": roofline,
+        "e2e": e2e_of(R, args.steps, world),
+        "gpu_launches": int(R["launches"]),
+        "wall_ms_per_step": R["wall_dev_ms"] / args.steps,
+        "roofline": roofline_of(R, wl_name, args.steps, world, value, clocks, True),
     }
+    if "sustained" in R:
+        line["sustained"] = R["sustained"]
+    if workloads:
+        line["workloads"] = workloads
     if hamming is not None:
         line["hamming"] = hamming
     os.sched_setaffinity(0, all_cpus)                         # the CPU legs use every host core again
     if world == 1 and not args.no_cpu:
         threads = host_threads()
         sample = max(32, 4 * threads)
-        fps, kind, sec, done = cpu_extractor_fps(make_frames(pkg, sample, 0), threads if True else 1, args.cpu_seconds)
+        cpu_frames = make_frames(pkg, sample, 0)
+        fps, kind, sec, done = cpu_extractor_fps(cpu_frames, threads, args.cpu_seconds)
         line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads if kind == "reference" else 1, "kind": kind,
                                 "sample": "%d synthetic %dx%d frames x %d passes = %.1f s on %d threads (one extractor per thread); CPU %s"
                                           % (sample, w, h, done // sample, sec, threads if kind == "reference" else 1, cpu_model())}
         if kind == "reference":
-            fps1, _, sec1, done1 = cpu_extractor_fps(make_frames(pkg, 16, 0), 1, min(args.cpu_seconds, 5.0))
+            fps1, _, sec1, done1 = cpu_extractor_fps(cpu_frames[:16], 1, min(args.cpu_seconds, 5.0))
             line["cpu_baseline"]["single_thread_value"] = fps1
-        line["cpu_baseline"]["opencv_primitives"] = cv2_primitives(make_frames(pkg, 8, 0), level_sizes(w, h, PARAMS["nlevels"], PARAMS["scale"]), threads)
+        line["cpu_baseline"]["opencv_primitives"] = cv2_primitives(cpu_frames[:8], level_sizes(w, h, PARAMS["nlevels"], PARAMS["scale"]), threads)
+        for k, wl in workloads.items():                       # short CPU legs of the other shapes (about 2 s each)
+            name, nfk = WORKLOADS[k]
+            PARAMS["nfeatures"] = nfk
+            smp = make_frames_of(pkg, name, max(16, threads), 0)
+            fpsk, kindk, seck, donek = cpu_extractor_fps(smp, threads, 2.0)
+            wl["cpu_baseline"] = {"value": fpsk, "unit": UNIT, "cores": threads if kindk == "reference" else 1, "kind": kindk,
+                                  "sample": "%d frames x %d passes = %.1f s" % (len(smp), donek // len(smp), seck)}
+            PARAMS["nfeatures"] = nf
     if world > 1:
         dist.destroy_process_group()
     print(json.dumps(line), flush=True)
     return 0
 
 
-def bench_hamming(pkg, torch, dist, rank, world, local_rank, num_keyframes, n_per_kf, reps=3):
-    """All-pairs keyframe matching (BASELINE config 5 shape, K keyframes x n descriptors): every rank holds all
-    descriptors, owns round-robin blocks of the upper-triangular pair list, counts accepted matches per pair
-    (best <= TH_LOW && best < 0.6 * second) and the counts are exchanged with ONE all_gather (NCCL)."""
+def make_frames_of(pkg, name, count, start):
+    w, h, _, base, _ = pkg.synth.CONFIGS[name]
+    return np.stack([pkg.synth.synth(w, h, base + start + i) for i in range(count)])
+
+
+def bench_hamming(pkg, ctx, num_keyframes, n_per_kf, reps=3, cpu=False):
+    """All-pairs keyframe matching (BASELINE config 5: K keyframes x n descriptors) through the C ABI's sharded entry point
+    (orbgpu_matcher_all_pairs_sharded): every rank holds all descriptors and owns round-robin blocks of the upper-triangular
+    pair list (block size adapted to the pair count so that every rank gets at least 16 blocks), counts accepted matches
+    per pair (best <= TH_LOW && best < 0.6 * second); the counts are exchanged with ONE ncclAllGather issued from C++ on the
+    kernel's own stream and put in pair order by one scatter kernel.  The first pass is also checked against the
+    torch.distributed gather of the per-rank counts (my-slam_b200/shard.py)."""
+    torch, dist, rank, world = ctx.torch, ctx.dist, ctx.rank, ctx.world
     shard = pkg.shard
+    L = pkg.lib()
     desc = pkg.synth.keyframe_descriptors(num_keyframes, n_per_kf)
-    pairs = shard.all_pairs(num_keyframes)
-    block = 4096
-    mine = np.concatenate([pairs[s:e] for s, e in shard.pair_blocks_of_rank(len(pairs), rank, world, block)] or
-                          [np.zeros((0, 2), np.int32)])
-    m = pkg.ORBmatcher(0.6, True, device=local_rank)
+    npairs = num_keyframes * (num_keyframes - 1) // 2
+    block = shard.adaptive_pair_block(npairs, world)
+    m = pkg.ORBmatcher(0.6, True, device=ctx.local_rank)
     d_desc = torch.from_numpy(desc).cuda()
     m.set_keyframes_device(d_desc.data_ptr(), num_keyframes, n_per_kf)
-    d_pairs = torch.from_numpy(np.ascontiguousarray(mine)).cuda()
-    d_counts = torch.zeros((max(len(mine), 1),), dtype=torch.int32, device="cuda")
-    best_ms, gather_ms, full = None, 0.0, None
-    for _ in range(reps + 1):                                  # first pass = warm-up
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        e0.record()
-        if len(mine):
-            m.count_pairs_device(d_pairs.data_ptr(), len(mine), d_counts.data_ptr())   # synchronous; kernel on the matcher's stream
-        e1.record()
-        full = shard.gather_pair_counts(d_counts[:len(mine)], len(pairs), rank, world, block, dist=dist, device="cuda")
-        e2.record()
-        torch.cuda.synchronize()
-        k_ms = m.last_kernel_ms() if len(mine) else 0.0
-        g_ms = e1.elapsed_time(e2)
-        t = torch.tensor([k_ms + g_ms, k_ms, g_ms], dtype=torch.float64, device="cuda")
+    comm = None
+    if world > 1:                                              # rank 0's NCCL id reaches the other ranks through torch.distributed (plumbing)
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(pkg.Comm.unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        comm = pkg.Comm(ctx.local_rank, rank, world, bytes(idt.cpu().numpy().tobytes()))
+    d_full = torch.full((npairs,), -1, dtype=torch.int32, device="cuda")
+    best, times = None, []
+    for rep in range(reps + 1):                                # first pass = warm-up (pair lists, NCCL channels)
+        ctx.barrier()
+        k_ms, g_ms, tot = m.all_pairs_sharded(comm, d_full.data_ptr())
+        t = torch.tensor([tot, k_ms, -k_ms], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        tot, k_ms, g_ms = [float(x) for x in t.tolist()]
-        if best_ms is None or tot < best_ms[0]:
-            best_ms = (tot, k_ms, g_ms)
+        tot_w, k_max, neg_k_min = [float(x) for x in t.tolist()]
+        if rep > 0 and (best is None or tot_w < best[0]):
+            best = (tot_w, k_max, -neg_k_min)
+        if rep == 0:                                           # cross-check: the same counts through the Python-side sharding + torch gather
+            pairs = shard.all_pairs(num_keyframes)
+            mine = shard.pairs_of_rank(pairs, rank, world, block)
+            plan = shard.gather_plan(npairs, world, block, device="cuda")
+            d_pairs = torch.from_numpy(mine).cuda()
+            d_counts = torch.zeros((max(len(mine), 1),), dtype=torch.int32, device="cuda")
+            if len(mine):
+                m.count_pairs_device(d_pairs.data_ptr(), len(mine), d_counts.data_ptr())
+            full2 = shard.gather_pair_counts(d_counts[:len(mine)], plan, dist=dist if world > 1 else None)
+            if not torch.equal(full2, d_full):
+                raise RuntimeError("Hamming: C++ ncclAllGather path and torch.distributed gather disagree")
+            del pairs, mine, plan, d_pairs, d_counts, full2
+    full = d_full
+    tot, k_ms, k_min = best
+    g_ms = tot - k_ms                                          # everything after the slowest rank's kernel: all_gather + scatter
+    brk = {"kernel_ms_slowest_rank": k_ms, "kernel_ms_fastest_rank": k_min, "imbalance_ms": k_ms - k_min,
+           "all_gather_plus_scatter_ms_after_slowest_kernel": g_ms, "gather_frac_of_kernel": g_ms / k_ms if k_ms > 0 else None,
+           "note": "total = CUDA events on the matcher's stream from before the kernel to after the scatter, max over ranks; a rank "
+                   "that finishes its kernel early waits inside ncclAllGather for the slowest one, which is imbalance, not NCCL time"}
+    if comm is not None:
+        comm.close()
     m.close()
-    tot, k_ms, g_ms = best_ms
-    npairs = len(pairs)
-    return {"metric": "hamming_query_matches_per_s", "value": npairs * n_per_kf / (tot * 1e-3), "unit": "matches/s",
-            "distance_evals_per_s": npairs * float(n_per_kf) * n_per_kf / (tot * 1e-3), "keyframes": num_keyframes,
-            "descriptors_per_keyframe": n_per_kf, "pairs": npairs, "kernel_ms": k_ms, "gather_ms": g_ms,
-            "gather": "one all_gather of int32 counts (NCCL)" if world > 1 else "none (1 GPU)",
-            "accepted_total": int(full.clamp(min=0).sum().item()), "timing": "best of %d, max over ranks" % reps}
+    dist_per_s = npairs * float(n_per_kf) * n_per_kf / (tot * 1e-3)
+    out = {"metric": "hamming_query_matches_per_s", "value": npairs * n_per_kf / (tot * 1e-3), "unit": "matches/s",
+           "distance_evals_per_s": dist_per_s, "keyframes": num_keyframes,
+           "descriptors_per_keyframe": n_per_kf, "pairs": npairs, "pair_block": block, "kernel_ms": k_ms, "gather_ms": g_ms, "total_ms": tot,
+           "gather": "one ncclAllGather of int32 counts issued from C++ on the kernel's stream + one scatter kernel" if world > 1 else "none (1 GPU)",
+           "api": "orbgpu_matcher_all_pairs_sharded", "breakdown": brk, "accepted_total": int(full.clamp(min=0).sum().item()),
+           "timing": "best of %d, max over ranks; CUDA events on the matcher's stream" % reps}
+    if rank == 0:
+        # roofline of k_match_count_pairs: thread-level POPC per second against the measured POPC rate of this GPU
+        pk = C.c_double(0.0); lk = C.c_double(0.0)
+        L.orbgpu_debug_pipe_peak(ctx.local_rank, 0, C.byref(pk)); L.orbgpu_debug_pipe_peak(ctx.local_rank, 1, C.byref(lk))
+        popc_per_dist = POPC_PER_DISTANCE
+        kernel_dist_per_s = npairs / world * float(n_per_kf) * n_per_kf / (k_ms * 1e-3)     # one GPU's kernel
+        hbm, _ = load_peaks()
+        out["roofline"] = {"bound": "popc", "kernel": "k_match_count_pairs", "achieved": kernel_dist_per_s * popc_per_dist, "peak": pk.value,
+                           "unit": "POPC/s", "frac": kernel_dist_per_s * popc_per_dist / pk.value if pk.value else None,
+                           "popc_per_distance": popc_per_dist, "peak_source": "measured here: orbgpu_debug_pipe_peak (register-only POPC kernel, best of 3)",
+                           "alu_pipe": {"ops_per_distance": ALU_PER_DISTANCE, "achieved": kernel_dist_per_s * ALU_PER_DISTANCE, "peak": lk.value,
+                                        "frac": kernel_dist_per_s * ALU_PER_DISTANCE / lk.value if lk.value else None,
+                                        "what": "LOP3 / VIMNMX / IADD3 share the ALU pipe; peak = measured LOP3 rate (orbgpu_debug_pipe_peak)"},
+                           "hbm": {"bytes_per_pair": 64 * n_per_kf, "achieved_gbs": npairs / world * 64.0 * n_per_kf / (k_ms * 1e-3) / 1e9, "peak_gbs": hbm,
+                                   "frac": npairs / world * 64.0 * n_per_kf / (k_ms * 1e-3) / 1e9 / hbm}}
+    if cpu and rank == 0:
+        import oracle_lib
+        po = oracle_lib.OraclePort()
+        sub = 64
+        sdesc = np.ascontiguousarray(desc[:sub]); spairs = shard.all_pairs(sub)
+        threads = host_threads()
+        legs = {}
+        ref_counts = None
+        for name, popcnt, thr, cnt in (("swar_1_thread", False, 1, 96), ("popcnt_1_thread", True, 1, 192),
+                                       ("swar_all_threads", False, threads, len(spairs)), ("popcnt_all_threads", True, threads, len(spairs))):
+            c, sec = po.count_pairs_bench(sdesc, spairs[:cnt], 50, 0.6, threads=thr, popcnt=popcnt)
+            legs[name] = {"distance_evals_per_s": cnt * float(n_per_kf) * n_per_kf / sec, "matches_per_s": cnt * n_per_kf / sec,
+                          "threads": thr, "pairs": cnt, "seconds": sec}
+            if cnt == len(spairs):
+                ref_counts = c
+        # the GPU counts of the same pairs (pairs of keyframes < 64 in the full upper-triangular list) must equal the CPU's
+        idx = np.array([a * num_keyframes - a * (a + 1) // 2 + (b - a - 1) for a, b in spairs], np.int64)
+        same = bool(np.array_equal(full.cpu().numpy()[idx], ref_counts))
+        out["cpu_baseline"] = {"value": legs["swar_all_threads"]["matches_per_s"], "unit": "matches/s", "cores": threads, "kind": "port",
+                               "sample": "all %d pairs of the first %d keyframes (1-thread legs: the first 96 / 192 pairs); the M2 scan of "
+                                         "src/ORBmatcher.cc:201-226 with DescriptorDistance as written (SWAR, :1647-1663) and with the popcnt "
+                                         "instruction; CPU %s" % (len(spairs), sub, cpu_model()),
+                               "legs": legs, "counts_equal_gpu": same}
+        if not same:
+            raise RuntimeError("Hamming: GPU pair counts differ from the CPU oracle on the 64-keyframe subset")
+    return out
+
+
+POPC_PER_DISTANCE = 4          # hamming256_t in csrc/orb_match.cu
+ALU_PER_DISTANCE = 16.5        # 14 LOP3 + 1.5 VIMNMX.U16x2 + 1 IADD3 per distance in the inner loop (SASS, profiles/)
 
 
 def main():
@@ -630,22 +905,28 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_STEP, help="frames per step per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="wall time budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--hamming-keyframes", type=int, default=384, help="keyframes of the all-pairs Hamming leg (0 = skip; 4096 = full config 5)")
+    ap.add_argument("--hamming-keyframes", type=int, default=-1,
+                    help="keyframes of the all-pairs Hamming leg (0 = skip; -1 = 1024 below 8 GPUs, the full config 5 = 4096 at 8 GPUs)")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the C2 / C3 / C4 lines")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the sustained device-resident loop (0 = skip)")
     ap.add_argument("--streams", type=int, default=0, help="internal chunk streams; 0 = library default")
     ap.add_argument("--chunk", type=int, default=0, help="max frames per chunk; 0 = library default")
     ap.add_argument("--workload", default="C1", choices=["C1", "C2", "C3", "C4"],
                     help="BASELINE.json extraction config (default C1 = the shape the metric is quoted on)")
     args = ap.parse_args()
     global WORKLOAD, METRIC
-    WORKLOAD = {"C1": "C1_tum_640x480_nf1000", "C2": "C2_kitti_1241x376_nf2000", "C3": "C3_euroc_752x480_nf1000",
-                "C4": "C4_hd_1920x1080_nf4000"}[args.workload]
-    PARAMS["nfeatures"] = {"C1": 1000, "C2": 2000, "C3": 1000, "C4": 4000}[args.workload]
+    WORKLOAD, PARAMS["nfeatures"] = WORKLOADS[args.workload]
     if args.workload != "C1":
         METRIC = "orb_extract_frames_per_s_" + WORKLOAD.split("_", 1)[1]
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "ours" and world == 1 and args.gpus > 1:
+        # convenience: python bench.py --gpus N re-launches itself under torchrun (before stdout is rerouted below)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
     # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr
     sys.stdout.flush()
     real_stdout = os.fdopen(os.dup(1), "w")
@@ -653,11 +934,6 @@ def main():
     sys.stdout = real_stdout
     if args.impl == "reference":
         return run_reference(args, rank)
-    if world == 1 and args.gpus > 1:
-        # convenience: python bench.py --gpus N re-launches itself under torchrun
-        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
-               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
-        return subprocess.call(cmd)
     return run_ours(args, rank, world, local_rank)
 
 

@@ -71,7 +71,8 @@ int orbgpu_extract(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t
 
 /* Same operator over n same-shape frames (frame i at frames + i*frame_stride, rows row_stride apart),
  * host buffers; H2D copy, kernels and D2H copy of successive chunks overlap on internal streams.
- * Output for frame i: kps + i*capacity, desc + i*capacity*32, n_out[i].  Pinned (cudaHostAlloc /
+ * Output for frame i: kps + i*capacity, desc + i*capacity*32, n_out[i]; records at index n_out[i] and beyond are
+ * undefined (pinned output buffers receive whole rows of the device arrays).  Pinned (cudaHostAlloc /
  * cudaHostRegister) caller buffers are used in place; pageable ones are staged through the
  * library's pinned ring. */
 int orbgpu_extract_batch(orbgpu_extractor* e, const uint8_t* frames, int n, int w, int h,
@@ -89,6 +90,14 @@ int orbgpu_extract_batch_async(orbgpu_extractor* e, const uint8_t* frames, int n
                                size_t row_stride, size_t frame_stride,
                                orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
 int orbgpu_wait(orbgpu_extractor* e);
+
+/* orbgpu_extract_batch over several GPUs of one process: handle r (created on its own device) extracts the r-th contiguous
+ * block of the n frames on its own host thread, results land in the caller's arrays in frame order.  Frames are
+ * independent, so nothing is exchanged between the GPUs (the one-extractor-per-thread pattern of src/Frame.cc:78-81 with
+ * one GPU per thread).  Returns the first error of any handle. */
+int orbgpu_extract_batch_multi(orbgpu_extractor** handles, int num_handles, const uint8_t* frames, int n, int w, int h,
+                               size_t row_stride, size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity,
+                               int* n_out);
 
 /* Same, with every buffer already resident in device memory (frames, kps, desc, n_out are device
  * pointers of this extractor's device).  Returns after the work has completed. */
@@ -419,6 +428,14 @@ double orbgpu_last_batch_ms(orbgpu_extractor* e);
  * successive chunks overlap.  streams = 1 serialises the chunks (per-stage event times are then those of
  * each kernel running alone).  Small chunks keep a chunk's pyramid + blurred levels inside L2. */
 int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames);
+/* Largest chunk (frames) the device buffers of one stream context hold for this shape: min(64, 1.5 GB / bytes per frame). */
+int orbgpu_chunk_capacity(orbgpu_extractor* e, int w, int h);
+
+/* Host-buffer entry points (orbgpu_extract, _batch, _batch_async, orbgpu_submit) replay the kernels of a chunk from a CUDA
+ * graph captured on first use per (stream context, frame count): one graph launch per chunk instead of 11 kernel launches
+ * and 4 event calls from the host thread.  on = 0 switches back to direct launches (default on; profiling mode always
+ * launches directly so that the stage events bracket one kernel each).  Results are identical either way. */
+int orbgpu_set_graphs(orbgpu_extractor* e, int on);
 
 /* ---- matcher ------------------------------------------------------------------------------- */
 
@@ -460,6 +477,27 @@ int orbgpu_matcher_count_pairs(orbgpu_matcher* m, const int32_t* kf_a, const int
 /* device-resident variant: d_pairs = num_pairs x (a, b) int32 pairs, d_counts int32[num_pairs] */
 int orbgpu_matcher_count_pairs_device(orbgpu_matcher* m, const int32_t* d_pairs, int num_pairs,
                                       int th_low, float ratio, int32_t* d_counts);
+/* All-pairs keyframe matching sharded over GPUs (BASELINE config 5: "pair blocks sharded over 8 B200 with NCCL result
+ * gather"; the one-extractor-per-thread pattern of src/Frame.cc:78-81 carried over to one matcher per GPU).  Every rank's
+ * matcher holds ALL keyframes; the upper-triangular pair list (a < b, row-major, K (K - 1) / 2 pairs) is cut into blocks of
+ * min(4096, pairs / (16 world)) pairs dealt round-robin to the ranks; each rank counts its pairs and the counts are
+ * exchanged with ONE ncclAllGather enqueued on the kernel's own stream (no host synchronisation between the last tile
+ * and the gather) and put in pair order by one scatter kernel.  d_counts = device int32[K (K - 1) / 2] on every rank;
+ * ms3 (may be NULL) = kernel, gather + scatter, total milliseconds (CUDA events on that stream).  NCCL is bound at run
+ * time (dlopen libnccl.so.2); without it the comm calls return ORBGPU_ERR_UNSUPPORTED.
+ *  - one process per GPU: rank 0 calls orbgpu_comm_unique_id (128 bytes), hands the id to the other ranks by any means,
+ *    every rank calls orbgpu_comm_init_rank and then orbgpu_matcher_all_pairs_sharded (collective: all ranks call it);
+ *    comm == NULL runs the single-GPU form (no NCCL);
+ *  - one process, n GPUs: orbgpu_comm_init_all(comms, devices, n) and orbgpu_matcher_all_pairs_multi from ONE host
+ *    thread (matcher r on devices[r]; the gather is one ncclGroup). */
+typedef struct orbgpu_comm orbgpu_comm;
+int orbgpu_comm_unique_id(void* id128);
+int orbgpu_comm_init_rank(orbgpu_comm** out, int device, int rank, int world, const void* id128);
+int orbgpu_comm_init_all(orbgpu_comm** out, const int* devices, int n);
+void orbgpu_comm_destroy(orbgpu_comm* c);
+int orbgpu_matcher_all_pairs_sharded(orbgpu_matcher* m, orbgpu_comm* c, int th_low, float ratio, int32_t* d_counts, double* ms3);
+int orbgpu_matcher_all_pairs_multi(orbgpu_matcher** ms, orbgpu_comm** cs, int n, int th_low, float ratio, int32_t** d_counts,
+                                   double* ms3);
 /* milliseconds of the most recent count_pairs kernel (CUDA events on its stream) */
 double orbgpu_matcher_last_kernel_ms(orbgpu_matcher* m);
 
@@ -558,6 +596,13 @@ int orbgpu_bowdb_clear(orbgpu_bowdb* db);
 int orbgpu_bowdb_size(const orbgpu_bowdb* db);
 int orbgpu_bowdb_query(orbgpu_bowdb* db, const uint32_t* qw, const double* qv, int nq, int32_t* common_words,
                        int32_t* first_common, double* scores);
+
+/* Measured instruction-rate ceilings behind the roofline of the matching kernels (SURVEY.md section 8(d) asks for a
+ * popc micro-benchmark beside the HBM figure; the reference has no counterpart): which = 0 thread-level POPC per second,
+ * which = 1 thread-level LOP3 per second, best of three launches of a register-only kernel (8 CTAs of 256 threads per SM,
+ * eight independent chains per thread), CUDA events on the launching stream.  k_match_* spends 5 POPC per 256-bit distance
+ * (src/ORBmatcher.cc:1647-1663 spends 8 SWAR popcounts). */
+int orbgpu_debug_pipe_peak(int device, int which, double* ops_per_s);
 
 /* ---- misc ---------------------------------------------------------------------------------- */
 const char* orbgpu_strerror(int code);

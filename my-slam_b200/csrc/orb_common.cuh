@@ -23,6 +23,31 @@
 #endif
 #ifndef ORB_BLUR_THREADS
 #define ORB_BLUR_THREADS 128 // tasks per k_blur CTA
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (kernel, DEVICE): the opt-in is remembered per device
+// ordinal, behind a mutex, so that handles on several GPUs of one process -- possibly on different host threads -- each
+// raise the limit on their own device.  One instance per kernel (a function-local static at the launch site).
+#include <mutex>
+struct OrbSmemOptIn {
+    std::mutex mu;
+    int configured[64] = {};
+    template <class K>
+    cudaError_t ensure(K kernel, int bytes)
+    {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+        std::lock_guard<std::mutex> lk(mu);
+        if (bytes > configured[dev]) {
+            e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (e != cudaSuccess) return e;
+            configured[dev] = bytes;
+        }
+        return cudaSuccess;
+    }
+};
+
 #endif
 
 struct OrbLevel {

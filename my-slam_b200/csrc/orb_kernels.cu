@@ -105,13 +105,18 @@ int orb_launch_repitch(const uint8_t* src, long long src_frame_stride, int src_p
 // WORDS: the 4 pixel pairs lie inside three aligned words starting at word wb.  Pixel j's pair (bytes o_j, o_j + 1
 // of the 12-byte window) is cut out by one PRMT whose selector sel[j] was fixed at thread start; lowpair[j] tells
 // whether it lies in words (0,1) or (1,2).
-template <bool WORDS>
+// NC: the source level was written by an earlier launch and may be read through the non-coherent path (__ldg); the
+// fused tail kernel reads levels it wrote itself a barrier ago and must use ordinary loads.
+template <bool NC> __device__ __forceinline__ unsigned rs_ldw(const uint32_t* p) { return NC ? __ldg(p) : *p; }
+template <bool NC> __device__ __forceinline__ unsigned rs_ldb(const uint8_t* p) { return NC ? (unsigned)__ldg(p) : (unsigned)*p; }
+
+template <bool WORDS, bool NC>
 __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int wb, int wlast, const int s[4], const unsigned sel[4],
                                             const bool lowpair[4], const unsigned a01[4], int sw, int H[4])
 {
     if (WORDS) {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(row);
-        const unsigned w0 = __ldg(p + wb), w1 = __ldg(p + min(wb + 1, wlast)), w2 = __ldg(p + min(wb + 2, wlast));
+        const unsigned w0 = rs_ldw<NC>(p + wb), w1 = rs_ldw<NC>(p + min(wb + 1, wlast)), w2 = rs_ldw<NC>(p + min(wb + 2, wlast));
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const unsigned pair = __byte_perm(lowpair[j] ? w0 : w1, lowpair[j] ? w1 : w2, sel[j]);
@@ -120,15 +125,16 @@ __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int
     } else {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            H[j] = (int)(__ldg(row + s[j]) * (a01[j] & 0xFFFFu) + __ldg(row + min(s[j] + 1, sw - 1)) * (a01[j] >> 16));
+            H[j] = (int)(rs_ldb<NC>(row + s[j]) * (a01[j] & 0xFFFFu) + rs_ldb<NC>(row + min(s[j] + 1, sw - 1)) * (a01[j] >> 16));
     }
 }
 
 #define RS_SRC_ROWS 12        // source rows one strip of RS_ROWS output rows may touch on the shared-memory path
 
-template <bool WORDS>
-__device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel& D, const uint8_t* __restrict__ src, int sp,
-                                             int sw, int sh, uint8_t* __restrict__ dst, int wc, int y0, const int s[4],
+// s_h: this thread's private shared-memory column, rows STRIDE entries apart
+template <bool WORDS, bool NC, int STRIDE>
+__device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel& D, const uint8_t* src, int sp,
+                                             int sw, int sh, uint8_t* dst, int wc, int y0, const int s[4],
                                              const unsigned sel[4], const bool lowpair[4], const unsigned a01[4], int wb,
                                              int wlast, uint2* s_h)
 {
@@ -145,7 +151,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
     if (rlast - rfirst < RS_SRC_ROWS) {
         // every source row of the strip exactly once: H rows go to this thread's private shared-memory column
         // (no reuse logic, no divergence, all row loads independent), then the vertical pass reads two of them
-        uint2* hcol = s_h + threadIdx.x;                       // H >> 4 <= 32640: two 16-bit values per word
+        uint2* hcol = s_h;                                     // H >> 4 <= 32640: two 16-bit values per word
         if (WORDS) {
             // six rows at a time: their 18 word loads are issued before the first use (row indices clamped to the last
             // needed row instead of a branch per row, which kept each row's loads behind the previous row's arithmetic)
@@ -156,7 +162,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
                     const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)min(rfirst + h + i, rlast) * sp);
-                    w0[i] = __ldg(p + wb); w1[i] = __ldg(p + wb1); w2[i] = __ldg(p + wb2);
+                    w0[i] = rs_ldw<NC>(p + wb); w1[i] = rs_ldw<NC>(p + wb1); w2[i] = rs_ldw<NC>(p + wb2);
                 }
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
@@ -166,7 +172,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
                         const unsigned pair = __byte_perm(lowpair[j] ? w0[i] : w1[i], lowpair[j] ? w1[i] : w2[i], sel[j]);
                         H[j] = (int)__dp2a_lo(a01[j], pair, 0u);
                     }
-                    hcol[(h + i) * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+                    hcol[(h + i) * STRIDE] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
                 }
             }
         } else {
@@ -174,8 +180,8 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
             for (int i = 0; i < RS_SRC_ROWS; ++i) {
                 if (rfirst + i <= rlast) {
                     int H[4];
-                    resize_hrow<WORDS>(src + (size_t)(rfirst + i) * sp, wb, wlast, s, sel, lowpair, a01, sw, H);
-                    hcol[i * RS_THREADS] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
+                    resize_hrow<WORDS, NC>(src + (size_t)(rfirst + i) * sp, wb, wlast, s, sel, lowpair, a01, sw, H);
+                    hcol[i * STRIDE] = make_uint2(__byte_perm(H[0] >> 4, H[1] >> 4, 0x5410), __byte_perm(H[2] >> 4, H[3] >> 4, 0x5410));
                 }
             }
         }
@@ -184,8 +190,8 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
             const int dy = y0 + k;
             if (dy < D.h) {
                 const int b0 = (int)(b01[k] & 0xFFFFu), b1 = (int)(b01[k] >> 16);
-                const uint2 A = hcol[(min(max(sy[k], 0), sh - 1) - rfirst) * RS_THREADS];
-                const uint2 B = hcol[(min(max(sy[k] + 1, 0), sh - 1) - rfirst) * RS_THREADS];
+                const uint2 A = hcol[(min(max(sy[k], 0), sh - 1) - rfirst) * STRIDE];
+                const uint2 B = hcol[(min(max(sy[k] + 1, 0), sh - 1) - rfirst) * STRIDE];
                 const int v0 = (((b0 * (int)(A.x & 0xFFFFu)) >> 16) + ((b1 * (int)(B.x & 0xFFFFu)) >> 16) + 2) >> 2;
                 const int v1 = (((b0 * (int)(A.x >> 16)) >> 16) + ((b1 * (int)(B.x >> 16)) >> 16) + 2) >> 2;
                 const int v2 = (((b0 * (int)(A.y & 0xFFFFu)) >> 16) + ((b1 * (int)(B.y & 0xFFFFu)) >> 16) + 2) >> 2;
@@ -209,7 +215,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
             for (int j = 0; j < 4; ++j) Ha[j] = Hb[j];
             ya = yb;
         } else if (r0 != ya) {
-            resize_hrow<WORDS>(src + (size_t)r0 * sp, wb, wlast, s, sel, lowpair, a01, sw, Ha);
+            resize_hrow<WORDS, NC>(src + (size_t)r0 * sp, wb, wlast, s, sel, lowpair, a01, sw, Ha);
             ya = r0;
         }
         if (r1 == ya) {
@@ -217,7 +223,7 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
             for (int j = 0; j < 4; ++j) Hb[j] = Ha[j];
             yb = ya;
         } else if (r1 != yb) {
-            resize_hrow<WORDS>(src + (size_t)r1 * sp, wb, wlast, s, sel, lowpair, a01, sw, Hb);
+            resize_hrow<WORDS, NC>(src + (size_t)r1 * sp, wb, wlast, s, sel, lowpair, a01, sw, Hb);
             yb = r1;
         }
         uint32_t packed = 0;
@@ -230,23 +236,21 @@ __device__ __forceinline__ void resize_strip(const OrbPlanDev& P, const OrbLevel
     }
 }
 
-// One thread = 4 horizontally adjacent output pixels (one aligned 32-bit store per row) x RS_ROWS rows.  The
+// One task = 4 horizontally adjacent output pixels (one aligned 32-bit store per row) x RS_ROWS rows of level l.  The
 // x-axis table entries of the 4 pixels stay in registers; a source row costs three aligned word loads and
 // four IDP.2A dot products, and is reused when consecutive output rows share it.
-__global__ void __launch_bounds__(RS_THREADS, 8) k_resize_level(OrbPlanDev P, int l)
+template <bool NC, int STRIDE>
+__device__ __forceinline__ void resize_task(const OrbPlanDev& P, int l, int frame, int task, uint2* s_h)
 {
-    __shared__ uint2 s_h[RS_SRC_ROWS * RS_THREADS];            // [source row][thread]: H >> 4 of the thread's 4 pixels, 16 bits each
     const OrbLevel& D = P.lv[l];
-    const int frame = blockIdx.y;
     const int nwc = (D.w + 3) >> 2;
-    const int task = blockIdx.x * RS_THREADS + threadIdx.x;
     const int strip = task / nwc, wc = task - strip * nwc;
     const int y0 = strip * RS_ROWS;
     if (y0 >= D.h) return;
     const int sw = P.lv[l - 1].w, sh = P.lv[l - 1].h;
-    const uint8_t* __restrict__ src = orb_level_ptr(P, l - 1, frame);
+    const uint8_t* src = orb_level_ptr(P, l - 1, frame);
     const int sp = orb_level_pitch(P, l - 1);
-    uint8_t* __restrict__ dst = P.pyr + (long long)frame * P.pyr_frame_bytes + D.pyr_off;
+    uint8_t* dst = P.pyr + (long long)frame * P.pyr_frame_bytes + D.pyr_off;
 
     int s[4];
     unsigned a01[4];
@@ -272,16 +276,85 @@ __global__ void __launch_bounds__(RS_THREADS, 8) k_resize_level(OrbPlanDev P, in
     const int wlast = (sp >> 2) - 1;
     const bool words = ((sp & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 3) == 0) && (smax + 1 - 4 * wb <= 11) &&
                        (wb + 2 <= wlast || 4 * wlast + 3 >= min(smax + 1, sw - 1));
-    if (words) resize_strip<true>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
-    else resize_strip<false>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
+    if (words) resize_strip<true, NC, STRIDE>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
+    else resize_strip<false, NC, STRIDE>(P, D, src, sp, sw, sh, dst, wc, y0, s, sel, lowpair, a01, wb, wlast, s_h);
+}
+
+__global__ void __launch_bounds__(RS_THREADS, 8) k_resize_level(OrbPlanDev P, int l)
+{
+    __shared__ uint2 s_h[RS_SRC_ROWS * RS_THREADS];            // [source row][thread]: H >> 4 of the thread's 4 pixels, 16 bits each
+    resize_task<true, RS_THREADS>(P, l, blockIdx.y, blockIdx.x * RS_THREADS + threadIdx.x, s_h + threadIdx.x);
+}
+
+// The small levels in ONE launch: level l reads level l - 1, so every level used to be its own launch, and from about
+// 300 x 230 px down a launch is 7-9 us of launch floor for a grid of a few CTAs per frame.  Here a CLUSTER of RT_CLUSTER
+// CTAs owns one frame and walks the levels first .. nlevels - 1 with a cluster barrier in between (release / acquire at
+// cluster scope: the level just written by the sibling CTAs is visible); levels written inside this launch are read with
+// L2-coherent loads (ld.global.cg), never through the non-coherent path.
+#define RT_THREADS 512
+#ifndef RT_CLUSTER
+#define RT_CLUSTER 4
+#endif
+#ifndef RT_MINB
+#define RT_MINB 2
+#endif
+template <> __device__ __forceinline__ unsigned rs_ldw<false>(const uint32_t* p) { return __ldcg(p); }
+template <> __device__ __forceinline__ unsigned rs_ldb<false>(const uint8_t* p) { return (unsigned)__ldcg(p); }
+
+__global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS, RT_MINB) k_resize_tail(OrbPlanDev P, int first)
+{
+    extern __shared__ __align__(16) uint8_t rt_smem[];
+    uint2* s_h = reinterpret_cast<uint2*>(rt_smem) + threadIdx.x;
+    const int frame = blockIdx.x / RT_CLUSTER;
+    const int t0 = (blockIdx.x % RT_CLUSTER) * RT_THREADS + threadIdx.x;
+    for (int l = first; l < P.nlevels; ++l) {
+        const OrbLevel& D = P.lv[l];
+        const int ntask = ((D.w + 3) >> 2) * ((D.h + RS_ROWS - 1) / RS_ROWS);
+        for (int t = t0; t < ntask; t += RT_CLUSTER * RT_THREADS) resize_task<false, RT_THREADS>(P, l, frame, t, s_h);
+        if (l + 1 < P.nlevels) {                               // level l complete in every CTA of the cluster before level l + 1 reads it
+            asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        }
+    }
+}
+
+// first level of the fused tail: the first level whose grid is below RT_MAX_TASKS tasks per frame, if at least two
+// levels follow from there; nlevels = no tail
+// MEASURED AND SWITCHED OFF (B200, C1, profiles/r2_resize_tail_variants.txt): one 1024-thread CTA per frame 0.78 -> 0.91 ms
+// of pyramid time per 512 frames; clusters of 2 / 4 / 8 CTAs x 512 threads 0.75 / 0.82 / 1.05 ms, and with every variant the
+// overlapped pipeline LOSES 3-8 % (182 k -> 168-176 k frames/s): the tail's few long-lived, latency-bound CTAs sit on SMs
+// the other chunks' kernels would fill, while four tiny launches leave those SMs free.  Build with -DORB_RESIZE_TAIL=1 to
+// measure again.
+#ifndef ORB_RESIZE_TAIL
+#define ORB_RESIZE_TAIL 0
+#endif
+#define RT_MAX_TASKS 2400
+int orb_resize_tail_first(const OrbPlanDev& P)
+{
+#if !ORB_RESIZE_TAIL
+    return P.nlevels;
+#else
+    for (int l = 1; l < P.nlevels; ++l) {
+        const int ntask = ((P.lv[l].w + 3) / 4) * ((P.lv[l].h + RS_ROWS - 1) / RS_ROWS);
+        if (ntask <= RT_MAX_TASKS) return (P.nlevels - l >= 2) ? l : P.nlevels;
+    }
+    return P.nlevels;
+#endif
 }
 
 int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
 {
     int launches = 0;
-    for (int l = 1; l < P.nlevels; ++l) {
+    const int tail = orb_resize_tail_first(P);
+    for (int l = 1; l < tail; ++l) {
         const int ntask = ((P.lv[l].w + 3) / 4) * ((P.lv[l].h + RS_ROWS - 1) / RS_ROWS);
         k_resize_level<<<dim3((ntask + RS_THREADS - 1) / RS_THREADS, nframes), RS_THREADS, 0, st>>>(P, l);
+        ++launches;
+    }
+    if (tail < P.nlevels) {
+        const int smem = RS_SRC_ROWS * RT_THREADS * (int)sizeof(uint2);
+        static OrbSmemOptIn optin;
+        if (optin.ensure(k_resize_tail, smem) != cudaSuccess) return -1;
+        k_resize_tail<<<nframes * RT_CLUSTER, RT_THREADS, smem, st>>>(P, tail);
         ++launches;
     }
     return launches;
@@ -541,11 +614,8 @@ int orb_fast_smem_bytes(int max_cw, int max_ch)
 
 int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream_t st)
 {
-    static int configured = 0;
-    if (smem_bytes > configured) {
-        if (cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) return -1;
-        configured = smem_bytes;
-    }
+    static OrbSmemOptIn optin;
+    if (optin.ensure(k_fast_cells, smem_bytes) != cudaSuccess) return -1;
     dim3 grid((P.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes);
     k_fast_cells<<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P, smem_bytes / (FAST_WARPS * 2 * FAST_TP));
     return 1;
@@ -833,11 +903,8 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(OrbPlanDev P, int key_sm
 int orb_launch_octree(const OrbPlanDev& P, int nframes, int key_smem_cap, int node_smem_cap, cudaStream_t st)
 {
     const int smem = (int)((((size_t)7 * key_smem_cap + 15) & ~(size_t)15) + (size_t)OCT_NODE_BYTES * node_smem_cap + 64);
-    static int configured = 0;
-    if (smem > configured) {
-        if (cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
-        configured = smem;
-    }
+    static OrbSmemOptIn optin;
+    if (optin.ensure(k_octree, smem) != cudaSuccess) return -1;
     k_octree<<<dim3(P.nlevels, nframes), OCT_THREADS, smem, st>>>(P, key_smem_cap, node_smem_cap);
     return 1;
 }
@@ -865,11 +932,8 @@ int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N,
                              cudaStream_t st)
 {
     const int smem = (int)((((size_t)7 * key_smem_cap + 15) & ~(size_t)15) + (size_t)OCT_NODE_BYTES * node_smem_cap + 64);
-    static int configured = 0;
-    if (smem > configured) {
-        if (cudaFuncSetAttribute(k_octree_single, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
-        configured = smem;
-    }
+    static OrbSmemOptIn optin;
+    if (optin.ensure(k_octree_single, smem) != cudaSuccess) return -1;
     k_octree_single<<<1, OCT_THREADS, smem, st>>>(d_keys, n, W, H, N, n_ini, hx, node_cap, d_scratch, d_out, d_count,
                                                   key_smem_cap, node_smem_cap);
     return 1;

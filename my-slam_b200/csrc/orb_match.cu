@@ -6,13 +6,19 @@
 // float contraction: one thread owns one query descriptor in 8 registers, candidate descriptors are
 // staged in shared memory as uint4 pairs and broadcast to the warp.  No tensor cores.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
+#include <algorithm>
 #include <new>
+#include <vector>
 
 #include "../../include/orbgpu.h"
+#include "orb_common.cuh"
 
 #define MATCH_THREADS 128
 #define MATCH_TILE 128        // candidates staged per shared-memory tile (4 KB)
@@ -45,25 +51,76 @@ __device__ __forceinline__ int hamming256(const uint4& q0, const uint4& q1, cons
     return __popc(s1) + __popc(s2) + 2 * (__popc(k0) + __popc(k1) + __popc(k2));
 }
 
+// The scan kernels' distance: 4 POPC and 14 LOP3 per 256 bits.  ncu shows the scan bound by the ALU pipe (LOP3, 64
+// lanes / clk / SM) with POPC (XU pipe, 16 lanes / clk / SM) close behind, so both counts matter:
+//  * the three weight-2 carry words of hamming256 go through one more carry-save adder (2 LOP3) and come out as one
+//    weight-2 and one weight-4 word: 4 POPC instead of 5;
+//  * descriptors are held TRANSFORMED, t(c) = (c.x, c.x ^ c.y, c.x ^ c.y ^ c.z, c.w) per 128-bit half (the query in
+//    registers, the candidates in the shared-memory tile, transformed once when the tile is staged).  XOR commutes with
+//    the transform, so one LOP3 each gives x0 = q0 ^ c0, y = x0 ^ x1 and s = x0 ^ x1 ^ x2, and the carry of the group is
+//    the 3-input function  maj(x0, x1, x2) = y ? ~s : x0  (x0 != x1 makes the third input x2 = s ^ 1 decide, else x0):
+//    4 LOP3 per three-word group instead of 3 XOR + 2.
+__device__ __forceinline__ uint4 hamming_transform(const uint4& c) { return make_uint4(c.x, c.x ^ c.y, c.x ^ c.y ^ c.z, c.w); }
+
+__device__ __forceinline__ int hamming256_t(const uint4& q0, const uint4& q1, const uint4& c0, const uint4& c1)
+{
+    const unsigned xa = q0.x ^ c0.x, ya = q0.y ^ c0.y, sa = q0.z ^ c0.z, ka = (ya & ~sa) | (~ya & xa);
+    const unsigned xb = q1.x ^ c1.x, yb = q1.y ^ c1.y, sb = q1.z ^ c1.z, kb = (yb & ~sb) | (~yb & xb);
+    const unsigned x3 = q0.w ^ c0.w, x7 = q1.w ^ c1.w;
+    const unsigned s2 = csa_sum(x3, x7, sa), kc = csa_carry(x3, x7, sa);
+    const unsigned t0 = csa_sum(ka, kb, kc), f0 = csa_carry(ka, kb, kc);
+    return __popc(sb) + __popc(s2) + 2 * __popc(t0) + 4 * __popc(f0);
+}
+
 // (distance, index) packed as d << 22 | j: min over the packed value is the lowest distance and, among equal
 // distances, the lowest index -- the strict '<' update of src/ORBmatcher.cc:201-226.  Needs j < 2^22.
 #define MATCH_IDX_BITS 22
 #define MATCH_INIT ((256u << MATCH_IDX_BITS) | ((1u << MATCH_IDX_BITS) - 1u))
 
-// scan all nB candidates (index order) for this thread's query; the CTA cooperates on staging
+// Stage one tile of candidates in shared memory, transformed (hamming_transform).  The CTA cooperates.
+__device__ __forceinline__ void stage_tile(const uint4* __restrict__ B, int t0, int tn, uint4* s_tile)
+{
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * tn; i += MATCH_THREADS) s_tile[i] = hamming_transform(__ldg(B + 2 * (size_t)t0 + i));
+    __syncthreads();
+}
+
+// Best / second-best scan of all nB candidates (index order) for this thread's (transformed) query, two candidates per
+// step: inside a tile the key is 16 bits (distance << 6 | pair number, at most 64 pairs), the even candidate in the low
+// half and the odd one in the high half of one register, so one packed 16x2 min / max serves two candidates
+// (3 VIMNMX per two distances instead of six).  After each tile the four 16-bit winners are widened to the 32-bit
+// (distance, global index) key and merged: all keys are distinct, so the two smallest keys overall are among the two
+// smallest of each half.
 __device__ __forceinline__ void scan_candidates(const uint4* __restrict__ B, int nB, bool active, const uint4& q0,
                                                 const uint4& q1, uint4* s_tile, int& best, int& second, int& best_idx)
 {
     unsigned pb = MATCH_INIT, ps = MATCH_INIT;                 // best and second-best packed values
     for (int t0 = 0; t0 < nB; t0 += MATCH_TILE) {
         const int tn = min(MATCH_TILE, nB - t0);
-        __syncthreads();
-        for (int i = threadIdx.x; i < 2 * tn; i += MATCH_THREADS) s_tile[i] = __ldg(B + 2 * (size_t)t0 + i);
-        __syncthreads();
+        stage_tile(B, t0, tn, s_tile);
         if (active) {
+            unsigned b2 = 0xFFFFFFFFu, s2 = 0xFFFFFFFFu;
+            const int np = tn >> 1;
 #pragma unroll 4
-            for (int j = 0; j < tn; ++j) {
-                const unsigned cur = ((unsigned)hamming256(q0, q1, s_tile[2 * j], s_tile[2 * j + 1]) << MATCH_IDX_BITS) | (unsigned)(t0 + j);
+            for (int jj = 0; jj < np; ++jj) {
+                const int da = hamming256_t(q0, q1, s_tile[4 * jj], s_tile[4 * jj + 1]);
+                const int db = hamming256_t(q0, q1, s_tile[4 * jj + 2], s_tile[4 * jj + 3]);
+                const unsigned cur = (unsigned)(db * 64 + jj) * 65536u + (unsigned)(da * 64 + jj);
+                const unsigned hi = __vmaxu2(b2, cur);
+                b2 = __vminu2(b2, cur);
+                s2 = __vminu2(s2, hi);
+            }
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+                const unsigned v = ((h & 2) ? s2 : b2) >> ((h & 1) * 16) & 0xFFFFu;           // 0xFFFF = empty: widens to a key above MATCH_INIT
+                const unsigned cur = ((v >> 6) << MATCH_IDX_BITS) | (unsigned)(t0 + 2 * (int)(v & 63u) + (h & 1));
+                const unsigned hi = max(pb, cur);
+                pb = min(pb, cur);
+                ps = min(ps, hi);
+            }
+            if (tn & 1) {
+                const int j = tn - 1;
+                const unsigned cur = ((unsigned)hamming256_t(q0, q1, s_tile[2 * j], s_tile[2 * j + 1]) << MATCH_IDX_BITS) | (unsigned)(t0 + j);
                 const unsigned hi = max(pb, cur);
                 pb = min(pb, cur);
                 ps = min(ps, hi);
@@ -76,6 +133,42 @@ __device__ __forceinline__ void scan_candidates(const uint4* __restrict__ B, int
     if (nB == 0) best_idx = -1;
 }
 
+// The all-pairs count needs the best and the second-best DISTANCE only (accept rule of src/ORBmatcher.cc:228-232), not the
+// index: the key is the bare distance, two candidates per register, and the running best / second of the even and the
+// odd candidates are merged once at the end (multiset semantics: a distance that occurs twice is its own second-best,
+// exactly as the strict '<' scan leaves it).
+__device__ __forceinline__ void scan_distances(const uint4* __restrict__ B, int nB, bool active, const uint4& q0,
+                                               const uint4& q1, uint4* s_tile, int& best, int& second)
+{
+    unsigned b2 = 0x01000100u, s2 = 0x01000100u;               // 256 | 256 << 16
+    for (int t0 = 0; t0 < nB; t0 += MATCH_TILE) {
+        const int tn = min(MATCH_TILE, nB - t0);
+        stage_tile(B, t0, tn, s_tile);
+        if (active) {
+            const int np = tn >> 1;
+#pragma unroll 4
+            for (int jj = 0; jj < np; ++jj) {
+                const int da = hamming256_t(q0, q1, s_tile[4 * jj], s_tile[4 * jj + 1]);
+                const int db = hamming256_t(q0, q1, s_tile[4 * jj + 2], s_tile[4 * jj + 3]);
+                const unsigned cur = (unsigned)db * 65536u + (unsigned)da;
+                const unsigned hi = __vmaxu2(b2, cur);
+                b2 = __vminu2(b2, cur);
+                s2 = __vminu2(s2, hi);
+            }
+            if (tn & 1) {                                       // odd tail: the last candidate alone, its partner is "no candidate" (256)
+                const int da = hamming256_t(q0, q1, s_tile[2 * (tn - 1)], s_tile[2 * (tn - 1) + 1]);
+                const unsigned cur = 256u * 65536u + (unsigned)da;
+                const unsigned hi = __vmaxu2(b2, cur);
+                b2 = __vminu2(b2, cur);
+                s2 = __vminu2(s2, hi);
+            }
+        }
+    }
+    const int be = (int)(b2 & 0xFFFFu), bo = (int)(b2 >> 16), se = (int)(s2 & 0xFFFFu), so = (int)(s2 >> 16);
+    best = min(be, bo);
+    second = min(max(be, bo), min(se, so));
+}
+
 __global__ void __launch_bounds__(MATCH_THREADS) k_match_bruteforce(const uint4* __restrict__ A, int nA,
                                                                     const uint4* __restrict__ B, int nB,
                                                                     int32_t* best_idx, uint16_t* best, uint16_t* second)
@@ -84,7 +177,7 @@ __global__ void __launch_bounds__(MATCH_THREADS) k_match_bruteforce(const uint4*
     const int q = blockIdx.x * MATCH_THREADS + threadIdx.x;
     const bool active = q < nA;
     uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
-    if (active) { q0 = __ldg(A + 2 * (size_t)q); q1 = __ldg(A + 2 * (size_t)q + 1); }
+    if (active) { q0 = hamming_transform(__ldg(A + 2 * (size_t)q)); q1 = hamming_transform(__ldg(A + 2 * (size_t)q + 1)); }
     int b1 = 256, b2 = 256, bi = -1;
     scan_candidates(B, nB, active, q0, q1, s_tile, b1, b2, bi);
     if (active) { best_idx[q] = bi; best[q] = (uint16_t)b1; second[q] = (uint16_t)b2; }
@@ -102,9 +195,9 @@ __global__ void __launch_bounds__(MATCH_THREADS) k_match_count_pairs(const uint4
     const int q = blockIdx.x * MATCH_THREADS + threadIdx.x;
     const bool active = q < n_per_kf;
     uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
-    if (active) { q0 = __ldg(A + 2 * (size_t)q); q1 = __ldg(A + 2 * (size_t)q + 1); }
-    int b1 = 256, b2 = 256, bi = -1;
-    scan_candidates(B, n_per_kf, active, q0, q1, s_tile, b1, b2, bi);
+    if (active) { q0 = hamming_transform(__ldg(A + 2 * (size_t)q)); q1 = hamming_transform(__ldg(A + 2 * (size_t)q + 1)); }
+    int b1 = 256, b2 = 256;
+    scan_distances(B, n_per_kf, active, q0, q1, s_tile, b1, b2);
     const bool ok = active && b1 <= th_low && (float)b1 < __fmul_rn(ratio, (float)b2);
     const int c = __syncthreads_count(ok);
     if (threadIdx.x == 0 && c) atomicAdd(&counts[blockIdx.y], c);
@@ -144,6 +237,35 @@ __global__ void __launch_bounds__(DD_WARPS * 32) k_distinctive(const uint4* __re
     if (lane == 0) best_idx[g] = (int)(best & 0xFFFFu);
 }
 
+// Instruction-rate micro-benchmarks behind the roofline of the matching kernels ("a popc
+// micro-benchmark peak").  Eight independent dependency chains per thread; which = 0: one POPC per chain step (plus the
+// XOR and the add that keep the value alive, both on the faster ALU pipe), which = 1: LOP3 only.  out keeps the result
+// live.  The kernel reports nothing itself: the host divides the op count by the CUDA-event time.
+__global__ void __launch_bounds__(256) k_pipe_peak(unsigned* out, int iters, int which)
+{
+    unsigned a[8];
+    const unsigned k = (blockIdx.x * 256u + threadIdx.x) * 0x9E3779B9u + 0x7F4A7C15u;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = k ^ (0x01010101u * (unsigned)(j + 1));
+    if (which == 0) {
+        for (int i = 0; i < iters; ++i) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = (unsigned)__popc(a[j] ^ k) + a[j];
+        }
+    } else {
+        unsigned m = k | 1u;
+        for (int i = 0; i < iters; ++i) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = (a[j] & m) ^ a[(j + 1) & 7];                // one LOP3 (a 3-input function)
+            m += 2u;                                                                       // keeps the loop from collapsing
+        }
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r ^= a[j];
+    if (r == 0x12345678u) out[0] = r;                                                      // practically never true
+}
+
 struct orbgpu_matcher {
     int device = 0;
     cudaStream_t st = nullptr;
@@ -152,7 +274,85 @@ struct orbgpu_matcher {
     int num_kf = 0, n_per_kf = 0;
     int2* d_pairs = nullptr; int32_t* d_counts = nullptr; int pair_cap = 0;
     double last_ms = 0;
+    // all-pairs sharded over ranks (orbgpu_matcher_all_pairs_sharded): this rank's pair list, its counts padded to the
+    // per-rank length, and the all_gather receive buffer; rebuilt when (keyframes, rank, world) change
+    int sh_kf = 0, sh_rank = -1, sh_world = 0, sh_block = 0, sh_mine = 0, sh_per_rank = 0;
+    int2* d_sh_pairs = nullptr; int32_t* d_sh_local = nullptr; int32_t* d_sh_all = nullptr;
+    cudaEvent_t e2 = nullptr;
+    double sh_kernel_ms = 0, sh_gather_ms = 0;
 };
+
+// NCCL is bound at run time (dlopen of the libnccl.so.2 the process already holds, or the system one): liborbgpu.so has
+// no link-time dependency on it, and hosts that never shard never load it.
+namespace {
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+std::mutex g_nccl_mu;
+NcclApi g_nccl;
+bool g_nccl_tried = false;
+
+const NcclApi* nccl_api()
+{
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (!g_nccl_tried) {
+        g_nccl_tried = true;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (h) {
+            NcclApi a;
+            a.lib = h;
+            *(void**)&a.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+            *(void**)&a.CommInitRank = dlsym(h, "ncclCommInitRank");
+            *(void**)&a.CommInitAll = dlsym(h, "ncclCommInitAll");
+            *(void**)&a.CommDestroy = dlsym(h, "ncclCommDestroy");
+            *(void**)&a.AllGather = dlsym(h, "ncclAllGather");
+            *(void**)&a.GroupStart = dlsym(h, "ncclGroupStart");
+            *(void**)&a.GroupEnd = dlsym(h, "ncclGroupEnd");
+            *(void**)&a.GetErrorString = dlsym(h, "ncclGetErrorString");
+            if (a.GetUniqueId && a.CommInitRank && a.CommInitAll && a.CommDestroy && a.AllGather && a.GroupStart && a.GroupEnd && a.GetErrorString)
+                g_nccl = a;
+        }
+    }
+    return g_nccl.lib ? &g_nccl : nullptr;
+}
+}  // namespace
+
+#define NC(call)                                                                                      \
+    do {                                                                                              \
+        const ncclResult_t _r = (call);                                                               \
+        if (_r != ncclSuccess) {                                                                      \
+            char _b[256];                                                                             \
+            snprintf(_b, sizeof(_b), "%s: %s", #call, nccl_api() ? nccl_api()->GetErrorString(_r) : "?"); \
+            orbgpu_internal_set_error(_b);                                                            \
+            return ORBGPU_ERR_CUDA;                                                                   \
+        }                                                                                             \
+    } while (0)
+
+struct orbgpu_comm {
+    int device = 0, rank = 0, world = 1;
+    ncclComm_t comm = nullptr;
+};
+
+// all_gather output (rank-major, per_rank padded slots each) -> pair order.  Slot i of rank r holds pair
+// ((i / block) * world + r) * block + i % block (blocks of `block` pairs dealt round-robin).
+__global__ void __launch_bounds__(256) k_scatter_pair_counts(const int32_t* __restrict__ all, int per_rank, int world, int block,
+                                                             int num_pairs, int32_t* __restrict__ out)
+{
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    if (t >= per_rank * world) return;
+    const int r = t / per_rank, i = t - r * per_rank;
+    const long long p = ((long long)(i / block) * world + r) * block + i % block;
+    if (p < num_pairs) out[p] = all[t];
+}
 
 // MapPoint::UpdateNormalAndDepth (src/MapPoint.cc:330-371), one thread per map point: the mean viewing direction is a float
 // accumulation in observation order, so a point's walk stays serial while the points run in parallel.  OpenCV's arithmetic:
@@ -331,12 +531,9 @@ int orbgpu_distinctive_descriptors(int device, const uint8_t* desc, const int32_
         if (group_start[g + 1] - group_start[g] > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;     // row index rides in 16 bits
     }
     CUM(cudaSetDevice(device));
-    static thread_local bool attr_set = false;
     const size_t smem = (size_t)DD_WARPS * DD_BINS * 32 * sizeof(unsigned short);
-    if (!attr_set) {
-        CUM(cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    static OrbSmemOptIn optin;
+    CUM(optin.ensure(k_distinctive, (int)smem));
     const size_t o_gs = up256((size_t)32 * (size_t)total), o_out = up256(o_gs + (size_t)4 * (size_t)(n_groups + 1)),
                  bytes = up256(o_out + (size_t)4 * (size_t)n_groups);
     MatchScratch& S = g_scratch;
@@ -391,6 +588,34 @@ int orbgpu_update_normals_and_depths(int device, const float* pos, const int32_t
     return ORBGPU_OK;
 }
 
+int orbgpu_debug_pipe_peak(int device, int which, double* ops_per_s)
+{
+    if (!ops_per_s || which < 0 || which > 1) return ORBGPU_ERR_ARG;
+    MatchScratch& S = g_scratch;
+    const int rc = S.ensure(device, 256);
+    if (rc != ORBGPU_OK) return rc;
+    int sms = 0;
+    CUM(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    cudaEvent_t e0, e1;
+    CUM(cudaEventCreate(&e0)); CUM(cudaEventCreate(&e1));
+    const int iters = 8192, ctas = sms * 8;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {                                                    // first pass warms the clocks
+        cudaEventRecord(e0, S.st);
+        k_pipe_peak<<<ctas, 256, 0, S.st>>>(reinterpret_cast<unsigned*>(S.d), iters, which);
+        cudaEventRecord(e1, S.st);
+        cudaError_t ce = cudaStreamSynchronize(S.st);
+        float ms = 0.f;
+        if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+        if (ce != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); CUM(ce); }
+        const double rate = (double)ctas * 256.0 * iters * 8.0 / (ms * 1e-3);
+        if (rep > 0 && rate > best) best = rate;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *ops_per_s = best;
+    return ORBGPU_OK;
+}
+
 int orbgpu_matcher_create(orbgpu_matcher** out, int device)
 {
     if (!out) return ORBGPU_ERR_ARG;
@@ -403,7 +628,7 @@ int orbgpu_matcher_create(orbgpu_matcher** out, int device)
     if (!m) return ORBGPU_ERR_NOMEM;
     m->device = device;
     CUM(cudaStreamCreateWithFlags(&m->st, cudaStreamNonBlocking));
-    CUM(cudaEventCreate(&m->e0)); CUM(cudaEventCreate(&m->e1));
+    CUM(cudaEventCreate(&m->e0)); CUM(cudaEventCreate(&m->e1)); CUM(cudaEventCreate(&m->e2));
     *out = m;
     return ORBGPU_OK;
 }
@@ -415,6 +640,8 @@ void orbgpu_matcher_destroy(orbgpu_matcher* m)
     if (m->st) cudaStreamSynchronize(m->st);
     if (m->own_desc) cudaFree(m->d_desc);
     cudaFree(m->d_pairs); cudaFree(m->d_counts);
+    cudaFree(m->d_sh_pairs); cudaFree(m->d_sh_local); cudaFree(m->d_sh_all);
+    if (m->e2) cudaEventDestroy(m->e2);
     if (m->e0) cudaEventDestroy(m->e0);
     if (m->e1) cudaEventDestroy(m->e1);
     if (m->st) cudaStreamDestroy(m->st);
@@ -493,6 +720,189 @@ int orbgpu_matcher_count_pairs(orbgpu_matcher* m, const int32_t* kf_a, const int
     int rc = orbgpu_matcher_count_pairs_device(m, reinterpret_cast<const int32_t*>(m->d_pairs), num_pairs, th_low, ratio, m->d_counts);
     if (rc != ORBGPU_OK) return rc;
     CUM(cudaMemcpy(counts, m->d_counts, sizeof(int32_t) * (size_t)num_pairs, cudaMemcpyDeviceToHost));
+    return ORBGPU_OK;
+}
+
+// ---- all-pairs matching sharded over ranks, result gather by ncclAllGather on the kernel's own stream -------------------
+
+int orbgpu_comm_unique_id(void* id128)
+{
+    if (!id128) return ORBGPU_ERR_ARG;
+    const NcclApi* N = nccl_api();
+    if (!N) { orbgpu_internal_set_error("libnccl.so.2 not found"); return ORBGPU_ERR_UNSUPPORTED; }
+    ncclUniqueId id;
+    NC(N->GetUniqueId(&id));
+    memcpy(id128, &id, sizeof(id));
+    return ORBGPU_OK;
+}
+
+int orbgpu_comm_init_rank(orbgpu_comm** out, int device, int rank, int world, const void* id128)
+{
+    if (!out || !id128 || world < 1 || rank < 0 || rank >= world) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    const NcclApi* N = nccl_api();
+    if (!N) { orbgpu_internal_set_error("libnccl.so.2 not found"); return ORBGPU_ERR_UNSUPPORTED; }
+    CUM(cudaSetDevice(device));
+    orbgpu_comm* c = new (std::nothrow) orbgpu_comm();
+    if (!c) return ORBGPU_ERR_NOMEM;
+    c->device = device; c->rank = rank; c->world = world;
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof(id));
+    const ncclResult_t r = N->CommInitRank(&c->comm, world, id, rank);
+    if (r != ncclSuccess) { delete c; NC(r); }
+    *out = c;
+    return ORBGPU_OK;
+}
+
+int orbgpu_comm_init_all(orbgpu_comm** out, const int* devices, int n)
+{
+    if (!out || !devices || n < 1 || n > 64) return ORBGPU_ERR_ARG;
+    for (int i = 0; i < n; ++i) out[i] = nullptr;
+    const NcclApi* N = nccl_api();
+    if (!N) { orbgpu_internal_set_error("libnccl.so.2 not found"); return ORBGPU_ERR_UNSUPPORTED; }
+    ncclComm_t comms[64];
+    NC(N->CommInitAll(comms, n, devices));
+    for (int i = 0; i < n; ++i) {
+        orbgpu_comm* c = new (std::nothrow) orbgpu_comm();
+        if (!c) return ORBGPU_ERR_NOMEM;
+        c->device = devices[i]; c->rank = i; c->world = n; c->comm = comms[i];
+        out[i] = c;
+    }
+    return ORBGPU_OK;
+}
+
+void orbgpu_comm_destroy(orbgpu_comm* c)
+{
+    if (!c) return;
+    const NcclApi* N = nccl_api();
+    if (N && c->comm) { cudaSetDevice(c->device); N->CommDestroy(c->comm); }
+    delete c;
+}
+
+static int adaptive_pair_block(long long num_pairs, int world)
+{
+    long long b = num_pairs / (16LL * (world > 0 ? world : 1));          // every rank owns at least 16 blocks (my-slam_b200/shard.py)
+    if (b > 4096) b = 4096;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+// this rank's share of the upper-triangular pair list (a < b, row-major), blocks of `block` pairs dealt round-robin
+static int sharded_prepare(orbgpu_matcher* m, int rank, int world)
+{
+    if (m->sh_kf == m->num_kf && m->sh_rank == rank && m->sh_world == world && m->d_sh_pairs) return ORBGPU_OK;
+    const long long K = m->num_kf, P = K * (K - 1) / 2;
+    if (P < 1 || P > 0x7FFFFFFF) return ORBGPU_ERR_UNSUPPORTED;
+    const int block = adaptive_pair_block(P, world);
+    const long long nblocks = (P + block - 1) / block;
+    const long long per_rank_blocks = (nblocks + world - 1) / world;
+    const long long per_rank = per_rank_blocks * block;
+    std::vector<int2> mine;
+    mine.reserve((size_t)per_rank);
+    // walk the pair list once, keeping the pairs whose block belongs to this rank
+    long long p = 0;
+    for (int a = 0; a < K - 1; ++a) {
+        for (int b = a + 1; b < K; ++b, ++p)
+            if ((p / block) % world == rank) mine.push_back(make_int2(a, b));
+    }
+    cudaFree(m->d_sh_pairs); cudaFree(m->d_sh_local); cudaFree(m->d_sh_all);
+    m->d_sh_pairs = nullptr; m->d_sh_local = nullptr; m->d_sh_all = nullptr;
+    CUM(cudaMalloc(&m->d_sh_pairs, sizeof(int2) * std::max<size_t>(mine.size(), 1)));
+    CUM(cudaMalloc(&m->d_sh_local, sizeof(int32_t) * (size_t)per_rank));
+    CUM(cudaMalloc(&m->d_sh_all, sizeof(int32_t) * (size_t)per_rank * world));
+    if (!mine.empty()) CUM(cudaMemcpy(m->d_sh_pairs, mine.data(), sizeof(int2) * mine.size(), cudaMemcpyHostToDevice));
+    m->sh_kf = m->num_kf; m->sh_rank = rank; m->sh_world = world; m->sh_block = block;
+    m->sh_mine = (int)mine.size(); m->sh_per_rank = (int)per_rank;
+    return ORBGPU_OK;
+}
+
+// enqueue: counts of this rank's pairs -> (gather is enqueued by the caller) -> scatter into pair order
+static int sharded_enqueue_kernel(orbgpu_matcher* m, int th_low, float ratio)
+{
+    CUM(cudaMemsetAsync(m->d_sh_local, 0, sizeof(int32_t) * (size_t)m->sh_per_rank, m->st));
+    CUM(cudaEventRecord(m->e0, m->st));
+    const int qblocks = (m->n_per_kf + MATCH_THREADS - 1) / MATCH_THREADS;
+    for (int p0 = 0; p0 < m->sh_mine; p0 += 65535) {
+        const int np = m->sh_mine - p0 < 65535 ? m->sh_mine - p0 : 65535;
+        k_match_count_pairs<<<dim3(qblocks, np), MATCH_THREADS, 0, m->st>>>(m->d_desc, m->n_per_kf, m->d_sh_pairs + p0, th_low, ratio,
+                                                                           m->d_sh_local + p0);
+    }
+    CUM(cudaGetLastError());
+    CUM(cudaEventRecord(m->e1, m->st));
+    return ORBGPU_OK;
+}
+static int sharded_enqueue_scatter(orbgpu_matcher* m, int world, int32_t* d_counts)
+{
+    const long long K = m->num_kf, P = K * (K - 1) / 2;
+    const int slots = m->sh_per_rank * world;
+    k_scatter_pair_counts<<<(slots + 255) / 256, 256, 0, m->st>>>(world > 1 ? m->d_sh_all : m->d_sh_local, m->sh_per_rank, world, m->sh_block,
+                                                                  (int)P, d_counts);
+    CUM(cudaGetLastError());
+    CUM(cudaEventRecord(m->e2, m->st));
+    return ORBGPU_OK;
+}
+static int sharded_finish(orbgpu_matcher* m, double* ms3)
+{
+    CUM(cudaStreamSynchronize(m->st));
+    float k = 0.f, g = 0.f;
+    CUM(cudaEventElapsedTime(&k, m->e0, m->e1));
+    CUM(cudaEventElapsedTime(&g, m->e1, m->e2));
+    m->sh_kernel_ms = k; m->sh_gather_ms = g; m->last_ms = k;
+    if (ms3) { ms3[0] = k; ms3[1] = g; ms3[2] = (double)k + g; }
+    return ORBGPU_OK;
+}
+
+int orbgpu_matcher_all_pairs_sharded(orbgpu_matcher* m, orbgpu_comm* c, int th_low, float ratio, int32_t* d_counts, double* ms3)
+{
+    if (!m || !m->d_desc || !d_counts || m->num_kf < 2) return ORBGPU_ERR_ARG;
+    const int rank = c ? c->rank : 0, world = c ? c->world : 1;
+    if (c && c->device != m->device) return ORBGPU_ERR_ARG;
+    CUM(cudaSetDevice(m->device));
+    int rc;
+    if ((rc = sharded_prepare(m, rank, world)) != ORBGPU_OK) return rc;
+    if ((rc = sharded_enqueue_kernel(m, th_low, ratio)) != ORBGPU_OK) return rc;
+    if (world > 1) {                                           // on the kernel's stream: no host synchronisation between the last tile and the gather
+        const NcclApi* N = nccl_api();
+        NC(N->AllGather(m->d_sh_local, m->d_sh_all, (size_t)m->sh_per_rank, ncclInt32, c->comm, m->st));
+    }
+    if ((rc = sharded_enqueue_scatter(m, world, d_counts)) != ORBGPU_OK) return rc;
+    return sharded_finish(m, ms3);
+}
+
+int orbgpu_matcher_all_pairs_multi(orbgpu_matcher** ms, orbgpu_comm** cs, int n, int th_low, float ratio, int32_t** d_counts, double* ms3)
+{
+    if (!ms || !cs || !d_counts || n < 1) return ORBGPU_ERR_ARG;
+    for (int r = 0; r < n; ++r)
+        if (!ms[r] || !cs[r] || !d_counts[r] || !ms[r]->d_desc || cs[r]->world != n || cs[r]->rank != r || cs[r]->device != ms[r]->device ||
+            ms[r]->num_kf != ms[0]->num_kf || ms[r]->n_per_kf != ms[0]->n_per_kf || ms[r]->num_kf < 2)
+            return ORBGPU_ERR_ARG;
+    int rc;
+    for (int r = 0; r < n; ++r) {                              // every GPU starts its own pairs
+        CUM(cudaSetDevice(ms[r]->device));
+        if ((rc = sharded_prepare(ms[r], r, n)) != ORBGPU_OK) return rc;
+        if ((rc = sharded_enqueue_kernel(ms[r], th_low, ratio)) != ORBGPU_OK) return rc;
+    }
+    if (n > 1) {                                               // one grouped all_gather, each rank's part on that rank's stream
+        const NcclApi* N = nccl_api();
+        NC(N->GroupStart());
+        for (int r = 0; r < n; ++r) {
+            const ncclResult_t g = N->AllGather(ms[r]->d_sh_local, ms[r]->d_sh_all, (size_t)ms[r]->sh_per_rank, ncclInt32, cs[r]->comm, ms[r]->st);
+            if (g != ncclSuccess) { N->GroupEnd(); NC(g); }
+        }
+        NC(N->GroupEnd());
+    }
+    for (int r = 0; r < n; ++r) {
+        CUM(cudaSetDevice(ms[r]->device));
+        if ((rc = sharded_enqueue_scatter(ms[r], n, d_counts[r])) != ORBGPU_OK) return rc;
+    }
+    double worst[3] = {0, 0, 0};
+    for (int r = 0; r < n; ++r) {
+        CUM(cudaSetDevice(ms[r]->device));
+        double t[3];
+        if ((rc = sharded_finish(ms[r], t)) != ORBGPU_OK) return rc;
+        for (int k = 0; k < 3; ++k) worst[k] = t[k] > worst[k] ? t[k] : worst[k];
+    }
+    if (ms3) { ms3[0] = worst[0]; ms3[1] = worst[1]; ms3[2] = worst[2]; }
     return ORBGPU_OK;
 }
 

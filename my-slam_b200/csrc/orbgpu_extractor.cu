@@ -11,6 +11,8 @@
 #include <string.h>
 #include <algorithm>
 #include <new>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/orbgpu.h"
@@ -82,6 +84,14 @@ struct StreamCtx {
     int user_capacity = 0;
     uint64_t ticket = 0; bool ticket_live = false;
     int job_w = 0, job_h = 0;
+    // the chunk's kernels (pyramid .. describe, with the blur fork / join on the side stream) captured once as a CUDA graph
+    // per (buffers, frame count): one cudaGraphLaunch per chunk instead of 11 launches + 4 event calls from the host thread
+    // (a few frame counts are kept: the last chunk of a batch is usually shorter than the others)
+    static const int NGRAPH = 4;
+    cudaGraphExec_t gexec[NGRAPH] = {};
+    int g_frames[NGRAPH] = {}, g_launches[NGRAPH] = {};
+    uint64_t g_epoch[NGRAPH] = {};     // plan generation each graph was captured for
+    uint64_t g_used[NGRAPH] = {}, g_clock = 0;
 };
 
 }  // namespace
@@ -111,6 +121,8 @@ struct orbgpu_extractor {
     uint8_t* d_aux = nullptr; size_t d_aux_cap = 0;   // stereo / undistort outputs of the last frame, grown on demand
     uint8_t* h_aux = nullptr; size_t h_aux_cap = 0;   // pinned mirror
     int last_ctx = -1;                 // context holding the most recent single frame (pyramid / debug views)
+    bool use_graphs = true;            // host-buffer chunks replay a captured graph of their kernels (orbgpu_set_graphs)
+    uint64_t epoch = 1;                // bumped whenever a plan or a context's buffers change: invalidates captured graphs
     // scratch for orbgpu_octree
     uint8_t* d_oct_scratch = nullptr; size_t oct_scratch_bytes = 0;
 };
@@ -297,6 +309,7 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
                          (size_t)sel_total * 4 + (size_t)np.kmax * 60 + 256;
     np.chunk_cap = (int)std::min<size_t>(64, std::max<size_t>(1, ((size_t)1536 << 20) / np.bytes_per_frame));
 
+    struct Guard { Plan& p; bool keep = false; ~Guard() { if (!keep) p.free_dev(); } } guard{np};   // a failed upload frees what was allocated
     CU(cudaMalloc(&np.d_cells, sizeof(OrbCell) * std::max<size_t>(np.cells.size(), 1)));
     CU(cudaMalloc(&np.d_rs_ofs, sizeof(short) * std::max<size_t>(rs_ofs.size(), 1)));
     CU(cudaMalloc(&np.d_rs_a, sizeof(short) * std::max<size_t>(rs_a.size(), 1)));
@@ -309,12 +322,18 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
 
     pl.free_dev();
     pl = np;
+    guard.keep = true;
     e->last_ctx = -1;
+    ++e->epoch;
     return ORBGPU_OK;
 }
 
 static void ctx_free_buffers(StreamCtx& c)
 {
+    for (int k = 0; k < StreamCtx::NGRAPH; ++k) {
+        if (c.gexec[k]) { cudaGraphExecDestroy(c.gexec[k]); c.gexec[k] = nullptr; }
+        c.g_frames[k] = 0;
+    }
     cudaFree(c.d_raw); c.d_raw = nullptr; c.raw_bytes = 0;
     cudaFree(c.d_in); cudaFree(c.d_pyr); cudaFree(c.d_blur); cudaFree(c.d_scratch); cudaFree(c.d_desc);
     cudaFree(c.d_cellcnt); cudaFree(c.d_slots); cudaFree(c.d_sel); cudaFree(c.d_selcnt); cudaFree(c.d_candcnt);
@@ -332,7 +351,7 @@ static int ctx_reserve(orbgpu_extractor* e, StreamCtx& c, int frames, int plan_w
 {
     const Plan& pl = e->plan;
     if (c.cap >= frames && c.job_w == plan_w && c.job_h == plan_h) return ORBGPU_OK;
-    ctx_free_buffers(c);
+    ctx_free_buffers(c);                                      // also drops the context's captured graph
     const OrbPlanDev& D = pl.dev;
     const size_t n = (size_t)frames;
     CU(cudaMalloc(&c.d_in, n * pl.in_frame_bytes + 64));
@@ -393,6 +412,45 @@ static int enqueue_kernels(orbgpu_extractor* e, StreamCtx& c, const uint8_t* d_s
     if (prof) CU(cudaEventRecord(c.ev[EV_DESC], c.st));
     CU(cudaGetLastError());
     e->launches += (uint64_t)total;
+    return ORBGPU_OK;
+}
+
+// The same chunk through a captured graph (host-buffer path: every pointer the kernels see belongs to the context, so the
+// graph only depends on the frame count).  Captured on first use, replayed afterwards; profiling mode and handles with
+// graphs switched off take the direct path.
+static int enqueue_kernels_graph(orbgpu_extractor* e, StreamCtx& c, int nframes)
+{
+    const Plan& pl = e->plan;
+    const uint8_t* src = c.d_in;
+    const long long fs = (long long)(pl.in_pitch * pl.h);
+    if (e->profiling || !e->use_graphs)
+        return enqueue_kernels(e, c, src, fs, (int)pl.in_pitch, nframes, c.d_kps, c.d_desc, c.d_nout, pl.kmax);
+    int slot = -1, victim = 0;
+    for (int k = 0; k < StreamCtx::NGRAPH; ++k) {
+        if (c.gexec[k] && c.g_frames[k] == nframes && c.g_epoch[k] == e->epoch) { slot = k; break; }
+        if (!c.gexec[k] || c.g_epoch[k] != e->epoch) victim = k;               // prefer an empty or stale slot
+        else if (c.gexec[victim] && c.g_epoch[victim] == e->epoch && c.g_used[k] < c.g_used[victim]) victim = k;
+    }
+    if (slot < 0) {
+        slot = victim;
+        if (c.gexec[slot]) { cudaGraphExecDestroy(c.gexec[slot]); c.gexec[slot] = nullptr; }
+        const uint64_t l0 = e->launches;
+        CU(cudaStreamBeginCapture(c.st, cudaStreamCaptureModeRelaxed));
+        const int rc = enqueue_kernels(e, c, src, fs, (int)pl.in_pitch, nframes, c.d_kps, c.d_desc, c.d_nout, pl.kmax);
+        cudaGraph_t g = nullptr;
+        const cudaError_t ce = cudaStreamEndCapture(c.st, &g);
+        c.g_launches[slot] = (int)(e->launches - l0);
+        e->launches = l0;
+        if (rc != ORBGPU_OK) { if (g) cudaGraphDestroy(g); return rc; }
+        CU(ce);
+        const cudaError_t ci = cudaGraphInstantiate(&c.gexec[slot], g, 0);
+        cudaGraphDestroy(g);
+        CU(ci);
+        c.g_frames[slot] = nframes; c.g_epoch[slot] = e->epoch;
+    }
+    c.g_used[slot] = ++c.g_clock;
+    CU(cudaGraphLaunch(c.gexec[slot], c.st));
+    e->launches += (uint64_t)c.g_launches[slot];
     return ORBGPU_OK;
 }
 
@@ -516,7 +574,7 @@ static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, i
     if (prof) CU(cudaEventRecord(c.ev[EV_BEGIN], c.st));
     if ((rc = upload_frames(e, c, src, m, w, h, row_stride, frame_stride, pinned_in)) != ORBGPU_OK) return rc;
     if (prof) CU(cudaEventRecord(c.ev[EV_UP], c.st));
-    if ((rc = enqueue_kernels(e, c, c.d_in, (long long)(e->plan.in_pitch * h), (int)e->plan.in_pitch, m, c.d_kps, c.d_desc, c.d_nout, e->plan.kmax)) != ORBGPU_OK) return rc;
+    if ((rc = enqueue_kernels_graph(e, c, m)) != ORBGPU_OK) return rc;
     if ((rc = download_results(e, c, m, kps, desc, n_out, capacity, pinned_out)) != ORBGPU_OK) return rc;
     if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
     CU(cudaEventRecord(c.done, c.st));
@@ -723,6 +781,32 @@ int orbgpu_extract_batch_async(orbgpu_extractor* e, const uint8_t* frames, int n
     return enqueue_host_batch(e, frames, n, w, h, row_stride, frame_stride, kps, desc, capacity, n_out);
 }
 
+// One process, several GPUs: handle r (its own device) takes the r-th contiguous block of frames on its own host thread --
+// the reference's one-extractor-per-thread pattern (src/Frame.cc:78-81) with one GPU per thread.  No data-path exchange.
+int orbgpu_extract_batch_multi(orbgpu_extractor** handles, int num_handles, const uint8_t* frames, int n, int w, int h,
+                               size_t row_stride, size_t frame_stride, orbgpu_keypoint* kps, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!handles || num_handles < 1 || !frames || !kps || !desc || !n_out || n < 1) return ORBGPU_ERR_ARG;
+    for (int r = 0; r < num_handles; ++r) if (!handles[r]) return ORBGPU_ERR_ARG;
+    if (num_handles == 1) return orbgpu_extract_batch(handles[0], frames, n, w, h, row_stride, frame_stride, kps, desc, capacity, n_out);
+    std::vector<int> rc((size_t)num_handles, ORBGPU_OK);
+    std::vector<std::string> err((size_t)num_handles);
+    std::vector<std::thread> th;
+    for (int r = 0; r < num_handles; ++r) {
+        const int i0 = (int)((long long)n * r / num_handles), i1 = (int)((long long)n * (r + 1) / num_handles);
+        if (i1 <= i0) continue;
+        th.emplace_back([=, &rc, &err]() {
+            rc[r] = orbgpu_extract_batch(handles[r], frames + (size_t)i0 * frame_stride, i1 - i0, w, h, row_stride, frame_stride,
+                                         kps + (size_t)i0 * capacity, desc + (size_t)i0 * capacity * 32, capacity, n_out + i0);
+            if (rc[r] != ORBGPU_OK) err[r] = g_cuda_err;          // the error text is thread-local: carry it to the caller
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int r = 0; r < num_handles; ++r)
+        if (rc[r] != ORBGPU_OK) { orbgpu_internal_set_error(err[r].c_str()); return rc[r]; }
+    return ORBGPU_OK;
+}
+
 int orbgpu_wait(orbgpu_extractor* e)
 {
     if (!e) return ORBGPU_ERR_ARG;
@@ -759,7 +843,7 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
         if ((rc = ctx_finish(e, c)) != ORBGPU_OK) result = rc;
         if ((rc = ctx_reserve(e, c, chunk, w, h)) != ORBGPU_OK) { result = rc; break; }
         const bool prof = e->profiling;
-        if (prof) { CU(cudaEventRecord(c.ev[EV_BEGIN], c.st)); CU(cudaEventRecord(c.ev[EV_UP], c.st)); }
+        if (prof) { cudaEventRecord(c.ev[EV_BEGIN], c.st); cudaEventRecord(c.ev[EV_UP], c.st); }
         const uint8_t* lvl0 = d_frames + (size_t)i0 * frame_stride;
         long long lvl0_frame = (long long)frame_stride;
         int lvl0_pitch = (int)row_stride;
@@ -771,15 +855,15 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
                                ? orb_launch_repitch(lvl0, (long long)frame_stride, (int)row_stride, c.d_in, (int)dp, w, h, m, c.st)
                                : orb_launch_cvt_gray(lvl0, (long long)frame_stride, (int)row_stride, e->in_channels, e->in_rgb, c.d_in,
                                                      (int)dp, w, h, m, c.st);
-            if (nl < 0) return ORBGPU_ERR_CUDA;
+            if (nl < 0) { result = ORBGPU_ERR_CUDA; break; }      // earlier chunks are in flight: fall through to the common drain
             e->launches += 1;
             lvl0 = c.d_in; lvl0_frame = (long long)(dp * h); lvl0_pitch = (int)dp;
         }
         rc = enqueue_kernels(e, c, lvl0, lvl0_frame, lvl0_pitch, m,
                              d_kps + (size_t)i0 * capacity, d_desc + (size_t)i0 * capacity * 32, d_n_out + i0, capacity);
         if (rc != ORBGPU_OK) { result = rc; break; }
-        if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
-        CU(cudaEventRecord(c.done, c.st));
+        if (prof) cudaEventRecord(c.ev[EV_DOWN], c.st);
+        if (cudaEventRecord(c.done, c.st) != cudaSuccess) { result = ORBGPU_ERR_CUDA; break; }
         c.busy = true; c.profiled = prof; c.job_frames = m; c.staged_out = false; c.user_nout = nullptr;
     }
     if (result == ORBGPU_OK) result = batch_end(e);
@@ -1095,19 +1179,26 @@ int orbgpu_undistort_points(int device, const float* xy, int n, const float* K4,
 }
 
 // ---- float-step test hooks ------------------------------------------------------------------------
+namespace {
+struct DevBuf {                        // frees on every exit path of the hooks below
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+};
+}  // namespace
+
 int orbgpu_debug_atan2(orbgpu_extractor* e, const float* y, const float* x, int n, float* out_deg)
 {
     if (!e || !y || !x || !out_deg || n < 1) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
-    float* d = nullptr;
-    CU(cudaMalloc(&d, 3 * sizeof(float) * (size_t)n));
+    DevBuf buf;
+    CU(cudaMalloc(&buf.p, 3 * sizeof(float) * (size_t)n));
+    float* d = static_cast<float*>(buf.p);
     CU(cudaMemcpy(d, y, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d + n, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
     orb_debug_atan2(d, d + n, n, d + 2 * (size_t)n, 0);
     e->launches += 1;
     CU(cudaMemcpy(out_deg, d + 2 * (size_t)n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
-    cudaFree(d);
     return ORBGPU_OK;
 }
 
@@ -1116,14 +1207,14 @@ int orbgpu_debug_sincosf(orbgpu_extractor* e, const float* rad, int n, float* ou
     if (!e || !rad || !out_sin || !out_cos || n < 1) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
-    float* d = nullptr;
-    CU(cudaMalloc(&d, 3 * sizeof(float) * (size_t)n));
+    DevBuf buf;
+    CU(cudaMalloc(&buf.p, 3 * sizeof(float) * (size_t)n));
+    float* d = static_cast<float*>(buf.p);
     CU(cudaMemcpy(d, rad, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
     orb_debug_sincosf(d, n, d + n, d + 2 * (size_t)n, 0);
     e->launches += 1;
     CU(cudaMemcpy(out_sin, d + n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(out_cos, d + 2 * (size_t)n, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
-    cudaFree(d);
     return ORBGPU_OK;
 }
 
@@ -1132,14 +1223,14 @@ int orbgpu_debug_sincos_checksum(orbgpu_extractor* e, uint32_t first_bits, uint3
     if (!e || !checksum) return ORBGPU_ERR_ARG;
     int rc;
     if ((rc = use_device(e)) != ORBGPU_OK) return rc;
-    unsigned long long* d = nullptr;
-    CU(cudaMalloc(&d, sizeof(unsigned long long)));
+    DevBuf buf;
+    CU(cudaMalloc(&buf.p, sizeof(unsigned long long)));
+    unsigned long long* d = static_cast<unsigned long long*>(buf.p);
     CU(cudaMemset(d, 0, sizeof(unsigned long long)));
     orb_debug_sincos_checksum(first_bits, count, step, d, 0);
     e->launches += 1;
     unsigned long long h = 0;
     CU(cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost));
-    cudaFree(d);
     *checksum = h;
     return ORBGPU_OK;
 }
@@ -1182,6 +1273,24 @@ int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames)
         if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
     e->nstream[0] = e->nstream[1] = streams;
     e->max_chunk[0] = e->max_chunk[1] = max_chunk_frames;
+    return ORBGPU_OK;
+}
+
+int orbgpu_chunk_capacity(orbgpu_extractor* e, int w, int h)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    return e->plan.chunk_cap;
+}
+
+int orbgpu_set_graphs(orbgpu_extractor* e, int on)
+{
+    if (!e) return ORBGPU_ERR_ARG;
+    for (int s = 0; s < NSTREAM; ++s)
+        if (e->ctx[s].busy || e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    e->use_graphs = on != 0;
     return ORBGPU_OK;
 }
 

@@ -5,6 +5,7 @@
 
 #include <cassert>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 
@@ -16,12 +17,16 @@ static_assert(sizeof(cv::KeyPoint) == sizeof(orbgpu_keypoint), "cv::KeyPoint mus
 
 const int EDGE_THRESHOLD = 19;    // src/ORBextractor.cc:76: width of the frame around every pyramid level
 
+// live extractors of this process: the second one (a stereo pair) switches the pyramid download on for all of them
+static std::mutex g_live_mu;
+static std::vector<ORBextractor*> g_live;
+
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : ORBextractor(_nfeatures, _scaleFactor, _nlevels, _iniThFAST, _minThFAST, 0) {}
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST, int cudaDevice)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
-      mpHandle(0), mbDownloadPyramid(false), mLastError("ok"), mLastW(0), mLastH(0), mChannels(1)
+      mpHandle(0), mbDownloadPyramid(false), mbDownloadExplicit(false), mLastError("ok"), mLastW(0), mLastH(0), mChannels(1)
 {
     const int rc = orbgpu_create(&mpHandle, cudaDevice, _nfeatures, _scaleFactor, _nlevels, _iniThFAST, _minThFAST);
     if (rc != ORBGPU_OK)      // the reference has no failure path here; there is no CPU path to fall back to
@@ -37,9 +42,22 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
     mvLevelSigma2.assign(s4.begin() + 2 * nlevels, s4.begin() + 3 * nlevels);
     mvInvLevelSigma2.assign(s4.begin() + 3 * nlevels, s4.begin() + 4 * nlevels);
     mvImagePyramid.resize(nlevels);
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live.push_back(this);
+    if (g_live.size() >= 2)
+        for (size_t i = 0; i < g_live.size(); ++i)
+            if (!g_live[i]->mbDownloadExplicit) g_live[i]->mbDownloadPyramid = true;
 }
 
-ORBextractor::~ORBextractor() { orbgpu_destroy(mpHandle); }
+ORBextractor::~ORBextractor()
+{
+    {
+        std::lock_guard<std::mutex> lk(g_live_mu);
+        for (size_t i = 0; i < g_live.size(); ++i)
+            if (g_live[i] == this) { g_live.erase(g_live.begin() + (long)i); break; }
+    }
+    orbgpu_destroy(mpHandle);
+}
 
 // keypoints.clear() + fill, descriptors.create(N,32,CV_8U) or release() when N == 0 (:1066-1074)
 void ORBextractor::Finish(int n, std::vector<cv::KeyPoint>& keypoints, cv::OutputArray descriptors)
@@ -127,16 +145,20 @@ bool ORBextractor::ExtractBatch(const std::vector<cv::Mat>& frames, std::vector<
     if (n == 0) return true;
     const int w = frames[0].cols, h = frames[0].rows;
     for (int i = 0; i < n; ++i)
-        if (frames[i].cols != w || frames[i].rows != h || frames[i].empty()) { mLastError = "ExtractBatch: frames must share one shape"; return false; }
+        if (frames[i].cols != w || frames[i].rows != h || frames[i].empty() || frames[i].channels() != mChannels) {
+            mLastError = "ExtractBatch: frames must share one shape and the handle's channel count";
+            return false;
+        }
     const int cap = orbgpu_max_keypoints(mpHandle, w, h);
     if (cap < 0) { mLastError = orbgpu_strerror(cap); return false; }
-    std::vector<unsigned char> dense((size_t)n * w * h);
+    const size_t rb = (size_t)w * mChannels;                    // bytes per dense row (colour input: SetColorInput)
+    std::vector<unsigned char> dense((size_t)n * rb * h);
     for (int i = 0; i < n; ++i)
-        for (int y = 0; y < h; ++y) std::memcpy(&dense[((size_t)i * h + y) * w], frames[i].ptr(y), (size_t)w);
+        for (int y = 0; y < h; ++y) std::memcpy(&dense[((size_t)i * h + y) * rb], frames[i].ptr(y), rb);
     std::vector<orbgpu_keypoint> kps((size_t)n * cap);
     std::vector<unsigned char> desc((size_t)n * cap * 32);
     std::vector<int> nout((size_t)n);
-    const int rc = orbgpu_extract_batch(mpHandle, dense.data(), n, w, h, (size_t)w, (size_t)w * h, kps.data(), desc.data(), cap, nout.data());
+    const int rc = orbgpu_extract_batch(mpHandle, dense.data(), n, w, h, rb, rb * h, kps.data(), desc.data(), cap, nout.data());
     if (rc != ORBGPU_OK) { mLastError = orbgpu_strerror(rc); return false; }
     for (int i = 0; i < n; ++i) {
         const int k = nout[i];

@@ -43,7 +43,11 @@ public:
     std::vector<cv::Mat> mvImagePyramid;
 
     // ---- additions ----
-    void SetPyramidDownload(bool on) { mbDownloadPyramid = on; }
+    // mvImagePyramid is filled (device -> host, 19-px REFLECT_101 frame rebuilt) after every frame when this is on.  Default:
+    // off while the process holds ONE extractor (monocular: nothing reads the member), on for every extractor from the
+    // moment a second one exists -- the stereo Frame constructor's left / right pair, whose ComputeStereoMatches reads
+    // mvImagePyramid of both (src/Frame.cc:473, :563-580).  An explicit call here overrides the default for good.
+    void SetPyramidDownload(bool on) { mbDownloadPyramid = on; mbDownloadExplicit = true; }
     // Accept the camera image as it arrives (3 or 4 interleaved 8-bit channels, R,G,B or B,G,R order) and do the
     // cv::cvtColor(..., CV_*2GRAY) of Tracking::GrabImage* (src/Tracking.cc:244-257) on the device; channels = 1 restores
     // the reference contract (CV_8UC1).  GrayImage() returns what mImGray would hold after the host conversion.
@@ -82,6 +86,7 @@ protected:
 
     orbgpu_extractor* mpHandle;
     bool mbDownloadPyramid;
+    bool mbDownloadExplicit;
     const char* mLastError;
     std::vector<unsigned char> mKpScratch, mDescScratch;   // staging for the C ABI (caller-owned buffers)
     int mLastW, mLastH;

@@ -137,7 +137,10 @@ static int cmd_stereo(int argc, char** argv)
     fwrite(&n, 4, 1, out);
     fwrite(uR.data(), 4, (size_t)n, out); fwrite(depth.data(), 4, (size_t)n, out);
     fclose(out);
-    printf("%d %d\n", (int)kL.size(), (int)kR.size());
+    // an unchanged stereo Frame.cc reads mvImagePyramid of both extractors (src/Frame.cc:473, :563-580): with two live
+    // extractors the download is on by default, without any call to SetPyramidDownload
+    printf("%d %d %d %d %d %d\n", (int)kL.size(), (int)kR.size(), exL.mvImagePyramid[0].cols, exL.mvImagePyramid[0].rows,
+           exR.mvImagePyramid[7].cols, exR.mvImagePyramid[7].rows);
     return 0;
 }
 

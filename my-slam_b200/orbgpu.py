@@ -282,6 +282,7 @@ def lib():
         "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_extract_batch_async": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_wait": (i32, [vp]),
+        "orbgpu_extract_batch_multi": (i32, [vp, i32, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_stereo_match": (i32, [vp, vp, f32, f32, vp, vp, i32, pi]),
         "orbgpu_set_input_format": (i32, [vp, i32, i32]),
         "orbgpu_submit": (i32, [vp, vp, i32, i32, sz, C.POINTER(u64)]),
@@ -300,6 +301,8 @@ def lib():
         "orbgpu_launch_count": (u64, [vp]),
         "orbgpu_last_batch_ms": (C.c_double, [vp]),
         "orbgpu_set_batching": (i32, [vp, i32, i32]),
+        "orbgpu_set_graphs": (i32, [vp, i32]),
+        "orbgpu_chunk_capacity": (i32, [vp, i32, i32]),
         "orbgpu_undistort_keypoints": (i32, [vp, vp, vp, i32, vp, i32, pi]),
         "orbgpu_undistort_points": (i32, [i32, vp, i32, vp, vp, i32, vp]),
         "orbgpu_search_for_initialization": (i32, [i32, vp, vp, i32, vp, vp, i32, vp, vp, i32, f32, i32, vp, pi]),
@@ -335,6 +338,7 @@ def lib():
         "orbgpu_update_normals_and_depths": (i32, [i32, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp]),
         "orbgpu_match_bruteforce": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
         "orbgpu_match_bruteforce_noalloc": (i32, [i32, vp, i32, vp, i32, vp, vp, vp]),
+        "orbgpu_debug_pipe_peak": (i32, [i32, i32, C.POINTER(C.c_double)]),
         "orbgpu_matcher_create": (i32, [C.POINTER(vp), i32]),
         "orbgpu_matcher_destroy": (None, [vp]),
         "orbgpu_matcher_set_keyframes": (i32, [vp, vp, i32, i32]),
@@ -342,6 +346,12 @@ def lib():
         "orbgpu_matcher_count_pairs": (i32, [vp, vp, vp, i32, i32, f32, vp]),
         "orbgpu_matcher_count_pairs_device": (i32, [vp, vp, i32, i32, f32, vp]),
         "orbgpu_matcher_last_kernel_ms": (C.c_double, [vp]),
+        "orbgpu_comm_unique_id": (i32, [vp]),
+        "orbgpu_comm_init_rank": (i32, [C.POINTER(vp), i32, i32, i32, vp]),
+        "orbgpu_comm_init_all": (i32, [vp, vp, i32]),
+        "orbgpu_comm_destroy": (None, [vp]),
+        "orbgpu_matcher_all_pairs_sharded": (i32, [vp, vp, i32, f32, vp, vp]),
+        "orbgpu_matcher_all_pairs_multi": (i32, [vp, vp, i32, i32, f32, vp, vp]),
         "orbgpu_strerror": (C.c_char_p, [i32]),
         "orbgpu_last_cuda_error": (C.c_char_p, []),
         "orbgpu_device_count": (i32, []),
@@ -537,7 +547,24 @@ class ORBextractor:
 
     def set_batching(self, streams, max_chunk_frames): _check(self._L.orbgpu_set_batching(self._h, int(streams), int(max_chunk_frames)))
 
+    def chunk_capacity(self, w, h): return _check(self._L.orbgpu_chunk_capacity(self._h, w, h))
+
+    def set_graphs(self, on): _check(self._L.orbgpu_set_graphs(self._h, int(bool(on))))
+
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
+
+
+def extract_batch_multi(extractors, frames):
+    """frames [n,h,w] uint8 through several extractor handles (one per GPU) in one call: orbgpu_extract_batch_multi."""
+    n, h, w = frames.shape
+    cap = extractors[0].max_keypoints(w, h)
+    for e in extractors[1:]:
+        assert e.max_keypoints(w, h) == cap
+    kps = np.zeros((n, cap), KP_DTYPE); desc = np.zeros((n, cap, 32), np.uint8); n_out = np.zeros(n, np.int32)
+    hs = (C.c_void_p * len(extractors))(*[e._h for e in extractors])
+    _check(lib().orbgpu_extract_batch_multi(hs, len(extractors), _p(frames), n, w, h, frames.strides[1], frames.strides[0],
+                                            _p(kps), _p(desc), cap, _p(n_out)))
+    return kps, desc, n_out
 
 
 def undistort_points(xy, K4, dist, device=0):
@@ -743,12 +770,62 @@ class ORBmatcher:
     def last_kernel_ms(self):
         return float(self._L.orbgpu_matcher_last_kernel_ms(self._matcher()))
 
+    def all_pairs_sharded(self, comm, counts_ptr, th_low=None):
+        """Collective over the ranks of `comm` (None = this GPU alone): counts of ALL K (K - 1) / 2 pairs land in the device
+        buffer counts_ptr on every rank.  Returns (kernel ms, gather + scatter ms, total ms)."""
+        ms = (C.c_double * 3)()
+        _check(self._L.orbgpu_matcher_all_pairs_sharded(self._matcher(), comm._h if comm is not None else None,
+                                                        self.TH_LOW if th_low is None else th_low, float(self.mfNNratio), counts_ptr, ms))
+        return ms[0], ms[1], ms[2]
+
     def close(self):
         if self._m is not None:
             self._L.orbgpu_matcher_destroy(self._m)
             self._m = None
 
     __del__ = close
+
+
+class Comm:
+    """NCCL communicator created by the C ABI (orbgpu_comm_*): one rank of a one-process-per-GPU job."""
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_ubyte * 128)()
+        _check(lib().orbgpu_comm_unique_id(buf))
+        return bytes(buf)
+
+    def __init__(self, device, rank, world, id128):
+        self._h = C.c_void_p()
+        buf = (C.c_ubyte * 128).from_buffer_copy(id128)
+        _check(lib().orbgpu_comm_init_rank(C.byref(self._h), device, rank, world, buf))
+        self.rank, self.world, self.device = rank, world, device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbgpu_comm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def all_pairs_multi(matchers, devices, counts_ptrs, th_low=50, ratio=0.6):
+    """One process, several GPUs: matchers[r] on devices[r], one NCCL group gather (orbgpu_matcher_all_pairs_multi)."""
+    L = lib()
+    n = len(matchers)
+    comms = (C.c_void_p * n)()
+    devs = (C.c_int * n)(*devices)
+    _check(L.orbgpu_comm_init_all(comms, devs, n))
+    try:
+        ms = (C.c_void_p * n)(*[m._matcher() for m in matchers])
+        cp = (C.c_void_p * n)(*counts_ptrs)
+        t = (C.c_double * 3)()
+        _check(L.orbgpu_matcher_all_pairs_multi(ms, comms, n, th_low, ratio, cp, t))
+        return t[0], t[1], t[2]
+    finally:
+        for i in range(n):
+            if comms[i]:
+                L.orbgpu_comm_destroy(comms[i])
 
 
 class ORBVocabulary:

@@ -5,11 +5,13 @@
 #include "orb_pattern.h"   // the 512-point rBRIEF table (data constant, my-slam_b200/csrc)
 
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <list>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -411,6 +413,57 @@ int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int 
     for (int i = 0; i < nA; ++i)
         if (b1[i] <= th_low && (float)b1[i] < ratio * (float)b2[i]) ++c;
     return c;
+}
+
+// All-pairs form of the scan (BASELINE config 5) for the timed CPU baseline of the Hamming half of the metric:
+// pair p = (a, b) counts the rows of keyframe a whose best match in keyframe b passes the accept rule of
+// src/ORBmatcher.cc:228-232.  popcnt = 0: DescriptorDistance exactly as the reference writes it (the SWAR formula of
+// src/ORBmatcher.cc:1647-1663, orbport_hamming256); popcnt = 1: the same scan with the hardware popcount
+// instruction (what a CPU maintainer would write today).  Pairs are dealt to `threads` host threads in contiguous
+// slices.  Returns the wall time in seconds.
+}  // extern "C"
+static inline int hamming256_popcnt(const uint8_t* a, const uint8_t* b)
+{
+    uint64_t x[4], y[4];
+    std::memcpy(x, a, 32); std::memcpy(y, b, 32);
+    return __builtin_popcountll(x[0] ^ y[0]) + __builtin_popcountll(x[1] ^ y[1]) + __builtin_popcountll(x[2] ^ y[2]) +
+           __builtin_popcountll(x[3] ^ y[3]);
+}
+template <bool POPCNT>
+static void count_pairs_slice(const uint8_t* desc, int n, const int32_t* pairs, int p0, int p1, int th_low, float ratio, int32_t* counts)
+{
+    for (int p = p0; p < p1; ++p) {
+        const uint8_t* A = desc + 32 * (size_t)n * pairs[2 * p];
+        const uint8_t* B = desc + 32 * (size_t)n * pairs[2 * p + 1];
+        int c = 0;
+        for (int i = 0; i < n; ++i) {
+            int b1 = 256, b2 = 256;
+            for (int j = 0; j < n; ++j) {
+                const int d = POPCNT ? hamming256_popcnt(A + 32 * (size_t)i, B + 32 * (size_t)j)
+                                     : orbport_hamming256(A + 32 * (size_t)i, B + 32 * (size_t)j);
+                if (d < b1) { b2 = b1; b1 = d; }
+                else if (d < b2) b2 = d;
+            }
+            if (b1 <= th_low && (float)b1 < ratio * (float)b2) ++c;
+        }
+        counts[p] = c;
+    }
+}
+extern "C" {
+double orbport_count_pairs_bench(const uint8_t* desc, int n_per_kf, const int32_t* pairs, int num_pairs, int th_low, float ratio,
+                                 int32_t* counts, int threads, int popcnt)
+{
+    if (threads < 1) threads = 1;
+    if (threads > num_pairs) threads = num_pairs > 0 ? num_pairs : 1;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; ++t) {
+        const int p0 = (int)((long long)num_pairs * t / threads), p1 = (int)((long long)num_pairs * (t + 1) / threads);
+        if (popcnt) th.emplace_back(count_pairs_slice<true>, desc, n_per_kf, pairs, p0, p1, th_low, ratio, counts);
+        else        th.emplace_back(count_pairs_slice<false>, desc, n_per_kf, pairs, p0, p1, th_low, ratio, counts);
+    }
+    for (auto& x : th) x.join();
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
 }  // extern "C"

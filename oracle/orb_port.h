@@ -49,6 +49,10 @@ void orbport_match_bruteforce(const uint8_t* A, int nA, const uint8_t* B, int nB
                               int32_t* best_idx, uint16_t* best, uint16_t* second);
 /* accepted-match count of one keyframe pair: best <= th_low && float(best) < ratio*float(second) */
 int orbport_match_count(const uint8_t* A, int nA, const uint8_t* B, int nB, int th_low, float ratio);
+/* all-pairs counts over a keyframe table (BASELINE config 5), `threads` host threads; popcnt = 0: the reference's SWAR
+ * DescriptorDistance (src/ORBmatcher.cc:1647-1663), 1: hardware popcount.  Returns wall seconds (the timed CPU baseline). */
+double orbport_count_pairs_bench(const uint8_t* desc, int n_per_kf, const int32_t* pairs, int num_pairs, int th_low, float ratio,
+                                 int32_t* counts, int threads, int popcnt);
 
 /* Frame::ComputeStereoMatches (src/Frame.cc:466-640).  PINNED: the reference's own src/Frame.cc compiles
  * unchanged against oracle/cvshim2 into oracle/_ref/libframeref.so (oracle/ref_frame_wrap.cc) and

@@ -264,6 +264,16 @@ class OraclePort:
                                             _ptr(m12), _ptr(m21))
         return nm, m12[:side1.n].copy(), m21[:side2.n].copy()
 
+    def count_pairs_bench(self, desc, pairs, th_low=50, ratio=0.6, threads=1, popcnt=False):
+        """All-pairs accepted-match counts on the CPU (timed): returns (counts int32[P], seconds)."""
+        desc = np.ascontiguousarray(desc, np.uint8); pairs = np.ascontiguousarray(pairs, np.int32)
+        counts = np.zeros(len(pairs), np.int32)
+        f = self.L.orbport_count_pairs_bench
+        f.restype = C.c_double
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_int]
+        sec = f(_ptr(desc), desc.shape[1], _ptr(pairs), len(pairs), th_low, ratio, _ptr(counts), threads, 1 if popcnt else 0)
+        return counts, sec
+
     def match_count(self, A, B, th_low=50, ratio=0.6):
         A = np.ascontiguousarray(A, np.uint8); B = np.ascontiguousarray(B, np.uint8)
         return self.L.orbport_match_count(_ptr(A), len(A), _ptr(B), len(B), th_low, ratio)

@@ -290,3 +290,30 @@ def test_async_batches_equal_synchronous_results(pkg):
     assert ex.last_batch_ms() > 0
     kps, desc = ex(batches[0][0])                               # the handle is usable synchronously again
     assert len(kps) == want[0][2][0]
+
+
+def test_graph_replay_equals_direct_launches(pkg):
+    """Host-buffer chunks replay a captured CUDA graph of their kernels (orbgpu_set_graphs, default on): same bytes as
+    direct launches, for batch sizes that change the per-context frame count (graph cache), shapes that change the plan
+    (graphs invalidated) and the single-frame call; the launch counter counts the kernels inside the graph."""
+    synth = pkg.synth
+    exg = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    exd = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    exd.set_graphs(False)
+    for (w, h), sizes in (((640, 480), (19, 3, 19, 64, 1, 40)), ((333, 251), (9, 2, 9)), ((640, 480), (5,))):
+        frames = np.stack([synth.synth(w, h, 0xBEEF00 + i) for i in range(max(sizes))])
+        for n in sizes:
+            lg, ld = exg.launch_count(), exd.launch_count()
+            kg, dg, ng = exg.extract_batch(frames[:n])
+            kd, dd, nd = exd.extract_batch(frames[:n])
+            assert exg.launch_count() - lg == exd.launch_count() - ld > 0
+            assert np.array_equal(ng, nd) and ng.sum() > 0
+            for i in range(n):
+                assert kg[i, :ng[i]].tobytes() == kd[i, :nd[i]].tobytes() and np.array_equal(dg[i, :ng[i]], dd[i, :nd[i]])
+        k1, d1 = exg(frames[0]); k2, d2 = exd(frames[0])
+        assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    # profiling mode takes the direct path and still agrees
+    exg.set_profiling(True)
+    k3, d3 = exg(frames[0])
+    exg.set_profiling(False)
+    assert k3.tobytes() == k2.tobytes() and np.array_equal(d3, d2)

@@ -106,6 +106,9 @@ def test_cpp_stereo_matches_equal_oracle(cli, pkg, oracle, tmp_path):
                                np.float32(bf), np.float32(b))
     assert n == len(kL) and u.tobytes() == ou.tobytes() and d.tobytes() == od.tobytes()
     assert (u >= 0).sum() > 300
+    # two live extractors = a stereo pair: mvImagePyramid of both is filled by default (src/Frame.cc:473, :563-580 read it)
+    vals = list(map(int, r.stdout.split()))
+    assert vals[:2] == [len(kL), len(kR)] and vals[2:4] == [640, 480] and vals[4:6] == [179, 134]
 
 
 @pytest.mark.parametrize("name,levelsup", [("k10-depth4", 2), ("ragged", 2), ("ties", 4)])

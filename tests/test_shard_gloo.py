@@ -44,7 +44,11 @@ def _worker(rank, world, port, tmp):
         local = []
         for s, e in shard.pair_blocks_of_rank(len(pairs), rank, world, block):
             local += [port_lib.match_count(desc[a], desc[b], 50, 0.6) for a, b in pairs[s:e]]
-        full = shard.gather_pair_counts(np.array(local, np.int32), len(pairs), rank, world, block, dist=dist).numpy()
+        mine = shard.pairs_of_rank(pairs, rank, world, block)
+        assert len(mine) == len(local)
+        assert np.array_equal(mine, np.concatenate([pairs[s:e] for s, e in shard.pair_blocks_of_rank(len(pairs), rank, world, block)]))
+        plan = shard.gather_plan(len(pairs), world, block)
+        full = shard.gather_pair_counts(np.array(local, np.int32), plan, dist=dist).numpy()
         want = np.array([port_lib.match_count(desc[a], desc[b], 50, 0.6) for a, b in pairs], np.int32)
         assert np.array_equal(full, want), (rank, full, want)
         assert want.max() > 0
@@ -85,3 +89,28 @@ def test_pair_blocks_cover_every_pair_once():
     for n, world in [(10, 3), (1024, 8), (2, 4)]:
         allf = np.sort(np.concatenate([shard.frames_of_rank(n, r, world) for r in range(world)]))
         assert np.array_equal(allf, np.arange(n))
+
+
+def test_adaptive_block_and_gather_plan():
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as g
+    shard = g.load_package().shard
+    # config-5 sizes: every rank gets at least 16 blocks, ranks differ by at most one block
+    for K, world in [(384, 8), (1024, 1), (1024, 4), (4096, 8), (6, 8)]:
+        P = K * (K - 1) // 2
+        block = shard.adaptive_pair_block(P, world)
+        assert 1 <= block <= 4096
+        sizes = [len(shard.pair_index_of_rank(P, r, world, block)) for r in range(world)]
+        assert sum(sizes) == P
+        if P >= 16 * world:
+            assert max(sizes) - min(sizes) <= block and max(sizes) <= 1.07 * (P / world) + 1
+        # gather with world 1 semantics on the CPU: concatenating every rank's padded buffer and scattering = identity
+        plan = shard.gather_plan(P, world, block)
+        want = (np.arange(P, dtype=np.int32) * 7 + 3) % 1000
+        allc = np.full(world * plan["per_rank"], -1, np.int32)
+        for r in range(world):
+            idx = shard.pair_index_of_rank(P, r, world, block)
+            allc[r * plan["per_rank"]: r * plan["per_rank"] + len(idx)] = want[idx]
+        full = np.empty(P, np.int32)
+        full[plan["dst"].numpy()] = allc[plan["src"].numpy()]
+        assert np.array_equal(full, want)
