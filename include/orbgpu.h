@@ -428,7 +428,7 @@ double orbgpu_last_batch_ms(orbgpu_extractor* e);
  * successive chunks overlap.  streams = 1 serialises the chunks (per-stage event times are then those of
  * each kernel running alone).  Small chunks keep a chunk's pyramid + blurred levels inside L2. */
 int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames);
-/* Largest chunk (frames) the device buffers of one stream context hold for this shape: min(64, 1.5 GB / bytes per frame). */
+/* Largest chunk (frames) the device buffers of one stream context hold for this shape: min(128, 1.5 GB / bytes per frame). */
 int orbgpu_chunk_capacity(orbgpu_extractor* e, int w, int h);
 
 /* Host-buffer entry points (orbgpu_extract, _batch, _batch_async, orbgpu_submit) replay the kernels of a chunk from a CUDA

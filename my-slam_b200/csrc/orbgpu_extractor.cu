@@ -307,7 +307,7 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
     np.bytes_per_frame = np.in_frame_bytes + (size_t)D.pyr_frame_bytes + (size_t)D.blur_frame_bytes +
                          (size_t)D.slot_frame_words * 4 + (size_t)D.scratch_frame_bytes + (size_t)D.ncells * 4 +
                          (size_t)sel_total * 4 + (size_t)np.kmax * 60 + 256;
-    np.chunk_cap = (int)std::min<size_t>(64, std::max<size_t>(1, ((size_t)1536 << 20) / np.bytes_per_frame));
+    np.chunk_cap = (int)std::min<size_t>(128, std::max<size_t>(1, ((size_t)1536 << 20) / np.bytes_per_frame));
 
     struct Guard { Plan& p; bool keep = false; ~Guard() { if (!keep) p.free_dev(); } } guard{np};   // a failed upload frees what was allocated
     CU(cudaMalloc(&np.d_cells, sizeof(OrbCell) * std::max<size_t>(np.cells.size(), 1)));

@@ -18,6 +18,8 @@ ORACLE = os.path.join(ROOT, "oracle")
 PORT_SO = os.path.join(ORACLE, "_build", "liborbport.so")
 REF_SO = os.path.join(ORACLE, "_ref", "liborbref.so")
 FRAME_REF_SO = os.path.join(ORACLE, "_ref", "libframeref.so")
+# the same reference tree with src/ORBmatcher.cc replaced by the product's my-slam_b200/host/ORBmatcher_gpu.cc (calls liborbgpu.so)
+FRAME_GPU_SO = os.path.join(ORACLE, "_ref", "libframegpu.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
@@ -374,12 +376,16 @@ def have_frame_ref():
     return os.path.exists(FRAME_REF_SO)
 
 
+def have_frame_gpu():
+    return os.path.exists(FRAME_GPU_SO) and os.path.exists(FRAME_REF_SO)
+
+
 class OracleFrameRef:
     """The unmodified reference Frame / ORBmatcher code (oracle/ref_frame_wrap.cc).  Method names and results follow the
     frame-side methods of OraclePort so a test can run one case through both."""
 
-    def __init__(self, scale_tables=None):
-        L = self.L = C.CDLL(FRAME_REF_SO)
+    def __init__(self, scale_tables=None, so=None):
+        L = self.L = C.CDLL(so or FRAME_REF_SO)
         L.frameref_gemm3.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_void_p]
         L.frameref_neg_rt_t.argtypes = [C.c_void_p] * 4
         L.frameref_features_in_area.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int,
