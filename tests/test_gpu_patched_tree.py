@@ -181,3 +181,47 @@ def test_patched_sim3_routines(pkg, port, ref, gpu, scene, cfg):
         assert gn == wn and np.array_equal(gm, wm)
         total += wn
     assert total > 100
+
+
+# ---- the Frame-constructor rows, reference library -> device directly --------------------------------------------------------
+@pytest.mark.parametrize("shape", [(640, 480, 1000, (6, 14, 27)), (1241, 376, 2000, (3, 40))])
+def test_device_stereo_matches_equal_reference_frame_code(pkg, oracle, ref, shape):
+    """f1: Frame::ComputeStereoMatches (src/Frame.cc:466-640) executed by the reference's own Frame.cc vs orbgpu_stereo_match."""
+    from test_stereo import _oracle_pair
+    w, h, nf, disp = shape
+    left, right, po, args = _oracle_pair(pkg, oracle, w, h, 0x57E2E002 + w, nf, disp)
+    exL = pkg.ORBextractor(nf, 1.2, 8, 20, 7); exR = pkg.ORBextractor(nf, 1.2, 8, 20, 7)
+    exL(left); exR(right)
+    for bf, b in [(386.1448, 0.5372), (10.0, 0.8)]:
+        wu, wd = ref.stereo_matches(*args, bf, b)
+        u, d = pkg.stereo_match(exL, exR, bf, b)
+        assert (wu >= 0).sum() > 20 and u.tobytes() == wu.tobytes() and d.tobytes() == wd.tobytes()
+
+
+def test_device_undistort_keypoints_equal_reference_frame_code(pkg, ref):
+    """f4: Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cc:404-463) executed by the reference's own Frame.cc on the
+    keypoints the device extracted, vs orbgpu_undistort_keypoints (device-resident keypoints) and orbgpu_undistort_points."""
+    img = pkg.synth.synth(640, 480, 0x5EED0000 + 77)
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    k, _ = ex(img)
+    K4 = np.array([517.306408, 516.469215, 318.643040, 255.313989], np.float32)          # TUM1.yaml
+    dist = np.array([0.262383, -0.953104, -0.005358, 0.002628, 1.163314], np.float32)
+    want, b4 = ref.undistort_keypoints(k, K4, dist, 640, 480)
+    got = ex.undistort_keypoints(K4, dist)
+    assert len(got) == len(k) > 900 and got.tobytes() == want.tobytes()
+    corners = np.array([[0, 0], [640, 0], [0, 480], [640, 480]], np.float32)
+    co = pkg.undistort_points(corners, K4, dist)
+    mine = np.array([min(co[0, 0], co[2, 0]), max(co[1, 0], co[3, 0]), min(co[0, 1], co[1, 1]), max(co[2, 1], co[3, 1])], np.float32)
+    assert mine.tobytes() == b4.tobytes()
+
+
+def test_device_extractor_equals_unmodified_reference_extractor(pkg):
+    """E7: ORBextractor::operator() executed by the UNMODIFIED reference src/ORBextractor.cc (oracle/_ref/liborbref.so) vs the
+    device, on frames that are not among the golden cases."""
+    if not oracle_lib.have_ref():
+        pytest.skip("oracle/_ref/liborbref.so not built")
+    for (w, h, nf, seed) in ((640, 480, 1000, 0xABC001), (752, 480, 1000, 0xABC002), (1241, 376, 2000, 0xABC003)):
+        img = pkg.synth.synth(w, h, seed)
+        rk, rd = oracle_lib.OracleRef(nf, 1.2, 8, 20, 7).extract(img)
+        k, d = pkg.ORBextractor(nf, 1.2, 8, 20, 7)(img)
+        assert len(k) == len(rk) > 0.9 * nf and k.tobytes() == rk.tobytes() and np.array_equal(d, rd)
