@@ -24,6 +24,15 @@
 #ifndef ORB_BLUR_THREADS
 #define ORB_BLUR_THREADS 128 // tasks per k_blur CTA
 
+// Index checks of our own (compute-sanitizer is closed on this pool): compiled in with -DORB_DEBUG_CHECKS, a failed check
+// traps the kernel with file:line (device assert).  The release build compiles them out.
+#ifdef ORB_DEBUG_CHECKS
+#include <assert.h>
+#define ORB_CHECK(cond) assert(cond)
+#else
+#define ORB_CHECK(cond) ((void)0)
+#endif
+
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (kernel, DEVICE): the opt-in is remembered per device
 // ordinal, behind a mutex, so that handles on several GPUs of one process -- possibly on different host threads -- each
 // raise the limit on their own device.  One instance per kernel (a function-local static at the launch site).

@@ -370,7 +370,9 @@ int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
 // local maxima with score >= iniTh, or, if the cell has none, those with score >= minTh.  They
 // are written in row-major order (warp ballot + popc prefix) to the cell's slot area.
 // =================================================================================================
-#define FAST_TP 64            // shared-memory row pitch of the cell tile (max cell image width is 59)
+#ifndef FAST_TP
+#define FAST_TP 64            // shared-memory row pitch of the cell tile and score map (max cell image width is 59); multiple of 16
+#endif
 #ifndef FAST_WARPS
 #define FAST_WARPS 8
 #endif
@@ -459,6 +461,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
         if (c < nw) {
             const uint8_t* g = img - sh + (size_t)(lane >> 4) * pitch + 4 * c;
             uint8_t* t = tile + (lane >> 4) * FAST_TP + 4 * c;
+            ORB_CHECK(ch <= tile_rows && 4 * nw <= FAST_TP);
             for (int r = lane >> 4; r < ch; r += 2, g += 2 * (size_t)pitch, t += 2 * FAST_TP) __pipeline_memcpy_async(t, g, 4);
         }
         __pipeline_commit();
@@ -501,6 +504,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
             const bool c_ = V_ > th;                                                     \
             const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                         \
             if (c_) {                                                                    \
+                ORB_CHECK(o_ >= 3 * FAST_TP + 3 && o_ < (tile_rows - 3) * FAST_TP);      \
                 smap[o_] = (uint8_t)(V_ - 1);                                            \
                 const int p_ = ncor + __popc(bc_ & lt);                                  \
                 if (p_ < FAST_CCAP) cl[p_] = (uint16_t)o_;                               \
@@ -533,6 +537,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                 for (int b = 0; b < 4; ++b)
                     if (f & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(off + b); ++pos; }
                 tail += __shfl_sync(0xffffffffu, incl, 31);
+                ORB_CHECK(tail - head <= FAST_QCAP);
                 __syncwarp();
                 while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
                 __syncwarp();
@@ -578,7 +583,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                     int rank = 0;
                     for (int j = 0; j < K2; ++j) rank += kl[j] < key;
                     const int o = (int)(key >> 8);
-                    if (rank < cell.cap) slot[rank] = ORB_PACK((o & (FAST_TP - 1)) - cs + cell.off_x, (o >> 6) - 3 + cell.off_y, key & 0xFF);
+                    if (rank < cell.cap) slot[rank] = ORB_PACK(o % FAST_TP - cs + cell.off_x, o / FAST_TP - 3 + cell.off_y, key & 0xFF);
                 }
                 cnt = K2;
             } else dense = true;
@@ -716,6 +721,7 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
     for (int k = tid; k < nK; k += OCT_THREADS) {
         int r = (int)__fdiv_rn((float)ORB_PX(o.kxy[k]), hx);
         r = min(r, n_ini - 1);
+        ORB_CHECK(r >= 0 && n_ini <= node_cap);
         o.knode[k] = (uint16_t)r;
         atomicAdd(&o.cnt[0][r], 1);
     }
@@ -816,6 +822,7 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
                     const int kc = o.cc[4 * i + q];
                     if (kc > 0) {
                         const int pos = Mnew - 1 - c; ++c;
+                        ORB_CHECK(pos >= 0 && pos < newSize && newSize <= node_cap);
                         bnd2[pos] = make_short4((q & 1) ? (short)mx : b.x, (q & 1) ? b.y : (short)mx,
                                                 (q & 2) ? (short)my : b.z, (q & 2) ? b.w : (short)my);
                         cnt2[pos] = kc;
@@ -825,6 +832,7 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
                 }
             } else {
                 const int pos = Mnew + i - o.A[i];
+                ORB_CHECK(pos >= Mnew && pos < newSize);
                 o.np[i] = pos;
                 bnd2[pos] = bnd[i];
                 cnt2[pos] = cnt[i];
@@ -832,8 +840,10 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
         }
         if (to_expand) atomicAdd(&s_misc[2], to_expand);
         __syncthreads();
+        const int prev_n = n; (void)prev_n;
         for (int k = tid; k < nK; k += OCT_THREADS) {
             const int nd = o.knode[k];
+            ORB_CHECK(nd < prev_n);
             const int r = o.B[nd];
             o.knode[k] = (uint16_t)((r >= 0 && r < nCommit) ? o.cc[4 * nd + o.kq[k]] : o.np[nd]);
         }
@@ -891,6 +901,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(OrbPlanDev P, int key_sm
             if (cbase[mid] <= k) lo = mid + 1; else hi = mid;
         }
         const int c = lo - 1;
+        ORB_CHECK(c >= 0 && c < L.ncells && k - cbase[c] < cells[c].cap && (keys_in_smem ? k < key_smem_cap : k < L.slot_total));
         o.kxy[k] = slots[cells[c].slot_off + (k - cbase[c])];
     }
     __syncthreads();
@@ -1183,6 +1194,7 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
     if (idx >= cnt_l) return;
     const int o = before + idx;
     if (o >= P.kp_capacity) return;
+    ORB_CHECK(o >= 0 && l < P.nlevels && idx >= 0);
     const uint32_t key = P.sel[(long long)frame * P.sel_total + g];
     const int cx = ORB_PX(key) + ORB_BORDER, cy = ORB_PY(key) + ORB_BORDER;
 
@@ -1197,6 +1209,7 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
     int m10 = 0, m01 = 0;
     if (lane < ORB_PATCH) {
         const int vm = (int)((ORB_UMAX_NIBBLES >> (4 * abs(u))) & 15ull);
+        ORB_CHECK(cx >= ORB_HALF_PATCH && cy >= ORB_HALF_PATCH && cx + ORB_HALF_PATCH < L.w && cy + ORB_HALF_PATCH < L.h);
         const uint8_t* c = img + (size_t)cy * pitch + cx + u;
         int sum = __ldg(c);
 #pragma unroll
@@ -1233,6 +1246,7 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
         const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        ORB_CHECK(cy + r0 >= 0 && cy + r0 < L.h && cx + c0 >= 0 && cx + c0 < L.w && cy + r1 >= 0 && cy + r1 < L.h && cx + c1 >= 0 && cx + c1 < L.w);
         t0[k] = __ldg(bc + r0 * L.pitch + c0); t1[k] = __ldg(bc + r1 * L.pitch + c1);
     }
 #pragma unroll

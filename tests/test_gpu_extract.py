@@ -256,6 +256,26 @@ def test_float_steps_match_host(pkg, oracle, ex1000):
     assert ex1000.debug_sincos_checksum(0, count, 7) == L.orbo_sincos_checksum(0, count, 7, 1)
 
 
+def test_sincos_exhaustive_over_the_angle_domain(pkg, oracle, ex1000):
+    """EVERY float in [0, 2*pi] (step 1: 1 086 918 619 bit patterns -- keypoint angles are degrees in [0, 360) times pi/180):
+    the device's sincosf follower vs the host's glibc sincosf, as an order-independent 64-bit checksum of (x, sin x, cos x).
+    The host side is split over the cores (ctypes releases the GIL); chunk sums add modulo 2^64."""
+    from concurrent.futures import ThreadPoolExecutor
+    L = oracle.OraclePort().L
+    L.orbo_sincos_checksum.restype = C.c_uint64
+    L.orbo_sincos_checksum.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
+    total = int(np.float32(6.2831855).view(np.uint32)) + 1
+    nchunk = 64
+    edges = [total * i // nchunk for i in range(nchunk + 1)]
+    with ThreadPoolExecutor(max(1, len(os.sched_getaffinity(0)))) as pool:
+        parts = list(pool.map(lambda i: L.orbo_sincos_checksum(edges[i], edges[i + 1] - edges[i], 1, 1), range(nchunk)))
+    host = sum(parts) & 0xFFFFFFFFFFFFFFFF
+    dev = 0
+    for i in range(0, nchunk, 8):                              # eight launches: each stays well below the watchdog-free seconds range
+        dev = (dev + ex1000.debug_sincos_checksum(edges[i], edges[i + 8] - edges[i], 1)) & 0xFFFFFFFFFFFFFFFF
+    assert dev == host
+
+
 def test_launches_are_counted(pkg):
     ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
     before = ex.launch_count()
