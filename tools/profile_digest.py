@@ -12,7 +12,7 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CMD = "python bench.py --frames 192 --steps 2 --warmup 3 --no-cpu --hamming-keyframes 0"
+CMD = "python bench.py --frames 192 --steps 2 --warmup 3 --no-cpu --hamming-keyframes 0 --no-workloads --sustained-seconds 0"
 STAGE = {"k_resize_level": "pyramid", "k_fast_cells": "fast_cells", "k_octree": "octree", "k_blur": "blur", "k_describe": "describe"}
 
 
