@@ -770,8 +770,8 @@ def run_ours(args, rank, world, local_rank):
         for k, wl in workloads.items():                       # short CPU legs of the other shapes (about 2 s each)
             name, nfk = WORKLOADS[k]
             PARAMS["nfeatures"] = nfk
-            smp = make_frames_of(pkg, name, max(16, threads), 0)
-            fpsk, kindk, seck, donek = cpu_extractor_fps(smp, threads, 2.0)
+            smp = make_frames_of(pkg, name, max(32, 2 * threads), 0)
+            fpsk, kindk, seck, donek = cpu_extractor_fps(smp, threads, 3.0)
             wl["cpu_baseline"] = {"value": fpsk, "unit": UNIT, "cores": threads if kindk == "reference" else 1, "kind": kindk,
                                   "sample": "%d frames x %d passes = %.1f s" % (len(smp), donek // len(smp), seck)}
             PARAMS["nfeatures"] = nf

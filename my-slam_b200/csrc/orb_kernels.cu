@@ -953,8 +953,9 @@ int orb_launch_octree_single(const uint32_t* d_keys, int n, int W, int H, int N,
 // =================================================================================================
 // GaussianBlur 7x7, sigma 2, REFLECT_101, in OpenCV's unsigned fixed point: 8.8 taps
 // [18,34,48,56,48,34,18], horizontal sums in 16 bits, vertical sums in 32 bits, (v + 2^15) >> 16.
-// One CTA = one 128 x 32 output tile of one level of one frame; the (128+6) x (32+6) input window
-// is staged in shared memory with the border reflection applied at load time.
+// One thread = one 4-pixel word column x ORB_BLUR_ROWS output rows: the horizontal sums of the last seven input rows
+// live in registers (no shared memory), three aligned word loads per input row issued one row ahead; the row-end columns
+// (REFLECT_101) are separate work items on a byte path.  The work list (pl.d_tiles) is built with the plan.
 // =================================================================================================
 #define BLUR_R ORB_BLUR_ROWS   // output rows per thread (4 x the 7-row register ring)
 #define BLUR_THREADS ORB_BLUR_THREADS
