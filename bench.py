@@ -775,6 +775,9 @@ def run_ours(args, rank, world, local_rank):
             wl["cpu_baseline"] = {"value": fpsk, "unit": UNIT, "cores": threads if kindk == "reference" else 1, "kind": kindk,
                                   "sample": "%d frames x %d passes = %.1f s" % (len(smp), donek // len(smp), seck)}
             PARAMS["nfeatures"] = nf
+    if world == 1 and args.rows:
+        import rows_bench                                     # tests/: uses the oracle as checker and as each row's cpu_baseline
+        line["rows"] = rows_bench.run()
     if world > 1:
         dist.destroy_process_group()
     print(json.dumps(line), flush=True)
@@ -908,6 +911,9 @@ def main():
     ap.add_argument("--hamming-keyframes", type=int, default=-1,
                     help="keyframes of the all-pairs Hamming leg (0 = skip; -1 = 1024 below 8 GPUs, the full config 5 = 4096 at 8 GPUs)")
     ap.add_argument("--no-workloads", action="store_true", help="skip the C2 / C3 / C4 lines")
+    ap.add_argument("--rows", action="store_true",
+                    help="add the SURVEY section-8(f) rows (stereo matcher, searches, Fuse, Sim3, BoW ...): public C-ABI call vs its CPU restatement "
+                         "on one thread, each checked against the oracle first (tests/rows_bench.py; N = 1 only)")
     ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the sustained device-resident loop (0 = skip)")
     ap.add_argument("--streams", type=int, default=0, help="internal chunk streams; 0 = library default")
     ap.add_argument("--chunk", type=int, default=0, help="max frames per chunk; 0 = library default")

@@ -409,7 +409,10 @@ __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
     return max(lo, hi) - 256;
 }
 
-#define FAST_QCAP 256         // ring queue of quick-test survivors (per warp)
+#ifndef FAST_P1_UNROLL
+#define FAST_P1_UNROLL 1      // row groups of the quick test per queue insertion (1 or 2)
+#endif
+#define FAST_QCAP (256 * FAST_P1_UNROLL)   // ring queue of quick-test survivors (per warp)
 #define FAST_CCAP 256         // corner list (per warp); denser cells take the dense path
 #define FAST_KCAP 96          // strict maxima ranked by pairwise comparison; more take the dense path
 
@@ -514,6 +517,48 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
 
         if (th <= 126) {
             const unsigned K = (unsigned)(127 - th) * 0x01010101u;
+#if FAST_P1_UNROLL == 2
+            // two row groups per iteration: the "any survivor?" vote, the prefix scan of the per-lane counts and the loop
+            // overhead are paid once per 2 * rpi rows (the queue holds FAST_QCAP = 512 entries: at most 31 + 256 are live)
+            for (int y0 = 0; y0 < ih; y0 += 2 * rpi) {
+                unsigned fA = 0, fB = 0;
+                const int offA = loff + y0 * FAST_TP, offB = offA + rpi * FAST_TP;
+                if (lrow_ok) {
+                    if (y0 + lrow < ih) {
+                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + offA);
+                        const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
+                        const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
+                        fA = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
+                    }
+                    if (y0 + rpi + lrow < ih) {
+                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + offB);
+                        const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
+                        const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
+                        fB = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, (fA | fB) != 0) == 0) continue;
+                const int mine = __popc(fA) + __popc(fB);
+                int incl = mine;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int u = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += u;
+                }
+                int pos = tail + incl - mine;
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if (fA & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(offA + b); ++pos; }
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if (fB & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(offB + b); ++pos; }
+                tail += __shfl_sync(0xffffffffu, incl, 31);
+                ORB_CHECK(tail - head <= FAST_QCAP);
+                __syncwarp();
+                while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
+                __syncwarp();
+            }
+#else
             for (int y0 = 0; y0 < ih; y0 += rpi) {             // rpi rows of nwi words per iteration
                 unsigned f = 0;
                 const int off = loff + y0 * FAST_TP;
@@ -542,6 +587,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                 while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
                 __syncwarp();
             }
+#endif
         } else {                                               // thresholds above 126: score every pixel
             for (int i = 0; i < iw * ih; i += 32) {
                 const int idx = i + lane, y = idx / iw, x = idx - y * iw;

@@ -26,7 +26,8 @@ def med(f, reps=30, warm=3):
     return float(np.median(t)) * 1e3
 
 
-def main():
+def run():
+    """-> {row: {"gpu_ms": ..., "cpu_ms": ...}}; every row's results are checked against the oracle before it is timed."""
     pkg = g.load_package()
     po = oracle_lib.OraclePort()
     out = {"unit": "ms per call (median)", "cpu": "oracle restatement, 1 thread"}
@@ -204,7 +205,11 @@ def main():
         "gpu_ms_detect_with_python_host_part": med(lambda: db.detect_relocalization_candidates(qq, lambda k: neighbours[k])),
         "cpu_ms": med(lambda: oracle_lib.port_db_detect(dargs), 10, 2), "candidates": len(got),
         "sharing_words": int(want[0].sum())}
-    print(json.dumps(out, indent=1))
+    return out
+
+
+def main():
+    print(json.dumps(run(), indent=1))
 
 
 if __name__ == "__main__":
