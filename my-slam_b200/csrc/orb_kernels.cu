@@ -410,10 +410,12 @@ __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
 }
 
 #ifndef FAST_P1_UNROLL
-#define FAST_P1_UNROLL 1      // row groups of the quick test per queue insertion (1 or 2)
+#define FAST_P1_UNROLL 3      // row groups of the quick test per queue insertion (1 .. 3)
 #endif
-#define FAST_QCAP (256 * FAST_P1_UNROLL)   // ring queue of quick-test survivors (per warp)
+#define FAST_QCAP (FAST_P1_UNROLL == 1 ? 256 : 512)   // ring queue of quick-test survivors (per warp): power of two >= 31 + 128 * unroll
+#ifndef FAST_CCAP
 #define FAST_CCAP 256         // corner list (per warp); denser cells take the dense path
+#endif
 #define FAST_KCAP 96          // strict maxima ranked by pairwise comparison; more take the dense path
 
 // flags (bit 7 of each byte) of  max(a, b) > th  for 4 packed bytes, th <= 126; K = (127 - th) * 0x01010101
@@ -422,10 +424,10 @@ __device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned b, unsigned K)
     return ((a & 0x7f7f7f7fu) + K) | a | ((b & 0x7f7f7f7fu) + K) | b;
 }
 
-__device__ __forceinline__ int fast_max8(const uint8_t* s)
+__device__ __forceinline__ int fast_max8(const uint8_t* s, int p)
 {
-    return max(max(max((int)s[-FAST_TP - 1], (int)s[-FAST_TP]), max((int)s[-FAST_TP + 1], (int)s[-1])),
-               max(max((int)s[1], (int)s[FAST_TP - 1]), max((int)s[FAST_TP], (int)s[FAST_TP + 1])));
+    return max(max(max((int)s[-p - 1], (int)s[-p]), max((int)s[-p + 1], (int)s[-1])),
+               max(max((int)s[1], (int)s[p - 1]), max((int)s[p], (int)s[p + 1])));
 }
 
 // One warp = one cell, exactly as the reference runs it: cv::FAST(cell, iniThFAST, nonmax) and, when that
@@ -436,8 +438,9 @@ __device__ __forceinline__ int fast_max8(const uint8_t* s)
 //      score = V - 1 where V > th, into the cell-local score map; corners are also appended to a list;
 //   3. strict 8-neighbour maxima of the listed corners, ranked by position (row-major) by pairwise comparison
 //      and written in order.  Cells too dense for the lists fall back to an ordered scan of the score map.
-__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, int tile_rows)
+__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
 {
+    const int tile_rows = P.fast_rows, spw = P.fast_spw;
     extern __shared__ __align__(16) uint8_t fast_smem[];
     __shared__ uint16_t s_queue[FAST_WARPS][FAST_QCAP];
     __shared__ uint16_t s_corner[FAST_WARPS][FAST_CCAP];
@@ -448,7 +451,11 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
     if (cell_id >= P.ncells) return;
     const OrbCell cell = P.cells[cell_id];
     const int l = cell.level;
-    uint8_t* tile = fast_smem + (size_t)warp * 2 * FAST_TP * tile_rows;
+    // per warp: the cell tile (pitch FAST_TP) and the score map of the cell interior with a 1-px rim (pitch spw): entry
+    // (x + 1) + (y + 1) * spw for interior pixel (x, y).  The map is kept as small as the cell allows: k_fast_cells' shared
+    // memory decides the L1 carve-out of every SM it runs on (4 CTAs x 40 KB fit the 164 KB step, 47 KB did not).
+    const int warp_bytes = FAST_TP * tile_rows + ((spw * (tile_rows - 4) + 15) & ~15);
+    uint8_t* tile = fast_smem + (size_t)warp * warp_bytes;
     uint8_t* smap = tile + FAST_TP * tile_rows;
     const int cw = cell.cw, ch = cell.ch, iw = cw - 6, ih = ch - 6;
     uint32_t* cnt_out = P.cellcnt + (long long)frame * P.ncells + cell_id;
@@ -493,8 +500,8 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
     for (int attempt = 0; attempt < 2; ++attempt) {
         const int th = attempt ? P.min_th : P.ini_th;
         {
-            uint4* z = reinterpret_cast<uint4*>(smap + 2 * FAST_TP);        // rows 2 .. ih+3: interior + NMS rim
-            for (int i = lane; i < (ih + 2) * (FAST_TP / 16); i += 32) z[i] = make_uint4(0, 0, 0, 0);
+            uint4* z = reinterpret_cast<uint4*>(smap);                      // interior + NMS rim
+            for (int i = lane; i < ((ih + 2) * spw + 15) >> 4; i += 32) z[i] = make_uint4(0, 0, 0, 0);
         }
         __syncwarp();
         int head = 0, tail = 0, ncor = 0;
@@ -508,7 +515,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
             const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                         \
             if (c_) {                                                                    \
                 ORB_CHECK(o_ >= 3 * FAST_TP + 3 && o_ < (tile_rows - 3) * FAST_TP);      \
-                smap[o_] = (uint8_t)(V_ - 1);                                            \
+                smap[(o_ / FAST_TP - 2) * spw + o_ % FAST_TP - cs + 1] = (uint8_t)(V_ - 1);    \
                 const int p_ = ncor + __popc(bc_ & lt);                                  \
                 if (p_ < FAST_CCAP) cl[p_] = (uint16_t)o_;                               \
             }                                                                            \
@@ -517,60 +524,27 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
 
         if (th <= 126) {
             const unsigned K = (unsigned)(127 - th) * 0x01010101u;
-#if FAST_P1_UNROLL == 2
-            // two row groups per iteration: the "any survivor?" vote, the prefix scan of the per-lane counts and the loop
-            // overhead are paid once per 2 * rpi rows (the queue holds FAST_QCAP = 512 entries: at most 31 + 256 are live)
-            for (int y0 = 0; y0 < ih; y0 += 2 * rpi) {
-                unsigned fA = 0, fB = 0;
-                const int offA = loff + y0 * FAST_TP, offB = offA + rpi * FAST_TP;
-                if (lrow_ok) {
-                    if (y0 + lrow < ih) {
-                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + offA);
+            // FAST_P1_UNROLL row groups per iteration: the "any survivor?" vote, the prefix scan of the per-lane counts and the
+            // loop overhead are paid once per FAST_P1_UNROLL * rpi rows (at most 31 + 128 * FAST_P1_UNROLL queue entries are live)
+            for (int y0 = 0; y0 < ih; y0 += FAST_P1_UNROLL * rpi) {
+                unsigned f[FAST_P1_UNROLL];
+                const int off0 = loff + y0 * FAST_TP;
+                int mine = 0;
+                unsigned any = 0;
+#pragma unroll
+                for (int g = 0; g < FAST_P1_UNROLL; ++g) {
+                    f[g] = 0;
+                    if (lrow_ok && y0 + g * rpi + lrow < ih) {
+                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off0 + g * rpi * FAST_TP);
                         const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
                         const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
-                        fA = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
+                        f[g] = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
                     }
-                    if (y0 + rpi + lrow < ih) {
-                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + offB);
-                        const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
-                        const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
-                        fB = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
-                    }
+                    any |= f[g];
+                    mine += __popc(f[g]);
                 }
-                if (__ballot_sync(0xffffffffu, (fA | fB) != 0) == 0) continue;
-                const int mine = __popc(fA) + __popc(fB);
-                int incl = mine;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const int u = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += u;
-                }
-                int pos = tail + incl - mine;
-#pragma unroll
-                for (int b = 0; b < 4; ++b)
-                    if (fA & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(offA + b); ++pos; }
-#pragma unroll
-                for (int b = 0; b < 4; ++b)
-                    if (fB & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(offB + b); ++pos; }
-                tail += __shfl_sync(0xffffffffu, incl, 31);
-                ORB_CHECK(tail - head <= FAST_QCAP);
-                __syncwarp();
-                while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
-                __syncwarp();
-            }
-#else
-            for (int y0 = 0; y0 < ih; y0 += rpi) {             // rpi rows of nwi words per iteration
-                unsigned f = 0;
-                const int off = loff + y0 * FAST_TP;
-                if (lrow_ok && y0 + lrow < ih) {
-                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(tile + off);
-                    const unsigned wm = wp[0], wl = wp[-1], wr = wp[1], wn = wp[3 * FAST_TP / 4], ws = wp[-3 * FAST_TP / 4];
-                    const unsigned we = __byte_perm(wm, wr, 0x6543), ww = __byte_perm(wl, wm, 0x4321);
-                    f = fast_gt4(__vabsdiffu4(wn, wm), __vabsdiffu4(ws, wm), K) & fast_gt4(__vabsdiffu4(we, wm), __vabsdiffu4(ww, wm), K) & lmask;
-                }
-                if (__ballot_sync(0xffffffffu, f != 0) == 0) continue;
+                if (__ballot_sync(0xffffffffu, any != 0) == 0) continue;
                 // queue order is irrelevant (results are keyed by position): exclusive prefix of the per-lane counts
-                const int mine = __popc(f);
                 int incl = mine;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -579,15 +553,17 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                 }
                 int pos = tail + incl - mine;
 #pragma unroll
-                for (int b = 0; b < 4; ++b)
-                    if (f & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(off + b); ++pos; }
+                for (int g = 0; g < FAST_P1_UNROLL; ++g) {
+#pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                        if (f[g] & (0x80u << (8 * b))) { q[pos & (FAST_QCAP - 1)] = (uint16_t)(off0 + g * rpi * FAST_TP + b); ++pos; }
+                }
                 tail += __shfl_sync(0xffffffffu, incl, 31);
                 ORB_CHECK(tail - head <= FAST_QCAP);
                 __syncwarp();
                 while (tail - head >= 32) { FAST_DRAIN(true); head += 32; }
                 __syncwarp();
             }
-#endif
         } else {                                               // thresholds above 126: score every pixel
             for (int i = 0; i < iw * ih; i += 32) {
                 const int idx = i + lane, y = idx / iw, x = idx - y * iw;
@@ -614,8 +590,9 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                 unsigned key = 0;
                 if (i + lane < ncor) {
                     const int o = cl[i + lane];
-                    const int v = smap[o];
-                    kp = v > fast_max8(smap + o);
+                    const uint8_t* sp = smap + (o / FAST_TP - 2) * spw + o % FAST_TP - cs + 1;
+                    const int v = sp[0];
+                    kp = v > fast_max8(sp, spw);
                     key = ((unsigned)o << 8) | (unsigned)v;
                 }
                 const unsigned bk = __ballot_sync(0xffffffffu, kp);
@@ -643,9 +620,9 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
                 bool kp = false;
                 if (idx < tot) {
                     y = __float2int_rd(((float)idx + 0.5f) * inv_iw); x = idx - y * iw;
-                    const uint8_t* sp = smap + (y + 3) * FAST_TP + cs + x;
+                    const uint8_t* sp = smap + (y + 1) * spw + x + 1;
                     v = sp[0];
-                    kp = v > 0 && v > fast_max8(sp);
+                    kp = v > 0 && v > fast_max8(sp, spw);
                 }
                 const unsigned bk = __ballot_sync(0xffffffffu, kp);
                 if (kp) { const int p = cnt + __popc(bk & lt); if (p < cell.cap) slot[p] = ORB_PACK(x + cell.off_x, y + cell.off_y, v); }
@@ -660,7 +637,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P, in
 int orb_fast_smem_bytes(int max_cw, int max_ch)
 {
     if (max_cw + 3 > FAST_TP) return -1;                  // + up to 3 bytes of alignment shift
-    return FAST_WARPS * 2 * FAST_TP * max_ch;
+    return FAST_WARPS * (FAST_TP * max_ch + ((orb_fast_spw(max_cw) * (max_ch - 4) + 15) & ~15));
 }
 
 int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream_t st)
@@ -668,7 +645,7 @@ int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream
     static OrbSmemOptIn optin;
     if (optin.ensure(k_fast_cells, smem_bytes) != cudaSuccess) return -1;
     dim3 grid((P.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    k_fast_cells<<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P, smem_bytes / (FAST_WARPS * 2 * FAST_TP));
+    k_fast_cells<<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P);
     return 1;
 }
 
