@@ -109,7 +109,7 @@ struct orbgpu_extractor {
     // how a batch call is cut up: [0] host-buffer calls (finer chunks pipeline PCIe against the kernels),
     // [1] device-buffer calls (fewer, larger launches); orbgpu_set_batching overrides both
     int nstream[2] = {8, 4};            // chunk streams a batch call deals its chunks to (1..NSTREAM)
-    int max_chunk[2] = {32, 64};        // frames per chunk (upper bound; also capped by plan.chunk_cap)
+    int max_chunk[2] = {64, 128};       // frames per chunk (upper bound; also capped by plan.chunk_cap); B200 sweep: profiles/r2_batching_sweep.txt
     double stage_ms[ORBGPU_NUM_STAGES] = {};
     uint64_t launches = 0;
     uint64_t next_ticket = 1;
