@@ -416,9 +416,15 @@ def measure_extraction(ctx, pkg, frames_np, nfeatures, steps, warmup, args, seri
     cap = ex.max_keypoints(w, h)
     if args.streams or args.chunk:
         ex.set_batching(args.streams or 4, args.chunk or 64)
-    h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
-    h_frames.numpy()[:] = frames_np
-    d_frames = h_frames.cuda()
+    wc = None
+    if args.wc_input:                                         # frames in write-combined pinned memory (orbgpu_host_alloc): CPU-write-only
+        wc = pkg.HostBuffer((n, h, w), np.uint8, write_combined=True)
+        wc.array[:] = frames_np
+        h_frames = torch.from_numpy(wc.array)
+    else:
+        h_frames = torch.empty((n, h, w), dtype=torch.uint8, pin_memory=True)
+        h_frames.numpy()[:] = frames_np
+    d_frames = torch.from_numpy(frames_np).cuda() if wc is not None else h_frames.cuda()
     d_kps = torch.empty((n, cap, 28), dtype=torch.uint8, device="cuda")
     d_desc = torch.empty((n, cap, 32), dtype=torch.uint8, device="cuda")
     d_nout = torch.empty((n,), dtype=torch.int32, device="cuda")
@@ -540,6 +546,8 @@ def measure_extraction(ctx, pkg, frames_np, nfeatures, steps, warmup, args, seri
         ex.set_profiling(False)
     ex.close()
     del d_frames, d_kps, d_desc, d_nout, h_frames, outs
+    if wc is not None:
+        wc.close()
     torch.cuda.empty_cache()
     return R
 
@@ -910,6 +918,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--hamming-keyframes", type=int, default=-1,
                     help="keyframes of the all-pairs Hamming leg (0 = skip; -1 = 1024 below 8 GPUs, the full config 5 = 4096 at 8 GPUs)")
+    ap.add_argument("--wc-input", action="store_true", help="keep the host frames in write-combined pinned memory (orbgpu_host_alloc)")
     ap.add_argument("--no-workloads", action="store_true", help="skip the C2 / C3 / C4 lines")
     ap.add_argument("--rows", action="store_true",
                     help="add the SURVEY section-8(f) rows (stereo matcher, searches, Fuse, Sim3, BoW ...): public C-ABI call vs its CPU restatement "

@@ -105,6 +105,14 @@ int orbgpu_extract_batch_device(orbgpu_extractor* e, const uint8_t* d_frames, in
                                 size_t row_stride, size_t frame_stride,
                                 orbgpu_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out);
 
+/* Page-locked host memory for the caller's frame / result buffers (the batch entry points use pinned caller buffers in place;
+ * this spares a caller that does not link the CUDA runtime a cudaHostAlloc of its own).  write_combined != 0 asks for
+ * write-combined memory: meant for buffers the CPU only WRITES (camera frames on their way to the GPU) -- the device reads
+ * them without snooping the CPU caches, CPU reads of such memory are very slow, so never use it for results.  The memory
+ * is portable across the devices of the process.  The reference keeps frames in cv::Mat heap memory (src/Tracking.cc:239). */
+int orbgpu_host_alloc(void** out, size_t bytes, int write_combined);
+void orbgpu_host_free(void* p);
+
 /* Input pixel format of the frames handed to every extraction entry point of this handle: 1 (gray, default),
  * 3 or 4 interleaved 8-bit channels; rgb_order != 0 means R,G,B[,A], else B,G,R[,A].  Colour frames are converted
  * on the device exactly as Tracking::GrabImageMonocular does on the host before it constructs the Frame

@@ -21,12 +21,38 @@ __device__ __align__(16) int8_t g_pattern[1024];
 // 15,15,15,15,14,14,14,13,13,12,11,10,9,8,6,3.  The disc is symmetric, so column u holds rows |v| <= umax[|u|].
 #define ORB_UMAX_NIBBLES 0x3689abcddeeeffffull
 
+// IC_Angle weights for the word path of k_describe: the 31 x 31 window around a keypoint is read as 31 rows x 9 aligned
+// words starting at column cx - 15 - s, s = (cx - 15) & 3.  Entry [s][row * 9 + word] = (the four bytes' u as signed bytes
+// where the pixel lies in the disc, else 0; 1 per byte in the disc, else 0): row v = row - 15 holds |u| <= umax[|v|]
+// (src/ORBextractor.cc:86-103).
+#ifndef ORB_IC_WORDS_PATH
+#define ORB_IC_WORDS_PATH 1
+#endif
+#define IC_WORDS 9
+#define IC_ITEMS 288          // 31 * 9 = 279 items, padded to 9 per lane
+__device__ __align__(16) uint2 g_ic_weights[4 * IC_ITEMS];
+
 int orb_upload_constants(const int* umax16)
 {
     // the disc table is a constant of the algorithm (HALF_PATCH_SIZE 15); the kernels carry it packed
     for (int i = 0; i < 16; ++i)
         if (umax16[i] != (int)((ORB_UMAX_NIBBLES >> (4 * i)) & 15ull)) return -1;
     if (cudaMemcpyToSymbol(g_pattern, ORB_PATTERN_XY, 1024) != cudaSuccess) return -1;
+    static uint2 tab[4 * IC_ITEMS];
+    for (int sft = 0; sft < 4; ++sft)
+        for (int i = 0; i < IC_ITEMS; ++i) {
+            const int row = i / IC_WORDS, word = i % IC_WORDS, v = row - ORB_HALF_PATCH;
+            unsigned wu = 0, wm = 0;
+            for (int b = 0; b < 4; ++b) {
+                const int u = 4 * word + b - sft - ORB_HALF_PATCH;
+                if (row < ORB_PATCH && abs(u) <= ORB_HALF_PATCH && abs(u) <= umax16[abs(v)]) {
+                    wu |= (unsigned)(u & 0xFF) << (8 * b);
+                    wm |= 1u << (8 * b);
+                }
+            }
+            tab[sft * IC_ITEMS + i] = make_uint2(wu, wm);
+        }
+    if (cudaMemcpyToSymbol(g_ic_weights, tab, sizeof(tab)) != cudaSuccess) return -1;
     return 0;
 }
 
@@ -1229,8 +1255,37 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
     // ---- IC_Angle on the unblurred level: lane = column u of the disc, rows v = -vm .. vm
     const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame);
     const int pitch = orb_level_pitch(P, l);
-    const int u = lane - ORB_HALF_PATCH;
     int m10 = 0, m01 = 0;
+#if ORB_IC_WORDS_PATH
+    {
+        // lane -> items lane, lane + 32, ...: item = (row, word) of the 31 x 9-word window; consecutive lanes read consecutive
+        // words of a row (one instruction spans about 3.5 rows).  Nine independent word loads + nine weight loads per lane,
+        // then two IDP.4A each: sum of u * I (u8 x s8) and the row's plain sum (times v) -- the integer moments of :86-103.
+        const int sft = (cx - ORB_HALF_PATCH) & 3;
+        const uint8_t* w0 = img + (size_t)(cy - ORB_HALF_PATCH) * pitch + (cx - ORB_HALF_PATCH - sft);
+        const uint2* wt = g_ic_weights + sft * IC_ITEMS + lane;
+        unsigned pix[IC_WORDS];
+        uint2 wgt[IC_WORDS];
+        int rows[IC_WORDS];
+#pragma unroll
+        for (int k = 0; k < IC_WORDS; ++k) {
+            const int i = lane + 32 * k;
+            const int row = min((i * 57) >> 9, ORB_PATCH - 1);          // i / 9 for i < 288; the padding items reread row 30 with weight 0
+            const int word = i - IC_WORDS * ((i * 57) >> 9);
+            rows[k] = row;
+            wgt[k] = __ldg(wt + 32 * k);
+            pix[k] = __ldg(reinterpret_cast<const unsigned*>(w0 + (size_t)row * pitch) + (i < ORB_PATCH * IC_WORDS ? word : 0));
+        }
+#pragma unroll
+        for (int k = 0; k < IC_WORDS; ++k) {
+            int su;
+            asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(su) : "r"(pix[k]), "r"(wgt[k].x), "r"(m10));
+            m10 = su;
+            m01 += (rows[k] - ORB_HALF_PATCH) * (int)__dp4a(pix[k], wgt[k].y, 0u);
+        }
+    }
+#else
+    const int u = lane - ORB_HALF_PATCH;
     if (lane < ORB_PATCH) {
         const int vm = (int)((ORB_UMAX_NIBBLES >> (4 * abs(u))) & 15ull);
         ORB_CHECK(cx >= ORB_HALF_PATCH && cy >= ORB_HALF_PATCH && cx + ORB_HALF_PATCH < L.w && cy + ORB_HALF_PATCH < L.h);
@@ -1246,6 +1301,7 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
         }
         m10 = u * sum;
     }
+#endif
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         m10 += __shfl_xor_sync(0xffffffffu, m10, d);

@@ -1277,6 +1277,19 @@ int orbgpu_set_batching(orbgpu_extractor* e, int streams, int max_chunk_frames)
     return ORBGPU_OK;
 }
 
+int orbgpu_host_alloc(void** out, size_t bytes, int write_combined)
+{
+    if (!out || bytes == 0) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    CU(cudaHostAlloc(out, bytes, write_combined ? (cudaHostAllocWriteCombined | cudaHostAllocPortable) : cudaHostAllocPortable));
+    return ORBGPU_OK;
+}
+
+void orbgpu_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+
 int orbgpu_chunk_capacity(orbgpu_extractor* e, int w, int h)
 {
     if (!e) return ORBGPU_ERR_ARG;

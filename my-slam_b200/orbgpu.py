@@ -282,6 +282,8 @@ def lib():
         "orbgpu_extract_batch_device": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_extract_batch_async": (i32, [vp, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_wait": (i32, [vp]),
+        "orbgpu_host_alloc": (i32, [C.POINTER(vp), sz, i32]),
+        "orbgpu_host_free": (None, [vp]),
         "orbgpu_extract_batch_multi": (i32, [vp, i32, vp, i32, i32, i32, sz, sz, vp, vp, i32, vp]),
         "orbgpu_stereo_match": (i32, [vp, vp, f32, f32, vp, vp, i32, pi]),
         "orbgpu_set_input_format": (i32, [vp, i32, i32]),
@@ -552,6 +554,26 @@ class ORBextractor:
     def set_graphs(self, on): _check(self._L.orbgpu_set_graphs(self._h, int(bool(on))))
 
     def last_batch_ms(self): return float(self._L.orbgpu_last_batch_ms(self._h))
+
+
+class HostBuffer:
+    """Page-locked host memory from orbgpu_host_alloc as a numpy array (`.array`); write_combined for CPU-write-only inputs."""
+
+    def __init__(self, shape, dtype=np.uint8, write_combined=False):
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._p = C.c_void_p()
+        _check(lib().orbgpu_host_alloc(C.byref(self._p), n, int(bool(write_combined))))
+        buf = (C.c_ubyte * n).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        self.ptr = self._p.value
+
+    def close(self):
+        if getattr(self, "_p", None) and self._p.value:
+            self.array = None
+            lib().orbgpu_host_free(self._p)
+            self._p = C.c_void_p()
+
+    __del__ = close
 
 
 def extract_batch_multi(extractors, frames):
