@@ -1016,14 +1016,62 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
+// Input row number with REFLECT_101.  From 8 rows up one reflection per side is exact for every row a strip USES
+// (-3 <= i <= hgt + 2); rows past the strip's last output are loaded but never used and are only clamped into the image.
+__device__ __forceinline__ int blur_row(int i, int hgt)
+{
+    if (hgt < 8) return reflect101(i, hgt);
+    const int a = i < 0 ? -i : i;
+    const int b = a >= hgt ? 2 * (hgt - 1) - a : a;
+    return min(max(b, 0), hgt - 1);
+}
+
 // The 12-byte window (wl, wm, wr) of one input row around word column wc: bytes I(4wc - 4 .. 4wc + 7).
 // WORDS: three aligned 32-bit loads (the whole window lies inside the row); otherwise byte loads with
 // REFLECT_101 (row ends, or rows that are not 4-byte aligned).
-template <bool WORDS>
-__device__ __forceinline__ uint3 blur_load(const uint8_t* __restrict__ rowp, int wc, int w)
+// Right-edge columns on aligned rows (mode 2): the window's bytes beyond the row end are REFLECT_101 copies of bytes that
+// lie in the four aligned words wc - 2 .. wc + 1, and the four source bytes of each output word always fall into two
+// ADJACENT words of those, so an output word is one PRMT of a word pair; which pair (0..2) and the selector are fixed per
+// thread (blur_edge_sel) -- four word loads and two PRMT per row instead of ten byte loads and their reassembly.
+struct BlurEdgeSel { unsigned sel_m, sel_r; int pair_m, pair_r, w3; };
+
+__device__ __forceinline__ BlurEdgeSel blur_edge_sel(int wc, int w, int pitch)
+{
+    BlurEdgeSel e;
+    unsigned sel[2]; int pr[2];
+#pragma unroll
+    for (int X = 1; X <= 2; ++X) {
+        int o[4], mn = 16;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int i = 4 * wc - 4 + 4 * X + b;
+            const int sidx = i >= w ? 2 * (w - 1) - i : i;              // one reflection: w >= 16 and i < w + 8
+            o[b] = sidx - 4 * (wc - 2);
+            mn = min(mn, o[b]);
+        }
+        const int pi = min(mn >> 2, 2);
+        unsigned sl = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) sl |= (unsigned)(o[b] - 4 * pi) << (4 * b);
+        sel[X - 1] = sl; pr[X - 1] = pi;
+    }
+    e.sel_m = sel[0]; e.sel_r = sel[1]; e.pair_m = pr[0]; e.pair_r = pr[1];
+    e.w3 = min(wc + 1, (pitch >> 2) - 1) - wc;                        // word wc + 1 if it lies inside the pitch, else wc again
+    return e;
+}
+
+template <int MODE>
+__device__ __forceinline__ uint3 blur_load(const uint8_t* __restrict__ rowp, int wc, int w, const BlurEdgeSel& es)
 {
     unsigned wl, wm, wr;
-    if (WORDS) {
+    const bool WORDS = MODE == 1;
+    if (MODE == 2) {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(rowp) + wc;
+        const unsigned q0 = __ldg(p - 2), q1 = __ldg(p - 1), q2 = __ldg(p), q3 = __ldg(p + es.w3);
+        wl = q1;
+        wm = __byte_perm(es.pair_m == 0 ? q0 : (es.pair_m == 1 ? q1 : q2), es.pair_m == 0 ? q1 : (es.pair_m == 1 ? q2 : q3), es.sel_m);
+        wr = __byte_perm(es.pair_r == 0 ? q0 : (es.pair_r == 1 ? q1 : q2), es.pair_r == 0 ? q1 : (es.pair_r == 1 ? q2 : q3), es.sel_r);
+    } else if (WORDS) {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(rowp) + wc;
         wm = __ldg(p);
         wr = __ldg(p + 1);
@@ -1073,25 +1121,79 @@ __device__ __forceinline__ void blur_hsum(const uint3 r, unsigned h[4])
 #ifndef BLUR_AHEAD
 #define BLUR_AHEAD 1
 #endif
-template <bool WORDS, bool INNER>
+#ifndef BLUR_VDP2A
+#define BLUR_VDP2A 1          // vertical pass with IDP.2A on row pairs (0: adds + IMADs on single rows)
+#endif
+#ifndef BLUR_EDGE_WORDS
+#define BLUR_EDGE_WORDS 1     // right-edge columns of aligned rows on the word + PRMT path (0: byte path)
+#endif
+template <int MODE, bool INNER>
 __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int sp, uint8_t* __restrict__ dst, int dp,
                                            int w, int hgt, int wc, int y0)
 {
+    BlurEdgeSel es = {0, 0, 0, 0, 0};
+    if (MODE == 2) es = blur_edge_sel(wc, w, sp);
     // input row y0 - 3 + k; rows are REFLECT_101-mapped only in the first / last strip; INNER: known at compile time not
     // to need it (the word path, where the row arithmetic is a visible share of the instructions)
     const bool inner = INNER || (y0 >= 3 && y0 + BLUR_R + 3 + BLUR_AHEAD <= hgt);
+#if !BLUR_VDP2A
     unsigned ring[7][4];
+#endif
     // the row numbers of the 6 + BLUR_AHEAD start-up rows first (reflect101 is a loop: computed between the loads it put a
     // branch after every row and serialised their round trips), then all their loads, then the sums
     int yy0[6 + BLUR_AHEAD];
 #pragma unroll
-    for (int k = 0; k < 6 + BLUR_AHEAD; ++k) yy0[k] = inner ? y0 - 3 + k : reflect101(y0 - 3 + k, hgt);
+    for (int k = 0; k < 6 + BLUR_AHEAD; ++k) yy0[k] = inner ? y0 - 3 + k : blur_row(y0 - 3 + k, hgt);
     uint3 first[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) first[k] = blur_load<WORDS>(src + (size_t)yy0[k] * sp, wc, w);
+    for (int k = 0; k < 6; ++k) first[k] = blur_load<MODE>(src + (size_t)yy0[k] * sp, wc, w, es);
     uint3 ahead[BLUR_AHEAD];                                   // rows y0 + 3 .. y0 + 3 + BLUR_AHEAD - 1, in flight
 #pragma unroll
-    for (int a = 0; a < BLUR_AHEAD; ++a) ahead[a] = blur_load<WORDS>(src + (size_t)yy0[6 + a] * sp, wc, w);
+    for (int a = 0; a < BLUR_AHEAD; ++a) ahead[a] = blur_load<MODE>(src + (size_t)yy0[6 + a] * sp, wc, w, es);
+#if BLUR_VDP2A
+    // vertical pass on PAIRS of adjacent rows: pr[m % 7][p] = h_m | h_{m+1} << 16 (h < 2^16), so that
+    // v_j = (18, 34).(h_j, h_j+1) + (48, 56).(h_j+2, h_j+3) + (48, 34).(h_j+4, h_j+5) + 18 h_j+6 is three IDP.2A and one IMAD
+    // per pixel, plus one PRMT per pixel and row to form the newest pair, instead of three adds and four IMADs
+    const unsigned K01 = 18u | (34u << 8), K23 = 48u | (56u << 8), K45 = 48u | (34u << 8);
+    unsigned pr[7][4], hprev[4];
+    {
+        unsigned h0[4], h1[4];
+        blur_hsum(first[0], h0);
+#pragma unroll
+        for (int k = 1; k < 6; ++k) {
+            blur_hsum(first[k], h1);
+#pragma unroll
+            for (int p = 0; p < 4; ++p) { pr[k - 1][p] = __byte_perm(h0[p], h1[p], 0x5410); h0[p] = h1[p]; }
+        }
+#pragma unroll
+        for (int p = 0; p < 4; ++p) hprev[p] = h0[p];
+    }
+    for (int yb = 0; yb < BLUR_R; yb += 7) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            const int y = y0 + yb + j;
+            const uint3 cur = ahead[0];
+#pragma unroll
+            for (int a = 0; a + 1 < BLUR_AHEAD; ++a) ahead[a] = ahead[a + 1];
+            {
+                const int yn = y + 3 + BLUR_AHEAD;             // rows past the strip are loaded but never used
+                const int yy = inner ? yn : blur_row(yn, hgt);
+                ahead[BLUR_AHEAD - 1] = blur_load<MODE>(src + (size_t)yy * sp, wc, w, es);
+            }
+            unsigned hn[4], v[4];
+            blur_hsum(cur, hn);
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                pr[(j + 5) % 7][p] = __byte_perm(hprev[p], hn[p], 0x5410);
+                hprev[p] = hn[p];
+                v[p] = __dp2a_lo(pr[j % 7][p], K01, __dp2a_lo(pr[(j + 2) % 7][p], K23, __dp2a_lo(pr[(j + 4) % 7][p], K45, 18u * hn[p] + 32768u)));
+            }
+            const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+            if (y < hgt) *reinterpret_cast<uint32_t*>(dst + (size_t)y * dp + 4 * wc) = out;
+        }
+    }
+}
+#else
 #pragma unroll
     for (int k = 0; k < 6; ++k) blur_hsum(first[k], ring[k]);
     for (int yb = 0; yb < BLUR_R; yb += 7) {
@@ -1103,8 +1205,8 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int 
             for (int a = 0; a + 1 < BLUR_AHEAD; ++a) ahead[a] = ahead[a + 1];
             {
                 const int yn = y + 3 + BLUR_AHEAD;             // rows past the strip are loaded but never used
-                const int yy = inner ? yn : reflect101(yn, hgt);
-                ahead[BLUR_AHEAD - 1] = blur_load<WORDS>(src + (size_t)yy * sp, wc, w);
+                const int yy = inner ? yn : blur_row(yn, hgt);
+                ahead[BLUR_AHEAD - 1] = blur_load<MODE>(src + (size_t)yy * sp, wc, w, es);
             }
             blur_hsum(cur, ring[(j + 6) % 7]);
             unsigned v[4];
@@ -1118,11 +1220,25 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int 
         }
     }
 }
+#endif
+
+// the rare paths as real calls: inlined beside the word path they cost it spilled registers under the kernel's 56-register cap
+__device__ __noinline__ void blur_strip_edge(const uint8_t* src, int sp, uint8_t* dst, int dp, int w, int hgt, int wc, int y0)
+{
+    blur_strip<2, false>(src, sp, dst, dp, w, hgt, wc, y0);
+}
+__device__ __noinline__ void blur_strip_bytes(const uint8_t* src, int sp, uint8_t* dst, int dp, int w, int hgt, int wc, int y0)
+{
+    blur_strip<0, false>(src, sp, dst, dp, w, hgt, wc, y0);
+}
 
 // Work list entry: (level, first task, kind).  kind 0 = interior word columns [0, nfast) on the aligned
 // word path; kind 1 = the remaining columns (row ends; or every column when the level's rows are not
 // 4-byte aligned) on the byte path.  Splitting them keeps every warp on one path.
-__global__ void __launch_bounds__(BLUR_THREADS, 9) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
+#ifndef BLUR_MINB
+#define BLUR_MINB 9
+#endif
+__global__ void __launch_bounds__(BLUR_THREADS, BLUR_MINB) k_blur(OrbPlanDev P, const int4* __restrict__ tiles)
 {
     const int4 t = tiles[blockIdx.x];
     const int l = t.x, frame = blockIdx.y;
@@ -1139,12 +1255,13 @@ __global__ void __launch_bounds__(BLUR_THREADS, 9) k_blur(OrbPlanDev P, const in
         const int strip = task / nfast, wc = task - strip * nfast;
         if (strip * BLUR_R >= hgt) return;
         const int y0 = strip * BLUR_R;
-        blur_strip<true, false>(src, sp, dst, L.pitch, w, hgt, wc, y0);
+        blur_strip<1, false>(src, sp, dst, L.pitch, w, hgt, wc, y0);
     } else {
         const int nslow = nwc - nfast;
         const int strip = task / nslow, wc = nfast + task - strip * nslow;
         if (strip * BLUR_R >= hgt) return;
-        blur_strip<false, false>(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
+        if (BLUR_EDGE_WORDS && aligned && w >= 16 && wc >= 2) blur_strip_edge(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
+        else blur_strip_bytes(src, sp, dst, L.pitch, w, hgt, wc, strip * BLUR_R);
     }
 }
 
