@@ -695,6 +695,9 @@ int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream
 #define OCT_THREADS 256
 #endif
 #define OCT_NODE_BYTES 64     // per-node bytes in the node pool (see carve below)
+#ifndef OCT_AGG_NODES
+#define OCT_AGG_NODES 48      // sweeps over at most this many fresh nodes count children with warp-aggregated atomics
+#endif
 
 struct OctPools {
     uint32_t* kxy; uint16_t* knode; uint8_t* kq;                 // per key
@@ -755,6 +758,16 @@ __device__ int block_excl_scan(int* a, int n, int* s_part /* 33 ints of shared m
     return total;
 }
 
+// counter[idx] += 1 for every active lane, with ONE shared-memory atomic per distinct idx in the warp: while the tree has
+// few nodes thousands of keys hit a handful of counters and per-lane atomics on one address serialise 32-fold
+__device__ __forceinline__ void oct_count(int* counter, int idx, bool agg)
+{
+    if (agg) {
+        const unsigned peers = __match_any_sync(__activemask(), idx);
+        if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) atomicAdd(&counter[idx], __popc(peers));
+    } else atomicAdd(&counter[idx], 1);
+}
+
 // Runs the octree on keys o.kxy[0..nK); writes the survivors (packed) to out[0..count) in list order.
 __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N, int n_ini, float hx,
                           uint32_t* out, int out_cap, int* s_part, int* s_misc)
@@ -772,7 +785,7 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
         r = min(r, n_ini - 1);
         ORB_CHECK(r >= 0 && n_ini <= node_cap);
         o.knode[k] = (uint16_t)r;
-        atomicAdd(&o.cnt[0][r], 1);
+        oct_count(o.cnt[0], r, true);
     }
     __syncthreads();
     for (int i = tid; i < n_ini; i += OCT_THREADS) o.A[i] = o.cnt[0][i] > 0;
@@ -799,7 +812,7 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
                 const uint32_t p = o.kxy[k];
                 const int q = (ORB_PX(p) < mx ? 0 : 1) + (ORB_PY(p) < my ? 0 : 2);
                 o.kq[k] = (uint8_t)q;
-                atomicAdd(&o.cc[4 * nd + q], 1);
+                oct_count(o.cc, 4 * nd + q, M <= OCT_AGG_NODES);
             }
         }
         __syncthreads();
