@@ -816,62 +816,88 @@ __device__ int octree_run(OctPools& o, int nK, int node_cap, int W, int H, int N
             }
         }
         __syncthreads();
-        // ---- processing order of the expandable nodes
-        int nE;
-        if (!phaseB) {
-            for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (i < M && cnt[i] > 1);
-            nE = block_excl_scan(o.A, n, s_part);
+        int nE, nCommit, Mnew, newSize;
+        if (!phaseB && n <= 16384) {
+            // full sweep: every expandable node is split, in list order, so the rank of a node, the list growth before it and
+            // the number of committed nodes before ANY node come out of ONE scan over (expandable << 16 | nonempty children - 1)
+            // instead of three scans (4 barriers each)
             for (int i = tid; i < n; i += OCT_THREADS) {
                 const bool e = (i < M && cnt[i] > 1);
-                o.B[i] = e ? o.A[i] : -1;
-                if (e) o.ord[o.A[i]] = i;
+                const int g = e ? (o.cc[4 * i] > 0) + (o.cc[4 * i + 1] > 0) + (o.cc[4 * i + 2] > 0) + (o.cc[4 * i + 3] > 0) - 1 : 0;
+                o.A[i] = ((int)e << 16) | g;
             }
-        } else {
-            int local = 0;
+            const int total = block_excl_scan(o.A, n, s_part);
+            nE = total >> 16;
             for (int i = tid; i < n; i += OCT_THREADS) {
-                int rank = -1;
-                if (i < M && cnt[i] > 1) {
-                    const int ci = cnt[i];
-                    rank = 0;
-                    for (int j = 0; j < M; ++j) {
-                        const int cj = cnt[j];
-                        rank += (cj > 1) && (cj > ci || (cj == ci && j < i));
-                    }
-                    o.ord[rank] = i;
-                    ++local;
-                }
-                o.B[i] = rank;
+                const int v = o.A[i], rank = v >> 16;
+                const bool e = (i < M && cnt[i] > 1);
+                o.B[i] = e ? rank : -1;
+                if (e) { o.ord[rank] = i; o.X[rank] = v & 0xFFFF; }
+                o.A[i] = rank;                                // committed nodes before i
             }
-            if (local) atomicAdd(&s_misc[0], local);
+            if (tid == 0) { o.X[nE] = total & 0xFFFF; s_misc[2] = 0; }
             __syncthreads();
-            nE = s_misc[0];
-        }
-        __syncthreads();
-        // ---- X[r] = list growth caused by the parents processed before r (nonempty children - 1)
-        for (int r = tid; r < nE; r += OCT_THREADS) {
-            const int p = o.ord[r];
-            o.X[r] = (o.cc[4 * p] > 0) + (o.cc[4 * p + 1] > 0) + (o.cc[4 * p + 2] > 0) + (o.cc[4 * p + 3] > 0) - 1;
-        }
-        const int growth_all = block_excl_scan(o.X, nE, s_part);
-        if (tid == 0) o.X[nE] = growth_all;
-        __syncthreads();
-        // committed prefix: everything in a full sweep; in a budgeted pass, parents reached while size < N
-        int nCommit = nE;
-        if (phaseB) {
-            int local = 0;
-            for (int r = tid; r < nE; r += OCT_THREADS) local += (n + o.X[r] < N);
-            if (local) atomicAdd(&s_misc[1], local);
+            nCommit = nE;
+            Mnew = o.X[nCommit] + nCommit;
+            newSize = n - nCommit + Mnew;
+            if (newSize > node_cap || newSize > out_cap) return -1;  // cannot happen (see node_cap derivation)
+        } else {
+            // ---- processing order of the expandable nodes
+            if (!phaseB) {
+                for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (i < M && cnt[i] > 1);
+                nE = block_excl_scan(o.A, n, s_part);
+                for (int i = tid; i < n; i += OCT_THREADS) {
+                    const bool e = (i < M && cnt[i] > 1);
+                    o.B[i] = e ? o.A[i] : -1;
+                    if (e) o.ord[o.A[i]] = i;
+                }
+            } else {
+                int local = 0;
+                for (int i = tid; i < n; i += OCT_THREADS) {
+                    int rank = -1;
+                    if (i < M && cnt[i] > 1) {
+                        const int ci = cnt[i];
+                        rank = 0;
+                        for (int j = 0; j < M; ++j) {
+                            const int cj = cnt[j];
+                            rank += (cj > 1) && (cj > ci || (cj == ci && j < i));
+                        }
+                        o.ord[rank] = i;
+                        ++local;
+                    }
+                    o.B[i] = rank;
+                }
+                if (local) atomicAdd(&s_misc[0], local);
+                __syncthreads();
+                nE = s_misc[0];
+            }
             __syncthreads();
-            nCommit = s_misc[1];
+            // ---- X[r] = list growth caused by the parents processed before r (nonempty children - 1)
+            for (int r = tid; r < nE; r += OCT_THREADS) {
+                const int p = o.ord[r];
+                o.X[r] = (o.cc[4 * p] > 0) + (o.cc[4 * p + 1] > 0) + (o.cc[4 * p + 2] > 0) + (o.cc[4 * p + 3] > 0) - 1;
+            }
+            const int growth_all = block_excl_scan(o.X, nE, s_part);
+            if (tid == 0) o.X[nE] = growth_all;
+            __syncthreads();
+            // committed prefix: everything in a full sweep; in a budgeted pass, parents reached while size < N
+            nCommit = nE;
+            if (phaseB) {
+                int local = 0;
+                for (int r = tid; r < nE; r += OCT_THREADS) local += (n + o.X[r] < N);
+                if (local) atomicAdd(&s_misc[1], local);
+                __syncthreads();
+                nCommit = s_misc[1];
+            }
+            Mnew = o.X[nCommit] + nCommit;
+            newSize = n - nCommit + Mnew;
+            if (newSize > node_cap || newSize > out_cap) return -1;      // cannot happen (see node_cap derivation)
+            // ---- unsplit nodes keep their order behind the new ones
+            for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (o.B[i] >= 0 && o.B[i] < nCommit);
+            block_excl_scan(o.A, n, s_part);
+            if (tid == 0) s_misc[2] = 0;
+            __syncthreads();
         }
-        const int Mnew = o.X[nCommit] + nCommit;
-        const int newSize = n - nCommit + Mnew;
-        if (newSize > node_cap || newSize > out_cap) return -1;      // cannot happen (see node_cap derivation)
-        // ---- unsplit nodes keep their order behind the new ones
-        for (int i = tid; i < n; i += OCT_THREADS) o.A[i] = (o.B[i] >= 0 && o.B[i] < nCommit);
-        block_excl_scan(o.A, n, s_part);
-        if (tid == 0) s_misc[2] = 0;
-        __syncthreads();
         int to_expand = 0;
         for (int i = tid; i < n; i += OCT_THREADS) {
             const int r = o.B[i];
