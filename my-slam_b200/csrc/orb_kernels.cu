@@ -739,21 +739,17 @@ __device__ int block_excl_scan(int* a, int n, int* s_part /* 33 ints of shared m
     }
     if (lane == 31) s_part[warp] = inc;
     __syncthreads();
-    if (warp == 0) {
-        int w = lane < OCT_THREADS / 32 ? s_part[lane] : 0;
-        int winc = w;
+    // every warp scans the OCT_THREADS / 32 warp totals itself (one barrier less than a scan by warp 0 alone)
+    const int w = lane < OCT_THREADS / 32 ? s_part[lane] : 0;
+    int winc = w;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, winc, d);
-            if (lane >= d) winc += t;
-        }
-        if (lane < OCT_THREADS / 32) s_part[lane] = winc - w;
-        if (lane == OCT_THREADS / 32 - 1) s_part[32] = winc;
+    for (int d = 1; d < OCT_THREADS / 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane >= d) winc += t;
     }
-    __syncthreads();
-    int run = s_part[warp] + inc - sum;
+    const int total = __shfl_sync(0xffffffffu, winc, OCT_THREADS / 32 - 1);
+    int run = __shfl_sync(0xffffffffu, winc - w, warp) + inc - sum;
     for (int i = lo; i < hi; ++i) { const int v = a[i]; a[i] = run; run += v; }
-    const int total = s_part[32];
     __syncthreads();
     return total;
 }
