@@ -719,12 +719,12 @@ def run_ours(args, rank, world, local_rank):
 
     workloads = {}
     if secondary:
-        c3, R3 = run_c3_sequence(ctx, pkg, frames.pop("C3"), c3_total, args, max(3, min(args.steps, 5)), 3)
+        c3, R3 = run_c3_sequence(ctx, pkg, frames.pop("C3"), c3_total, args, max(3, min(args.steps, 10)), 3)
         workloads["C3"] = c3
         if world == 1:
             for k in ("C2", "C4"):
                 name, nfk = WORKLOADS[k]
-                st = max(3, min(args.steps, 5))
+                st = max(3, min(args.steps, 10))
                 Rk = measure_extraction(ctx, pkg, frames.pop(k), nfk, st, 3, args, serial_pass=True, copy_probe=False)
                 vk = Rk["n"] * st / (Rk["dev_ms"] * 1e-3)
                 rk = roofline_of(Rk, name, st, 1, vk, clocks, False)
