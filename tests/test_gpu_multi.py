@@ -90,3 +90,24 @@ def test_two_gpus_in_one_process(pkg):
     b0 = pkg.distinctive_descriptors(desc.reshape(-1, 32)[:300], g, device=0)
     b1 = pkg.distinctive_descriptors(desc.reshape(-1, 32)[:300], g, device=1)
     assert np.array_equal(b0, b1)
+
+
+def test_host_alloc_pinned_and_write_combined_inputs(pkg):
+    """orbgpu_host_alloc: frames in page-locked (and write-combined) memory of the library are used in place by the batch
+    entry points and give the same results as pageable numpy memory."""
+    synth = pkg.synth
+    frames = np.stack([synth.synth(640, 480, 0xA110C + i) for i in range(6)])
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    want = ex.extract_batch(frames)
+    for wc in (False, True):
+        hb = pkg.HostBuffer(frames.shape, np.uint8, write_combined=wc)
+        hb.array[:] = frames
+        got = ex.extract_batch(hb.array)
+        assert np.array_equal(got[2], want[2])
+        for i in range(len(frames)):
+            n = want[2][i]
+            assert got[0][i, :n].tobytes() == want[0][i, :n].tobytes() and np.array_equal(got[1][i, :n], want[1][i, :n])
+        hb.close()
+    L = pkg.lib()
+    p = C.c_void_p()
+    assert L.orbgpu_host_alloc(C.byref(p), 0, 0) == -1 and L.orbgpu_host_alloc(None, 16, 0) == -1
