@@ -96,7 +96,7 @@ struct OrbPlanDev {              // passed by value to every kernel
     int ncells;
     int sel_total;               // sum of sel_cap
     int kp_capacity;             // per-frame capacity of kps/desc
-    int fast_rows, fast_spw;     // k_fast_cells: rows of a warp's cell tile (max cell height); pitch of its score map
+    int fast_rows, fast_spw, fast_tp;   // k_fast_cells: rows of a warp's cell tile (max cell height); pitch of its score map and of the tile
     long long pyr_frame_bytes, blur_frame_bytes, slot_frame_words, scratch_frame_bytes;
     // level 0 source
     const uint8_t* src;          // frame 0, row 0
@@ -175,6 +175,7 @@ int orb_launch_cvt_gray(const uint8_t* src, long long src_frame_stride, int src_
 int orb_upload_constants(const int* umax16);
 int orb_fast_smem_bytes(int max_cw, int max_ch);
 // pitch of the per-warp FAST score map: interior width + the 1-px rim the NMS reads, rounded up to 4
+int orb_fast_tile_pitch(int max_cw);
 inline int orb_fast_spw(int max_cw) { return ((max_cw - 6 + 2) + 3) & ~3; }
 int orb_debug_atan2(const float* d_y, const float* d_x, int n, float* d_out, cudaStream_t st);
 int orb_debug_sincosf(const float* d_rad, int n, float* d_s, float* d_c, cudaStream_t st);

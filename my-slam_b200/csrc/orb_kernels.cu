@@ -396,13 +396,15 @@ int orb_launch_pyramid(const OrbPlanDev& P, int nframes, cudaStream_t st)
 // local maxima with score >= iniTh, or, if the cell has none, those with score >= minTh.  They
 // are written in row-major order (warp ballot + popc prefix) to the cell's slot area.
 // =================================================================================================
-#ifndef FAST_TP
-#define FAST_TP 64            // shared-memory row pitch of the cell tile and score map (max cell image width is 59); multiple of 16
-#endif
+// Shared-memory row pitch of the cell tile: 48 B when every cell image of the shape (plus up to 3 B of alignment shift) fits,
+// else 64 B.  With 48 B a CTA needs 37 KB, four of them fit the 164 KB carve-out step and the SM keeps 64 KB of L1 for
+// whatever runs beside FAST (k_describe takes 2.3 times as long with the 32 KB that the 196 KB step leaves).
+inline int orb_fast_pitch(int max_cw) { return max_cw + 3 <= 48 ? 48 : 64; }
 #ifndef FAST_WARPS
 #define FAST_WARPS 8
 #endif
 
+template <int FAST_TP>
 __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
 {
     // e_k = (v - p_k + 256) | (p_k - v + 256) << 16, built with one IMAD per circle pixel
@@ -464,6 +466,7 @@ __device__ __forceinline__ int fast_max8(const uint8_t* s, int p)
 //      score = V - 1 where V > th, into the cell-local score map; corners are also appended to a list;
 //   3. strict 8-neighbour maxima of the listed corners, ranked by position (row-major) by pairwise comparison
 //      and written in order.  Cells too dense for the lists fall back to an ordered scan of the score map.
+template <int FAST_TP>
 __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
 {
     const int tile_rows = P.fast_rows, spw = P.fast_spw;
@@ -536,7 +539,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
 #define FAST_DRAIN(active)                                                               \
         {                                                                                \
             int o_ = 0, V_ = 0;                                                          \
-            if (active) { o_ = q[(head + lane) & (FAST_QCAP - 1)]; V_ = fast_arc_value(tile + o_); } \
+            if (active) { o_ = q[(head + lane) & (FAST_QCAP - 1)]; V_ = fast_arc_value<FAST_TP>(tile + o_); } \
             const bool c_ = V_ > th;                                                     \
             const unsigned bc_ = __ballot_sync(0xffffffffu, c_);                         \
             if (c_) {                                                                    \
@@ -660,18 +663,26 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
     if (lane == 0) *cnt_out = (uint32_t)min(cnt, cell.cap);
 }
 
+int orb_fast_tile_pitch(int max_cw) { return orb_fast_pitch(max_cw); }
+
 int orb_fast_smem_bytes(int max_cw, int max_ch)
 {
-    if (max_cw + 3 > FAST_TP) return -1;                  // + up to 3 bytes of alignment shift
-    return FAST_WARPS * (FAST_TP * max_ch + ((orb_fast_spw(max_cw) * (max_ch - 4) + 15) & ~15));
+    if (max_cw + 3 > 64) return -1;                       // + up to 3 bytes of alignment shift
+    return FAST_WARPS * (orb_fast_pitch(max_cw) * max_ch + ((orb_fast_spw(max_cw) * (max_ch - 4) + 15) & ~15));
 }
 
 int orb_launch_fast(const OrbPlanDev& P, int nframes, int smem_bytes, cudaStream_t st)
 {
-    static OrbSmemOptIn optin;
-    if (optin.ensure(k_fast_cells, smem_bytes) != cudaSuccess) return -1;
     dim3 grid((P.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    k_fast_cells<<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P);
+    if (P.fast_tp == 48) {
+        static OrbSmemOptIn optin;
+        if (optin.ensure(k_fast_cells<48>, smem_bytes) != cudaSuccess) return -1;
+        k_fast_cells<48><<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P);
+    } else {
+        static OrbSmemOptIn optin;
+        if (optin.ensure(k_fast_cells<64>, smem_bytes) != cudaSuccess) return -1;
+        k_fast_cells<64><<<grid, FAST_WARPS * 32, smem_bytes, st>>>(P);
+    }
     return 1;
 }
 

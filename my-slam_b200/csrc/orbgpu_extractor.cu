@@ -299,7 +299,7 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
     np.kmax = sel_total;
     np.ntiles = (int)tiles.size();
     np.fast_smem = orb_fast_smem_bytes(max_cw, max_ch);
-    D.fast_rows = max_ch; D.fast_spw = orb_fast_spw(max_cw);
+    D.fast_rows = max_ch; D.fast_spw = orb_fast_spw(max_cw); D.fast_tp = orb_fast_tile_pitch(max_cw);
     if (np.fast_smem < 0 || np.fast_smem > 200 * 1024) return ORBGPU_ERR_UNSUPPORTED;
     np.key_smem_cap = std::min(std::max(8 * D.lv[0].nfeat, 1024), 6144);
     np.node_smem_cap = std::min(max_node_cap, 1024);
