@@ -60,6 +60,22 @@ def test_every_stage_matches_oracle(pkg, oracle, shape):
     assert kps.tobytes() == okps.tobytes() and np.array_equal(desc, odesc)
 
 
+@pytest.mark.parametrize("shape", [(641, 480), (642, 361), (643, 200), (752, 480), (1241, 376), (401, 333), (130, 131), (203, 149)])
+def test_blur_row_ends_and_pyramid_for_every_width_residue(pkg, oracle, shape):
+    """The row-end columns of the blur (word + PRMT path with REFLECT_101) and the resize tails: level widths of every residue
+    modulo 4 and 16 (the eight levels of each shape give 64 different widths), noise images so that every byte matters."""
+    w, h = shape
+    img = pkg.synth.noise(w, h, 77 + w)
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7); po = oracle.OraclePort(500, 1.2, 8, 20, 7)
+    ex(img); po.extract(img)
+    for l in range(8):
+        assert np.array_equal(ex.pyramid_level(l), po.level_pixels(l)), "pyramid level %d" % l
+        ob = po.level_pixels(l, blurred=True)
+        if ob is not None:
+            gb = ex.debug_blurred(l)
+            assert np.array_equal(gb, ob), ("blurred level %d" % l, np.argwhere(gb != ob)[:4])
+
+
 def test_angles_within_north_star_tolerance_and_bitwise(pkg, oracle):
     img = pkg.synth.synth(640, 480, 999)
     kps, _ = pkg.ORBextractor(1000, 1.2, 8, 20, 7)(img)
