@@ -1375,12 +1375,17 @@ __device__ __forceinline__ void orb_sincosf(float y, float* sinp, float* cosp)
     if (n & 1) { *sinp = fc; *cosp = fs; } else { *sinp = fs; *cosp = fc; }
 }
 
+#ifndef DESC_PER_WARP
+#define DESC_PER_WARP 2
+#endif
+#ifndef DESC_MINB
+#define DESC_MINB 6
+#endif
 struct OrbKeypointRec { float x, y, size, angle, response; int octave, class_id; };
 
-__global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
+__global__ void __launch_bounds__(256, DESC_MINB) k_describe(OrbPlanDev P)
 {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, frame = blockIdx.y;
-    const int g = blockIdx.x * 8 + warp;
     const int* selcnt = P.selcnt + (long long)frame * ORB_MAX_LEVELS;
     // per-level survivor counts, one per lane; exclusive prefix = output offset of each level
     const int cl = lane < P.nlevels ? selcnt[lane] : 0;
@@ -1390,12 +1395,13 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
         const int t = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += t;
     }
-    if (g == 0) {
+    if (blockIdx.x == 0 && warp == 0) {
         const bool bad = __any_sync(0xffffffffu, cl < 0);
         const int tot = __shfl_sync(0xffffffffu, incl, ORB_MAX_LEVELS - 1);
         if (lane == 0) P.nout[frame] = (bad || tot > P.kp_capacity) ? -1 : tot;
     }
-    if (g >= P.sel_total) return;
+    // DESC_PER_WARP slots per warp (stride = the grid): fewer, longer-lived CTAs, the prologue above paid once per warp
+    for (int g = blockIdx.x * 8 + warp; g < P.sel_total; g += gridDim.x * 8) {
     // level of slot g: the last level whose sel_off <= g
     const unsigned lv_mask = __ballot_sync(0xffffffffu, lane < P.nlevels && P.lv[min(lane, ORB_MAX_LEVELS - 1)].sel_off <= g &&
                                                         P.lv[min(lane, ORB_MAX_LEVELS - 1)].sel_cap > 0);
@@ -1404,9 +1410,9 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
     const int idx = g - L.sel_off;
     const int cnt_l = __shfl_sync(0xffffffffu, cl, l);
     const int before = __shfl_sync(0xffffffffu, incl - max(cl, 0), l);
-    if (idx >= cnt_l) return;
+    if (idx >= cnt_l) continue;
     const int o = before + idx;
-    if (o >= P.kp_capacity) return;
+    if (o >= P.kp_capacity) continue;
     ORB_CHECK(o >= 0 && l < P.nlevels && idx >= 0);
     const uint32_t key = P.sel[(long long)frame * P.sel_total + g];
     const int cx = ORB_PX(key) + ORB_BORDER, cy = ORB_PY(key) + ORB_BORDER;
@@ -1503,11 +1509,13 @@ __global__ void __launch_bounds__(256) k_describe(OrbPlanDev P)
         kp.size = L.kp_size; kp.angle = angle; kp.response = (float)ORB_PS(key); kp.octave = l; kp.class_id = -1;
         reinterpret_cast<OrbKeypointRec*>(P.kps)[(long long)frame * P.kp_capacity + o] = kp;
     }
+    }
 }
 
 int orb_launch_describe(const OrbPlanDev& P, int nframes, cudaStream_t st)
 {
-    k_describe<<<dim3(P.sel_total > 0 ? (P.sel_total + 7) / 8 : 1, nframes), 256, 0, st>>>(P);   // >= 1 block: block 0 writes nout
+    const int ctas = P.sel_total > 0 ? (P.sel_total + 8 * DESC_PER_WARP - 1) / (8 * DESC_PER_WARP) : 1;   // >= 1 block: block 0 writes nout
+    k_describe<<<dim3(ctas, nframes), 256, 0, st>>>(P);
     return 1;
 }
 
