@@ -437,6 +437,9 @@ __device__ __forceinline__ int fast_arc_value(const uint8_t* c)
     return max(lo, hi) - 256;
 }
 
+#ifndef FAST_STAGE8
+#define FAST_STAGE8 1         // stage cells with 8-byte cp.async where the cell is narrow enough for a shift of up to 7 columns
+#endif
 #ifndef FAST_P1_UNROLL
 #define FAST_P1_UNROLL 3      // row groups of the quick test per queue insertion (1 .. 3)
 #endif
@@ -494,7 +497,18 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
     const int pitch = orb_level_pitch(P, l);
     const uint8_t* __restrict__ img = orb_level_ptr(P, l, frame) + (long long)cell.ini_y * pitch + cell.ini_x;
     int sh = 0;
-    if (((pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img - cell.ini_x) & 3) == 0)) {
+    if (FAST_STAGE8 && ((pitch & 7) == 0) && ((reinterpret_cast<uintptr_t>(img - cell.ini_x) & 7) == 0) && cw + 7 <= FAST_TP) {
+        // 8-byte copies: eight lanes per row, four rows per step (half the LDGSTS of the 4-byte form below)
+        sh = cell.ini_x & 7;
+        const int nw = (cw + sh + 7) >> 3, c = lane & 7;
+        if (c < nw) {
+            const uint8_t* g = img - sh + (size_t)(lane >> 3) * pitch + 8 * c;
+            uint8_t* t = tile + (lane >> 3) * FAST_TP + 8 * c;
+            for (int r = lane >> 3; r < ch; r += 4, g += 4 * (size_t)pitch, t += 4 * FAST_TP) __pipeline_memcpy_async(t, g, 8);
+        }
+        __pipeline_commit();
+        __pipeline_wait_prior(0);
+    } else if (((pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(img - cell.ini_x) & 3) == 0)) {
         sh = cell.ini_x & 3;
         const int nw = (cw + sh + 3) >> 2, c = lane & 15;
         if (c < nw) {
@@ -515,7 +529,9 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
     const int w0 = cs >> 2, nwi = ((ce - 1) >> 2) - w0 + 1;    // words of a row that hold interior pixels
     const float inv_iw = 1.0f / (float)iw;
     // pass-1 lane layout, fixed for the cell: rpi = 32 / nwi rows per iteration, lane -> (row lrow, word w0 + lcol)
-    const int rpi = 32 / nwi, lrow = lane / nwi, lcol = lane - lrow * nwi;
+    // 32 / nwi and lane / nwi by one approximate float reciprocal (nwi <= 16; the 0.01 keeps exact quotients above the integer)
+    const float inv_nwi = __fdividef(1.0f, (float)nwi);
+    const int rpi = __float2int_rz(32.01f * inv_nwi), lrow = __float2int_rz(((float)lane + 0.01f) * inv_nwi), lcol = lane - lrow * nwi;
     const bool lrow_ok = lrow < rpi;
     const int loff = (3 + lrow) * FAST_TP + 4 * (w0 + lcol);   // tile offset of the lane's word in the first iteration
     unsigned lmask = 0x80808080u;                              // flag bits of the word's bytes that are interior pixels
