@@ -16,6 +16,14 @@ CMD = "python bench.py --frames 192 --steps 2 --warmup 3 --no-cpu --hamming-keyf
 STAGE = {"k_resize_level": "pyramid", "k_fast_cells": "fast_cells", "k_octree": "octree", "k_blur": "blur", "k_describe": "describe"}
 
 
+def kernel_base(name):
+    """'void k_fast_cells<48>(OrbPlanDev)' -> 'k_fast_cells'"""
+    n = name.split("(")[0].strip()
+    if n.startswith("void "):
+        n = n[5:]
+    return n.split("<")[0]
+
+
 def main(tag):
     go, pr = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
     # ---- launch list -> shares
@@ -26,7 +34,7 @@ def main(tag):
     for r in rows:
         if r.get("Metric Name") != "gpu__time_duration.sum":
             continue
-        k = r["Kernel Name"].split("(")[0]
+        k = kernel_base(r["Kernel Name"])
         v = float(r["Metric Value"].replace(",", ""))
         v = v / 1000.0 if r["Metric Unit"] in ("ns", "nsecond") else v
         tot[k] += v; cnt[k] += 1
@@ -54,7 +62,7 @@ def main(tag):
     frames = None
     dram = collections.defaultdict(float); inst = collections.defaultdict(float)
     for r in rr[2:]:
-        k = r[ix["Kernel Name"]].split("(")[0]
+        k = kernel_base(r[ix["Kernel Name"]])
         g = r[ix["Grid Size"]].strip("()").split(",")
         frames = int(g[1])
         dram[STAGE[k]] += val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum")
