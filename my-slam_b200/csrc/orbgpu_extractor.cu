@@ -303,6 +303,16 @@ static int build_plan(orbgpu_extractor* e, int w, int h)
     if (np.fast_smem < 0 || np.fast_smem > 200 * 1024) return ORBGPU_ERR_UNSUPPORTED;
     np.key_smem_cap = std::min(std::max(8 * D.lv[0].nfeat, 1024), 6144);
     np.node_smem_cap = std::min(max_node_cap, 1024);
+    {
+        // k_octree runs 4 CTAs per SM (64 registers x 256 threads): keep 4 x (shared memory + 1 KB) inside the 196 KB carve-out
+        // step, or every kernel co-resident with it loses its L1.  Node tables first (they are touched in
+        // every pass), keys with what is left; whatever does not fit lives in the global scratch area as before.
+        // B200, C2 (1241 x 376, 2000 features: 52 KB before): 89 k -> 123 k frames/s with 47 KB; 39 KB and 31 KB are no better.
+        const int budget = 47 * 1024 - 64;
+        if (64 * np.node_smem_cap > budget - 7 * 1024) np.node_smem_cap = 0;          // node tables too large: all in scratch
+        const int left = budget - 64 * np.node_smem_cap;
+        np.key_smem_cap = std::max(std::min(np.key_smem_cap, left / 7), 16);
+    }
     np.in_pitch = align_up((size_t)w, 16);
     np.in_frame_bytes = np.in_pitch * h;
     np.bytes_per_frame = np.in_frame_bytes + (size_t)D.pyr_frame_bytes + (size_t)D.blur_frame_bytes +
