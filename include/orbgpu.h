@@ -151,6 +151,14 @@ int orbgpu_stereo_match(orbgpu_extractor* left, orbgpu_extractor* right, float b
 int orbgpu_undistort_keypoints(orbgpu_extractor* e, const float* K4, const float* dist, int ndist,
                                orbgpu_keypoint* kps_un, int capacity, int* n_out);
 
+/* orbgpu_extract followed by orbgpu_undistort_keypoints behind ONE synchronisation: what the monocular Frame constructor
+ * does with each image (ExtractORB, then UndistortKeyPoints: src/Frame.cc:118-126, :404-435).  kps = mvKeys, kps_un =
+ * mvKeysUn (both `capacity` records), desc = mDescriptors.  The frame stays the handle's "most recent frame" for
+ * orbgpu_stereo_match / orbgpu_pyramid_level. */
+int orbgpu_extract_undistorted(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride, const float* K4,
+                               const float* dist, int ndist, orbgpu_keypoint* kps, orbgpu_keypoint* kps_un, uint8_t* desc,
+                               int capacity, int* n_out);
+
 /* cv::undistortPoints(xy, K, D, noArray(), K) on n arbitrary points (host buffers, x0 y0 x1 y1 ...): the four image
  * corners of Frame::ComputeImageBounds (src/Frame.cc:437-463), or any point list. */
 int orbgpu_undistort_points(int device, const float* xy, int n, const float* K4, const float* dist, int ndist, float* out_xy);
@@ -392,6 +400,56 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
  * and nmatches[p]. */
 int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation_args* args, int n_pairs, int32_t* matches12,
                                           int* nmatches);
+
+/* ---- resident keyframe store ------------------------------------------------------------------------------------
+ * The reference passes KeyFrame objects; a KeyFrame's mvKeysUn, mDescriptors, mvuRight, mFeatVec and level tables are
+ * written once (src/KeyFrame.cc:32-58, ComputeBoW :66-76) and read by every later search.  orbgpu_kf_add uploads them once;
+ * the searches below name keyframes by id and send only what changes between calls (map-point flags, poses, F12), so
+ * SearchByBoW / SearchForTriangulation stop re-staging 100-250 KB per call.  Ids are small integers, reused after
+ * orbgpu_kf_erase.  Add / erase / search may be called from different threads (Tracking, LocalMapping, LoopClosing);
+ * erasing a keyframe while a search that names it is running is the caller's race. */
+typedef struct orbgpu_kfstore orbgpu_kfstore;
+typedef struct orbgpu_kf_data {
+    int32_t n;                        /* pKF->N */
+    const orbgpu_keypoint* keys_un;   /* pKF->mvKeysUn */
+    const uint8_t* desc;              /* pKF->mDescriptors, n x 32 */
+    const float* u_right;             /* pKF->mvuRight; NULL = monocular (all -1) */
+    const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;   /* pKF->mFeatVec, flattened
+                                         as for orbgpu_search_by_bow (call after ComputeBoW) */
+    const float* scale_factors;       /* pKF->mvScaleFactors[nlevels] */
+    const float* level_sigma2;        /* pKF->mvLevelSigma2[nlevels] */
+    int32_t nlevels;
+    float fx, fy, cx, cy;             /* pKF->fx .. cy */
+} orbgpu_kf_data;
+int orbgpu_kfstore_create(orbgpu_kfstore** out, int device);
+void orbgpu_kfstore_destroy(orbgpu_kfstore* s);
+int orbgpu_kfstore_size(orbgpu_kfstore* s);                                  /* live keyframes */
+int orbgpu_kf_add(orbgpu_kfstore* s, const orbgpu_kf_data* kf, int32_t* id); /* returns when the keyframe is resident */
+int orbgpu_kf_erase(orbgpu_kfstore* s, int32_t id);                          /* KeyFrame::SetBadFlag / map reset */
+
+/* ORBmatcher::SearchByBoW with side 1 = stored keyframe id1 (valid1[n1] as in orbgpu_bow_side).  Side 2 is either a
+ * stored keyframe (id2 >= 0, valid2[n2], frame2 = NULL: the KeyFrame/KeyFrame overload, src/ORBmatcher.cc:522-655) or a
+ * Frame given by its arrays (id2 = -1, valid2 ignored, frame2 != NULL: the KeyFrame/Frame overload, :159-288).
+ * Outputs as orbgpu_search_by_bow. */
+int orbgpu_kf_search_by_bow(orbgpu_kfstore* s, int32_t id1, const uint8_t* valid1, int32_t id2, const uint8_t* valid2,
+                            const orbgpu_bow_side* frame2, float nnratio, int check_orientation, int strict_th_low,
+                            int32_t* match12, int32_t* match21, int* nmatches);
+
+/* ORBmatcher::SearchForTriangulation between two stored keyframes (src/ORBmatcher.cc:657-820); the camera and level
+ * tables of pKF2 come from the store.  Outputs as orbgpu_search_for_triangulation(_batch). */
+typedef struct orbgpu_kf_triangulation_job {
+    int32_t id1, id2;
+    const uint8_t* has_map_point1;   /* pKF1->GetMapPoint(idx) != NULL, n1 flags */
+    const uint8_t* has_map_point2;
+    float F12[9];                    /* row-major 3 x 3 (LocalMapping::ComputeF12 stays host) */
+    float Cw1[3];                    /* pKF1->GetCameraCenter() */
+    float T2w[16];                   /* pose of pKF2, 4 x 4 row-major */
+    int32_t only_stereo;             /* bOnlyStereo */
+    int32_t check_orientation;       /* mbCheckOrientation */
+} orbgpu_kf_triangulation_job;
+int orbgpu_kf_search_for_triangulation(orbgpu_kfstore* s, const orbgpu_kf_triangulation_job* job, int32_t* matches12, int* nmatches);
+int orbgpu_kf_search_for_triangulation_batch(orbgpu_kfstore* s, const orbgpu_kf_triangulation_job* jobs, int n_jobs,
+                                             int32_t* matches12, int* nmatches);
 
 /* Per-stage views of the most recent orbgpu_extract call, for parity tests of the intermediate
  * results (SURVEY.md section 4 test plan): blurred level (GaussianBlur, src/ORBextractor.cc:1088),

@@ -14,5 +14,5 @@ from .orbgpu import (KP_DTYPE, ORBextractor, ORBmatcher, OrbGpuError, device_cou
                      FuseArgs, fuse_args, fuse_search, fuse_search_batch,
                      RelocProjectionArgs, reloc_projection_args, search_by_projection_keyframe, distinctive_descriptors,
                      fuse_search_sim3, search_by_projection_sim3, search_by_sim3,
-                     ORBVocabulary, write_vocabulary_text, KeyFrameDatabase, update_normals_and_depths, Comm, all_pairs_multi, extract_batch_multi, HostBuffer)  # noqa: F401
+                     ORBVocabulary, write_vocabulary_text, KeyFrameDatabase, update_normals_and_depths, Comm, all_pairs_multi, extract_batch_multi, HostBuffer, KeyFrameStore, KfData, KfTriangulationJob)  # noqa: F401
 from . import shard, synth  # noqa: F401

@@ -23,7 +23,14 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <time.h>
 #include <string.h>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <new>
+#include <algorithm>
 #include <vector>
 #include "../../include/orbgpu.h"
 #include "orb_common.cuh"
@@ -567,6 +574,96 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_bow_resolve(const uint32_t*
     if (t == 0) *nmatches_out = s_nmatches;
 }
 
+// Both steps in one launch for ordinary vocabularies (a node holds a handful of features): one WARP per shared node.  The
+// node's features of side 2 (descriptor, index, "still free" flag) are staged in the warp's slice of shared memory once;
+// the node's queries are loaded 32 at a time, one per lane, and broadcast by shuffle; each query is one XOR / POPC pass
+// over the slice and two warp minima.  Nothing goes through global candidate lists or a single CTA.  Nodes with more than
+// BOW_NODE_CAP features of side 2 read them from memory with the "free" flags in the uploaded copy of valid2 (a feature
+// lies in one node, so only this warp touches its flag).  The host keeps the two-kernel path above for degenerate
+// vocabularies (one node holding everything), where the distance evaluations need the whole GPU.
+#define BOW_NODE_CAP 256
+__device__ __forceinline__ uint4 shfl4(const uint4& v, int src)
+{
+    return make_uint4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src),
+                      __shfl_sync(0xffffffffu, v.w, src));
+}
+__device__ __forceinline__ int hamming_rr(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(128) k_bow_fused(const BowQuery* __restrict__ Q, const int* __restrict__ gstart, int ngroups,
+                                                   const uint8_t* __restrict__ desc1, const uint8_t* __restrict__ desc2,
+                                                   const uint32_t* __restrict__ indices2, uint8_t* __restrict__ free2, float nnratio,
+                                                   int th_low_excl, int* __restrict__ accepted)
+{
+    __shared__ uint4 s_lo[4][BOW_NODE_CAP], s_hi[4][BOW_NODE_CAP];       // the two halves apart: conflict-free LDS.128
+    __shared__ uint32_t s_i2[4][BOW_NODE_CAP];
+    __shared__ uint8_t s_free[4][BOW_NODE_CAP];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int g = blockIdx.x * 4 + w;
+    if (g >= ngroups) return;
+    const int q0 = gstart[g], q1 = gstart[g + 1];
+    if (q0 >= q1) return;
+    const int start = Q[q0].start, len = Q[q0].len;            // every query of a node searches the same list
+    const bool staged = len <= BOW_NODE_CAP;
+    if (staged) {
+        for (int p = lane; p < len; p += 32) {
+            const uint32_t i2 = indices2[start + p];
+            s_i2[w][p] = i2;
+            s_lo[w][p] = __ldg(reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2);
+            s_hi[w][p] = __ldg(reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2 + 1);
+            s_free[w][p] = free2[i2];
+        }
+        __syncwarp();
+    }
+    for (int qb = q0; qb < q1; qb += 32) {
+        uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+        if (qb + lane < q1) {
+            const int idx1 = Q[qb + lane].idx1;
+            a0 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)idx1);
+            a1 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)idx1 + 1);
+        }
+        const int m = min(32, q1 - qb);
+        for (int j = 0; j < m; ++j) {
+            const uint4 b0 = shfl4(a0, j), b1 = shfl4(a1, j);
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
+            if (staged) {
+                for (int p = lane; p < len; p += 32) {
+                    if (!s_free[w][p]) continue;
+                    const unsigned key = ((unsigned)hamming_rr(b0, b1, s_lo[w][p], s_hi[w][p]) << 16) | (unsigned)p;
+                    if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+                }
+            } else {
+                for (int p = lane; p < len; p += 32) {
+                    const uint32_t i2 = indices2[start + p];
+                    if (!free2[i2]) continue;
+                    const unsigned key = ((unsigned)hamming_regs(b0, b1, reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2) << 16) | (unsigned)p;
+                    if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+                }
+            }
+            const unsigned m1 = __reduce_min_sync(0xffffffffu, k1);
+            const unsigned m2 = __reduce_min_sync(0xffffffffu, k1 == m1 ? k2 : k1);
+            const int bestDist1 = m1 == 0xFFFFFFFFu ? 256 : (int)(m1 >> 16);       // bestDist1 / bestDist2 start at 256 (:199-201)
+            const int bestDist2 = m2 == 0xFFFFFFFFu ? 256 : (int)(m2 >> 16);
+            int res = -1;
+            if (bestDist1 < th_low_excl && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) {
+                const int bp = (int)(m1 & 0xFFFFu);
+                if (staged) {
+                    res = (int)s_i2[w][bp];
+                    if (lane == 0) s_free[w][bp] = 0;
+                } else {
+                    res = (int)indices2[start + bp];
+                    if (lane == 0) free2[res] = 0;
+                }
+                __syncwarp();
+            }
+            if (lane == 0) accepted[qb + j] = res;
+        }
+    }
+}
+
 // ---- Frame::isInFrustum (src/Frame.cc:269-325) ---------------------------------------------------------------------
 // glibc 2.39 logf (sysdeps/ieee754/flt-32/e_logf.c, the routine the reference object calls from MapPoint::PredictScale)
 // followed operation by operation in double; tests/test_local_map.py sweeps float bit patterns against the host's logf
@@ -879,7 +976,7 @@ __global__ void __launch_bounds__(256) k_tri_match(const BowQuery* __restrict__ 
                                                    const float* __restrict__ keys2, const uint8_t* __restrict__ desc2,
                                                    const float* __restrict__ ur2, const uint8_t* __restrict__ has_mp2,
                                                    const uint32_t* __restrict__ indices2, const float* __restrict__ scale2,
-                                                   const float* __restrict__ sigma2, int* __restrict__ matches12)
+                                                   const float* __restrict__ sigma2, int* __restrict__ result)
 {
     const int lane = threadIdx.x & 31;
     const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -915,7 +1012,7 @@ __global__ void __launch_bounds__(256) k_tri_match(const BowQuery* __restrict__ 
         best = min(best, ((unsigned)d << 16) | (unsigned)(0xFFFF - p));
     }
     best = __reduce_min_sync(0xffffffffu, best);
-    if (lane == 0 && best != 0xFFFFFFFFu) matches12[B.idx1] = (int)indices2[B.start + (0xFFFF - (int)(best & 0xFFFFu))];
+    if (lane == 0) result[q] = best != 0xFFFFFFFFu ? (int)indices2[B.start + (0xFFFF - (int)(best & 0xFFFFu))] : -1;
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
@@ -1680,38 +1777,87 @@ int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projecti
     return ORBGPU_OK;
 }
 
+}  // extern "C"
+
+// cudaMemcpyAsync of a few KB takes the driver's inline path and costs the calling thread 5-8 us more than a 32 KB copy
+// (measured on B200: enqueue 15.2 -> 7.5 us for the 14 KB of a resident SearchByBoW); small uploads are padded up to this
+// size with whatever follows them in the pinned block (the device block is at least as large)
+static const size_t SEARCH_MIN_UPLOAD = (size_t)32 << 10;
+
+// ORBGPU_TRACE_SEARCH=1: host-clock phases of the BoW-gated searches on stderr (where a call's microseconds go)
+struct PhaseTrace {
+    bool on; const char* what; int k = 0; double t[8]; const char* name[8];
+    explicit PhaseTrace(const char* w) : what(w) { static const bool env = getenv("ORBGPU_TRACE_SEARCH") != nullptr; on = env; mark("entry"); }
+    void mark(const char* n)
+    {
+        if (!on || k >= 8) return;
+        timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+        t[k] = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; name[k++] = n;
+    }
+    ~PhaseTrace()
+    {
+        if (!on) return;
+        fprintf(stderr, "[orbgpu] %s:", what);
+        for (int i = 1; i < k; ++i) fprintf(stderr, " %s %.1f", name[i], t[i] - t[i - 1]);
+        fprintf(stderr, " | total %.1f us\n", t[k - 1] - t[0]);
+    }
+};
+
+// ---- the two BoW-gated searches on "side views" ---------------------------------------------------------------------
+// A side is what the engine reads of one KeyFrame / Frame.  The arrays that gate the search (FeatureVector, map-point
+// flags, angles) are read on the host; keypoints, descriptors, mvuRight and the FeatureVector's index list are either
+// host arrays uploaded with the call (orbgpu_search_by_bow, orbgpu_search_for_triangulation) or already resident in HBM
+// (orbgpu_kf_* below: a keyframe's mvKeysUn / mDescriptors / mvuRight / mFeatVec never change after construction).
+struct SideView {
+    int n = 0, n_nodes = 0;
+    const uint32_t* node_ids = nullptr; const int32_t* node_start = nullptr; const uint32_t* indices = nullptr;   // host
+    const uint8_t* flags = nullptr;                  // host: "valid" (SearchByBoW) / "has map point" (SearchForTriangulation)
+    const float* angle = nullptr; int angle_stride = 1;                            // host, floats
+    const float* u_right = nullptr;                  // host (only_stereo test of side 1)
+    const orbgpu_keypoint* h_keys = nullptr; const uint8_t* h_desc = nullptr;      // uploaded per call ...
+    const float* d_keys = nullptr; const uint8_t* d_desc = nullptr;                // ... or resident
+    const float* d_ur = nullptr; const uint32_t* d_indices = nullptr;
+    bool resident() const { return d_desc != nullptr; }
+    int nidx() const { return n_nodes > 0 ? node_start[n_nodes] : 0; }
+};
+
+static int check_feature_vector(int n, const uint32_t* node_ids, const int32_t* node_start, const uint32_t* indices, int n_nodes)
+{
+    if (n_nodes < 0 || (n_nodes > 0 && (!node_ids || !node_start || !indices))) return ORBGPU_ERR_ARG;
+    if (n_nodes > 0 && node_start[0] != 0) return ORBGPU_ERR_ARG;
+    for (int i = 0; i < n_nodes; ++i) {
+        if (node_start[i] > node_start[i + 1] || (i && node_ids[i - 1] >= node_ids[i])) return ORBGPU_ERR_ARG;
+        for (int c = node_start[i]; c < node_start[i + 1]; ++c) if (indices[c] >= (uint32_t)n) return ORBGPU_ERR_ARG;
+    }
+    return ORBGPU_OK;
+}
+
 // One SearchForTriangulation problem, split so that several (LocalMapping::CreateNewMapPoints runs one per neighbouring
 // keyframe, src/LocalMapping.cc:239-270) can be enqueued back to back on the workspace stream and waited for once.
+struct TriProblem {
+    SideView s1, s2;
+    const float* F12 = nullptr; const float* Cw1 = nullptr; const float* T2w = nullptr;
+    float fx = 0, fy = 0, cx = 0, cy = 0;            // pKF2
+    const float* h_scale2 = nullptr; const float* h_sigma2 = nullptr;              // uploaded per call ...
+    const float* d_scale2 = nullptr; const float* d_sigma2 = nullptr;              // ... or resident
+    int only_stereo = 0, check_orientation = 0;
+};
 struct TriJob {
-    const orbgpu_triangulation_args* a = nullptr;
+    TriProblem P;
     std::vector<BowQuery> hq;
     TriCam C;
     int nq = 0;
-    size_t base = 0, bytes = 0, in_bytes = 0;        // region inside the workspace
-    size_t o_k1, o_d1, o_u1, o_k2, o_d2, o_u2, o_m2, o_i2, o_q, o_sc, o_sg, o_m12;
+    size_t base = 0, bytes = 0, in_bytes = 0, up_bytes = 0;   // region inside the workspace; what is uploaded
+    size_t o_k1 = 0, o_d1 = 0, o_u1 = 0, o_k2 = 0, o_d2 = 0, o_u2 = 0, o_m2 = 0, o_i2 = 0, o_q = 0, o_sc = 0, o_sg = 0, o_m12 = 0;
 };
 
-// validation, the merge walk over the two FeatureVectors, the epipole; lays the job's region out
+// the merge walk over the two FeatureVectors, the epipole; lays the job's region out (inputs already validated)
 static int tri_prepare(TriJob& J, int32_t* matches12, int* nmatches)
 {
-    const orbgpu_triangulation_args* a = J.a;
+    const TriProblem& P = J.P;
+    const SideView &s1 = P.s1, &s2 = P.s2;
     std::vector<BowQuery>& hq = J.hq;
-    if (!a || !matches12 || !nmatches || a->nlevels < 1 || !a->scale_factors2 || !a->level_sigma2) return ORBGPU_ERR_ARG;
-    const orbgpu_triangulation_side* S[2] = {&a->kf1, &a->kf2};
-    for (int k = 0; k < 2; ++k) {
-        const orbgpu_triangulation_side* s = S[k];
-        if (s->n < 0 || s->n_nodes < 0 || (s->n > 0 && (!s->keys_un || !s->desc || !s->has_map_point || !s->u_right)) ||
-            (s->n_nodes > 0 && (!s->node_ids || !s->node_start || !s->indices))) return ORBGPU_ERR_ARG;
-        if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
-        for (int i = 0; i < s->n_nodes; ++i) {
-            if (s->node_start[i] > s->node_start[i + 1] || (i && s->node_ids[i - 1] >= s->node_ids[i])) return ORBGPU_ERR_ARG;
-            for (int c = s->node_start[i]; c < s->node_start[i + 1]; ++c) if (s->indices[c] >= (uint32_t)s->n) return ORBGPU_ERR_ARG;
-        }
-    }
-    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
     const int n1 = s1.n, n2 = s2.n;
-    for (int i = 0; i < n2; ++i)
-        if (s2.keys_un[i].octave < 0 || s2.keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
     *nmatches = 0;
     for (int i = 0; i < n1; ++i) matches12[i] = -1;
     // the merge walk over the two FeatureVectors (:689-696, :782-789) -> queries in visiting order
@@ -1721,8 +1867,8 @@ static int tri_prepare(TriJob& J, int32_t* matches12, int* nmatches)
             const int st = s2.node_start[it2], len = s2.node_start[it2 + 1] - st;
             for (int c = s1.node_start[it1]; c < s1.node_start[it1 + 1]; ++c) {
                 const int idx1 = (int)s1.indices[c];
-                if (s1.has_map_point[idx1] || len == 0) continue;                      // :703-706
-                if (a->only_stereo && !(s1.u_right[idx1] >= 0)) continue;              // :708-712
+                if (s1.flags[idx1] || len == 0) continue;                              // :703-706
+                if (P.only_stereo && !(s1.u_right[idx1] >= 0)) continue;               // :708-712
                 BowQuery q; q.idx1 = idx1; q.start = st; q.len = len;
                 hq.push_back(q);
             }
@@ -1735,66 +1881,79 @@ static int tri_prepare(TriJob& J, int32_t* matches12, int* nmatches)
     }
     J.nq = (int)hq.size();
     if (J.nq == 0) return ORBGPU_OK;
-    const int nidx2 = s2.node_start[s2.n_nodes];
+    const int nidx2 = s2.nidx();
     if (nidx2 > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;
     TriCam& C = J.C;
     // epipole of pKF1's centre in pKF2 (:664-670): C2 = R2w*Cw + t2w is cv::gemm's 3x3 float case
     float C2[3];
     for (int r = 0; r < 3; ++r) {
-        volatile float t = a->T2w[4 * r] * a->Cw1[0];          // (volatile: keep the host compiler from contracting)
-        t = t + a->T2w[4 * r + 1] * a->Cw1[1];
-        t = t + a->T2w[4 * r + 2] * a->Cw1[2];
-        C2[r] = (float)((double)t * 1.0 + (double)a->T2w[4 * r + 3] * 1.0);
+        volatile float t = P.T2w[4 * r] * P.Cw1[0];            // (volatile: keep the host compiler from contracting)
+        t = t + P.T2w[4 * r + 1] * P.Cw1[1];
+        t = t + P.T2w[4 * r + 2] * P.Cw1[2];
+        C2[r] = (float)((double)t * 1.0 + (double)P.T2w[4 * r + 3] * 1.0);
     }
     {
         const float invz = 1.0f / C2[2];
-        volatile float px = a->fx * C2[0]; px = px * invz; px = px + a->cx;
-        volatile float py = a->fy * C2[1]; py = py * invz; py = py + a->cy;
+        volatile float px = P.fx * C2[0]; px = px * invz; px = px + P.cx;
+        volatile float py = P.fy * C2[1]; py = py * invz; py = py + P.cy;
         C.ex = px; C.ey = py;
     }
-    for (int i = 0; i < 9; ++i) C.F[i] = a->F12[i];
-    C.only_stereo = a->only_stereo ? 1 : 0;
+    for (int i = 0; i < 9; ++i) C.F[i] = P.F12[i];
+    C.only_stereo = P.only_stereo ? 1 : 0;
 
     Layout L;
-    J.o_k1 = L.add(sizeof(orbgpu_keypoint) * (size_t)n1); J.o_d1 = L.add(32 * (size_t)n1); J.o_u1 = L.add(4 * (size_t)n1);
-    J.o_k2 = L.add(sizeof(orbgpu_keypoint) * (size_t)n2); J.o_d2 = L.add(32 * (size_t)n2); J.o_u2 = L.add(4 * (size_t)n2);
-    J.o_m2 = L.add((size_t)n2); J.o_i2 = L.add(4 * (size_t)nidx2); J.o_q = L.add(sizeof(BowQuery) * (size_t)J.nq);
-    J.o_sc = L.add(4 * (size_t)a->nlevels); J.o_sg = L.add(4 * (size_t)a->nlevels);
+    if (!s1.resident()) { J.o_k1 = L.add(sizeof(orbgpu_keypoint) * (size_t)n1); J.o_d1 = L.add(32 * (size_t)n1); J.o_u1 = L.add(4 * (size_t)n1); }
+    if (!s2.resident()) {
+        J.o_k2 = L.add(sizeof(orbgpu_keypoint) * (size_t)n2); J.o_d2 = L.add(32 * (size_t)n2); J.o_u2 = L.add(4 * (size_t)n2);
+        J.o_i2 = L.add(4 * (size_t)nidx2);
+    }
+    if (!P.d_scale2) { J.o_sc = L.add(4 * (size_t)ORBGPU_MAX_LEVELS); J.o_sg = L.add(4 * (size_t)ORBGPU_MAX_LEVELS); }
+    J.o_m2 = L.add((size_t)n2); J.o_q = L.add(sizeof(BowQuery) * (size_t)J.nq);
     J.in_bytes = L.off;
-    J.o_m12 = L.add(4 * (size_t)n1);
-    J.bytes = L.off;
+    J.o_m12 = L.add(4 * (size_t)J.nq);                         // one result per query
+    J.up_bytes = std::max(J.in_bytes, SEARCH_MIN_UPLOAD);      // (the padding reads on into the job's own region)
+    J.bytes = std::max(L.off, J.up_bytes);
     return ORBGPU_OK;
 }
 
 // stage the inputs in the pinned mirror, upload, launch, download: all asynchronous on the workspace stream
-static int tri_enqueue(Workspace& W, const TriJob& J)
+static int tri_enqueue(Workspace& W, const TriJob& J, int nlevels)
 {
     if (J.nq == 0) return ORBGPU_OK;
-    const orbgpu_triangulation_args* a = J.a;
-    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
-    const int n1 = s1.n, n2 = s2.n, nidx2 = s2.node_start[s2.n_nodes];
+    const TriProblem& P = J.P;
+    const SideView &s1 = P.s1, &s2 = P.s2;
+    const int n1 = s1.n, n2 = s2.n;
     uint8_t* h = W.h + J.base;
     uint8_t* d = W.d + J.base;
-    memcpy(h + J.o_k1, s1.keys_un, sizeof(orbgpu_keypoint) * (size_t)n1);
-    memcpy(h + J.o_d1, s1.desc, 32 * (size_t)n1);
-    memcpy(h + J.o_u1, s1.u_right, 4 * (size_t)n1);
-    memcpy(h + J.o_k2, s2.keys_un, sizeof(orbgpu_keypoint) * (size_t)n2);
-    memcpy(h + J.o_d2, s2.desc, 32 * (size_t)n2);
-    memcpy(h + J.o_u2, s2.u_right, 4 * (size_t)n2);
-    memcpy(h + J.o_m2, s2.has_map_point, (size_t)n2);
-    memcpy(h + J.o_i2, s2.indices, 4 * (size_t)nidx2);
+    const float *k1 = s1.d_keys, *u1 = s1.d_ur, *k2 = s2.d_keys, *u2 = s2.d_ur, *sc = P.d_scale2, *sg = P.d_sigma2;
+    const uint8_t *d1 = s1.d_desc, *d2 = s2.d_desc;
+    const uint32_t* i2 = s2.d_indices;
+    if (!s1.resident()) {
+        memcpy(h + J.o_k1, s1.h_keys, sizeof(orbgpu_keypoint) * (size_t)n1);
+        memcpy(h + J.o_d1, s1.h_desc, 32 * (size_t)n1);
+        memcpy(h + J.o_u1, s1.u_right, 4 * (size_t)n1);
+        k1 = reinterpret_cast<const float*>(d + J.o_k1); d1 = d + J.o_d1; u1 = reinterpret_cast<const float*>(d + J.o_u1);
+    }
+    if (!s2.resident()) {
+        memcpy(h + J.o_k2, s2.h_keys, sizeof(orbgpu_keypoint) * (size_t)n2);
+        memcpy(h + J.o_d2, s2.h_desc, 32 * (size_t)n2);
+        memcpy(h + J.o_u2, s2.u_right, 4 * (size_t)n2);
+        memcpy(h + J.o_i2, s2.indices, 4 * (size_t)s2.nidx());
+        k2 = reinterpret_cast<const float*>(d + J.o_k2); d2 = d + J.o_d2; u2 = reinterpret_cast<const float*>(d + J.o_u2);
+        i2 = reinterpret_cast<const uint32_t*>(d + J.o_i2);
+    }
+    if (!P.d_scale2) {
+        memcpy(h + J.o_sc, P.h_scale2, 4 * (size_t)nlevels);
+        memcpy(h + J.o_sg, P.h_sigma2, 4 * (size_t)nlevels);
+        sc = reinterpret_cast<const float*>(d + J.o_sc); sg = reinterpret_cast<const float*>(d + J.o_sg);
+    }
+    memcpy(h + J.o_m2, s2.flags, (size_t)n2);
     memcpy(h + J.o_q, J.hq.data(), sizeof(BowQuery) * (size_t)J.nq);
-    memcpy(h + J.o_sc, a->scale_factors2, 4 * (size_t)a->nlevels);
-    memcpy(h + J.o_sg, a->level_sigma2, 4 * (size_t)a->nlevels);
-    CUS(cudaMemcpyAsync(d, h, J.in_bytes, cudaMemcpyHostToDevice, W.st));
-    CUS(cudaMemsetAsync(d + J.o_m12, 0xFF, 4 * (size_t)n1, W.st));
-    k_tri_match<<<(J.nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(d + J.o_q), J.nq, J.C, reinterpret_cast<const float*>(d + J.o_k1),
-                                                  d + J.o_d1, reinterpret_cast<const float*>(d + J.o_u1), reinterpret_cast<const float*>(d + J.o_k2),
-                                                  d + J.o_d2, reinterpret_cast<const float*>(d + J.o_u2), d + J.o_m2,
-                                                  reinterpret_cast<const uint32_t*>(d + J.o_i2), reinterpret_cast<const float*>(d + J.o_sc),
-                                                  reinterpret_cast<const float*>(d + J.o_sg), reinterpret_cast<int*>(d + J.o_m12));
+    CUS(cudaMemcpyAsync(d, h, J.up_bytes, cudaMemcpyHostToDevice, W.st));
+    k_tri_match<<<(J.nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(d + J.o_q), J.nq, J.C, k1, d1, u1, k2, d2, u2, d + J.o_m2,
+                                                  i2, sc, sg, reinterpret_cast<int*>(d + J.o_m12));
     CUS(cudaGetLastError());
-    CUS(cudaMemcpyAsync(h + J.o_m12, d + J.o_m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, W.st));
+    CUS(cudaMemcpyAsync(h + J.o_m12, d + J.o_m12, 4 * (size_t)J.nq, cudaMemcpyDeviceToHost, W.st));
     return ORBGPU_OK;
 }
 
@@ -1802,19 +1961,21 @@ static int tri_enqueue(Workspace& W, const TriJob& J)
 static void tri_finish(const Workspace& W, const TriJob& J, int32_t* matches12, int* nmatches)
 {
     if (J.nq == 0) return;
-    const orbgpu_triangulation_args* a = J.a;
-    const orbgpu_triangulation_side &s1 = a->kf1, &s2 = a->kf2;
+    const SideView &s1 = J.P.s1, &s2 = J.P.s2;
     const std::vector<BowQuery>& hq = J.hq;
     const int nq = J.nq;
-    memcpy(matches12, W.h + J.base + J.o_m12, 4 * (size_t)s1.n);
+    const int* res = reinterpret_cast<const int*>(W.h + J.base + J.o_m12);       // matches12 is all -1 since tri_prepare
     int nm = 0;
-    for (int q = 0; q < nq; ++q) nm += matches12[hq[q].idx1] >= 0;
-    if (a->check_orientation) {                                // :760-776, :794-813
+    for (int q = 0; q < nq; ++q) { matches12[hq[q].idx1] = res[q]; nm += res[q] >= 0; }
+    if (J.P.check_orientation) {                               // :760-776, :794-813
         int bin_of[30] = {0};
         std::vector<int> bin((size_t)nq, -1);
         for (int q = 0; q < nq; ++q) {
             const int i1 = hq[q].idx1;
-            if (matches12[i1] >= 0) { bin[q] = rot_bin(s1.keys_un[i1].angle, s2.keys_un[matches12[i1]].angle); bin_of[bin[q]]++; }
+            if (matches12[i1] >= 0) {
+                bin[q] = rot_bin(s1.angle[(size_t)i1 * s1.angle_stride], s2.angle[(size_t)matches12[i1] * s2.angle_stride]);
+                bin_of[bin[q]]++;
+            }
         }
         int ind1 = -1, ind2 = -1, ind3 = -1;
         three_maxima(bin_of, 30, ind1, ind2, ind3);
@@ -1827,6 +1988,49 @@ static void tri_finish(const Workspace& W, const TriJob& J, int32_t* matches12, 
     *nmatches = nm;
 }
 
+// all jobs enqueued back to back on the calling thread's workspace stream, one wait; job p writes s1.n entries of
+// matches12 right after those of job p - 1
+static int tri_run(int device, std::vector<TriJob>& jobs, const int* nlevels, int32_t* matches12, int* nmatches)
+{
+    const size_t n_jobs = jobs.size();
+    PhaseTrace tr("search_for_triangulation");
+    std::vector<size_t> out_off(n_jobs);
+    size_t total = 0, out = 0;
+    for (size_t p = 0; p < n_jobs; ++p) {
+        TriJob& J = jobs[p];
+        out_off[p] = out;
+        const int rc = tri_prepare(J, matches12 + out, nmatches + p);
+        if (rc != ORBGPU_OK) return rc;
+        out += (size_t)J.P.s1.n;
+        J.base = total;
+        total += J.bytes;
+    }
+    if (total == 0) return ORBGPU_OK;
+    tr.mark("walk");
+    Workspace& W = g_ws;
+    int rc = W.reserve(device, total, total);
+    if (rc != ORBGPU_OK) return rc;
+    for (size_t p = 0; p < n_jobs; ++p) {
+        rc = tri_enqueue(W, jobs[p], nlevels[p]);
+        if (rc != ORBGPU_OK) { cudaStreamSynchronize(W.st); return rc; }
+    }
+    tr.mark("stage+enqueue");
+    CUS(cudaStreamSynchronize(W.st));
+    tr.mark("wait");
+    for (size_t p = 0; p < n_jobs; ++p) tri_finish(W, jobs[p], matches12 + out_off[p], nmatches + p);
+    tr.mark("finish");
+    return ORBGPU_OK;
+}
+
+static void view_of(SideView& v, const orbgpu_triangulation_side& s)
+{
+    v.n = s.n; v.n_nodes = s.n_nodes; v.node_ids = s.node_ids; v.node_start = s.node_start; v.indices = s.indices;
+    v.flags = s.has_map_point; v.u_right = s.u_right; v.h_keys = s.keys_un; v.h_desc = s.desc;
+    v.angle = s.keys_un ? &s.keys_un[0].angle : nullptr; v.angle_stride = (int)(sizeof(orbgpu_keypoint) / sizeof(float));
+}
+
+extern "C" {
+
 int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation_args* args, int n_pairs, int32_t* matches12,
                                           int* nmatches)
 {
@@ -1834,29 +2038,28 @@ int orbgpu_search_for_triangulation_batch(int device, const orbgpu_triangulation
     if (n_pairs == 0) return ORBGPU_OK;
     if (!args || !matches12 || !nmatches) return ORBGPU_ERR_ARG;
     std::vector<TriJob> jobs((size_t)n_pairs);
-    std::vector<size_t> out_off((size_t)n_pairs);
-    size_t total = 0, out = 0;
+    std::vector<int> nlevels((size_t)n_pairs);
     for (int p = 0; p < n_pairs; ++p) {
-        TriJob& J = jobs[(size_t)p];
-        J.a = args + p;
-        out_off[(size_t)p] = out;
-        const int rc = tri_prepare(J, matches12 + out, nmatches + p);
-        if (rc != ORBGPU_OK) return rc;
-        out += (size_t)(args[p].kf1.n > 0 ? args[p].kf1.n : 0);
-        J.base = total;
-        total += J.bytes;
+        const orbgpu_triangulation_args* a = args + p;
+        if (a->nlevels < 1 || a->nlevels > ORBGPU_MAX_LEVELS || !a->scale_factors2 || !a->level_sigma2) return ORBGPU_ERR_ARG;
+        const orbgpu_triangulation_side* S[2] = {&a->kf1, &a->kf2};
+        for (int k = 0; k < 2; ++k) {
+            const orbgpu_triangulation_side* s = S[k];
+            if (s->n < 0 || (s->n > 0 && (!s->keys_un || !s->desc || !s->has_map_point || !s->u_right))) return ORBGPU_ERR_ARG;
+            if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+            const int rc = check_feature_vector(s->n, s->node_ids, s->node_start, s->indices, s->n_nodes);
+            if (rc != ORBGPU_OK) return rc;
+        }
+        for (int i = 0; i < a->kf2.n; ++i)
+            if (a->kf2.keys_un[i].octave < 0 || a->kf2.keys_un[i].octave >= a->nlevels) return ORBGPU_ERR_ARG;
+        TriProblem& P = jobs[(size_t)p].P;
+        view_of(P.s1, a->kf1); view_of(P.s2, a->kf2);
+        P.F12 = a->F12; P.Cw1 = a->Cw1; P.T2w = a->T2w; P.fx = a->fx; P.fy = a->fy; P.cx = a->cx; P.cy = a->cy;
+        P.h_scale2 = a->scale_factors2; P.h_sigma2 = a->level_sigma2;
+        P.only_stereo = a->only_stereo; P.check_orientation = a->check_orientation;
+        nlevels[(size_t)p] = a->nlevels;
     }
-    if (total == 0) return ORBGPU_OK;
-    Workspace& W = g_ws;
-    int rc = W.reserve(device, total, total);
-    if (rc != ORBGPU_OK) return rc;
-    for (int p = 0; p < n_pairs; ++p) {
-        rc = tri_enqueue(W, jobs[(size_t)p]);
-        if (rc != ORBGPU_OK) { cudaStreamSynchronize(W.st); return rc; }
-    }
-    CUS(cudaStreamSynchronize(W.st));
-    for (int p = 0; p < n_pairs; ++p) tri_finish(W, jobs[(size_t)p], matches12 + out_off[(size_t)p], nmatches + p);
-    return ORBGPU_OK;
+    return tri_run(device, jobs, nlevels.data(), matches12, nmatches);
 }
 
 int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args* a, int32_t* matches12, int* nmatches)
@@ -1864,22 +2067,14 @@ int orbgpu_search_for_triangulation(int device, const orbgpu_triangulation_args*
     return orbgpu_search_for_triangulation_batch(device, a, a ? 1 : 0, matches12, nmatches);
 }
 
-int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow_side* s2, float nnratio, int check_orientation,
-                         int strict_th_low, int32_t* match12, int32_t* match21, int* nmatches)
+}  // extern "C"
+
+// SearchByBoW on two side views (inputs already validated)
+static int bow_run(int device, const SideView& s1, const SideView& s2, float nnratio, int check_orientation, int strict_th_low,
+                   int32_t* match12, int32_t* match21, int* nmatches)
 {
-    if (!s1 || !s2 || !match12 || !match21 || !nmatches) return ORBGPU_ERR_ARG;
-    const orbgpu_bow_side* S[2] = {s1, s2};
-    for (int k = 0; k < 2; ++k) {
-        const orbgpu_bow_side* s = S[k];
-        if (s->n < 0 || s->n_nodes < 0 || (s->n > 0 && (!s->desc || !s->valid || !s->angle)) ||
-            (s->n_nodes > 0 && (!s->node_ids || !s->node_start || !s->indices))) return ORBGPU_ERR_ARG;
-        if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
-        for (int i = 0; i < s->n_nodes; ++i) {
-            if (s->node_start[i] > s->node_start[i + 1] || (i && s->node_ids[i - 1] >= s->node_ids[i])) return ORBGPU_ERR_ARG;
-            for (int a = s->node_start[i]; a < s->node_start[i + 1]; ++a) if (s->indices[a] >= (uint32_t)s->n) return ORBGPU_ERR_ARG;
-        }
-    }
-    const int n1 = s1->n, n2 = s2->n;
+    const int n1 = s1.n, n2 = s2.n;
+    PhaseTrace tr("search_by_bow");
     *nmatches = 0;
     for (int i = 0; i < n1; ++i) match12[i] = -1;
     for (int i = 0; i < n2; ++i) match21[i] = -1;
@@ -1887,65 +2082,103 @@ int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow
     std::vector<BowQuery> hq;
     std::vector<int> gstart;                                   // query ranges per shared node
     int cap = 0, it1 = 0, it2 = 0;
-    while (it1 != s1->n_nodes && it2 != s2->n_nodes) {
-        if (s1->node_ids[it1] == s2->node_ids[it2]) {
-            const int st = s2->node_start[it2], len = s2->node_start[it2 + 1] - st;
+    while (it1 != s1.n_nodes && it2 != s2.n_nodes) {
+        if (s1.node_ids[it1] == s2.node_ids[it2]) {
+            const int st = s2.node_start[it2], len = s2.node_start[it2 + 1] - st;
             gstart.push_back((int)hq.size());
-            for (int a = s1->node_start[it1]; a < s1->node_start[it1 + 1]; ++a) {
-                const int idx1 = (int)s1->indices[a];
-                if (!s1->valid[idx1] || len == 0) continue;
+            for (int a = s1.node_start[it1]; a < s1.node_start[it1 + 1]; ++a) {
+                const int idx1 = (int)s1.indices[a];
+                if (!s1.flags[idx1] || len == 0) continue;
                 BowQuery q; q.idx1 = idx1; q.start = st; q.len = len;
                 hq.push_back(q);
                 cap = len > cap ? len : cap;
             }
             ++it1; ++it2;
-        } else if (s1->node_ids[it1] < s2->node_ids[it2]) {
-            while (it1 != s1->n_nodes && s1->node_ids[it1] < s2->node_ids[it2]) ++it1;
+        } else if (s1.node_ids[it1] < s2.node_ids[it2]) {
+            while (it1 != s1.n_nodes && s1.node_ids[it1] < s2.node_ids[it2]) ++it1;
         } else {
-            while (it2 != s2->n_nodes && s2->node_ids[it2] < s1->node_ids[it1]) ++it2;
+            while (it2 != s2.n_nodes && s2.node_ids[it2] < s1.node_ids[it1]) ++it2;
         }
     }
     const int nq = (int)hq.size(), ngroups = (int)gstart.size();
     gstart.push_back(nq);
     if (nq == 0) return ORBGPU_OK;
+    // one warp per node (k_bow_fused) unless some node is so large that its distance evaluations want the whole GPU
+    long long heaviest = 0;
+    for (int g = 0; g < ngroups; ++g)
+        if (gstart[(size_t)g + 1] > gstart[(size_t)g])
+            heaviest = std::max(heaviest, (long long)(gstart[(size_t)g + 1] - gstart[(size_t)g]) * ((hq[(size_t)gstart[(size_t)g]].len + 31) / 32));
+    const bool fused = heaviest <= 256;
     if (nq > GRID_MAX_KEYS || (size_t)nq * (size_t)cap > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
-    const int nidx2 = s2->node_start[s2->n_nodes];
+    const int nidx2 = s2.nidx();
     Layout L;
-    const size_t o_d1 = L.add(32 * (size_t)n1), o_d2 = L.add(32 * (size_t)n2), o_v2 = L.add((size_t)n2);
-    const size_t o_i2 = L.add(4 * (size_t)nidx2), o_q = L.add(sizeof(BowQuery) * (size_t)nq), o_g = L.add(4 * (size_t)(ngroups + 1));
+    size_t o_d1 = 0, o_d2 = 0, o_i2 = 0;
+    if (!s1.resident()) o_d1 = L.add(32 * (size_t)n1);
+    if (!s2.resident()) { o_d2 = L.add(32 * (size_t)n2); o_i2 = L.add(4 * (size_t)nidx2); }
+    const size_t o_v2 = L.add((size_t)n2);
+    const size_t o_q = L.add(sizeof(BowQuery) * (size_t)nq), o_g = L.add(4 * (size_t)(ngroups + 1));
     const size_t in_bytes = L.off;
     const size_t o_acc = L.add(4 * (size_t)nq), o_nm = L.add(4);
     const size_t io_bytes = L.off;
-    const size_t o_cn = L.add(4 * (size_t)nq), o_cand = L.add(4 * (size_t)nq * cap);
+    size_t o_cn = 0, o_cand = 0;
+    if (!fused) { o_cn = L.add(4 * (size_t)nq); o_cand = L.add(4 * (size_t)nq * cap); }
+    tr.mark("walk");
     Workspace& W = g_ws;
-    int rc = W.reserve(device, L.off, io_bytes);
+    int rc = W.reserve(device, std::max(L.off, SEARCH_MIN_UPLOAD), std::max(io_bytes, SEARCH_MIN_UPLOAD));
     if (rc != ORBGPU_OK) return rc;
-    memcpy(W.h + o_d1, s1->desc, 32 * (size_t)n1);
-    memcpy(W.h + o_d2, s2->desc, 32 * (size_t)n2);
-    memcpy(W.h + o_v2, s2->valid, (size_t)n2);
-    memcpy(W.h + o_i2, s2->indices, 4 * (size_t)nidx2);
+    tr.mark("reserve");
+    const uint8_t *d1 = s1.d_desc, *d2 = s2.d_desc;
+    const uint32_t* i2 = s2.d_indices;
+    if (!s1.resident()) { memcpy(W.h + o_d1, s1.h_desc, 32 * (size_t)n1); d1 = W.d + o_d1; }
+    if (!s2.resident()) {
+        memcpy(W.h + o_d2, s2.h_desc, 32 * (size_t)n2);
+        memcpy(W.h + o_i2, s2.indices, 4 * (size_t)nidx2);
+        d2 = W.d + o_d2; i2 = reinterpret_cast<const uint32_t*>(W.d + o_i2);
+    }
+    memcpy(W.h + o_v2, s2.flags, (size_t)n2);
     memcpy(W.h + o_q, hq.data(), sizeof(BowQuery) * (size_t)nq);
     memcpy(W.h + o_g, gstart.data(), 4 * (size_t)(ngroups + 1));
-    CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
-    uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
-    int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
-    k_bow_candidates<<<(nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), nq, W.d + o_d1, W.d + o_d2,
-                                                     reinterpret_cast<const uint32_t*>(W.d + o_i2), d_cand, cap, d_cn);
-    k_bow_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, cap, nq, n2, W.d + o_v2, reinterpret_cast<const int*>(W.d + o_g),
-                                                              ngroups, nnratio, strict_th_low ? 50 : 51,
-                                                              reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
+    tr.mark("stage");
+    CUS(cudaMemcpyAsync(W.d, W.h, std::max(in_bytes, SEARCH_MIN_UPLOAD), cudaMemcpyHostToDevice, W.st));
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (tr.on) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventRecord(ev0, W.st); }
+    if (fused) {
+        k_bow_fused<<<(ngroups + 3) / 4, 128, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), reinterpret_cast<const int*>(W.d + o_g),
+                                                          ngroups, d1, d2, i2, W.d + o_v2, nnratio, strict_th_low ? 50 : 51,
+                                                          reinterpret_cast<int*>(W.d + o_acc));
+    } else {
+        uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
+        int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+        k_bow_candidates<<<(nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), nq, d1, d2, i2, d_cand, cap, d_cn);
+        k_bow_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, cap, nq, n2, W.d + o_v2, reinterpret_cast<const int*>(W.d + o_g),
+                                                                  ngroups, nnratio, strict_th_low ? 50 : 51,
+                                                                  reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
+    }
     CUS(cudaGetLastError());
+    if (tr.on) cudaEventRecord(ev1, W.st);
     CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    tr.mark("enqueue");
     CUS(cudaStreamSynchronize(W.st));
+    tr.mark("wait");
+    if (tr.on) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        fprintf(stderr, "[orbgpu]   kernels %.1f us; nq %d groups %d longest list %d heaviest node %lld %s\n", ms * 1e3, nq, ngroups, cap,
+                heaviest, fused ? "one warp per node" : "two kernels");
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    }
     const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
-    int nm = *reinterpret_cast<const int*>(W.h + o_nm);
+    int nm = 0;
     for (int q = 0; q < nq; ++q)
-        if (acc[q] >= 0) { match12[hq[q].idx1] = acc[q]; match21[acc[q]] = hq[q].idx1; }
+        if (acc[q] >= 0) { match12[hq[q].idx1] = acc[q]; match21[acc[q]] = hq[q].idx1; nm++; }
     if (check_orientation) {                                   // :268-285, :628-652
         int bin_of[30] = {0};
         std::vector<int> bin((size_t)nq, -1);
         for (int q = 0; q < nq; ++q)
-            if (acc[q] >= 0) { bin[q] = rot_bin(s1->angle[hq[q].idx1], s2->angle[acc[q]]); bin_of[bin[q]]++; }
+            if (acc[q] >= 0) {
+                bin[q] = rot_bin(s1.angle[(size_t)hq[q].idx1 * s1.angle_stride], s2.angle[(size_t)acc[q] * s2.angle_stride]);
+                bin_of[bin[q]]++;
+            }
         int ind1 = -1, ind2 = -1, ind3 = -1;
         three_maxima(bin_of, 30, ind1, ind2, ind3);
         for (int q = 0; q < nq; ++q) {
@@ -1955,7 +2188,256 @@ int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow
         }
     }
     *nmatches = nm;
+    tr.mark("finish");
     return ORBGPU_OK;
+}
+
+static int view_of_bow(SideView& v, const orbgpu_bow_side* s)
+{
+    if (s->n < 0 || (s->n > 0 && (!s->desc || !s->valid || !s->angle))) return ORBGPU_ERR_ARG;
+    if (s->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+    const int rc = check_feature_vector(s->n, s->node_ids, s->node_start, s->indices, s->n_nodes);
+    if (rc != ORBGPU_OK) return rc;
+    v.n = s->n; v.n_nodes = s->n_nodes; v.node_ids = s->node_ids; v.node_start = s->node_start; v.indices = s->indices;
+    v.flags = s->valid; v.angle = s->angle; v.angle_stride = 1; v.h_desc = s->desc;
+    return ORBGPU_OK;
+}
+
+extern "C" int orbgpu_search_by_bow(int device, const orbgpu_bow_side* s1, const orbgpu_bow_side* s2, float nnratio, int check_orientation,
+                                    int strict_th_low, int32_t* match12, int32_t* match21, int* nmatches)
+{
+    if (!s1 || !s2 || !match12 || !match21 || !nmatches) return ORBGPU_ERR_ARG;
+    SideView v1, v2;
+    int rc;
+    if ((rc = view_of_bow(v1, s1)) != ORBGPU_OK || (rc = view_of_bow(v2, s2)) != ORBGPU_OK) return rc;
+    return bow_run(device, v1, v2, nnratio, check_orientation, strict_th_low, match12, match21, nmatches);
+}
+
+// ---- resident keyframe store ---------------------------------------------------------------------------------------
+// The reference hands every search the KeyFrame object itself; behind a C ABI that means re-staging 100-250 KB of
+// keypoints / descriptors per call although a keyframe's mvKeysUn, mDescriptors, mvuRight and mFeatVec are written once in
+// the constructor / ComputeBoW (src/KeyFrame.cc:32-58, :66-76) and never again.  The store keeps them in HBM; searches
+// name keyframes by id and send only what changes between calls (map-point flags, poses).  What the host-side gating
+// needs (FeatureVector, angles, mvuRight) is kept in host copies beside the device block.
+namespace {
+
+struct KfSlot {
+    bool live = false;
+    int n = 0, n_nodes = 0, nlevels = 0;
+    float fx = 0, fy = 0, cx = 0, cy = 0;
+    uint8_t* d = nullptr; size_t bytes = 0;          // keys | desc | u_right | indices | scale factors | level sigma2
+    size_t o_keys = 0, o_desc = 0, o_ur = 0, o_idx = 0, o_sc = 0, o_sg = 0;
+    std::vector<uint32_t> node_ids, indices;
+    std::vector<int32_t> node_start;
+    std::vector<float> angle, u_right;
+};
+
+}  // namespace
+
+struct orbgpu_kfstore {
+    int device = 0;
+    std::mutex mu;                                   // slot table and block pool; searches copy what they need under it
+    std::vector<std::shared_ptr<KfSlot> > slots;   // searches hold a reference while they run
+    std::vector<int> free_ids;
+    // device memory comes in 32 MB slabs cut into blocks of 16 KB multiples; erased blocks are reused by size class
+    // (no cudaMalloc / cudaFree on the add / erase path once a slab has room)
+    static const size_t SLAB = (size_t)32 << 20, QUANTUM = (size_t)16 << 10;
+    std::vector<uint8_t*> slabs;
+    size_t slab_used = SLAB;
+    std::map<size_t, std::vector<uint8_t*> > pool;
+    int live = 0;
+
+    uint8_t* block(size_t bytes)
+    {
+        std::vector<uint8_t*>& fl = pool[bytes];
+        if (!fl.empty()) { uint8_t* p = fl.back(); fl.pop_back(); return p; }
+        if (bytes > SLAB) return nullptr;
+        if (slab_used + bytes > SLAB) {
+            uint8_t* s = nullptr;
+            if (cudaMalloc(&s, SLAB) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+            slabs.push_back(s); slab_used = 0;
+        }
+        uint8_t* p = slabs.back() + slab_used;
+        slab_used += bytes;
+        return p;
+    }
+};
+
+static void side_of_slot(SideView& v, const KfSlot& s, const uint8_t* flags)
+{
+    v.n = s.n; v.n_nodes = s.n_nodes; v.node_ids = s.node_ids.data(); v.node_start = s.node_start.data(); v.indices = s.indices.data();
+    v.flags = flags; v.angle = s.angle.data(); v.angle_stride = 1; v.u_right = s.u_right.data();
+    v.d_keys = reinterpret_cast<const float*>(s.d + s.o_keys); v.d_desc = s.d + s.o_desc;
+    v.d_ur = reinterpret_cast<const float*>(s.d + s.o_ur); v.d_indices = reinterpret_cast<const uint32_t*>(s.d + s.o_idx);
+}
+
+static std::shared_ptr<KfSlot> slot_of(orbgpu_kfstore* st, int id)
+{
+    if (id < 0 || id >= (int)st->slots.size()) return nullptr;
+    return st->slots[(size_t)id];
+}
+
+extern "C" {
+
+int orbgpu_kfstore_create(orbgpu_kfstore** out, int device)
+{
+    if (!out) return ORBGPU_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    CUS(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return ORBGPU_ERR_ARG;
+    orbgpu_kfstore* st = new (std::nothrow) orbgpu_kfstore();
+    if (!st) return ORBGPU_ERR_NOMEM;
+    st->device = device;
+    st->slots.reserve(1024);
+    *out = st;
+    return ORBGPU_OK;
+}
+
+void orbgpu_kfstore_destroy(orbgpu_kfstore* st)
+{
+    if (!st) return;
+    cudaSetDevice(st->device);
+    for (uint8_t* s : st->slabs) cudaFree(s);
+    delete st;
+}
+
+int orbgpu_kfstore_size(orbgpu_kfstore* st)
+{
+    if (!st) return ORBGPU_ERR_ARG;
+    std::lock_guard<std::mutex> g(st->mu);
+    return st->live;
+}
+
+int orbgpu_kf_add(orbgpu_kfstore* st, const orbgpu_kf_data* k, int32_t* id)
+{
+    if (!st || !k || !id) return ORBGPU_ERR_ARG;
+    *id = -1;
+    if (k->n < 0 || (k->n > 0 && (!k->keys_un || !k->desc))) return ORBGPU_ERR_ARG;
+    if (k->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
+    if (k->nlevels < 1 || k->nlevels > ORBGPU_MAX_LEVELS || !k->scale_factors || !k->level_sigma2) return ORBGPU_ERR_ARG;
+    int rc = check_feature_vector(k->n, k->node_ids, k->node_start, k->indices, k->n_nodes);
+    if (rc != ORBGPU_OK) return rc;
+    for (int i = 0; i < k->n; ++i)
+        if (k->keys_un[i].octave < 0 || k->keys_un[i].octave >= k->nlevels) return ORBGPU_ERR_ARG;
+    const int n = k->n, nidx = k->n_nodes > 0 ? k->node_start[k->n_nodes] : 0;
+    if (nidx > 0xFFFF) return ORBGPU_ERR_UNSUPPORTED;
+    std::shared_ptr<KfSlot> sp = std::make_shared<KfSlot>();
+    KfSlot& s = *sp;
+    Layout L;
+    s.o_keys = L.add(sizeof(orbgpu_keypoint) * (size_t)n); s.o_desc = L.add(32 * (size_t)n); s.o_ur = L.add(4 * (size_t)n);
+    s.o_idx = L.add(4 * (size_t)nidx); s.o_sc = L.add(4 * (size_t)ORBGPU_MAX_LEVELS); s.o_sg = L.add(4 * (size_t)ORBGPU_MAX_LEVELS);
+    s.bytes = (L.off + orbgpu_kfstore::QUANTUM - 1) / orbgpu_kfstore::QUANTUM * orbgpu_kfstore::QUANTUM;
+    s.n = n; s.n_nodes = k->n_nodes; s.nlevels = k->nlevels; s.fx = k->fx; s.fy = k->fy; s.cx = k->cx; s.cy = k->cy;
+    s.node_ids.assign(k->node_ids, k->node_ids + k->n_nodes);
+    s.node_start.assign(k->node_start, k->node_start + (k->n_nodes > 0 ? k->n_nodes + 1 : 0));
+    if (k->n_nodes == 0) s.node_start.assign(1, 0);
+    s.indices.assign(k->indices, k->indices + nidx);
+    s.angle.resize((size_t)n); s.u_right.resize((size_t)n);
+    for (int i = 0; i < n; ++i) { s.angle[(size_t)i] = k->keys_un[i].angle; s.u_right[(size_t)i] = k->u_right ? k->u_right[i] : -1.f; }
+    // stage the block in the calling thread's pinned mirror, one upload, wait: the block is complete when the id is handed out
+    Workspace& W = g_ws;
+    if ((rc = W.reserve(st->device, 0, L.off)) != ORBGPU_OK) return rc;
+    memset(W.h, 0, L.off);
+    memcpy(W.h + s.o_keys, k->keys_un, sizeof(orbgpu_keypoint) * (size_t)n);
+    memcpy(W.h + s.o_desc, k->desc, 32 * (size_t)n);
+    memcpy(W.h + s.o_ur, s.u_right.data(), 4 * (size_t)n);
+    memcpy(W.h + s.o_idx, s.indices.data(), 4 * (size_t)nidx);
+    memcpy(W.h + s.o_sc, k->scale_factors, 4 * (size_t)k->nlevels);
+    memcpy(W.h + s.o_sg, k->level_sigma2, 4 * (size_t)k->nlevels);
+    {
+        std::lock_guard<std::mutex> g(st->mu);
+        s.d = st->block(s.bytes);
+    }
+    if (!s.d) return ORBGPU_ERR_NOMEM;
+    cudaError_t ce = cudaMemcpyAsync(s.d, W.h, L.off, cudaMemcpyHostToDevice, W.st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(W.st);
+    std::lock_guard<std::mutex> g(st->mu);
+    if (ce != cudaSuccess) {
+        st->pool[s.bytes].push_back(s.d);
+        orbgpu_internal_set_error(cudaGetErrorString(ce));
+        return ORBGPU_ERR_CUDA;
+    }
+    s.live = true;
+    int slot;
+    if (!st->free_ids.empty()) { slot = st->free_ids.back(); st->free_ids.pop_back(); st->slots[(size_t)slot] = sp; }
+    else { slot = (int)st->slots.size(); st->slots.push_back(sp); }
+    st->live++;
+    *id = slot;
+    return ORBGPU_OK;
+}
+
+int orbgpu_kf_erase(orbgpu_kfstore* st, int32_t id)
+{
+    if (!st) return ORBGPU_ERR_ARG;
+    std::lock_guard<std::mutex> g(st->mu);
+    std::shared_ptr<KfSlot> s = slot_of(st, id);
+    if (!s) return ORBGPU_ERR_STATE;
+    st->pool[s->bytes].push_back(s->d);
+    st->slots[(size_t)id].reset();
+    st->free_ids.push_back(id);
+    st->live--;
+    return ORBGPU_OK;
+}
+
+// A search takes a reference to the slots it names under the lock, so orbgpu_kf_add / orbgpu_kf_erase from other threads
+// cannot move or free their host tables under it.  Erasing a keyframe while a search that names it is in flight is still
+// the caller's race (its device block may be handed to the next keyframe), as deleting the KeyFrame would be in the reference.
+int orbgpu_kf_search_by_bow(orbgpu_kfstore* st, int32_t id1, const uint8_t* valid1, int32_t id2, const uint8_t* valid2,
+                            const orbgpu_bow_side* frame2, float nnratio, int check_orientation, int strict_th_low,
+                            int32_t* match12, int32_t* match21, int* nmatches)
+{
+    if (!st || !valid1 || !match12 || !match21 || !nmatches) return ORBGPU_ERR_ARG;
+    if ((id2 >= 0) == (frame2 != nullptr)) return ORBGPU_ERR_ARG;          // side 2: a stored keyframe OR a Frame's arrays
+    if (id2 >= 0 && !valid2) return ORBGPU_ERR_ARG;
+    std::shared_ptr<KfSlot> k1, k2;
+    {
+        std::lock_guard<std::mutex> g(st->mu);
+        k1 = slot_of(st, id1);
+        if (id2 >= 0) k2 = slot_of(st, id2);
+        if (!k1 || (id2 >= 0 && !k2)) return ORBGPU_ERR_STATE;
+    }
+    SideView v1, v2;
+    side_of_slot(v1, *k1, valid1);
+    if (id2 >= 0) side_of_slot(v2, *k2, valid2);
+    else { const int rc = view_of_bow(v2, frame2); if (rc != ORBGPU_OK) return rc; }
+    return bow_run(st->device, v1, v2, nnratio, check_orientation, strict_th_low, match12, match21, nmatches);
+}
+
+int orbgpu_kf_search_for_triangulation_batch(orbgpu_kfstore* st, const orbgpu_kf_triangulation_job* jobs_in, int n_jobs,
+                                             int32_t* matches12, int* nmatches)
+{
+    if (!st || n_jobs < 0) return ORBGPU_ERR_ARG;
+    if (n_jobs == 0) return ORBGPU_OK;
+    if (!jobs_in || !matches12 || !nmatches) return ORBGPU_ERR_ARG;
+    std::vector<TriJob> jobs((size_t)n_jobs);
+    std::vector<std::shared_ptr<KfSlot> > k((size_t)2 * n_jobs);
+    std::vector<int> nlevels((size_t)n_jobs);
+    {
+        std::lock_guard<std::mutex> g(st->mu);
+        for (int p = 0; p < n_jobs; ++p) {
+            const orbgpu_kf_triangulation_job& j = jobs_in[p];
+            if (!j.has_map_point1 || !j.has_map_point2) return ORBGPU_ERR_ARG;
+            k[(size_t)2 * p] = slot_of(st, j.id1); k[(size_t)2 * p + 1] = slot_of(st, j.id2);
+            if (!k[(size_t)2 * p] || !k[(size_t)2 * p + 1]) return ORBGPU_ERR_STATE;
+        }
+    }
+    for (int p = 0; p < n_jobs; ++p) {
+        const orbgpu_kf_triangulation_job& j = jobs_in[p];
+        const KfSlot &k1 = *k[(size_t)2 * p], &k2 = *k[(size_t)2 * p + 1];
+        TriProblem& P = jobs[(size_t)p].P;
+        side_of_slot(P.s1, k1, j.has_map_point1); side_of_slot(P.s2, k2, j.has_map_point2);
+        P.F12 = j.F12; P.Cw1 = j.Cw1; P.T2w = j.T2w; P.fx = k2.fx; P.fy = k2.fy; P.cx = k2.cx; P.cy = k2.cy;
+        P.d_scale2 = reinterpret_cast<const float*>(k2.d + k2.o_sc); P.d_sigma2 = reinterpret_cast<const float*>(k2.d + k2.o_sg);
+        P.only_stereo = j.only_stereo; P.check_orientation = j.check_orientation;
+        nlevels[(size_t)p] = k2.nlevels;
+    }
+    return tri_run(st->device, jobs, nlevels.data(), matches12, nmatches);
+}
+
+int orbgpu_kf_search_for_triangulation(orbgpu_kfstore* st, const orbgpu_kf_triangulation_job* job, int32_t* matches12, int* nmatches)
+{
+    return orbgpu_kf_search_for_triangulation_batch(st, job, job ? 1 : 0, matches12, nmatches);
 }
 
 }  // extern "C"

@@ -574,9 +574,12 @@ static int download_results(orbgpu_extractor* e, StreamCtx& c, int m, orbgpu_key
 }
 
 // one chunk, host buffers: upload -> kernels -> download, all asynchronous on the context's stream
+struct UndistortReq { const float* K4; const float* dist; int ndist; };   // orbgpu_extract_undistorted: one more kernel + copy per frame
+extern "C" { static int reserve_aux(orbgpu_extractor* e, size_t bytes); }   // defined with the frame-side entry points below
+
 static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, int m, int w, int h, size_t row_stride,
                         size_t frame_stride, bool pinned_in, orbgpu_keypoint* kps, uint8_t* desc, int* n_out,
-                        int capacity, bool pinned_out)
+                        int capacity, bool pinned_out, const UndistortReq* und = nullptr)
 {
     int rc;
     if ((rc = ctx_finish(e, c)) != ORBGPU_OK) return rc;
@@ -586,7 +589,12 @@ static int submit_chunk(orbgpu_extractor* e, StreamCtx& c, const uint8_t* src, i
     if ((rc = upload_frames(e, c, src, m, w, h, row_stride, frame_stride, pinned_in)) != ORBGPU_OK) return rc;
     if (prof) CU(cudaEventRecord(c.ev[EV_UP], c.st));
     if ((rc = enqueue_kernels_graph(e, c, m)) != ORBGPU_OK) return rc;
+    if (und) {                                                  // mvKeysUn beside mvKeys, behind the same synchronisation (m == 1)
+        orb_launch_undistort_keypoints(und->K4, und->dist, und->ndist, c.d_kps, e->d_aux, c.d_nout, e->plan.kmax, c.st);
+        e->launches += 1;
+    }
     if ((rc = download_results(e, c, m, kps, desc, n_out, capacity, pinned_out)) != ORBGPU_OK) return rc;
+    if (und) CU(cudaMemcpyAsync(e->h_aux, e->d_aux, sizeof(orbgpu_keypoint) * (size_t)e->plan.kmax, cudaMemcpyDeviceToHost, c.st));
     if (prof) CU(cudaEventRecord(c.ev[EV_DOWN], c.st));
     CU(cudaEventRecord(c.done, c.st));
     c.busy = true; c.profiled = prof; c.job_frames = m;
@@ -1173,6 +1181,34 @@ int orbgpu_undistort_keypoints(orbgpu_extractor* e, const float* K4, const float
     if (capacity < n) return ORBGPU_ERR_CAPACITY;
     memcpy(kps_un, e->h_aux, sizeof(orbgpu_keypoint) * (size_t)n);
     return ORBGPU_OK;
+}
+
+// orbgpu_extract + orbgpu_undistort_keypoints behind one synchronisation: the Frame constructor's ExtractORB + UndistortKeyPoints
+// (src/Frame.cc:118-126, :404-435) cost one device round trip instead of two.
+int orbgpu_extract_undistorted(orbgpu_extractor* e, const uint8_t* img, int w, int h, size_t stride, const float* K4, const float* dist,
+                               int ndist, orbgpu_keypoint* kps, orbgpu_keypoint* kps_un, uint8_t* desc, int capacity, int* n_out)
+{
+    if (!e || !n_out || !K4 || !dist || ndist < 4 || ndist > 12) return ORBGPU_ERR_ARG;
+    if (!img || w == 0 || h == 0) { *n_out = -1; return ORBGPU_OK; }       // empty image: outputs untouched, as orbgpu_extract
+    if (!kps || !kps_un || !desc || w < 1 || h < 1 || stride < (size_t)w * e->in_channels) return ORBGPU_ERR_ARG;
+    int rc;
+    if ((rc = use_device(e)) != ORBGPU_OK) return rc;
+    if (e->async_open) return ORBGPU_ERR_STATE;
+    for (int s = 0; s < NSTREAM; ++s) if (e->ctx[s].ticket_live) return ORBGPU_ERR_STATE;
+    if ((rc = build_plan(e, w, h)) != ORBGPU_OK) return rc;
+    if (capacity < e->plan.kmax) return ORBGPU_ERR_CAPACITY;
+    for (int s = 0; s < NSTREAM; ++s) if ((rc = ctx_finish(e, e->ctx[s])) != ORBGPU_OK) return rc;   // d_aux may be regrown below
+    if ((rc = reserve_aux(e, sizeof(orbgpu_keypoint) * (size_t)e->plan.kmax + 16)) != ORBGPU_OK) return rc;
+    if ((rc = batch_begin(e)) != ORBGPU_OK) return rc;
+    e->next_ctx = 0;
+    const UndistortReq und = {K4, dist, ndist};
+    StreamCtx& c = e->ctx[0];
+    rc = submit_chunk(e, c, img, 1, w, h, stride, stride * (size_t)h, is_pinned(img), kps, desc, n_out, capacity,
+                      is_pinned(kps) && is_pinned(desc) && is_pinned(n_out), &und);
+    const int result = finish_all(e, rc);
+    e->last_ctx = result == ORBGPU_OK ? 0 : -1;
+    if (result == ORBGPU_OK && *n_out > 0) memcpy(kps_un, e->h_aux, sizeof(orbgpu_keypoint) * (size_t)*n_out);
+    return result;
 }
 
 int orbgpu_undistort_points(int device, const float* xy, int n, const float* K4, const float* dist, int ndist, float* out_xy)

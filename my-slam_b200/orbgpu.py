@@ -232,6 +232,113 @@ def search_by_bow(side1, side2, nnratio=0.7, check_orientation=True, strict_th_l
     return nm.value, m12[:side1.n].copy(), m21[:side2.n].copy()
 
 
+class KfData(C.Structure):
+    """orbgpu_kf_data (include/orbgpu.h): what a KeyFrame never changes after construction / ComputeBoW."""
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("desc", C.c_void_p), ("u_right", C.c_void_p),
+                ("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p), ("n_nodes", C.c_int32),
+                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p), ("nlevels", C.c_int32),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float)]
+
+
+class KfTriangulationJob(C.Structure):
+    """orbgpu_kf_triangulation_job (include/orbgpu.h)."""
+    _fields_ = [("id1", C.c_int32), ("id2", C.c_int32), ("has_map_point1", C.c_void_p), ("has_map_point2", C.c_void_p),
+                ("F12", C.c_float * 9), ("Cw1", C.c_float * 3), ("T2w", C.c_float * 16), ("only_stereo", C.c_int32),
+                ("check_orientation", C.c_int32)]
+
+
+class KeyFrameStore:
+    """Keyframes resident in HBM (orbgpu_kfstore): add once, search by id."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        self.device = device
+        _check(lib().orbgpu_kfstore_create(C.byref(self._h), device))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().orbgpu_kfstore_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __len__(self):
+        return _check(lib().orbgpu_kfstore_size(self._h))
+
+    def add(self, keys_un, desc, u_right, node_ids, node_start, indices, scale_factors, level_sigma2, cam=(0, 0, 0, 0)):
+        """-> id.  u_right None = monocular."""
+        f32 = np.float32
+        k = np.ascontiguousarray(keys_un, KP_DTYPE); d = np.ascontiguousarray(desc, np.uint8)
+        ur = None if u_right is None else np.ascontiguousarray(u_right, f32)
+        ni = np.ascontiguousarray(node_ids, np.uint32); ns = np.ascontiguousarray(node_start, np.int32)
+        ix = np.ascontiguousarray(indices, np.uint32)
+        sc = np.ascontiguousarray(scale_factors, f32); sg = np.ascontiguousarray(level_sigma2, f32)
+        a = KfData()
+        a.n = len(k); a.keys_un = k.ctypes.data; a.desc = d.ctypes.data; a.u_right = None if ur is None else ur.ctypes.data
+        a.node_ids = ni.ctypes.data; a.node_start = ns.ctypes.data; a.indices = ix.ctypes.data; a.n_nodes = len(ni)
+        a.scale_factors = sc.ctypes.data; a.level_sigma2 = sg.ctypes.data; a.nlevels = len(sc)
+        a.fx, a.fy, a.cx, a.cy = [float(v) for v in cam]
+        kid = C.c_int32(-1)
+        _check(lib().orbgpu_kf_add(self._h, C.byref(a), C.byref(kid)))
+        if self._sizes is None:
+            self._sizes = {}
+        self._sizes[kid.value] = a.n
+        return kid.value
+
+    def erase(self, kid):
+        _check(lib().orbgpu_kf_erase(self._h, int(kid)))
+
+    def search_by_bow(self, id1, valid1, id2=-1, valid2=None, frame2=None, nnratio=0.7, check_orientation=True,
+                      strict_th_low=False):
+        """SearchByBoW with keyframe id1 against stored keyframe id2 (valid2) or a Frame's BowSide (frame2)
+        -> (nmatches, match12[n1], match21[n2])."""
+        v1 = np.ascontiguousarray(valid1, np.uint8)
+        v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+        n2 = frame2.n if frame2 is not None else (0 if v2 is None else len(v2))
+        m12 = np.zeros(max(len(v1), 1), np.int32); m21 = np.zeros(max(n2, 1), np.int32); nm = C.c_int(0)
+        _check(lib().orbgpu_kf_search_by_bow(self._h, int(id1), _p(v1), int(id2), None if v2 is None else _p(v2),
+                                             None if frame2 is None else C.addressof(frame2), float(nnratio),
+                                             int(check_orientation), int(strict_th_low), _p(m12), _p(m21), C.byref(nm)))
+        return nm.value, m12[:len(v1)].copy(), m21[:n2].copy()
+
+    @staticmethod
+    def triangulation_job(id1, has_mp1, id2, has_mp2, F12, Cw1, T2w, only_stereo=False, check_orientation=True):
+        """-> (struct, keepalive)."""
+        f32 = np.float32
+        h1 = np.ascontiguousarray(has_mp1, np.uint8); h2 = np.ascontiguousarray(has_mp2, np.uint8)
+        j = KfTriangulationJob()
+        j.id1 = int(id1); j.id2 = int(id2); j.has_map_point1 = h1.ctypes.data; j.has_map_point2 = h2.ctypes.data
+        j.F12 = (C.c_float * 9)(*[float(v) for v in np.asarray(F12, f32).reshape(9)])
+        j.Cw1 = (C.c_float * 3)(*[float(v) for v in np.asarray(Cw1, f32).reshape(3)])
+        j.T2w = (C.c_float * 16)(*[float(v) for v in np.asarray(T2w, f32).reshape(16)])
+        j.only_stereo = int(only_stereo); j.check_orientation = int(check_orientation)
+        return j, (h1, h2)
+
+    def search_for_triangulation(self, job):
+        """-> (nmatches, vMatches12[n1])."""
+        m12 = np.empty(max(self._sizes[job.id1], 1), np.int32); nm = C.c_int(0)
+        _check(lib().orbgpu_kf_search_for_triangulation(self._h, C.byref(job), _p(m12), C.byref(nm)))
+        return nm.value, m12[:self._sizes[job.id1]]
+
+    def search_for_triangulation_batch(self, jobs):
+        n = len(jobs)
+        if n == 0:
+            return []
+        arr = (KfTriangulationJob * n)(*jobs)
+        sizes = [self._n_of(j) for j in jobs]
+        m12 = np.zeros(max(sum(sizes), 1), np.int32); nm = np.zeros(n, np.int32)
+        _check(lib().orbgpu_kf_search_for_triangulation_batch(self._h, C.cast(arr, C.c_void_p), n, _p(m12), _p(nm)))
+        out, o = [], 0
+        for k, sz in enumerate(sizes):
+            out.append((int(nm[k]), m12[o:o + sz].copy())); o += sz
+        return out
+
+    def _n_of(self, job):
+        return self._sizes[job.id1]
+
+    _sizes = None                      # id -> N of the stored keyframe (output sizes of the triangulation search)
+
+
 def projection_args(world_pos, mp_desc, mp_valid, mp_observed, last_octave, last_angle, Tcw_last, cur_keys_un, cur_desc,
                     cur_u_right, cur_occupied, Tcw_cur, cam, bf, b, bounds, scale_factors, th, mono, check_orientation=True):
     """Builds a ProjectionArgs; returns (struct, keepalive list of the arrays it points into)."""
@@ -307,6 +414,7 @@ def lib():
         "orbgpu_chunk_capacity": (i32, [vp, i32, i32]),
         "orbgpu_undistort_keypoints": (i32, [vp, vp, vp, i32, vp, i32, pi]),
         "orbgpu_undistort_points": (i32, [i32, vp, i32, vp, vp, i32, vp]),
+        "orbgpu_extract_undistorted": (i32, [vp, vp, i32, i32, sz, vp, vp, i32, vp, vp, vp, i32, pi]),
         "orbgpu_search_for_initialization": (i32, [i32, vp, vp, i32, vp, vp, i32, vp, vp, i32, f32, i32, vp, pi]),
         "orbgpu_search_by_projection": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_local_points": (i32, [i32, vp, vp, pi]),
@@ -321,6 +429,14 @@ def lib():
         "orbgpu_search_for_triangulation": (i32, [i32, vp, vp, pi]),
         "orbgpu_search_for_triangulation_batch": (i32, [i32, vp, i32, vp, vp]),
         "orbgpu_fuse_search_batch": (i32, [i32, vp, i32, vp]),
+        "orbgpu_kfstore_create": (i32, [C.POINTER(vp), i32]),
+        "orbgpu_kfstore_destroy": (None, [vp]),
+        "orbgpu_kfstore_size": (i32, [vp]),
+        "orbgpu_kf_add": (i32, [vp, vp, C.POINTER(C.c_int32)]),
+        "orbgpu_kf_erase": (i32, [vp, i32]),
+        "orbgpu_kf_search_by_bow": (i32, [vp, i32, vp, i32, vp, vp, f32, i32, i32, vp, vp, pi]),
+        "orbgpu_kf_search_for_triangulation": (i32, [vp, vp, vp, pi]),
+        "orbgpu_kf_search_for_triangulation_batch": (i32, [vp, vp, i32, vp, vp]),
         "orbgpu_hamming256": (i32, [vp, vp]),
         "orbgpu_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp]),
         "orbgpu_vocabulary_create": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
@@ -487,6 +603,21 @@ class ORBextractor:
         kps = np.empty(cap, KP_DTYPE); n = C.c_int(0)
         _check(self._L.orbgpu_undistort_keypoints(self._h, _p(K4), _p(dist), len(dist), _p(kps), cap, C.byref(n)))
         return kps[:n.value].copy()
+
+    def extract_undistorted(self, image, K4, dist):
+        """ExtractORB + UndistortKeyPoints of the Frame constructor in one device round trip (orbgpu_extract_undistorted)
+        -> (mvKeys, mvKeysUn, mDescriptors); gray images only."""
+        if image is None or image.size == 0:
+            return None, None, None
+        if image.strides[-1] != 1:
+            image = np.ascontiguousarray(image)
+        K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+        h, w = image.shape[:2]
+        cap = self._last_cap = self.max_keypoints(w, h)
+        kps = np.zeros(cap, KP_DTYPE); un = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int(0)
+        _check(self._L.orbgpu_extract_undistorted(self._h, _p(image), w, h, image.strides[0], _p(K4), _p(dist), len(dist),
+                                                  _p(kps), _p(un), _p(desc), cap, C.byref(n)))
+        return kps[:n.value].copy(), un[:n.value].copy(), desc[:n.value].copy()
 
     # mvImagePyramid, include/ORBextractor.h:85
     def pyramid_level(self, level, bordered=False):

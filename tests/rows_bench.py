@@ -57,6 +57,14 @@ def run():
     pts = np.ascontiguousarray(np.stack([kL["x"], kL["y"]], 1))
     assert np.array_equal(np.stack([exL.undistort_keypoints(K, D)[f] for f in ("x", "y")], 1), cpu_und(pts))
     out["undistort_keypoints_1000"] = {"gpu_ms": med(lambda: exL.undistort_keypoints(K, D)), "cpu_ms": med(lambda: cpu_und(pts))}
+    # the Frame constructor's ExtractORB + UndistortKeyPoints: two calls against the fused one (the extraction is in both)
+    fk, fu, fd = exL.extract_undistorted(left, K, D)
+    assert fk.tobytes() == kL.tobytes() and fu.tobytes() == exL.undistort_keypoints(K, D).tobytes()
+    out["extract_then_undistort_640x480_1000kp"] = {
+        "gpu_ms_two_calls": med(lambda: (exL(left), exL.undistort_keypoints(K, D))),
+        "gpu_ms": med(lambda: exL.extract_undistorted(left, K, D)),
+        "gpu_ms_extract_alone": med(lambda: exL(left)),
+        "cpu_ms": med(lambda: (pl.extract(left), cpu_und(pts)), 5, 1)}
     big = (np.random.default_rng(1).random((1 << 22, 2)) * np.array([640.0, 480.0])).astype(np.float32)
     assert pkg.undistort_points(big, K, D).tobytes() == cpu_und(big).tobytes()
     out["undistort_points_4M"] = {"gpu_ms": med(lambda: pkg.undistort_points(big, K, D), 5, 1), "cpu_ms": med(lambda: cpu_und(big), 3, 1)}
@@ -79,6 +87,18 @@ def run():
     assert a[0] == o[0] and np.array_equal(a[1], o[1])
     out["search_by_bow_1000x1000_100nodes"] = {"gpu_ms": med(lambda: pkg.search_by_bow(s1, s2)), "cpu_ms": med(lambda: po.search_by_bow(s1, s2)),
                                               "nmatches": a[0]}
+    # the same searches with the keyframe(s) resident in HBM (orbgpu_kfstore): keyframe/frame (tracking) and keyframe/keyframe
+    store = pkg.KeyFrameStore()
+    sc8 = po.tables()[0][0]; sg8 = (sc8 * sc8).astype(np.float32)
+    a1, a2 = keep
+    i1 = store.add(k1, d1, None, a1["node_ids"], a1["node_start"], a1["indices"], sc8, sg8)
+    i2 = store.add(k2, d2, None, a2["node_ids"], a2["node_start"], a2["indices"], sc8, sg8)
+    r = store.search_by_bow(i1, a1["valid"], -1, None, s2)
+    assert r[0] == o[0] and np.array_equal(r[1], o[1])
+    out["search_by_bow_1000x1000_100nodes"]["gpu_ms_keyframe_resident"] = med(lambda: store.search_by_bow(i1, a1["valid"], -1, None, s2))
+    r = store.search_by_bow(i1, a1["valid"], i2, a2["valid"])
+    assert r[0] == o[0] and np.array_equal(r[1], o[1])
+    out["search_by_bow_1000x1000_100nodes"]["gpu_ms_both_resident"] = med(lambda: store.search_by_bow(i1, a1["valid"], i2, a2["valid"]))
     # --- local-map search: SearchByProjection(Frame, vector<MapPoint*>, th), 1000 and 4000 map points against 1000 features
     import test_local_points as tl
     for rep, th in [(1, 1.0), (4, 3.0)]:
@@ -97,6 +117,14 @@ def run():
         assert a[0] == o[0] and np.array_equal(a[1], o[1])
         out["search_for_triangulation_%dx%d_100nodes" % (len(G1[0]), len(G2[0]))] = {
             "gpu_ms": med(lambda: pkg.search_for_triangulation(args)), "cpu_ms": med(lambda: po.search_for_triangulation(args)), "nmatches": a[0]}
+        sc, sg = keep[2]
+        j1 = store.add(keep[0][0], keep[0][1], keep[0][3], keep[0][4], keep[0][5], keep[0][6], sc, sg, tt.CAM)
+        j2 = store.add(keep[1][0], keep[1][1], keep[1][3], keep[1][4], keep[1][5], keep[1][6], sc, sg, tt.CAM)
+        job, kj = store.triangulation_job(j1, keep[0][2], j2, keep[1][2], np.ctypeslib.as_array(args.F12), np.ctypeslib.as_array(args.Cw1),
+                                          np.ctypeslib.as_array(args.T2w), False, True)
+        r = store.search_for_triangulation(job)
+        assert r[0] == o[0] and np.array_equal(r[1], o[1])
+        out["search_for_triangulation_%dx%d_100nodes" % (len(G1[0]), len(G2[0]))]["gpu_ms_resident"] = med(lambda: store.search_for_triangulation(job))
         if nf == 1000:          # one keyframe against 20 neighbours in one call (CreateNewMapPoints), per pair
             many = [tt.tri_scene(pkg, po, G1, G2, 4 + i, 100, False, True, 0.5) for i in range(20)]
             bl = [m[0] for m in many]
@@ -105,6 +133,18 @@ def run():
             out["search_for_triangulation_batch_20_pairs_%dx%d_per_pair" % (len(G1[0]), len(G2[0]))] = {
                 "gpu_ms": med(lambda: pkg.search_for_triangulation_batch(bl)) / 20,
                 "cpu_ms": med(lambda: [po.search_for_triangulation(b) for b in bl], 10, 1) / 20}
+            jl, kl = [], []
+            for m in many:
+                kp = m[1]
+                x1 = store.add(kp[0][0], kp[0][1], kp[0][3], kp[0][4], kp[0][5], kp[0][6], sc, sg, tt.CAM)
+                x2 = store.add(kp[1][0], kp[1][1], kp[1][3], kp[1][4], kp[1][5], kp[1][6], sc, sg, tt.CAM)
+                jb = store.triangulation_job(x1, kp[0][2], x2, kp[1][2], np.ctypeslib.as_array(m[0].F12), np.ctypeslib.as_array(m[0].Cw1),
+                                             np.ctypeslib.as_array(m[0].T2w), False, True)
+                jl.append(jb[0]); kl.append(jb[1])
+            rg = store.search_for_triangulation_batch(jl)
+            assert all(x[0] == y[0] and np.array_equal(x[1], y[1]) for x, y in zip(rg, got))
+            out["search_for_triangulation_batch_20_pairs_%dx%d_per_pair" % (len(G1[0]), len(G2[0]))]["gpu_ms_resident"] = \
+                med(lambda: store.search_for_triangulation_batch(jl)) / 20
     # --- Tracking::SearchLocalPoints in one call: isInFrustum for 4000 local map points + the search against 1000 features
     import test_local_map as tm
     G1 = (np.concatenate([k1] * 4), np.concatenate([d1] * 4))

@@ -55,6 +55,28 @@ def test_device_keypoints_undistorted_in_place_of_the_host_pass(pkg, oracle):
 
 
 @pytest.mark.gpu
+def test_extract_and_undistort_in_one_call_equals_the_two_calls(pkg, oracle):
+    """orbgpu_extract_undistorted: ExtractORB + UndistortKeyPoints of the Frame constructor behind one synchronisation"""
+    ex = pkg.ORBextractor(1200, 1.2, 8, 20, 7); two = pkg.ORBextractor(1200, 1.2, 8, 20, 7)
+    for seed, (w, h), c in [(0x0D157, (752, 480), 1), (0x0D158, (640, 480), 0), (0x0D159, (752, 480), 1), (0x0D15A, (203, 149), 0)]:
+        img = pkg.synth.synth(w, h, seed)
+        K, D = GOLD["K_%d" % c], GOLD["D_%d" % c]
+        kps, un, desc = ex.extract_undistorted(img, K, D)
+        k2, d2 = two(img)
+        assert kps.tobytes() == k2.tobytes() and desc.tobytes() == d2.tobytes() and len(kps) > 50
+        assert un.tobytes() == two.undistort_keypoints(K, D).tobytes()
+        want = oracle_undistort(oracle, np.stack([kps["x"], kps["y"]], 1), K, D)
+        assert np.stack([un["x"], un["y"]], 1).tobytes() == want.tobytes()
+    # the frame stays the handle's most recent frame; a zero first coefficient copies the keypoints; an empty image is a no-op
+    assert ex.pyramid_level(1).shape == two.pyramid_level(1).shape
+    kps, un, _ = ex.extract_undistorted(img, K, np.zeros(4, np.float32))
+    assert un.tobytes() == kps.tobytes()
+    assert ex.extract_undistorted(np.zeros((0, 0), np.uint8), K, D) == (None, None, None)
+    with pytest.raises(pkg.OrbGpuError):
+        ex.extract_undistorted(img, K, np.zeros(3, np.float32))
+
+
+@pytest.mark.gpu
 def test_undistort_argument_errors(pkg):
     ex = pkg.ORBextractor(500, 1.2, 8, 20, 7)
     with pytest.raises(RuntimeError):
