@@ -416,8 +416,8 @@ typedef struct orbgpu_kf_data {
     const float* u_right;             /* pKF->mvuRight; NULL = monocular (all -1) */
     const uint32_t* node_ids; const int32_t* node_start; const uint32_t* indices; int32_t n_nodes;   /* pKF->mFeatVec, flattened
                                          as for orbgpu_search_by_bow (call after ComputeBoW) */
-    const float* scale_factors;       /* pKF->mvScaleFactors[nlevels] */
-    const float* level_sigma2;        /* pKF->mvLevelSigma2[nlevels] */
+    const float* scale_factors;       /* pKF->mvScaleFactors[nlevels]; read by the triangulation search only (NULL = zeros) */
+    const float* level_sigma2;        /* pKF->mvLevelSigma2[nlevels]; likewise */
     int32_t nlevels;
     float fx, fy, cx, cy;             /* pKF->fx .. cy */
 } orbgpu_kf_data;

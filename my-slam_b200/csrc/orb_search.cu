@@ -2315,7 +2315,7 @@ int orbgpu_kf_add(orbgpu_kfstore* st, const orbgpu_kf_data* k, int32_t* id)
     *id = -1;
     if (k->n < 0 || (k->n > 0 && (!k->keys_un || !k->desc))) return ORBGPU_ERR_ARG;
     if (k->n > GRID_MAX_KEYS) return ORBGPU_ERR_UNSUPPORTED;
-    if (k->nlevels < 1 || k->nlevels > ORBGPU_MAX_LEVELS || !k->scale_factors || !k->level_sigma2) return ORBGPU_ERR_ARG;
+    if (k->nlevels < 1 || k->nlevels > ORBGPU_MAX_LEVELS) return ORBGPU_ERR_ARG;
     int rc = check_feature_vector(k->n, k->node_ids, k->node_start, k->indices, k->n_nodes);
     if (rc != ORBGPU_OK) return rc;
     for (int i = 0; i < k->n; ++i)
@@ -2343,8 +2343,8 @@ int orbgpu_kf_add(orbgpu_kfstore* st, const orbgpu_kf_data* k, int32_t* id)
     memcpy(W.h + s.o_desc, k->desc, 32 * (size_t)n);
     memcpy(W.h + s.o_ur, s.u_right.data(), 4 * (size_t)n);
     memcpy(W.h + s.o_idx, s.indices.data(), 4 * (size_t)nidx);
-    memcpy(W.h + s.o_sc, k->scale_factors, 4 * (size_t)k->nlevels);
-    memcpy(W.h + s.o_sg, k->level_sigma2, 4 * (size_t)k->nlevels);
+    if (k->scale_factors) memcpy(W.h + s.o_sc, k->scale_factors, 4 * (size_t)k->nlevels);     // (the block was zeroed above)
+    if (k->level_sigma2) memcpy(W.h + s.o_sg, k->level_sigma2, 4 * (size_t)k->nlevels);
     {
         std::lock_guard<std::mutex> g(st->mu);
         s.d = st->block(s.bytes);

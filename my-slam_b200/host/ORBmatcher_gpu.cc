@@ -19,9 +19,11 @@
 #include <stdint.h>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <set>
 #include <stdexcept>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "orbgpu.h"
@@ -38,6 +40,9 @@ static_assert(sizeof(cv::KeyPoint) == sizeof(orbgpu_keypoint), "cv::KeyPoint mus
 
 #ifndef ORBGPU_MATCHER_DEVICE
 #define ORBGPU_MATCHER_DEVICE 0           // CUDA ordinal the matcher's calls run on
+#endif
+#ifndef ORBGPU_MATCHER_RESIDENT_KEYFRAMES
+#define ORBGPU_MATCHER_RESIDENT_KEYFRAMES 4096   // keyframes kept in HBM by the BoW-gated searches (~70 KB each), least recently used out first
 #endif
 
 namespace {
@@ -126,6 +131,64 @@ struct KeyFrameSnap {
     }
 };
 
+// Keyframes resident in HBM.  What the BoW-gated searches read of a KeyFrame -- mvKeysUn, mDescriptors, mvuRight, mFeatVec,
+// the level tables and intrinsics -- is written once (KeyFrame constructor, ComputeBoW: src/KeyFrame.cc:32-58, :66-76), so it
+// is uploaded the first time a search names the keyframe (orbgpu_kf_add) and referred to by id afterwards; a call then
+// carries only the map-point flags and poses.  An entry is refreshed when the keyframe's FeatureVector has been computed
+// since (a keyframe searched before LocalMapping::ProcessNewKeyFrame ran ComputeBoW), and the least recently used entries
+// go when the table is full (culled keyframes are never searched again, so they age out).  Shared by the matcher objects of
+// all threads (Tracking, LocalMapping, LoopClosing), as the keyframes are.
+class ResidentKeyFrames {
+public:
+    orbgpu_kfstore* store()
+    {
+        std::lock_guard<std::mutex> g(mu_);
+        open();
+        return store_;
+    }
+    int32_t id_of(KeyFrame* pKF)
+    {
+        std::lock_guard<std::mutex> g(mu_);
+        open();
+        const size_t fv = pKF->mFeatVec.size();
+        std::unordered_map<const KeyFrame*, Entry>::iterator it = map_.find(pKF);
+        if (it != map_.end()) {
+            if (it->second.mnId == pKF->mnId && it->second.fv_nodes == fv) { it->second.used = ++clock_; return it->second.id; }
+            orbgpu_kf_erase(store_, it->second.id);
+            map_.erase(it);
+        }
+        if (map_.size() >= (size_t)ORBGPU_MATCHER_RESIDENT_KEYFRAMES) {
+            std::unordered_map<const KeyFrame*, Entry>::iterator lru = map_.begin();
+            for (it = map_.begin(); it != map_.end(); ++it) if (it->second.used < lru->second.used) lru = it;
+            orbgpu_kf_erase(store_, lru->second.id);
+            map_.erase(lru);
+        }
+        const FlatFeatVec f(pKF->mFeatVec);
+        std::vector<uint8_t> tmp;
+        orbgpu_kf_data k;
+        std::memset(&k, 0, sizeof(k));
+        k.n = pKF->N; k.keys_un = keys_of(pKF->mvKeysUn); k.desc = dense_desc(pKF->mDescriptors, tmp);
+        k.u_right = pKF->mvuRight.empty() ? 0 : pKF->mvuRight.data();
+        k.node_ids = f.ids.data(); k.node_start = f.start.data(); k.indices = f.idx.data(); k.n_nodes = f.n_nodes();
+        k.scale_factors = pKF->mvScaleFactors.data(); k.level_sigma2 = pKF->mvLevelSigma2.data(); k.nlevels = pKF->mnScaleLevels;
+        k.fx = pKF->fx; k.fy = pKF->fy; k.cx = pKF->cx; k.cy = pKF->cy;
+        Entry e;
+        check(orbgpu_kf_add(store_, &k, &e.id), "keyframe upload");
+        e.mnId = pKF->mnId; e.fv_nodes = fv; e.used = ++clock_;
+        map_[pKF] = e;
+        return e.id;
+    }
+
+private:
+    struct Entry { int32_t id; long unsigned int mnId; size_t fv_nodes; uint64_t used; };
+    void open() { if (!store_) check(orbgpu_kfstore_create(&store_, ORBGPU_MATCHER_DEVICE), "keyframe store"); }
+    std::mutex mu_;
+    orbgpu_kfstore* store_ = 0;
+    std::unordered_map<const KeyFrame*, Entry> map_;
+    uint64_t clock_ = 0;
+};
+ResidentKeyFrames g_keyframes;      // released with the process
+
 void points_into(orbgpu_fuse_args& a, const PointSnap& s, const std::vector<uint8_t>& present)
 {
     a.n_points = (int32_t)present.size();
@@ -206,21 +269,21 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPoi
     vpMapPointMatches = vector<MapPoint*>(F.N, static_cast<MapPoint*>(NULL));
     const int n1 = pKF->N, n2 = F.N;
     if (n1 == 0 || n2 == 0) return 0;
-    std::vector<uint8_t> valid1((size_t)n1), valid2((size_t)n2, 1), t1, t2;          // a Frame's features are all eligible
-    std::vector<float> ang1((size_t)n1), ang2((size_t)n2 + 1);
+    std::vector<uint8_t> valid1((size_t)n1), valid2((size_t)n2, 1), t2;              // a Frame's features are all eligible
+    std::vector<float> ang2((size_t)n2 + 1);
     for (int i = 0; i < n1; ++i) {
         MapPoint* p = vpMapPointsKF[(size_t)i];
         valid1[(size_t)i] = p && !p->isBad();
-        ang1[(size_t)i] = pKF->mvKeysUn[(size_t)i].angle;
     }
     for (int i = 0; i < n2; ++i) ang2[(size_t)i] = F.mvKeys[(size_t)i].angle;        // the frame side reads mvKeys (:245)
-    const FlatFeatVec f1(pKF->mFeatVec), f2(F.mFeatVec);
-    orbgpu_bow_side s1, s2;
-    bow_side_of(s1, pKF->mDescriptors, n1, &valid1, ang1, f1, t1);
+    const FlatFeatVec f2(F.mFeatVec);
+    orbgpu_bow_side s2;
     bow_side_of(s2, F.mDescriptors, n2, &valid2, ang2, f2, t2);
     std::vector<int32_t> m12((size_t)n1, -1), m21((size_t)n2, -1);
     int nmatches = 0;
-    check(orbgpu_search_by_bow(ORBGPU_MATCHER_DEVICE, &s1, &s2, mfNNratio, mbCheckOrientation, 0, m12.data(), m21.data(), &nmatches), "SearchByBoW(KF, F)");
+    // the keyframe is resident (uploaded the first time it is searched); the frame travels with the call
+    check(orbgpu_kf_search_by_bow(g_keyframes.store(), g_keyframes.id_of(pKF), valid1.data(), -1, 0, &s2, mfNNratio, mbCheckOrientation, 0,
+                                  m12.data(), m21.data(), &nmatches), "SearchByBoW(KF, F)");
     for (int i2 = 0; i2 < n2; ++i2)
         if (m21[(size_t)i2] >= 0) vpMapPointMatches[(size_t)i2] = vpMapPointsKF[(size_t)m21[(size_t)i2]];
     return nmatches;
@@ -232,25 +295,20 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& v
     vpMatches12 = vector<MapPoint*>(vpMapPoints1.size(), static_cast<MapPoint*>(NULL));
     const int n1 = (int)vpMapPoints1.size(), n2 = (int)vpMapPoints2.size();
     if (n1 == 0 || n2 == 0) return 0;
-    std::vector<uint8_t> valid1((size_t)n1), valid2((size_t)n2), t1, t2;
-    std::vector<float> ang1((size_t)n1), ang2((size_t)n2);
+    std::vector<uint8_t> valid1((size_t)n1), valid2((size_t)n2);
     for (int i = 0; i < n1; ++i) {
         MapPoint* p = vpMapPoints1[(size_t)i];
         valid1[(size_t)i] = p && !p->isBad();
-        ang1[(size_t)i] = pKF1->mvKeysUn[(size_t)i].angle;
     }
     for (int i = 0; i < n2; ++i) {
         MapPoint* p = vpMapPoints2[(size_t)i];
         valid2[(size_t)i] = p && !p->isBad();
-        ang2[(size_t)i] = pKF2->mvKeysUn[(size_t)i].angle;
     }
-    const FlatFeatVec f1(pKF1->mFeatVec), f2(pKF2->mFeatVec);
-    orbgpu_bow_side s1, s2;
-    bow_side_of(s1, pKF1->mDescriptors, n1, &valid1, ang1, f1, t1);
-    bow_side_of(s2, pKF2->mDescriptors, n2, &valid2, ang2, f2, t2);
     std::vector<int32_t> m12((size_t)n1, -1), m21((size_t)n2, -1);
     int nmatches = 0;
-    check(orbgpu_search_by_bow(ORBGPU_MATCHER_DEVICE, &s1, &s2, mfNNratio, mbCheckOrientation, 1, m12.data(), m21.data(), &nmatches), "SearchByBoW(KF, KF)");
+    const int32_t id1 = g_keyframes.id_of(pKF1), id2 = g_keyframes.id_of(pKF2);      // both resident: only the flags travel
+    check(orbgpu_kf_search_by_bow(g_keyframes.store(), id1, valid1.data(), id2, valid2.data(), 0, mfNNratio, mbCheckOrientation, 1,
+                                  m12.data(), m21.data(), &nmatches), "SearchByBoW(KF, KF)");
     for (int i1 = 0; i1 < n1; ++i1)
         if (m12[(size_t)i1] >= 0) vpMatches12[(size_t)i1] = vpMapPoints2[(size_t)m12[(size_t)i1]];
     return nmatches;
@@ -312,29 +370,22 @@ int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F
     vMatchedPairs.clear();
     const int n1 = pKF1->N, n2 = pKF2->N;
     if (n1 == 0 || n2 == 0) return 0;
-    orbgpu_triangulation_args a;
+    orbgpu_kf_triangulation_job a;
     std::memset(&a, 0, sizeof(a));
-    std::vector<uint8_t> has1((size_t)n1), has2((size_t)n2), t1, t2;
+    std::vector<uint8_t> has1((size_t)n1), has2((size_t)n2);
     for (int i = 0; i < n1; ++i) has1[(size_t)i] = pKF1->GetMapPoint((size_t)i) != NULL;
     for (int i = 0; i < n2; ++i) has2[(size_t)i] = pKF2->GetMapPoint((size_t)i) != NULL;
-    const FlatFeatVec f1(pKF1->mFeatVec), f2(pKF2->mFeatVec);
-    a.kf1.keys_un = keys_of(pKF1->mvKeysUn); a.kf1.desc = dense_desc(pKF1->mDescriptors, t1); a.kf1.n = n1;
-    a.kf1.has_map_point = has1.data(); a.kf1.u_right = pKF1->mvuRight.data();
-    a.kf1.node_ids = f1.ids.data(); a.kf1.node_start = f1.start.data(); a.kf1.indices = f1.idx.data(); a.kf1.n_nodes = f1.n_nodes();
-    a.kf2.keys_un = keys_of(pKF2->mvKeysUn); a.kf2.desc = dense_desc(pKF2->mDescriptors, t2); a.kf2.n = n2;
-    a.kf2.has_map_point = has2.data(); a.kf2.u_right = pKF2->mvuRight.data();
-    a.kf2.node_ids = f2.ids.data(); a.kf2.node_start = f2.start.data(); a.kf2.indices = f2.idx.data(); a.kf2.n_nodes = f2.n_nodes();
+    a.id1 = g_keyframes.id_of(pKF1); a.id2 = g_keyframes.id_of(pKF2);                // keypoints, descriptors, mvuRight, mFeatVec: resident
+    a.has_map_point1 = has1.data(); a.has_map_point2 = has2.data();
     for (int r = 0; r < 3; ++r)
         for (int c = 0; c < 3; ++c) a.F12[3 * r + c] = F12.at<float>(r, c);
     const cv::Mat Cw = pKF1->GetCameraCenter();
     for (int k = 0; k < 3; ++k) a.Cw1[k] = Cw.at<float>(k);
     pose16(pKF2->GetPose(), a.T2w);
-    a.fx = pKF2->fx; a.fy = pKF2->fy; a.cx = pKF2->cx; a.cy = pKF2->cy;
-    a.scale_factors2 = pKF2->mvScaleFactors.data(); a.level_sigma2 = pKF2->mvLevelSigma2.data(); a.nlevels = pKF2->mnScaleLevels;
     a.only_stereo = bOnlyStereo; a.check_orientation = mbCheckOrientation;
     std::vector<int32_t> m12((size_t)n1, -1);
     int nmatches = 0;
-    check(orbgpu_search_for_triangulation(ORBGPU_MATCHER_DEVICE, &a, m12.data(), &nmatches), "SearchForTriangulation");
+    check(orbgpu_kf_search_for_triangulation(g_keyframes.store(), &a, m12.data(), &nmatches), "SearchForTriangulation");
     vMatchedPairs.reserve((size_t)nmatches);
     for (int i = 0; i < n1; ++i)
         if (m12[(size_t)i] >= 0) vMatchedPairs.push_back(make_pair((size_t)i, (size_t)m12[(size_t)i]));

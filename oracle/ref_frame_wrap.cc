@@ -698,6 +698,57 @@ int frameref_search_by_bow(const frameport_bow_side* s1, const frameport_bow_sid
     return nm;
 }
 
+// SearchByBoW(pKF1, pKF2) three times on the SAME two KeyFrame objects, as a running system calls it: (a) before pKF2's
+// FeatureVector exists (ComputeBoW not run yet: nothing can match), (b) after it has been filled in, (c) after every third
+// map point of pKF1 has been erased from the keyframe.  match12_abc = three arrays of s1->n entries; returns the three
+// counts packed as a + 1000 * (b + 1000 * c).  (For a matcher that keeps keyframes resident: hit, refresh, changed flags.)
+long frameref_search_by_bow_thrice(const frameport_bow_side* s1, const frameport_bow_side* s2, float nnratio, int check_orientation,
+                                   int* match12_abc)
+{
+    const float bounds[4] = {0.f, 640.f, 0.f, 480.f};
+    set_frame_statics(bounds, 1.f, 1.f, 0.f, 0.f);
+    World world;
+    const float origin[3] = {0, 0, 0};
+    const frameport_bow_side* sides[2] = {s1, s2};
+    Frame F[2];
+    KeyFrame* KF[2] = {0, 0};
+    std::map<MapPoint*, int> index_of2;
+    for (int s = 0; s < 2; ++s) {
+        const frameport_bow_side* sd = sides[s];
+        std::vector<KP> keys((size_t)sd->n);
+        for (int i = 0; i < sd->n; ++i) {
+            std::memset(&keys[i], 0, sizeof(KP));
+            keys[i].x = 10.f + (float)(i % 600); keys[i].y = 10.f + (float)(i % 400);
+            keys[i].angle = sd->angle[i];
+        }
+        fill_frame(F[s], keys.data(), sd->desc, sd->n);
+        F[s].mTcw = cv::Mat::eye(4, 4, CV_32F);
+        F[s].mbf = 1.f; F[s].mb = 1.f; F[s].mThDepth = 1.f; F[s].mTimeStamp = 0; F[s].mnId = (unsigned long)(s + 1);
+        F[s].mnScaleLevels = 1; F[s].mfScaleFactor = 1.2f; F[s].mfLogScaleFactor = std::log(1.2f);
+        if (s == 0) fill_feature_vector(F[s].mFeatVec, sd);
+        for (int i = 0; i < sd->n; ++i)
+            if (!sd->valid || sd->valid[i]) {
+                MapPoint* p = world.point(origin, sd->desc + 32 * (size_t)i, 1, false);
+                F[s].mvpMapPoints[i] = p;
+                if (s == 1) index_of2[p] = i;
+            }
+        KF[s] = new KeyFrame(F[s], &world.map, static_cast<KeyFrameDatabase*>(NULL));
+        world.keyframes.push_back(KF[s]);
+    }
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    long nm[3];
+    for (int pass = 0; pass < 3; ++pass) {
+        if (pass == 1) fill_feature_vector(KF[1]->mFeatVec, s2);
+        if (pass == 2)
+            for (int i = 0; i < s1->n; i += 3) KF[0]->EraseMapPointMatch((size_t)i);
+        std::vector<MapPoint*> matches;
+        nm[pass] = matcher.SearchByBoW(KF[0], KF[1], matches);
+        int* out = match12_abc + (size_t)pass * s1->n;
+        for (int i1 = 0; i1 < s1->n; ++i1) out[i1] = matches[i1] ? index_of2[matches[i1]] : -1;
+    }
+    return nm[0] + 1000 * (nm[1] + 1000 * nm[2]);
+}
+
 // SearchForTriangulation between two KeyFrames built by the reference's constructor from plain arrays.  T1w is the pose
 // of pKF1; the camera centre the reference derives from it (KeyFrame::SetPose, GetCameraCenter) is returned in cw1_out so
 // the restatement can be given exactly the value the reference used (a->Cw1 is ignored here).

@@ -546,6 +546,16 @@ class OracleFrameRef:
                                            _ptr(m12), _ptr(m21))
         return nm, m12[:side1.n].copy(), m21[:side2.n].copy()
 
+    def search_by_bow_thrice(self, side1, side2, nnratio=0.7, check_orientation=True):
+        """SearchByBoW(pKF1, pKF2) on the same two KeyFrame objects: before pKF2 has a FeatureVector, after, and after every
+        third map point of pKF1 was erased -> [(nmatches, match12)] * 3."""
+        f = self.L.frameref_search_by_bow_thrice
+        f.restype = C.c_long
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p]
+        m = _i32(3 * side1.n)
+        packed = f(C.byref(side1), C.byref(side2), nnratio, int(check_orientation), _ptr(m))
+        return [(int(packed // 1000 ** k % 1000), m[k * side1.n:(k + 1) * side1.n].copy()) for k in range(3)]
+
     def stereo_matches(self, kL, dL, kR, dR, lvlL, lvlR, bf, b):
         nl = len(lvlL)
         lvlL = [np.ascontiguousarray(a, np.uint8) for a in lvlL]; lvlR = [np.ascontiguousarray(a, np.uint8) for a in lvlR]

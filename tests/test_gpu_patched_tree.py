@@ -94,6 +94,20 @@ def test_patched_search_by_bow(pkg, ref, gpu, scene, kf_kf):
     assert total > 300
 
 
+def test_patched_search_by_bow_on_the_same_keyframes_again(pkg, ref, gpu, scene):
+    """The patched matcher keeps keyframes resident in HBM: the same two KeyFrame objects searched before pKF2 has a
+    FeatureVector, after ComputeBoW filled it in (the resident copy must be refreshed) and after map points were erased from
+    pKF1 (only the flags change) -- each time what the unmodified reference returns."""
+    F1, F2, _ = scene
+    for seed, words in [(3, 24), (4, 100)]:
+        s1, s2, keep = bow_sides(pkg, F1, F2, seed, True, words)
+        want = ref.search_by_bow_thrice(s1, s2, 0.75, True)
+        got = gpu.search_by_bow_thrice(s1, s2, 0.75, True)
+        assert want[0][0] == 0 and want[1][0] > 100 and 0 < want[2][0] < want[1][0]
+        for g, w in zip(got, want):
+            assert g[0] == w[0] and np.array_equal(g[1], w[1])
+
+
 @pytest.mark.parametrize("th", [1.0, 3.0])
 def test_patched_search_local_points_and_local_map(pkg, port, ref, gpu, scene, th):
     F1, F2, bounds = scene
