@@ -1,3 +1,9 @@
+#!/usr/bin/env python
+"""Where the microseconds of a BoW-gated search go: runs SearchByBoW and SearchForTriangulation with host arrays and with the
+keyframes resident in HBM (orbgpu_kfstore) under ORBGPU_TRACE_SEARCH=1, which makes the library print the host-clock phases
+of every call (merge walk, staging, enqueue, wait, finish) and the kernel time between two CUDA events to stderr.
+    python tools/trace_probe.py 2>&1 | grep orbgpu
+The scene builders live under tests/ (they use the oracle for nothing but the level tables here)."""
 import os, sys
 os.environ["ORBGPU_TRACE_SEARCH"] = "1"
 sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
