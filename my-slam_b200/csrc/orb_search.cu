@@ -1116,6 +1116,50 @@ void set_grid(GridDev& G, uint8_t* d, size_t o_keys, size_t o_desc, size_t o_sta
 
 }  // namespace
 
+// cudaMemcpyAsync of a few KB takes the driver's inline path and costs the calling thread 5-8 us more than a 32 KB copy
+// (measured on B200: enqueue 15.2 -> 7.5 us for the 14 KB of a resident SearchByBoW); small uploads are padded up to this
+// size with whatever follows them in the pinned block (the device block is at least as large)
+static const size_t SEARCH_MIN_UPLOAD = (size_t)32 << 10;
+
+// ORBGPU_TRACE_SEARCH=1: host-clock phases of the BoW-gated searches on stderr (where a call's microseconds go)
+struct PhaseTrace {
+    bool on; const char* what; int k = 0; double t[8]; const char* name[8];
+    explicit PhaseTrace(const char* w) : what(w) { static const bool env = getenv("ORBGPU_TRACE_SEARCH") != nullptr; on = env; mark("entry"); }
+    void mark(const char* n)
+    {
+        if (!on || k >= 8) return;
+        timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+        t[k] = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; name[k++] = n;
+    }
+    ~PhaseTrace()
+    {
+        if (!on) return;
+        fprintf(stderr, "[orbgpu] %s:", what);
+        for (int i = 1; i < k; ++i) fprintf(stderr, " %s %.1f", name[i], t[i] - t[i - 1]);
+        fprintf(stderr, " | total %.1f us\n", t[k - 1] - t[0]);
+    }
+};
+
+// ORBGPU_TRACE_SEARCH=1, device side: time between marks on one stream (CUDA events), printed by the destructor
+struct StreamTrace {
+    bool on; cudaStream_t st; int k = 0; cudaEvent_t ev[10]; const char* name[10];
+    StreamTrace(bool enabled, cudaStream_t s) : on(enabled), st(s) { mark("begin"); }
+    void mark(const char* n)
+    {
+        if (!on || k >= 10) return;
+        cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], st); name[k++] = n;
+    }
+    ~StreamTrace()
+    {
+        if (!on) return;
+        cudaEventSynchronize(ev[k - 1]);
+        fprintf(stderr, "[orbgpu]   device:");
+        for (int i = 1; i < k; ++i) { float ms = 0.f; cudaEventElapsedTime(&ms, ev[i - 1], ev[i]); fprintf(stderr, " %s %.1f", name[i], ms * 1e3); }
+        fprintf(stderr, " us\n");
+        for (int i = 0; i < k; ++i) cudaEventDestroy(ev[i]);
+    }
+};
+
 extern "C" {
 
 int orbgpu_search_for_initialization(int device, const orbgpu_keypoint* keys1_un, const uint8_t* desc1, int n1,
@@ -1196,6 +1240,7 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     if (!(a->bounds[1] > a->bounds[0]) || !(a->bounds[3] > a->bounds[2])) return ORBGPU_ERR_ARG;
     const int n1 = a->n_last, n2 = a->n_cur;
     if (n1 > GRID_MAX_KEYS || n2 > GRID_MAX_KEYS || (size_t)n1 * (size_t)n2 > ((size_t)1 << 26)) return ORBGPU_ERR_UNSUPPORTED;
+    PhaseTrace tr("search_by_projection");
     for (int i = 0; i < n1; ++i)
         if (a->mp_valid[i] && (a->last_octave[i] < 0 || a->last_octave[i] >= a->nlevels)) return ORBGPU_ERR_ARG;
     *nmatches = 0;
@@ -1243,21 +1288,31 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     memcpy(W.h + o_oct, a->last_octave, 4 * (size_t)n1);
     memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
     memcpy(W.h + o_ur, a->cur_u_right, 4 * (size_t)n2);
+    tr.mark("stage");
+    StreamTrace dt(tr.on, W.st);
     CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    dt.mark("upload");
     GridDev G;
     set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
     AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
     k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    dt.mark("grid");
     k_proj_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
                                                        reinterpret_cast<const int*>(W.d + o_oct), reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
+    dt.mark("queries");
     k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
+    dt.mark("candidates");
     k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, 100, reinterpret_cast<int*>(W.d + o_cm),
                                                                reinterpret_cast<int*>(W.d + o_acc), reinterpret_cast<int*>(W.d + o_nm));
+    dt.mark("resolve");
     CUS(cudaGetLastError());
     CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    dt.mark("download");
+    tr.mark("enqueue");
     CUS(cudaStreamSynchronize(W.st));
+    tr.mark("wait");
     memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
     const int* acc = reinterpret_cast<const int*>(W.h + o_acc);
     int nm = *reinterpret_cast<const int*>(W.h + o_nm);
@@ -1388,6 +1443,7 @@ int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const or
     const size_t io_bytes = L.off;
     const size_t o_start = L.add(4 * (GRID_CELLS + 1)), o_sorted = L.add(4 * (size_t)n2), o_cn = L.add(4 * (size_t)n1);
     const size_t o_q = L.add(sizeof(AreaQuery) * (size_t)n1), o_cl = L.add(4 * (size_t)n1 * (size_t)(n2 > 0 ? n2 : 1));
+    PhaseTrace tr("search_local_map");
     Workspace& W = g_ws;
     int rc = W.reserve(device, L.off, io_bytes);
     if (rc != ORBGPU_OK) return rc;
@@ -1405,7 +1461,10 @@ int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const or
     memcpy(W.h + o_maxd, a->max_distance, 4 * (size_t)n1);
     memcpy(W.h + o_mind, a->min_distance, 4 * (size_t)n1);
     memcpy(W.h + o_scale, a->scale_factors, 4 * (size_t)a->nlevels);
+    tr.mark("stage");
+    StreamTrace dt(tr.on, W.st);
     CUS(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.st));
+    dt.mark("upload");
     CUS(cudaMemsetAsync(W.d + o_nm, 0, 8, W.st));
     TrackOut T;
     T.in_view = W.d + o_iv; T.proj_x = reinterpret_cast<float*>(W.d + o_px); T.proj_y = reinterpret_cast<float*>(W.d + o_py);
@@ -1421,14 +1480,21 @@ int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const or
         set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
         uint32_t* d_cl = reinterpret_cast<uint32_t*>(W.d + o_cl);
         int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
+        dt.mark("frustum");
         k_grid_build<<<1, 1024, 0, W.st>>>(G);
+        dt.mark("grid");
         k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cl, n2, d_cn);
+        dt.mark("candidates");
         k_local_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cl, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, G.keys, a->nnratio,
                                                                     reinterpret_cast<int*>(W.d + o_cm), d_nm);
     }
     CUS(cudaGetLastError());
+    dt.mark("resolve");
     CUS(cudaMemcpyAsync(W.h + in_bytes, W.d + in_bytes, io_bytes - in_bytes, cudaMemcpyDeviceToHost, W.st));
+    dt.mark("download");
+    tr.mark("enqueue");
     CUS(cudaStreamSynchronize(W.st));
+    tr.mark("wait");
     if (n2) memcpy(cur_match, W.h + o_cm, 4 * (size_t)n2);
     *nmatches = reinterpret_cast<const int*>(W.h + o_nm)[0];
     *n_in_view = reinterpret_cast<const int*>(W.h + o_nm)[1];
@@ -1778,30 +1844,6 @@ int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projecti
 }
 
 }  // extern "C"
-
-// cudaMemcpyAsync of a few KB takes the driver's inline path and costs the calling thread 5-8 us more than a 32 KB copy
-// (measured on B200: enqueue 15.2 -> 7.5 us for the 14 KB of a resident SearchByBoW); small uploads are padded up to this
-// size with whatever follows them in the pinned block (the device block is at least as large)
-static const size_t SEARCH_MIN_UPLOAD = (size_t)32 << 10;
-
-// ORBGPU_TRACE_SEARCH=1: host-clock phases of the BoW-gated searches on stderr (where a call's microseconds go)
-struct PhaseTrace {
-    bool on; const char* what; int k = 0; double t[8]; const char* name[8];
-    explicit PhaseTrace(const char* w) : what(w) { static const bool env = getenv("ORBGPU_TRACE_SEARCH") != nullptr; on = env; mark("entry"); }
-    void mark(const char* n)
-    {
-        if (!on || k >= 8) return;
-        timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
-        t[k] = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; name[k++] = n;
-    }
-    ~PhaseTrace()
-    {
-        if (!on) return;
-        fprintf(stderr, "[orbgpu] %s:", what);
-        for (int i = 1; i < k; ++i) fprintf(stderr, " %s %.1f", name[i], t[i] - t[i - 1]);
-        fprintf(stderr, " | total %.1f us\n", t[k - 1] - t[0]);
-    }
-};
 
 // ---- the two BoW-gated searches on "side views" ---------------------------------------------------------------------
 // A side is what the engine reads of one KeyFrame / Frame.  The arrays that gate the search (FeatureVector, map-point
