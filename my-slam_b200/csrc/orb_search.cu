@@ -2381,10 +2381,12 @@ int orbgpu_kf_add(orbgpu_kfstore* st, const orbgpu_kf_data* k, int32_t* id)
     Workspace& W = g_ws;
     if ((rc = W.reserve(st->device, 0, L.off)) != ORBGPU_OK) return rc;
     memset(W.h, 0, L.off);
-    memcpy(W.h + s.o_keys, k->keys_un, sizeof(orbgpu_keypoint) * (size_t)n);
-    memcpy(W.h + s.o_desc, k->desc, 32 * (size_t)n);
-    memcpy(W.h + s.o_ur, s.u_right.data(), 4 * (size_t)n);
-    memcpy(W.h + s.o_idx, s.indices.data(), 4 * (size_t)nidx);
+    if (n > 0) {
+        memcpy(W.h + s.o_keys, k->keys_un, sizeof(orbgpu_keypoint) * (size_t)n);
+        memcpy(W.h + s.o_desc, k->desc, 32 * (size_t)n);
+        memcpy(W.h + s.o_ur, s.u_right.data(), 4 * (size_t)n);
+    }
+    if (nidx > 0) memcpy(W.h + s.o_idx, s.indices.data(), 4 * (size_t)nidx);
     if (k->scale_factors) memcpy(W.h + s.o_sc, k->scale_factors, 4 * (size_t)k->nlevels);     // (the block was zeroed above)
     if (k->level_sigma2) memcpy(W.h + s.o_sg, k->level_sigma2, 4 * (size_t)k->nlevels);
     {
