@@ -155,7 +155,9 @@ __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ row, int
     }
 }
 
-#define RS_SRC_ROWS 12        // source rows one strip of RS_ROWS output rows may touch on the shared-memory path
+#ifndef RS_SRC_ROWS
+#define RS_SRC_ROWS 12        // source rows one strip of RS_ROWS output rows may touch on the shared-memory path (a multiple of 6)
+#endif
 
 // s_h: this thread's private shared-memory column, rows STRIDE entries apart
 template <bool WORDS, bool NC, int STRIDE>
