@@ -20,6 +20,7 @@
 //                       a true sequential dependence in the reference, kept as such
 // The rotation histogram + ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) finish on the host, O(matches).
 #include <cuda_runtime.h>
+#include <limits.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -662,6 +663,93 @@ __global__ void __launch_bounds__(128) k_bow_fused(const BowQuery* __restrict__ 
             if (lane == 0) accepted[qb + j] = res;
         }
     }
+}
+
+// The ordinary case -- every shared node has at most BOW_NODE_CAP features of side 2 and at most BOW_NODE_QUERIES queries --
+// without any cross-lane reduction in the order-dependent part.  One CTA per node (its queries dealt to the warps 32 at a time):
+//   1. the node's features of side 2 are staged in shared memory; the distance of every (query, feature) pair goes into a
+//      shared-memory matrix, lane = query, the feature's descriptor read as a broadcast;
+//   2. the reference's in-order rule "a feature accepted by an earlier query is gone" is solved as a fixed point instead of
+//      a walk: every query (lane = query, all at once) takes its best / second best among the features that no EARLIER
+//      query currently takes and decides; then taken[p] = the lowest query index that takes p is rebuilt; repeat until no
+//      decision changes.  After round k the first k queries hold their final decision (query 0 is never blocked, and a
+//      query whose predecessors are final sees exactly the sequential state), so the loop ends after at most nq + 1 rounds
+//      and at a state in which every decision is consistent with all earlier ones -- the sequential result.  In practice a
+//      handful of rounds: a decision only changes when a predecessor took one of its two best features.
+// A round costs ~len shared-memory reads per lane and no shuffles; the warp-per-node walk above pays two warp reductions
+// and ~0.4 us per query, one query after the other.
+#define BOW_NODE_QUERIES 256
+#define BOW_DIST_ENTRIES (BOW_NODE_QUERIES * 32 + 3 * BOW_NODE_QUERIES + 64)   // nq * (len + 3) with nq * ceil(len / 32) <= 256
+
+#define BOW_ROUND_WARPS 4          // a node's queries are dealt to the warps 32 at a time; an ordinary node keeps one warp busy
+
+__global__ void __launch_bounds__(32 * BOW_ROUND_WARPS) k_bow_rounds(const BowQuery* __restrict__ Q, const int* __restrict__ gstart,
+                                                                     const uint8_t* __restrict__ desc1, const uint8_t* __restrict__ desc2,
+                                                                     const uint32_t* __restrict__ indices2, const uint8_t* __restrict__ valid2,
+                                                                     float nnratio, int th_low_excl, int* __restrict__ accepted)
+{
+    __shared__ uint4 s_lo[BOW_NODE_CAP], s_hi[BOW_NODE_CAP];
+    __shared__ uint32_t s_i2[BOW_NODE_CAP];
+    __shared__ int s_taken[BOW_NODE_CAP];                      // lowest query index that currently takes the feature; -1 = never free
+    __shared__ uint8_t s_valid[BOW_NODE_CAP];
+    __shared__ unsigned short s_dist[BOW_DIST_ENTRIES];
+    __shared__ short s_take[BOW_NODE_QUERIES];                 // list position the query currently takes, -1 = none
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = blockIdx.x;
+    const int q0 = gstart[g], nq = gstart[g + 1] - q0;
+    if (nq <= 0) return;
+    const int start = Q[q0].start, len = Q[q0].len;            // every query of a node searches the same list
+    int stride = (len + 1) & ~1;                               // row pitch of the distance matrix in 16-bit entries:
+    if (((stride >> 1) & 1) == 0) stride += 2;                 // an odd number of words, so lane = query is conflict-free
+    for (int p = tid; p < len; p += 32 * BOW_ROUND_WARPS) {
+        const uint32_t i2 = indices2[start + p];
+        s_i2[p] = i2;
+        s_lo[p] = __ldg(reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2);
+        s_hi[p] = __ldg(reinterpret_cast<const uint4*>(desc2) + 2 * (size_t)i2 + 1);
+        const uint8_t v = valid2[i2];
+        s_valid[p] = v;
+        s_taken[p] = v ? INT_MAX : -1;
+    }
+    __syncthreads();
+    for (int qb = 32 * warp; qb < nq; qb += 32 * BOW_ROUND_WARPS) {
+        const int q = qb + lane;
+        if (q < nq) {
+            const int idx1 = Q[q0 + q].idx1;
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)idx1);
+            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)idx1 + 1);
+            unsigned short* row = s_dist + q * stride;
+#pragma unroll 4
+            for (int p = 0; p < len; ++p) row[p] = (unsigned short)hamming_rr(a0, a1, s_lo[p], s_hi[p]);
+            s_take[q] = -1;
+        }
+    }
+    __syncthreads();
+    for (int round = 0; round <= nq; ++round) {
+        bool changed = false;
+        for (int qb = 32 * warp; qb < nq; qb += 32 * BOW_ROUND_WARPS) {
+            const int q = qb + lane;
+            if (q >= nq) continue;
+            const unsigned short* row = s_dist + q * stride;
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;       // (distance << 16) | list position: the earliest wins ties
+#pragma unroll 4
+            for (int p = 0; p < len; ++p) {
+                const unsigned key = s_taken[p] < q ? 0xFFFFFFFFu : (((unsigned)row[p] << 16) | (unsigned)p);
+                const unsigned hi = max(k1, key);              // keep the two smallest of {k1, k2, key}
+                k1 = min(k1, key); k2 = min(k2, hi);
+            }
+            const int bestDist1 = k1 == 0xFFFFFFFFu ? 256 : (int)(k1 >> 16);       // bestDist1 / bestDist2 start at 256 (:199-201)
+            const int bestDist2 = k2 == 0xFFFFFFFFu ? 256 : (int)(k2 >> 16);
+            const int take = (bestDist1 < th_low_excl && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) ? (int)(k1 & 0xFFFFu) : -1;
+            if (take != (int)s_take[q]) { s_take[q] = (short)take; changed = true; }
+        }
+        if (!__syncthreads_or(changed)) break;
+        for (int p = tid; p < len; p += 32 * BOW_ROUND_WARPS) s_taken[p] = s_valid[p] ? INT_MAX : -1;
+        __syncthreads();
+        for (int q = tid; q < nq; q += 32 * BOW_ROUND_WARPS)
+            if (s_take[q] >= 0) atomicMin(&s_taken[s_take[q]], q);
+        __syncthreads();
+    }
+    for (int q = tid; q < nq; q += 32 * BOW_ROUND_WARPS) accepted[q0 + q] = s_take[q] >= 0 ? (int)s_i2[s_take[q]] : -1;
 }
 
 // ---- Frame::isInFrustum (src/Frame.cc:269-325) ---------------------------------------------------------------------
@@ -2184,7 +2272,10 @@ static int bow_run(int device, const SideView& s1, const SideView& s2, float nnr
     CUS(cudaMemcpyAsync(W.d, W.h, std::max(in_bytes, SEARCH_MIN_UPLOAD), cudaMemcpyHostToDevice, W.st));
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (tr.on) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventRecord(ev0, W.st); }
-    if (fused) {
+    if (fused && cap <= BOW_NODE_CAP) {
+        k_bow_rounds<<<ngroups, 32 * BOW_ROUND_WARPS, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), reinterpret_cast<const int*>(W.d + o_g), d1, d2, i2,
+                                               W.d + o_v2, nnratio, strict_th_low ? 50 : 51, reinterpret_cast<int*>(W.d + o_acc));
+    } else if (fused) {
         k_bow_fused<<<(ngroups + 3) / 4, 128, 0, W.st>>>(reinterpret_cast<const BowQuery*>(W.d + o_q), reinterpret_cast<const int*>(W.d + o_g),
                                                           ngroups, d1, d2, i2, W.d + o_v2, nnratio, strict_th_low ? 50 : 51,
                                                           reinterpret_cast<int*>(W.d + o_acc));
@@ -2206,7 +2297,7 @@ static int bow_run(int device, const SideView& s1, const SideView& s2, float nnr
         float ms = 0.f;
         cudaEventElapsedTime(&ms, ev0, ev1);
         fprintf(stderr, "[orbgpu]   kernels %.1f us; nq %d groups %d longest list %d heaviest node %lld %s\n", ms * 1e3, nq, ngroups, cap,
-                heaviest, fused ? "one warp per node" : "two kernels");
+                heaviest, fused && cap <= BOW_NODE_CAP ? "fixed-point rounds" : fused ? "one warp per node" : "two kernels");
         cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     }
     const int* acc = reinterpret_cast<const int*>(W.h + o_acc);

@@ -151,6 +151,44 @@ def test_store_bookkeeping_and_errors(pkg, port):
     store.close()
 
 
+def test_search_by_bow_kernel_paths(pkg, port):
+    """The three device paths of SearchByBoW against the oracle: fixed-point rounds (ordinary vocabularies), one warp per
+    node with the features read from memory (a node of side 2 larger than the shared-memory slice, few queries), and the
+    two-kernel path (one node holding everything); heavy contention: many queries for few features, pooled descriptors."""
+    po = oracle_lib.OraclePort()
+    store = pkg.KeyFrameStore()
+    sc, sg = level_tables(port)
+    rng = np.random.default_rng(77)
+    pool = rng.integers(0, 256, (6, 32), dtype=np.uint8)
+
+    def near(n):                                                   # descriptors a few bits away from a small pool: many ties
+        d = pool[rng.integers(0, len(pool), n)].copy()
+        flips = rng.integers(0, 256, (n, 3))
+        for i in range(n):
+            for b in flips[i]:
+                d[i, b >> 3] ^= np.uint8(1 << (b & 7))
+        return d
+
+    def one_node(n, node=5):
+        return np.array([node], np.uint32), np.array([0, n], np.int32), rng.permutation(n).astype(np.uint32)
+    total = 0
+    for n1, n2 in [(3, 600), (200, 30), (64, 128), (256, 32), (7, 257), (900, 700)]:
+        k1, _ = random_frame(rng, n1, 640, 480, pool); k2, _ = random_frame(rng, n2, 640, 480, pool)
+        d1, d2 = near(n1), near(n2)
+        f1, f2 = one_node(n1), one_node(n2)
+        v1 = (rng.random(n1) < 0.9).astype(np.uint8); v2 = (rng.random(n2) < 0.9).astype(np.uint8)
+        s1, keep1 = pkg.bow_side(d1, v1, k1["angle"], *f1); s2, keep2 = pkg.bow_side(d2, v2, k2["angle"], *f2)
+        i1 = store.add(k1, d1, None, f1[0], f1[1], f1[2], sc, sg); i2 = store.add(k2, d2, None, f2[0], f2[1], f2[2], sc, sg)
+        for ratio, strict in [(0.9, True), (0.7, False), (1.5, True)]:
+            want = po.search_by_bow(s1, s2, ratio, True, strict)
+            got = store.search_by_bow(i1, v1, i2, v2, None, ratio, True, strict)
+            assert got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2]), (n1, n2, ratio)
+            plain = pkg.search_by_bow(s1, s2, ratio, True, strict)
+            assert plain[0] == want[0] and np.array_equal(plain[1], want[1])
+            total += want[0]
+    assert total > 100
+
+
 def test_many_keyframes_stay_intact_and_threads_can_share_the_store(pkg, port):
     """600 keyframes (two 32 MB slabs), a third erased and re-added in another order; searches from four threads."""
     store = pkg.KeyFrameStore()
