@@ -64,12 +64,20 @@ struct AreaQuery {                // one GetFeaturesInArea call + the descriptor
 
 __device__ __forceinline__ int key_octave(const float* keys, int i) { return __float_as_int(keys[7 * (size_t)i + 5]); }
 
+// Frame::AssignFeaturesToGrid (src/Frame.cc:230-245) as a counting sort by cell: one CTA; dynamic shared memory holds the
+// cell of every key and the keys in cell order (2 x 2 bytes x n).  Order inside a cell = index order (the push_back order of
+// the reference): keys are dropped into their cell's range in arrival order and every key then takes its place by its rank
+// among the keys of its own range -- shared-memory reads only, the same code for a cell of two keys and a cell of two hundred.
+#define GRID_BUILD_SMEM (4 * GRID_MAX_KEYS)
 __global__ void __launch_bounds__(1024) k_grid_build(GridDev G)
 {
-    __shared__ int s_cnt[GRID_CELLS];
-    __shared__ short s_cell[GRID_MAX_KEYS];
-    __shared__ int s_part[1024];
-    const int t = threadIdx.x;
+    extern __shared__ __align__(16) short grid_smem[];
+    __shared__ int s_cnt[GRID_CELLS];                          // counts, then the running end of every cell's range
+    __shared__ int s_start[GRID_CELLS];
+    __shared__ int s_warp[32];
+    short* s_cell = grid_smem;                                 // [n] cell of key i, -1 = outside the grid
+    short* s_sorted = grid_smem + G.n;                         // [n] keys in cell order
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     for (int c = t; c < GRID_CELLS; c += 1024) s_cnt[c] = 0;
     __syncthreads();
     for (int i = t; i < G.n; i += 1024) {
@@ -82,54 +90,38 @@ __global__ void __launch_bounds__(1024) k_grid_build(GridDev G)
         if (c >= 0) atomicAdd(&s_cnt[c], 1);
     }
     __syncthreads();
-    // exclusive scan of 3072 counts: 3 per thread
+    // exclusive scan of the 3072 counts: 3 per thread, a shuffle scan per warp and one over the warp totals
     const int c0 = s_cnt[3 * t], c1 = s_cnt[3 * t + 1], c2 = s_cnt[3 * t + 2];
-    s_part[t] = c0 + c1 + c2;
+    int incl = c0 + c1 + c2;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += u; }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    for (int s = 1; s < 1024; s <<= 1) {
-        const int v = t >= s ? s_part[t - s] : 0;
-        __syncthreads();
-        s_part[t] += v;
-        __syncthreads();
+    if (warp == 0) {
+        int w = s_warp[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += u; }
+        s_warp[lane] = w;
     }
-    const int base = s_part[t] - (c0 + c1 + c2);
-    s_cnt[3 * t] = base; s_cnt[3 * t + 1] = base + c0; s_cnt[3 * t + 2] = base + c0 + c1;
-    G.cell_start[3 * t] = base; G.cell_start[3 * t + 1] = base + c0; G.cell_start[3 * t + 2] = base + c0 + c1;
-    if (t == 1023) G.cell_start[GRID_CELLS] = s_part[1023];
     __syncthreads();
-    // Order inside a cell = index order (the push_back order of AssignFeaturesToGrid).  Keys are dropped into their
-    // cell's range in arrival order, then every short range is put in index order by one thread; a range too long for
-    // that takes, per key, its rank = number of earlier keys of the same cell.
+    const int base = (warp ? s_warp[warp - 1] : 0) + incl - (c0 + c1 + c2);
+    const int total = s_warp[31];
+    s_cnt[3 * t] = base; s_cnt[3 * t + 1] = base + c0; s_cnt[3 * t + 2] = base + c0 + c1;
+    s_start[3 * t] = base; s_start[3 * t + 1] = base + c0; s_start[3 * t + 2] = base + c0 + c1;
+    G.cell_start[3 * t] = base; G.cell_start[3 * t + 1] = base + c0; G.cell_start[3 * t + 2] = base + c0 + c1;
+    if (t == 1023) G.cell_start[GRID_CELLS] = total;
+    __syncthreads();
     for (int i = t; i < G.n; i += 1024) {
         const int c = s_cell[i];
-        if (c >= 0) G.sorted[atomicAdd(&s_cnt[c], 1)] = i;       // s_cnt[c] runs from the cell's start to its end
+        if (c >= 0) s_sorted[atomicAdd(&s_cnt[c], 1)] = (short)i;     // s_cnt[c] runs from the cell's start to its end
     }
     __syncthreads();
-    const int len3[3] = {c0, c1, c2};
-    bool any_long = false;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int len = len3[k], start = s_cnt[3 * t + k] - len;
-        if (len < 2) continue;
-        if (len > 48) { any_long = true; continue; }
-        int* a = G.sorted + start;
-        for (int x = 1; x < len; ++x) {                          // insertion sort of a handful of indices
-            const int v = a[x];
-            int y = x - 1;
-            for (; y >= 0 && a[y] > v; --y) a[y + 1] = a[y];
-            a[y + 1] = v;
-        }
-    }
-    if (__syncthreads_or(any_long)) {
-        for (int i = t; i < G.n; i += 1024) {
-            const int c = s_cell[i];
-            if (c < 0) continue;
-            const int end = s_cnt[c], start = G.cell_start[c];
-            if (end - start <= 48) continue;
-            int rank = 0;
-            for (int j = 0; j < i; ++j) rank += s_cell[j] == c;
-            G.sorted[start + rank] = i;
-        }
+    for (int k = t; k < total; k += 1024) {
+        const int v = s_sorted[k], c = s_cell[v];
+        const int start = s_start[c], end = s_cnt[c];
+        int rank = 0;
+        for (int j = start; j < end; ++j) rank += s_sorted[j] < v;
+        G.sorted[start + rank] = v;
     }
 }
 
@@ -162,12 +154,27 @@ __global__ void __launch_bounds__(256) k_area_candidates(GridDev G, const AreaQu
             const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(qdesc) + 2 * (size_t)q);
             const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(qdesc) + 2 * (size_t)q + 1);
             uint32_t* out = cand + (size_t)q * cap;
-            for (int ix = nMinCellX; ix <= nMaxCellX; ++ix) {
-                if (nMinCellY > nMaxCellY) break;
-                const int p0 = G.cell_start[ix * GRID_ROWS + nMinCellY], p1 = G.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
-                for (int pb = p0; pb < p1; pb += 32) {
-                    const int p = pb + lane;
-                    bool ok = p < p1;
+            // the window's columns (a column of cells is one contiguous range of the sorted keys), 32 at a time: lane = column
+            // loads its range, a shuffle scan lays the ranges end to end, and the lanes then walk the concatenation -- one chain
+            // of dependent loads (range -> key index -> key, descriptor) for the whole window instead of one per column
+            for (int cb = nMinCellX; cb <= nMaxCellX && nMinCellY <= nMaxCellY; cb += 32) {
+                const int ncols = min(32, nMaxCellX - cb + 1);
+                int p0 = 0, len = 0;
+                if (lane < ncols) {
+                    p0 = G.cell_start[(cb + lane) * GRID_ROWS + nMinCellY];
+                    len = G.cell_start[(cb + lane) * GRID_ROWS + nMaxCellY + 1] - p0;
+                }
+                int incl = len;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += u; }
+                const int all = __shfl_sync(0xffffffffu, incl, 31);
+                for (int base = 0; base < all; base += 32) {
+                    const int idx = base + lane;
+                    int col = 0;
+                    for (int c = 0; c + 1 < ncols; ++c) col += idx >= __shfl_sync(0xffffffffu, incl, c);
+                    const int cp0 = __shfl_sync(0xffffffffu, p0, col), cin = __shfl_sync(0xffffffffu, incl, col), cl = __shfl_sync(0xffffffffu, len, col);
+                    const int p = cp0 + idx - (cin - cl);
+                    bool ok = idx < all;
                     int i2 = 0;
                     if (ok) {
                         i2 = G.sorted[p];
@@ -215,31 +222,36 @@ struct ResolveStage {
 __device__ ResolveStage stage_lists(unsigned char* smem, size_t used, const uint32_t* __restrict__ cand, const int* __restrict__ cand_n,
                                     int cap, int nq)
 {
-    __shared__ int s_part[RESOLVE_THREADS];
+    __shared__ int s_warp[RESOLVE_THREADS / 32];
     __shared__ int s_total;
-    const int t = threadIdx.x;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     ResolveStage S;
     S.off = reinterpret_cast<int*>(smem + used); used += sizeof(int) * (size_t)nq;
     S.cnt = reinterpret_cast<unsigned short*>(smem + used); used += sizeof(unsigned short) * (size_t)nq;
     used = (used + 15) & ~(size_t)15;
     uint32_t* s_cand = reinterpret_cast<uint32_t*>(smem + used);
     const int room = (int)((RESOLVE_SMEM - used) / sizeof(uint32_t));
+    // exclusive prefix of the list lengths: `per` consecutive queries per thread, then one shuffle scan per warp and one
+    // over the warp totals (three barriers)
     const int per = (nq + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
     const int q0 = min(t * per, nq), q1 = min(q0 + per, nq);
     int sum = 0;
     for (int q = q0; q < q1; ++q) sum += cand_n[q];
-    s_part[t] = sum;
+    int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += u; }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    for (int s = 1; s < RESOLVE_THREADS; s <<= 1) {
-        const int v = t >= s ? s_part[t - s] : 0;
-        __syncthreads();
-        s_part[t] += v;
-        __syncthreads();
+    if (warp == 0) {
+        int w = s_warp[lane];                                  // RESOLVE_THREADS / 32 == 32 warp totals
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += u; }
+        s_warp[lane] = w;
+        if (lane == 31) s_total = w;
     }
-    if (t == RESOLVE_THREADS - 1) s_total = s_part[t];
     __syncthreads();
     const bool fits = s_total <= room;
-    int run = s_part[t] - sum;
+    int run = (warp ? s_warp[warp - 1] : 0) + incl - sum;
     for (int q = q0; q < q1; ++q) {
         const int c = cand_n[q];
         S.off[q] = fits ? run : q * cap;
@@ -248,11 +260,14 @@ __device__ ResolveStage stage_lists(unsigned char* smem, size_t used, const uint
     }
     __syncthreads();
     if (fits) {
-        const int warp = t >> 5, lane = t & 31;
-        for (int q = warp; q < nq; q += RESOLVE_THREADS / 32) {
-            const int c = S.cnt[q], o = S.off[q];
+        // one thread per query: its loads are independent of each other, so a list costs one memory round trip, and all
+        // lists are in flight at once (a warp per list walked 1/32 of the queries one dependent round trip after the other)
+        for (int q = t; q < nq; q += RESOLVE_THREADS) {
+            const int c = S.cnt[q];
+            uint32_t* dst = s_cand + S.off[q];
             const uint32_t* src = cand + (size_t)q * cap;
-            for (int p = lane; p < c; p += 32) s_cand[o + p] = src[p];
+#pragma unroll 4
+            for (int p = 0; p < c; ++p) dst[p] = src[p];
         }
     }
     S.base = fits ? s_cand : cand;
@@ -382,6 +397,19 @@ __global__ void k_proj_queries(ProjCam C, const float* __restrict__ world_pos, c
     Q[i] = q;
 }
 
+// ---- the in-order rule as a fixed point ----------------------------------------------------------------------------
+// SearchByProjection visits its queries in index order because an accepted match occupies its feature for every later
+// query (mvpMapPoints[i2] with Observations() > 0).  Instead of walking the queries, the two kernels below iterate: every
+// query at once (one thread per query, the whole CTA) scans its candidate list for the best (and second best) feature
+// that is neither occupied from the start nor currently taken by an EARLIER blocking query, and decides; taken[f] = the
+// lowest index of a blocking query that takes f is rebuilt with shared-memory atomicMin; repeat until no decision
+// changes.  After round k the first k queries hold their final decision (query 0 is never blocked, and a query whose
+// predecessors are final sees exactly the sequential state), so the loop stops after at most n + 1 rounds in a state where
+// every decision is consistent with all earlier ones: the sequential result.  Decisions only change when a predecessor
+// took one of the query's best features, so real scenes need a handful of rounds, each a parallel scan -- against one
+// dependent pass per 1..32 queries for the speculative walk this replaces (k_init_resolve above still walks: there a
+// feature's state is a distance that falls with every new owner, not a flag).
+
 // the loop over the last frame's points (src/ORBmatcher.cc:1353-1443) on the candidate lists
 __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t* __restrict__ cand, const int* __restrict__ cand_n, int cap,
                                                                   int n_last, int n_cur, const uint8_t* __restrict__ observed,
@@ -390,50 +418,49 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_proj_resolve(const uint32_t
                                                                   int* __restrict__ nmatches_out)
 {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_count;
     const int t = threadIdx.x;
-    unsigned char* taker = smem;
-    unsigned char* occupied = smem + (size_t)n_cur;            // mvpMapPoints[i2] && Observations() > 0
-    unsigned char* obs = smem + 2 * (size_t)n_cur;
-    for (int i = t; i < n_cur; i += RESOLVE_THREADS) { taker[i] = TAKER_NONE; occupied[i] = occupied_in[i]; cur_match[i] = -1; }
-    for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed ? observed[i] : 1; accepted[i] = -1; }
-    const size_t used = (2 * (size_t)n_cur + (size_t)n_last + 15) & ~(size_t)15;
+    int* taken = reinterpret_cast<int*>(smem);                 // lowest blocking query that takes the feature; -1 = occupied from the start
+    unsigned char* occ0 = smem + 4 * (size_t)n_cur;            // mvpMapPoints[i2] && Observations() > 0 on entry (:1403-1405)
+    unsigned char* obs = occ0 + (size_t)n_cur;
+    size_t used = (5 * (size_t)n_cur + (size_t)n_last + 1) & ~(size_t)1;
+    short* take = reinterpret_cast<short*>(smem + used);       // feature the query currently takes, -1 = none
+    used = (used + 2 * (size_t)n_last + 15) & ~(size_t)15;
+    for (int i = t; i < n_cur; i += RESOLVE_THREADS) { const unsigned char o = occupied_in[i]; occ0[i] = o; taken[i] = o ? -1 : INT_MAX; cur_match[i] = -1; }
+    for (int i = t; i < n_last; i += RESOLVE_THREADS) { obs[i] = observed ? observed[i] : 1; take[i] = -1; }
+    if (t == 0) s_count = 0;
     const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_last);
-    if (t >= 32) return;
-    const int lane = t;
-    int nmatches = 0;
-    for (int qb = 0; qb < n_last;) {
-        const int i = qb + lane;
-        const int cnt = i < n_last ? S.cnt[i] : 0;
-        const uint32_t* c = S.base + (i < n_last ? S.off[i] : 0);
-        unsigned best = 0xFFFFFFFFu;
-        for (int p = 0; p < cnt; ++p) {
-            const uint32_t e = c[p];
-            if (occupied[e >> CAND_DIST_BITS]) continue;       // :1403-1405
-            best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
+    for (int round = 0; round <= n_last; ++round) {
+        bool changed = false;
+        for (int i = t; i < n_last; i += RESOLVE_THREADS) {
+            const int cnt = S.cnt[i];
+            const uint32_t* c = S.base + S.off[i];
+            unsigned best = 0xFFFFFFFFu;                       // (distance << 16) | list position: the earliest wins ties
+            for (int p = 0; p < cnt; ++p) {
+                const uint32_t e = c[p];
+                if (taken[e >> CAND_DIST_BITS] < i) continue;
+                best = min(best, ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p);
+            }
+            int tk = -1;                                       // bestDist < 256 by construction; max_dist = TH_HIGH or ORBdist
+            if (best != 0xFFFFFFFFu && (int)(best >> 16) <= max_dist) tk = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
+            if (tk != (int)take[i]) { take[i] = (short)tk; changed = true; }
         }
-        int take = -1;                                         // bestDist < 256 by construction; max_dist = TH_HIGH or ORBdist
-        if (best != 0xFFFFFFFFu && (int)(best >> 16) <= max_dist) take = (int)(c[best & 0xFFFFu] >> CAND_DIST_BITS);
-        const bool blocks = take >= 0 && obs[i];               // an unobserved point leaves the feature free (:1431)
-        const unsigned blockers = __ballot_sync(0xffffffffu, blocks);
-        int ncommit = 32;
-        if (blockers) {                                        // later lanes may have decided on stale state
-            post_taker(taker, blocks, take, lane);
-            const bool invalid = take >= 0 && taker[take] < lane;     // no second best here: only the best can go stale
-            const unsigned inv = __ballot_sync(0xffffffffu, invalid);
-            if (inv) ncommit = __ffs(inv) - 1;
-            if (blocks) taker[take] = TAKER_NONE;
-        }
-        const bool commit = take >= 0 && lane < ncommit;
-        if (commit) {
-            atomicMax(&cur_match[take], i);                    // the last point in index order keeps the feature
-            if (blocks) occupied[take] = 1;
-            accepted[i] = take;
-        }
-        nmatches += __popc(__ballot_sync(0xffffffffu, commit));
-        __syncwarp();
-        qb += ncommit;
+        if (!__syncthreads_or(changed)) break;
+        for (int f = t; f < n_cur; f += RESOLVE_THREADS) taken[f] = occ0[f] ? -1 : INT_MAX;
+        __syncthreads();
+        for (int i = t; i < n_last; i += RESOLVE_THREADS)
+            if (take[i] >= 0 && obs[i]) atomicMin(&taken[take[i]], i);          // an unobserved point leaves the feature free (:1431)
+        __syncthreads();
     }
-    if (lane == 0) *nmatches_out = nmatches;
+    int mine = 0;
+    for (int i = t; i < n_last; i += RESOLVE_THREADS) {
+        const int tk = take[i];
+        accepted[i] = tk;
+        if (tk >= 0) { atomicMax(&cur_match[tk], i); ++mine; }                  // the last point in index order keeps the feature
+    }
+    if (mine) atomicAdd(&s_count, mine);
+    __syncthreads();
+    if (t == 0) *nmatches_out = s_count;
 }
 
 // SearchByProjection(Frame, vector<MapPoint*>): the loop over the local map points (src/ORBmatcher.cc:50-122) on the
@@ -445,61 +472,59 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_local_resolve(const uint32_
                                                                    float nnratio, int* __restrict__ cur_match, int* __restrict__ nmatches_out)
 {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_count;
     const int t = threadIdx.x;
-    unsigned char* taker = smem;
-    unsigned char* occupied = smem + (size_t)n_cur;            // F.mvpMapPoints[idx] && Observations() > 0 (:89-91)
-    unsigned char* oct = smem + 2 * (size_t)n_cur;             // F.mvKeysUn[idx].octave
-    unsigned char* obs = smem + 3 * (size_t)n_cur;
+    int* taken = reinterpret_cast<int*>(smem);                 // lowest blocking point that takes the feature; -1 = occupied from the start
+    unsigned char* occ0 = smem + 4 * (size_t)n_cur;            // F.mvpMapPoints[idx] && Observations() > 0 on entry (:89-91)
+    unsigned char* oct = occ0 + (size_t)n_cur;                 // F.mvKeysUn[idx].octave
+    unsigned char* obs = oct + (size_t)n_cur;
+    size_t used = (6 * (size_t)n_cur + (size_t)n_points + 1) & ~(size_t)1;
+    short* take = reinterpret_cast<short*>(smem + used);       // feature the point currently takes, -1 = none
+    used = (used + 2 * (size_t)n_points + 15) & ~(size_t)15;
     for (int i = t; i < n_cur; i += RESOLVE_THREADS) {
-        taker[i] = TAKER_NONE; occupied[i] = occupied_in[i]; oct[i] = (unsigned char)key_octave(keys, i); cur_match[i] = -1;
+        const unsigned char o = occupied_in[i];
+        occ0[i] = o; taken[i] = o ? -1 : INT_MAX; oct[i] = (unsigned char)key_octave(keys, i); cur_match[i] = -1;
     }
-    for (int i = t; i < n_points; i += RESOLVE_THREADS) obs[i] = observed[i];
-    const size_t used = (3 * (size_t)n_cur + (size_t)n_points + 15) & ~(size_t)15;
+    for (int i = t; i < n_points; i += RESOLVE_THREADS) { obs[i] = observed[i]; take[i] = -1; }
+    if (t == 0) s_count = 0;
     const ResolveStage S = stage_lists(smem, used, cand, cand_n, cap, n_points);
-    if (t >= 32) return;
-    const int lane = t;
-    int nmatches = 0;
-    for (int qb = 0; qb < n_points;) {
-        const int i = qb + lane;
-        const int cnt = i < n_points ? S.cnt[i] : 0;
-        const uint32_t* c = S.base + (i < n_points ? S.off[i] : 0);
-        unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
-        for (int p = 0; p < cnt; ++p) {
-            const uint32_t e = c[p];
-            if (occupied[e >> CAND_DIST_BITS]) continue;
-            const unsigned key = ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p;
-            if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+    for (int round = 0; round <= n_points; ++round) {          // the fixed point of the in-order rule, see k_proj_resolve
+        bool changed = false;
+        for (int i = t; i < n_points; i += RESOLVE_THREADS) {
+            const int cnt = S.cnt[i];
+            const uint32_t* c = S.base + S.off[i];
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
+            for (int p = 0; p < cnt; ++p) {
+                const uint32_t e = c[p];
+                if (taken[e >> CAND_DIST_BITS] < i) continue;
+                const unsigned key = ((e & ((1u << CAND_DIST_BITS) - 1u)) << 16) | (unsigned)p;
+                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+            }
+            int tk = -1;
+            if (k1 != 0xFFFFFFFFu && (int)(k1 >> 16) <= 100) { // TH_HIGH (:113); a distance of 256 never replaces the initial 256
+                const int bestDist = (int)(k1 >> 16);
+                const int bestIdx = (int)(c[k1 & 0xFFFFu] >> CAND_DIST_BITS);
+                int bestDist2 = 256, bestLevel2 = -1;
+                if (k2 != 0xFFFFFFFFu && (int)(k2 >> 16) < 256) { bestDist2 = (int)(k2 >> 16); bestLevel2 = oct[c[k2 & 0xFFFFu] >> CAND_DIST_BITS]; }
+                if (!((int)oct[bestIdx] == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2))) tk = bestIdx;    // :115-116
+            }
+            if (tk != (int)take[i]) { take[i] = (short)tk; changed = true; }
         }
-        int take = -1;
-        if (k1 != 0xFFFFFFFFu && (int)(k1 >> 16) <= 100) {     // TH_HIGH (:113); a distance of 256 never replaces the initial 256
-            const int bestDist = (int)(k1 >> 16);
-            const int bestIdx = (int)(c[k1 & 0xFFFFu] >> CAND_DIST_BITS);
-            int bestDist2 = 256, bestLevel2 = -1;
-            if (k2 != 0xFFFFFFFFu && (int)(k2 >> 16) < 256) { bestDist2 = (int)(k2 >> 16); bestLevel2 = oct[c[k2 & 0xFFFFu] >> CAND_DIST_BITS]; }
-            if (!((int)oct[bestIdx] == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2))) take = bestIdx;    // :115-116
-        }
-        const bool blocks = take >= 0 && obs[i];               // an unobserved point does not reserve its feature (:89-91)
-        const unsigned blockers = __ballot_sync(0xffffffffu, blocks);
-        int ncommit = 32;
-        if (blockers) {                                        // later lanes may have decided on stale state
-            post_taker(taker, blocks, take, lane);
-            bool invalid = false;
-            if (k1 != 0xFFFFFFFFu) invalid = taker[c[k1 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
-            if (k2 != 0xFFFFFFFFu) invalid = invalid || taker[c[k2 & 0xFFFFu] >> CAND_DIST_BITS] < lane;
-            const unsigned inv = __ballot_sync(0xffffffffu, invalid);
-            if (inv) ncommit = __ffs(inv) - 1;
-            if (blocks) taker[take] = TAKER_NONE;
-        }
-        const bool commit = take >= 0 && lane < ncommit;
-        if (commit) {
-            atomicMax(&cur_match[take], i);                    // the last point in index order keeps the feature
-            if (blocks) occupied[take] = 1;
-        }
-        nmatches += __popc(__ballot_sync(0xffffffffu, commit));
-        __syncwarp();
-        qb += ncommit;
+        if (!__syncthreads_or(changed)) break;
+        for (int f = t; f < n_cur; f += RESOLVE_THREADS) taken[f] = occ0[f] ? -1 : INT_MAX;
+        __syncthreads();
+        for (int i = t; i < n_points; i += RESOLVE_THREADS)
+            if (take[i] >= 0 && obs[i]) atomicMin(&taken[take[i]], i);          // an unobserved point does not reserve its feature (:89-91)
+        __syncthreads();
     }
-    if (lane == 0) *nmatches_out = nmatches;
+    int mine = 0;
+    for (int i = t; i < n_points; i += RESOLVE_THREADS) {
+        const int tk = take[i];
+        if (tk >= 0) { atomicMax(&cur_match[tk], i); ++mine; }                  // the last point in index order keeps the feature
+    }
+    if (mine) atomicAdd(&s_count, mine);
+    __syncthreads();
+    if (t == 0) *nmatches_out = s_count;
 }
 
 // ---- SearchByBoW (src/ORBmatcher.cc:159-288, :522-655) -----------------------------------------------------------
@@ -1135,6 +1160,7 @@ struct Workspace {
         }
         if (!st) CUS(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         if (!attr_set) {
+            CUS(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_BUILD_SMEM));
             CUS(cudaFuncSetAttribute(k_init_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
@@ -1290,7 +1316,7 @@ int orbgpu_search_for_initialization(int device, const orbgpu_keypoint* keys1_un
     set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, bounds4);
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
-    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
     k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, reinterpret_cast<const AreaQuery*>(W.d + o_q), W.d + o_qdesc, n1, nullptr, d_cand,
                                                       n2, d_cn);
     k_init_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, nnratio, reinterpret_cast<int*>(W.d + o_m12),
@@ -1385,7 +1411,7 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
     AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
-    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
     dt.mark("grid");
     k_proj_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
                                                        reinterpret_cast<const int*>(W.d + o_oct), reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
@@ -1474,7 +1500,7 @@ int orbgpu_search_local_points(int device, const orbgpu_local_points_args* a, in
     set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
-    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
     k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, reinterpret_cast<const AreaQuery*>(W.d + o_q), W.d + o_qdesc, n1,
                                                       reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
     k_local_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, G.keys, a->nnratio,
@@ -1569,7 +1595,7 @@ int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const or
         uint32_t* d_cl = reinterpret_cast<uint32_t*>(W.d + o_cl);
         int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
         dt.mark("frustum");
-        k_grid_build<<<1, 1024, 0, W.st>>>(G);
+        k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
         dt.mark("grid");
         k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cl, n2, d_cn);
         dt.mark("candidates");
@@ -1684,7 +1710,7 @@ static int fuse_run(int device, const orbgpu_fuse_args* a, FuseCam C, int chi2_g
     G.winX = C.minX; G.winY = C.minY;                          // src/KeyFrame.cc:574-586 subtract the int members
     FuseQuery* d_q = reinterpret_cast<FuseQuery*>(D + o_q);
     AreaQuery* d_aq = occupied ? reinterpret_cast<AreaQuery*>(D + o_aq) : nullptr;
-    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
     k_fuse_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, D + o_pres, reinterpret_cast<const float*>(D + o_pos), reinterpret_cast<const float*>(D + o_nrm),
                                                        reinterpret_cast<const float*>(D + o_maxd), reinterpret_cast<const float*>(D + o_mind),
                                                        reinterpret_cast<const float*>(D + o_scale), n1, d_q, d_aq);
@@ -1899,7 +1925,7 @@ int orbgpu_search_by_projection_keyframe(int device, const orbgpu_reloc_projecti
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
     AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
-    k_grid_build<<<1, 1024, 0, W.st>>>(G);
+    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
     k_reloc_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_valid, reinterpret_cast<const float*>(W.d + o_pos),
                                                         reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
                                                         reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
