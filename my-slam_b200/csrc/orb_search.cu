@@ -69,7 +69,7 @@ __device__ __forceinline__ int key_octave(const float* keys, int i) { return __f
 // the reference): keys are dropped into their cell's range in arrival order and every key then takes its place by its rank
 // among the keys of its own range -- shared-memory reads only, the same code for a cell of two keys and a cell of two hundred.
 #define GRID_BUILD_SMEM (4 * GRID_MAX_KEYS)
-__global__ void __launch_bounds__(1024) k_grid_build(GridDev G)
+__device__ __forceinline__ void grid_build_cta(const GridDev& G)      // one CTA of 1024 threads, 4 * G.n bytes of dynamic shared memory
 {
     extern __shared__ __align__(16) short grid_smem[];
     __shared__ int s_cnt[GRID_CELLS];                          // counts, then the running end of every cell's range
@@ -124,6 +124,14 @@ __global__ void __launch_bounds__(1024) k_grid_build(GridDev G)
         G.sorted[start + rank] = v;
     }
 }
+
+__global__ void __launch_bounds__(1024) k_grid_build(GridDev G) { grid_build_cta(G); }
+
+// The kernels that turn map points into window queries do not depend on the grid of the searched frame: launched with
+// 1024-thread blocks and one block more than the queries need, that last block builds the grid (one launch and one kernel
+// boundary less per call).
+#define GRID_RIDER_BLOCK(G)                                              \
+    if (blockIdx.x == gridDim.x - 1) { grid_build_cta(G); return; }
 
 __device__ __forceinline__ int hamming_regs(const uint4& a0, const uint4& a1, const uint4* __restrict__ b)
 {
@@ -364,9 +372,11 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_init_resolve(const uint32_t
 // SearchByProjection(Frame, Frame): projection of the last frame's map points (src/ORBmatcher.cc:1361-1391)
 struct ProjCam { float R[9], t[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, th; int forward, backward; };
 
-__global__ void k_proj_queries(ProjCam C, const float* __restrict__ world_pos, const uint8_t* __restrict__ valid,
-                               const int* __restrict__ last_octave, const float* __restrict__ scale, int n, AreaQuery* __restrict__ Q)
+__global__ void __launch_bounds__(1024) k_proj_queries(ProjCam C, const float* __restrict__ world_pos, const uint8_t* __restrict__ valid,
+                                                       const int* __restrict__ last_octave, const float* __restrict__ scale, int n,
+                                                       AreaQuery* __restrict__ Q, GridDev G)
 {
+    GRID_RIDER_BLOCK(G)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     AreaQuery q;
@@ -824,10 +834,12 @@ __global__ void k_debug_logf(const float* __restrict__ x, int n, float* __restri
 struct FrustumCam { float R[9], t[3], Ow[3], fx, fy, cx, cy, bf, minX, maxX, minY, maxY, cos_limit, log_scale, th; int nlevels; };
 struct TrackOut { uint8_t* in_view; float *proj_x, *proj_y, *proj_xr, *view_cos; int* scale_level; };
 
-__global__ void k_frustum(FrustumCam C, const uint8_t* __restrict__ candidate, const float* __restrict__ world_pos,
-                          const float* __restrict__ normal, const float* __restrict__ max_distance, const float* __restrict__ min_distance,
-                          const float* __restrict__ scale, int n, TrackOut T, AreaQuery* __restrict__ Q, int* __restrict__ n_in_view)
+__global__ void __launch_bounds__(1024) k_frustum(FrustumCam C, const uint8_t* __restrict__ candidate, const float* __restrict__ world_pos,
+                                                  const float* __restrict__ normal, const float* __restrict__ max_distance,
+                                                  const float* __restrict__ min_distance, const float* __restrict__ scale, int n, TrackOut T,
+                                                  AreaQuery* __restrict__ Q, int* __restrict__ n_in_view, GridDev G, int with_grid)
 {
+    if (with_grid) { GRID_RIDER_BLOCK(G) }
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool in = false;
     if (i < n) {
@@ -1161,6 +1173,8 @@ struct Workspace {
         if (!st) CUS(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         if (!attr_set) {
             CUS(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_BUILD_SMEM));
+            CUS(cudaFuncSetAttribute(k_proj_queries, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_BUILD_SMEM));
+            CUS(cudaFuncSetAttribute(k_frustum, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_BUILD_SMEM));
             CUS(cudaFuncSetAttribute(k_init_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_proj_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
             CUS(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, RESOLVE_SMEM));
@@ -1411,11 +1425,11 @@ int orbgpu_search_by_projection(int device, const orbgpu_projection_args* a, int
     uint32_t* d_cand = reinterpret_cast<uint32_t*>(W.d + o_cand);
     int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
     AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
-    k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
-    dt.mark("grid");
-    k_proj_queries<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
-                                                       reinterpret_cast<const int*>(W.d + o_oct), reinterpret_cast<const float*>(W.d + o_scale), n1, d_q);
-    dt.mark("queries");
+    // the queries and, in one block more, the grid of the current frame
+    k_proj_queries<<<(n1 + 1023) / 1024 + 1, 1024, 4 * (size_t)G.n, W.st>>>(C, reinterpret_cast<const float*>(W.d + o_pos), W.d + o_valid,
+                                                                             reinterpret_cast<const int*>(W.d + o_oct),
+                                                                             reinterpret_cast<const float*>(W.d + o_scale), n1, d_q, G);
+    dt.mark("grid+queries");
     k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cand, n2, d_cn);
     dt.mark("candidates");
     k_proj_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cand, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, 100, reinterpret_cast<int*>(W.d + o_cm),
@@ -1586,17 +1600,18 @@ int orbgpu_search_local_map(int device, const orbgpu_local_map_args* a, const or
     T.scale_level = reinterpret_cast<int*>(W.d + o_lvl);
     AreaQuery* d_q = reinterpret_cast<AreaQuery*>(W.d + o_q);
     int* d_nm = reinterpret_cast<int*>(W.d + o_nm);
-    k_frustum<<<(n1 + 127) / 128, 128, 0, W.st>>>(C, W.d + o_cand, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
-                                                  reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
-                                                  reinterpret_cast<const float*>(W.d + o_scale), n1, T, d_q, d_nm + 1);
+    GridDev G;
+    memset(&G, 0, sizeof(G));
+    if (n2) set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
+    // isInFrustum for every point and, in one block more, the grid of the frame (when there is a frame to search)
+    k_frustum<<<(n1 + 1023) / 1024 + (n2 ? 1 : 0), 1024, 4 * (size_t)n2, W.st>>>(
+        C, W.d + o_cand, reinterpret_cast<const float*>(W.d + o_pos), reinterpret_cast<const float*>(W.d + o_nrm),
+        reinterpret_cast<const float*>(W.d + o_maxd), reinterpret_cast<const float*>(W.d + o_mind),
+        reinterpret_cast<const float*>(W.d + o_scale), n1, T, d_q, d_nm + 1, G, n2 ? 1 : 0);
     if (n2) {
-        GridDev G;
-        set_grid(G, W.d, o_keys, o_desc, o_start, o_sorted, n2, a->bounds);
         uint32_t* d_cl = reinterpret_cast<uint32_t*>(W.d + o_cl);
         int* d_cn = reinterpret_cast<int*>(W.d + o_cn);
-        dt.mark("frustum");
-        k_grid_build<<<1, 1024, 4 * (size_t)G.n, W.st>>>(G);
-        dt.mark("grid");
+        dt.mark("frustum+grid");
         k_area_candidates<<<(n1 + 7) / 8, 256, 0, W.st>>>(G, d_q, W.d + o_qdesc, n1, reinterpret_cast<const float*>(W.d + o_ur), d_cl, n2, d_cn);
         dt.mark("candidates");
         k_local_resolve<<<1, RESOLVE_THREADS, RESOLVE_SMEM, W.st>>>(d_cl, d_cn, n2, n1, n2, W.d + o_obs, W.d + o_occ, G.keys, a->nnratio,
