@@ -1096,16 +1096,28 @@ __global__ void k_reloc_queries(RelocCam C, const uint8_t* __restrict__ valid, c
 // reference's running test is "dist > bestDist -> skip" (:734).
 struct TriCam { float F[9]; float ex, ey; int only_stereo; };
 
-__global__ void __launch_bounds__(256) k_tri_match(const BowQuery* __restrict__ Q, int nq, TriCam C, const float* __restrict__ keys1,
-                                                   const uint8_t* __restrict__ desc1, const float* __restrict__ ur1,
-                                                   const float* __restrict__ keys2, const uint8_t* __restrict__ desc2,
-                                                   const float* __restrict__ ur2, const uint8_t* __restrict__ has_mp2,
-                                                   const uint32_t* __restrict__ indices2, const float* __restrict__ scale2,
-                                                   const float* __restrict__ sigma2, int* __restrict__ result)
+// one entry per keyframe pair; the table travels with the inputs, blockIdx.y picks the pair: the neighbours of
+// CreateNewMapPoints are one launch
+struct TriJobDev {
+    const BowQuery* Q; int nq; TriCam C;
+    const float* keys1; const uint8_t* desc1; const float* ur1;
+    const float* keys2; const uint8_t* desc2; const float* ur2; const uint8_t* has_mp2; const uint32_t* indices2;
+    const float* scale2; const float* sigma2; int* result;
+};
+
+__global__ void __launch_bounds__(256) k_tri_match(const TriJobDev* __restrict__ jobs)
 {
+    const TriJobDev& J = jobs[blockIdx.y];
     const int lane = threadIdx.x & 31;
     const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int nq = J.nq;
     if (q >= nq) return;
+    const BowQuery* __restrict__ Q = J.Q;
+    const TriCam C = J.C;
+    const float* __restrict__ keys1 = J.keys1; const uint8_t* __restrict__ desc1 = J.desc1; const float* __restrict__ ur1 = J.ur1;
+    const float* __restrict__ keys2 = J.keys2; const uint8_t* __restrict__ desc2 = J.desc2; const float* __restrict__ ur2 = J.ur2;
+    const uint8_t* __restrict__ has_mp2 = J.has_mp2; const uint32_t* __restrict__ indices2 = J.indices2;
+    const float* __restrict__ scale2 = J.scale2; const float* __restrict__ sigma2 = J.sigma2; int* __restrict__ result = J.result;
     const BowQuery B = Q[q];
     const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1);
     const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(desc1) + 2 * (size_t)B.idx1 + 1);
@@ -2018,8 +2030,9 @@ struct TriJob {
     std::vector<BowQuery> hq;
     TriCam C;
     int nq = 0;
-    size_t base = 0, bytes = 0, in_bytes = 0, up_bytes = 0;   // region inside the workspace; what is uploaded
-    size_t o_k1 = 0, o_d1 = 0, o_u1 = 0, o_k2 = 0, o_d2 = 0, o_u2 = 0, o_m2 = 0, o_i2 = 0, o_q = 0, o_sc = 0, o_sg = 0, o_m12 = 0;
+    size_t base = 0, in_bytes = 0;                   // the job's inputs inside the workspace: [base, base + in_bytes)
+    size_t out = 0;                                  // its results (one int per query) in the result area shared by all jobs
+    size_t o_k1 = 0, o_d1 = 0, o_u1 = 0, o_k2 = 0, o_d2 = 0, o_u2 = 0, o_m2 = 0, o_i2 = 0, o_q = 0, o_sc = 0, o_sg = 0;
 };
 
 // the merge walk over the two FeatureVectors, the epipole; lays the job's region out (inputs already validated)
@@ -2081,16 +2094,15 @@ static int tri_prepare(TriJob& J, int32_t* matches12, int* nmatches)
     if (!P.d_scale2) { J.o_sc = L.add(4 * (size_t)ORBGPU_MAX_LEVELS); J.o_sg = L.add(4 * (size_t)ORBGPU_MAX_LEVELS); }
     J.o_m2 = L.add((size_t)n2); J.o_q = L.add(sizeof(BowQuery) * (size_t)J.nq);
     J.in_bytes = L.off;
-    J.o_m12 = L.add(4 * (size_t)J.nq);                         // one result per query
-    J.up_bytes = std::max(J.in_bytes, SEARCH_MIN_UPLOAD);      // (the padding reads on into the job's own region)
-    J.bytes = std::max(L.off, J.up_bytes);
     return ORBGPU_OK;
 }
 
-// stage the inputs in the pinned mirror, upload, launch, download: all asynchronous on the workspace stream
-static int tri_enqueue(Workspace& W, const TriJob& J, int nlevels)
+// launch == false: stage the job's inputs in the pinned mirror (tri_run uploads the inputs of all jobs with one copy);
+// launch == true: the job's entry of the device job table (device pointers of its operands, results into the result area
+// shared by all jobs)
+static int tri_enqueue(Workspace& W, const TriJob& J, int nlevels, bool launch, TriJobDev* table)
 {
-    if (J.nq == 0) return ORBGPU_OK;
+    if (J.nq == 0) { if (launch) { memset(table, 0, sizeof(*table)); } return ORBGPU_OK; }
     const TriProblem& P = J.P;
     const SideView &s1 = P.s1, &s2 = P.s2;
     const int n1 = s1.n, n2 = s2.n;
@@ -2100,31 +2112,39 @@ static int tri_enqueue(Workspace& W, const TriJob& J, int nlevels)
     const uint8_t *d1 = s1.d_desc, *d2 = s2.d_desc;
     const uint32_t* i2 = s2.d_indices;
     if (!s1.resident()) {
-        memcpy(h + J.o_k1, s1.h_keys, sizeof(orbgpu_keypoint) * (size_t)n1);
-        memcpy(h + J.o_d1, s1.h_desc, 32 * (size_t)n1);
-        memcpy(h + J.o_u1, s1.u_right, 4 * (size_t)n1);
+        if (!launch) {
+            memcpy(h + J.o_k1, s1.h_keys, sizeof(orbgpu_keypoint) * (size_t)n1);
+            memcpy(h + J.o_d1, s1.h_desc, 32 * (size_t)n1);
+            memcpy(h + J.o_u1, s1.u_right, 4 * (size_t)n1);
+        }
         k1 = reinterpret_cast<const float*>(d + J.o_k1); d1 = d + J.o_d1; u1 = reinterpret_cast<const float*>(d + J.o_u1);
     }
     if (!s2.resident()) {
-        memcpy(h + J.o_k2, s2.h_keys, sizeof(orbgpu_keypoint) * (size_t)n2);
-        memcpy(h + J.o_d2, s2.h_desc, 32 * (size_t)n2);
-        memcpy(h + J.o_u2, s2.u_right, 4 * (size_t)n2);
-        memcpy(h + J.o_i2, s2.indices, 4 * (size_t)s2.nidx());
+        if (!launch) {
+            memcpy(h + J.o_k2, s2.h_keys, sizeof(orbgpu_keypoint) * (size_t)n2);
+            memcpy(h + J.o_d2, s2.h_desc, 32 * (size_t)n2);
+            memcpy(h + J.o_u2, s2.u_right, 4 * (size_t)n2);
+            memcpy(h + J.o_i2, s2.indices, 4 * (size_t)s2.nidx());
+        }
         k2 = reinterpret_cast<const float*>(d + J.o_k2); d2 = d + J.o_d2; u2 = reinterpret_cast<const float*>(d + J.o_u2);
         i2 = reinterpret_cast<const uint32_t*>(d + J.o_i2);
     }
     if (!P.d_scale2) {
-        memcpy(h + J.o_sc, P.h_scale2, 4 * (size_t)nlevels);
-        memcpy(h + J.o_sg, P.h_sigma2, 4 * (size_t)nlevels);
+        if (!launch) {
+            memcpy(h + J.o_sc, P.h_scale2, 4 * (size_t)nlevels);
+            memcpy(h + J.o_sg, P.h_sigma2, 4 * (size_t)nlevels);
+        }
         sc = reinterpret_cast<const float*>(d + J.o_sc); sg = reinterpret_cast<const float*>(d + J.o_sg);
     }
-    memcpy(h + J.o_m2, s2.flags, (size_t)n2);
-    memcpy(h + J.o_q, J.hq.data(), sizeof(BowQuery) * (size_t)J.nq);
-    CUS(cudaMemcpyAsync(d, h, J.up_bytes, cudaMemcpyHostToDevice, W.st));
-    k_tri_match<<<(J.nq + 7) / 8, 256, 0, W.st>>>(reinterpret_cast<const BowQuery*>(d + J.o_q), J.nq, J.C, k1, d1, u1, k2, d2, u2, d + J.o_m2,
-                                                  i2, sc, sg, reinterpret_cast<int*>(d + J.o_m12));
-    CUS(cudaGetLastError());
-    CUS(cudaMemcpyAsync(h + J.o_m12, d + J.o_m12, 4 * (size_t)J.nq, cudaMemcpyDeviceToHost, W.st));
+    if (!launch) {
+        memcpy(h + J.o_m2, s2.flags, (size_t)n2);
+        memcpy(h + J.o_q, J.hq.data(), sizeof(BowQuery) * (size_t)J.nq);
+        return ORBGPU_OK;
+    }
+    TriJobDev& T = *table;
+    T.Q = reinterpret_cast<const BowQuery*>(d + J.o_q); T.nq = J.nq; T.C = J.C;
+    T.keys1 = k1; T.desc1 = d1; T.ur1 = u1; T.keys2 = k2; T.desc2 = d2; T.ur2 = u2; T.has_mp2 = d + J.o_m2; T.indices2 = i2;
+    T.scale2 = sc; T.sigma2 = sg; T.result = reinterpret_cast<int*>(W.d + J.out);
     return ORBGPU_OK;
 }
 
@@ -2135,7 +2155,7 @@ static void tri_finish(const Workspace& W, const TriJob& J, int32_t* matches12, 
     const SideView &s1 = J.P.s1, &s2 = J.P.s2;
     const std::vector<BowQuery>& hq = J.hq;
     const int nq = J.nq;
-    const int* res = reinterpret_cast<const int*>(W.h + J.base + J.o_m12);       // matches12 is all -1 since tri_prepare
+    const int* res = reinterpret_cast<const int*>(W.h + J.out);                  // matches12 is all -1 since tri_prepare
     int nm = 0;
     for (int q = 0; q < nq; ++q) { matches12[hq[q].idx1] = res[q]; nm += res[q] >= 0; }
     if (J.P.check_orientation) {                               // :760-776, :794-813
@@ -2159,33 +2179,43 @@ static void tri_finish(const Workspace& W, const TriJob& J, int32_t* matches12, 
     *nmatches = nm;
 }
 
-// all jobs enqueued back to back on the calling thread's workspace stream, one wait; job p writes s1.n entries of
-// matches12 right after those of job p - 1
+// All jobs in ONE upload, one kernel each, ONE download and one wait (a copy costs ~10 us of latency on its own, whatever its
+// size: twenty jobs with their own copies spent most of their time in them).  Job p writes s1.n entries of matches12 right
+// after those of job p - 1.
 static int tri_run(int device, std::vector<TriJob>& jobs, const int* nlevels, int32_t* matches12, int* nmatches)
 {
     const size_t n_jobs = jobs.size();
     PhaseTrace tr("search_for_triangulation");
     std::vector<size_t> out_off(n_jobs);
-    size_t total = 0, out = 0;
+    size_t total_in = (sizeof(TriJobDev) * n_jobs + 255) & ~(size_t)255, out = 0, total_q = 0;      // the job table first
+    int max_q = 0;
     for (size_t p = 0; p < n_jobs; ++p) {
         TriJob& J = jobs[p];
         out_off[p] = out;
         const int rc = tri_prepare(J, matches12 + out, nmatches + p);
         if (rc != ORBGPU_OK) return rc;
         out += (size_t)J.P.s1.n;
-        J.base = total;
-        total += J.bytes;
+        J.base = total_in;
+        total_in += (J.in_bytes + 255) & ~(size_t)255;
+        total_q += (size_t)J.nq;
+        max_q = std::max(max_q, J.nq);
     }
-    if (total == 0) return ORBGPU_OK;
+    if (total_q == 0) return ORBGPU_OK;
+    const size_t up_bytes = std::max(total_in, SEARCH_MIN_UPLOAD);
+    size_t o = up_bytes;
+    for (size_t p = 0; p < n_jobs; ++p) { jobs[p].out = o; o += 4 * (size_t)jobs[p].nq; }
     tr.mark("walk");
     Workspace& W = g_ws;
-    int rc = W.reserve(device, total, total);
+    int rc = W.reserve(device, o, o);
     if (rc != ORBGPU_OK) return rc;
-    for (size_t p = 0; p < n_jobs; ++p) {
-        rc = tri_enqueue(W, jobs[p], nlevels[p]);
-        if (rc != ORBGPU_OK) { cudaStreamSynchronize(W.st); return rc; }
-    }
-    tr.mark("stage+enqueue");
+    TriJobDev* table = reinterpret_cast<TriJobDev*>(W.h);
+    for (size_t p = 0; p < n_jobs; ++p) { tri_enqueue(W, jobs[p], nlevels[p], false, nullptr); tri_enqueue(W, jobs[p], nlevels[p], true, table + p); }
+    tr.mark("stage");
+    CUS(cudaMemcpyAsync(W.d, W.h, up_bytes, cudaMemcpyHostToDevice, W.st));
+    k_tri_match<<<dim3((unsigned)((max_q + 7) / 8), (unsigned)n_jobs), 256, 0, W.st>>>(reinterpret_cast<const TriJobDev*>(W.d));
+    CUS(cudaGetLastError());
+    CUS(cudaMemcpyAsync(W.h + up_bytes, W.d + up_bytes, 4 * total_q, cudaMemcpyDeviceToHost, W.st));
+    tr.mark("enqueue");
     CUS(cudaStreamSynchronize(W.st));
     tr.mark("wait");
     for (size_t p = 0; p < n_jobs; ++p) tri_finish(W, jobs[p], matches12 + out_off[p], nmatches + p);
