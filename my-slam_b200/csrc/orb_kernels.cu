@@ -544,14 +544,19 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(OrbPlanDev P)
     uint32_t* slot = P.slots + (long long)frame * P.slot_frame_words + P.lv[l].slot_off + cell.slot_off;
     int cnt = 0;
 
+    int ncor = 0;
     for (int attempt = 0; attempt < 2; ++attempt) {
         const int th = attempt ? P.min_th : P.ini_th;
+#ifdef FAST_SKIP_REZERO
+        if (attempt == 0 || ncor > 0)                                       // a first attempt without a single corner left the map all zero
+#endif
         {
             uint4* z = reinterpret_cast<uint4*>(smap);                      // interior + NMS rim
             for (int i = lane; i < ((ih + 2) * spw + 15) >> 4; i += 32) z[i] = make_uint4(0, 0, 0, 0);
         }
         __syncwarp();
-        int head = 0, tail = 0, ncor = 0;
+        int head = 0, tail = 0;
+        ncor = 0;
 
         // scores 32 queued pixels with the arc network; corners go to the score map and the corner list
 #define FAST_DRAIN(active)                                                               \
