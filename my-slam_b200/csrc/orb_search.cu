@@ -12,12 +12,14 @@
 // ix * 48 + iy with the index order kept inside a cell (= the push_back order of AssignFeaturesToGrid); the cells
 // (ix, iyMin..iyMax) of one window column are then ONE contiguous range, so a window is nMaxCellX - nMinCellX + 1
 // ranges visited in the reference's order.  Three steps per call:
-//   k_grid_build        one CTA: cell ids, per-cell counts, exclusive scan, in-cell rank by index
-//   k_area_candidates   one warp per query: walks the window ranges, keeps order with ballot prefix sums, evaluates the
-//                       Hamming distance of every candidate and stores (index, distance) lists
-//   k_init_resolve / k_proj_resolve   one CTA stages lists + state in shared memory, then warp 0 walks the queries in index order and applies the reference's
-//                       order-dependent rules (vMatchedDistance / vnMatches21 stealing; mvpMapPoints occupancy) --
-//                       a true sequential dependence in the reference, kept as such
+//   k_grid_build        one CTA: cell ids, per-cell counts, exclusive scan, in-cell rank by index (also as the last block of
+//                       the kernels that compute the queries: it does not depend on them)
+//   k_area_candidates   one warp per query: walks the window's column ranges laid end to end, keeps order with ballot prefix
+//                       sums, evaluates the Hamming distance of every candidate and stores (index, distance) lists
+//   k_*_resolve         one CTA stages lists + state in shared memory and applies the reference's order-dependent rules
+//                       (mvpMapPoints occupancy: k_proj_resolve / k_local_resolve iterate the rule to its fixed point, all
+//                       queries at once; vMatchedDistance / vnMatches21 stealing: k_init_resolve walks the queries in
+//                       index order, 1..32 per pass) -- bit-exact with the sequential loops either way
 // The rotation histogram + ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) finish on the host, O(matches).
 #include <cuda_runtime.h>
 #include <limits.h>
